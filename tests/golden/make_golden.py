@@ -1,0 +1,214 @@
+"""Generate the golden fixtures under tests/golden/ FROM THE REFERENCE ITSELF.
+
+Run in the build container only (needs /root/reference and oracle/_ref built by
+`make -C oracle ref`):   python tests/golden/make_golden.py
+
+Sources of truth:
+  * Marlin format / quantiser / ScalarType ids: the reference's own Python files, loaded by path
+    (aphrodite/quantization/utils/{quant_utils,marlin_utils,marlin_utils_test}.py,
+    aphrodite/scalar_type.py) with stub modules for the unrelated imports they pull in.
+  * paged_attention_v1/v2 and reshape_and_cache: the UNMODIFIED reference CPU backend
+    (kernels/cpu/attention.cpp, kernels/cpu/cache.cpp) compiled into oracle/_ref.
+The fixtures are what travels to the GPU box; /root/reference does not.
+"""
+import importlib.util
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import synth  # noqa: E402
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF = "/root/reference"
+
+
+def _stub(name, **attrs):
+    m = types.ModuleType(name)
+    m.__dict__.update(attrs)
+    m.__path__ = []
+    sys.modules[name] = m
+    return m
+
+
+def _load(name, path):
+    spec = importlib.util.spec_from_file_location(name, path)
+    m = importlib.util.module_from_spec(spec)
+    sys.modules[name] = m
+    spec.loader.exec_module(m)
+    return m
+
+
+def load_reference_python():
+    _stub("aphrodite")
+    st = _load("aphrodite.scalar_type", f"{REF}/aphrodite/scalar_type.py")
+    _stub("aphrodite.common")
+    _stub("aphrodite.common.envs")
+    sys.modules["aphrodite.common"].envs = sys.modules["aphrodite.common.envs"]
+    _stub("aphrodite._custom_ops")
+    sys.modules["aphrodite"]._custom_ops = sys.modules["aphrodite._custom_ops"]
+    _stub("aphrodite.modeling")
+    _stub("aphrodite.modeling.layers")
+    _stub("aphrodite.modeling.layers.linear", LinearBase=object)
+    _stub("aphrodite.platforms", current_platform=None)
+    _stub("aphrodite.quantization")
+    _stub("aphrodite.quantization.qqq", MARLIN_QQQ_SUPPORTED_NUM_BITS=[4])
+    _stub("aphrodite.quantization.utils")
+    base = f"{REF}/aphrodite/quantization/utils"
+    qu = _load("aphrodite.quantization.utils.quant_utils", f"{base}/quant_utils.py")
+    mu = _load("aphrodite.quantization.utils.marlin_utils", f"{base}/marlin_utils.py")
+    mt = _load("aphrodite.quantization.utils.marlin_utils_test", f"{base}/marlin_utils_test.py")
+    return st, qu, mu, mt
+
+
+def raw(t: torch.Tensor) -> np.ndarray:
+    if t.dtype in (torch.bfloat16, torch.float16):
+        return t.contiguous().view(torch.int16).numpy()
+    return t.contiguous().numpy()
+
+
+def make_marlin(st, qu, mu, mt):
+    out = {}
+    ids = st.scalar_types
+    out["id_uint4"] = np.array([ids.uint4.id], dtype=np.int64)
+    out["id_uint4b8"] = np.array([ids.uint4b8.id], dtype=np.int64)
+    out["id_uint8"] = np.array([ids.uint8.id], dtype=np.int64)
+    out["id_uint8b128"] = np.array([ids.uint8b128.id], dtype=np.int64)
+    out["perm4"] = mt.get_weight_perm(4).numpy()
+    out["perm8"] = mt.get_weight_perm(8).numpy()
+    sp, sps = mu.get_scale_perms()
+    out["scale_perm"] = np.array(sp)
+    out["scale_perm_single"] = np.array(sps)
+    cases = []
+    g = torch.Generator().manual_seed(0)
+    # (K, N, bits, group, zero_points, dtype)
+    for ci, (k, n, bits, gs, zp, dt) in enumerate([
+        (128, 64, 4, 128, False, torch.bfloat16),
+        (256, 128, 4, 128, False, torch.bfloat16),
+        (256, 128, 4, -1, False, torch.float16),
+        (256, 64, 4, 32, False, torch.float16),
+        (128, 128, 8, 64, False, torch.float16),
+        (256, 128, 4, 128, True, torch.float16),
+        (128, 64, 8, -1, False, torch.bfloat16),
+        (256, 64, 4, 64, True, torch.bfloat16),
+    ]):
+        w = torch.randn(k, n, generator=g).to(dt)
+        if zp:
+            qt = ids.uint4 if bits == 4 else ids.uint8
+            w_ref, bq, s, bz = mt.awq_marlin_quantize(w, qt, gs)
+        else:
+            qt = ids.uint4b8 if bits == 4 else ids.uint8b128
+            w_ref, bq, s, _gi, _si, _rp = mt.marlin_quantize(w, qt, gs, False)
+            bz = None
+        pre = f"c{ci}_"
+        out[pre + "meta"] = np.array([k, n, bits, gs, int(zp), {torch.bfloat16: 2, torch.float16: 1}[dt]])
+        out[pre + "w"] = raw(w)
+        out[pre + "w_ref"] = raw(w_ref)
+        out[pre + "b_q_weight"] = bq.numpy()
+        out[pre + "b_scales"] = raw(s)
+        if bz is not None:
+            out[pre + "b_zeros"] = bz.numpy()
+        cases.append(ci)
+    out["num_cases"] = np.array([len(cases)])
+    np.savez_compressed(os.path.join(HERE, "marlin_golden.npz"), **out)
+    print("marlin_golden.npz:", len(out), "arrays")
+
+
+def load_refcpu():
+    flags = open("/proc/cpuinfo").read()
+    isa = "avx512bf16" if "avx512_bf16" in flags else ("avx512" if "avx512f" in flags else "avx2")
+    torch.ops.load_library(os.path.join(ROOT, "oracle", "_ref", f"refcpu_{isa}.so"))
+    return torch.ops._refcpu
+
+
+def make_attention(ref):
+    out = {}
+    g = torch.Generator().manual_seed(0)
+    # (S, H, KVH, D, max_len, dtype, alibi, version)
+    cases = [
+        (3, 8, 8, 64, 100, torch.bfloat16, False, 1),
+        (4, 8, 2, 128, 700, torch.bfloat16, False, 2),
+        (2, 4, 4, 128, 200, torch.float16, True, 1),
+        (3, 16, 2, 128, 1100, torch.float16, False, 2),
+        (2, 4, 1, 64, 50, torch.float32, False, 1),
+        (2, 12, 12, 64, 512, torch.bfloat16, False, 1),
+        (2, 8, 2, 256, 300, torch.bfloat16, True, 2),
+        (2, 6, 2, 96, 130, torch.float16, False, 1),
+    ]
+    bs = 16
+    for ci, (S, H, KVH, D, max_len, dt, alibi, ver) in enumerate(cases):
+        x = 16 // torch.tensor([], dtype=dt).element_size()
+        sl = torch.randint(1, max_len + 1, (S,), generator=g, dtype=torch.int32)
+        sl[-1] = max_len
+        mb = (max_len + bs - 1) // bs
+        nb = S * mb + 3
+        bt = torch.from_numpy(synth.permutation(nb, 100 + ci)[: S * mb].reshape(S, mb)).to(torch.int32)
+        sc = float(D) ** -0.5
+        q = synth.tensor((S, H, D), 200 + ci, dt, sc)
+        kc = synth.tensor((nb, KVH, D // x, bs, x), 300 + ci, dt, sc)
+        vc = synth.tensor((nb, KVH, D, bs), 400 + ci, dt, sc)
+        slopes = torch.randn(H, generator=g).float() if alibi else None
+        o = torch.empty_like(q)
+        one = torch.tensor(1.0)
+        if ver == 1:
+            ref.paged_attention_v1(o, q, kc, vc, KVH, sc, bt, sl, bs, max_len, slopes, "auto", one, one,
+                                   0, 0, 0, 64, 0)
+        else:
+            P = (max_len + 511) // 512
+            es = torch.empty(S, H, P)
+            ml = torch.empty(S, H, P)
+            tmp = torch.empty(S, H, P, D, dtype=dt)
+            ref.paged_attention_v2(o, es, ml, tmp, q, kc, vc, KVH, sc, bt, sl, bs, max_len, slopes, "auto",
+                                   one, one, 0, 0, 0, 64, 0)
+        pre = f"a{ci}_"
+        out[pre + "meta"] = np.array([S, H, KVH, D, max_len, {torch.float32: 0, torch.float16: 1,
+                                                               torch.bfloat16: 2}[dt], int(alibi), ver, nb])
+        out[pre + "seq_lens"] = sl.numpy()
+        out[pre + "block_tables"] = bt.numpy()
+        if alibi:
+            out[pre + "alibi"] = slopes.numpy()
+        out[pre + "out"] = raw(o)
+    out["num_cases"] = np.array([len(cases)])
+    np.savez_compressed(os.path.join(HERE, "attention_golden.npz"), **out)
+    print("attention_golden.npz:", len(out), "arrays")
+
+
+def make_cache(ref):
+    out = {}
+    g = torch.Generator().manual_seed(0)
+    cases = [(42, 8, 64, 16, 8, torch.bfloat16), (42, 4, 128, 16, 4, torch.float32),
+             (17, 2, 80, 16, 4, torch.float32), (9, 2, 256, 16, 2, torch.bfloat16)]
+    for ci, (T, KVH, D, bs, nb, dt) in enumerate(cases):
+        x = 16 // torch.tensor([], dtype=dt).element_size()
+        qkv = synth.tensor((T, 3, KVH, D), 500 + ci, dt, 2.0)
+        key, value = qkv[:, 1], qkv[:, 2]
+        slots = torch.from_numpy(synth.permutation(nb * bs, 600 + ci)[:T]).to(torch.int64)
+        slots[T // 2] = -1
+        kc = synth.tensor((nb, KVH, D // x, bs, x), 700 + ci, dt, 2.0)
+        vc = synth.tensor((nb, KVH, D, bs), 800 + ci, dt, 2.0)
+        kc0, vc0 = kc.clone(), vc.clone()
+        one = torch.tensor(1.0)
+        ref.reshape_and_cache(key, value, kc, vc, slots, "auto", one, one)
+        pre = f"r{ci}_"
+        out[pre + "meta"] = np.array([T, KVH, D, bs, nb, {torch.float32: 0, torch.float16: 1,
+                                                           torch.bfloat16: 2}[dt]])
+        out[pre + "slots"] = slots.numpy()
+        # only the touched blocks change; store the whole result (small pools)
+        out[pre + "kc1"] = raw(kc)
+        out[pre + "vc1"] = raw(vc)
+    out["num_cases"] = np.array([len(cases)])
+    np.savez_compressed(os.path.join(HERE, "cache_golden.npz"), **out)
+    print("cache_golden.npz:", len(out), "arrays")
+
+
+if __name__ == "__main__":
+    torch.manual_seed(0)
+    mods = load_reference_python()
+    make_marlin(*mods)
+    ref = load_refcpu()
+    make_attention(ref)
+    make_cache(ref)

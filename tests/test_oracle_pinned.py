@@ -1,0 +1,140 @@
+"""Pins the oracle (oracle/) against the reference: golden vectors generated from the reference's
+own Python code and from its unmodified CPU backend (tests/golden/make_golden.py), and - when
+oracle/_ref is present - against the reference CPU backend run live."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import synth
+from oracle import marlin_format as mf
+from oracle import oracle
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+DT = {0: torch.float32, 1: torch.float16, 2: torch.bfloat16}
+
+
+def _t(a, dt):
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    return t.view(dt) if dt in (torch.float16, torch.bfloat16) else t
+
+
+def test_scalar_type_ids_and_perms():
+    g = np.load(os.path.join(G, "marlin_golden.npz"))
+    assert mf.UINT4 == int(g["id_uint4"][0]) and mf.UINT4B8 == int(g["id_uint4b8"][0])
+    assert mf.UINT8 == int(g["id_uint8"][0]) and mf.UINT8B128 == int(g["id_uint8b128"][0])
+    assert mf.UINT4B8 == 1125899907892224
+    assert np.array_equal(mf.weight_perm(4), g["perm4"])
+    assert np.array_equal(mf.weight_perm(8), g["perm8"])
+    sp, sps = mf._scale_perms()
+    assert np.array_equal(sp, g["scale_perm"]) and np.array_equal(sps, g["scale_perm_single"])
+
+
+def test_marlin_quantize_matches_reference_python():
+    g = np.load(os.path.join(G, "marlin_golden.npz"))
+    for ci in range(int(g["num_cases"][0])):
+        k, n, bits, gs, zp, dtc = [int(v) for v in g[f"c{ci}_meta"]]
+        dt = DT[dtc]
+        w = _t(g[f"c{ci}_w"], dt)
+        w_ref, b, s, bz = mf.marlin_quantize(w, bits, gs, bool(zp))
+        assert torch.equal(w_ref.view(torch.int16), _t(g[f"c{ci}_w_ref"], dt).view(torch.int16)), ci
+        assert np.array_equal(b.numpy(), g[f"c{ci}_b_q_weight"]), ci
+        assert np.array_equal(s.view(torch.int16).numpy(), g[f"c{ci}_b_scales"]), ci
+        if zp:
+            assert np.array_equal(bz.numpy(), g[f"c{ci}_b_zeros"]), ci
+        # the inverse maps decode the reference's tensors back to the reference's w_ref
+        back = mf.dequantize(torch.from_numpy(g[f"c{ci}_b_q_weight"]), _t(g[f"c{ci}_b_scales"], dt),
+                             torch.from_numpy(g[f"c{ci}_b_zeros"]) if zp else None, k, n, bits, gs, bool(zp))
+        assert torch.equal(back.view(torch.int16), _t(g[f"c{ci}_w_ref"], dt).view(torch.int16)), ci
+
+
+def _attn_case(g, ci):
+    S, H, KVH, D, max_len, dtc, alibi, ver, nb = [int(v) for v in g[f"a{ci}_meta"]]
+    dt = DT[dtc]
+    x = 16 // torch.tensor([], dtype=dt).element_size()
+    sc = float(D) ** -0.5
+    q = synth.tensor((S, H, D), 200 + ci, dt, sc)
+    kc = synth.tensor((nb, KVH, D // x, 16, x), 300 + ci, dt, sc)
+    vc = synth.tensor((nb, KVH, D, 16), 400 + ci, dt, sc)
+    sl = torch.from_numpy(g[f"a{ci}_seq_lens"])
+    bt = torch.from_numpy(g[f"a{ci}_block_tables"])
+    al = torch.from_numpy(g[f"a{ci}_alibi"]) if alibi else None
+    ref = _t(g[f"a{ci}_out"], dt)
+    return dict(S=S, H=H, KVH=KVH, D=D, max_len=max_len, dt=dt, ver=ver, q=q, kc=kc, vc=vc, sl=sl, bt=bt,
+                al=al, ref=ref, sc=sc)
+
+
+def test_attention_oracle_vs_reference_cpu_golden():
+    g = np.load(os.path.join(G, "attention_golden.npz"))
+    for ci in range(int(g["num_cases"][0])):
+        c = _attn_case(g, ci)
+        o64, o = oracle.paged_attention(c["q"], c["kc"], c["vc"], c["KVH"], c["sc"], c["bt"], c["sl"], 16,
+                                        alibi_slopes=c["al"])
+        ref = c["ref"].double()
+        # the reference CPU backend accumulates in fp32 and rounds once to the scalar dtype;
+        # reference test tolerance: atol 1e-3 (tests/kernels/test_attention.py:323-326) + dtype rtol
+        rtol = {torch.float32: 1.3e-6, torch.float16: 1e-3, torch.bfloat16: 1.6e-2}[c["dt"]]
+        err = (o64 - ref).abs()
+        assert bool((err <= 1e-3 + rtol * ref.abs()).all()), (ci, float(err.max()))
+
+
+def test_cache_oracle_vs_reference_cpu_golden():
+    g = np.load(os.path.join(G, "cache_golden.npz"))
+    for ci in range(int(g["num_cases"][0])):
+        T, KVH, D, bs, nb, dtc = [int(v) for v in g[f"r{ci}_meta"]]
+        dt = DT[dtc]
+        x = 16 // torch.tensor([], dtype=dt).element_size()
+        qkv = synth.tensor((T, 3, KVH, D), 500 + ci, dt, 2.0)
+        slots = torch.from_numpy(g[f"r{ci}_slots"])
+        kc = synth.tensor((nb, KVH, D // x, bs, x), 700 + ci, dt, 2.0)
+        vc = synth.tensor((nb, KVH, D, bs), 800 + ci, dt, 2.0)
+        oracle.reshape_and_cache(qkv[:, 1], qkv[:, 2], kc, vc, slots, "auto", 1.0, 1.0)
+        i = torch.int16 if dt != torch.float32 else torch.int32
+        assert torch.equal(kc.view(i), _t(g[f"r{ci}_kc1"], dt).view(i)), ci
+        assert torch.equal(vc.view(i), _t(g[f"r{ci}_vc1"], dt).view(i)), ci
+
+
+@pytest.mark.skipif(oracle.refcpu() is None, reason="oracle/_ref not built")
+def test_oracle_vs_live_reference_cpu():
+    ref = oracle.refcpu()
+    S, H, KVH, D, L = 3, 8, 2, 128, 333
+    dt = torch.bfloat16
+    sc = D ** -0.5
+    nb = S * 21 + 1
+    q = synth.tensor((S, H, D), 1, dt, sc)
+    kc = synth.tensor((nb, KVH, D // 8, 16, 8), 2, dt, sc)
+    vc = synth.tensor((nb, KVH, D, 16), 3, dt, sc)
+    bt = torch.from_numpy(synth.permutation(nb, 4)[: S * 21].reshape(S, 21)).to(torch.int32)
+    sl = torch.tensor([17, 200, L], dtype=torch.int32)
+    o = torch.empty_like(q)
+    one = torch.tensor(1.0)
+    ref.paged_attention_v1(o, q, kc, vc, KVH, sc, bt, sl, 16, L, None, "auto", one, one, 0, 0, 0, 64, 0)
+    o64, _ = oracle.paged_attention(q, kc, vc, KVH, sc, bt, sl, 16)
+    assert float((o64 - o.double()).abs().max()) < 1e-3
+
+
+def test_fp8_codec_known_answers():
+    # E4M3: 448 is the max finite; saturate-to-finite; 1.0 = 0x38; E5M2: 1.0 = 0x3C, max 57344
+    x = torch.tensor([0.0, 1.0, -1.0, 448.0, 1e6, -1e6, 2.0 ** -9, 0.3], dtype=torch.float32)
+    e4 = oracle.fp8_encode(x, 1.0, "fp8_e4m3")
+    assert e4.tolist()[:7] == [0x00, 0x38, 0xB8, 0x7E, 0x7E, 0xFE, 0x01]
+    e5 = oracle.fp8_encode(x, 1.0, "fp8_e5m2")
+    assert e5.tolist()[:3] == [0x00, 0x3C, 0xBC] and e5.tolist()[4] == 0x7B
+    # every byte decodes and re-encodes to itself (idempotence; NaN codes excluded)
+    allb = torch.arange(256, dtype=torch.uint8)
+    for kv, nan in (("fp8_e4m3", {0x7F, 0xFF}), ("fp8_e5m2", set(range(0x7C, 0x80)) | set(range(0xFC, 0x100)))):
+        dec = oracle.fp8_decode(allb, torch.float32, 1.0, kv)
+        re = oracle.fp8_encode(dec, 1.0, kv)
+        ok = [int(re[i]) == i for i in range(256) if i not in nan]
+        assert all(ok), kv
+    # scaled: encode(x, s) == encode(x / s, 1)
+    y = synth.tensor((1000,), 9, torch.bfloat16, 3.0)
+    assert torch.equal(oracle.fp8_encode(y, 0.05, "fp8"), oracle.fp8_encode((y.float() / 0.05), 1.0, "fp8"))
+
+
+def test_gemm_oracle():
+    a = synth.tensor((5, 64), 11, torch.bfloat16, 1.0)
+    w = synth.tensor((64, 32), 12, torch.bfloat16, 1.0)
+    c = oracle.gemm(a, w)
+    assert torch.allclose(c, a.double() @ w.double(), atol=1e-12)
