@@ -1,0 +1,116 @@
+"""Host-side mirror of the reference's Python op wrappers for the decode hot path.
+
+Same names, argument order, defaults and error behaviour as
+/root/reference/aphrodite/_custom_ops.py:65-123 (paged attention), :909-929 (gptq_marlin_gemm),
+:1444-1456 (reshape_and_cache), :1504-1508 (convert_fp8); they resolve `torch.ops._C.*` lazily at
+call time, so inside a live Aphrodite the reference's own wrappers reach the same kernels.
+"""
+from __future__ import annotations
+
+from typing import Optional, Union
+
+import torch
+
+from ._loader import load
+
+
+def _ops():
+    load()
+    return torch.ops._C, torch.ops._C_cache_ops
+
+
+def paged_attention_v1(
+    out: torch.Tensor,
+    query: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    num_kv_heads: int,
+    scale: float,
+    block_tables: torch.Tensor,
+    seq_lens: torch.Tensor,
+    block_size: int,
+    max_seq_len: int,
+    alibi_slopes: Optional[torch.Tensor],
+    kv_cache_dtype: str,
+    k_scale: torch.Tensor,
+    v_scale: torch.Tensor,
+    tp_rank: int = 0,
+    blocksparse_local_blocks: int = 0,
+    blocksparse_vert_stride: int = 0,
+    blocksparse_block_size: int = 64,
+    blocksparse_head_sliding_step: int = 0,
+) -> None:
+    _ops()[0].paged_attention_v1(out, query, key_cache, value_cache, num_kv_heads, scale, block_tables, seq_lens,
+                                 block_size, max_seq_len, alibi_slopes, kv_cache_dtype, k_scale, v_scale, tp_rank,
+                                 blocksparse_local_blocks, blocksparse_vert_stride, blocksparse_block_size,
+                                 blocksparse_head_sliding_step)
+
+
+def paged_attention_v2(
+    out: torch.Tensor,
+    exp_sum: torch.Tensor,
+    max_logits: torch.Tensor,
+    tmp_out: torch.Tensor,
+    query: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    num_kv_heads: int,
+    scale: float,
+    block_tables: torch.Tensor,
+    seq_lens: torch.Tensor,
+    block_size: int,
+    max_seq_len: int,
+    alibi_slopes: Optional[torch.Tensor],
+    kv_cache_dtype: str,
+    k_scale: torch.Tensor,
+    v_scale: torch.Tensor,
+    tp_rank: int = 0,
+    blocksparse_local_blocks: int = 0,
+    blocksparse_vert_stride: int = 0,
+    blocksparse_block_size: int = 64,
+    blocksparse_head_sliding_step: int = 0,
+) -> None:
+    _ops()[0].paged_attention_v2(out, exp_sum, max_logits, tmp_out, query, key_cache, value_cache, num_kv_heads,
+                                 scale, block_tables, seq_lens, block_size, max_seq_len, alibi_slopes,
+                                 kv_cache_dtype, k_scale, v_scale, tp_rank, blocksparse_local_blocks,
+                                 blocksparse_vert_stride, blocksparse_block_size, blocksparse_head_sliding_step)
+
+
+def reshape_and_cache(
+    key: torch.Tensor,
+    value: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    slot_mapping: torch.Tensor,
+    kv_cache_dtype: str,
+    k_scale: torch.Tensor,
+    v_scale: torch.Tensor,
+) -> None:
+    _ops()[1].reshape_and_cache(key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype, k_scale, v_scale)
+
+
+def convert_fp8(output: torch.Tensor, input: torch.Tensor, scale: float = 1.0, kv_dtype: str = "fp8") -> None:
+    _ops()[1].convert_fp8(output, input, scale, kv_dtype)
+
+
+def gptq_marlin_gemm(a: torch.Tensor,
+                     b_q_weight: torch.Tensor,
+                     b_scales: torch.Tensor,
+                     b_zeros: torch.Tensor,
+                     g_idx: torch.Tensor,
+                     perm: torch.Tensor,
+                     workspace: torch.Tensor,
+                     b_q_type: Union[int, "object"],
+                     size_m: int,
+                     size_n: int,
+                     size_k: int,
+                     is_k_full: bool,
+                     has_zp: bool = False,
+                     use_atomic_add: bool = False,
+                     use_fp32_reduce: bool = False,
+                     is_zp_float: bool = False) -> torch.Tensor:
+    # the reference passes a ScalarType and forwards `.id`; plain ints are accepted too
+    type_id = b_q_type.id if hasattr(b_q_type, "id") else int(b_q_type)
+    return _ops()[0].gptq_marlin_gemm(a, b_q_weight, b_scales, b_zeros, g_idx, perm, workspace, type_id, size_m,
+                                      size_n, size_k, is_k_full, has_zp, use_atomic_add, use_fp32_reduce,
+                                      is_zp_float)

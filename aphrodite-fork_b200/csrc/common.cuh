@@ -1,0 +1,71 @@
+// Shared helpers for the sm_100a kernels behind include/aphrodite_b200.h.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_fp8.h>
+#include <cuda_runtime.h>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+
+#include "../../include/aphrodite_b200.h"
+
+namespace aphb200 {
+
+// Thread-local error text behind aph_b200_last_error().
+char* error_buffer();
+int set_error(int code, const char* fmt, ...);
+
+#define APH_CHECK(cond, code, ...)                        \
+  do {                                                    \
+    if (!(cond)) return ::aphb200::set_error(code, __VA_ARGS__); \
+  } while (0)
+
+#define APH_LAUNCH_CHECK()                                                               \
+  do {                                                                                   \
+    cudaError_t e__ = cudaGetLastError();                                                \
+    if (e__ != cudaSuccess)                                                              \
+      return ::aphb200::set_error(APH_ERR_CUDA, "CUDA launch failed: %s", cudaGetErrorString(e__)); \
+  } while (0)
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// Number of SMs of the current device (cached per device; cudaDeviceGetAttribute is not
+// free and the reference pays it on every GEMM call, gptq_marlin.cu:2104-2110).
+int sm_count();
+
+template <typename T>
+struct ScalarTraits;
+template <>
+struct ScalarTraits<float> {
+  static __device__ __forceinline__ float to_float(float v) { return v; }
+  static __device__ __forceinline__ float from_float(float v) { return v; }
+};
+template <>
+struct ScalarTraits<__half> {
+  static __device__ __forceinline__ float to_float(__half v) { return __half2float(v); }
+  static __device__ __forceinline__ __half from_float(float v) { return __float2half_rn(v); }
+};
+template <>
+struct ScalarTraits<__nv_bfloat16> {
+  static __device__ __forceinline__ float to_float(__nv_bfloat16 v) { return __bfloat162float(v); }
+  static __device__ __forceinline__ __nv_bfloat16 from_float(float v) { return __float2bfloat16_rn(v); }
+};
+
+// FP8 write codec, identical to the reference's
+// __nv_cvt_float_to_fp8(float(x) / scale, __NV_SATFINITE, kind)
+// (kernels/quantization/fp8/nvidia/quant_utils.cuh:457-489): true IEEE division, RN-even,
+// saturate-to-finite. Never compile this file with --use_fast_math.
+template <int KV>
+__device__ __forceinline__ uint8_t fp8_encode(float x, float scale) {
+  return (uint8_t)__nv_cvt_float_to_fp8(__fdiv_rn(x, scale), __NV_SATFINITE,
+                                        KV == APH_KV_FP8_E5M2 ? __NV_E5M2 : __NV_E4M3);
+}
+// FP8 read codec: fp8 -> half (exact) -> float (quant_utils.cuh:295-300,348-359 before scaling).
+template <int KV>
+__device__ __forceinline__ float fp8_decode(uint8_t b) {
+  __half_raw r = __nv_cvt_fp8_to_halfraw((__nv_fp8_storage_t)b, KV == APH_KV_FP8_E5M2 ? __NV_E5M2 : __NV_E4M3);
+  return __half2float(__half(r));
+}
+
+}  // namespace aphb200

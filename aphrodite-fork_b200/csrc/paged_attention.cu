@@ -1,0 +1,171 @@
+// Host entry points aph_paged_attention_v1 / _v2: argument checks (the reference's TORCH_CHECKs,
+// paged_attention_v1.cu:100-168), split-K partition choice and dispatch to the per-head-size
+// translation units (paged_attention_inst.cu).
+#include "paged_attention.cuh"
+
+namespace aphb200 {
+namespace pa {
+
+#define APH_DECL(D) int launch_pa_d##D(const Params& p, int dtype, int kv_dtype, int block_size, cudaStream_t stream);
+APH_DECL(64)
+APH_DECL(128)
+#ifndef APH_FAST_BUILD
+APH_DECL(32)
+APH_DECL(80)
+APH_DECL(96)
+APH_DECL(112)
+APH_DECL(192)
+APH_DECL(256)
+#endif
+#undef APH_DECL
+
+struct Split {
+  int partition_tokens;
+  int num_partitions;
+};
+
+// Partition choice: enough CTAs for >= 4 waves at 3 CTAs/SM, partitions of >= 256 tokens
+// (multiple of 256 so that they start on stage and page boundaries for every block size).
+static Split choose_split(int num_seqs, int num_heads, int num_kv_heads, int max_seq_len) {
+  const int G = num_heads / num_kv_heads;
+  const int tiles = (G + HEADS_PER_CTA - 1) / HEADS_PER_CTA;
+  const int64_t units = (int64_t)num_seqs * num_kv_heads * tiles;
+  const int64_t target = (int64_t)sm_count() * 3 * 4;
+  int64_t p_want = units > 0 ? (target + units - 1) / units : 1;
+  if (p_want < 1) p_want = 1;
+  int msl = max_seq_len < 1 ? 1 : max_seq_len;
+  int64_t pt = (msl + p_want - 1) / p_want;
+  pt = ((pt + 255) / 256) * 256;
+  Split s;
+  s.partition_tokens = (int)pt;
+  s.num_partitions = (int)((msl + pt - 1) / pt);
+  return s;
+}
+
+static int run(void* out, const void* query, const void* key_cache, const void* value_cache, int num_seqs,
+               int num_heads, int num_kv_heads, int head_size, float scale, const int32_t* block_tables,
+               const int32_t* seq_lens, int block_size, int max_seq_len, int max_num_blocks_per_seq,
+               const float* alibi_slopes, int64_t q_stride, int64_t out_stride, int64_t kv_block_stride,
+               int64_t kv_head_stride, int dtype, int kv_dtype, const float* k_scale, const float* v_scale,
+               int tp_rank, int bs_local_blocks, int bs_vert_stride, int bs_block_size, int bs_head_sliding_step,
+               void* workspace, size_t workspace_bytes, void* stream) {
+  APH_CHECK(num_seqs >= 0 && num_heads > 0 && num_kv_heads > 0 && head_size > 0, APH_ERR_INVALID_ARGUMENT,
+            "paged_attention: bad sizes");
+  APH_CHECK(num_heads % num_kv_heads == 0, APH_ERR_INVALID_ARGUMENT,
+            "paged_attention: num_heads %d not a multiple of num_kv_heads %d", num_heads, num_kv_heads);
+  APH_CHECK(kv_dtype == APH_KV_AUTO || (k_scale && v_scale), APH_ERR_INVALID_ARGUMENT,
+            "paged_attention: fp8 kv cache needs k_scale and v_scale");
+  const int esz = kv_dtype == APH_KV_AUTO ? (dtype == APH_DT_F32 ? 4 : 2) : 1;
+  APH_CHECK(aligned16(key_cache) && aligned16(value_cache) && (kv_block_stride * esz) % 16 == 0 &&
+                (kv_head_stride * esz) % 16 == 0,
+            APH_ERR_INVALID_ARGUMENT, "paged_attention: kv cache pages must be 16-byte aligned");
+  APH_CHECK(kv_head_stride == (int64_t)head_size * block_size, APH_ERR_INVALID_ARGUMENT,
+            "paged_attention: kv cache must be contiguous within a (block, head) page");
+  if (bs_vert_stride > 1)
+    APH_CHECK(bs_block_size > 0, APH_ERR_INVALID_ARGUMENT, "paged_attention: blocksparse_block_size must be > 0");
+  if (num_seqs == 0) return APH_OK;
+
+  const Split sp = choose_split(num_seqs, num_heads, num_kv_heads, max_seq_len);
+  Params p;
+  p.out = out;
+  p.q = query;
+  p.k_cache = key_cache;
+  p.v_cache = value_cache;
+  p.block_tables = block_tables;
+  p.seq_lens = seq_lens;
+  p.alibi_slopes = alibi_slopes;
+  p.k_scale = k_scale;
+  p.v_scale = v_scale;
+  p.num_seqs = num_seqs;
+  p.num_heads = num_heads;
+  p.num_kv_heads = num_kv_heads;
+  p.max_blocks_per_seq = max_num_blocks_per_seq;
+  p.partition_tokens = sp.partition_tokens;
+  p.num_partitions = sp.num_partitions;
+  p.q_stride = q_stride;
+  p.out_stride = out_stride;
+  p.kv_block_stride = kv_block_stride;
+  p.kv_head_stride = kv_head_stride;
+  p.scale = scale;
+  p.tp_rank = tp_rank;
+  p.bs_local_blocks = bs_local_blocks;
+  p.bs_vert_stride = bs_vert_stride;
+  p.bs_block_size = bs_block_size;
+  p.bs_head_sliding_step = bs_head_sliding_step;
+  p.part_o = nullptr;
+  p.part_ml = nullptr;
+  if (sp.num_partitions > 1) {
+    const size_t n_o = (size_t)num_seqs * num_heads * sp.num_partitions * head_size;
+    const size_t need = n_o * 4 + (size_t)num_seqs * num_heads * sp.num_partitions * 8;
+    APH_CHECK(workspace != nullptr && workspace_bytes >= need && aligned16(workspace), APH_ERR_WORKSPACE,
+              "paged_attention: workspace of %zu bytes needed, %zu given", need, workspace_bytes);
+    p.part_o = (float*)workspace;
+    p.part_ml = (float*)workspace + n_o;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  switch (head_size) {
+    case 64: return launch_pa_d64(p, dtype, kv_dtype, block_size, s);
+    case 128: return launch_pa_d128(p, dtype, kv_dtype, block_size, s);
+#ifndef APH_FAST_BUILD
+    case 32: return launch_pa_d32(p, dtype, kv_dtype, block_size, s);
+    case 80: return launch_pa_d80(p, dtype, kv_dtype, block_size, s);
+    case 96: return launch_pa_d96(p, dtype, kv_dtype, block_size, s);
+    case 112: return launch_pa_d112(p, dtype, kv_dtype, block_size, s);
+    case 192: return launch_pa_d192(p, dtype, kv_dtype, block_size, s);
+    case 256: return launch_pa_d256(p, dtype, kv_dtype, block_size, s);
+#endif
+    default: return set_error(APH_ERR_INVALID_ARGUMENT, "Unsupported head size: %d", head_size);
+  }
+}
+
+}  // namespace pa
+}  // namespace aphb200
+
+using namespace aphb200;
+
+extern "C" size_t aph_paged_attention_workspace_bytes(int num_seqs, int num_heads, int num_kv_heads, int head_size,
+                                                      int max_seq_len) {
+  if (num_seqs <= 0 || num_heads <= 0 || num_kv_heads <= 0 || head_size <= 0) return 0;
+  const pa::Split sp = pa::choose_split(num_seqs, num_heads, num_kv_heads, max_seq_len);
+  if (sp.num_partitions <= 1) return 0;
+  const size_t n = (size_t)num_seqs * num_heads * sp.num_partitions;
+  return n * head_size * 4 + n * 8;
+}
+
+extern "C" int aph_paged_attention_v1(void* out, const void* query, const void* key_cache, const void* value_cache,
+                                      int num_seqs, int num_heads, int num_kv_heads, int head_size, float scale,
+                                      const int32_t* block_tables, const int32_t* seq_lens, int block_size,
+                                      int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes,
+                                      int64_t q_stride, int64_t out_stride, int64_t kv_block_stride,
+                                      int64_t kv_head_stride, int dtype, int kv_dtype, const float* k_scale,
+                                      const float* v_scale, int tp_rank, int blocksparse_local_blocks,
+                                      int blocksparse_vert_stride, int blocksparse_block_size,
+                                      int blocksparse_head_sliding_step, void* workspace, size_t workspace_bytes,
+                                      void* stream) {
+  return pa::run(out, query, key_cache, value_cache, num_seqs, num_heads, num_kv_heads, head_size, scale,
+                 block_tables, seq_lens, block_size, max_seq_len, max_num_blocks_per_seq, alibi_slopes, q_stride,
+                 out_stride, kv_block_stride, kv_head_stride, dtype, kv_dtype, k_scale, v_scale, tp_rank,
+                 blocksparse_local_blocks, blocksparse_vert_stride, blocksparse_block_size,
+                 blocksparse_head_sliding_step, workspace, workspace_bytes, stream);
+}
+
+extern "C" int aph_paged_attention_v2(void* out, float* exp_sums, float* max_logits, void* tmp_out,
+                                      const void* query, const void* key_cache, const void* value_cache,
+                                      int num_seqs, int num_heads, int num_kv_heads, int head_size, float scale,
+                                      const int32_t* block_tables, const int32_t* seq_lens, int block_size,
+                                      int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes,
+                                      int64_t q_stride, int64_t out_stride, int64_t kv_block_stride,
+                                      int64_t kv_head_stride, int dtype, int kv_dtype, const float* k_scale,
+                                      const float* v_scale, int tp_rank, int blocksparse_local_blocks,
+                                      int blocksparse_vert_stride, int blocksparse_block_size,
+                                      int blocksparse_head_sliding_step, void* workspace, size_t workspace_bytes,
+                                      void* stream) {
+  (void)exp_sums;
+  (void)max_logits;
+  (void)tmp_out;  // sized for 512-token partitions by the caller; this implementation partitions differently
+  return pa::run(out, query, key_cache, value_cache, num_seqs, num_heads, num_kv_heads, head_size, scale,
+                 block_tables, seq_lens, block_size, max_seq_len, max_num_blocks_per_seq, alibi_slopes, q_stride,
+                 out_stride, kv_block_stride, kv_head_stride, dtype, kv_dtype, k_scale, v_scale, tp_rank,
+                 blocksparse_local_blocks, blocksparse_vert_stride, blocksparse_block_size,
+                 blocksparse_head_sliding_step, workspace, workspace_bytes, stream);
+}

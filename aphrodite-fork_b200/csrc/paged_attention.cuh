@@ -1,0 +1,149 @@
+// Paged single-query (decode) attention for sm_100a: GQA-packed split-K kernel + reduce.
+//
+// Replaces /root/reference/kernels/attention/attention_kernels.cuh:86-495 (main kernel) and
+// :563-668 (v2 reduce). Same inputs, same result within the stated tolerance; different design:
+//
+//   * one CTA per (sequence, kv head [x tile of 8 q heads], partition): all q heads that share
+//     a kv head are packed into one MMA operand, so every KV byte is fetched from HBM once
+//     (the reference launches one CTA per q head and re-reads each kv head G times);
+//   * KV pages are streamed by cp.async.bulk (1-D TMA bulk copy, SASS UBLKCP) straight from
+//     the paged cache layout into a per-warp ring of shared-memory stages, completion tracked
+//     by mbarriers - no register staging, no CTA-wide barriers in the main loop;
+//   * S^T = K Q^T and O^T = V^T P^T run on mma.sync.m16n8k16 with TOKENS as the M dimension
+//     and the 8 packed q heads as N, so no tensor-core work is wasted on head padding and the
+//     cache layouts ([D/x][bs][x] for K, [D][bs] for V) are exactly the row-major A operands;
+//   * FP8 KV is converted in registers (cvt.rn.f16x2.e4m3x2 / e5m2x2, exact) and fed to f16
+//     MMAs; k_scale is folded into the logit scale and v_scale into the output;
+//   * online softmax in the exp2 domain with warp-shuffle max/sum reductions, one pass over KV
+//     (the reference makes two sweeps and round-trips logits through shared memory);
+//   * the split-K partition size is chosen from the problem size, partials are fp32.
+#pragma once
+#include "common.cuh"
+
+namespace aphb200 {
+namespace pa {
+
+constexpr int NW = 4;            // warps per CTA
+constexpr int THREADS = NW * 32;
+constexpr int HEADS_PER_CTA = 8;  // q heads packed into the MMA N dimension
+constexpr float LOG2E = 1.4426950408889634f;
+
+struct Params {
+  void* out;                 // [S, H, D] scalar
+  const void* q;             // [S, H, D] scalar
+  const void* k_cache;
+  const void* v_cache;
+  const int32_t* block_tables;
+  const int32_t* seq_lens;
+  const float* alibi_slopes;  // [H] or null
+  const float* k_scale;       // device scalars (fp8 only)
+  const float* v_scale;
+  float* part_o;              // [S, H, P, D] fp32 partial numerators
+  float* part_ml;             // [S, H, P, 2] (max in log2 domain, sum)
+  int num_seqs, num_heads, num_kv_heads;
+  int max_blocks_per_seq;
+  int partition_tokens;       // tokens per partition (multiple of the stage size)
+  int num_partitions;
+  int64_t q_stride, out_stride, kv_block_stride, kv_head_stride;  // elements
+  float scale;
+  int tp_rank, bs_local_blocks, bs_vert_stride, bs_block_size, bs_head_sliding_step;
+};
+
+// ---------------------------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "DONE:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+// 1-D bulk async copy global -> shared, completion counted in bytes on an mbarrier.
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+               : "r"(addr));
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t a) {
+  uint32_t d;
+  asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(d) : "r"(a));
+  return d;
+}
+
+// m16n8k16, A row-major (4 regs), B col-major (2 regs), fp32 accumulate. F16 = true: f16 inputs.
+template <bool F16>
+__device__ __forceinline__ void mma16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                         uint32_t b1) {
+  if constexpr (F16) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+  } else {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+  }
+}
+
+// two fp8 (low 16 bits of w, or high 16 bits) -> f16x2, exact.
+template <int KV>
+__device__ __forceinline__ uint32_t fp8x2_to_f16x2(uint16_t v) {
+  uint32_t d;
+  if constexpr (KV == APH_KV_FP8_E5M2)
+    asm("cvt.rn.f16x2.e5m2x2 %0, %1;" : "=r"(d) : "h"(v));
+  else
+    asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(d) : "h"(v));
+  return d;
+}
+
+template <bool F16>
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  if constexpr (F16) {
+    __half2 h = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+  } else {
+    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+}
+
+// Token permutation used with FP8 KV (see kernel comment): S^T row r <-> token TAU(r) of the group.
+__device__ __forceinline__ int tau_fp8(int r) {
+  const int rr = r & 7, tt = rr >> 1;
+  const int hi = (r >> 3);                      // 0: rows 0-7, 1: rows 8-15
+  const int shift = ((tt >= 2) ^ hi) ? 2 : 0;   // rows<8: +2 for tt>=2 ; rows>=8: +2 for tt<2
+  return 4 * tt + shift + (rr & 1);
+}
+
+}  // namespace pa
+}  // namespace aphb200

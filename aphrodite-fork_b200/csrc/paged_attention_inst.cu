@@ -1,0 +1,74 @@
+// One translation unit per head size (compiled with -DAPH_PA_HEAD_SIZE=<D>) so that the
+// template instantiations build in parallel. Defines launch_pa_d<D>().
+#include "paged_attention_kernel.cuh"
+
+#ifndef APH_PA_HEAD_SIZE
+#error "compile with -DAPH_PA_HEAD_SIZE=<head size>"
+#endif
+
+namespace aphb200 {
+namespace pa {
+
+#define APH_CAT2(a, b) a##b
+#define APH_CAT(a, b) APH_CAT2(a, b)
+
+template <typename scalar_t, int KV, int BS>
+static int launch_one(const Params& p, cudaStream_t stream) {
+  constexpr int D = APH_PA_HEAD_SIZE;
+  using C = Cfg<scalar_t, KV, D, BS>;
+  auto kern = paged_attention_kernel<scalar_t, KV, D, BS>;
+  static bool attr_set[64] = {false};  // per device; idempotent, so a benign race at worst
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES) != cudaSuccess)
+      return set_error(APH_ERR_CUDA, "paged_attention: cannot reserve %d bytes of shared memory", C::SMEM_BYTES);
+    attr_set[dev] = true;
+  }
+  const int G = p.num_heads / p.num_kv_heads;
+  const int tiles = (G + HEADS_PER_CTA - 1) / HEADS_PER_CTA;
+  dim3 grid(p.num_kv_heads * tiles, p.num_seqs, p.num_partitions);
+  kern<<<grid, C::NTHREADS, C::SMEM_BYTES, stream>>>(p);
+  APH_LAUNCH_CHECK();
+  if (p.num_partitions > 1) {
+    dim3 rgrid(p.num_heads, p.num_seqs);
+    paged_attention_reduce_kernel<scalar_t, D><<<rgrid, D >= 128 ? 128 : 64, 0, stream>>>(p, KV != APH_KV_AUTO);
+    APH_LAUNCH_CHECK();
+  }
+  return APH_OK;
+}
+
+template <typename scalar_t, int KV>
+static int launch_bs(const Params& p, int block_size, cudaStream_t stream) {
+  switch (block_size) {
+    case 16: return launch_one<scalar_t, KV, 16>(p, stream);
+#ifndef APH_FAST_BUILD
+    case 8: return launch_one<scalar_t, KV, 8>(p, stream);
+    case 32: return launch_one<scalar_t, KV, 32>(p, stream);
+#endif
+    default: return set_error(APH_ERR_INVALID_ARGUMENT, "Unsupported block size: %d", block_size);
+  }
+}
+
+int APH_CAT(launch_pa_d, APH_PA_HEAD_SIZE)(const Params& p, int dtype, int kv_dtype, int block_size,
+                                          cudaStream_t stream) {
+  if (kv_dtype == APH_KV_AUTO) {
+    if (dtype == APH_DT_BF16) return launch_bs<__nv_bfloat16, APH_KV_AUTO>(p, block_size, stream);
+    if (dtype == APH_DT_F16) return launch_bs<__half, APH_KV_AUTO>(p, block_size, stream);
+    return set_error(APH_ERR_UNSUPPORTED, "paged_attention: float32 KV cache is not implemented on this path");
+  }
+  if (kv_dtype == APH_KV_FP8_E4M3) {
+    if (dtype == APH_DT_BF16) return launch_bs<__nv_bfloat16, APH_KV_FP8_E4M3>(p, block_size, stream);
+    if (dtype == APH_DT_F16) return launch_bs<__half, APH_KV_FP8_E4M3>(p, block_size, stream);
+    return launch_bs<float, APH_KV_FP8_E4M3>(p, block_size, stream);
+  }
+  if (kv_dtype == APH_KV_FP8_E5M2) {
+    if (dtype == APH_DT_BF16) return launch_bs<__nv_bfloat16, APH_KV_FP8_E5M2>(p, block_size, stream);
+    if (dtype == APH_DT_F16) return launch_bs<__half, APH_KV_FP8_E5M2>(p, block_size, stream);
+    return launch_bs<float, APH_KV_FP8_E5M2>(p, block_size, stream);
+  }
+  return set_error(APH_ERR_INVALID_ARGUMENT, "paged_attention: unsupported kv cache dtype %d", kv_dtype);
+}
+
+}  // namespace pa
+}  // namespace aphb200

@@ -1,0 +1,416 @@
+// Main split-K decode attention kernel and the partition reduce kernel (see paged_attention.cuh
+// for the design summary).
+#pragma once
+#include <type_traits>
+
+#include "paged_attention.cuh"
+
+namespace aphb200 {
+namespace pa {
+
+template <typename scalar_t, int KV, int D, int BS>
+struct Cfg {
+  static constexpr int ESZ = (KV == APH_KV_AUTO) ? (int)sizeof(scalar_t) : 1;  // cache element bytes
+  static constexpr bool FP8 = KV != APH_KV_AUTO;
+  static constexpr bool F16MMA = FP8 || std::is_same<scalar_t, __half>::value;
+  static constexpr int ST = BS > 16 ? BS : 16;  // tokens per pipeline stage
+  static constexpr int SG = ST / 16;            // 16-token MMA groups per stage
+  static constexpr int SP = ST / BS;            // cache pages per stage
+  static constexpr int KPAGE = D * BS * ESZ;    // bytes of one K (or V) page of one kv head
+  static constexpr int STAGE = 2 * SP * KPAGE;  // bytes per stage (K pages then V pages)
+  static constexpr int NS = (16384 / STAGE) >= 2 ? ((16384 / STAGE) > 8 ? 8 : (16384 / STAGE)) : 2;
+  static constexpr int NWARPS = (STAGE * NS * 4 <= 160 * 1024) ? 4 : 2;
+  static constexpr int NTHREADS = NWARPS * 32;
+  static constexpr int DP = D + 4;  // padded row of the cross-warp merge buffer (floats)
+  static constexpr int PIPE_BYTES = NWARPS * NS * STAGE;
+  static constexpr int MERGE_BYTES = NWARPS * HEADS_PER_CTA * DP * 4;
+  static constexpr int SMEM_BYTES = (PIPE_BYTES > MERGE_BYTES ? PIPE_BYTES : MERGE_BYTES) + NWARPS * NS * 8;
+  static constexpr int CTAS_PER_SM = (SMEM_BYTES + 1024) * 3 <= 227 * 1024 ? 3 : ((SMEM_BYTES + 1024) * 2 <= 227 * 1024 ? 2 : 1);
+};
+
+template <typename scalar_t, int KV, int D, int BS>
+__global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar_t, KV, D, BS>::CTAS_PER_SM)
+    paged_attention_kernel(const Params p) {
+  using C = Cfg<scalar_t, KV, D, BS>;
+  constexpr bool F16 = C::F16MMA;
+  constexpr int NWARPS = C::NWARPS, NS = C::NS, ST = C::ST, SG = C::SG, SP = C::SP, KPAGE = C::KPAGE;
+  constexpr int KS = D / 16;  // k-steps of Q K^T == m-tiles of P V
+
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ float m_s[NWARPS][HEADS_PER_CTA], l_s[NWARPS][HEADS_PER_CTA];
+
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int G = p.num_heads / p.num_kv_heads;
+  const int tiles = (G + HEADS_PER_CTA - 1) / HEADS_PER_CTA;
+  const int kvh = blockIdx.x / tiles, tile = blockIdx.x % tiles;
+  const int seq = blockIdx.y, part = blockIdx.z;
+  const int head0 = kvh * G + tile * HEADS_PER_CTA;       // first q head of this CTA
+  const int Gv = min(HEADS_PER_CTA, G - tile * HEADS_PER_CTA);  // valid q heads
+  const int L = p.seq_lens[seq];
+  const int part_start = part * p.partition_tokens;
+  const int P = p.num_partitions;
+
+  if (part_start >= L) {
+    // Nothing to attend to. With a single partition the output is defined as zeros
+    // (reference: empty loops leave accs = 0, attention_kernels.cuh:366-371).
+    if (P == 1 && L <= 0) {
+      scalar_t* o = (scalar_t*)p.out + (int64_t)seq * p.out_stride + (int64_t)head0 * D;
+      for (int i = threadIdx.x; i < Gv * D; i += C::NTHREADS) o[i] = ScalarTraits<scalar_t>::from_float(0.f);
+    }
+    return;
+  }
+  const int part_end = min(part_start + p.partition_tokens, L);
+  const int n_stages = (part_end - part_start + ST - 1) / ST;
+  const int n_my = w < n_stages ? (n_stages - w + NWARPS - 1) / NWARPS : 0;
+  const int num_seq_pages = (L + BS - 1) / BS;
+
+  uint8_t* my_pipe = smem + (size_t)w * NS * C::STAGE;
+  const uint32_t pipe_u32 = smem_u32(my_pipe);
+  const uint32_t bar_u32 = smem_u32(smem + (C::PIPE_BYTES > C::MERGE_BYTES ? C::PIPE_BYTES : C::MERGE_BYTES)) + w * NS * 8;
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < NS; ++s) mbar_init(bar_u32 + s * 8, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  // ---- block-table prefetch: lane j holds the page numbers of this warp's stage (ib + j) ----
+  const int32_t* bt = p.block_tables + (int64_t)seq * p.max_blocks_per_seq;
+  int bt_reg[SP];
+  int ib = 0;
+  auto bt_fill = [&]() {
+    const int si = ib + lane;
+#pragma unroll
+    for (int pg = 0; pg < SP; ++pg) {
+      const int page = (part_start + (w + si * NWARPS) * ST) / BS + pg;
+      bt_reg[pg] = (si < n_my && page < num_seq_pages) ? bt[page] : 0;
+    }
+  };
+  bt_fill();
+
+  const uint8_t* kc = (const uint8_t*)p.k_cache + (int64_t)kvh * p.kv_head_stride * C::ESZ;
+  const uint8_t* vc = (const uint8_t*)p.v_cache + (int64_t)kvh * p.kv_head_stride * C::ESZ;
+  const int64_t blk_bytes = p.kv_block_stride * C::ESZ;
+
+  auto issue = [&](int i) {  // all lanes call (shuffles); lane 0 issues the copies
+    if (i - ib >= 32) {
+      ib += 32;
+      bt_fill();
+    }
+    int blk[SP];
+#pragma unroll
+    for (int pg = 0; pg < SP; ++pg) blk[pg] = __shfl_sync(0xffffffffu, bt_reg[pg], i - ib);
+    if (lane == 0) {
+      const int slot = i % NS;
+      const int page0 = (part_start + (w + i * NWARPS) * ST) / BS;
+      const int npages = min(SP, num_seq_pages - page0);
+      const uint32_t bar = bar_u32 + slot * 8;
+      const uint32_t dst = pipe_u32 + slot * C::STAGE;
+      mbar_expect_tx(bar, (uint32_t)(npages * 2 * KPAGE));
+#pragma unroll
+      for (int pg = 0; pg < SP; ++pg) {
+        if (pg < npages) {
+          const int64_t off = (int64_t)blk[pg] * blk_bytes;
+          bulk_g2s(dst + pg * KPAGE, kc + off, KPAGE, bar);
+          bulk_g2s(dst + (SP + pg) * KPAGE, vc + off, KPAGE, bar);
+        }
+      }
+    }
+  };
+
+  // ---- Q^T B-fragments (heads along N = lane/4) ----
+  float sc = p.scale * LOG2E;
+  float v_scale = 1.f;
+  if constexpr (C::FP8) {
+    sc *= *p.k_scale;
+    v_scale = *p.v_scale;
+  }
+  uint32_t qb[KS][2];
+  {
+    const bool hv = g < Gv;
+    const scalar_t* qp = (const scalar_t*)p.q + (int64_t)seq * p.q_stride + (int64_t)(head0 + (hv ? g : 0)) * D;
+    float qf[KS][4];
+    float amax = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      const int d0 = C::FP8 ? 16 * ks + 4 * t : 16 * ks + 2 * t;
+      const int d1 = C::FP8 ? d0 + 2 : d0 + 8;
+      qf[ks][0] = hv ? ScalarTraits<scalar_t>::to_float(qp[d0]) : 0.f;
+      qf[ks][1] = hv ? ScalarTraits<scalar_t>::to_float(qp[d0 + 1]) : 0.f;
+      qf[ks][2] = hv ? ScalarTraits<scalar_t>::to_float(qp[d1]) : 0.f;
+      qf[ks][3] = hv ? ScalarTraits<scalar_t>::to_float(qp[d1 + 1]) : 0.f;
+      amax = fmaxf(amax, fmaxf(fmaxf(fabsf(qf[ks][0]), fabsf(qf[ks][1])), fmaxf(fabsf(qf[ks][2]), fabsf(qf[ks][3]))));
+    }
+    float qs = 1.f;
+    if constexpr (F16 && !std::is_same<scalar_t, __half>::value) {
+      // wide-range query fed to an f16 MMA: pre-scale by a power of two so that it cannot overflow
+#pragma unroll
+      for (int o = 16; o >= 1; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+      if (amax > 16384.f && amax < 3.0e38f) {
+        int ex;
+        frexpf(amax, &ex);
+        qs = ldexpf(1.f, 14 - ex);
+      }
+      sc /= qs;
+    }
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      qb[ks][0] = pack2<F16>(qf[ks][0] * qs, qf[ks][1] * qs);
+      qb[ks][1] = pack2<F16>(qf[ks][2] * qs, qf[ks][3] * qs);
+    }
+  }
+
+  // per-thread softmax columns = heads (2t, 2t+1) of this CTA
+  float slope[2] = {0.f, 0.f};
+  int bs_off[2] = {0, 0};
+  const bool sparse = p.bs_vert_stride > 1;
+  const int q_bs_id = sparse ? (L - 1) / p.bs_block_size : 0;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int hh = head0 + min(2 * t + j, Gv - 1);
+    if (p.alibi_slopes) slope[j] = p.alibi_slopes[hh] * LOG2E;
+    if (sparse)
+      bs_off[j] = p.bs_head_sliding_step >= 0 ? (p.tp_rank * p.num_heads + hh) * p.bs_head_sliding_step + 1
+                                              : (p.tp_rank * p.num_kv_heads + kvh) * (-p.bs_head_sliding_step) + 1;
+  }
+
+  // S^T row r of a 16-token group <-> token rowtok(r) of the group
+  const int tokA = C::FP8 ? tau_fp8(g) : g;
+  const int tokB = C::FP8 ? tau_fp8(g + 8) : g + 8;
+
+  float o_acc[KS][4];
+#pragma unroll
+  for (int mt = 0; mt < KS; ++mt)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) o_acc[mt][e] = 0.f;
+  float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+
+  // ---- prologue ----
+#pragma unroll 1
+  for (int i = 0; i < NS && i < n_my; ++i) issue(i);
+
+#pragma unroll 1
+  for (int i = 0; i < n_my; ++i) {
+    const int slot = i % NS;
+    mbar_wait(bar_u32 + slot * 8, (i / NS) & 1);
+    const uint32_t stage_k = pipe_u32 + slot * C::STAGE;
+    const uint32_t stage_v = stage_k + SP * KPAGE;
+    const int tok0 = part_start + (w + i * NWARPS) * ST;
+
+#pragma unroll
+    for (int sg = 0; sg < SG; ++sg) {
+      const int gs = tok0 + sg * 16;
+      if (gs >= part_end) break;
+      // ---------------- S^T = K Q^T ----------------
+      float s[4] = {0.f, 0.f, 0.f, 0.f};
+      if constexpr (!C::FP8) {
+        const int mi = lane >> 3, r = lane & 7;
+        const int ts = sg * 16 + r + (mi & 1) * 8;
+        const uint32_t base = stage_k + (ts / BS) * KPAGE + (mi >> 1) * (BS * 16) + (ts % BS) * 16;
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) {
+          uint32_t a0, a1, a2, a3;
+          ldsm_x4(base + ks * (BS * 32), a0, a1, a2, a3);
+          mma16816<F16>(s, a0, a1, a2, a3, qb[ks][0], qb[ks][1]);
+        }
+      } else {
+        const int tsA = sg * 16 + tokA, tsB = sg * 16 + tokB;
+        const uint32_t baseA = stage_k + (tsA / BS) * KPAGE + (tsA % BS) * 16 + 4 * t;
+        const uint32_t baseB = stage_k + (tsB / BS) * KPAGE + (tsB % BS) * 16 + 4 * t;
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) {
+          const uint32_t wa = lds32(baseA + ks * (BS * 16));
+          const uint32_t wb = lds32(baseB + ks * (BS * 16));
+          const uint32_t a0 = fp8x2_to_f16x2<KV>((uint16_t)(wa & 0xffffu));
+          const uint32_t a2 = fp8x2_to_f16x2<KV>((uint16_t)(wa >> 16));
+          const uint32_t a1 = fp8x2_to_f16x2<KV>((uint16_t)(wb & 0xffffu));
+          const uint32_t a3 = fp8x2_to_f16x2<KV>((uint16_t)(wb >> 16));
+          mma16816<F16>(s, a0, a1, a2, a3, qb[ks][0], qb[ks][1]);
+        }
+      }
+      // ---------------- online softmax (exp2 domain) ----------------
+      const int ta = gs + tokA, tb = gs + tokB;
+      float x[4];
+      x[0] = s[0] * sc + slope[0] * (float)(ta - L + 1);
+      x[1] = s[1] * sc + slope[1] * (float)(ta - L + 1);
+      x[2] = s[2] * sc + slope[0] * (float)(tb - L + 1);
+      x[3] = s[3] * sc + slope[1] * (float)(tb - L + 1);
+      if (ta >= L) x[0] = x[1] = -INFINITY;
+      if (tb >= L) x[2] = x[3] = -INFINITY;
+      if (sparse) {
+        const int kba = (ta / BS) * BS / p.bs_block_size, kbb = (tb / BS) * BS / p.bs_block_size;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const bool keep_a = ((kba + bs_off[j]) % p.bs_vert_stride == 0) || (kba > q_bs_id - p.bs_local_blocks);
+          const bool keep_b = ((kbb + bs_off[j]) % p.bs_vert_stride == 0) || (kbb > q_bs_id - p.bs_local_blocks);
+          if (!keep_a) x[j] = -INFINITY;
+          if (!keep_b) x[2 + j] = -INFINITY;
+        }
+      }
+      float mx[2] = {fmaxf(x[0], x[2]), fmaxf(x[1], x[3])};
+#pragma unroll
+      for (int o = 4; o <= 16; o <<= 1) {
+        mx[0] = fmaxf(mx[0], __shfl_xor_sync(0xffffffffu, mx[0], o));
+        mx[1] = fmaxf(mx[1], __shfl_xor_sync(0xffffffffu, mx[1], o));
+      }
+      float alpha[2], pr[4];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const float m_new = fmaxf(m_run[j], mx[j]);
+        const float m_use = m_new == -INFINITY ? 0.f : m_new;
+        alpha[j] = ex2(m_run[j] - m_use);
+        pr[j] = ex2(x[j] - m_use);
+        pr[2 + j] = ex2(x[2 + j] - m_use);
+        l_run[j] = l_run[j] * alpha[j] + pr[j] + pr[2 + j];
+        m_run[j] = m_new;
+      }
+      if (__any_sync(0xffffffffu, alpha[0] != 1.f || alpha[1] != 1.f)) {
+#pragma unroll
+        for (int mt = 0; mt < KS; ++mt) {
+          o_acc[mt][0] *= alpha[0];
+          o_acc[mt][1] *= alpha[1];
+          o_acc[mt][2] *= alpha[0];
+          o_acc[mt][3] *= alpha[1];
+        }
+      }
+      // P^T B-fragments: transpose the two 8x8 (token x head) blocks across the warp
+      const uint32_t pb0 = movmatrix_trans(pack2<F16>(pr[0], pr[1]));
+      const uint32_t pb1 = movmatrix_trans(pack2<F16>(pr[2], pr[3]));
+
+      // ---------------- O^T += V^T P^T ----------------
+      const bool tail = gs + 16 > L;  // V of tokens >= L may hold anything (NaN): zero it
+      if constexpr (!C::FP8) {
+        const int mi = lane >> 3, r = lane & 7;
+        const int ts = sg * 16 + (mi >> 1) * 8;
+        const uint32_t base = stage_v + (ts / BS) * KPAGE + (r + (mi & 1) * 8) * (BS * 2) + (ts % BS) * 2;
+        uint32_t mk0 = 0xffffffffu, mk2 = 0xffffffffu;
+        if (tail) {
+          const int c0 = gs + 2 * t, c2 = gs + 8 + 2 * t;
+          mk0 = (c0 < L ? 0x0000ffffu : 0u) | (c0 + 1 < L ? 0xffff0000u : 0u);
+          mk2 = (c2 < L ? 0x0000ffffu : 0u) | (c2 + 1 < L ? 0xffff0000u : 0u);
+        }
+#pragma unroll
+        for (int mt = 0; mt < KS; ++mt) {
+          uint32_t a0, a1, a2, a3;
+          ldsm_x4(base + mt * (16 * BS * 2), a0, a1, a2, a3);
+          if (tail) {
+            a0 &= mk0;
+            a1 &= mk0;
+            a2 &= mk2;
+            a3 &= mk2;
+          }
+          mma16816<F16>(o_acc[mt], a0, a1, a2, a3, pb0, pb1);
+        }
+      } else {
+        const int ts = sg * 16 + 4 * t;
+        const uint32_t base = stage_v + (ts / BS) * KPAGE + g * BS + (ts % BS);
+        uint32_t mk = 0xffffffffu;
+        if (tail) {
+          const int c = gs + 4 * t;
+          mk = (c < L ? 0xffu : 0u) | (c + 1 < L ? 0xff00u : 0u) | (c + 2 < L ? 0xff0000u : 0u) |
+               (c + 3 < L ? 0xff000000u : 0u);
+        }
+        const uint32_t sel = t >= 2 ? 0x1032u : 0x3210u;  // swap 16-bit halves for t >= 2 (see tau_fp8)
+#pragma unroll
+        for (int mt = 0; mt < KS; ++mt) {
+          uint32_t wa = lds32(base + mt * (16 * BS));
+          uint32_t wb = lds32(base + mt * (16 * BS) + 8 * BS);
+          if (tail) {
+            wa &= mk;
+            wb &= mk;
+          }
+          wa = __byte_perm(wa, 0, sel);
+          wb = __byte_perm(wb, 0, sel);
+          const uint32_t a0 = fp8x2_to_f16x2<KV>((uint16_t)(wa & 0xffffu));
+          const uint32_t a2 = fp8x2_to_f16x2<KV>((uint16_t)(wa >> 16));
+          const uint32_t a1 = fp8x2_to_f16x2<KV>((uint16_t)(wb & 0xffffu));
+          const uint32_t a3 = fp8x2_to_f16x2<KV>((uint16_t)(wb >> 16));
+          mma16816<F16>(o_acc[mt], a0, a1, a2, a3, pb0, pb1);
+        }
+      }
+    }
+    __syncwarp();
+    if (i + NS < n_my) issue(i + NS);
+  }
+
+  // ---- per-warp row sums, then cross-warp merge through shared memory ----
+#pragma unroll
+  for (int o = 4; o <= 16; o <<= 1) {
+    l_run[0] += __shfl_xor_sync(0xffffffffu, l_run[0], o);
+    l_run[1] += __shfl_xor_sync(0xffffffffu, l_run[1], o);
+  }
+  __syncthreads();  // every warp is done with its pipeline stages: reuse them as the merge buffer
+  float* o_s = reinterpret_cast<float*>(smem);
+  if (g == 0) {
+    m_s[w][2 * t] = m_run[0];
+    m_s[w][2 * t + 1] = m_run[1];
+    l_s[w][2 * t] = l_run[0];
+    l_s[w][2 * t + 1] = l_run[1];
+  }
+#pragma unroll
+  for (int mt = 0; mt < KS; ++mt) {
+    float* r0 = o_s + (size_t)(w * HEADS_PER_CTA + 2 * t) * C::DP + 16 * mt + g;
+    r0[0] = o_acc[mt][0];
+    r0[C::DP] = o_acc[mt][1];
+    r0[8] = o_acc[mt][2];
+    r0[C::DP + 8] = o_acc[mt][3];
+  }
+  __syncthreads();
+
+  for (int idx = threadIdx.x; idx < Gv * D; idx += C::NTHREADS) {
+    const int h = idx / D, d = idx % D;
+    float m_tot = -INFINITY;
+#pragma unroll
+    for (int ww = 0; ww < NWARPS; ++ww) m_tot = fmaxf(m_tot, m_s[ww][h]);
+    const float m_use = m_tot == -INFINITY ? 0.f : m_tot;
+    float acc = 0.f, l_tot = 0.f;
+#pragma unroll
+    for (int ww = 0; ww < NWARPS; ++ww) {
+      const float wgt = ex2(m_s[ww][h] - m_use);
+      acc += o_s[(size_t)(ww * HEADS_PER_CTA + h) * C::DP + d] * wgt;
+      l_tot += l_s[ww][h] * wgt;
+    }
+    const int head = head0 + h;
+    if (P == 1) {
+      // reference normaliser: 1 / (sum + 1e-6), attention_kernels.cuh:342
+      const float inv = __fdividef(1.f, l_tot + 1e-6f);
+      ((scalar_t*)p.out)[(int64_t)seq * p.out_stride + (int64_t)head * D + d] =
+          ScalarTraits<scalar_t>::from_float(acc * inv * v_scale);
+    } else {
+      const int64_t pi = ((int64_t)seq * p.num_heads + head) * P + part;
+      p.part_o[pi * D + d] = acc;
+      if (d == 0) {
+        p.part_ml[pi * 2] = m_tot;
+        p.part_ml[pi * 2 + 1] = l_tot;
+      }
+    }
+  }
+}
+
+// Split-K reduce: out[s,h,:] = sum_j O_j 2^(m_j - m) / (sum_j l_j 2^(m_j - m) + 1e-6) * v_scale.
+// Follows the reference's reduce (attention_kernels.cuh:604-667) on fp32 partials.
+template <typename scalar_t, int D>
+__global__ void __launch_bounds__(128) paged_attention_reduce_kernel(const Params p, const bool fp8) {
+  const int head = blockIdx.x, seq = blockIdx.y;
+  const int L = p.seq_lens[seq];
+  const int P = p.num_partitions;
+  const int np = L <= 0 ? 0 : min(P, (L + p.partition_tokens - 1) / p.partition_tokens);
+  const int64_t base = ((int64_t)seq * p.num_heads + head) * P;
+  const float v_scale = fp8 ? *p.v_scale : 1.f;
+  float m_tot = -INFINITY;
+  for (int j = 0; j < np; ++j) m_tot = fmaxf(m_tot, p.part_ml[(base + j) * 2]);
+  const float m_use = m_tot == -INFINITY ? 0.f : m_tot;
+  float denom = 0.f;
+  for (int j = 0; j < np; ++j) denom += p.part_ml[(base + j) * 2 + 1] * ex2(p.part_ml[(base + j) * 2] - m_use);
+  const float inv = __fdividef(1.f, denom + 1e-6f) * v_scale;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    float acc = 0.f;
+    for (int j = 0; j < np; ++j) acc += p.part_o[(base + j) * D + d] * ex2(p.part_ml[(base + j) * 2] - m_use);
+    ((scalar_t*)p.out)[(int64_t)seq * p.out_stride + (int64_t)head * D + d] =
+        ScalarTraits<scalar_t>::from_float(acc * inv);
+  }
+}
+
+}  // namespace pa
+}  // namespace aphb200

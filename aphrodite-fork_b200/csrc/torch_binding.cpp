@@ -1,0 +1,281 @@
+// Thin torch C++ extension over the C ABI (include/aphrodite_b200.h).
+//
+// Registers CUDA implementations for exactly the reference's four op schemas
+// (/root/reference/kernels/torch_bindings.cpp:41-51, :54-65, :326-333, :696-702) with the
+// reference's C++ signatures (kernels/ops.h:32-54, kernels/cache.h:21-25,
+// kernels/quantization/gptq_marlin/gptq_marlin.cu:2263-2270).
+//
+// Two build flavours of this one file (SURVEY.md 8b "Loading into a live Aphrodite"):
+//   -DAPH_DEFINE_SCHEMAS  standalone: also defines the schemas (TORCH_LIBRARY_FRAGMENT), for
+//                         processes where aphrodite._C is not loaded (the GPU test box);
+//   (no flag)             overlay: impl-only registration that overrides the CUDA kernels of an
+//                         already-imported aphrodite._C.
+// convert_fp8 (cache_kernels.cu:499-577) is registered too because the reference's tests and
+// create_kv_caches_with_random depend on it.
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <torch/all.h>
+#include <torch/library.h>
+
+#include <optional>
+#include <string>
+
+#include "../../include/aphrodite_b200.h"
+
+namespace {
+
+inline void check_status(int st, const char* op) {
+  TORCH_CHECK(st == APH_OK, op, ": ", aph_b200_last_error());
+}
+
+inline int dtype_code(const torch::Tensor& t, const char* op) {
+  switch (t.scalar_type()) {
+    case at::ScalarType::Float: return APH_DT_F32;
+    case at::ScalarType::Half: return APH_DT_F16;
+    case at::ScalarType::BFloat16: return APH_DT_BF16;
+    default: TORCH_CHECK(false, op, ": unsupported data type ", t.scalar_type());
+  }
+  return -1;
+}
+
+inline int kv_code(const std::string& s) {
+  const int kv = aph_kv_dtype_from_string(s.c_str());
+  TORCH_CHECK(kv >= 0, "Unsupported data type of kv cache: ", s);
+  return kv;
+}
+
+inline void* stream_of() { return (void*)at::cuda::getCurrentCUDAStream().stream(); }
+
+void paged_attention_impl(bool v2, torch::Tensor& out, torch::Tensor* exp_sums, torch::Tensor* max_logits,
+                          torch::Tensor* tmp_out, torch::Tensor& query, torch::Tensor& key_cache,
+                          torch::Tensor& value_cache, int64_t num_kv_heads, double scale, torch::Tensor& block_tables,
+                          torch::Tensor& seq_lens, int64_t block_size, int64_t max_seq_len,
+                          const std::optional<torch::Tensor>& alibi_slopes, const std::string& kv_cache_dtype,
+                          torch::Tensor& k_scale, torch::Tensor& v_scale, int64_t tp_rank,
+                          int64_t blocksparse_local_blocks, int64_t blocksparse_vert_stride,
+                          int64_t blocksparse_block_size, int64_t blocksparse_head_sliding_step) {
+  const char* op = v2 ? "paged_attention_v2" : "paged_attention_v1";
+  TORCH_CHECK(query.is_cuda() && key_cache.is_cuda() && value_cache.is_cuda() && out.is_cuda(), op,
+              ": tensors must be on a CUDA device");
+  TORCH_CHECK(query.dim() == 3 && out.dim() == 3, op, ": query/out must be [num_seqs, num_heads, head_size]");
+  TORCH_CHECK(query.stride(2) == 1 && query.stride(1) == query.size(2), op, ": query heads must be contiguous");
+  TORCH_CHECK(out.stride(2) == 1 && out.stride(1) == out.size(2), op, ": out heads must be contiguous");
+  TORCH_CHECK(block_tables.scalar_type() == at::ScalarType::Int && seq_lens.scalar_type() == at::ScalarType::Int, op,
+              ": block_tables and seq_lens must be int32");
+  TORCH_CHECK(block_tables.dim() == 2 && block_tables.stride(1) == 1, op, ": block_tables must be 2-D, row-major");
+  TORCH_CHECK(k_scale.scalar_type() == at::ScalarType::Float && v_scale.scalar_type() == at::ScalarType::Float, op,
+              ": k_scale / v_scale must be float32 tensors");
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  const int kv = kv_code(kv_cache_dtype);
+  const int dt = dtype_code(query, op);
+  const int num_seqs = (int)query.size(0), num_heads = (int)query.size(1), head_size = (int)query.size(2);
+  const float* alibi = nullptr;
+  if (alibi_slopes.has_value() && alibi_slopes->defined()) {
+    TORCH_CHECK(alibi_slopes->scalar_type() == at::ScalarType::Float && alibi_slopes->is_contiguous(), op,
+                ": alibi_slopes must be contiguous float32");
+    alibi = alibi_slopes->data_ptr<float>();
+  }
+  const size_t ws_bytes =
+      aph_paged_attention_workspace_bytes(num_seqs, num_heads, (int)num_kv_heads, head_size, (int)max_seq_len);
+  torch::Tensor ws;
+  void* ws_ptr = nullptr;
+  if (ws_bytes > 0) {
+    // torch caching allocator: stream-ordered and CUDA-graph safe, like the reference's temporaries
+    ws = torch::empty({(int64_t)ws_bytes}, torch::TensorOptions().dtype(torch::kUInt8).device(query.device()));
+    ws_ptr = ws.data_ptr();
+  }
+  int st;
+  if (!v2) {
+    st = aph_paged_attention_v1(out.data_ptr(), query.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(),
+                                num_seqs, num_heads, (int)num_kv_heads, head_size, (float)scale,
+                                block_tables.data_ptr<int32_t>(), seq_lens.data_ptr<int32_t>(), (int)block_size,
+                                (int)max_seq_len, (int)block_tables.size(1), alibi, query.stride(0), out.stride(0),
+                                key_cache.stride(0), key_cache.stride(1), dt, kv, k_scale.data_ptr<float>(),
+                                v_scale.data_ptr<float>(), (int)tp_rank, (int)blocksparse_local_blocks,
+                                (int)blocksparse_vert_stride, (int)blocksparse_block_size,
+                                (int)blocksparse_head_sliding_step, ws_ptr, ws_bytes, stream_of());
+  } else {
+    st = aph_paged_attention_v2(out.data_ptr(), exp_sums->data_ptr<float>(), max_logits->data_ptr<float>(),
+                                tmp_out->data_ptr(), query.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(),
+                                num_seqs, num_heads, (int)num_kv_heads, head_size, (float)scale,
+                                block_tables.data_ptr<int32_t>(), seq_lens.data_ptr<int32_t>(), (int)block_size,
+                                (int)max_seq_len, (int)block_tables.size(1), alibi, query.stride(0), out.stride(0),
+                                key_cache.stride(0), key_cache.stride(1), dt, kv, k_scale.data_ptr<float>(),
+                                v_scale.data_ptr<float>(), (int)tp_rank, (int)blocksparse_local_blocks,
+                                (int)blocksparse_vert_stride, (int)blocksparse_block_size,
+                                (int)blocksparse_head_sliding_step, ws_ptr, ws_bytes, stream_of());
+  }
+  check_status(st, op);
+}
+
+void paged_attention_v1(torch::Tensor& out, torch::Tensor& query, torch::Tensor& key_cache, torch::Tensor& value_cache,
+                        int64_t num_kv_heads, double scale, torch::Tensor& block_tables, torch::Tensor& seq_lens,
+                        int64_t block_size, int64_t max_seq_len, const std::optional<torch::Tensor>& alibi_slopes,
+                        const std::string& kv_cache_dtype, torch::Tensor& k_scale, torch::Tensor& v_scale,
+                        const int64_t tp_rank, const int64_t blocksparse_local_blocks,
+                        const int64_t blocksparse_vert_stride, const int64_t blocksparse_block_size,
+                        const int64_t blocksparse_head_sliding_step) {
+  paged_attention_impl(false, out, nullptr, nullptr, nullptr, query, key_cache, value_cache, num_kv_heads, scale,
+                       block_tables, seq_lens, block_size, max_seq_len, alibi_slopes, kv_cache_dtype, k_scale, v_scale,
+                       tp_rank, blocksparse_local_blocks, blocksparse_vert_stride, blocksparse_block_size,
+                       blocksparse_head_sliding_step);
+}
+
+void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tensor& max_logits, torch::Tensor& tmp_out,
+                        torch::Tensor& query, torch::Tensor& key_cache, torch::Tensor& value_cache,
+                        int64_t num_kv_heads, double scale, torch::Tensor& block_tables, torch::Tensor& seq_lens,
+                        int64_t block_size, int64_t max_seq_len, const std::optional<torch::Tensor>& alibi_slopes,
+                        const std::string& kv_cache_dtype, torch::Tensor& k_scale, torch::Tensor& v_scale,
+                        const int64_t tp_rank, const int64_t blocksparse_local_blocks,
+                        const int64_t blocksparse_vert_stride, const int64_t blocksparse_block_size,
+                        const int64_t blocksparse_head_sliding_step) {
+  paged_attention_impl(true, out, &exp_sums, &max_logits, &tmp_out, query, key_cache, value_cache, num_kv_heads, scale,
+                       block_tables, seq_lens, block_size, max_seq_len, alibi_slopes, kv_cache_dtype, k_scale, v_scale,
+                       tp_rank, blocksparse_local_blocks, blocksparse_vert_stride, blocksparse_block_size,
+                       blocksparse_head_sliding_step);
+}
+
+void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache, torch::Tensor& value_cache,
+                       torch::Tensor& slot_mapping, const std::string& kv_cache_dtype, torch::Tensor& k_scale,
+                       torch::Tensor& v_scale) {
+  const char* op = "reshape_and_cache";
+  TORCH_CHECK(key.is_cuda() && value.is_cuda() && key_cache.is_cuda() && value_cache.is_cuda(), op,
+              ": tensors must be on a CUDA device");
+  TORCH_CHECK(key.dim() == 3 && value.dim() == 3 && key_cache.dim() == 5 && value_cache.dim() == 4, op,
+              ": bad tensor ranks");
+  TORCH_CHECK(key.stride(2) == 1 && key.stride(1) == key.size(2) && value.stride(2) == 1 &&
+                  value.stride(1) == value.size(2),
+              op, ": key/value heads must be contiguous");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long && slot_mapping.is_contiguous(), op,
+              ": slot_mapping must be contiguous int64");
+  TORCH_CHECK(k_scale.scalar_type() == at::ScalarType::Float && v_scale.scalar_type() == at::ScalarType::Float, op,
+              ": k_scale / v_scale must be float32 tensors");
+  const at::cuda::OptionalCUDAGuard guard(device_of(key));
+  const int kv = kv_code(kv_cache_dtype);
+  // reference: num_tokens = slot_mapping.size(0) (cache_kernels.cu:379)
+  const int st = aph_reshape_and_cache(
+      key.data_ptr(), value.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(), slot_mapping.data_ptr<int64_t>(),
+      slot_mapping.size(0), key.stride(0), value.stride(0), (int)key.size(1), (int)key.size(2),
+      (int)key_cache.size(3), (int)key_cache.size(4), key_cache.stride(0), dtype_code(key, op), kv,
+      k_scale.data_ptr<float>(), v_scale.data_ptr<float>(), stream_of());
+  check_status(st, op);
+}
+
+void convert_fp8(torch::Tensor& dst_cache, torch::Tensor& src_cache, const double scale,
+                 const std::string& kv_cache_dtype) {
+  const char* op = "convert_fp8";
+  TORCH_CHECK(src_cache.is_cuda() && dst_cache.is_cuda() && src_cache.device() == dst_cache.device(), op,
+              ": src and dst must be on the same CUDA device");
+  TORCH_CHECK(src_cache.is_contiguous() && dst_cache.is_contiguous() && src_cache.numel() == dst_cache.numel(), op,
+              ": src and dst must be contiguous and of equal size");
+  const at::cuda::OptionalCUDAGuard guard(device_of(src_cache));
+  int kv = kv_code(kv_cache_dtype);
+  if (kv == APH_KV_AUTO) kv = APH_KV_FP8_E4M3;  // reference: "auto" behaves as e4m3 here (cache_kernels.cu:540-556)
+  int st;
+  if (dst_cache.scalar_type() == at::ScalarType::Byte) {
+    st = aph_convert_fp8(dst_cache.data_ptr(), src_cache.data_ptr(), src_cache.numel(), (float)scale,
+                         dtype_code(src_cache, op), kv, 0, stream_of());
+  } else {
+    TORCH_CHECK(src_cache.scalar_type() == at::ScalarType::Byte, op, ": one of src/dst must be uint8");
+    st = aph_convert_fp8(dst_cache.data_ptr(), src_cache.data_ptr(), src_cache.numel(), (float)scale,
+                         dtype_code(dst_cache, op), kv, 1, stream_of());
+  }
+  check_status(st, op);
+}
+
+torch::Tensor gptq_marlin_gemm(torch::Tensor& a, torch::Tensor& b_q_weight, torch::Tensor& b_scales,
+                               torch::Tensor& b_zeros, torch::Tensor& g_idx, torch::Tensor& perm,
+                               torch::Tensor& workspace, int64_t const& b_q_type_id, int64_t size_m, int64_t size_n,
+                               int64_t size_k, bool is_k_full, bool has_zp, bool use_atomic_add, bool use_fp32_reduce,
+                               bool is_zp_float) {
+  const char* op = "gptq_marlin_gemm";
+  // argument checks of the reference entry point, gptq_marlin.cu:2271-2332
+  TORCH_CHECK(a.is_cuda() && b_q_weight.is_cuda() && b_scales.is_cuda() && workspace.is_cuda(), op,
+              ": tensors must be on a CUDA device");
+  TORCH_CHECK(a.dim() == 2 && a.size(0) == size_m, "Shape mismatch: a.size(0) = ", a.size(0), ", size_m = ", size_m);
+  TORCH_CHECK(a.size(1) == size_k, "Shape mismatch: a.size(1) = ", a.size(1), ", size_k = ", size_k);
+  TORCH_CHECK(a.stride(1) == 1, "A must be contiguous in its last dimension");
+  TORCH_CHECK(b_q_weight.is_contiguous(), "b_q_weight is not contiguous");
+  TORCH_CHECK(b_scales.is_contiguous() && b_scales.dim() == 2, "b_scales must be a contiguous 2-D tensor");
+  TORCH_CHECK(b_scales.scalar_type() == a.scalar_type(), "b_scales type must match a");
+  TORCH_CHECK(b_scales.size(1) == size_n, "b_scales dim 1 = ", b_scales.size(1), " is not size_n = ", size_n);
+  TORCH_CHECK(b_q_weight.scalar_type() == at::ScalarType::Int && workspace.scalar_type() == at::ScalarType::Int, op,
+              ": b_q_weight and workspace must be int32");
+  const at::cuda::OptionalCUDAGuard guard(device_of(a));
+  const int dt = dtype_code(a, op);
+  torch::Tensor c = torch::empty({size_m, size_n}, a.options());
+  if (size_m == 0) return c;
+  const size_t sbytes = aph_gptq_marlin_gemm_scratch_bytes(size_m, size_n, size_k);
+  torch::Tensor scratch;
+  void* sptr = nullptr;
+  if (sbytes > 0) {
+    scratch = torch::empty({(int64_t)sbytes}, torch::TensorOptions().dtype(torch::kUInt8).device(a.device()));
+    sptr = scratch.data_ptr();
+  }
+  const void* zp = (has_zp && b_zeros.numel() > 0) ? b_zeros.data_ptr() : nullptr;
+  const int32_t* gi = g_idx.numel() > 0 ? g_idx.data_ptr<int32_t>() : nullptr;
+  const int32_t* pm = perm.numel() > 0 ? perm.data_ptr<int32_t>() : nullptr;
+  const int st = aph_gptq_marlin_gemm(c.data_ptr(), a.data_ptr(), b_q_weight.data_ptr(), b_scales.data_ptr(), zp, gi,
+                                      pm, workspace.data_ptr<int32_t>(), workspace.numel(), b_q_type_id, size_m,
+                                      size_n, size_k, a.stride(0), b_scales.size(0), is_k_full, has_zp,
+                                      use_atomic_add, use_fp32_reduce, is_zp_float, dt, sptr, sbytes, stream_of());
+  check_status(st, op);
+  return c;
+}
+
+}  // namespace
+
+#ifdef APH_DEFINE_SCHEMAS
+TORCH_LIBRARY_FRAGMENT(_C, ops) {
+  ops.def(
+      "paged_attention_v1("
+      "    Tensor! out, Tensor query, Tensor key_cache,"
+      "    Tensor value_cache, int num_kv_heads, float scale,"
+      "    Tensor block_tables, Tensor seq_lens, int block_size,"
+      "    int max_seq_len, Tensor? alibi_slopes,"
+      "    str kv_cache_dtype, Tensor k_scale, Tensor v_scale,"
+      "    int tp_rank, int blocksparse_local_blocks,"
+      "    int blocksparse_vert_stride, int blocksparse_block_size,"
+      "    int blocksparse_head_sliding_step) -> ()");
+  ops.def(
+      "paged_attention_v2("
+      "    Tensor! out, Tensor! exp_sums, Tensor! max_logits,"
+      "    Tensor! tmp_out, Tensor query, Tensor key_cache,"
+      "    Tensor value_cache, int num_kv_heads, float scale,"
+      "    Tensor block_tables, Tensor seq_lens, int block_size,"
+      "    int max_seq_len, Tensor? alibi_slopes,"
+      "    str kv_cache_dtype, Tensor k_scale, Tensor v_scale,"
+      "    int tp_rank, int blocksparse_local_blocks,"
+      "    int blocksparse_vert_stride, int blocksparse_block_size,"
+      "    int blocksparse_head_sliding_step) -> ()");
+  ops.def(
+      "gptq_marlin_gemm(Tensor a, Tensor b_q_weight, Tensor b_scales, "
+      "Tensor b_zeros, Tensor g_idx, Tensor perm, Tensor workspace, "
+      "int b_q_type, "
+      "SymInt size_m, SymInt size_n, SymInt size_k, bool is_k_full, "
+      "bool has_zp, bool use_atomic_add, bool use_fp32_reduce, "
+      "bool is_zp_float) -> Tensor",
+      {at::Tag::needs_fixed_stride_order});
+}
+TORCH_LIBRARY_FRAGMENT(_C_cache_ops, ops) {
+  ops.def(
+      "reshape_and_cache(Tensor key, Tensor value,"
+      "                  Tensor! key_cache, Tensor! value_cache,"
+      "                  Tensor slot_mapping,"
+      "                  str kv_cache_dtype,"
+      "                  Tensor k_scale, Tensor v_scale) -> ()");
+  ops.def(
+      "convert_fp8(Tensor! dst_cache, Tensor src_cache, float scale, "
+      "str kv_cache_dtype) -> ()");
+}
+#endif
+
+TORCH_LIBRARY_IMPL(_C, CUDA, ops) {
+  ops.impl("paged_attention_v1", &paged_attention_v1);
+  ops.impl("paged_attention_v2", &paged_attention_v2);
+  ops.impl("gptq_marlin_gemm", &gptq_marlin_gemm);
+}
+TORCH_LIBRARY_IMPL(_C_cache_ops, CUDA, ops) {
+  ops.impl("reshape_and_cache", &reshape_and_cache);
+  ops.impl("convert_fp8", &convert_fp8);
+}

@@ -1,0 +1,143 @@
+/*
+ * aphrodite_b200.h - C ABI of the B200-native decode hot path.
+ *
+ * The reference has no C ABI: its boundary is "C++ functions taking torch::Tensor&, registered
+ * by schema string" (/root/reference/kernels/torch_bindings.cpp:41-65,326-333,
+ * 696-702). This header is the torch-free layer underneath that boundary: plain pointers, sizes
+ * and a CUDA stream. aphrodite-fork_b200/csrc/torch_binding.cpp registers the reference's four
+ * schema strings on top of it, so `torch.ops._C.*` / `torch.ops._C_cache_ops.*` callers
+ * (aphrodite/_custom_ops.py) are unchanged, and any other host (ctypes, cgo, JNI) can bind the
+ * same entry points directly.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream);
+ *   - all calls are asynchronous on `stream`, never synchronise, never allocate: scratch is
+ *     passed in by the caller (sizes from the *_workspace_bytes functions) so that the calls
+ *     are CUDA-graph capturable, like the reference ops (worker/model_runner.py:1487-1646);
+ *   - return value: 0 on success, an aph_status_t otherwise; aph_b200_last_error() returns a
+ *     thread-local message (the torch binding turns it into c10::Error / RuntimeError, the
+ *     reference's error behaviour: TORCH_CHECK, SURVEY.md 8b "Errors").
+ */
+#ifndef APHRODITE_B200_H_
+#define APHRODITE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define APH_B200_ABI_VERSION 1
+
+typedef enum {
+  APH_OK = 0,
+  APH_ERR_INVALID_ARGUMENT = 1, /* shape / alignment / value the reference would TORCH_CHECK */
+  APH_ERR_UNSUPPORTED = 2,      /* legal in the reference, not implemented here yet          */
+  APH_ERR_WORKSPACE = 3,        /* scratch buffer too small                                   */
+  APH_ERR_CUDA = 4              /* launch failed (cudaGetLastError)                           */
+} aph_status_t;
+
+/* scalar_t of query / key / value / a (reference: at::ScalarType Float / Half / BFloat16) */
+typedef enum { APH_DT_F32 = 0, APH_DT_F16 = 1, APH_DT_BF16 = 2 } aph_dtype_t;
+
+/* reference: enum Fp8KVCacheDataType, kernels/attention/dtype_fp8.cuh:14-18 */
+typedef enum { APH_KV_AUTO = 0, APH_KV_FP8_E4M3 = 1, APH_KV_FP8_E5M2 = 2 } aph_kv_dtype_t;
+
+int aph_b200_abi_version(void);
+const char* aph_b200_last_error(void);
+
+/* "auto" | "fp8" | "fp8_e4m3" | "fp8_e5m2" -> aph_kv_dtype_t, -1 if unknown
+ * (reference: DISPATCH_BY_KV_CACHE_DTYPE, kernels/quantization/fp8/nvidia/quant_utils.cuh:532-570) */
+int aph_kv_dtype_from_string(const char* kv_cache_dtype);
+
+/* ---------------------------------------------------------------------------------------------
+ * reshape_and_cache - replaces kernels/cache_kernels.cu:369-395 (kernel :210-262).
+ *   key, value   [num_tokens, num_kv_heads, head_size] scalar dtype, row strides in ELEMENTS
+ *   key_cache    [num_blocks, num_kv_heads, head_size/x, block_size, x]
+ *   value_cache  [num_blocks, num_kv_heads, head_size, block_size]
+ *                cache element = scalar dtype (AUTO) or uint8 (FP8); x = 16 / sizeof(cache elt)
+ *   slot_mapping [num_tokens] int64, slot < 0 = padding token, skipped
+ *   k_scale, v_scale: device pointers to one float each (only read for FP8)
+ * Bit-exact with the reference, including the FP8 bytes.
+ * ------------------------------------------------------------------------------------------- */
+int aph_reshape_and_cache(const void* key, const void* value, void* key_cache, void* value_cache,
+                          const int64_t* slot_mapping, int64_t num_tokens, int64_t key_stride,
+                          int64_t value_stride, int num_kv_heads, int head_size, int block_size, int x,
+                          int64_t cache_block_stride, int dtype, int kv_dtype, const float* k_scale,
+                          const float* v_scale, void* stream);
+
+/* convert_fp8 - replaces kernels/cache_kernels.cu:499-577 (also accepts E5M2, which the
+ * reference rejects). dst/src: one of them is uint8 (fp8), the other `dtype`; n elements.
+ * direction: 0 = scalar -> fp8 (dst = fp8(src / scale)), 1 = fp8 -> scalar (dst = src * scale). */
+int aph_convert_fp8(void* dst, const void* src, int64_t n, float scale, int dtype, int kv_dtype,
+                    int direction, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * paged attention - replaces kernels/attention/paged_attention_v1.cu:170-192 and
+ * paged_attention_v2.cu:176-201 (kernel attention_kernels.cuh:86-495, reduce :563-668).
+ * One implementation serves both entry points: a GQA-packed split-K kernel whose partition
+ * size is chosen from the problem size (not the API's 512), plus a reduce kernel.
+ *   out          [num_seqs, num_heads, head_size] scalar dtype, row stride out_stride (elements)
+ *   query        [num_seqs, num_heads, head_size] scalar dtype, row stride q_stride (elements)
+ *   key_cache / value_cache as above; kv_block_stride / kv_head_stride in ELEMENTS
+ *   block_tables [num_seqs, max_num_blocks_per_seq] int32; seq_lens [num_seqs] int32
+ *   alibi_slopes [num_heads] float or NULL
+ *   max_seq_len  static upper bound on seq_lens (CUDA-graph rule)
+ *   workspace    >= aph_paged_attention_workspace_bytes(...) bytes, 16-byte aligned
+ * v2's caller-allocated exp_sums / max_logits / tmp_out are accepted and left untouched (they
+ * are sized for 512-token partitions and never read back by the caller, paged_attn.py:155-165).
+ * ------------------------------------------------------------------------------------------- */
+size_t aph_paged_attention_workspace_bytes(int num_seqs, int num_heads, int num_kv_heads, int head_size,
+                                           int max_seq_len);
+
+int aph_paged_attention_v1(void* out, const void* query, const void* key_cache, const void* value_cache,
+                           int num_seqs, int num_heads, int num_kv_heads, int head_size, float scale,
+                           const int32_t* block_tables, const int32_t* seq_lens, int block_size,
+                           int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes,
+                           int64_t q_stride, int64_t out_stride, int64_t kv_block_stride,
+                           int64_t kv_head_stride, int dtype, int kv_dtype, const float* k_scale,
+                           const float* v_scale, int tp_rank, int blocksparse_local_blocks,
+                           int blocksparse_vert_stride, int blocksparse_block_size,
+                           int blocksparse_head_sliding_step, void* workspace, size_t workspace_bytes,
+                           void* stream);
+
+int aph_paged_attention_v2(void* out, float* exp_sums, float* max_logits, void* tmp_out, const void* query,
+                           const void* key_cache, const void* value_cache, int num_seqs, int num_heads,
+                           int num_kv_heads, int head_size, float scale, const int32_t* block_tables,
+                           const int32_t* seq_lens, int block_size, int max_seq_len,
+                           int max_num_blocks_per_seq, const float* alibi_slopes, int64_t q_stride,
+                           int64_t out_stride, int64_t kv_block_stride, int64_t kv_head_stride, int dtype,
+                           int kv_dtype, const float* k_scale, const float* v_scale, int tp_rank,
+                           int blocksparse_local_blocks, int blocksparse_vert_stride,
+                           int blocksparse_block_size, int blocksparse_head_sliding_step, void* workspace,
+                           size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * gptq_marlin_gemm - replaces kernels/quantization/gptq_marlin/gptq_marlin.cu:2263-2468.
+ *   c            [size_m, size_n] scalar dtype (written; caller-allocated here, the torch
+ *                binding allocates and returns it like the reference :2336-2341)
+ *   a            [size_m, size_k] scalar dtype, row stride lda elements (lda % 8 == 0)
+ *   b_q_weight   [size_k/16, size_n*16/pack] int32, Marlin layout (marlin_utils_test.py:30-92)
+ *   b_scales     [num_groups, size_n] scalar dtype, Marlin-permuted (marlin_utils.py:204-225)
+ *   b_zeros      [num_groups, size_n/pack] int32 or NULL (has_zp)
+ *   g_idx, perm  [size_k] int32 or NULL (act-order)
+ *   workspace    the reference's int32 lock buffer (>= size_n/64*16 ints); left all-zero
+ *   b_q_type     ScalarType id (kernels/core/scalar_type.hpp:100-138): uint4b8, uint8b128,
+ *                uint4 (has_zp), uint8 (has_zp)
+ *   scratch      >= aph_gptq_marlin_gemm_scratch_bytes(...) bytes (fp32 split-K partials)
+ * ------------------------------------------------------------------------------------------- */
+size_t aph_gptq_marlin_gemm_scratch_bytes(int64_t size_m, int64_t size_n, int64_t size_k);
+
+int aph_gptq_marlin_gemm(void* c, const void* a, const void* b_q_weight, const void* b_scales,
+                         const void* b_zeros, const int32_t* g_idx, const int32_t* perm, int32_t* workspace,
+                         int64_t workspace_ints, int64_t b_q_type, int64_t size_m, int64_t size_n,
+                         int64_t size_k, int64_t lda, int64_t num_groups, int is_k_full, int has_zp,
+                         int use_atomic_add, int use_fp32_reduce, int is_zp_float, int dtype, void* scratch,
+                         size_t scratch_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* APHRODITE_B200_H_ */
