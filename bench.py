@@ -1,0 +1,353 @@
+#!/usr/bin/env python
+"""Headline benchmark: paged-attention decode KV GB/s on BASELINE.json configs[1] (C2).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+A "step" is one pass of the decode attention hot path over one batch: `paged_attention_v2`
+(our kernels through the reference's op schema) over 64 sequences x 4096 context, 32 q / 8 kv
+heads, head 128, FP8-E4M3 KV, block 16. `value` = algorithmic KV bytes (K and V, every kv head
+once) / device time with everything resident in HBM; `e2e` = the same metric through the public
+API (PagedAttention.write_to_paged_cache + forward_decode) with the step's inputs (query, new K/V
+token, slot mapping, block tables, sequence lengths) starting in pinned HOST memory and the
+output copied back, copies inside the timed region. The KV cache itself is device-resident state
+(it never lives on the host in the reference either: worker/cache_engine.py).
+
+Multi-GPU (torchrun, one rank per GPU): attention has no exchange step; every rank runs the same
+per-GPU workload on its own KV pool (weak scaling), value = total bytes / max-over-ranks time.
+
+--impl reference: the reference's own CPU implementation of the path (oracle/_ref = unmodified
+kernels/cpu/attention.cpp, bf16 KV because the CPU backend has no FP8) on the host cores, each step
+a bounded sample of the workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H, KVH, D, BS = 32, 8, 128, 16
+BATCH, CTX = 64, 4096
+METRIC = "paged-attn decode KV GB/s"
+WORKLOAD = "C2: paged_attention_v2 Llama-3-8B shape 32q/8kv d128, fp8_e4m3 KV, block 16, batch 64 x ctx 4096"
+
+
+def kv_bytes(batch, ctx, kvh, d, esz):
+    return 2 * batch * ctx * kvh * d * esz
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    def __init__(self, index=0):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_reference_run(seconds_target, batch, ctx, threads=None):
+    """Times the reference CPU backend (oracle/_ref) on a bounded sample: `batch` sequences of the C2
+    shape with bf16 KV. Returns (GB/s, cores, kind, sample description, ms per call, calls)."""
+    import torch
+    from oracle import oracle
+    cores = threads or os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    ref = oracle.refcpu()
+    kind = "reference" if ref is not None else "port"
+    dt = torch.bfloat16
+    nblk = batch * ctx // BS
+    g = torch.Generator().manual_seed(0)
+    sc = D ** -0.5
+    q = ((torch.rand(batch, H, D, generator=g) * 2 - 1) * sc).to(dt)
+    kc = ((torch.rand(nblk, KVH, D // 8, BS, 8, generator=g) * 2 - 1) * sc).to(dt)
+    vc = ((torch.rand(nblk, KVH, D, BS, generator=g) * 2 - 1) * sc).to(dt)
+    bt = torch.randperm(nblk, generator=g).to(torch.int32).reshape(batch, ctx // BS)
+    sl = torch.full((batch,), ctx, dtype=torch.int32)
+    out = torch.empty_like(q)
+    one = torch.tensor(1.0)
+
+    def call():
+        if ref is not None:
+            ref.paged_attention_v1(out, q, kc, vc, KVH, sc, bt, sl, BS, ctx, None, "auto", one, one, 0, 0, 0, 64, 0)
+        else:
+            oracle.paged_attention(q, kc, vc, KVH, sc, bt, sl, BS)
+
+    call()
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        call()
+        n += 1
+        el = time.perf_counter() - t0
+        if el >= seconds_target or n >= 2000:
+            break
+    gbs = kv_bytes(batch, ctx, KVH, D, 2) * n / el / 1e9
+    sample = (f"{n} calls of {'kernels/cpu/attention.cpp paged_attention_v1 (oracle/_ref)' if ref is not None else 'oracle port'}"
+              f" on {batch} seqs x {ctx} ctx, 32q/8kv d128, bf16 KV (CPU backend has no FP8), {cores} threads")
+    return gbs, cores, kind, sample, el / n * 1e3, n
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warm = args.steps, args.warmup
+    # bounded sample per step: 4 sequences of the C2 shape (67 MB of bf16 KV)
+    import torch
+    from oracle import oracle
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sb = 4
+    ref = oracle.refcpu()
+    kind = "reference" if ref is not None else "port"
+    dt = torch.bfloat16
+    nblk = sb * CTX // BS
+    g = torch.Generator().manual_seed(0)
+    sc = D ** -0.5
+    q = ((torch.rand(sb, H, D, generator=g) * 2 - 1) * sc).to(dt)
+    kc = ((torch.rand(nblk, KVH, D // 8, BS, 8, generator=g) * 2 - 1) * sc).to(dt)
+    vc = ((torch.rand(nblk, KVH, D, BS, generator=g) * 2 - 1) * sc).to(dt)
+    bt = torch.randperm(nblk, generator=g).to(torch.int32).reshape(sb, CTX // BS)
+    sl = torch.full((sb,), CTX, dtype=torch.int32)
+    out = torch.empty_like(q)
+    one = torch.tensor(1.0)
+
+    def call():
+        if ref is not None:
+            ref.paged_attention_v1(out, q, kc, vc, KVH, sc, bt, sl, BS, CTX, None, "auto", one, one, 0, 0, 0, 64, 0)
+        else:
+            oracle.paged_attention(q, kc, vc, KVH, sc, bt, sl, BS)
+
+    for _ in range(warm):
+        call()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        call()
+    el = time.perf_counter() - t0
+    val = kv_bytes(sb, CTX, KVH, D, 2) * steps / el / 1e9
+    sample = (f"each step = {sb} seqs x {CTX} ctx of the C2 shape with bf16 KV (the CPU backend has no FP8), "
+              f"{'kernels/cpu/attention.cpp via oracle/_ref' if ref is not None else 'oracle port'}, {cores} threads")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(val, 3), "unit": "GB/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": warm, "ms_per_step": round(el / steps * 1e3, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16 (f32 accumulate)", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": sample},
+        "cpu_baseline": {"value": round(val, 3), "unit": "GB/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": round(val, 3), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import aphrodite_fork_b200 as A
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: there is no CPU fallback for the product path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    A.load()
+    steps, warm = args.steps, max(args.warmup, 3)
+
+    # ---- synthetic C2 inputs (seed 0), KV pool = 16384 distinct blocks = 512 MiB FP8 > L2 ----
+    g = torch.Generator(device=dev).manual_seed(0 + rank)
+    nblk = BATCH * CTX // BS
+    sc = D ** -0.5
+    one = torch.tensor(1.0, device=dev)
+    npools = 2  # alternate between two pools: 1 GiB of KV in rotation
+    pools = []
+    for _ in range(npools):
+        src = ((torch.rand(nblk, KVH, D // 16, BS, 16, generator=g, device=dev) * 2 - 1) * sc).to(torch.bfloat16)
+        kc = torch.empty(src.shape, dtype=torch.uint8, device=dev)
+        A.ops.convert_fp8(kc, src, 1.0, "fp8")
+        src = ((torch.rand(nblk, KVH, D, BS, generator=g, device=dev) * 2 - 1) * sc).to(torch.bfloat16)
+        vc = torch.empty(src.shape, dtype=torch.uint8, device=dev)
+        A.ops.convert_fp8(vc, src, 1.0, "fp8")
+        pools.append((kc, vc))
+    del src
+    q = ((torch.rand(BATCH, H, D, generator=g, device=dev) * 2 - 1) * sc).to(torch.bfloat16)
+    bt = torch.randperm(nblk, generator=g, device=dev).to(torch.int32).reshape(BATCH, CTX // BS)
+    sl = torch.full((BATCH,), CTX, dtype=torch.int32, device=dev)
+    out = torch.empty_like(q)
+    P = (CTX + 511) // 512
+    exp_sums = torch.empty(BATCH, H, P, dtype=torch.float32, device=dev)
+    max_logits = torch.empty_like(exp_sums)
+    tmp_out = torch.empty(BATCH, H, P, D, dtype=torch.bfloat16, device=dev)
+
+    def step(i):
+        kc, vc = pools[i % npools]
+        A.ops.paged_attention_v2(out, exp_sums, max_logits, tmp_out, q, kc, vc, KVH, sc, bt, sl, BS, CTX, None, "fp8",
+                                 one, one)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(warm):
+        step(i)
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for i in range(steps):
+        step(i)
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    per_step_bytes = kv_bytes(BATCH, CTX, KVH, D, 1)
+    value = per_step_bytes * steps * world / (ms * 1e-3) / 1e9
+    per_gpu = per_step_bytes * steps / (ms * 1e-3) / 1e9
+
+    # ---- e2e: public API, host-resident step inputs, copies inside the timed region ----
+    pin = dict(pin_memory=True)
+    q_h = q.cpu().pin_memory()
+    newkv_h = ((torch.rand(BATCH, 2, KVH, D) * 2 - 1) * sc).to(torch.bfloat16).pin_memory()
+    bt_h = bt.cpu().pin_memory()
+    sl_h = sl.cpu().pin_memory()
+    slots_h = (bt_h[:, -1].to(torch.int64) * BS + (BS - 1)).pin_memory()  # slot of token ctx-1 of every sequence
+    out_h = torch.empty(BATCH, H, D, dtype=torch.bfloat16, **pin)
+    h2d = sum(t.numel() * t.element_size() for t in (q_h, newkv_h, bt_h, sl_h, slots_h))
+    d2h = out_h.numel() * out_h.element_size()
+
+    def e2e_step(i):
+        kc, vc = pools[i % npools]
+        qd = q_h.to(dev, non_blocking=True)
+        nkv = newkv_h.to(dev, non_blocking=True)
+        btd = bt_h.to(dev, non_blocking=True)
+        sld = sl_h.to(dev, non_blocking=True)
+        sd = slots_h.to(dev, non_blocking=True)
+        A.PagedAttention.write_to_paged_cache(nkv[:, 0], nkv[:, 1], kc, vc, sd, "fp8", one, one)
+        o = A.PagedAttention.forward_decode(qd, kc, vc, btd, sld, CTX, "fp8", KVH, sc, None, one, one)
+        out_h.copy_(o, non_blocking=True)
+
+    for i in range(warm):
+        e2e_step(i)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        e2e_step(i)
+    e1.record()
+    barrier()
+    ems = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ems], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ems = float(t.item())
+    e2e_val = per_step_bytes * steps * world / (ems * 1e-3) / 1e9
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        line = {
+            "metric": METRIC, "value": round(value, 2), "unit": "GB/s", "n_gpus": world, "steps": steps,
+            "warmup": warm, "ms_per_step": round(ms / steps, 5), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f16 mma / f32 accumulate over fp8_e4m3 KV, bf16 q/out", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "per_gpu": "full C2 batch per rank (weak scaling, no collective on this path)",
+                       "l2": "two 512 MiB FP8 KV pools alternated, block tables = random permutation of distinct "
+                             "blocks: inputs larger than the 126 MB L2",
+                       "kv_bytes_per_step": per_step_bytes},
+            "roofline": {"bound": "hbm", "achieved": round(per_gpu, 2), "peak": peak, "unit": "GB/s",
+                         "frac": round(per_gpu / peak, 4), "traffic": None,
+                         "note": f"algorithmic KV bytes / CUDA-event time of the whole op (split-K kernel + reduce) per launch; "
+                                 f"peak = {peak_src}"},
+            "e2e": {"value": round(e2e_val, 2), "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": round(ems / steps, 5),
+                    "api": "PagedAttention.write_to_paged_cache + forward_decode (host-pinned q/new-kv/slots/"
+                           "block_tables/seq_lens -> device, output -> host)"},
+            "gpu_launches": 2 * steps,
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu:
+            gbs, cores, kind, sample, cms, n = cpu_reference_run(12.0, 4, CTX)
+            line["cpu_baseline"] = {"value": round(gbs, 3), "unit": "GB/s", "cores": cores, "kind": kind,
+                                    "sample": sample, "ms_per_call": round(cms, 3)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()
