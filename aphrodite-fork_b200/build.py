@@ -79,7 +79,10 @@ def build(verbose: bool = False) -> str:
     binding = os.path.join(CSRC, "torch_binding.cpp")
     inc = [f"-I{p}" for p in ce.include_paths(device_type="cuda")] + [f"-I{sysconfig.get_paths()['include']}"]
     tlib = os.path.join(os.path.dirname(torch.__file__), "lib")
-    cxx = os.environ.get("CXX", "g++")
+    # NOT $CXX: the image exports CXX=/opt/gcc/bin/g++, a wrapper that links libstdc++ statically; a second,
+    # uninitialised copy of the C++ runtime inside the torch process segfaults on the first ostream << int
+    # (seen as a crash inside TORCH_CHECK message formatting). Use the system driver.
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
     common = [cxx, "-std=c++17", "-O2", "-fPIC", "-shared", "-D_GLIBCXX_USE_CXX11_ABI=1", "-w", *inc, binding,
               f"-L{LIB}", "-laphrodite_b200", f"-L{tlib}", "-ltorch", "-ltorch_cpu", "-ltorch_cuda", "-lc10",
               "-lc10_cuda", "-Wl,-rpath,$ORIGIN", f"-Wl,-rpath,{tlib}"]

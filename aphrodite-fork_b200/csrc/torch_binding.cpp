@@ -183,13 +183,10 @@ void convert_fp8(torch::Tensor& dst_cache, torch::Tensor& src_cache, const doubl
   check_status(st, op);
 }
 
-torch::Tensor gptq_marlin_gemm(torch::Tensor& a, torch::Tensor& b_q_weight, torch::Tensor& b_scales,
-                               torch::Tensor& b_zeros, torch::Tensor& g_idx, torch::Tensor& perm,
-                               torch::Tensor& workspace, int64_t const& b_q_type_id, int64_t size_m, int64_t size_n,
-                               int64_t size_k, bool is_k_full, bool has_zp, bool use_atomic_add, bool use_fp32_reduce,
-                               bool is_zp_float) {
+// argument checks of the reference entry point, gptq_marlin.cu:2271-2332
+void check_gemm_args(const torch::Tensor& a, const torch::Tensor& b_q_weight, const torch::Tensor& b_scales,
+                     const torch::Tensor& workspace, int64_t size_m, int64_t size_n, int64_t size_k) {
   const char* op = "gptq_marlin_gemm";
-  // argument checks of the reference entry point, gptq_marlin.cu:2271-2332
   TORCH_CHECK(a.is_cuda() && b_q_weight.is_cuda() && b_scales.is_cuda() && workspace.is_cuda(), op,
               ": tensors must be on a CUDA device");
   TORCH_CHECK(a.dim() == 2 && a.size(0) == size_m, "Shape mismatch: a.size(0) = ", a.size(0), ", size_m = ", size_m);
@@ -201,6 +198,15 @@ torch::Tensor gptq_marlin_gemm(torch::Tensor& a, torch::Tensor& b_q_weight, torc
   TORCH_CHECK(b_scales.size(1) == size_n, "b_scales dim 1 = ", b_scales.size(1), " is not size_n = ", size_n);
   TORCH_CHECK(b_q_weight.scalar_type() == at::ScalarType::Int && workspace.scalar_type() == at::ScalarType::Int, op,
               ": b_q_weight and workspace must be int32");
+}
+
+torch::Tensor gptq_marlin_gemm(torch::Tensor& a, torch::Tensor& b_q_weight, torch::Tensor& b_scales,
+                               torch::Tensor& b_zeros, torch::Tensor& g_idx, torch::Tensor& perm,
+                               torch::Tensor& workspace, int64_t const& b_q_type_id, int64_t size_m, int64_t size_n,
+                               int64_t size_k, bool is_k_full, bool has_zp, bool use_atomic_add, bool use_fp32_reduce,
+                               bool is_zp_float) {
+  const char* op = "gptq_marlin_gemm";
+  check_gemm_args(a, b_q_weight, b_scales, workspace, size_m, size_n, size_k);
   const at::cuda::OptionalCUDAGuard guard(device_of(a));
   const int dt = dtype_code(a, op);
   torch::Tensor c = torch::empty({size_m, size_n}, a.options());

@@ -1,0 +1,162 @@
+"""GPU parity: gptq_marlin_gemm through the registered torch op (-> C ABI) against the oracle.
+Mirrors /root/reference/tests/kernels/test_marlin_gemm.py:181-254 (GPTQ) and :382-441 (AWQ): inputs
+are quantised and laid out with the oracle's restatement of the reference Python (pinned by
+tests/golden/marlin_golden.npz); truth = a @ w_ref in double.
+
+Tolerances: the reference metric mean|out-ref|/mean|ref| < 0.04 (test_marlin_gemm.py:57-59,254) is
+asserted at the much tighter 5e-3, plus max|out-ref| <= 1e-2*max|ref| (bf16) / 2e-3 (f16)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import synth
+from oracle import marlin_format as mf
+from oracle import oracle
+
+pytestmark = pytest.mark.gpu
+DT = {1: torch.float16, 2: torch.bfloat16}
+
+
+def _ops():
+    import aphrodite_fork_b200 as A
+    return A.ops
+
+
+def _type_id(bits, zp):
+    return {(4, False): mf.UINT4B8, (4, True): mf.UINT4, (8, False): mf.UINT8B128, (8, True): mf.UINT8}[(bits, zp)]
+
+
+def run_gemm(a, b, s, bz, M, N, K, bits, has_zp, use_fp32_reduce=True, use_atomic_add=False):
+    ops = _ops()
+    dev = "cuda"
+    ws = torch.zeros(N // 64 * 16, dtype=torch.int32, device=dev)
+    empty_i = torch.empty(0, dtype=torch.int32, device=dev)
+    zeros = bz.to(dev) if bz is not None else empty_i
+    out = ops.gptq_marlin_gemm(a, b.to(dev), s.to(dev), zeros, empty_i, empty_i, ws, _type_id(bits, has_zp), M, N, K,
+                               True, has_zp, use_atomic_add, use_fp32_reduce, False)
+    torch.cuda.synchronize()
+    assert int(ws.abs().sum()) == 0, "workspace (lock buffer) must be left all-zero"
+    return out
+
+
+def check(out, ref64, dtype, what):
+    o = out.detach().cpu().double()
+    assert torch.isfinite(o).all(), what
+    err = (o - ref64).abs()
+    mean_rel = float(err.mean() / ref64.abs().mean())
+    max_rel = float(err.max() / ref64.abs().max())
+    assert mean_rel < 5e-3, f"{what}: mean-rel {mean_rel:.3e}"
+    assert max_rel < (1e-2 if dtype == torch.bfloat16 else 2e-3), f"{what}: max|err|/max|ref| {max_rel:.3e}"
+    return mean_rel, max_rel
+
+
+_cache = {}
+
+
+def quantized(K, N, bits, gs, zp, dtype, seed):
+    key = (K, N, bits, gs, zp, dtype, seed)
+    if key not in _cache:
+        w = synth.tensor((K, N), seed, dtype, 1.0)
+        _cache[key] = mf.marlin_quantize(w, bits, gs, zp)
+    return _cache[key]
+
+
+def case(M, K, N, gs, dtype, zp=False, seed=1, lda_pad=0, **kw):
+    w_ref, b, s, bz = quantized(K, N, 4, gs, zp, dtype, seed)
+    a_full = synth.tensor((M, K + lda_pad), seed + 100, dtype, 1.0)
+    a = a_full[:, :K]
+    ref = oracle.gemm(a.contiguous(), w_ref)
+    a_d = a_full.cuda()[:, :K]
+    out = run_gemm(a_d, b, s, bz, M, N, K, 4, zp, **kw)
+    assert out.shape == (M, N) and out.dtype == dtype
+    return check(out, ref, dtype, f"M{M} K{K} N{N} g{gs} {dtype} zp{zp}")
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("gs", [-1, 32, 64, 128])
+@pytest.mark.parametrize("M", [1, 2, 5, 8, 13, 16, 31, 32, 33, 64, 100])
+def test_gptq_marlin_gemm_sweep(dtype, gs, M):
+    # MNK_FACTORS-style shapes (test_marlin_gemm.py:45-52): K = 128*k, N = 64*n / 128*n / 256*n
+    case(M, 256, 128, gs, dtype, seed=1)
+    case(M, 512, 192, gs, dtype, seed=2)
+    case(M, 1024, 512, gs, dtype, seed=3)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("gs", [-1, 32, 64, 128])
+@pytest.mark.parametrize("M", [1, 7, 16, 40])
+def test_awq_marlin_gemm_zero_points(dtype, gs, M):
+    case(M, 512, 256, gs, dtype, zp=True, seed=7)
+    case(M, 256, 64, gs, dtype, zp=True, seed=8)
+
+
+@pytest.mark.parametrize("M", [1, 16, 64, 256])
+def test_gptq_marlin_gemm_llama_shapes(M):
+    # C3 shapes (tests/benchmarks/kernels/benchmark_shapes.py:3-8) at g128, bf16; the widest / deepest ones
+    case(M, 4096, 6144, 128, torch.bfloat16, seed=3)
+    if M <= 16:
+        case(M, 14336, 4096, 128, torch.bfloat16, seed=4)
+
+
+def test_gptq_marlin_gemm_strided_a_and_flags():
+    case(9, 512, 256, 128, torch.bfloat16, lda_pad=64, use_fp32_reduce=False)
+    case(9, 512, 256, 128, torch.float16, lda_pad=8, use_atomic_add=True)
+    # TP=8 per-rank shapes of Llama-3.1-70B: 8192x1280 (qkv), 1024x8192 (o)
+    case(4, 8192, 1280, 128, torch.bfloat16, seed=21)
+    case(4, 1024, 8192, 128, torch.bfloat16, seed=22)
+
+
+def test_gptq_marlin_gemm_golden_reference_python():
+    """Marlin tensors produced by the REFERENCE's own Python quantiser/layout code."""
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "marlin_golden.npz"))
+    for ci in range(int(g["num_cases"][0])):
+        K, N, bits, gs, zp, dtc = [int(v) for v in g[f"c{ci}_meta"]]
+        if bits != 4:
+            continue
+        dt = DT[dtc]
+        w_ref = torch.from_numpy(g[f"c{ci}_w_ref"]).view(dt)
+        b = torch.from_numpy(g[f"c{ci}_b_q_weight"])
+        s = torch.from_numpy(g[f"c{ci}_b_scales"]).view(dt)
+        bz = torch.from_numpy(g[f"c{ci}_b_zeros"]) if zp else None
+        for M in (1, 16, 37):
+            a = synth.tensor((M, K), 900 + ci + M, dt, 1.0)
+            out = run_gemm(a.cuda(), b, s, bz, M, N, K, 4, bool(zp))
+            check(out, oracle.gemm(a, w_ref), dt, f"golden {ci} M{M}")
+
+
+def test_gptq_marlin_gemm_linearity_and_zero():
+    # size-independent properties at a full Llama shape: zero input -> zero output; f(2a) = 2 f(a) exactly
+    K, N, M = 4096, 4096, 16
+    w_ref, b, s, bz = quantized(K, N, 4, 128, False, torch.bfloat16, 5)
+    a = synth.tensor((M, K), 77, torch.bfloat16, 1.0).cuda()
+    o1 = run_gemm(a, b, s, bz, M, N, K, 4, False)
+    o2 = run_gemm(a * 2, b, s, bz, M, N, K, 4, False)
+    assert torch.equal(o2, o1 * 2)
+    oz = run_gemm(torch.zeros_like(a), b, s, bz, M, N, K, 4, False)
+    assert int((oz != 0).sum()) == 0
+    assert torch.equal(run_gemm(a, b, s, bz, M, N, K, 4, False), o1), "must be deterministic run to run"
+
+
+def test_gptq_marlin_gemm_errors():
+    ops = _ops()
+    dev = "cuda"
+    K, N, M = 256, 128, 4
+    w_ref, b, s, bz = quantized(K, N, 4, 128, False, torch.bfloat16, 6)
+    a = torch.zeros(M, K, dtype=torch.bfloat16, device=dev)
+    e = torch.empty(0, dtype=torch.int32, device=dev)
+    ws = torch.zeros(N // 64 * 16, dtype=torch.int32, device=dev)
+    with pytest.raises(RuntimeError):  # wrong type id for has_zp=False
+        ops.gptq_marlin_gemm(a, b.to(dev), s.to(dev), e, e, e, ws, mf.UINT4, M, N, K, True, False, False, True, False)
+    with pytest.raises(RuntimeError):  # shape mismatch
+        ops.gptq_marlin_gemm(a, b.to(dev), s.to(dev), e, e, e, ws, mf.UINT4B8, M + 1, N, K, True, False, False, True, False)
+    with pytest.raises(RuntimeError):  # workspace too small
+        ops.gptq_marlin_gemm(a, b.to(dev), s.to(dev), e, e, e, ws[:4], mf.UINT4B8, M, N, K, True, False, False, True, False)
+    out = ops.gptq_marlin_gemm(a[:0], b.to(dev), s.to(dev), e, e, e, ws, mf.UINT4B8, 0, N, K, True, False, False, True, False)
+    assert out.shape == (0, N)
+
+
+def smoke_gemm():
+    """Used by __graft_entry__.smoke()."""
+    return case(16, 512, 256, 128, torch.bfloat16, seed=42)

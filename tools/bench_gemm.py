@@ -1,0 +1,45 @@
+"""W4A16 GEMM microbench on the C3 shapes (Llama-3.1-8B, g128): us per call, HBM GB/s on the
+algorithmic bytes (K*N/2 + K/g*N*2 + M*K*2 + M*N*2) and TFLOP/s, with rotating weight buffers > L2."""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import aphrodite_fork_b200 as A
+
+UINT4B8 = 1125899907892224
+SHAPES = {"qkv": (4096, 6144), "o": (4096, 4096), "gate_up": (4096, 28672), "down": (14336, 4096)}
+
+
+def bench(name, K, N, M, g=128, iters=50):
+    dev = "cuda"
+    nbuf = max(2, int(300e6 // (K * N // 2)) + 1)
+    gen = torch.Generator(device=dev).manual_seed(0)
+    bs = [torch.randint(-2**31, 2**31 - 1, (K // 16, N * 2), dtype=torch.int32, device=dev, generator=gen) for _ in range(nbuf)]
+    ss = [(torch.rand(K // g, N, device=dev, generator=gen) * 0.01 + 0.005).to(torch.bfloat16) for _ in range(nbuf)]
+    a = torch.randn(M, K, device=dev, generator=gen).to(torch.bfloat16)
+    e = torch.empty(0, dtype=torch.int32, device=dev)
+    ws = torch.zeros(N // 64 * 16, dtype=torch.int32, device=dev)
+    f = lambda i: A.ops.gptq_marlin_gemm(a, bs[i % nbuf], ss[i % nbuf], e, e, e, ws, UINT4B8, M, N, K, True)
+    for i in range(5):
+        f(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters):
+        f(i)
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) / iters * 1e3
+    byt = K * N // 2 + (K // g) * N * 2 + M * K * 2 + M * N * 2
+    return {"shape": name, "K": K, "N": N, "M": M, "us": round(us, 2), "GBps": round(byt / us / 1e3, 1),
+            "TFLOPs": round(2 * M * N * K / us / 1e6, 1)}
+
+
+if __name__ == "__main__":
+    A.load()
+    ms = [int(x) for x in sys.argv[1].split(",")] if len(sys.argv) > 1 else [1, 16, 64, 256]
+    for name, (K, N) in SHAPES.items():
+        for M in ms:
+            print(json.dumps(bench(name, K, N, M)), flush=True)
