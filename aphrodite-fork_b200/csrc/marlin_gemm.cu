@@ -14,378 +14,57 @@
 //     per group:  acc += s[g,n] * (sum_k a_k (OFF + q_kn) - (OFF + zp[g,n]) * sum_k a_k), with
 //     sum_k a_k produced by one extra MMA against an all-ones tile. 7 ALU ops per 8 weights
 //     instead of the reference's 15;
-//   * stream-K over (n-slice, k-tile) work items with a deterministic "last arriver reduces"
-//     fix-up through an fp32 scratch (no spin locks; the caller's lock buffer is used as the
-//     per-slice arrival counter and is left all-zero);
-//   * 4-stage cp.async pipeline for weights, activations (XOR-swizzled for ldmatrix), scales
-//     and zero points.
+//   * one CTA per (output slice of 64/128/256 columns, k chunk); K is split only as far as needed to
+//     put a CTA on every SM, partial tiles meet in an fp32 scratch with a deterministic "last arriver
+//     reduces" fix-up (no spin locks; the caller's lock buffer is the per-slice arrival counter and is
+//     left all-zero);
+//   * a dedicated producer warp streams weights, activations, scales and zero points with 1-D
+//     bulk async copies (TMA engine, SASS UBLKCP) into a 4-6 stage ring, full/empty mbarriers,
+//     no CTA-wide barrier in the main loop; each consumer warp owns 64 output columns and whole
+//     128-row stages (warps of narrower slices take alternate stages), so the per-group flush is
+//     amortised over 8 k16 steps.
 // Large batches (M >= 64) are meant for the tcgen05 path; here they run as chunks of 32 rows.
-#include <type_traits>
-
-#include "common.cuh"
+#include "marlin_gemm_kernel.cuh"
 
 namespace aphb200 {
 namespace mg {
 
-constexpr int KT = 128;    // k rows per pipeline stage
-constexpr int STAGES = 4;
-constexpr int KWARPS = 4;  // warps along k inside a stage (32 rows each)
-
-struct Params {
-  const void* a;
-  const uint8_t* b;   // Marlin weights, bytes
-  const uint8_t* s;   // scales, bytes
-  const uint8_t* zp;  // zero points, bytes (or null)
-  void* c;
-  float* scratch;
-  int* counters;
-  int N, K;
-  int64_t lda;
-  int m0, m_rows;      // this launch covers rows [m0, m0 + m_rows) of a / c
-  int group_size;      // == K for channelwise
-  int k_tiles, n_slices, total_tiles, tiles_per_cta, max_contrib;
-};
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
-  const int sz = valid ? 16 : 0;  // src-size 0: the 16 destination bytes are zero-filled
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-__device__ __forceinline__ void ldsm_x2(uint32_t addr, uint32_t& r0, uint32_t& r1) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(addr));
-}
-__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
-               : "r"(addr));
-}
-template <bool F16>
-__device__ __forceinline__ void mma16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
-                                         uint32_t b1) {
-  if constexpr (F16) {
-    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
-  } else {
-    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
-  }
-}
-
-template <typename scalar_t, int NB, int NWN>
-struct Cfg {
-  static constexpr bool F16 = std::is_same<scalar_t, __half>::value;
-  static constexpr int NT = 64 * NWN;          // output columns per CTA slice
-  static constexpr int MP = 8 * NB;            // padded batch rows per launch
-  static constexpr int THREADS = 32 * KWARPS * NWN;
-  static constexpr int B_BYTES = 8 * NT * 8;   // 8 k16-rows x NT columns of int4
-  static constexpr int A_BYTES = MP * KT * 2;
-  static constexpr int S_BYTES = 4 * NT * 2;   // up to 4 groups per stage
-  static constexpr int Z_BYTES = 4 * (NT / 8) * 4;
-  static constexpr int STAGE_BYTES = B_BYTES + A_BYTES + S_BYTES + Z_BYTES;
-  static constexpr int RP = NT + 4;            // padded row of the reduction buffer (floats)
-  static constexpr int RED_BYTES = KWARPS * MP * RP * 4;
-  static constexpr int PIPE_BYTES = STAGES * STAGE_BYTES;
-  static constexpr int SMEM_BYTES = PIPE_BYTES > RED_BYTES ? PIPE_BYTES : RED_BYTES;
-  static constexpr uint32_t MAGIC = F16 ? 0x64006400u : 0x43004300u;  // 1024 / 128 as packed pairs
-  static constexpr float OFFSET = F16 ? 1024.f : 128.f;
-  static constexpr uint32_t ONES = F16 ? 0x3c003c00u : 0x3f803f80u;
-};
-
-template <typename scalar_t, int NB, int NWN, bool HAS_ZP>
-__global__ void __launch_bounds__(Cfg<scalar_t, NB, NWN>::THREADS) marlin_w4a16_kernel(const Params p) {
-  using C = Cfg<scalar_t, NB, NWN>;
-  constexpr bool F16 = C::F16;
-  constexpr int NT = C::NT, MP = C::MP, THREADS = C::THREADS;
-  extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ int s_last;
-
-  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  const int wn = w % NWN, wk = w / NWN;
-  const int g = lane >> 2, t = lane & 3;
-  const bool grouped = p.group_size < p.K;
-  const int gps = grouped ? KT / p.group_size : 0;  // groups per stage (1, 2, 4)
-
-  const int tile_begin = blockIdx.x * p.tiles_per_cta;
-  const int tile_end = min(tile_begin + p.tiles_per_cta, p.total_tiles);
-  const uint32_t smem_base = smem_u32(smem);
-  const uint8_t* a_bytes = (const uint8_t*)p.a;
-
-  int cur = tile_begin;
-  while (cur < tile_end) {
-    const int slice = cur / p.k_tiles;
-    const int kb = cur % p.k_tiles;
-    const int ke = min(p.k_tiles, kb + (tile_end - cur));
-    const int nk = ke - kb;
-
-    // ---------------- stage loader ----------------
-    auto load_stage = [&](int it) {
-      const int st = it % STAGES;
-      const int k0 = (kb + it) * KT;
-      const uint32_t sB = smem_base + st * C::STAGE_BYTES;
-      const uint32_t sA = sB + C::B_BYTES;
-      const uint32_t sS = sA + C::A_BYTES;
-      const uint32_t sZ = sS + C::S_BYTES;
-      // weights: 8 rows of NT*8 bytes, contiguous per row in global memory
-      constexpr int BCH = C::B_BYTES / 16;
-#pragma unroll
-      for (int c = tid; c < BCH; c += THREADS) {
-        const int row = c / (NT / 2), col = c % (NT / 2);
-        const uint8_t* src = p.b + ((int64_t)(k0 / 16 + row) * p.N + (int64_t)slice * NT) * 8 + col * 16;
-        cp_async16(sB + row * (NT * 8) + col * 16, src, true);
-      }
-      // activations: MP rows x 16 chunks, XOR swizzle on the chunk index
-      constexpr int ACH = MP * 16;
-#pragma unroll
-      for (int c = tid; c < ACH; c += THREADS) {
-        const int row = c >> 4, ch = c & 15;
-        const bool valid = row < p.m_rows;
-        const uint8_t* src = a_bytes + ((int64_t)(p.m0 + (valid ? row : 0)) * p.lda + k0 + ch * 8) * 2;
-        cp_async16(sA + row * 256 + ((ch ^ (row & 7)) * 16), src, valid);
-      }
-      if (grouped) {
-        const int g0 = k0 / p.group_size;
-        const int sch = gps * (NT / 8);
-        for (int c = tid; c < sch; c += THREADS) {
-          const int gr = c / (NT / 8), cc = c % (NT / 8);
-          const uint8_t* src = p.s + ((int64_t)(g0 + gr) * p.N + (int64_t)slice * NT) * 2 + cc * 16;
-          cp_async16(sS + gr * (NT * 2) + cc * 16, src, true);
-        }
-        if constexpr (HAS_ZP) {
-          const int zch = gps * (NT / 32);
-          for (int c = tid; c < zch; c += THREADS) {
-            const int gr = c / (NT / 32), cc = c % (NT / 32);
-            const uint8_t* src = p.zp + ((int64_t)(g0 + gr) * (p.N / 8) + (int64_t)slice * (NT / 8)) * 4 + cc * 16;
-            cp_async16(sZ + gr * (NT / 8) * 4 + cc * 16, src, true);
-          }
-        }
-      }
-    };
-
-    float acc[4][NB][4], part[4][NB][4], asum[NB][4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-#pragma unroll
-      for (int b = 0; b < NB; ++b)
-#pragma unroll
-        for (int e = 0; e < 4; ++e) acc[j][b][e] = part[j][b][e] = 0.f;
-#pragma unroll
-    for (int b = 0; b < NB; ++b)
-#pragma unroll
-      for (int e = 0; e < 4; ++e) asum[b][e] = 0.f;
-
-    // acc += s * (part - zc * asum); part = asum = 0. sc[j][h], zc[j][h]: tile j, row g (h=0) / g+8 (h=1)
-    auto flush = [&](const float (&sc)[4][2], const float (&zc)[4][2]) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-#pragma unroll
-        for (int b = 0; b < NB; ++b) {
-          acc[j][b][0] = fmaf(sc[j][0], fmaf(-zc[j][0], asum[b][0], part[j][b][0]), acc[j][b][0]);
-          acc[j][b][1] = fmaf(sc[j][0], fmaf(-zc[j][0], asum[b][1], part[j][b][1]), acc[j][b][1]);
-          acc[j][b][2] = fmaf(sc[j][1], fmaf(-zc[j][1], asum[b][0], part[j][b][2]), acc[j][b][2]);
-          acc[j][b][3] = fmaf(sc[j][1], fmaf(-zc[j][1], asum[b][1], part[j][b][3]), acc[j][b][3]);
-          part[j][b][0] = part[j][b][1] = part[j][b][2] = part[j][b][3] = 0.f;
-        }
-#pragma unroll
-      for (int b = 0; b < NB; ++b) asum[b][0] = asum[b][1] = asum[b][2] = asum[b][3] = 0.f;
-    };
-    auto decode_zp = [&](uint32_t zword, float (&zc)[4][2]) {
-      // nibble e' of the packed word holds column block interleave[e'] = {0,2,4,6,1,3,5,7}[e']
-      constexpr int inv[8] = {0, 4, 1, 5, 2, 6, 3, 7};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        zc[j][0] = C::OFFSET + (float)((zword >> (4 * inv[2 * j])) & 0xf);
-        zc[j][1] = C::OFFSET + (float)((zword >> (4 * inv[2 * j + 1])) & 0xf);
-      }
-    };
-
-    // ---------------- pipeline ----------------
-#pragma unroll 1
-    for (int s = 0; s < STAGES - 1; ++s) {
-      if (s < nk) load_stage(s);
-      cp_async_commit();
-    }
-#pragma unroll 1
-    for (int it = 0; it < nk; ++it) {
-      cp_async_wait<STAGES - 2>();
-      __syncthreads();
-      if (it + STAGES - 1 < nk) load_stage(it + STAGES - 1);
-      cp_async_commit();
-
-      const int st = it % STAGES;
-      const uint32_t sB = smem_base + st * C::STAGE_BYTES;
-      const uint32_t sA = sB + C::B_BYTES;
-#pragma unroll
-      for (int jj = 0; jj < 2; ++jj) {
-        const int kk = wk * 2 + jj;
-        uint4 bq;
-        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
-                     : "=r"(bq.x), "=r"(bq.y), "=r"(bq.z), "=r"(bq.w)
-                     : "r"(sB + kk * (NT * 8) + wn * 512 + lane * 16));
-        uint32_t bf[NB][2];
-        if constexpr (NB == 1) {
-          const int mi = (lane >> 3) & 1, r = lane & 7;
-          ldsm_x2(sA + r * 256 + (((kk * 2 + mi) ^ r) * 16), bf[0][0], bf[0][1]);
-        } else {
-#pragma unroll
-          for (int bb = 0; bb < NB; bb += 2) {
-            const int mi = lane >> 3, r = lane & 7;
-            const int row = (bb + (mi >> 1)) * 8 + r;
-            ldsm_x4(sA + row * 256 + (((kk * 2 + (mi & 1)) ^ r) * 16), bf[bb][0], bf[bb][1], bf[bb + 1][0],
-                    bf[bb + 1][1]);
-          }
-        }
-#pragma unroll
-        for (int b = 0; b < NB; ++b) mma16816<F16>(asum[b], C::ONES, C::ONES, C::ONES, C::ONES, bf[b][0], bf[b][1]);
-        const uint32_t qs[4] = {bq.x, bq.y, bq.z, bq.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const uint32_t q = qs[j];
-          const uint32_t a0 = (q & 0x000f000fu) | C::MAGIC;
-          const uint32_t a2 = ((q >> 4) & 0x000f000fu) | C::MAGIC;
-          const uint32_t a1 = ((q >> 8) & 0x000f000fu) | C::MAGIC;
-          const uint32_t a3 = ((q >> 12) & 0x000f000fu) | C::MAGIC;
-#pragma unroll
-          for (int b = 0; b < NB; ++b) mma16816<F16>(part[j][b], a0, a1, a2, a3, bf[b][0], bf[b][1]);
-        }
-      }
-      if (grouped) {
-        const int k0 = (kb + it) * KT;
-        const int gl = (k0 + wk * 32) / p.group_size - k0 / p.group_size;
-        const uint8_t* sSp = smem + st * C::STAGE_BYTES + C::B_BYTES + C::A_BYTES;
-        const uint4 sv = *reinterpret_cast<const uint4*>(sSp + gl * (NT * 2) + wn * 128 + g * 16);
-        const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w};
-        float sc[4][2], zc[4][2];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if constexpr (F16) {
-            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&sw[j]));
-            sc[j][0] = f.x;
-            sc[j][1] = f.y;
-          } else {
-            const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&sw[j]));
-            sc[j][0] = f.x;
-            sc[j][1] = f.y;
-          }
-          zc[j][0] = zc[j][1] = C::OFFSET + 8.f;
-        }
-        if constexpr (HAS_ZP) {
-          const uint32_t zword =
-              *reinterpret_cast<const uint32_t*>(sSp + C::S_BYTES + gl * (NT / 8) * 4 + wn * 32 + g * 4);
-          decode_zp(zword, zc);
-        }
-        flush(sc, zc);
-      }
-    }
-    if (!grouped) {
-      // channelwise: one scale row, "single" permutation over 32-column blocks (marlin_utils.py:204-213)
-      float sc[4][2], zc[4][2];
-      const scalar_t* srow = reinterpret_cast<const scalar_t*>(p.s) + (int64_t)slice * NT + wn * 64;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int pos = (j >> 1) * 32 + 8 * (g >> 1) + (g & 1) + 4 * (j & 1);
-        sc[j][0] = ScalarTraits<scalar_t>::to_float(srow[pos]);
-        sc[j][1] = ScalarTraits<scalar_t>::to_float(srow[pos + 2]);
-        zc[j][0] = zc[j][1] = C::OFFSET + 8.f;
-      }
-      if constexpr (HAS_ZP) {
-        const uint32_t zword = *reinterpret_cast<const uint32_t*>(p.zp + ((int64_t)slice * (NT / 8) + wn * 8 + g) * 4);
-        decode_zp(zword, zc);
-      }
-      flush(sc, zc);
-    }
-
-    // ---------------- reduce the 4 k-warps through shared memory ----------------
-    cp_async_wait<0>();
-    __syncthreads();
-    float* red = reinterpret_cast<float*>(smem);
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-#pragma unroll
-      for (int b = 0; b < NB; ++b) {
-        float* r0 = red + (size_t)(wk * MP + b * 8 + 2 * t) * C::RP + wn * 64 + 16 * j + g;
-        r0[0] = acc[j][b][0];
-        r0[C::RP] = acc[j][b][1];
-        r0[8] = acc[j][b][2];
-        r0[C::RP + 8] = acc[j][b][3];
-      }
-    __syncthreads();
-
-    const int first_cta = (slice * p.k_tiles) / p.tiles_per_cta;
-    const int last_cta = ((slice + 1) * p.k_tiles - 1) / p.tiles_per_cta;
-    const int ncontrib = last_cta - first_cta + 1;
-    scalar_t* cout = reinterpret_cast<scalar_t*>(p.c);
-    const int nelem = p.m_rows * NT;
-    if (ncontrib == 1) {
-      for (int idx = tid; idx < nelem; idx += THREADS) {
-        const int m = idx / NT, n = idx % NT;
-        float v = 0.f;
-#pragma unroll
-        for (int kw = 0; kw < KWARPS; ++kw) v += red[(size_t)(kw * MP + m) * C::RP + n];
-        cout[(int64_t)(p.m0 + m) * p.N + (int64_t)slice * NT + n] = ScalarTraits<scalar_t>::from_float(v);
-      }
-    } else {
-      float* mine = p.scratch + ((size_t)slice * p.max_contrib + (blockIdx.x - first_cta)) * (size_t)(MP * NT);
-      for (int idx = tid; idx < nelem; idx += THREADS) {
-        const int m = idx / NT, n = idx % NT;
-        float v = 0.f;
-#pragma unroll
-        for (int kw = 0; kw < KWARPS; ++kw) v += red[(size_t)(kw * MP + m) * C::RP + n];
-        mine[idx] = v;
-      }
-      __threadfence();
-      __syncthreads();
-      if (tid == 0) s_last = (atomicAdd(&p.counters[slice], 1) == ncontrib - 1);
-      __syncthreads();
-      if (s_last) {
-        __threadfence();
-        const float* base = p.scratch + (size_t)slice * p.max_contrib * (size_t)(MP * NT);
-        for (int idx = tid; idx < nelem; idx += THREADS) {
-          float v = 0.f;
-          for (int ci = 0; ci < ncontrib; ++ci) v += __ldcg(base + (size_t)ci * (MP * NT) + idx);  // fixed order
-          const int m = idx / NT, n = idx % NT;
-          cout[(int64_t)(p.m0 + m) * p.N + (int64_t)slice * NT + n] = ScalarTraits<scalar_t>::from_float(v);
-        }
-        if (tid == 0) p.counters[slice] = 0;  // leave the caller's lock buffer all-zero
-      }
-    }
-    __syncthreads();  // the reduction buffer aliases the pipeline stages of the next segment
-    cur += nk;
-  }
-}
-
 struct Plan {
-  int nwn, tiles_per_cta, grid, max_contrib, k_tiles, n_slices;
+  int nt, split, tiles_per_chunk, grid, k_tiles, n_slices;
 };
 
+// Decomposition: output slices of NT columns x `split` equal k chunks, one CTA each. Prefer no
+// split (no partial traffic, no fix-up); split K only as far as needed to put a CTA on every SM.
 static Plan make_plan(int64_t N, int64_t K, int nb) {
-  Plan pl;
-  pl.nwn = (N % 128 == 0) ? 2 : 1;
-  const int nt = 64 * pl.nwn;
-  pl.k_tiles = (int)(K / KT);
-  pl.n_slices = (int)(N / nt);
-  const int64_t total = (int64_t)pl.k_tiles * pl.n_slices;
-  const int ctas_per_sm = nb <= 2 ? 2 : 1;
-  int64_t want = (int64_t)sm_count() * ctas_per_sm;
-  int64_t tpc = (total + want - 1) / want;
-  if (tpc < 2 && pl.k_tiles >= 2) tpc = 2;  // at least two k-tiles per CTA: bounds the fix-up fan-in
-  if (tpc < 1) tpc = 1;
-  pl.tiles_per_cta = (int)tpc;
-  pl.grid = (int)((total + tpc - 1) / tpc);
-  pl.max_contrib = (int)((pl.k_tiles + tpc - 1) / tpc) + 1;
-  return pl;
+  const int sms = sm_count();
+  const int k_tiles = (int)(K / KT);
+  const int nts[3] = {256, 128, 64};
+  Plan best{};
+  bool found = false;
+  for (int split = 1; split <= 8 && !found; ++split) {
+    if (split > k_tiles) break;
+    for (int i = 0; i < 3; ++i) {
+      const int nt = nts[i];
+      if (N % nt != 0) continue;
+      const int64_t ctas = (N / nt) * split;
+      best = Plan{nt, split, (k_tiles + split - 1) / split, (int)ctas, k_tiles, (int)(N / nt)};
+      if (ctas >= (int64_t)sms * 9 / 10) {
+        found = true;
+        break;
+      }
+    }
+  }
+  // tiles_per_chunk may leave the last chunk empty when split does not divide k_tiles: shrink split
+  while (best.split > 1 && (best.split - 1) * best.tiles_per_chunk >= k_tiles) --best.split;
+  best.grid = best.n_slices * best.split;
+  (void)nb;
+  return best;
 }
 
-template <typename scalar_t, int NB, int NWN, bool HAS_ZP>
+template <typename scalar_t, int NB, int NT, bool HAS_ZP>
 static int launch(const Params& p, int grid, cudaStream_t stream) {
-  using C = Cfg<scalar_t, NB, NWN>;
-  auto kern = marlin_w4a16_kernel<scalar_t, NB, NWN, HAS_ZP>;
+  using C = Cfg<scalar_t, NB, NT>;
+  auto kern = marlin_w4a16_kernel<scalar_t, NB, NT, HAS_ZP>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -394,16 +73,21 @@ static int launch(const Params& p, int grid, cudaStream_t stream) {
       return set_error(APH_ERR_CUDA, "gptq_marlin_gemm: cannot reserve %d bytes of shared memory", C::SMEM_BYTES);
     attr_set[dev] = true;
   }
-  kern<<<grid, C::THREADS, C::SMEM_BYTES, stream>>>(p);
+  kern<<<grid, THREADS, C::SMEM_BYTES, stream>>>(p);
   APH_LAUNCH_CHECK();
   return APH_OK;
 }
 
 template <typename scalar_t, int NB>
 static int launch_nb(const Params& p, const Plan& pl, bool has_zp, cudaStream_t stream) {
-  if (pl.nwn == 2)
-    return has_zp ? launch<scalar_t, NB, 2, true>(p, pl.grid, stream) : launch<scalar_t, NB, 2, false>(p, pl.grid, stream);
-  return has_zp ? launch<scalar_t, NB, 1, true>(p, pl.grid, stream) : launch<scalar_t, NB, 1, false>(p, pl.grid, stream);
+  switch (pl.nt) {
+    case 256:
+      return has_zp ? launch<scalar_t, NB, 256, true>(p, pl.grid, stream) : launch<scalar_t, NB, 256, false>(p, pl.grid, stream);
+    case 128:
+      return has_zp ? launch<scalar_t, NB, 128, true>(p, pl.grid, stream) : launch<scalar_t, NB, 128, false>(p, pl.grid, stream);
+    default:
+      return has_zp ? launch<scalar_t, NB, 64, true>(p, pl.grid, stream) : launch<scalar_t, NB, 64, false>(p, pl.grid, stream);
+  }
 }
 
 template <typename scalar_t>
@@ -415,12 +99,10 @@ static int run_typed(Params p, int64_t M, bool has_zp, float* scratch, size_t sc
     p.m0 = (int)m0;
     p.m_rows = rows;
     p.k_tiles = pl.k_tiles;
-    p.n_slices = pl.n_slices;
-    p.total_tiles = pl.k_tiles * pl.n_slices;
-    p.tiles_per_cta = pl.tiles_per_cta;
-    p.max_contrib = pl.max_contrib;
-    const size_t need = (size_t)pl.n_slices * pl.max_contrib * (8 * nb) * (64 * pl.nwn) * sizeof(float);
-    APH_CHECK(scratch != nullptr && scratch_bytes >= need, APH_ERR_WORKSPACE,
+    p.split = pl.split;
+    p.tiles_per_chunk = pl.tiles_per_chunk;
+    const size_t need = pl.split > 1 ? (size_t)pl.n_slices * pl.split * (8 * nb) * pl.nt * sizeof(float) : 0;
+    APH_CHECK(need == 0 || (scratch != nullptr && scratch_bytes >= need), APH_ERR_WORKSPACE,
               "gptq_marlin_gemm: scratch of %zu bytes needed, %zu given", need, scratch_bytes);
     p.scratch = scratch;
     int st;
@@ -451,7 +133,7 @@ extern "C" size_t aph_gptq_marlin_gemm_scratch_bytes(int64_t size_m, int64_t siz
   size_t worst = 0;
   for (int nb = 1; nb <= 4; nb *= 2) {
     const mg::Plan pl = mg::make_plan(size_n, size_k, nb);
-    const size_t need = (size_t)pl.n_slices * pl.max_contrib * (8 * nb) * (64 * pl.nwn) * sizeof(float);
+    const size_t need = pl.split > 1 ? (size_t)pl.n_slices * pl.split * (8 * nb) * pl.nt * sizeof(float) : 0;
     if (need > worst) worst = need;
   }
   return worst;
@@ -498,7 +180,7 @@ extern "C" int aph_gptq_marlin_gemm(void* c, const void* a, const void* b_q_weig
   if (size_m == 0) return APH_OK;
 
   mg::Params p;
-  p.a = a;
+  p.a = (const uint8_t*)a;
   p.b = (const uint8_t*)b_q_weight;
   p.s = (const uint8_t*)b_scales;
   p.zp = has_zp ? (const uint8_t*)b_zeros : nullptr;

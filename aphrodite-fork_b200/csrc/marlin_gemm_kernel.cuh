@@ -1,0 +1,309 @@
+// W4A16 dequant-GEMM kernel on Marlin-format weights (small / medium batch path, mma.sync).
+// See marlin_gemm.cu for the design summary.
+#pragma once
+#include <type_traits>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace aphb200 {
+namespace mg {
+
+using namespace ::aphb200::ptx;
+
+constexpr int KT = 128;        // k rows per pipeline stage (= 8 k16-rows of the Marlin layout)
+constexpr int CONSUMERS = 4;   // consumer warps per CTA (+ 1 producer warp)
+constexpr int THREADS = (CONSUMERS + 1) * 32;
+constexpr int A_ROW = 272;     // bytes per activation row in shared memory: 256 + 16 pad (conflict-free ldmatrix)
+
+struct Params {
+  const uint8_t* a;   // activations, bytes
+  const uint8_t* b;   // Marlin weights, bytes
+  const uint8_t* s;   // scales, bytes
+  const uint8_t* zp;  // zero points, bytes (or null)
+  void* c;
+  float* scratch;      // [n_slices][split][MP*NT] fp32 partials (split > 1 only)
+  int* counters;       // [n_slices] arrival counters, all-zero on entry and on exit
+  int N, K;
+  int64_t lda;         // elements
+  int m0, m_rows;      // this launch covers rows [m0, m0 + m_rows) of a / c
+  int group_size;      // == K for channelwise
+  int k_tiles;         // K / 128
+  int split;           // CTAs sharing one output slice (plain split-K over equal k chunks)
+  int tiles_per_chunk; // k-tiles per CTA
+};
+
+template <typename scalar_t, int NB, int NT>
+struct Cfg {
+  static constexpr bool F16 = std::is_same<scalar_t, __half>::value;
+  static constexpr int NWN = NT / 64;                 // consumer warps along n (64 columns each)
+  static constexpr int KG = CONSUMERS / NWN;          // stage groups: warps of group wg consume stages it % KG == wg
+  static constexpr int MP = 8 * NB;                   // padded batch rows per launch
+  static constexpr int B_BYTES = 8 * NT * 8;
+  static constexpr int A_BYTES = MP * A_ROW;
+  static constexpr int S_BYTES = 4 * NT * 2;          // up to 4 groups per stage
+  static constexpr int Z_BYTES = 4 * (NT / 8) * 4;
+  static constexpr int STAGE_BYTES = B_BYTES + A_BYTES + S_BYTES + Z_BYTES;
+  static constexpr int RP = NT + 4;                   // padded row of the reduction buffer (floats)
+  static constexpr int RED_BYTES = KG * MP * RP * 4;
+  static constexpr int CTAS_PER_SM = NB <= 2 ? 2 : 1;
+  static constexpr int BUDGET = (224 * 1024) / CTAS_PER_SM - 1024 - RED_BYTES - 256;
+  static constexpr int STAGES = BUDGET / STAGE_BYTES > 12 ? 12 : BUDGET / STAGE_BYTES;
+  static_assert(STAGES >= 3 && STAGES > KG, "pipeline too shallow");
+  static constexpr int BAR_BYTES = 2 * STAGES * 8;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + RED_BYTES + BAR_BYTES;
+  static constexpr uint32_t MAGIC = F16 ? 0x64006400u : 0x43004300u;  // 1024 / 128 as packed pairs
+  static constexpr float OFFSET = F16 ? 1024.f : 128.f;
+  static constexpr uint32_t ONES = F16 ? 0x3c003c00u : 0x3f803f80u;
+};
+
+template <typename scalar_t, int NB, int NT, bool HAS_ZP>
+__global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM) marlin_w4a16_kernel(const Params p) {
+  using C = Cfg<scalar_t, NB, NT>;
+  constexpr bool F16 = C::F16;
+  constexpr int MP = C::MP, STAGES = C::STAGES, NWN = C::NWN, KG = C::KG;
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ int s_last;
+
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const bool grouped = p.group_size < p.K;
+  const int gps = grouped ? KT / p.group_size : 0;  // groups per stage (1, 2, 4)
+  const int slice = blockIdx.x / p.split, chunk = blockIdx.x % p.split;
+  const int kb = chunk * p.tiles_per_chunk;
+  const int nk = min(p.k_tiles, kb + p.tiles_per_chunk) - kb;  // > 0 by construction
+  const uint32_t smem_base = smem_u32(smem);
+  float* red = reinterpret_cast<float*>(smem + STAGES * C::STAGE_BYTES);
+  const uint32_t full_bar = smem_base + STAGES * C::STAGE_BYTES + C::RED_BYTES;
+  const uint32_t empty_bar = full_bar + STAGES * 8;
+
+  // zero the activation rows that are never copied (rows >= m_rows), then init the barriers
+  for (int i = tid; i < STAGES * (C::A_BYTES / 16); i += THREADS) {
+    const int st = i / (C::A_BYTES / 16), off = (i % (C::A_BYTES / 16)) * 16;
+    if (off / A_ROW >= p.m_rows) *reinterpret_cast<uint4*>(smem + st * C::STAGE_BYTES + C::B_BYTES + off) = make_uint4(0, 0, 0, 0);
+  }
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar + s * 8, 1);
+      mbar_init(empty_bar + s * 8, NWN);  // a stage is consumed by the NWN warps of one stage group
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  if (w == CONSUMERS) {
+    // ============================ producer warp: bulk async copies ============================
+    const uint32_t stage_tx = (uint32_t)(C::B_BYTES + p.m_rows * 256 + gps * NT * 2 + (HAS_ZP ? gps * (NT / 8) * 4 : 0));
+    // per-lane source pointers for k-tile kb, advanced by constant strides per k-tile
+    const uint8_t* src_b = p.b + ((int64_t)(kb * 8 + (lane & 7)) * p.N + (int64_t)slice * NT) * 8;
+    const int64_t step_b = (int64_t)8 * p.N * 8;
+    const uint8_t* src_a = p.a + ((int64_t)(p.m0 + (lane < p.m_rows ? lane : 0)) * p.lda + (int64_t)kb * KT) * 2;
+    const int gr = lane & 3;
+    const uint8_t* src_s = grouped ? p.s + ((int64_t)(kb * gps + gr) * p.N + (int64_t)slice * NT) * 2 : p.s;
+    const uint8_t* src_z =
+        (HAS_ZP && grouped) ? p.zp + ((int64_t)(kb * gps + gr) * (p.N / 8) + (int64_t)slice * (NT / 8)) * 4 : p.zp;
+    const int64_t step_s = (int64_t)gps * p.N * 2, step_z = (int64_t)gps * (p.N / 8) * 4;
+#pragma unroll 1
+    for (int it = 0; it < nk; ++it) {
+      const int st = it % STAGES;
+      mbar_wait(empty_bar + st * 8, ((it / STAGES) & 1) ^ 1);
+      const uint32_t sB = smem_base + st * C::STAGE_BYTES;
+      const uint32_t fb = full_bar + st * 8;
+      if (lane == 0) mbar_expect_tx(fb, stage_tx);
+      __syncwarp();
+      if (lane < 8) {
+        bulk_g2s(sB + lane * (NT * 8), src_b, NT * 8, fb);
+      } else if (lane < 12) {
+        if (gr < gps) bulk_g2s(sB + C::B_BYTES + C::A_BYTES + gr * (NT * 2), src_s, NT * 2, fb);
+      } else if (lane < 16) {
+        if constexpr (HAS_ZP) {
+          if (gr < gps) bulk_g2s(sB + C::B_BYTES + C::A_BYTES + C::S_BYTES + gr * (NT / 8) * 4, src_z, (NT / 8) * 4, fb);
+        }
+      }
+      if (lane < p.m_rows) bulk_g2s(sB + C::B_BYTES + lane * A_ROW, src_a, 256, fb);
+      src_b += step_b;
+      src_a += 256;
+      src_s += step_s;
+      src_z += step_z;
+    }
+    return;
+  }
+
+  // ================================ consumer warps ================================
+  const int wn = w % NWN, wg = w / NWN;
+  const int g = lane >> 2, t = lane & 3;
+  const uint32_t offB = (uint32_t)(wn * 512 + lane * 16);
+  uint32_t offA;  // ldmatrix row address of k16-row 0
+  if constexpr (NB == 1) {
+    offA = (uint32_t)(C::B_BYTES + (lane & 7) * A_ROW + (((lane >> 3) & 1) * 16));
+  } else {
+    offA = (uint32_t)(C::B_BYTES + (((lane >> 4) & 1) * 8 + (lane & 7)) * A_ROW + (((lane >> 3) & 1) * 16));
+  }
+
+  float acc[4][NB][4], part[4][NB][4], asum[NB][4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int b = 0; b < NB; ++b)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[j][b][e] = part[j][b][e] = 0.f;
+#pragma unroll
+  for (int b = 0; b < NB; ++b)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) asum[b][e] = 0.f;
+
+  // acc += s * (part - zc * asum); part = asum = 0.   sc[j][h], zc[j][h]: tile j, row g (h=0) / g+8 (h=1)
+  auto flush = [&](const float (&sc)[4][2], const float (&zc)[4][2]) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int b = 0; b < NB; ++b) {
+        acc[j][b][0] = fmaf(sc[j][0], fmaf(-zc[j][0], asum[b][0], part[j][b][0]), acc[j][b][0]);
+        acc[j][b][1] = fmaf(sc[j][0], fmaf(-zc[j][0], asum[b][1], part[j][b][1]), acc[j][b][1]);
+        acc[j][b][2] = fmaf(sc[j][1], fmaf(-zc[j][1], asum[b][0], part[j][b][2]), acc[j][b][2]);
+        acc[j][b][3] = fmaf(sc[j][1], fmaf(-zc[j][1], asum[b][1], part[j][b][3]), acc[j][b][3]);
+        part[j][b][0] = part[j][b][1] = part[j][b][2] = part[j][b][3] = 0.f;
+      }
+#pragma unroll
+    for (int b = 0; b < NB; ++b) asum[b][0] = asum[b][1] = asum[b][2] = asum[b][3] = 0.f;
+  };
+  auto decode_zp = [&](uint32_t zword, float (&zc)[4][2]) {
+    // nibble e' of the packed word holds column block interleave[e'] = {0,2,4,6,1,3,5,7}[e']
+    constexpr int inv[8] = {0, 4, 1, 5, 2, 6, 3, 7};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      zc[j][0] = C::OFFSET + (float)((zword >> (4 * inv[2 * j])) & 0xf);
+      zc[j][1] = C::OFFSET + (float)((zword >> (4 * inv[2 * j + 1])) & 0xf);
+    }
+  };
+  auto flush_from_smem = [&](const uint8_t* stage, int gl) {
+    const uint8_t* sSp = stage + C::B_BYTES + C::A_BYTES;
+    const uint4 sv = *reinterpret_cast<const uint4*>(sSp + gl * (NT * 2) + wn * 128 + g * 16);
+    const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w};
+    float sc[4][2], zc[4][2];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if constexpr (F16) {
+        const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&sw[j]));
+        sc[j][0] = f.x;
+        sc[j][1] = f.y;
+      } else {
+        sc[j][0] = __uint_as_float(sw[j] << 16);
+        sc[j][1] = __uint_as_float(sw[j] & 0xffff0000u);
+      }
+      zc[j][0] = zc[j][1] = C::OFFSET + 8.f;
+    }
+    if constexpr (HAS_ZP) {
+      const uint32_t zword = *reinterpret_cast<const uint32_t*>(sSp + C::S_BYTES + gl * (NT / 8) * 4 + wn * 32 + g * 4);
+      decode_zp(zword, zc);
+    }
+    flush(sc, zc);
+  };
+
+  const int rows_per_group = grouped ? p.group_size / 16 : (1 << 30);  // k16-rows per quantisation group
+
+#pragma unroll 1
+  for (int it = wg; it < nk; it += KG) {
+    const int st = it % STAGES;
+    mbar_wait(full_bar + st * 8, (it / STAGES) & 1);
+    const uint32_t sbase = smem_base + st * C::STAGE_BYTES;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      uint32_t q[4];
+      lds128(sbase + offB + r * (NT * 8), q[0], q[1], q[2], q[3]);
+      uint32_t bf[NB][2];
+      if constexpr (NB == 1) {
+        ldsm_x2(sbase + offA + r * 32, bf[0][0], bf[0][1]);
+      } else {
+#pragma unroll
+        for (int bb = 0; bb < NB; bb += 2)
+          ldsm_x4(sbase + offA + bb * 8 * A_ROW + r * 32, bf[bb][0], bf[bb][1], bf[bb + 1][0], bf[bb + 1][1]);
+      }
+#pragma unroll
+      for (int b = 0; b < NB; ++b) mma16816<F16>(asum[b], C::ONES, C::ONES, C::ONES, C::ONES, bf[b][0], bf[b][1]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t a0 = and_or(q[j], 0x000f000fu, C::MAGIC);
+        const uint32_t a2 = and_or(q[j] >> 4, 0x000f000fu, C::MAGIC);
+        const uint32_t a1 = and_or(q[j] >> 8, 0x000f000fu, C::MAGIC);
+        const uint32_t a3 = and_or(q[j] >> 12, 0x000f000fu, C::MAGIC);
+#pragma unroll
+        for (int b = 0; b < NB; ++b) mma16816<F16>(part[j][b], a0, a1, a2, a3, bf[b][0], bf[b][1]);
+      }
+      // quantisation-group boundary: group sizes 32 / 64 end inside the stage, 128 at its end
+      if ((r & 1) == 1 && ((r + 1) % rows_per_group) == 0)
+        flush_from_smem(smem + st * C::STAGE_BYTES, r / rows_per_group);
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty_bar + st * 8);
+  }
+  if (!grouped) {
+    // channelwise: one scale row, "single" permutation over 32-column blocks (marlin_utils.py:204-213)
+    float sc[4][2], zc[4][2];
+    const scalar_t* srow = reinterpret_cast<const scalar_t*>(p.s) + (int64_t)slice * NT + wn * 64;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int pos = (j >> 1) * 32 + 8 * (g >> 1) + (g & 1) + 4 * (j & 1);
+      sc[j][0] = ScalarTraits<scalar_t>::to_float(srow[pos]);
+      sc[j][1] = ScalarTraits<scalar_t>::to_float(srow[pos + 2]);
+      zc[j][0] = zc[j][1] = C::OFFSET + 8.f;
+    }
+    if constexpr (HAS_ZP) {
+      const uint32_t zword = *reinterpret_cast<const uint32_t*>(p.zp + ((int64_t)slice * (NT / 8) + wn * 8 + g) * 4);
+      decode_zp(zword, zc);
+    }
+    flush(sc, zc);
+  }
+
+  // ---------------- reduce the stage groups through shared memory, then the split-K fix-up ----------------
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+      float* r0 = red + (size_t)(wg * MP + b * 8 + 2 * t) * C::RP + wn * 64 + 16 * j + g;
+      r0[0] = acc[j][b][0];
+      r0[C::RP] = acc[j][b][1];
+      r0[8] = acc[j][b][2];
+      r0[C::RP + 8] = acc[j][b][3];
+    }
+  constexpr int CT = CONSUMERS * 32;
+  named_bar_sync(1, CT);
+
+  scalar_t* cout = reinterpret_cast<scalar_t*>(p.c) + (int64_t)p.m0 * p.N + (int64_t)slice * NT;
+  const int nelem = p.m_rows * NT;
+  if (p.split == 1) {
+    for (int idx = tid; idx < nelem; idx += CT) {
+      const int m = idx / NT, n = idx % NT;
+      float v = 0.f;
+#pragma unroll
+      for (int kg = 0; kg < KG; ++kg) v += red[(size_t)(kg * MP + m) * C::RP + n];
+      cout[(int64_t)m * p.N + n] = ScalarTraits<scalar_t>::from_float(v);
+    }
+    return;
+  }
+  float* base = p.scratch + (size_t)slice * p.split * (size_t)(MP * NT);
+  float* mine = base + (size_t)chunk * (MP * NT);
+  for (int idx = tid; idx < nelem; idx += CT) {
+    const int m = idx / NT, n = idx % NT;
+    float v = 0.f;
+#pragma unroll
+    for (int kg = 0; kg < KG; ++kg) v += red[(size_t)(kg * MP + m) * C::RP + n];
+    __stcg(mine + idx, v);
+  }
+  __threadfence();
+  named_bar_sync(1, CT);
+  if (tid == 0) s_last = (atomicAdd(&p.counters[slice], 1) == p.split - 1);
+  named_bar_sync(1, CT);
+  if (!s_last) return;
+  __threadfence();
+  // last arriver: deterministic sum over the chunks in index order
+  for (int idx = tid; idx < nelem; idx += CT) {
+    float v = 0.f;
+    for (int ci = 0; ci < p.split; ++ci) v += __ldcg(base + (size_t)ci * (MP * NT) + idx);
+    const int m = idx / NT, n = idx % NT;
+    cout[(int64_t)m * p.N + n] = ScalarTraits<scalar_t>::from_float(v);
+  }
+  if (tid == 0) p.counters[slice] = 0;  // leave the caller's lock buffer all-zero
+}
+
+}  // namespace mg
+}  // namespace aphb200

@@ -26,12 +26,28 @@ def bench(name, K, N, M, g=128, iters=50):
         f(i)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(iters):
-        f(i)
-    e1.record()
-    torch.cuda.synchronize()
-    us = e0.elapsed_time(e1) / iters * 1e3
+    if os.environ.get("NOGRAPH"):
+        e0.record()
+        for i in range(iters):
+            f(i)
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) / iters * 1e3
+    else:
+        # CUDA graph of `iters` calls over rotating weight buffers: device time without host launch gaps
+        st = torch.cuda.Stream()
+        with torch.cuda.stream(st):
+            gph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gph, stream=st):
+                for i in range(iters):
+                    f(i)
+            gph.replay()
+            st.synchronize()
+            e0.record(st)
+            gph.replay()
+            e1.record(st)
+            st.synchronize()
+        us = e0.elapsed_time(e1) / iters * 1e3
     byt = K * N // 2 + (K // g) * N * 2 + M * K * 2 + M * N * 2
     return {"shape": name, "K": K, "N": N, "M": M, "us": round(us, 2), "GBps": round(byt / us / 1e3, 1),
             "TFLOPs": round(2 * M * N * K / us / 1e6, 1)}
