@@ -24,45 +24,93 @@
 //     128-row stages (warps of narrower slices take alternate stages), so the per-group flush is
 //     amortised over 8 k16 steps.
 // Large batches (M >= 64) are meant for the tcgen05 path; here they run as chunks of 32 rows.
+#include <cstdlib>
+
+#include <cuda.h>  // CUtensorMap types only; the encoder is fetched through the runtime (no libcuda link)
+
 #include "marlin_gemm_kernel.cuh"
+#include "marlin_gemm_tc.cuh"
 
 namespace aphb200 {
 namespace mg {
 
 struct Plan {
-  int nt, split, tiles_per_chunk, grid, k_tiles, n_slices;
+  int nt, split, stages_per_chunk, grid, k_stages, n_slices;
 };
 
 // Decomposition: output slices of NT columns x `split` equal k chunks, one CTA each. Prefer no
 // split (no partial traffic, no fix-up); split K only as far as needed to put a CTA on every SM.
 static Plan make_plan(int64_t N, int64_t K, int nb) {
   const int sms = sm_count();
-  const int k_tiles = (int)(K / KT);
   const int nts[3] = {256, 128, 64};
   Plan best{};
   bool found = false;
   for (int split = 1; split <= 8 && !found; ++split) {
-    if (split > k_tiles) break;
     for (int i = 0; i < 3; ++i) {
       const int nt = nts[i];
       if (N % nt != 0) continue;
+      const int ks = KT * (CONSUMERS / (nt / 64));
+      const int k_stages = (int)((K + ks - 1) / ks);
+      if (split > k_stages) continue;
       const int64_t ctas = (N / nt) * split;
-      best = Plan{nt, split, (k_tiles + split - 1) / split, (int)ctas, k_tiles, (int)(N / nt)};
+      best = Plan{nt, split, (k_stages + split - 1) / split, (int)ctas, k_stages, (int)(N / nt)};
       if (ctas >= (int64_t)sms * 9 / 10) {
         found = true;
         break;
       }
     }
   }
-  // tiles_per_chunk may leave the last chunk empty when split does not divide k_tiles: shrink split
-  while (best.split > 1 && (best.split - 1) * best.tiles_per_chunk >= k_tiles) --best.split;
+  // stages_per_chunk may leave the last chunk empty when split does not divide k_stages: shrink split
+  while (best.split > 1 && (best.split - 1) * best.stages_per_chunk >= best.k_stages) --best.split;
   best.grid = best.n_slices * best.split;
   (void)nb;
   return best;
 }
 
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      sym = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(sym);
+  }();
+  return fn;
+}
+
+// 2-D row-major tensor [rows][cols] of `elt_bytes`-wide elements, row pitch in bytes, box [box_rows][box_cols].
+static int make_map_2d(CUtensorMap* tm, CUtensorMapDataType dt, int elt_bytes, const void* base, uint64_t cols, uint64_t rows,
+                       uint64_t pitch_bytes, uint32_t box_cols, uint32_t box_rows, CUtensorMapSwizzle swz,
+                       CUtensorMapL2promotion promo) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  APH_CHECK(enc != nullptr, APH_ERR_CUDA, "gptq_marlin_gemm: driver has no cuTensorMapEncodeTiled");
+  const cuuint64_t dims[2] = {cols, rows};
+  const cuuint64_t strides[1] = {pitch_bytes};
+  const cuuint32_t box[2] = {box_cols, box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  (void)elt_bytes;
+  const CUresult r = enc(tm, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz, promo,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  APH_CHECK(r == CUDA_SUCCESS, APH_ERR_CUDA,
+            "gptq_marlin_gemm: cuTensorMapEncodeTiled failed (%d) for [%llu x %llu] pitch %llu box [%u x %u]", (int)r,
+            (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)pitch_bytes, box_rows, box_cols);
+  return APH_OK;
+}
+
+struct Operands {
+  const void *a, *b, *s, *zp;
+  int64_t M, lda;
+  int64_t num_groups;
+  bool f16;
+};
+
 template <typename scalar_t, int NB, int NT, bool HAS_ZP>
-static int launch(const Params& p, int grid, cudaStream_t stream) {
+static int launch(const Params& p, const Operands& op, int grid, cudaStream_t stream) {
   using C = Cfg<scalar_t, NB, NT>;
   auto kern = marlin_w4a16_kernel<scalar_t, NB, NT, HAS_ZP>;
   static bool attr_set[64] = {false};
@@ -73,48 +121,205 @@ static int launch(const Params& p, int grid, cudaStream_t stream) {
       return set_error(APH_ERR_CUDA, "gptq_marlin_gemm: cannot reserve %d bytes of shared memory", C::SMEM_BYTES);
     attr_set[dev] = true;
   }
-  kern<<<grid, THREADS, C::SMEM_BYTES, stream>>>(p);
+  const bool grouped = p.group_size < p.K;
+  const int gps = grouped ? KT / p.group_size : 0;
+  const CUtensorMapDataType dt16 = op.f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  alignas(64) CUtensorMap tmB, tmA, tmS, tmZ;
+  int st = make_map_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_UINT64, 8, op.b, (uint64_t)p.N, (uint64_t)p.K / 16, (uint64_t)p.N * 8, NT,
+                       8 * C::KG, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+  if (st != APH_OK) return st;
+  st = make_map_2d(&tmA, dt16, 2, op.a, (uint64_t)p.K, (uint64_t)op.M, (uint64_t)op.lda * 2, 64, C::MP, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+  if (st != APH_OK) return st;
+  if (grouped) {
+    st = make_map_2d(&tmS, dt16, 2, op.s, (uint64_t)p.N, (uint64_t)op.num_groups, (uint64_t)p.N * 2, NT, C::KG * gps,
+                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+    if (st != APH_OK) return st;
+    if (HAS_ZP) {
+      st = make_map_2d(&tmZ, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, op.zp, (uint64_t)p.N / 8, (uint64_t)op.num_groups,
+                       (uint64_t)p.N / 2, NT / 8, C::KG * gps, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+      if (st != APH_OK) return st;
+    } else {
+      tmZ = tmS;
+    }
+  } else {
+    tmS = tmB;  // never dereferenced
+    tmZ = tmB;
+  }
+  kern<<<grid, THREADS, C::SMEM_BYTES, stream>>>(p, tmB, tmA, tmS, tmZ);
   APH_LAUNCH_CHECK();
   return APH_OK;
 }
 
 template <typename scalar_t, int NB>
-static int launch_nb(const Params& p, const Plan& pl, bool has_zp, cudaStream_t stream) {
+static int launch_nb(const Params& p, const Operands& op, const Plan& pl, bool has_zp, cudaStream_t stream) {
   switch (pl.nt) {
     case 256:
-      return has_zp ? launch<scalar_t, NB, 256, true>(p, pl.grid, stream) : launch<scalar_t, NB, 256, false>(p, pl.grid, stream);
+      return has_zp ? launch<scalar_t, NB, 256, true>(p, op, pl.grid, stream) : launch<scalar_t, NB, 256, false>(p, op, pl.grid, stream);
     case 128:
-      return has_zp ? launch<scalar_t, NB, 128, true>(p, pl.grid, stream) : launch<scalar_t, NB, 128, false>(p, pl.grid, stream);
+      return has_zp ? launch<scalar_t, NB, 128, true>(p, op, pl.grid, stream) : launch<scalar_t, NB, 128, false>(p, op, pl.grid, stream);
     default:
-      return has_zp ? launch<scalar_t, NB, 64, true>(p, pl.grid, stream) : launch<scalar_t, NB, 64, false>(p, pl.grid, stream);
+      return has_zp ? launch<scalar_t, NB, 64, true>(p, op, pl.grid, stream) : launch<scalar_t, NB, 64, false>(p, op, pl.grid, stream);
   }
 }
 
 template <typename scalar_t>
-static int run_typed(Params p, int64_t M, bool has_zp, float* scratch, size_t scratch_bytes, cudaStream_t stream) {
+static int run_typed(Params p, const Operands& op, bool has_zp, float* scratch, size_t scratch_bytes, cudaStream_t stream) {
+  const int64_t M = op.M;
   for (int64_t m0 = 0; m0 < M; m0 += 32) {
     const int rows = (int)(M - m0 < 32 ? M - m0 : 32);
     const int nb = rows <= 8 ? 1 : (rows <= 16 ? 2 : 4);
     const Plan pl = make_plan(p.N, p.K, nb);
     p.m0 = (int)m0;
     p.m_rows = rows;
-    p.k_tiles = pl.k_tiles;
+    p.k_stages = pl.k_stages;
     p.split = pl.split;
-    p.tiles_per_chunk = pl.tiles_per_chunk;
+    p.stages_per_chunk = pl.stages_per_chunk;
     const size_t need = pl.split > 1 ? (size_t)pl.n_slices * pl.split * (8 * nb) * pl.nt * sizeof(float) : 0;
     APH_CHECK(need == 0 || (scratch != nullptr && scratch_bytes >= need), APH_ERR_WORKSPACE,
               "gptq_marlin_gemm: scratch of %zu bytes needed, %zu given", need, scratch_bytes);
     p.scratch = scratch;
     int st;
     if (nb == 1)
-      st = launch_nb<scalar_t, 1>(p, pl, has_zp, stream);
+      st = launch_nb<scalar_t, 1>(p, op, pl, has_zp, stream);
     else if (nb == 2)
-      st = launch_nb<scalar_t, 2>(p, pl, has_zp, stream);
+      st = launch_nb<scalar_t, 2>(p, op, pl, has_zp, stream);
     else
-      st = launch_nb<scalar_t, 4>(p, pl, has_zp, stream);
+      st = launch_nb<scalar_t, 4>(p, op, pl, has_zp, stream);
     if (st != APH_OK) return st;
   }
   return APH_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// tcgen05 path (marlin_gemm_tc.cuh): slices of 128 columns x k chunks, batch tiles of up to 256 rows
+// ------------------------------------------------------------------------------------------------
+struct PlanTc {
+  int split, stages_per_chunk, grid, k_stages, n_slices;
+};
+
+// Split K so that the CTAs fill whole waves of the machine; prefer the smallest split among near-equals.
+static PlanTc make_plan_tc(int64_t N, int64_t K, int ctas_per_sm) {
+  const int slots = sm_count() * ctas_per_sm;
+  const int n_slices = (int)(N / mgtc::NTILE);
+  const int k_stages = (int)((K + mgtc::KSTAGE - 1) / mgtc::KSTAGE);
+  int best_split = 1;
+  double best_score = -1.0;
+  for (int split = 1; split <= 16 && split <= k_stages; ++split) {
+    const int per = (k_stages + split - 1) / split;
+    if ((split - 1) * per >= k_stages) continue;  // would leave an empty chunk
+    if (per < 4 && split > 1) break;              // chunks too short to amortise the prologue
+    const int64_t ctas = (int64_t)n_slices * split;
+    const int64_t waves = (ctas + slots - 1) / slots;
+    // time ~ waves x (stages per CTA + fixed cost of ~3 stages); lower is better
+    const double t = (double)waves * (per + 3.0) + (split > 1 ? 1.0 : 0.0);
+    const double score = 1.0 / t;
+    if (score > best_score * 1.02) {
+      best_score = score;
+      best_split = split;
+    }
+  }
+  const int per = (k_stages + best_split - 1) / best_split;
+  return PlanTc{best_split, per, n_slices * best_split, k_stages, n_slices};
+}
+
+template <typename scalar_t, int MB, bool HAS_ZP>
+static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t scratch_bytes, cudaStream_t stream) {
+  using C = mgtc::Cfg<scalar_t, MB>;
+  auto kern = mgtc::marlin_w4a16_tc_kernel<scalar_t, MB, HAS_ZP>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES) != cudaSuccess)
+      return set_error(APH_ERR_CUDA, "gptq_marlin_gemm: cannot reserve %d bytes of shared memory", C::SMEM_BYTES);
+    attr_set[dev] = true;
+  }
+  const PlanTc pl = make_plan_tc(p.N, p.K, C::CTAS_PER_SM);
+  p.k_stages = pl.k_stages;
+  p.split = pl.split;
+  p.stages_per_chunk = pl.stages_per_chunk;
+  const size_t need = pl.split > 1 ? (size_t)pl.n_slices * pl.split * MB * mgtc::NTILE * sizeof(float) : 0;
+  APH_CHECK(need == 0 || (scratch != nullptr && scratch_bytes >= need), APH_ERR_WORKSPACE,
+            "gptq_marlin_gemm: scratch of %zu bytes needed, %zu given", need, scratch_bytes);
+  p.scratch = scratch;
+  const bool grouped = p.group_size < p.K;
+  const int gps = grouped ? mgtc::KSTAGE / p.group_size : 0;
+  const CUtensorMapDataType dt16 = op.f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  alignas(64) CUtensorMap tmB, tmA, tmS, tmZ;
+  int st = make_map_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_UINT64, 8, op.b, (uint64_t)p.N, (uint64_t)p.K / 16, (uint64_t)p.N * 8,
+                       mgtc::NTILE, 8, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+  if (st != APH_OK) return st;
+  st = make_map_2d(&tmA, dt16, 2, op.a, (uint64_t)p.K, (uint64_t)op.M, (uint64_t)op.lda * 2, 64, MB, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+  if (st != APH_OK) return st;
+  if (grouped) {
+    st = make_map_2d(&tmS, dt16, 2, op.s, (uint64_t)p.N, (uint64_t)op.num_groups, (uint64_t)p.N * 2, mgtc::NTILE, gps,
+                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+    if (st != APH_OK) return st;
+    if (HAS_ZP) {
+      st = make_map_2d(&tmZ, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, op.zp, (uint64_t)p.N / 8, (uint64_t)op.num_groups,
+                       (uint64_t)p.N / 2, mgtc::NTILE / 8, gps, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+      if (st != APH_OK) return st;
+    } else {
+      tmZ = tmS;
+    }
+  } else {
+    tmS = tmB;  // never dereferenced
+    tmZ = tmB;
+  }
+  kern<<<pl.grid, mgtc::THREADS, C::SMEM_BYTES, stream>>>(p, tmB, tmA, tmS, tmZ);
+  APH_LAUNCH_CHECK();
+  return APH_OK;
+}
+
+static int tile_rows_tc(int64_t rows) { return rows <= 16 ? 16 : rows <= 32 ? 32 : rows <= 64 ? 64 : rows <= 128 ? 128 : 256; }
+
+template <typename scalar_t>
+static int run_typed_tc(const Params& p0, const Operands& op, bool has_zp, float* scratch, size_t scratch_bytes, cudaStream_t stream) {
+  mgtc::Params p{};
+  p.s = p0.s;
+  p.zp = p0.zp;
+  p.c = p0.c;
+  p.counters = p0.counters;
+  p.N = p0.N;
+  p.K = p0.K;
+  p.group_size = p0.group_size;
+  for (int64_t m0 = 0; m0 < op.M; m0 += 256) {
+    const int rows = (int)(op.M - m0 < 256 ? op.M - m0 : 256);
+    p.m0 = (int)m0;
+    p.m_rows = rows;
+    int st;
+#define APH_TC_CASE(MBV)                                                                                  \
+  case MBV:                                                                                               \
+    st = has_zp ? launch_tc<scalar_t, MBV, true>(p, op, scratch, scratch_bytes, stream)                   \
+                : launch_tc<scalar_t, MBV, false>(p, op, scratch, scratch_bytes, stream);                 \
+    break;
+    switch (tile_rows_tc(rows)) {
+      APH_TC_CASE(16)
+      APH_TC_CASE(32)
+      APH_TC_CASE(64)
+      APH_TC_CASE(128)
+      default:
+        st = has_zp ? launch_tc<scalar_t, 256, true>(p, op, scratch, scratch_bytes, stream)
+                    : launch_tc<scalar_t, 256, false>(p, op, scratch, scratch_bytes, stream);
+    }
+#undef APH_TC_CASE
+    if (st != APH_OK) return st;
+  }
+  return APH_OK;
+}
+
+// which path serves a problem: APH_GEMM_PATH = mma | tc forces one (development), default by batch size
+static bool use_tc_path(int64_t M, int64_t N) {
+  if (N % mgtc::NTILE != 0) return false;
+  static const int forced = [] {
+    const char* e = getenv("APH_GEMM_PATH");
+    if (e == nullptr) return 0;
+    return e[0] == 't' ? 2 : e[0] == 'm' ? 1 : 0;
+  }();
+  if (forced) return forced == 2;
+  return M > 8;
 }
 
 // ScalarType ids, kernels/core/scalar_type.hpp:100-138 (values pinned in tests/golden/marlin_golden.npz)
@@ -135,6 +340,14 @@ extern "C" size_t aph_gptq_marlin_gemm_scratch_bytes(int64_t size_m, int64_t siz
     const mg::Plan pl = mg::make_plan(size_n, size_k, nb);
     const size_t need = pl.split > 1 ? (size_t)pl.n_slices * pl.split * (8 * nb) * pl.nt * sizeof(float) : 0;
     if (need > worst) worst = need;
+  }
+  if (size_n % mgtc::NTILE == 0) {
+    for (int cps = 1; cps <= 2; ++cps) {
+      const mg::PlanTc pl = mg::make_plan_tc(size_n, size_k, cps);
+      const int mb = cps == 2 ? 64 : 256;
+      const size_t need = pl.split > 1 ? (size_t)pl.n_slices * pl.split * mb * mgtc::NTILE * sizeof(float) : 0;
+      if (need > worst) worst = need;
+    }
   }
   return worst;
 }
@@ -180,17 +393,23 @@ extern "C" int aph_gptq_marlin_gemm(void* c, const void* a, const void* b_q_weig
   if (size_m == 0) return APH_OK;
 
   mg::Params p;
-  p.a = (const uint8_t*)a;
-  p.b = (const uint8_t*)b_q_weight;
   p.s = (const uint8_t*)b_scales;
   p.zp = has_zp ? (const uint8_t*)b_zeros : nullptr;
   p.c = c;
   p.counters = workspace;
   p.N = (int)size_n;
   p.K = (int)size_k;
-  p.lda = lda;
   p.group_size = (int)group_size;
+  {
+    const char* e = getenv("APH_GEMM_DBG");
+    p.dbg = e ? atoi(e) : 0;
+  }
+  mg::Operands op{a, b_q_weight, b_scales, has_zp ? b_zeros : nullptr, size_m, lda, num_groups, dtype == APH_DT_F16};
   cudaStream_t s = (cudaStream_t)stream;
-  if (dtype == APH_DT_F16) return mg::run_typed<__half>(p, size_m, has_zp != 0, (float*)scratch, scratch_bytes, s);
-  return mg::run_typed<__nv_bfloat16>(p, size_m, has_zp != 0, (float*)scratch, scratch_bytes, s);
+  if (mg::use_tc_path(size_m, size_n)) {
+    if (dtype == APH_DT_F16) return mg::run_typed_tc<__half>(p, op, has_zp != 0, (float*)scratch, scratch_bytes, s);
+    return mg::run_typed_tc<__nv_bfloat16>(p, op, has_zp != 0, (float*)scratch, scratch_bytes, s);
+  }
+  if (dtype == APH_DT_F16) return mg::run_typed<__half>(p, op, has_zp != 0, (float*)scratch, scratch_bytes, s);
+  return mg::run_typed<__nv_bfloat16>(p, op, has_zp != 0, (float*)scratch, scratch_bytes, s);
 }

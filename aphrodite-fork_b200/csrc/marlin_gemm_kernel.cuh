@@ -11,133 +11,137 @@ namespace mg {
 
 using namespace ::aphb200::ptx;
 
-constexpr int KT = 128;        // k rows per pipeline stage (= 8 k16-rows of the Marlin layout)
-constexpr int CONSUMERS = 4;   // consumer warps per CTA (+ 1 producer warp)
-constexpr int THREADS = (CONSUMERS + 1) * 32;
-constexpr int A_ROW = 272;     // bytes per activation row in shared memory: 256 + 16 pad (conflict-free ldmatrix)
+constexpr int KT = 128;        // k rows per warp block (= 8 k16-rows of the Marlin layout)
+constexpr int CONSUMERS = 4;   // consumer warps working on one stage
+constexpr int SG = 2;          // stage groups: the warps of group sg consume stages it % SG == sg (latency hiding)
+constexpr int THREADS = (SG * CONSUMERS + 1) * 32;  // + 1 producer warp
 
 struct Params {
-  const uint8_t* a;   // activations, bytes
-  const uint8_t* b;   // Marlin weights, bytes
-  const uint8_t* s;   // scales, bytes
+  const uint8_t* s;   // scales, bytes (channelwise path reads them directly)
   const uint8_t* zp;  // zero points, bytes (or null)
   void* c;
   float* scratch;      // [n_slices][split][MP*NT] fp32 partials (split > 1 only)
   int* counters;       // [n_slices] arrival counters, all-zero on entry and on exit
   int N, K;
-  int64_t lda;         // elements
   int m0, m_rows;      // this launch covers rows [m0, m0 + m_rows) of a / c
   int group_size;      // == K for channelwise
-  int k_tiles;         // K / 128
+  int k_stages;        // ceil(K / (128 * KG)) pipeline stages over the whole K
   int split;           // CTAs sharing one output slice (plain split-K over equal k chunks)
-  int tiles_per_chunk; // k-tiles per CTA
+  int stages_per_chunk;
+  int dbg;             // development switch (APH_GEMM_DBG): 1 = skip the math, 2 = skip the loads
 };
 
+// One pipeline stage holds KG x NWN warp blocks of (128 k x 64 n): 16 KiB of weights whatever the slice
+// width, fetched by ONE tiled TMA instruction; every consumer warp owns one block of every stage.
 template <typename scalar_t, int NB, int NT>
 struct Cfg {
   static constexpr bool F16 = std::is_same<scalar_t, __half>::value;
   static constexpr int NWN = NT / 64;                 // consumer warps along n (64 columns each)
-  static constexpr int KG = CONSUMERS / NWN;          // stage groups: warps of group wg consume stages it % KG == wg
+  static constexpr int KG = CONSUMERS / NWN;          // consumer warps along k (128 k each)
+  static constexpr int KS = KT * KG;                  // k extent of a stage
   static constexpr int MP = 8 * NB;                   // padded batch rows per launch
-  static constexpr int B_BYTES = 8 * NT * 8;
-  static constexpr int A_BYTES = MP * A_ROW;
-  static constexpr int S_BYTES = 4 * NT * 2;          // up to 4 groups per stage
-  static constexpr int Z_BYTES = 4 * (NT / 8) * 4;
-  static constexpr int STAGE_BYTES = B_BYTES + A_BYTES + S_BYTES + Z_BYTES;
+  static constexpr int B_BYTES = 8 * KG * NT * 8;     // [8*KG k16-rows][NT columns] x 8 bytes = 16 KiB
+  static constexpr int A_BOX = MP * 128;              // one activation box: MP rows x 64 k, 128B-swizzled
+  static constexpr int A_BYTES = 2 * KG * A_BOX;
+  static constexpr int S_BYTES = 4 * KG * NT * 2;     // up to 4 groups per 128 k
+  static constexpr int Z_BYTES = 4 * KG * (NT / 8) * 4;
+  static constexpr int STAGE_BYTES = (B_BYTES + A_BYTES + S_BYTES + Z_BYTES + 1023) / 1024 * 1024;
   static constexpr int RP = NT + 4;                   // padded row of the reduction buffer (floats)
-  static constexpr int RED_BYTES = KG * MP * RP * 4;
+  static constexpr int RED_BYTES = SG * KG * MP * RP * 4;
   static constexpr int CTAS_PER_SM = NB <= 2 ? 2 : 1;
-  static constexpr int BUDGET = (224 * 1024) / CTAS_PER_SM - 1024 - RED_BYTES - 256;
-  static constexpr int STAGES = BUDGET / STAGE_BYTES > 12 ? 12 : BUDGET / STAGE_BYTES;
-  static_assert(STAGES >= 3 && STAGES > KG, "pipeline too shallow");
-  static constexpr int BAR_BYTES = 2 * STAGES * 8;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + RED_BYTES + BAR_BYTES;
+  static constexpr int BUDGET = (224 * 1024) / CTAS_PER_SM - 2048 - RED_BYTES - 256;
+  static constexpr int STAGES = BUDGET / STAGE_BYTES > 8 ? 8 : BUDGET / STAGE_BYTES;
+  static_assert(STAGES >= 2, "pipeline too shallow");
+  static constexpr int BAR_BYTES = 2 * STAGES * 8 + 16;
+  static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + RED_BYTES + BAR_BYTES;
   static constexpr uint32_t MAGIC = F16 ? 0x64006400u : 0x43004300u;  // 1024 / 128 as packed pairs
   static constexpr float OFFSET = F16 ? 1024.f : 128.f;
   static constexpr uint32_t ONES = F16 ? 0x3c003c00u : 0x3f803f80u;
 };
 
+// Tensor maps (built on the host per call, marlin_gemm.cu):
+//   tmB: weights as a 2-D array of 8-byte words [K/16][N], box [8*KG][NT]
+//   tmA: activations [M][K] 16-bit, box [MP][64], SWIZZLE_128B, rows >= M read as zero
+//   tmS: scales [groups][N] 16-bit, box [KG*gps][NT];  tmZ: zero points [groups][N/8] 32-bit, box [KG*gps][NT/8]
 template <typename scalar_t, int NB, int NT, bool HAS_ZP>
-__global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM) marlin_w4a16_kernel(const Params p) {
+__global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
+    marlin_w4a16_kernel(const Params p, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmA,
+                        const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUtensorMap tmZ) {
   using C = Cfg<scalar_t, NB, NT>;
   constexpr bool F16 = C::F16;
   constexpr int MP = C::MP, STAGES = C::STAGES, NWN = C::NWN, KG = C::KG;
-  extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ int s_last;
+  extern __shared__ uint8_t smem_raw[];
 
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const bool grouped = p.group_size < p.K;
-  const int gps = grouped ? KT / p.group_size : 0;  // groups per stage (1, 2, 4)
+  const int gps = grouped ? KT / p.group_size : 0;  // groups per 128 k (1, 2, 4)
   const int slice = blockIdx.x / p.split, chunk = blockIdx.x % p.split;
-  const int kb = chunk * p.tiles_per_chunk;
-  const int nk = min(p.k_tiles, kb + p.tiles_per_chunk) - kb;  // > 0 by construction
-  const uint32_t smem_base = smem_u32(smem);
+  const int kb = chunk * p.stages_per_chunk;
+  const int nk = min(p.k_stages, kb + p.stages_per_chunk) - kb;  // > 0 by construction
+  // the 128-byte swizzle pattern is a function of the shared-memory address: align the ring to 1 KiB
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
   float* red = reinterpret_cast<float*>(smem + STAGES * C::STAGE_BYTES);
   const uint32_t full_bar = smem_base + STAGES * C::STAGE_BYTES + C::RED_BYTES;
   const uint32_t empty_bar = full_bar + STAGES * 8;
+  int* s_last = reinterpret_cast<int*>(smem + STAGES * C::STAGE_BYTES + C::RED_BYTES + 2 * STAGES * 8);
 
-  // zero the activation rows that are never copied (rows >= m_rows), then init the barriers
-  for (int i = tid; i < STAGES * (C::A_BYTES / 16); i += THREADS) {
-    const int st = i / (C::A_BYTES / 16), off = (i % (C::A_BYTES / 16)) * 16;
-    if (off / A_ROW >= p.m_rows) *reinterpret_cast<uint4*>(smem + st * C::STAGE_BYTES + C::B_BYTES + off) = make_uint4(0, 0, 0, 0);
-  }
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(full_bar + s * 8, 1);
-      mbar_init(empty_bar + s * 8, NWN);  // a stage is consumed by the NWN warps of one stage group
+      mbar_init(empty_bar + s * 8, CONSUMERS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
 
-  if (w == CONSUMERS) {
-    // ============================ producer warp: bulk async copies ============================
-    const uint32_t stage_tx = (uint32_t)(C::B_BYTES + p.m_rows * 256 + gps * NT * 2 + (HAS_ZP ? gps * (NT / 8) * 4 : 0));
-    // per-lane source pointers for k-tile kb, advanced by constant strides per k-tile
-    const uint8_t* src_b = p.b + ((int64_t)(kb * 8 + (lane & 7)) * p.N + (int64_t)slice * NT) * 8;
-    const int64_t step_b = (int64_t)8 * p.N * 8;
-    const uint8_t* src_a = p.a + ((int64_t)(p.m0 + (lane < p.m_rows ? lane : 0)) * p.lda + (int64_t)kb * KT) * 2;
-    const int gr = lane & 3;
-    const uint8_t* src_s = grouped ? p.s + ((int64_t)(kb * gps + gr) * p.N + (int64_t)slice * NT) * 2 : p.s;
-    const uint8_t* src_z =
-        (HAS_ZP && grouped) ? p.zp + ((int64_t)(kb * gps + gr) * (p.N / 8) + (int64_t)slice * (NT / 8)) * 4 : p.zp;
-    const int64_t step_s = (int64_t)gps * p.N * 2, step_z = (int64_t)gps * (p.N / 8) * 4;
+  if (w == SG * CONSUMERS) {
+    // ============================ producer: one thread, tiled TMA loads ============================
+    if (lane != 0) return;
+    prefetch_tensormap(&tmB);
+    prefetch_tensormap(&tmA);
+    if (grouped) prefetch_tensormap(&tmS);
+    if (HAS_ZP && grouped) prefetch_tensormap(&tmZ);
+    const uint64_t pol_stream = policy_evict_first();  // weights are read once
+    const uint64_t pol_keep = policy_evict_last();     // activations are shared by every CTA
+    const uint32_t stage_tx =
+        (uint32_t)(C::B_BYTES + C::A_BYTES + KG * gps * NT * 2 + (HAS_ZP ? KG * gps * (NT / 8) * 4 : 0));
 #pragma unroll 1
     for (int it = 0; it < nk; ++it) {
       const int st = it % STAGES;
+      const int ks = kb + it;
       mbar_wait(empty_bar + st * 8, ((it / STAGES) & 1) ^ 1);
       const uint32_t sB = smem_base + st * C::STAGE_BYTES;
       const uint32_t fb = full_bar + st * 8;
-      if (lane == 0) mbar_expect_tx(fb, stage_tx);
-      __syncwarp();
-      if (lane < 8) {
-        bulk_g2s(sB + lane * (NT * 8), src_b, NT * 8, fb);
-      } else if (lane < 12) {
-        if (gr < gps) bulk_g2s(sB + C::B_BYTES + C::A_BYTES + gr * (NT * 2), src_s, NT * 2, fb);
-      } else if (lane < 16) {
-        if constexpr (HAS_ZP) {
-          if (gr < gps) bulk_g2s(sB + C::B_BYTES + C::A_BYTES + C::S_BYTES + gr * (NT / 8) * 4, src_z, (NT / 8) * 4, fb);
-        }
+      if (p.dbg == 2) {
+        mbar_arrive(fb);
+        continue;
       }
-      if (lane < p.m_rows) bulk_g2s(sB + C::B_BYTES + lane * A_ROW, src_a, 256, fb);
-      src_b += step_b;
-      src_a += 256;
-      src_s += step_s;
-      src_z += step_z;
+      mbar_expect_tx(fb, stage_tx);
+      tma_load_2d_hint(sB, &tmB, slice * NT, ks * 8 * KG, fb, pol_stream);
+#pragma unroll
+      for (int i = 0; i < 2 * KG; ++i)
+        tma_load_2d_hint(sB + C::B_BYTES + i * C::A_BOX, &tmA, ks * C::KS + 64 * i, p.m0, fb, pol_keep);
+      if (grouped) {
+        tma_load_2d(sB + C::B_BYTES + C::A_BYTES, &tmS, slice * NT, ks * KG * gps, fb);
+        if constexpr (HAS_ZP) tma_load_2d(sB + C::B_BYTES + C::A_BYTES + C::S_BYTES, &tmZ, slice * (NT / 8), ks * KG * gps, fb);
+      }
     }
     return;
   }
 
   // ================================ consumer warps ================================
-  const int wn = w % NWN, wg = w / NWN;
+  const int sg = w / CONSUMERS, wi = w % CONSUMERS;
+  const int wn = wi % NWN, wg = wi / NWN;
   const int g = lane >> 2, t = lane & 3;
-  const uint32_t offB = (uint32_t)(wn * 512 + lane * 16);
-  uint32_t offA;  // ldmatrix row address of k16-row 0
-  if constexpr (NB == 1) {
-    offA = (uint32_t)(C::B_BYTES + (lane & 7) * A_ROW + (((lane >> 3) & 1) * 16));
-  } else {
-    offA = (uint32_t)(C::B_BYTES + (((lane >> 4) & 1) * 8 + (lane & 7)) * A_ROW + (((lane >> 3) & 1) * 16));
-  }
+  const uint32_t offB = (uint32_t)(wg * 8 * (NT * 8) + wn * 512 + lane * 16);
+  // ldmatrix row address inside a 128B-swizzled activation box: row rr, 16-byte chunk c -> rr*128 + ((c ^ (rr&7)) << 4)
+  const uint32_t a_row = (NB == 1) ? (uint32_t)(lane & 7) : (uint32_t)(((lane >> 4) & 1) * 8 + (lane & 7));
+  const uint32_t a_x = (uint32_t)(((lane >> 3) & 1) ^ (lane & 7));  // (k-half bit) ^ (row & 7)
+  const uint32_t offA = (uint32_t)(C::B_BYTES + wg * 2 * C::A_BOX) + a_row * 128;
+  uint32_t a_sw[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) a_sw[i] = ((uint32_t)(i << 1) ^ a_x) << 4;
 
   float acc[4][NB][4], part[4][NB][4], asum[NB][4];
 #pragma unroll
@@ -199,24 +203,27 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM) m
     flush(sc, zc);
   };
 
-  const int rows_per_group = grouped ? p.group_size / 16 : (1 << 30);  // k16-rows per quantisation group
+  // k16-rows per quantisation group (2, 4 or 8: powers of two) as a mask / shift; channelwise never flushes in the loop
+  const int rpg_mask = grouped ? p.group_size / 16 - 1 : 0x7fffffff;
+  const int rpg_shift = grouped ? 31 - __clz(p.group_size / 16) : 31;
 
 #pragma unroll 1
-  for (int it = wg; it < nk; it += KG) {
+  for (int it = sg; it < nk; it += SG) {
     const int st = it % STAGES;
     mbar_wait(full_bar + st * 8, (it / STAGES) & 1);
     const uint32_t sbase = smem_base + st * C::STAGE_BYTES;
+    if (p.dbg != 1)
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
       uint32_t q[4];
       lds128(sbase + offB + r * (NT * 8), q[0], q[1], q[2], q[3]);
       uint32_t bf[NB][2];
+      const uint32_t aaddr = sbase + offA + (r >> 2) * C::A_BOX + a_sw[r & 3];
       if constexpr (NB == 1) {
-        ldsm_x2(sbase + offA + r * 32, bf[0][0], bf[0][1]);
+        ldsm_x2(aaddr, bf[0][0], bf[0][1]);
       } else {
 #pragma unroll
-        for (int bb = 0; bb < NB; bb += 2)
-          ldsm_x4(sbase + offA + bb * 8 * A_ROW + r * 32, bf[bb][0], bf[bb][1], bf[bb + 1][0], bf[bb + 1][1]);
+        for (int bb = 0; bb < NB; bb += 2) ldsm_x4(aaddr + bb * 8 * 128, bf[bb][0], bf[bb][1], bf[bb + 1][0], bf[bb + 1][1]);
       }
 #pragma unroll
       for (int b = 0; b < NB; ++b) mma16816<F16>(asum[b], C::ONES, C::ONES, C::ONES, C::ONES, bf[b][0], bf[b][1]);
@@ -229,9 +236,9 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM) m
 #pragma unroll
         for (int b = 0; b < NB; ++b) mma16816<F16>(part[j][b], a0, a1, a2, a3, bf[b][0], bf[b][1]);
       }
-      // quantisation-group boundary: group sizes 32 / 64 end inside the stage, 128 at its end
-      if ((r & 1) == 1 && ((r + 1) % rows_per_group) == 0)
-        flush_from_smem(smem + st * C::STAGE_BYTES, r / rows_per_group);
+      // quantisation-group boundary: group sizes 32 / 64 end inside the warp block, 128 at its end
+      if ((r & 1) == 1 && ((r + 1) & rpg_mask) == 0)
+        flush_from_smem(smem + st * C::STAGE_BYTES, wg * gps + (r >> rpg_shift));
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(empty_bar + st * 8);
@@ -259,13 +266,13 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM) m
   for (int j = 0; j < 4; ++j)
 #pragma unroll
     for (int b = 0; b < NB; ++b) {
-      float* r0 = red + (size_t)(wg * MP + b * 8 + 2 * t) * C::RP + wn * 64 + 16 * j + g;
+      float* r0 = red + (size_t)((sg * KG + wg) * MP + b * 8 + 2 * t) * C::RP + wn * 64 + 16 * j + g;
       r0[0] = acc[j][b][0];
       r0[C::RP] = acc[j][b][1];
       r0[8] = acc[j][b][2];
       r0[C::RP + 8] = acc[j][b][3];
     }
-  constexpr int CT = CONSUMERS * 32;
+  constexpr int CT = SG * CONSUMERS * 32;
   named_bar_sync(1, CT);
 
   scalar_t* cout = reinterpret_cast<scalar_t*>(p.c) + (int64_t)p.m0 * p.N + (int64_t)slice * NT;
@@ -275,7 +282,7 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM) m
       const int m = idx / NT, n = idx % NT;
       float v = 0.f;
 #pragma unroll
-      for (int kg = 0; kg < KG; ++kg) v += red[(size_t)(kg * MP + m) * C::RP + n];
+      for (int kg = 0; kg < SG * KG; ++kg) v += red[(size_t)(kg * MP + m) * C::RP + n];
       cout[(int64_t)m * p.N + n] = ScalarTraits<scalar_t>::from_float(v);
     }
     return;
@@ -286,14 +293,14 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM) m
     const int m = idx / NT, n = idx % NT;
     float v = 0.f;
 #pragma unroll
-    for (int kg = 0; kg < KG; ++kg) v += red[(size_t)(kg * MP + m) * C::RP + n];
+    for (int kg = 0; kg < SG * KG; ++kg) v += red[(size_t)(kg * MP + m) * C::RP + n];
     __stcg(mine + idx, v);
   }
   __threadfence();
   named_bar_sync(1, CT);
-  if (tid == 0) s_last = (atomicAdd(&p.counters[slice], 1) == p.split - 1);
+  if (tid == 0) *s_last = (atomicAdd(&p.counters[slice], 1) == p.split - 1);
   named_bar_sync(1, CT);
-  if (!s_last) return;
+  if (!*s_last) return;
   __threadfence();
   // last arriver: deterministic sum over the chunks in index order
   for (int idx = tid; idx < nelem; idx += CT) {
