@@ -24,6 +24,7 @@
 //     128-row stages (warps of narrower slices take alternate stages), so the per-group flush is
 //     amortised over 8 k16 steps.
 // Large batches (M >= 64) are meant for the tcgen05 path; here they run as chunks of 32 rows.
+#include <cstdio>
 #include <cstdlib>
 
 #include <cuda.h>  // CUtensorMap types only; the encoder is fetched through the runtime (no libcuda link)
@@ -195,32 +196,30 @@ static int run_typed(Params p, const Operands& op, bool has_zp, float* scratch, 
 // tcgen05 path (marlin_gemm_tc.cuh): slices of 128 columns x k chunks, batch tiles of up to 256 rows
 // ------------------------------------------------------------------------------------------------
 struct PlanTc {
-  int split, stages_per_chunk, grid, k_stages, n_slices;
+  int grid, total, k_stages, m_tiles, n_slices;
 };
 
-// Split K so that the CTAs fill whole waves of the machine; prefer the smallest split among near-equals.
-static PlanTc make_plan_tc(int64_t N, int64_t K, int ctas_per_sm) {
-  const int slots = sm_count() * ctas_per_sm;
-  const int n_slices = (int)(N / mgtc::NTILE);
-  const int k_stages = (int)((K + mgtc::KSTAGE - 1) / mgtc::KSTAGE);
-  int best_split = 1;
-  double best_score = -1.0;
-  for (int split = 1; split <= 16 && split <= k_stages; ++split) {
-    const int per = (k_stages + split - 1) / split;
-    if ((split - 1) * per >= k_stages) continue;  // would leave an empty chunk
-    if (per < 4 && split > 1) break;              // chunks too short to amortise the prologue
-    const int64_t ctas = (int64_t)n_slices * split;
-    const int64_t waves = (ctas + slots - 1) / slots;
-    // time ~ waves x (stages per CTA + fixed cost of ~3 stages); lower is better
-    const double t = (double)waves * (per + 3.0) + (split > 1 ? 1.0 : 0.0);
-    const double score = 1.0 / t;
-    if (score > best_score * 1.02) {
-      best_score = score;
-      best_split = split;
-    }
-  }
-  const int per = (k_stages + best_split - 1) / best_split;
-  return PlanTc{best_split, per, n_slices * best_split, k_stages, n_slices};
+// Stream-K: one persistent CTA per SM, each taking an equal share of the (tile, k stage) list; fewer CTAs
+// only when the problem is too small to give each at least 4 stages.
+static PlanTc make_plan_tc(int64_t M, int64_t N, int64_t K, int mb) {
+  PlanTc pl;
+  pl.n_slices = (int)(N / mgtc::NTILE);
+  pl.k_stages = (int)((K + mgtc::KSTAGE - 1) / mgtc::KSTAGE);
+  pl.m_tiles = (int)((M + mb - 1) / mb);
+  pl.total = pl.n_slices * pl.m_tiles * pl.k_stages;
+  int g = sm_count();
+  if (g > pl.total / 4) g = pl.total / 4;
+  if (g < 1) g = 1;
+  pl.grid = g;
+  return pl;
+}
+
+static int tile_rows_tc(int64_t rows) { return rows <= 16 ? 16 : rows <= 32 ? 32 : rows <= 64 ? 64 : rows <= 128 ? 128 : 256; }
+
+static size_t scratch_bytes_tc(int64_t M, int64_t N, int64_t K) {
+  const int mb = tile_rows_tc(M);
+  const PlanTc pl = make_plan_tc(M, N, K, mb);
+  return (size_t)pl.grid * 2 * mb * mgtc::NTILE * sizeof(float);
 }
 
 template <typename scalar_t, int MB, bool HAS_ZP>
@@ -235,13 +234,14 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
       return set_error(APH_ERR_CUDA, "gptq_marlin_gemm: cannot reserve %d bytes of shared memory", C::SMEM_BYTES);
     attr_set[dev] = true;
   }
-  const PlanTc pl = make_plan_tc(p.N, p.K, C::CTAS_PER_SM);
+  const PlanTc pl = make_plan_tc(op.M, p.N, p.K, MB);
   p.k_stages = pl.k_stages;
-  p.split = pl.split;
-  p.stages_per_chunk = pl.stages_per_chunk;
-  const size_t need = pl.split > 1 ? (size_t)pl.n_slices * pl.split * MB * mgtc::NTILE * sizeof(float) : 0;
-  APH_CHECK(need == 0 || (scratch != nullptr && scratch_bytes >= need), APH_ERR_WORKSPACE,
-            "gptq_marlin_gemm: scratch of %zu bytes needed, %zu given", need, scratch_bytes);
+  p.m_tiles = pl.m_tiles;
+  p.total = pl.total;
+  p.M = (int)op.M;
+  const size_t need = (size_t)pl.grid * 2 * MB * mgtc::NTILE * sizeof(float);
+  APH_CHECK(scratch != nullptr && scratch_bytes >= need, APH_ERR_WORKSPACE, "gptq_marlin_gemm: scratch of %zu bytes needed, %zu given",
+            need, scratch_bytes);
   p.scratch = scratch;
   const bool grouped = p.group_size < p.K;
   const int gps = grouped ? mgtc::KSTAGE / p.group_size : 0;
@@ -268,12 +268,40 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
     tmS = tmB;  // never dereferenced
     tmZ = tmB;
   }
+  // development aid: APH_GEMM_TRACE=<file> dumps per-stage clock64 stamps of CTA 0 (synchronises!)
+  static const char* trace_path = getenv("APH_GEMM_TRACE");
+  p.trace = nullptr;
+  if (trace_path != nullptr) {
+    cudaMalloc(&p.trace, 72 * 8 * sizeof(unsigned long long));
+    cudaMemsetAsync(p.trace, 0, 72 * 8 * sizeof(unsigned long long), stream);
+  }
   kern<<<pl.grid, mgtc::THREADS, C::SMEM_BYTES, stream>>>(p, tmB, tmA, tmS, tmZ);
   APH_LAUNCH_CHECK();
+  if (trace_path != nullptr) {
+    unsigned long long host[72 * 8];
+    cudaStreamSynchronize(stream);
+    cudaMemcpy(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost);
+    cudaFree(p.trace);
+    if (FILE* f = fopen(trace_path, "w")) {
+      fprintf(f, "# MB=%d grid=%d total=%d SA=%d SW=%d: it mma_start fulla ready issued | dq_start fullw math_done slot_free\n", MB, pl.grid,
+              pl.total, C::SA, C::SW);
+      const unsigned long long t0 = host[4] ? host[4] : host[0];
+      for (int i = 0; i < 64 && host[i * 8 + 3]; ++i) {
+        fprintf(f, "%2d", i);
+        for (int j = 0; j < 8; ++j) fprintf(f, " %8lld", host[i * 8 + j] ? (long long)(host[i * 8 + j] - t0) : -1LL);
+        fprintf(f, "\n");
+      }
+      fprintf(f, "# epilogue per segment: wait_done done drained counted | then: reductions_start reductions_end setup_done kernel_entry\n");
+      for (int i = 64; i < 72; ++i) {
+        fprintf(f, "e%d", i - 64);
+        for (int j = 0; j < 8; ++j) fprintf(f, " %8lld", host[i * 8 + j] ? (long long)(host[i * 8 + j] - t0) : -1LL);
+        fprintf(f, "\n");
+      }
+      fclose(f);
+    }
+  }
   return APH_OK;
 }
-
-static int tile_rows_tc(int64_t rows) { return rows <= 16 ? 16 : rows <= 32 ? 32 : rows <= 64 ? 64 : rows <= 128 ? 128 : 256; }
 
 template <typename scalar_t>
 static int run_typed_tc(const Params& p0, const Operands& op, bool has_zp, float* scratch, size_t scratch_bytes, cudaStream_t stream) {
@@ -285,29 +313,22 @@ static int run_typed_tc(const Params& p0, const Operands& op, bool has_zp, float
   p.N = p0.N;
   p.K = p0.K;
   p.group_size = p0.group_size;
-  for (int64_t m0 = 0; m0 < op.M; m0 += 256) {
-    const int rows = (int)(op.M - m0 < 256 ? op.M - m0 : 256);
-    p.m0 = (int)m0;
-    p.m_rows = rows;
-    int st;
+  // the arrival counters live in the caller's lock buffer (N / 64 * 16 ints): one per (slice, batch tile)
+  APH_CHECK((op.M + 255) / 256 <= 32, APH_ERR_UNSUPPORTED, "gptq_marlin_gemm: size_m above 8192 is not supported in one call");
 #define APH_TC_CASE(MBV)                                                                                  \
   case MBV:                                                                                               \
-    st = has_zp ? launch_tc<scalar_t, MBV, true>(p, op, scratch, scratch_bytes, stream)                   \
-                : launch_tc<scalar_t, MBV, false>(p, op, scratch, scratch_bytes, stream);                 \
-    break;
-    switch (tile_rows_tc(rows)) {
-      APH_TC_CASE(16)
-      APH_TC_CASE(32)
-      APH_TC_CASE(64)
-      APH_TC_CASE(128)
-      default:
-        st = has_zp ? launch_tc<scalar_t, 256, true>(p, op, scratch, scratch_bytes, stream)
+    return has_zp ? launch_tc<scalar_t, MBV, true>(p, op, scratch, scratch_bytes, stream)                 \
+                  : launch_tc<scalar_t, MBV, false>(p, op, scratch, scratch_bytes, stream);
+  switch (tile_rows_tc(op.M)) {
+    APH_TC_CASE(16)
+    APH_TC_CASE(32)
+    APH_TC_CASE(64)
+    APH_TC_CASE(128)
+    default:
+      return has_zp ? launch_tc<scalar_t, 256, true>(p, op, scratch, scratch_bytes, stream)
                     : launch_tc<scalar_t, 256, false>(p, op, scratch, scratch_bytes, stream);
-    }
-#undef APH_TC_CASE
-    if (st != APH_OK) return st;
   }
-  return APH_OK;
+#undef APH_TC_CASE
 }
 
 // which path serves a problem: APH_GEMM_PATH = mma | tc forces one (development), default by batch size
@@ -342,12 +363,8 @@ extern "C" size_t aph_gptq_marlin_gemm_scratch_bytes(int64_t size_m, int64_t siz
     if (need > worst) worst = need;
   }
   if (size_n % mgtc::NTILE == 0) {
-    for (int cps = 1; cps <= 2; ++cps) {
-      const mg::PlanTc pl = mg::make_plan_tc(size_n, size_k, cps);
-      const int mb = cps == 2 ? 64 : 256;
-      const size_t need = pl.split > 1 ? (size_t)pl.n_slices * pl.split * mb * mgtc::NTILE * sizeof(float) : 0;
-      if (need > worst) worst = need;
-    }
+    const size_t need = mg::scratch_bytes_tc(size_m, size_n, size_k);
+    if (need > worst) worst = need;
   }
   return worst;
 }

@@ -31,27 +31,33 @@ namespace mgtc {
 
 using namespace ::aphb200::ptx;
 
-constexpr int NTILE = 128;   // output columns per CTA (= MMA M)
-constexpr int KSTAGE = 128;  // k per pipeline stage (= 8 k16-rows of the Marlin layout)
-constexpr int DQ_WARPS = 8;  // two per TMEM lane quadrant
-constexpr int THREADS = (3 + DQ_WARPS) * 32;
+constexpr int NTILE = 128;    // output columns per tile (= MMA M)
+constexpr int KSTAGE = 128;   // k per pipeline stage (= 8 k16-rows of the Marlin layout)
+constexpr int DQ_GROUP = 8;   // dequantiser warps working on one stage: two per TMEM lane quadrant
+constexpr int DQ_GROUPS = 2;  // group (it & 1) takes stage it
+constexpr int W_PROD = 0, W_MMA = 1, W_ACT = 2, W_MMA2 = 3, W_EPI0 = 4, W_DQ0 = 8;  // warp roles
+constexpr int EPI_WARPS = 4;
+constexpr int THREADS = (W_DQ0 + DQ_GROUP * DQ_GROUPS) * 32;
 constexpr int W_BYTES = 8 * NTILE * 8;
 constexpr int S_BYTES = 4 * NTILE * 2;
 constexpr int Z_BYTES = 4 * (NTILE / 8) * 4;
 constexpr int W_STAGE = W_BYTES + S_BYTES + Z_BYTES;  // 9472 bytes
 
+// The work is the flattened list of (tile, k stage) pairs, tile = (column slice, batch tile); CTA b of G
+// takes the contiguous range [b*T/G, (b+1)*T/G) (stream-K): every SM gets the same number of stages
+// whatever the shape. A tile whose k range is shared by several CTAs is finished by the last of them.
 struct Params {
   const uint8_t* s;   // scales (channelwise path reads them directly)
   const uint8_t* zp;  // zero points or null
   void* c;
-  float* scratch;     // [n_slices][split][MB*128] fp32 partials (split > 1 only)
-  int* counters;      // [n_slices] arrival counters, all-zero on entry and on exit
-  int N, K;
-  int m0, m_rows;     // this launch covers rows [m0, m0 + m_rows) of a / c
+  float* scratch;     // [G][2][MB*128] fp32 partial tiles (first / last segment of each CTA)
+  int* counters;      // [tiles] arrival counters, all-zero on entry and on exit
+  int N, K, M;
   int group_size;     // == K for channelwise
   int k_stages;       // ceil(K / 128)
-  int split;          // CTAs sharing one output slice
-  int stages_per_chunk;
+  int m_tiles;        // ceil(M / MB)
+  int total;          // T = tiles * k_stages
+  unsigned long long* trace;  // development: per-stage clock64 stamps of CTA 0 (APH_GEMM_TRACE), else null
 };
 
 template <typename scalar_t, int MB>
@@ -59,27 +65,39 @@ struct Cfg {
   static constexpr bool F16 = std::is_same<scalar_t, __half>::value;
   static constexpr int ACT_BOX = MB * 128;  // MB rows x 64 k, 128B-swizzled
   static constexpr int ACT_BYTES = 2 * ACT_BOX;
-  static constexpr int CTAS_PER_SM = MB <= 64 ? 2 : 1;
-  static constexpr int TMEM_COLS = CTAS_PER_SM == 2 ? 256 : 512;
-  static constexpr int D_COLS = MB <= 64 ? 64 : 256;
-  static constexpr int A_COL0 = D_COLS;
+  static constexpr int TMEM_COLS = 512;
+  static constexpr int NDBUF = MB <= 128 ? 2 : 1;  // accumulator buffers in TMEM (epilogue of one tile overlaps the next)
+  // One thread sustains about one tcgen05.mma per 50-100 cycles whatever its shape (tools/micro/umma_rate.cu), which
+  // is below the tensor pipe's rate for N <= 64: two issuer warps then take alternate stages, each accumulating into
+  // its own D tile; the epilogue adds the two.
+  static constexpr int NI = MB <= 64 ? 2 : 1;
+  static constexpr int A_COL0 = NI * NDBUF * MB < 64 ? 64 : NI * NDBUF * MB;
   // activation ring == TMEM weight-slot ring
-  static constexpr int SA_TMEM = (TMEM_COLS - D_COLS) / 64;
-  static constexpr int BUDGET = (227 * 1024) / CTAS_PER_SM - 1024 - 512 - (CTAS_PER_SM == 2 ? 1024 : 0);
+  static constexpr int SA_TMEM = (TMEM_COLS - A_COL0) / 64;
+  // the partial sums of a shared tile are merged at the end of the kernel through the then idle rings
+  static constexpr int FIX_BYTES = 0;
+  static constexpr int BUDGET = 227 * 1024 - 1024 - 1024 - FIX_BYTES - 4096;
   static constexpr int SA_SMEM = (BUDGET - 3 * W_STAGE) / ACT_BYTES;
   static constexpr int SA = SA_SMEM < SA_TMEM ? SA_SMEM : SA_TMEM;
-  static_assert(SA >= 2, "activation ring too shallow");
+  static_assert(SA >= 2 && SA <= 7, "activation ring depth");
   static constexpr int SW_FIT = (BUDGET - SA * ACT_BYTES) / W_STAGE;
   static constexpr int SW = SW_FIT > 8 ? 8 : SW_FIT;
   static_assert(SW >= 3, "weight ring too shallow");
-  static constexpr int ACT_OFF = 0;                  // activation slots first: 1 KiB aligned
+  static constexpr int ACT_OFF = 0;  // activation slots first: 1 KiB aligned
   static constexpr int W_OFF = SA * ACT_BYTES;
-  static constexpr int BAR_OFF = W_OFF + SW * W_STAGE;
-  static constexpr int BAR_BYTES = 512;
-  static constexpr int SMEM_BYTES = 1024 + BAR_OFF + BAR_BYTES;
+  static constexpr int FIX_OFF = W_OFF + SW * W_STAGE;
+  static constexpr int BAR_OFF = FIX_OFF + FIX_BYTES;
+  static constexpr int BAR_BYTES = 1024;
+  static constexpr int EPI_STAGE = 16 * NTILE * 2;  // [16 batch rows][128 columns] 16-bit: C rows leave as 16-byte vectors
+  static constexpr int STAGE_OFF = BAR_OFF + BAR_BYTES;
+  static constexpr int SMEM_BYTES = 1024 + STAGE_OFF + EPI_STAGE;
   static constexpr uint32_t MAGIC = F16 ? 0x64006400u : 0x43004300u;  // 1024 / 128 as packed pairs
   static constexpr uint32_t IDESC = umma_idesc_f16(F16 ? 0 : 1, NTILE, MB);
 };
+
+// first flattened index of CTA b, and the CTA that owns flattened index x
+__device__ __forceinline__ int range_lo(int b, int T, int G) { return (int)(((int64_t)b * T) / G); }
+__device__ __forceinline__ int owner_of(int x, int T, int G) { return (int)((((int64_t)x + 1) * G + T - 1) / T) - 1; }
 
 template <bool F16>
 __device__ __forceinline__ uint32_t sub_mul2(uint32_t x, uint32_t c, uint32_t s, bool mul) {
@@ -94,262 +112,459 @@ __device__ __forceinline__ uint32_t sub_mul2(uint32_t x, uint32_t c, uint32_t s,
   }
 }
 
+
+// Segments of a CTA's range [lo, hi): one per tile touched. Visit order: the tail segment first when it is a
+// partial tile, then the rest in natural order - so that tiles shared with a neighbour CTA are finished (and
+// their partial sums merged) early, and the kernel ends on tiles this CTA owns alone.
+struct SegIter {
+  int lo, hi, KS, m_tiles, nseg, tile0;
+  bool tail_first;
+  int seg;                              // visit index
+  int j, tile, k0, k1, slice, mt;       // current segment (j = natural index)
+  __device__ __forceinline__ SegIter(int lo_, int hi_, int ks, int mtiles) : lo(lo_), hi(hi_), KS(ks), m_tiles(mtiles), seg(0) {
+    tile0 = lo / KS;
+    nseg = (hi - 1) / KS - tile0 + 1;
+    tail_first = false;  // (tail-first visiting measured slower: the merge then competes with the main loop)
+    set();
+  }
+  __device__ __forceinline__ void set() {
+    j = tail_first ? (seg == 0 ? nseg - 1 : seg - 1) : seg;
+    tile = tile0 + j;
+    k0 = (j == 0) ? lo - tile0 * KS : 0;
+    k1 = (j == nseg - 1) ? hi - tile * KS : KS;
+    slice = tile / m_tiles;
+    mt = tile - slice * m_tiles;
+  }
+  __device__ __forceinline__ bool valid() const { return seg < nseg; }
+  __device__ __forceinline__ void advance() {
+    ++seg;
+    if (seg < nseg) set();
+  }
+};
+
 template <typename scalar_t, int MB, bool HAS_ZP>
-__global__ void __launch_bounds__(THREADS, Cfg<scalar_t, MB>::CTAS_PER_SM)
+__global__ void __launch_bounds__(THREADS, 1)
     marlin_w4a16_tc_kernel(const Params p, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmA,
                            const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUtensorMap tmZ) {
   using C = Cfg<scalar_t, MB>;
   constexpr bool F16 = C::F16;
-  constexpr int SA = C::SA, SW = C::SW;
+  constexpr int SA = C::SA, SW = C::SW, NDBUF = C::NDBUF;
   extern __shared__ uint8_t smem_raw[];
 
-  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31;
+  if (p.trace != nullptr && blockIdx.x == 0 && tid == 0) p.trace[512 + 48 + 3] = clock64();
+  // the warp index through a shuffle: ptxas then knows the role branches below are warp-uniform
+  const int w = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const bool grouped = p.group_size < p.K;
   const int gps = grouped ? KSTAGE / p.group_size : 0;  // groups per stage (1, 2, 4)
-  const int slice = blockIdx.x / p.split, chunk = blockIdx.x % p.split;
-  const int kb = chunk * p.stages_per_chunk;
-  const int nk = min(p.k_stages, kb + p.stages_per_chunk) - kb;  // > 0 by construction
+  const int G = gridDim.x, T = p.total, KS = p.k_stages;
+  const int lo = range_lo(blockIdx.x, T, G), hi = range_lo(blockIdx.x + 1, T, G);  // hi > lo: G <= T
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
   const uint32_t bar0 = smem_base + C::BAR_OFF;
-  const uint32_t fullw_bar = bar0, emptyw_bar = bar0 + 64, fulla_bar = bar0 + 128, ready_bar = bar0 + 192, emptya_bar = bar0 + 256,
-                 done_bar = bar0 + 320;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + C::BAR_OFF + 328);
-  int* s_last = reinterpret_cast<int*>(smem + C::BAR_OFF + 332);
+  // ready[slot]: 8 dequantiser warps + the activation producer's expect_tx arrival + the bytes of its two TMA loads
+  const uint32_t fullw_bar = bar0, emptyw_bar = bar0 + 64, fix_bar = bar0 + 128, ready_bar = bar0 + 192, emptya_bar = bar0 + 256,
+                 done_bar = bar0 + 320, dfree_bar = bar0 + 336;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + C::BAR_OFF + 352);
+  int* s_last = reinterpret_cast<int*>(smem + C::BAR_OFF + 356);
 
-  if (tid == 0) {
-    for (int s = 0; s < SW; ++s) {
-      mbar_init(fullw_bar + s * 8, 1);
-      mbar_init(emptyw_bar + s * 8, DQ_WARPS);
+  // barrier init, one barrier per thread of the last warp (warp 1 is busy allocating TMEM meanwhile)
+  if (tid >= THREADS - 32) {
+    const int i = tid - (THREADS - 32);
+    if (i < SW) mbar_init(fullw_bar + i * 8, 1);
+    if (i >= 8 && i < 8 + SW) mbar_init(emptyw_bar + (i - 8) * 8, DQ_GROUP);
+    if (i >= 16 && i < 16 + SA) mbar_init(ready_bar + (i - 16) * 8, DQ_GROUP + 1);
+    if (i >= 24 && i < 24 + SA) mbar_init(emptya_bar + (i - 24) * 8, 1);
+    if (i == 31) {
+      mbar_init(fix_bar, 1);
+      for (int s = 0; s < NDBUF; ++s) {
+        mbar_init(done_bar + s * 8, C::NI);
+        mbar_init(dfree_bar + s * 8, EPI_WARPS);
+      }
     }
-    for (int s = 0; s < SA; ++s) {
-      mbar_init(fulla_bar + s * 8, 1);
-      mbar_init(ready_bar + s * 8, DQ_WARPS);
-      mbar_init(emptya_bar + s * 8, 1);
-    }
-    mbar_init(done_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (w == 1) tmem_alloc(smem_u32(tmem_slot), C::TMEM_COLS);
+  if (tid == 0) {
+    prefetch_tensormap(&tmB);
+    prefetch_tensormap(&tmA);
+    prefetch_tensormap(&tmS);
+    prefetch_tensormap(&tmZ);
+  }
+  if (w == W_MMA) tmem_alloc(smem_u32(tmem_slot), C::TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (w == 0) {
+  // Every role walks the same list of segments (tile, k0..k1) and keeps the same global stage counter `it`.
+#define APH_SEGMENTS                                                                                         \
+  for (SegIter sg(lo, hi, KS, p.m_tiles); sg.valid(); sg.advance())
+#define APH_SEG_VARS                                                                                          \
+  const int tile = sg.tile, k0 = sg.k0, k1 = sg.k1, slice = sg.slice, mt = sg.mt, seg = sg.seg, segj = sg.j;  \
+  (void)tile; (void)slice; (void)mt; (void)seg; (void)segj;
+
+  // ---- merging a shared tile: sum the partial tiles of every contributor (in CTA order: deterministic) and write C.
+  //      Runs at the end of the kernel on the epilogue + dequantiser warps; the partials are pulled into the idle rings
+  //      with bulk copies (full L2 bandwidth, no register round trips). ----
+  constexpr int MT = (EPI_WARPS + DQ_GROUP * DQ_GROUPS) * 32;
+  int* s_pend = reinterpret_cast<int*>(smem + C::BAR_OFF + 368);  // npend, tile, tile
+  uint32_t fix_phase = 0;
+  auto merge_tile = [&](int tile, int mtid) {
+    const int slice = tile / p.m_tiles, mt = tile - slice * p.m_tiles;
+    const int m_rows = min(MB, p.M - mt * MB);
+    const int b_first = owner_of(tile * KS, T, G), b_last = owner_of(tile * KS + KS - 1, T, G);
+    const int n_c = b_last - b_first + 1;
+    scalar_t* crow = reinterpret_cast<scalar_t*>(p.c) + (int64_t)mt * MB * p.N + (int64_t)slice * NTILE;
+    const int units = m_rows * (NTILE / 4);              // float4 units of the tile
+    const int per = min(units, (C::BAR_OFF / 16) / n_c);  // units per contributor and chunk
+    for (int u0 = 0; u0 < units; u0 += per) {
+      const int cnt = min(per, units - u0);
+      if (mtid == 0) {
+        __threadfence();
+        asm volatile("fence.proxy.async;" ::: "memory");
+        mbar_expect_tx(fix_bar, (uint32_t)(n_c * cnt * 16));
+        for (int j = 0; j < n_c; ++j) {
+          const int bb = b_first + j;
+          const int slot = (range_lo(bb, T, G) / KS == tile) ? 0 : 1;
+          const float* src = p.scratch + ((size_t)bb * 2 + slot) * (size_t)(MB * NTILE) + (size_t)u0 * 4;
+          bulk_g2s(smem_base + (uint32_t)(j * per * 16), src, (uint32_t)(cnt * 16), fix_bar);
+        }
+      }
+      mbar_wait(fix_bar, fix_phase);
+      fix_phase ^= 1;
+      for (int idx = mtid; idx < cnt; idx += MT) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = 0; j < n_c; ++j) {
+          const float4 t = *reinterpret_cast<const float4*>(smem + (size_t)(j * per + idx) * 16);
+          v.x += t.x;
+          v.y += t.y;
+          v.z += t.z;
+          v.w += t.w;
+        }
+        const int u = u0 + idx;
+        const int m = u / (NTILE / 4), n = (u % (NTILE / 4)) * 4;
+        alignas(8) scalar_t o[4] = {ScalarTraits<scalar_t>::from_float(v.x), ScalarTraits<scalar_t>::from_float(v.y),
+                                    ScalarTraits<scalar_t>::from_float(v.z), ScalarTraits<scalar_t>::from_float(v.w)};
+        *reinterpret_cast<uint2*>(crow + (int64_t)m * p.N + n) = *reinterpret_cast<const uint2*>(o);
+      }
+      named_bar_sync(3, MT);  // the chunk buffer is reused
+    }
+    if (mtid == 0) p.counters[tile] = 0;  // leave the caller's lock buffer all-zero
+  };
+  auto merge_phase = [&](int mtid) {
+    named_bar_sync(3, MT);  // every segment is done: the rings are idle and the list of tiles to merge is published
+    const int n = s_pend[0];
+    for (int i = 0; i < n; ++i) merge_tile(s_pend[1 + i], mtid);
+  };
+
+  if (p.trace != nullptr && blockIdx.x == 0 && tid == 0) p.trace[512 + 48 + 2] = clock64();
+  if (w == W_PROD) {
     // ==================== weight producer: packed weights, scales, zero points ====================
     if (lane != 0) return;
     prefetch_tensormap(&tmB);
     if (grouped) prefetch_tensormap(&tmS);
     if (HAS_ZP && grouped) prefetch_tensormap(&tmZ);
-    const uint64_t pol_stream = policy_evict_first();  // weights are read once
+    const uint64_t pol_stream = policy_evict_first();  // weights are read once (or re-read from L2 by the next batch tile)
     const uint32_t stage_tx = (uint32_t)(W_BYTES + gps * NTILE * 2 + (HAS_ZP ? gps * (NTILE / 8) * 4 : 0));
+    int it = 0;
+    APH_SEGMENTS {
+      APH_SEG_VARS
 #pragma unroll 1
-    for (int it = 0; it < nk; ++it) {
-      const int sw = it % SW, ks = kb + it;
-      mbar_wait_relaxed(emptyw_bar + sw * 8, ((it / SW) & 1) ^ 1);
-      const uint32_t dst = smem_base + C::W_OFF + sw * W_STAGE;
-      const uint32_t fb = fullw_bar + sw * 8;
-      mbar_expect_tx(fb, stage_tx);
-      tma_load_2d_hint(dst, &tmB, slice * NTILE, ks * 8, fb, pol_stream);
-      if (grouped) {
-        tma_load_2d(dst + W_BYTES, &tmS, slice * NTILE, ks * gps, fb);
-        if constexpr (HAS_ZP) tma_load_2d(dst + W_BYTES + S_BYTES, &tmZ, slice * (NTILE / 8), ks * gps, fb);
+      for (int ks = k0; ks < k1; ++ks, ++it) {
+        const int sw = it % SW;
+        mbar_wait_relaxed(emptyw_bar + sw * 8, ((it / SW) & 1) ^ 1);
+        const uint32_t dst = smem_base + C::W_OFF + sw * W_STAGE;
+        const uint32_t fb = fullw_bar + sw * 8;
+        mbar_expect_tx(fb, stage_tx);
+        tma_load_2d_hint(dst, &tmB, slice * NTILE, ks * 8, fb, pol_stream);
+        if (grouped) {
+          tma_load_2d(dst + W_BYTES, &tmS, slice * NTILE, ks * gps, fb);
+          if constexpr (HAS_ZP) tma_load_2d(dst + W_BYTES + S_BYTES, &tmZ, slice * (NTILE / 8), ks * gps, fb);
+        }
       }
     }
     return;
   }
 
-  if (w == 2 + DQ_WARPS) {
+  if (w == W_ACT) {
     // ==================== activation producer ====================
     if (lane != 0) return;
     prefetch_tensormap(&tmA);
     const uint64_t pol_keep = policy_evict_last();  // activations are shared by every CTA
+    int it = 0;
+    APH_SEGMENTS {
+      APH_SEG_VARS
 #pragma unroll 1
-    for (int it = 0; it < nk; ++it) {
-      const int sa = it % SA, ks = kb + it;
-      mbar_wait_relaxed(emptya_bar + sa * 8, ((it / SA) & 1) ^ 1);
-      const uint32_t dst = smem_base + C::ACT_OFF + sa * C::ACT_BYTES;
-      const uint32_t fb = fulla_bar + sa * 8;
-      mbar_expect_tx(fb, (uint32_t)C::ACT_BYTES);
-      tma_load_2d_hint(dst, &tmA, ks * KSTAGE, p.m0, fb, pol_keep);
-      tma_load_2d_hint(dst + C::ACT_BOX, &tmA, ks * KSTAGE + 64, p.m0, fb, pol_keep);
+      for (int ks = k0; ks < k1; ++ks, ++it) {
+        const int sa = it % SA;
+        mbar_wait_relaxed(emptya_bar + sa * 8, ((it / SA) & 1) ^ 1);
+        const uint32_t dst = smem_base + C::ACT_OFF + sa * C::ACT_BYTES;
+        const uint32_t fb = ready_bar + sa * 8;
+        mbar_expect_tx(fb, (uint32_t)C::ACT_BYTES);
+        tma_load_2d_hint(dst, &tmA, ks * KSTAGE, mt * MB, fb, pol_keep);
+        tma_load_2d_hint(dst + C::ACT_BOX, &tmA, ks * KSTAGE + 64, mt * MB, fb, pol_keep);
+      }
     }
     return;
   }
 
-  if (w == 1) {
-    // ============================ MMA issuer: one thread ============================
-    if (lane == 0) {
-#pragma unroll 1
-      for (int it = 0; it < nk; ++it) {
-        const int sa = it % SA;
-        const uint32_t ph = (it / SA) & 1;
-        mbar_wait_relaxed(fulla_bar + sa * 8, ph);  // activations have landed (async proxy writes visible)
-        mbar_wait_relaxed(ready_bar + sa * 8, ph);  // dequantised weights are in TMEM
+  if (w == W_MMA || (C::NI == 2 && w == W_MMA2)) {
+    // ============================ MMA issuer(s): one elected lane of a convergent warp ============================
+    {
+      constexpr int NI = C::NI;
+      const int mi = (w == W_MMA) ? 0 : 1;  // takes the stages with it % NI == mi
+      constexpr uint32_t DESC_HI = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);  // SBO, version 1, SWIZZLE_128B
+      // This CTA owns all 512 TMEM columns, so its allocation starts at lane 0, column 0.
+      if (tmem_base != 0) __trap();
+      constexpr uint32_t tmem0 = 0;
+      int it = 0;
+      bool ok = false;  // result of an early, non-blocking look at the barrier of this issuer's next stage
+      APH_SEGMENTS {
+        APH_SEG_VARS
+        const int db = seg % NDBUF;
+        mbar_wait(dfree_bar + db * 8, ((seg / NDBUF) & 1) ^ 1);  // the epilogue has drained this accumulator
         tc_fence_after();
-        const uint32_t act = smem_base + C::ACT_OFF + sa * C::ACT_BYTES;
-        const uint32_t a_tmem = tmem_base + C::A_COL0 + sa * 64;
-#pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-          const uint64_t bdesc = umma_desc_sw128(act + (kk >> 2) * C::ACT_BOX + (kk & 3) * 32);
-          tc_mma_ts(tmem_base, a_tmem + kk * 8, bdesc, C::IDESC, (it > 0 || kk > 0) ? 1u : 0u);
+        const uint32_t d_tmem = tmem0 + (db * NI + mi) * MB;
+        uint32_t acc = 0;
+#pragma unroll 1
+        for (int ks = k0; ks < k1; ++ks, ++it) {
+          if (NI > 1 && (it % NI) != mi) continue;
+          const int sa = it % SA;
+          const bool tr = p.trace != nullptr && blockIdx.x == 0 && it < 64 && lane == 0;
+          if (tr) p.trace[it * 8 + 0] = clock64();
+          if (!ok) mbar_wait(ready_bar + sa * 8, (it / SA) & 1);  // activations landed and dequantised weights are in TMEM
+          tc_fence_after();
+          if (tr) p.trace[it * 8 + 2] = clock64();
+          const uint32_t desc_lo = (((smem_base + C::ACT_OFF + sa * C::ACT_BYTES) >> 4) & 0x3fffu) | (1u << 16);
+          const uint32_t a_tmem = tmem0 + C::A_COL0 + sa * 64;
+          const int nx = it + NI;
+          ok = mbar_test(ready_bar + (nx % SA) * 8, (nx / SA) & 1);  // poll the next stage while these MMAs are issued
+          tc_mma_ts_stage8(d_tmem, a_tmem, desc_lo, DESC_HI, C::IDESC, acc, (uint32_t)(C::ACT_BOX >> 4));
+          acc = 1;
+          tc_commit_elect(emptya_bar + sa * 8);  // slot (activations + TMEM weights) free once these MMAs retire
+          if (tr) p.trace[it * 8 + 3] = clock64();
         }
-        tc_commit(emptya_bar + sa * 8);  // slot (activations + TMEM weights) free once these MMAs retire
+        tc_commit_elect(done_bar + db * 8);
       }
-      tc_commit(done_bar);
     }
+    if (w != W_MMA) return;
     __syncwarp();
-    named_bar_sync(2, (DQ_WARPS + 1) * 32);  // every TMEM read of the epilogue is done
+    named_bar_sync(2, (EPI_WARPS + 1) * 32);  // every TMEM read of the epilogue is done
     tmem_dealloc(tmem_base, C::TMEM_COLS);
     return;
   }
 
-  // ================================ dequantiser warps ================================
-  const int qd = w & 3;            // TMEM lane quadrant this warp may access
-  const int h = (w - 2) >> 2;      // which half of the stage's k16-rows
-  const int g = lane >> 2;
-  const uint32_t offW = (uint32_t)(C::W_OFF + (4 * h) * (NTILE * 8) + (qd >> 1) * 512 + lane * 16 + (qd & 1) * 8);
-  const uint32_t offS = (uint32_t)(C::W_OFF + W_BYTES + (qd >> 1) * 128 + g * 16 + (qd & 1) * 8);
-  const uint32_t offZ = (uint32_t)(C::W_OFF + W_BYTES + S_BYTES + (qd >> 1) * 32 + g * 4);
-  const uint32_t a_lane = (uint32_t)(32 * qd) << 16;
-  const int rpg_shift = grouped ? 31 - __clz(p.group_size / 16) : 3;  // log2(k16-rows per group): 1, 2, 3
-  const bool two_groups = grouped && p.group_size == 32;              // a warp's 4 rows span two groups
+  if (w >= W_DQ0) {
+    // ================================ dequantiser warps ================================
+    const int qd = w & 3;                 // TMEM lane quadrant this warp may access
+    const int dw = w - W_DQ0;
+    const int h = (dw >> 2) & 1;          // which half of the stage's k16-rows
+    const int grp = dw >> 3;              // which stages: it & 1 == grp
+    const int g = lane >> 2;
+    const uint32_t offW = (uint32_t)(C::W_OFF + (4 * h) * (NTILE * 8) + (qd >> 1) * 512 + lane * 16 + (qd & 1) * 8);
+    const uint32_t offS = (uint32_t)(C::W_OFF + W_BYTES + (qd >> 1) * 128 + g * 16 + (qd & 1) * 8);
+    const uint32_t offZ = (uint32_t)(C::W_OFF + W_BYTES + S_BYTES + (qd >> 1) * 32 + g * 4);
+    const uint32_t a_lane = (uint32_t)(32 * qd) << 16;
+    const int rpg_shift = grouped ? 31 - __clz(p.group_size / 16) : 3;  // log2(k16-rows per group): 1, 2, 3
+    const bool two_groups = grouped && p.group_size == 32;              // a warp's 4 rows span two groups
 
-  uint32_t s_lo[2], s_hi[2], c_lo[2], c_hi[2];  // per 16-row tile: packed (x, x) for rows g and g + 8
-  c_lo[0] = c_lo[1] = c_hi[0] = c_hi[1] = C::MAGIC | 0x00080008u;
-  s_lo[0] = s_lo[1] = s_hi[0] = s_hi[1] = 0;
-  auto set_zp = [&](uint32_t zword) {
-    // nibble e' of the packed word holds column block {0,2,4,6,1,3,5,7}[e']: tile j rows g / g+8 sit in
-    // nibbles {0,4,1,5,2,6,3,7}[2j] and [2j+1] = j and j + 4
-#pragma unroll
-    for (int tt = 0; tt < 2; ++tt) {
-      const int j = 2 * (qd & 1) + tt;
-      const uint32_t zl = (zword >> (4 * j)) & 0xf;
-      const uint32_t zh = (zword >> (4 * j + 16)) & 0xf;
-      c_lo[tt] = C::MAGIC | zl | (zl << 16);
-      c_hi[tt] = C::MAGIC | zh | (zh << 16);
-    }
-  };
-  auto load_group = [&](uint32_t wstage, int gl) {
-    uint32_t sw0, sw1;
-    lds64(wstage + offS + gl * (NTILE * 2), sw0, sw1);
-    s_lo[0] = __byte_perm(sw0, sw0, 0x1010);
-    s_hi[0] = __byte_perm(sw0, sw0, 0x3232);
-    s_lo[1] = __byte_perm(sw1, sw1, 0x1010);
-    s_hi[1] = __byte_perm(sw1, sw1, 0x3232);
-    if constexpr (HAS_ZP) set_zp(lds32(wstage + offZ + gl * (NTILE / 8) * 4));
-  };
-  if (HAS_ZP && !grouped) set_zp(*reinterpret_cast<const uint32_t*>(p.zp + ((int64_t)slice * (NTILE / 8) + (qd >> 1) * 8 + g) * 4));
-
-  int pending = -1;  // activation/TMEM slot whose stores are issued but not yet published to the MMA warp
-  auto publish = [&]() {
-    tmem_wait_st();
-    tc_fence_before();
-    __syncwarp();
-    if (lane == 0) mbar_arrive(ready_bar + pending * 8);
-  };
-
-#pragma unroll 1
-  for (int it = 0; it < nk; ++it) {
-    const int sw = it % SW, sa = it % SA;
-    mbar_wait(fullw_bar + sw * 8, (it / SW) & 1);
-    const uint32_t wstage = smem_base + sw * W_STAGE;
-    uint32_t q[4][2];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) lds64(wstage + offW + i * (NTILE * 8), q[i][0], q[i][1]);
-    uint32_t a[2][16];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      if (grouped && (i == 0 || (i == 2 && two_groups))) load_group(wstage, (4 * h + i) >> rpg_shift);
+    uint32_t s_lo[2], s_hi[2], c_lo[2], c_hi[2];  // per 16-row tile: packed (x, x) for rows g and g + 8
+    c_lo[0] = c_lo[1] = c_hi[0] = c_hi[1] = C::MAGIC | 0x00080008u;
+    s_lo[0] = s_lo[1] = s_hi[0] = s_hi[1] = 0;
+    auto set_zp = [&](uint32_t zword) {
+      // nibble e' of the packed word holds column block {0,2,4,6,1,3,5,7}[e']: tile j rows g / g+8 sit in
+      // nibbles j and j + 4
 #pragma unroll
       for (int tt = 0; tt < 2; ++tt) {
-        const uint32_t a0 = and_or(q[i][tt], 0x000f000fu, C::MAGIC);
-        const uint32_t a2 = and_or(q[i][tt] >> 4, 0x000f000fu, C::MAGIC);
-        const uint32_t a1 = and_or(q[i][tt] >> 8, 0x000f000fu, C::MAGIC);
-        const uint32_t a3 = and_or(q[i][tt] >> 12, 0x000f000fu, C::MAGIC);
-        a[tt][4 * i + 0] = sub_mul2<F16>(a0, c_lo[tt], s_lo[tt], grouped);
-        a[tt][4 * i + 1] = sub_mul2<F16>(a1, c_hi[tt], s_hi[tt], grouped);
-        a[tt][4 * i + 2] = sub_mul2<F16>(a2, c_lo[tt], s_lo[tt], grouped);
-        a[tt][4 * i + 3] = sub_mul2<F16>(a3, c_hi[tt], s_hi[tt], grouped);
+        const int j = 2 * (qd & 1) + tt;
+        const uint32_t zl = (zword >> (4 * j)) & 0xf;
+        const uint32_t zh = (zword >> (4 * j + 16)) & 0xf;
+        c_lo[tt] = C::MAGIC | zl | (zl << 16);
+        c_hi[tt] = C::MAGIC | zh | (zh << 16);
       }
-    }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(emptyw_bar + sw * 8);  // this warp's words of the stage are in registers
-    if (pending >= 0) publish();                      // the previous stage's stores had the math above to land
-    mbar_wait(emptya_bar + sa * 8, ((it / SA) & 1) ^ 1);  // the MMAs that read this TMEM slot have retired
-    tc_fence_after();
-    const uint32_t a_tmem = tmem_base + a_lane + C::A_COL0 + sa * 64 + (4 * h) * 8;
-    tmem_st_16x128b_x8(a_tmem, a[0]);
-    tmem_st_16x128b_x8(a_tmem + (16u << 16), a[1]);
-    pending = sa;
-  }
-  if (pending >= 0) publish();
+    };
+    auto load_group = [&](uint32_t wstage, int gl) {
+      uint32_t sw0, sw1;
+      lds64(wstage + offS + gl * (NTILE * 2), sw0, sw1);
+      s_lo[0] = __byte_perm(sw0, sw0, 0x1010);
+      s_hi[0] = __byte_perm(sw0, sw0, 0x3232);
+      s_lo[1] = __byte_perm(sw1, sw1, 0x1010);
+      s_hi[1] = __byte_perm(sw1, sw1, 0x3232);
+      if constexpr (HAS_ZP) set_zp(lds32(wstage + offZ + gl * (NTILE / 8) * 4));
+    };
 
-  // ================================ epilogue ================================
-  mbar_wait(done_bar, 0);
-  tc_fence_after();
-  const int n_local = 32 * qd + lane;  // TMEM lane == output column inside the slice
-  float s_n = 1.f;
-  if (!grouped) {
-    // channelwise scales use the "single" permutation over 32-column blocks (marlin_utils.py:204-213)
-    const int nn = n_local & 63, j = nn >> 4, rr = nn & 15, gg = rr & 7;
-    const int pos = (j >> 1) * 32 + 8 * (gg >> 1) + (gg & 1) + 4 * (j & 1) + ((rr >> 3) << 1);
-    s_n = ScalarTraits<scalar_t>::to_float(reinterpret_cast<const scalar_t*>(p.s)[(int64_t)slice * NTILE + (n_local & 64) + pos]);
-  }
-  scalar_t* cout = reinterpret_cast<scalar_t*>(p.c) + (int64_t)p.m0 * p.N + (int64_t)slice * NTILE + n_local;
-  float* base = p.scratch + (size_t)slice * p.split * (size_t)(MB * NTILE);
-  float* mine = base + (size_t)chunk * (MB * NTILE);
+    int pending = -1;  // activation/TMEM slot whose stores are issued but not yet published to the MMA warp
+    auto publish = [&]() {
+      tmem_wait_st();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(ready_bar + pending * 8);
+    };
+
+    int it = 0;
+    APH_SEGMENTS {
+      APH_SEG_VARS
+      if (HAS_ZP && !grouped)
+        set_zp(*reinterpret_cast<const uint32_t*>(p.zp + ((int64_t)slice * (NTILE / 8) + (qd >> 1) * 8 + g) * 4));
 #pragma unroll 1
-  for (int cc = h; cc < MB / 16; cc += 2) {
-    if (16 * cc >= p.m_rows) break;
-    uint32_t v[16];
-    tmem_ld_32x32b_x16(tmem_base + a_lane + 16 * cc, v);
-    tmem_wait_ld();
+      for (int ks = k0; ks < k1; ++ks, ++it) {
+        if ((it & 1) != grp) continue;
+        const int sw = it % SW, sa = it % SA;
+        const bool tr = p.trace != nullptr && blockIdx.x == 0 && it < 64 && (dw & 7) == 0 && lane == 0;
+        if (tr) p.trace[it * 8 + 4] = clock64();
+        mbar_wait(fullw_bar + sw * 8, (it / SW) & 1);
+        if (tr) p.trace[it * 8 + 5] = clock64();
+        const uint32_t wstage = smem_base + sw * W_STAGE;
+        uint32_t q[4][2];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) {
-      const int m = 16 * cc + j;
-      if (m < p.m_rows) {
-        const float val = __uint_as_float(v[j]) * s_n;
-        if (p.split == 1)
-          cout[(int64_t)m * p.N] = ScalarTraits<scalar_t>::from_float(val);
-        else
-          __stcg(mine + m * NTILE + n_local, val);
+        for (int i = 0; i < 4; ++i) lds64(wstage + offW + i * (NTILE * 8), q[i][0], q[i][1]);
+        uint32_t a[2][16];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          if (grouped && (i == 0 || (i == 2 && two_groups))) load_group(wstage, (4 * h + i) >> rpg_shift);
+#pragma unroll
+          for (int tt = 0; tt < 2; ++tt) {
+            const uint32_t a0 = and_or(q[i][tt], 0x000f000fu, C::MAGIC);
+            const uint32_t a2 = and_or(q[i][tt] >> 4, 0x000f000fu, C::MAGIC);
+            const uint32_t a1 = and_or(q[i][tt] >> 8, 0x000f000fu, C::MAGIC);
+            const uint32_t a3 = and_or(q[i][tt] >> 12, 0x000f000fu, C::MAGIC);
+            a[tt][4 * i + 0] = sub_mul2<F16>(a0, c_lo[tt], s_lo[tt], grouped);
+            a[tt][4 * i + 1] = sub_mul2<F16>(a1, c_hi[tt], s_hi[tt], grouped);
+            a[tt][4 * i + 2] = sub_mul2<F16>(a2, c_lo[tt], s_lo[tt], grouped);
+            a[tt][4 * i + 3] = sub_mul2<F16>(a3, c_hi[tt], s_hi[tt], grouped);
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(emptyw_bar + sw * 8);  // this warp's words of the stage are in registers
+        if (pending >= 0) publish();                      // the previous stage's stores had the math above to land
+        if (tr) p.trace[it * 8 + 6] = clock64();
+        mbar_wait(emptya_bar + sa * 8, ((it / SA) & 1) ^ 1);  // the MMAs that read this TMEM slot have retired
+        tc_fence_after();
+        if (tr) p.trace[it * 8 + 7] = clock64();
+        const uint32_t a_tmem = tmem_base + a_lane + C::A_COL0 + sa * 64 + (4 * h) * 8;
+        tmem_st_16x128b_x8(a_tmem, a[0]);
+        tmem_st_16x128b_x8(a_tmem + (16u << 16), a[1]);
+        pending = sa;
       }
     }
+    if (pending >= 0) publish();
+    merge_phase(EPI_WARPS * 32 + tid - W_DQ0 * 32);
+    return;
   }
-  tc_fence_before();
-  named_bar_arrive(2, (DQ_WARPS + 1) * 32);
-  if (p.split == 1) return;
+  if (w < W_EPI0) return;  // second issuer warp idles when NI == 1
 
-  // ---------------- split-K: the last CTA to arrive sums the partials in chunk order ----------------
-  constexpr int CT = DQ_WARPS * 32;
-  const int ctid = tid - 64;
-  __threadfence();
-  named_bar_sync(1, CT);
-  if (ctid == 0) *s_last = (atomicAdd(&p.counters[slice], 1) == p.split - 1);
-  named_bar_sync(1, CT);
-  if (!*s_last) return;
-  __threadfence();
-  const int nvec = p.m_rows * (NTILE / 4);
-  scalar_t* crow = reinterpret_cast<scalar_t*>(p.c) + (int64_t)p.m0 * p.N + (int64_t)slice * NTILE;
-  const float4* base4 = reinterpret_cast<const float4*>(base);
-  for (int idx = ctid; idx < nvec; idx += CT) {
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 4
-    for (int ci = 0; ci < p.split; ++ci) {
-      const float4 t = __ldcg(base4 + (size_t)ci * (MB * NTILE / 4) + idx);
-      v.x += t.x;
-      v.y += t.y;
-      v.z += t.z;
-      v.w += t.w;
+  // ================================ epilogue warps ================================
+  {
+    const int qd = w & 3;
+    const int etid = tid - W_EPI0 * 32;
+    constexpr int ET = EPI_WARPS * 32;
+    const uint32_t d_lane = (uint32_t)(32 * qd) << 16;
+    const int n_local = 32 * qd + lane;  // TMEM lane == output column inside the slice
+    const int b = blockIdx.x;
+    uint8_t* stage = smem + C::STAGE_OFF;
+    int pend[2], npend = 0;  // shared tiles this CTA was the last to contribute to (at most its first and last)
+    int it0 = 0;             // global stage index of the segment's first stage
+    APH_SEGMENTS {
+      APH_SEG_VARS
+      const int db = seg % NDBUF;
+      // the second issuer's accumulator holds this segment's odd (or even) stages - if it got any
+      const bool two = C::NI == 2 && (k1 - k0) > 1;
+      const int lone = it0 % C::NI;  // with a single stage: the issuer that took it
+      it0 += k1 - k0;
+      const bool direct = (k0 == 0 && k1 == KS);
+      const int m_rows = min(MB, p.M - mt * MB);
+      float s_n = 1.f;
+      if (!grouped) {
+        // channelwise scales use the "single" permutation over 32-column blocks (marlin_utils.py:204-213)
+        const int nn = n_local & 63, j = nn >> 4, rr = nn & 15, gg = rr & 7;
+        const int pos = (j >> 1) * 32 + 8 * (gg >> 1) + (gg & 1) + 4 * (j & 1) + ((rr >> 3) << 1);
+        s_n = ScalarTraits<scalar_t>::to_float(reinterpret_cast<const scalar_t*>(p.s)[(int64_t)slice * NTILE + (n_local & 64) + pos]);
+      }
+      scalar_t* crow = reinterpret_cast<scalar_t*>(p.c) + (int64_t)mt * MB * p.N + (int64_t)slice * NTILE;
+      float* mine = p.scratch + ((size_t)b * 2 + (segj == 0 ? 0 : 1)) * (size_t)(MB * NTILE) + n_local;
+
+      const bool etr = p.trace != nullptr && b == 0 && etid == 0 && seg < 6;
+      if (etr) p.trace[512 + seg * 8 + 0] = clock64();
+      mbar_wait(done_bar + db * 8, (seg / NDBUF) & 1);
+      tc_fence_after();
+      if (etr) p.trace[512 + seg * 8 + 1] = clock64();
+      const uint32_t d0 = tmem_base + d_lane + (db * C::NI + (two ? 0 : lone)) * MB;
+      const uint32_t d1 = tmem_base + d_lane + (db * C::NI + 1) * MB;
+#pragma unroll 1
+      for (int cc = 0; cc < MB / 16; ++cc) {
+        const int rows = m_rows - 16 * cc;  // batch rows in this chunk of 16 accumulator columns
+        if (rows <= 0) break;
+        uint32_t v[16];
+        tmem_ld_32x32b_x16(d0 + 16 * cc, v);
+        if (two) {
+          uint32_t v2[16];
+          tmem_ld_32x32b_x16(d1 + 16 * cc, v2);
+          tmem_wait_ld();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(v2[j]));
+        } else {
+          tmem_wait_ld();
+        }
+        if (cc == MB / 16 - 1 || rows <= 16) {
+          // last TMEM read of this accumulator: the MMA warps may start the next tile in it
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(dfree_bar + db * 8);
+        }
+        if (direct) {
+          // transpose through shared memory so that C rows leave as 16-byte vectors
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            *reinterpret_cast<scalar_t*>(stage + j * (NTILE * 2) + n_local * 2) = ScalarTraits<scalar_t>::from_float(__uint_as_float(v[j]) * s_n);
+          named_bar_sync(1, ET);
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const int vec = etid + i * ET, row = vec >> 4, c16 = vec & 15;
+            if (row < rows)
+              *reinterpret_cast<uint4*>(crow + (int64_t)(16 * cc + row) * p.N + c16 * 8) =
+                  *reinterpret_cast<const uint4*>(stage + row * (NTILE * 2) + c16 * 16);
+          }
+          named_bar_sync(1, ET);  // the staging tile is reused by the next chunk
+        } else {
+          float* dst = mine + (size_t)(16 * cc) * NTILE;
+          if (rows >= 16) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) __stcg(dst + j * NTILE, __uint_as_float(v[j]) * s_n);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (j < rows) __stcg(dst + j * NTILE, __uint_as_float(v[j]) * s_n);
+          }
+        }
+      }
+      if (etr) p.trace[512 + seg * 8 + 2] = clock64();
+      if (direct) continue;
+
+      // ---- the tile's k range is shared with other CTAs: whoever arrives last merges the partials (at the end) ----
+      __threadfence();
+      named_bar_sync(1, ET);
+      if (etid == 0) {
+        const int n_c = owner_of(tile * KS + KS - 1, T, G) - owner_of(tile * KS, T, G) + 1;
+        *s_last = (atomicAdd(&p.counters[tile], 1) == n_c - 1);
+      }
+      named_bar_sync(1, ET);
+      if (*s_last) pend[npend++] = tile;
+      named_bar_sync(1, ET);  // s_last may be rewritten by the next segment
+      if (etr) p.trace[512 + seg * 8 + 3] = clock64();
     }
-    const int m = idx / (NTILE / 4), n = (idx % (NTILE / 4)) * 4;
-    scalar_t o[4] = {ScalarTraits<scalar_t>::from_float(v.x), ScalarTraits<scalar_t>::from_float(v.y),
-                     ScalarTraits<scalar_t>::from_float(v.z), ScalarTraits<scalar_t>::from_float(v.w)};
-    *reinterpret_cast<uint2*>(crow + (int64_t)m * p.N + n) = *reinterpret_cast<const uint2*>(o);
+    if (etid == 0) {
+      s_pend[0] = npend;
+      s_pend[1] = pend[0];
+      s_pend[2] = pend[1];
+    }
+    if (p.trace != nullptr && b == 0 && etid == 0) p.trace[512 + 48 + 0] = clock64();
+    merge_phase(etid);
+    if (p.trace != nullptr && b == 0 && etid == 0) p.trace[512 + 48 + 1] = clock64();
+    tc_fence_before();
+    named_bar_arrive(2, (EPI_WARPS + 1) * 32);
   }
-  if (ctid == 0) p.counters[slice] = 0;  // leave the caller's lock buffer all-zero
+#undef APH_SEGMENTS
+#undef APH_SEG_VARS
 }
 
 }  // namespace mgtc

@@ -212,5 +212,91 @@ __device__ __forceinline__ void tmem_st_16x128b_x8(uint32_t taddr, const uint32_
       : "memory");
 }
 
+// Warp-convergent variants: every lane executes the statement, one elected lane issues the tcgen05 op. Keeping the
+// control flow uniform lets ptxas feed the uniform datapath directly instead of looping over "active" lanes.
+__device__ __forceinline__ void tc_mma_ts_elect(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_desc_lo, uint32_t b_desc_hi, uint32_t idesc,
+                                                uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p, q;\n"
+      ".reg .b64 bd;\n"
+      "elect.sync _|q, 0xffffffff;\n"
+      "setp.ne.b32 p, %5, 0;\n"
+      "mov.b64 bd, {%2, %3};\n"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], bd, %4, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "r"(a_tmem), "r"(b_desc_lo), "r"(b_desc_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit_elect(uint32_t bar) {
+  asm volatile(
+      "{\n"
+      ".reg .pred q;\n"
+      "elect.sync _|q, 0xffffffff;\n"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n"
+      "}\n" ::"r"(bar)
+      : "memory");
+}
+
+// Eight K=16 MMAs of one 128-k stage in a single statement: the TMEM column and the descriptor start address
+// advance by constants, which keeps the operand arithmetic on the uniform datapath.
+__device__ __forceinline__ void tc_mma_ts_stage8(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_desc_lo, uint32_t b_desc_hi, uint32_t idesc,
+                                                 uint32_t accumulate_first, uint32_t box_step16) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p, q, t;\n"
+      ".reg .b64 bd;\n"
+      ".reg .b32 lo, at, lo4;\n"
+      "elect.sync _|q, 0xffffffff;\n"
+      "setp.ne.b32 p, %5, 0;\n"
+      "setp.eq.b32 t, 0, 0;\n"
+      "add.u32 lo4, %2, %6;\n"
+      "mov.b64 bd, {%2, %3};\n"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], bd, %4, p;\n"
+      "add.u32 lo, %2, 2;\n"
+      "mov.b64 bd, {lo, %3};\n"
+      "add.u32 at, %1, 8;\n"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [at], bd, %4, t;\n"
+      "add.u32 lo, %2, 4;\n"
+      "mov.b64 bd, {lo, %3};\n"
+      "add.u32 at, %1, 16;\n"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [at], bd, %4, t;\n"
+      "add.u32 lo, %2, 6;\n"
+      "mov.b64 bd, {lo, %3};\n"
+      "add.u32 at, %1, 24;\n"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [at], bd, %4, t;\n"
+      "mov.b64 bd, {lo4, %3};\n"
+      "add.u32 at, %1, 32;\n"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [at], bd, %4, t;\n"
+      "add.u32 lo, lo4, 2;\n"
+      "mov.b64 bd, {lo, %3};\n"
+      "add.u32 at, %1, 40;\n"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [at], bd, %4, t;\n"
+      "add.u32 lo, lo4, 4;\n"
+      "mov.b64 bd, {lo, %3};\n"
+      "add.u32 at, %1, 48;\n"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [at], bd, %4, t;\n"
+      "add.u32 lo, lo4, 6;\n"
+      "mov.b64 bd, {lo, %3};\n"
+      "add.u32 at, %1, 56;\n"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [at], bd, %4, t;\n"
+      "}\n" ::"r"(d_tmem),
+      "r"(a_tmem), "r"(b_desc_lo), "r"(b_desc_hi), "r"(idesc), "r"(accumulate_first), "r"(box_step16)
+      : "memory");
+}
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(done)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return done != 0;
+}
+
 }  // namespace ptx
 }  // namespace aphb200

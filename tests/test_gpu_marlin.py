@@ -100,6 +100,23 @@ def test_gptq_marlin_gemm_llama_shapes(M):
         case(M, 14336, 4096, 128, torch.bfloat16, seed=4)
 
 
+@pytest.mark.parametrize("M,K,N,gs", [(128, 1024, 512, 128), (256, 2048, 256, 64), (300, 1024, 512, 128), (1024, 512, 384, 32),
+                                      (520, 1024, 128, -1), (17, 8192, 128, 128), (64, 16384, 256, 128), (96, 4096, 1280, 128)])
+def test_gptq_marlin_gemm_large_batch_tensor_memory_path(M, K, N, gs):
+    # batch tiles of up to 256 rows, several batch tiles per call, stream-K ranges that split one tile over many CTAs
+    # (small N, deep K) - the tcgen05 path; test_marlin_gemm.py:45-52 sweeps M up to 257 the same way
+    case(M, K, N, gs, torch.bfloat16, seed=11)
+    case(M, K, N, gs, torch.float16, zp=(gs != -1), seed=12)
+
+
+def test_gptq_marlin_gemm_repeated_calls_leave_workspace_clean():
+    # back-to-back launches share the lock buffer (arrival counters) and the scratch: results must not depend on history
+    outs = []
+    for _ in range(3):
+        outs.append(case(48, 4096, 512, 128, torch.bfloat16, seed=5))
+    assert outs[0] == outs[1] == outs[2]
+
+
 def test_gptq_marlin_gemm_strided_a_and_flags():
     case(9, 512, 256, 128, torch.bfloat16, lda_pad=64, use_fp32_reduce=False)
     case(9, 512, 256, 128, torch.float16, lda_pad=8, use_atomic_add=True)

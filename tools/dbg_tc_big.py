@@ -1,0 +1,17 @@
+"""One eager call of the GEMM on a big shape (for compute-sanitizer): python tools/dbg_tc_big.py M K N"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import aphrodite_fork_b200 as A
+A.load()
+M, K, N = [int(x) for x in sys.argv[1:4]]
+dev = "cuda"
+b = torch.randint(-2**31, 2**31 - 1, (K // 16, N * 2), dtype=torch.int32, device=dev)
+s = (torch.rand(K // 128, N, device=dev) * 0.01 + 0.005).to(torch.bfloat16)
+a = torch.randn(M, K, device=dev).to(torch.bfloat16)
+e = torch.empty(0, dtype=torch.int32, device=dev)
+ws = torch.zeros(N // 64 * 16, dtype=torch.int32, device=dev)
+for i in range(3):
+    out = A.ops.gptq_marlin_gemm(a, b, s, e, e, e, ws, 1125899907892224, M, N, K, True)
+torch.cuda.synchronize()
+print("ok", out.float().abs().mean().item(), int(ws.abs().sum()))
