@@ -340,7 +340,8 @@ static bool use_tc_path(int64_t M, int64_t N) {
     return e[0] == 't' ? 2 : e[0] == 'm' ? 1 : 0;
   }();
   if (forced) return forced == 2;
-  return M > 8;
+  // measured crossover (tools/bench_gemm.py, C3 shapes): the register-accumulator kernel wins up to 16 rows
+  return M > 16;
 }
 
 // ScalarType ids, kernels/core/scalar_type.hpp:100-138 (values pinned in tests/golden/marlin_golden.npz)

@@ -1,0 +1,180 @@
+"""A Llama-shaped decode step built from the three hot-path kernels, tensor-parallel over `torch.distributed`.
+
+This is the caller side of SURVEY.md 3.1 reduced to what the hot path needs: per layer
+    qkv = W4A16 GEMM (column parallel)  ->  reshape_and_cache(k, v)  ->  paged attention (this rank's heads)
+    o   = W4A16 GEMM (row parallel)     ->  all_reduce
+    gu  = W4A16 GEMM (column parallel)  ->  SiLU(gate) * up
+    dn  = W4A16 GEMM (row parallel)     ->  all_reduce
+with residual adds. RMSNorm / RoPE are left out on purpose (the reference's layernorm and
+pos_encoding kernels are the next row, not this one); weights are synthetic. One step can be captured in a CUDA
+graph, the NCCL all_reduces included, which is how the reference runs decode (`cuda_communicator.py`).
+
+Reference call sites mirrored: modeling/models/llama.py:100-215 (layer structure and head split),
+modeling/layers/linear.py:474-484,1279-1283, attention/ops/paged_attn.py:60-160.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional
+
+import torch
+
+from . import _custom_ops as ops
+from .paged_attn import PagedAttention
+from .tp import MarlinShard, TPGroup, shard_heads, verify_marlin_supports_shape, marlin_make_workspace
+
+SCALAR_TYPE_UINT4B8 = 1125899907892224  # kernels/core/scalar_type.hpp:100-138
+
+
+@dataclass
+class DecodeConfig:
+    hidden: int
+    intermediate: int
+    num_heads: int
+    num_kv_heads: int
+    head_size: int
+    num_layers: int
+    group_size: int = 128
+    block_size: int = 16
+    kv_cache_dtype: str = "fp8"  # "auto" | "fp8" | "fp8_e4m3" | "fp8_e5m2"
+    dtype: torch.dtype = torch.bfloat16
+
+    # benchmark_shapes.py:3-8 / :57-62
+    @staticmethod
+    def llama3_8b(num_layers: int = 32, **kw) -> "DecodeConfig":
+        return DecodeConfig(4096, 14336, 32, 8, 128, num_layers, **kw)
+
+    @staticmethod
+    def llama3_70b(num_layers: int = 80, **kw) -> "DecodeConfig":
+        return DecodeConfig(8192, 28672, 64, 8, 128, num_layers, **kw)
+
+
+def _synthetic_marlin(size_k: int, size_n: int, group_size: int, dtype, device, gen, row_parallel: bool) -> MarlinShard:
+    """Random bytes in the Marlin layout: any int32 pattern is a valid packed 4-bit tile."""
+    groups = 1 if group_size == -1 else size_k // group_size
+    qw = torch.randint(-2**31, 2**31 - 1, (size_k // 16, size_n * 2), dtype=torch.int32, device=device, generator=gen)
+    sc = (torch.rand(groups, size_n, device=device, generator=gen) * 0.0005 + 0.00075).to(dtype)  # layer gain < 1
+    return MarlinShard(qw, sc, None, size_k, size_n, group_size, row_parallel)
+
+
+class MarlinLinear:
+    """apply() of the reference's GPTQMarlinLinearMethod (gptq_marlin.py:330-360) for one shard."""
+
+    def __init__(self, shard: MarlinShard):
+        self.w = shard
+        self.workspace = marlin_make_workspace(shard.size_n, shard.q_weight.device)
+        self.empty = torch.empty(0, dtype=torch.int32, device=shard.q_weight.device)
+
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        w = self.w
+        zeros = self.empty if w.zeros is None else w.zeros
+        return ops.gptq_marlin_gemm(x, w.q_weight, w.scales, zeros, self.empty, self.empty, self.workspace,
+                                    SCALAR_TYPE_UINT4B8, x.shape[0], w.size_n, w.size_k, True, w.zeros is not None, False,
+                                    True, False)
+
+
+class DecodeLayer:
+    def __init__(self, cfg: DecodeConfig, tp: TPGroup, num_blocks: int, device, gen):
+        self.cfg, self.tp = cfg, tp
+        t = tp.world_size
+        self.h, self.kvh = shard_heads(cfg.num_heads, cfg.num_kv_heads, t)
+        d = cfg.head_size
+        self.q_size, self.kv_size = self.h * d, self.kvh * d
+        inter_l = cfg.intermediate // t
+        g = cfg.group_size
+        for n_l, k_l, k in ((self.q_size + 2 * self.kv_size, cfg.hidden, cfg.hidden), (cfg.hidden, self.q_size, cfg.num_heads * d),
+                            (2 * inter_l, cfg.hidden, cfg.hidden), (cfg.hidden, inter_l, cfg.intermediate)):
+            verify_marlin_supports_shape(n_l, k_l, k, k if g == -1 else g)
+        mk = lambda k, n, row: MarlinLinear(_synthetic_marlin(k, n, g, cfg.dtype, device, gen, row))
+        self.qkv = mk(cfg.hidden, self.q_size + 2 * self.kv_size, False)
+        self.o = mk(self.q_size, cfg.hidden, True)
+        self.gate_up = mk(cfg.hidden, 2 * inter_l, False)
+        self.down = mk(inter_l, cfg.hidden, True)
+        fp8 = cfg.kv_cache_dtype != "auto"
+        shape = PagedAttention.get_kv_cache_shape(num_blocks, cfg.block_size, self.kvh, d)
+        if fp8:
+            self.kv_cache = torch.randint(0, 120, shape, dtype=torch.uint8, device=device, generator=gen)
+        else:
+            self.kv_cache = (torch.rand(shape, device=device, generator=gen) - 0.5).to(cfg.dtype)
+        self.key_cache, self.value_cache = PagedAttention.split_kv_cache(self.kv_cache, self.kvh, d)
+        self.k_scale = torch.ones((), dtype=torch.float32, device=device)
+        self.v_scale = torch.ones((), dtype=torch.float32, device=device)
+        self.scale = d ** -0.5
+
+    def forward(self, x: torch.Tensor, slot_mapping, block_tables, seq_lens, max_seq_len: int) -> torch.Tensor:
+        cfg, d = self.cfg, self.cfg.head_size
+        qkv = self.qkv(x)
+        q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
+        q = q.reshape(-1, self.h, d)
+        PagedAttention.write_to_paged_cache(k.reshape(-1, self.kvh, d), v.reshape(-1, self.kvh, d), self.key_cache,
+                                            self.value_cache, slot_mapping, cfg.kv_cache_dtype, self.k_scale, self.v_scale)
+        a = PagedAttention.forward_decode(q, self.key_cache, self.value_cache, block_tables, seq_lens, max_seq_len,
+                                          cfg.kv_cache_dtype, self.kvh, self.scale, None, self.k_scale, self.v_scale,
+                                          tp_rank=self.tp.rank)
+        x = x + self.tp.all_reduce(self.o(a.reshape(-1, self.q_size)))
+        gu = self.gate_up(x)
+        gate, up = gu.chunk(2, dim=-1)
+        x = x + self.tp.all_reduce(self.down(torch.nn.functional.silu(gate) * up))
+        return x
+
+
+class DecodeModel:
+    """`num_layers` layers over one set of paged-cache metadata; `step()` runs one decode step for the whole batch."""
+
+    def __init__(self, cfg: DecodeConfig, batch: int, ctx: int, tp: Optional[TPGroup] = None, device="cuda", seed: int = 0):
+        self.cfg, self.batch, self.ctx = cfg, batch, ctx
+        self.tp = tp if tp is not None else TPGroup()
+        gen = torch.Generator(device=device).manual_seed(seed)
+        bs = cfg.block_size
+        blocks_per_seq = (ctx + bs - 1) // bs
+        num_blocks = batch * blocks_per_seq
+        perm = torch.randperm(num_blocks, device=device, generator=gen).to(torch.int32)
+        self.block_tables = perm.view(batch, blocks_per_seq).contiguous()
+        self.seq_lens = torch.full((batch,), ctx, dtype=torch.int32, device=device)
+        last = self.block_tables[:, (ctx - 1) // bs].to(torch.int64)
+        self.slot_mapping = last * bs + (ctx - 1) % bs  # the new token is the last position of each sequence
+        self.layers: List[DecodeLayer] = [DecodeLayer(cfg, self.tp, num_blocks, device, gen) for _ in range(cfg.num_layers)]
+        self.x = (torch.randn(batch, cfg.hidden, device=device, generator=gen) * 0.05).to(cfg.dtype)
+        self.out = torch.empty_like(self.x)
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+
+    def _forward(self) -> None:
+        x = self.x
+        for layer in self.layers:
+            x = layer.forward(x, self.slot_mapping, self.block_tables, self.seq_lens, self.ctx)
+        self.out.copy_(x)
+
+    def capture(self) -> None:
+        """Capture one step (kernels and all_reduces) in a CUDA graph after a warm-up on a side stream."""
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(2):
+                self._forward()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._forward()
+
+    def step(self) -> torch.Tensor:
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self._forward()
+        return self.out
+
+    def launches_per_step(self) -> int:
+        """Kernels of this repo per step: 4 GEMMs + cache write + attention (+ its split-K reduce) per layer."""
+        return self.cfg.num_layers * 7
+
+    def kv_bytes_per_step(self) -> int:
+        l0 = self.layers[0]
+        return 2 * self.batch * self.ctx * l0.kvh * self.cfg.head_size * l0.kv_cache.element_size() * self.cfg.num_layers
+
+    def weight_bytes(self) -> int:
+        tot = 0
+        for l in self.layers:
+            for lin in (l.qkv, l.o, l.gate_up, l.down):
+                tot += lin.w.q_weight.numel() * 4 + lin.w.scales.numel() * 2
+        return tot

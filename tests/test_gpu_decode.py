@@ -1,0 +1,122 @@
+"""GPU parity of one decode step (GEMM -> cache write -> paged attention -> GEMM -> ... ) against the oracle, and
+the same step over 2 GPUs with NCCL when the box has them. Tolerance: the step chains four bf16 GEMM
+outputs and one attention per layer, so the bound is 3e-2 of the output's max magnitude (each stage is covered at its
+own, tighter, tolerance in test_gpu_marlin.py / test_gpu_attention.py)."""
+import os
+import socket
+
+import pytest
+import torch
+
+import aphrodite_fork_b200 as A
+from aphrodite_fork_b200.decode import DecodeConfig, DecodeModel
+from oracle import oracle
+from oracle import marlin_format as mf
+
+pytestmark = pytest.mark.gpu
+
+
+def _dq(lin):
+    w = lin.w
+    return mf.dequantize(w.q_weight.cpu(), w.scales.cpu(), None, w.size_k, w.size_n, 4, w.group_size, False)
+
+
+def _bf16(x64):
+    return x64.to(torch.bfloat16)
+
+
+def _reference_step(model: DecodeModel, caches_before):
+    """The same step on the CPU: fp64 GEMMs on the dequantised weights rounded to bf16 where the kernels round."""
+    cfg = model.cfg
+    x = model.x.cpu()
+    bt, sl, slots = model.block_tables.cpu(), model.seq_lens.cpu(), model.slot_mapping.cpu()
+    for layer, (kc, vc) in zip(model.layers, caches_before):
+        d = cfg.head_size
+        qkv = _bf16(oracle.gemm(x, _dq(layer.qkv)))
+        q, k, v = qkv.split([layer.q_size, layer.kv_size, layer.kv_size], dim=-1)
+        k = k.reshape(-1, layer.kvh, d).contiguous()
+        v = v.reshape(-1, layer.kvh, d).contiguous()
+        oracle.reshape_and_cache(k, v, kc, vc, slots, cfg.kv_cache_dtype, 1.0, 1.0)
+        _, a = oracle.paged_attention(q.reshape(-1, layer.h, d).contiguous(), kc, vc, layer.kvh, layer.scale, bt, sl,
+                                      cfg.block_size, None, cfg.kv_cache_dtype, 1.0, 1.0)
+        x = x + _bf16(oracle.gemm(a.reshape(-1, layer.q_size), _dq(layer.o)))
+        gu = _bf16(oracle.gemm(x, _dq(layer.gate_up)))
+        gate, up = gu.chunk(2, dim=-1)
+        x = x + _bf16(oracle.gemm(torch.nn.functional.silu(gate) * up, _dq(layer.down)))
+    return x
+
+
+@pytest.mark.parametrize("kv", ["auto", "fp8"])
+@pytest.mark.parametrize("batch", [3, 20])
+def test_decode_step_matches_oracle(kv, batch):
+    cfg = DecodeConfig(hidden=512, intermediate=1024, num_heads=8, num_kv_heads=2, head_size=64, num_layers=2,
+                       group_size=128, kv_cache_dtype=kv)
+    model = DecodeModel(cfg, batch=batch, ctx=77, seed=1)
+    before = [(l.key_cache.cpu().clone(), l.value_cache.cpu().clone()) for l in model.layers]
+    out = model.step().cpu().double()
+    ref = _reference_step(model, [(k.clone(), v.clone()) for k, v in before]).double()
+    assert torch.isfinite(out).all()
+    err = (out - ref).abs().max() / ref.abs().max()
+    assert float(err) < 3e-2, f"decode step differs from the oracle: {float(err):.3e}"
+    # positions other than the new token's slot are untouched by the step
+    kc_gpu, (kc_before, _) = model.layers[0].key_cache.cpu(), before[0]
+    changed = (kc_gpu.view(torch.uint8) != kc_before.view(torch.uint8)).flatten(2).any(dim=2).any(dim=1)
+    written_blocks = set((model.slot_mapping.cpu() // cfg.block_size).tolist())
+    assert set(changed.nonzero().flatten().tolist()) <= written_blocks
+
+
+def test_decode_step_under_cuda_graph_is_repeatable():
+    cfg = DecodeConfig(hidden=1024, intermediate=2048, num_heads=16, num_kv_heads=4, head_size=128, num_layers=3)
+    model = DecodeModel(cfg, batch=16, ctx=300, seed=2)
+    eager = model.step().clone()
+    model.capture()
+    g1 = model.step().clone()
+    g2 = model.step().clone()
+    assert torch.equal(g1, g2)
+    assert torch.allclose(g1.float(), eager.float(), rtol=2e-2, atol=1e-3)
+    assert model.launches_per_step() == 21
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _nccl_worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from aphrodite_fork_b200.tp import TPGroup
+        cfg = DecodeConfig(hidden=1024, intermediate=2048, num_heads=16, num_kv_heads=4, head_size=128, num_layers=2)
+        model = DecodeModel(cfg, batch=8, ctx=200, tp=TPGroup(), device=f"cuda:{rank}", seed=3)
+        assert (model.layers[0].h, model.layers[0].kvh) == (16 // world, 4 // world)
+        out = model.step().float()
+        # every rank must hold the same hidden state after the all_reduces
+        ref = out.clone()
+        dist.broadcast(ref, src=0)
+        same = bool(torch.equal(out, ref))
+        model.capture()
+        g = model.step().float()
+        q.put((rank, same, bool(torch.isfinite(out).all()), bool(torch.allclose(g, out, rtol=2e-2, atol=1e-3))))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_tensor_parallel_decode_step_over_nccl():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_nccl_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=300)
+        assert p.exitcode == 0
+    got = sorted(q.get(timeout=10) for _ in range(2))
+    assert got == [(0, True, True, True), (1, True, True, True)]

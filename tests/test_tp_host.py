@@ -1,0 +1,142 @@
+"""CPU tests of the tensor-parallel host logic: shape rules, head split, slicing of Marlin-format
+weights, and the all_reduce exchange over a world_size-2 gloo group. The oracle (CPU restatement of the format and of
+the GEMM) is the checker; the product code under test is aphrodite_fork_b200.tp only - no CUDA involved."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import aphrodite_fork_b200.tp as tp
+from oracle import marlin_format as mf
+import synth
+
+
+def test_verify_marlin_supports_shape_messages():
+    # marlin_utils.py:96-122: same three failure classes, same wording of the leading clause
+    tp.verify_marlin_supports_shape(1280, 8192, 8192, 128)          # C4 TP8 qkv
+    tp.verify_marlin_supports_shape(8192, 1024, 8192, 128)          # C4 TP8 o
+    with pytest.raises(ValueError, match="output_size_per_partition = 96 is not divisible by  min_thread_n = 64"):
+        tp.verify_marlin_supports_shape(96, 1024, 1024, 128)
+    with pytest.raises(ValueError, match="input_size_per_partition = 192 is not divisible by min_thread_k = 128"):
+        tp.verify_marlin_supports_shape(128, 192, 384, 64)
+    with pytest.raises(ValueError, match="input_size_per_partition = 1408 is not divisible by group_size = 256"):
+        tp.verify_marlin_supports_shape(128, 1408, 29568, 256)
+    ok, msg = tp.check_marlin_supports_shape(128, 3696, 29568, 128)   # Qwen2-72B inter / 8
+    assert not ok and "3696" in msg
+
+
+def test_flags_and_workspace():
+    assert tp.marlin_is_k_full(False, True) and tp.marlin_is_k_full(True, False) and not tp.marlin_is_k_full(True, True)
+    assert tp.marlin_repeat_scales_on_all_ranks(False, -1, True)
+    assert not tp.marlin_repeat_scales_on_all_ranks(False, 128, True)
+    assert not tp.marlin_repeat_scales_on_all_ranks(False, -1, False)
+    assert tp.marlin_repeat_scales_on_all_ranks(True, 128, False)
+    ws = tp.marlin_make_workspace(4096, "cpu")
+    assert ws.shape == (4096 // 64 * 16,) and ws.dtype == torch.int32 and int(ws.abs().sum()) == 0
+
+
+def test_shard_heads():
+    assert tp.shard_heads(64, 8, 8) == (8, 1)      # C4 TP8
+    assert tp.shard_heads(64, 8, 2) == (32, 4)
+    assert tp.shard_heads(32, 8, 1) == (32, 8)
+    assert tp.shard_heads(64, 8, 16) == (4, 1)     # kv heads replicated (llama.py:118-127)
+    with pytest.raises(ValueError):
+        tp.shard_heads(30, 8, 4)
+    with pytest.raises(ValueError):
+        tp.shard_heads(64, 8, 3)
+
+
+def _quantized(K, N, gs, zp, seed):
+    w = synth.tensor((K, N), seed, torch.bfloat16, 1.0)
+    return mf.marlin_quantize(w, 4, gs, zp)   # (w_ref, q_weight, scales, zeros)
+
+
+@pytest.mark.parametrize("gs,zp", [(128, False), (64, True), (-1, False), (32, False)])
+@pytest.mark.parametrize("tp_size", [2, 4])
+def test_shard_marlin_weight_matches_requantised_slices(gs, zp, tp_size):
+    """A slice of the packed tensors decodes to the same weights as the corresponding slice of the dense matrix."""
+    K, N = 1024, 512
+    w_ref, qw, sc, bz = _quantized(K, N, gs, zp, 3)
+    bz_t = bz if zp else None
+    for rank in range(tp_size):
+        col = tp.shard_marlin_weight(qw, sc, bz_t, K, N, gs, tp_size, rank, "column")
+        n_l = N // tp_size
+        got = mf.dequantize(col.q_weight, col.scales, col.zeros, K, n_l, 4, gs, zp)
+        assert torch.equal(got, w_ref[:, rank * n_l:(rank + 1) * n_l])
+        row = tp.shard_marlin_weight(qw, sc, bz_t, K, N, gs, tp_size, rank, "row")
+        k_l = K // tp_size
+        got = mf.dequantize(row.q_weight, row.scales, row.zeros, k_l, N, 4, gs, zp)
+        assert torch.equal(got, w_ref[rank * k_l:(rank + 1) * k_l])
+        assert row.is_row_parallel and not col.is_row_parallel
+        assert row.scales.shape[0] == (1 if gs == -1 else k_l // gs)
+
+
+def test_shard_marlin_weight_rejects_bad_splits():
+    K, N = 512, 192
+    w_ref, qw, sc, bz = _quantized(K, N, 128, False, 5)
+    with pytest.raises(ValueError, match="min_thread_n"):
+        tp.shard_marlin_weight(qw, sc, None, K, N, 128, 2, 0, "column")   # 96 columns per rank
+    with pytest.raises(ValueError, match="min_thread_k|group_size"):
+        tp.shard_marlin_weight(qw, sc, None, K, N, 128, 8, 0, "row")      # 64 rows per rank
+    with pytest.raises(ValueError):
+        tp.shard_marlin_weight(qw, sc, None, K, N, 128, 2, 2, "row")
+    with pytest.raises(ValueError):
+        tp.shard_marlin_weight(qw, sc, None, K, N, 128, 2, 0, "diagonal")
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _tp_worker(rank, world, port, result_q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        K, N, M, gs = 1024, 256, 5, 128
+        w_ref, qw, sc, bz = _quantized(K, N, gs, False, 9)
+        a = synth.tensor((M, K), 10, torch.bfloat16, 1.0)
+        grp = tp.TPGroup()
+        assert grp.world_size == world and grp.rank == rank
+        # column parallel: each rank owns N / world output columns, no exchange; gathered here only to check
+        col = tp.shard_marlin_weight(qw, sc, None, K, N, gs, world, rank, "column")
+        w_col = mf.dequantize(col.q_weight, col.scales, None, K, N // world, 4, gs, False)
+        y_col = a.float() @ w_col.float()
+        parts = [torch.empty_like(y_col) for _ in range(world)]
+        dist.all_gather(parts, y_col)
+        # row parallel: each rank owns K / world input rows and produces a full-width partial -> all_reduce
+        row = tp.shard_marlin_weight(qw, sc, None, K, N, gs, world, rank, "row")
+        k_l = K // world
+        w_row = mf.dequantize(row.q_weight, row.scales, None, k_l, N, 4, gs, False)
+        y_row = grp.all_reduce(a[:, rank * k_l:(rank + 1) * k_l].float() @ w_row.float())
+        full = a.float() @ w_ref.float()
+        ok_col = torch.allclose(torch.cat(parts, dim=1), full, rtol=1e-5, atol=1e-4)
+        ok_row = torch.allclose(y_row, full, rtol=1e-4, atol=1e-3)
+        result_q.put((rank, ok_col, ok_row))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_row_and_column_parallel_over_gloo_world_size_2():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_tp_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=240)
+        assert p.exitcode == 0
+    got = sorted(q.get(timeout=10) for _ in range(2))
+    assert got == [(0, True, True), (1, True, True)]
+
+
+def test_tp_group_is_a_noop_without_a_process_group():
+    g = tp.TPGroup()
+    x = torch.ones(3)
+    assert g.world_size == 1 and g.rank == 0 and g.all_reduce(x) is x and torch.equal(x, torch.ones(3))
