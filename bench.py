@@ -33,6 +33,9 @@ sys.path.insert(0, ROOT)
 H, KVH, D, BS = 32, 8, 128, 16
 BATCH, CTX = 64, 4096
 METRIC = "paged-attn decode KV GB/s"
+# dram__bytes_read.sum + dram__bytes_write.sum of the split-K kernel + its reduce for one launch of this workload, from the
+# `ncu --set full` capture summarised in profiles/r01_ncu_full_paged_attention_v1_raw.csv (539.1 MB + 8.5 MB)
+NCU_TRAFFIC_BYTES = 547_600_000
 WORKLOAD = "C2: paged_attention_v2 Llama-3-8B shape 32q/8kv d128, fp8_e4m3 KV, block 16, batch 64 x ctx 4096"
 
 
@@ -192,6 +195,77 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+
+def gemm_extras(torch, A, dev, iters=30):
+    """W4A16 GEMM on the C3 shapes (Llama-3.1-8B, g128, bf16): us/call under a CUDA graph with weights rotated through
+    > 256 MB of distinct buffers, HBM GB/s on the algorithmic bytes and TFLOP/s. Secondary numbers of BASELINE's metric."""
+    UINT4B8 = 1125899907892224
+    shapes = {"qkv": (4096, 6144), "o": (4096, 4096), "gate_up": (4096, 28672), "down": (14336, 4096)}
+    res = {}
+    gen = torch.Generator(device=dev).manual_seed(0)
+    e = torch.empty(0, dtype=torch.int32, device=dev)
+    for name, (K, N) in shapes.items():
+        nbuf = max(2, int(300e6 // (K * N // 2)) + 1)
+        bs = [torch.randint(-2**31, 2**31 - 1, (K // 16, N * 2), dtype=torch.int32, device=dev, generator=gen) for _ in range(nbuf)]
+        ss = [(torch.rand(K // 128, N, device=dev, generator=gen) * 0.01 + 0.005).to(torch.bfloat16) for _ in range(nbuf)]
+        ws = torch.zeros(N // 64 * 16, dtype=torch.int32, device=dev)
+        for M in (1, 16, 64, 256, 1024):
+            a = torch.randn(M, K, device=dev, generator=gen).to(torch.bfloat16)
+            f = lambda i: A.ops.gptq_marlin_gemm(a, bs[i % nbuf], ss[i % nbuf], e, e, e, ws, UINT4B8, M, N, K, True)
+            for i in range(3):
+                f(i)
+            st = torch.cuda.Stream()
+            st.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(st):
+                gph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gph, stream=st):
+                    for i in range(iters):
+                        f(i)
+                gph.replay()
+                st.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(st)
+                gph.replay()
+                e1.record(st)
+                st.synchronize()
+            us = e0.elapsed_time(e1) / iters * 1e3
+            byt = K * N // 2 + (K // 128) * N * 2 + M * K * 2 + M * N * 2
+            res[f"{name}_m{M}"] = {"us": round(us, 2), "GBps": round(byt / us / 1e3, 1), "TFLOPs": round(2 * M * N * K / us / 1e6, 1)}
+        del bs, ss
+    return res
+
+
+def decode_extras(torch, A, dev, world, steps=10):
+    """Decode tok/s of a Llama-shaped layer stack over the three kernels (+ NCCL all_reduce when world > 1), one CUDA
+    graph per step. 1 GPU: Llama-3.1-8B shapes (C3); N GPUs: Llama-3.1-70B shapes at TP = N (C4). Glue that is not on
+    the hot path (RMSNorm, RoPE) is left out, see aphrodite-fork_b200/decode.py."""
+    from aphrodite_fork_b200.decode import DecodeConfig, DecodeModel
+    from aphrodite_fork_b200.tp import TPGroup
+    cfg = DecodeConfig.llama3_8b() if world == 1 else DecodeConfig.llama3_70b()
+    model = DecodeModel(cfg, batch=BATCH, ctx=CTX, tp=TPGroup(), device=dev, seed=0)
+    model.capture()
+    for _ in range(3):
+        model.step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        model.step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return {"model": ("llama-3.1-8b" if world == 1 else "llama-3.1-70b") + f" shapes, {cfg.num_layers} layers, W4A16 g128, fp8 KV",
+            "tp": world, "batch": BATCH, "ctx": CTX, "ms_per_step": round(ms, 3), "tok_per_s": round(BATCH / (ms * 1e-3), 1),
+            "kernel_launches_per_step": model.launches_per_step(),
+            "hbm_bytes_per_step_per_gpu": model.kv_bytes_per_step() + model.weight_bytes(),
+            "hbm_GBps_per_gpu": round((model.kv_bytes_per_step() + model.weight_bytes()) / (ms * 1e-3) / 1e9, 1)}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -305,6 +379,20 @@ def run_ours(args):
         ems = float(t.item())
     e2e_val = per_step_bytes * steps * world / (ems * 1e-3) / 1e9
 
+    # ---- secondary numbers of BASELINE's metric: W4A16 GEMM TFLOP/s (rank 0) and decode tok/s (all ranks) ----
+    extras = {}
+    if not args.no_extras:
+        del pools
+        torch.cuda.empty_cache()
+        try:
+            if rank == 0:
+                extras["gemm_w4a16"] = gemm_extras(torch, A, dev)
+            barrier()
+            torch.cuda.empty_cache()
+            extras["decode"] = decode_extras(torch, A, dev, world)
+        except Exception as ex:  # the headline line must still be printed
+            extras["error"] = f"{type(ex).__name__}: {ex}"[:300]
+
     if rank == 0:
         peak, peak_src = peaks()
         line = {
@@ -316,7 +404,7 @@ def run_ours(args):
                              "blocks: inputs larger than the 126 MB L2",
                        "kv_bytes_per_step": per_step_bytes},
             "roofline": {"bound": "hbm", "achieved": round(per_gpu, 2), "peak": peak, "unit": "GB/s",
-                         "frac": round(per_gpu / peak, 4), "traffic": None,
+                         "frac": round(per_gpu / peak, 4), "traffic": NCU_TRAFFIC_BYTES,
                          "note": f"algorithmic KV bytes / CUDA-event time of the whole op (split-K kernel + reduce) per launch; "
                                  f"peak = {peak_src}"},
             "e2e": {"value": round(e2e_val, 2), "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -325,6 +413,7 @@ def run_ours(args):
                            "block_tables/seq_lens -> device, output -> host)"},
             "gpu_launches": 2 * steps,
             "clocks": clocks,
+            "extras": extras,
         }
         if world == 1 and not args.no_cpu:
             gbs, cores, kind, sample, cms, n = cpu_reference_run(12.0, 4, CTX)
@@ -342,6 +431,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extras", action="store_true", help="skip the GEMM / decode-loop secondary measurements")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
