@@ -84,7 +84,9 @@ def _free_port():
 
 
 def _nccl_worker(rank, world, port, q):
+    import faulthandler
     import torch.distributed as dist
+    faulthandler.dump_traceback_later(150, exit=True)  # a hang must end with a stack trace, not with the suite's timeout
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -101,7 +103,12 @@ def _nccl_worker(rank, world, port, q):
         same = bool(torch.equal(out, ref))
         model.capture()
         g = model.step().float()
-        q.put((rank, same, bool(torch.isfinite(out).all()), bool(torch.allclose(g, out, rtol=2e-2, atol=1e-3))))
+        res = (rank, same, bool(torch.isfinite(out).all()), bool(torch.allclose(g, out, rtol=2e-2, atol=1e-3)))
+        # the captured graph holds the communicator: drop it before the group is torn down
+        model.graph = None
+        del model
+        torch.cuda.synchronize()
+        q.put(res)
     finally:
         dist.destroy_process_group()
 
@@ -115,8 +122,8 @@ def test_tensor_parallel_decode_step_over_nccl():
     procs = [ctx.Process(target=_nccl_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
+    got = sorted(q.get(timeout=200) for _ in range(2))  # drain the queue before joining
     for p in procs:
-        p.join(timeout=300)
+        p.join(timeout=60)
         assert p.exitcode == 0
-    got = sorted(q.get(timeout=10) for _ in range(2))
     assert got == [(0, True, True, True), (1, True, True, True)]
