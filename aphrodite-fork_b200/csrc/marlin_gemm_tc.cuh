@@ -152,7 +152,9 @@ __global__ void __launch_bounds__(THREADS, 1)
   extern __shared__ uint8_t smem_raw[];
 
   const int tid = threadIdx.x, lane = tid & 31;
+#ifdef APH_GEMM_TRACE
   if (p.trace != nullptr && blockIdx.x == 0 && tid == 0) p.trace[512 + 48 + 3] = clock64();
+#endif
   // the warp index through a shuffle: ptxas then knows the role branches below are warp-uniform
   const int w = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const bool grouped = p.group_size < p.K;
@@ -257,7 +259,9 @@ __global__ void __launch_bounds__(THREADS, 1)
     for (int i = 0; i < n; ++i) merge_tile(s_pend[1 + i], mtid);
   };
 
+#ifdef APH_GEMM_TRACE
   if (p.trace != nullptr && blockIdx.x == 0 && tid == 0) p.trace[512 + 48 + 2] = clock64();
+#endif
   if (w == W_PROD) {
     // ==================== weight producer: packed weights, scales, zero points ====================
     if (lane != 0) return;
@@ -330,11 +334,15 @@ __global__ void __launch_bounds__(THREADS, 1)
         for (int ks = k0; ks < k1; ++ks, ++it) {
           if (NI > 1 && (it % NI) != mi) continue;
           const int sa = it % SA;
+#ifdef APH_GEMM_TRACE
           const bool tr = p.trace != nullptr && blockIdx.x == 0 && it < 64 && lane == 0;
           if (tr) p.trace[it * 8 + 0] = clock64();
+#endif
           if (!ok) mbar_wait(ready_bar + sa * 8, (it / SA) & 1);  // activations landed and dequantised weights are in TMEM
           tc_fence_after();
+#ifdef APH_GEMM_TRACE
           if (tr) p.trace[it * 8 + 2] = clock64();
+#endif
           const uint32_t desc_lo = (((smem_base + C::ACT_OFF + sa * C::ACT_BYTES) >> 4) & 0x3fffu) | (1u << 16);
           const uint32_t a_tmem = tmem0 + C::A_COL0 + sa * 64;
           const int nx = it + NI;
@@ -342,7 +350,9 @@ __global__ void __launch_bounds__(THREADS, 1)
           tc_mma_ts_stage8(d_tmem, a_tmem, desc_lo, DESC_HI, C::IDESC, acc, (uint32_t)(C::ACT_BOX >> 4));
           acc = 1;
           tc_commit_elect(emptya_bar + sa * 8);  // slot (activations + TMEM weights) free once these MMAs retire
+#ifdef APH_GEMM_TRACE
           if (tr) p.trace[it * 8 + 3] = clock64();
+#endif
         }
         tc_commit_elect(done_bar + db * 8);
       }
@@ -410,14 +420,21 @@ __global__ void __launch_bounds__(THREADS, 1)
       for (int ks = k0; ks < k1; ++ks, ++it) {
         if ((it & 1) != grp) continue;
         const int sw = it % SW, sa = it % SA;
+#ifdef APH_GEMM_TRACE
         const bool tr = p.trace != nullptr && blockIdx.x == 0 && it < 64 && (dw & 7) == 0 && lane == 0;
         if (tr) p.trace[it * 8 + 4] = clock64();
+#endif
         mbar_wait(fullw_bar + sw * 8, (it / SW) & 1);
+#ifdef APH_GEMM_TRACE
         if (tr) p.trace[it * 8 + 5] = clock64();
+#endif
         const uint32_t wstage = smem_base + sw * W_STAGE;
         uint32_t q[4][2];
 #pragma unroll
         for (int i = 0; i < 4; ++i) lds64(wstage + offW + i * (NTILE * 8), q[i][0], q[i][1]);
+        // the previous stage's TMEM stores had the wait and the loads above to land: hand that slot to the MMA warps
+        // before starting on this stage's arithmetic (publishing later would keep one more slot per group in limbo)
+        if (pending >= 0) publish();
         uint32_t a[2][16];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -436,11 +453,14 @@ __global__ void __launch_bounds__(THREADS, 1)
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(emptyw_bar + sw * 8);  // this warp's words of the stage are in registers
-        if (pending >= 0) publish();                      // the previous stage's stores had the math above to land
+#ifdef APH_GEMM_TRACE
         if (tr) p.trace[it * 8 + 6] = clock64();
+#endif
         mbar_wait(emptya_bar + sa * 8, ((it / SA) & 1) ^ 1);  // the MMAs that read this TMEM slot have retired
         tc_fence_after();
+#ifdef APH_GEMM_TRACE
         if (tr) p.trace[it * 8 + 7] = clock64();
+#endif
         const uint32_t a_tmem = tmem_base + a_lane + C::A_COL0 + sa * 64 + (4 * h) * 8;
         tmem_st_16x128b_x8(a_tmem, a[0]);
         tmem_st_16x128b_x8(a_tmem + (16u << 16), a[1]);
@@ -483,11 +503,17 @@ __global__ void __launch_bounds__(THREADS, 1)
       scalar_t* crow = reinterpret_cast<scalar_t*>(p.c) + (int64_t)mt * MB * p.N + (int64_t)slice * NTILE;
       float* mine = p.scratch + ((size_t)b * 2 + (segj == 0 ? 0 : 1)) * (size_t)(MB * NTILE) + n_local;
 
+#ifdef APH_GEMM_TRACE
       const bool etr = p.trace != nullptr && b == 0 && etid == 0 && seg < 6;
+#endif
+#ifdef APH_GEMM_TRACE
       if (etr) p.trace[512 + seg * 8 + 0] = clock64();
+#endif
       mbar_wait(done_bar + db * 8, (seg / NDBUF) & 1);
       tc_fence_after();
+#ifdef APH_GEMM_TRACE
       if (etr) p.trace[512 + seg * 8 + 1] = clock64();
+#endif
       const uint32_t d0 = tmem_base + d_lane + (db * C::NI + (two ? 0 : lone)) * MB;
       const uint32_t d1 = tmem_base + d_lane + (db * C::NI + 1) * MB;
 #pragma unroll 1
@@ -537,7 +563,9 @@ __global__ void __launch_bounds__(THREADS, 1)
           }
         }
       }
+#ifdef APH_GEMM_TRACE
       if (etr) p.trace[512 + seg * 8 + 2] = clock64();
+#endif
       if (direct) continue;
 
       // ---- the tile's k range is shared with other CTAs: whoever arrives last merges the partials (at the end) ----
@@ -550,16 +578,22 @@ __global__ void __launch_bounds__(THREADS, 1)
       named_bar_sync(1, ET);
       if (*s_last) pend[npend++] = tile;
       named_bar_sync(1, ET);  // s_last may be rewritten by the next segment
+#ifdef APH_GEMM_TRACE
       if (etr) p.trace[512 + seg * 8 + 3] = clock64();
+#endif
     }
     if (etid == 0) {
       s_pend[0] = npend;
       s_pend[1] = pend[0];
       s_pend[2] = pend[1];
     }
+#ifdef APH_GEMM_TRACE
     if (p.trace != nullptr && b == 0 && etid == 0) p.trace[512 + 48 + 0] = clock64();
+#endif
     merge_phase(etid);
+#ifdef APH_GEMM_TRACE
     if (p.trace != nullptr && b == 0 && etid == 0) p.trace[512 + 48 + 1] = clock64();
+#endif
     tc_fence_before();
     named_bar_arrive(2, (EPI_WARPS + 1) * 32);
   }
