@@ -123,3 +123,22 @@ def refcpu():
         torch.ops.load_library(path)
         _refcpu = torch.ops._refcpu
     return _refcpu
+
+
+_refcuda = None
+
+
+def refcuda():
+    """torch.ops._refcuda = the UNMODIFIED reference CUDA kernels (oracle/_ref/refcuda.so, built by
+    `make -C oracle refcuda` from the sources under /root/reference), or None when not built or
+    when there is no GPU. Same-hardware parity target and "kernel to beat"; checker only."""
+    global _refcuda
+    if _refcuda is None:
+        path = os.path.join(_HERE, "_ref", "refcuda.so")
+        if not os.path.exists(path):  # attention + cache only (linked before gptq_marlin.cu finished compiling)
+            path = os.path.join(_HERE, "_ref", "refcuda_partial.so")
+        if not os.path.exists(path) or not torch.cuda.is_available():
+            return None
+        torch.ops.load_library(path)
+        _refcuda = torch.ops._refcuda
+    return _refcuda

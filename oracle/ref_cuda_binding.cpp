@@ -1,0 +1,93 @@
+// TEST INFRASTRUCTURE ONLY (oracle). Never imported by the product path.
+//
+// Trimmed binding that exposes the UNMODIFIED reference CUDA kernels of the hot path
+//   /root/reference/kernels/attention/paged_attention_v1.cu  (:170-192)
+//   /root/reference/kernels/attention/paged_attention_v2.cu  (:176-201)
+//   /root/reference/kernels/cache_kernels.cu                 (reshape_and_cache :369-395 and the
+//                                                             other cache ops of that file)
+//   /root/reference/kernels/quantization/gptq_marlin/gptq_marlin.cu        (:2263-2474)
+//   /root/reference/kernels/quantization/gptq_marlin/gptq_marlin_repack.cu
+//   /root/reference/kernels/quantization/gptq_marlin/awq_marlin_repack.cu
+// under the private dispatcher namespace `_refcuda`, with the schema strings of
+// kernels/torch_bindings.cpp:41-65,326-347,680-734. The Marlin translation units register their
+// own CUDA impls into TORCH_EXTENSION_NAME (= _refcuda, set by oracle/Makefile). The sources are
+// compiled where they lie (oracle/Makefile, target `refcuda`, nvcc for sm_100a); nothing is copied
+// into this repository. It is the same-hardware parity target and "kernel to beat" on the GPU box.
+#include <torch/all.h>
+#include <torch/library.h>
+#include <optional>
+#include <string>
+#include <vector>
+
+#define ATTN_TAIL                                                                                  \
+  torch::Tensor &query, torch::Tensor &key_cache, torch::Tensor &value_cache, int64_t num_kv_heads, \
+      double scale, torch::Tensor &block_tables, torch::Tensor &seq_lens, int64_t block_size,      \
+      int64_t max_seq_len, const std::optional<torch::Tensor> &alibi_slopes,                       \
+      const std::string &kv_cache_dtype, torch::Tensor &k_scale, torch::Tensor &v_scale,           \
+      const int64_t tp_rank, const int64_t blocksparse_local_blocks,                               \
+      const int64_t blocksparse_vert_stride, const int64_t blocksparse_block_size,                 \
+      const int64_t blocksparse_head_sliding_step
+
+void paged_attention_v1(torch::Tensor& out, ATTN_TAIL);
+void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tensor& max_logits,
+                        torch::Tensor& tmp_out, ATTN_TAIL);
+void swap_blocks(torch::Tensor& src, torch::Tensor& dst, const torch::Tensor& block_mapping);
+void copy_blocks(std::vector<torch::Tensor> const& key_caches, std::vector<torch::Tensor> const& value_caches,
+                 const torch::Tensor& block_mapping);
+void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache,
+                       torch::Tensor& value_cache, torch::Tensor& slot_mapping,
+                       const std::string& kv_cache_dtype, torch::Tensor& k_scale, torch::Tensor& v_scale);
+void reshape_and_cache_flash(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache,
+                             torch::Tensor& value_cache, torch::Tensor& slot_mapping,
+                             const std::string& kv_cache_dtype, torch::Tensor& k_scale,
+                             torch::Tensor& v_scale);
+void concat_and_cache_mla(torch::Tensor& kv_c, torch::Tensor& k_pe, torch::Tensor& kv_cache,
+                          torch::Tensor& slot_mapping, const std::string& kv_cache_dtype,
+                          torch::Tensor& scale);
+void convert_fp8(torch::Tensor& dst_cache, torch::Tensor& src_cache, const double scale,
+                 const std::string& kv_cache_dtype);
+void gather_cache(torch::Tensor const& src_cache, torch::Tensor const& dst, torch::Tensor const& block_table,
+                  torch::Tensor const& cu_seq_lens, int64_t batch_size, std::optional<torch::Tensor> seq_starts);
+
+#define ATTN_SCHEMA_TAIL                                                                            \
+  "Tensor query, Tensor key_cache, Tensor value_cache, int num_kv_heads, float scale, "            \
+  "Tensor block_tables, Tensor seq_lens, int block_size, int max_seq_len, Tensor? alibi_slopes, "   \
+  "str kv_cache_dtype, Tensor k_scale, Tensor v_scale, int tp_rank, int blocksparse_local_blocks, " \
+  "int blocksparse_vert_stride, int blocksparse_block_size, int blocksparse_head_sliding_step) -> ()"
+
+TORCH_LIBRARY(_refcuda, ops) {
+  ops.def("paged_attention_v1(Tensor! out, " ATTN_SCHEMA_TAIL);
+  ops.impl("paged_attention_v1", torch::kCUDA, &paged_attention_v1);
+  ops.def("paged_attention_v2(Tensor! out, Tensor! exp_sums, Tensor! max_logits, Tensor! tmp_out, " ATTN_SCHEMA_TAIL);
+  ops.impl("paged_attention_v2", torch::kCUDA, &paged_attention_v2);
+  // impls registered by the Marlin translation units themselves
+  ops.def(
+      "gptq_marlin_gemm(Tensor a, Tensor b_q_weight, Tensor b_scales, Tensor b_zeros, Tensor g_idx, Tensor perm, "
+      "Tensor workspace, int b_q_type, SymInt size_m, SymInt size_n, SymInt size_k, bool is_k_full, bool has_zp, "
+      "bool use_atomic_add, bool use_fp32_reduce, bool is_zp_float) -> Tensor");
+  ops.def("gptq_marlin_repack(Tensor b_q_weight, Tensor perm, SymInt size_k, SymInt size_n, int num_bits) -> Tensor");
+  ops.def("awq_marlin_repack(Tensor b_q_weight, SymInt size_k, SymInt size_n, int num_bits) -> Tensor");
+  // cache ops (kernels/torch_bindings.cpp:680-734)
+  ops.def("swap_blocks(Tensor src, Tensor! dst, Tensor block_mapping) -> ()");
+  ops.impl("swap_blocks", torch::kCUDA, &swap_blocks);
+  ops.def("copy_blocks(Tensor(a!)[] key_caches, Tensor[](b!) value_caches, Tensor block_mapping) -> ()");
+  ops.impl("copy_blocks", torch::kCUDA, &copy_blocks);
+  ops.def(
+      "reshape_and_cache(Tensor key, Tensor value, Tensor! key_cache, Tensor! value_cache, Tensor slot_mapping, "
+      "str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()");
+  ops.impl("reshape_and_cache", torch::kCUDA, &reshape_and_cache);
+  ops.def(
+      "reshape_and_cache_flash(Tensor key, Tensor value, Tensor! key_cache, Tensor! value_cache, "
+      "Tensor slot_mapping, str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()");
+  ops.impl("reshape_and_cache_flash", torch::kCUDA, &reshape_and_cache_flash);
+  ops.def(
+      "concat_and_cache_mla(Tensor kv_c, Tensor k_pe, Tensor! kv_cache, Tensor slot_mapping, str kv_cache_dtype, "
+      "Tensor scale) -> ()");
+  ops.impl("concat_and_cache_mla", torch::kCUDA, &concat_and_cache_mla);
+  ops.def("convert_fp8(Tensor! dst_cache, Tensor src_cache, float scale, str kv_cache_dtype) -> ()");
+  ops.impl("convert_fp8", torch::kCUDA, &convert_fp8);
+  ops.def(
+      "gather_cache(Tensor src_cache, Tensor! dst, Tensor block_table, Tensor cu_seq_lens, int batch_size, "
+      "Tensor? seq_starts) -> ()");
+  ops.impl("gather_cache", torch::kCUDA, &gather_cache);
+}
