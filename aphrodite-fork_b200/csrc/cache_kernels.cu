@@ -2,9 +2,10 @@
 // Replaces /root/reference/kernels/cache_kernels.cu:210-262,369-395 (reshape_and_cache) and
 // :499-577 (convert_fp8). Results are bit-exact with the reference (same index arithmetic,
 // same __nv_cvt_float_to_fp8(x / scale, SATFINITE) codec); the design is different: the
-// K side moves whole x-element chunks (one 16-byte store per chunk, 128-bit loads), the
-// V side reads 128-bit vectors and scatters, and one CTA handles a slice of a token so that
-// decode-sized batches still spread over the SMs.
+// K side moves 128-bit input vectors into the x-chunks of the cache with one vector store each; the V
+// side writes groups of 8 tokens that fill consecutive slots of a block (prefill) transposed, as one
+// 8/16-byte store per cache row, and scatters lane-consecutive elements otherwise (decode); a group of
+// 8 tokens is sliced over several CTAs so that decode-sized batches still spread over the SMs.
 #include "common.cuh"
 
 namespace aphb200 {
@@ -51,68 +52,117 @@ __global__ void reshape_and_cache_generic_kernel(const scalar_t* __restrict__ ke
   }
 }
 
-// Vectorised path. X = elements per K chunk (16 / sizeof(cache_t)); requires 16-byte aligned
-// key/value rows. Work item = one K chunk (X elements -> one 16-byte store) and, for V, one
-// 16-byte input vector scattered element-wise (the layout puts one element per token in every
-// block_size-strided row, so the V store cannot be widened).
+// Vectorised path. One CTA serves (a slice of) a group of TG = 8 consecutive tokens; requires 16-byte aligned
+// key / value rows and cache blocks.
+//   K side: one work item per 128-bit input vector (LV elements); its LV converted elements are contiguous inside
+//           one x-chunk of the cache ([D/x][bs][x]), so they leave as one 16 / 8 / 4-byte store.
+//   V side: the layout [D][bs] gives a token ONE element in every bs-strided row, so a lone token can only scatter
+//           elements. Lanes take consecutive elements (a warp store then covers one contiguous 32*bs*sizeof span,
+//           the fewest cache lines this layout allows). When the TG tokens of the group occupy TG consecutive,
+//           TG-aligned slots of one block (every prefill chunk does) the group is written transposed instead: one
+//           thread gathers the TG tokens' values of one row and stores them as ONE 8- or 16-byte vector - 8x fewer
+//           store transactions than per-element scatter.
+constexpr int TG = 8;
+
 template <typename scalar_t, typename cache_t, int KV>
 __global__ void __launch_bounds__(256)
     reshape_and_cache_vec_kernel(const scalar_t* __restrict__ key, const scalar_t* __restrict__ value,
                                  cache_t* __restrict__ key_cache, cache_t* __restrict__ value_cache,
-                                 const int64_t* __restrict__ slot_mapping, int64_t key_stride, int64_t value_stride,
-                                 int num_heads, int head_size, int block_size, int64_t block_stride,
+                                 const int64_t* __restrict__ slot_mapping, int64_t num_tokens, int64_t key_stride,
+                                 int64_t value_stride, int num_heads, int head_size, int block_size, int64_t block_stride,
                                  const float* __restrict__ k_scale, const float* __restrict__ v_scale) {
   constexpr int X = 16 / sizeof(cache_t);        // elements per K chunk
-  constexpr int LV = 16 / sizeof(scalar_t);      // elements per 128-bit input vector
+  constexpr int LV = 16 / sizeof(scalar_t);      // elements per 128-bit input vector (LV divides X)
   using InVec = Pack<scalar_t, LV>;
-  const int64_t token = blockIdx.x;
-  const int64_t slot = slot_mapping[token];
-  if (slot < 0) return;
-  const int64_t blk = slot / block_size, off = slot % block_size;
+  __shared__ int64_t s_slot[TG];
+  __shared__ int s_run;
+  const int64_t t0 = (int64_t)blockIdx.x * TG;
+  const int nt = (int)(num_tokens - t0 < TG ? num_tokens - t0 : TG);
+  if (threadIdx.x < TG) s_slot[threadIdx.x] = (int)threadIdx.x < nt ? slot_mapping[t0 + threadIdx.x] : -1;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    bool run = nt == TG && s_slot[0] >= 0 && s_slot[0] % TG == 0 && block_size % TG == 0;
+    for (int i = 1; i < TG; ++i) run = run && s_slot[i] == s_slot[0] + i;
+    s_run = run;
+  }
+  __syncthreads();
   const int n = num_heads * head_size;
   float ks = 1.f, vs = 1.f;
   if constexpr (KV != APH_KV_AUTO) {
     ks = *k_scale;
     vs = *v_scale;
   }
-  const scalar_t* krow = key + token * key_stride;
-  const scalar_t* vrow = value + token * value_stride;
-  cache_t* kc = key_cache + blk * block_stride;
-  cache_t* vc = value_cache + blk * block_stride;
   const int tid = blockIdx.y * blockDim.x + threadIdx.x;
   const int nthreads = gridDim.y * blockDim.x;
+  auto cvt = [](scalar_t v, float sc) -> cache_t {
+    if constexpr (KV == APH_KV_AUTO)
+      return v;
+    else
+      return fp8_encode<KV>(ScalarTraits<scalar_t>::to_float(v), sc);
+  };
 
-  // K: chunk ci covers elements [ci*X, ci*X+X) of the token row (head_size % X == 0).
-  const int chunks_per_head = head_size / X;
-  for (int ci = tid; ci < n / X; ci += nthreads) {
-    const int h = ci / chunks_per_head, c = ci % chunks_per_head;
-    Pack<cache_t, X> o;
+  // ---- K: (token j, input vector ci) -> LV contiguous cache elements; two independent loads in flight
+  const int vecs = n / LV;
+  for (int w0 = tid; w0 < nt * vecs; w0 += 2 * nthreads) {
+    InVec in[2];
+    cache_t* dst[2] = {nullptr, nullptr};
 #pragma unroll
-    for (int j = 0; j < X / LV; ++j) {
-      const InVec in = *reinterpret_cast<const InVec*>(krow + ci * X + j * LV);
-#pragma unroll
-      for (int e = 0; e < LV; ++e) {
-        if constexpr (KV == APH_KV_AUTO)
-          o.v[j * LV + e] = in.v[e];
-        else
-          o.v[j * LV + e] = fp8_encode<KV>(ScalarTraits<scalar_t>::to_float(in.v[e]), ks);
-      }
+    for (int u = 0; u < 2; ++u) {
+      const int w = w0 + u * nthreads;
+      if (w >= nt * vecs) continue;
+      const int j = w / vecs, ci = w - j * vecs;
+      const int64_t slot = s_slot[j];
+      if (slot < 0) continue;
+      const int64_t blk = slot / block_size, off = slot % block_size;
+      in[u] = *reinterpret_cast<const InVec*>(key + (t0 + j) * key_stride + ci * LV);
+      const int i0 = ci * LV;
+      const int h = i0 / head_size, e0 = i0 % head_size;
+      dst[u] = key_cache + blk * block_stride + (int64_t)h * head_size * block_size + (int64_t)(e0 / X) * block_size * X +
+               off * X + e0 % X;
     }
-    cache_t* dst = kc + (int64_t)h * head_size * block_size + (int64_t)c * block_size * X + off * X;
-    *reinterpret_cast<Pack<cache_t, X>*>(dst) = o;
-  }
-  // V: 128-bit loads, element scatter.
-  for (int vi = tid; vi < n / LV; vi += nthreads) {
-    const InVec in = *reinterpret_cast<const InVec*>(vrow + vi * LV);
-    const int i0 = vi * LV;
-    const int h = i0 / head_size, e0 = i0 % head_size;  // LV divides head_size
-    cache_t* dst = vc + (int64_t)h * head_size * block_size + (int64_t)e0 * block_size + off;
 #pragma unroll
-    for (int e = 0; e < LV; ++e) {
-      if constexpr (KV == APH_KV_AUTO)
-        dst[(int64_t)e * block_size] = in.v[e];
-      else
-        dst[(int64_t)e * block_size] = fp8_encode<KV>(ScalarTraits<scalar_t>::to_float(in.v[e]), vs);
+    for (int u = 0; u < 2; ++u) {
+      if (dst[u] == nullptr) continue;
+      Pack<cache_t, LV> o;
+#pragma unroll
+      for (int e = 0; e < LV; ++e) o.v[e] = cvt(in[u].v[e], ks);
+      *reinterpret_cast<Pack<cache_t, LV>*>(dst[u]) = o;
+    }
+  }
+
+  // ---- V
+  if (s_run) {
+    const int64_t blk = s_slot[0] / block_size, off = s_slot[0] % block_size;
+    cache_t* vc = value_cache + blk * block_stride + off;
+    const scalar_t* vrow = value + t0 * value_stride;
+    for (int i = tid; i < n; i += nthreads) {
+      Pack<cache_t, TG> o;
+#pragma unroll
+      for (int j = 0; j < TG; ++j) o.v[j] = cvt(vrow[(int64_t)j * value_stride + i], vs);
+      *reinterpret_cast<Pack<cache_t, TG>*>(vc + (int64_t)i * block_size) = o;
+    }
+  } else {
+    // four independent loads in flight per thread before the dependent stores
+    const int total = nt * n;
+    for (int w0 = tid; w0 < total; w0 += 4 * nthreads) {
+      scalar_t v[4];
+      int64_t dst[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int w = w0 + u * nthreads;
+        dst[u] = -1;
+        if (w < total) {
+          const int j = w / n, i = w - j * n;
+          const int64_t slot = s_slot[j];
+          if (slot >= 0) {
+            dst[u] = (slot / block_size) * block_stride + (int64_t)i * block_size + slot % block_size;
+            v[u] = value[(t0 + j) * value_stride + i];
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (dst[u] >= 0) value_cache[dst[u]] = cvt(v[u], vs);
     }
   }
 }
@@ -125,20 +175,21 @@ int launch_reshape_and_cache(const void* key, const void* value, void* key_cache
   constexpr int X = 16 / sizeof(cache_t);
   constexpr int LV = 16 / sizeof(scalar_t);
   const int n = num_heads * head_size;
-  const bool vec_ok = x == X && head_size % X == 0 && head_size % LV == 0 && aligned16(key) && aligned16(value) &&
-                      aligned16(key_cache) && key_stride % LV == 0 && value_stride % LV == 0 &&
+  const bool vec_ok = x == X && X % LV == 0 && head_size % X == 0 && aligned16(key) && aligned16(value) &&
+                      aligned16(key_cache) && aligned16(value_cache) && key_stride % LV == 0 && value_stride % LV == 0 &&
                       (block_stride * (int64_t)sizeof(cache_t)) % 16 == 0;
   if (vec_ok) {
-    const int items = n / LV;  // V vectors dominate the item count
-    int threads = 256;
-    // spread one token over several CTAs when the batch is small (decode): aim for >= 2 waves
+    const int64_t groups = (num_tokens + TG - 1) / TG;
+    const int threads = 256;
+    // few tokens (decode): slice each group over several CTAs until the grid covers the SMs about twice
     int ysplit = 1;
     const int sms = sm_count();
-    while (ysplit * 2 * threads <= items && num_tokens * ysplit < 2LL * sms) ysplit *= 2;
-    while (threads > 32 && threads / 2 >= items) threads /= 2;
-    dim3 grid((unsigned)num_tokens, ysplit);
+    while (groups * ysplit < 2LL * sms && (int64_t)ysplit * threads < (int64_t)TG * n) ysplit *= 2;
+    // many tokens: at most 8 scattered elements per thread (memory-level parallelism comes from resident warps)
+    while ((int64_t)ysplit * threads * 8 < (int64_t)TG * n && ysplit < 64) ysplit *= 2;
+    dim3 grid((unsigned)groups, ysplit);
     reshape_and_cache_vec_kernel<scalar_t, cache_t, KV><<<grid, threads, 0, stream>>>(
-        (const scalar_t*)key, (const scalar_t*)value, (cache_t*)key_cache, (cache_t*)value_cache, slot_mapping,
+        (const scalar_t*)key, (const scalar_t*)value, (cache_t*)key_cache, (cache_t*)value_cache, slot_mapping, num_tokens,
         key_stride, value_stride, num_heads, head_size, block_size, block_stride, k_scale, v_scale);
   } else {
     dim3 grid((unsigned)num_tokens, 1);

@@ -14,15 +14,17 @@
 //     per group:  acc += s[g,n] * (sum_k a_k (OFF + q_kn) - (OFF + zp[g,n]) * sum_k a_k), with
 //     sum_k a_k produced by one extra MMA against an all-ones tile. 7 ALU ops per 8 weights
 //     instead of the reference's 15;
-//   * one CTA per (output slice of 64/128/256 columns, k chunk); K is split only as far as needed to
-//     put a CTA on every SM, partial tiles meet in an fp32 scratch with a deterministic "last arriver
-//     reduces" fix-up (no spin locks; the caller's lock buffer is the per-slice arrival counter and is
-//     left all-zero);
-//   * a dedicated producer warp streams weights, activations, scales and zero points with 1-D
-//     bulk async copies (TMA engine, SASS UBLKCP) into a 4-6 stage ring, full/empty mbarriers,
-//     no CTA-wide barrier in the main loop; each consumer warp owns 64 output columns and whole
-//     128-row stages (warps of narrower slices take alternate stages), so the per-group flush is
-//     amortised over 8 k16 steps.
+//   * stream-K: the slice-major list of (output slice of 64/128/256 columns, 16 KiB weight stage) items is cut
+//     into one equal contiguous range per co-resident CTA slot (2 per SM), so every SM streams the same number
+//     of bytes whatever the shape (224 slices on 296 slots left 72 SMs half idle before); a slice shared by
+//     neighbouring CTAs meets in an fp32 scratch with a deterministic "last arriver sums in CTA order" fix-up
+//     (no spin locks; the caller's lock buffer is the per-slice arrival counter and is left all-zero);
+//   * a dedicated producer thread streams weights, activations, scales and zero points with 2-D tiled TMA loads
+//     (SASS UTMALDG) into a ring of stages, full/empty mbarriers, no CTA-wide barrier in the main loop; each
+//     consumer warp owns 64 output columns and whole 128-row stages (two warp groups take alternate stages), so
+//     the per-group flush is amortised over 8 k16 steps;
+//   * programmatic dependent launch: the kernel triggers its dependents at once and the next GEMM of the stream
+//     fills its ring with weights while this one drains; activations / outputs are touched after griddepcontrol.wait.
 // Large batches (M >= 64) are meant for the tcgen05 path; here they run as chunks of 32 rows.
 #include <cstdio>
 #include <cstdlib>
@@ -36,37 +38,64 @@ namespace aphb200 {
 namespace mg {
 
 struct Plan {
-  int nt, split, stages_per_chunk, grid, k_stages, n_slices;
+  int nt, grid, k_stages, n_slices, total;
 };
 
-// Decomposition: output slices of NT columns x `split` equal k chunks, one CTA each. Prefer no
-// split (no partial traffic, no fix-up); split K only as far as needed to put a CTA on every SM.
+// Decomposition. The output is cut into slices of NT columns and K into stages of 16 KiB of packed weights (so the
+// number of (slice, stage) items, N*K/32768, does not depend on NT); the kernel gives CTA i the i-th of `grid` equal
+// contiguous ranges of the slice-major item list. Two families of plans come out of that one kernel:
+//   aligned   grid = n_slices * split with split | k_stages: every range is one chunk of one slice (plain split-K,
+//             no fix-up at all when split = 1);
+//   stream-K  grid = all co-resident CTA slots: perfectly even bytes per SM, but ranges straddle slices (two
+//             fix-ups per CTA, segment turn-arounds).
+// make_plan scores every candidate with a small cost model calibrated on B200 (tools/sweep_gemm_plan.py,
+// profiles/r01_gemm_plan_sweep.jsonl): a CTA retires one 16 KiB stage per ~0.75 us whether or not it shares its SM
+// (it is bound by its own warps' latency, not by the SM), so t = 0.75 us x (stages of the longest CTA) + 2.0 us if
+// slices are shared + 1.8 us if ranges are unaligned (0.75 / 1.8 become 1.3 / 6.0 at 9..16 rows, where every
+// segment turn-around moves twice the accumulators); the cheapest candidate wins. APH_GEMM_NT / APH_GEMM_GRID force a plan (development).
 static Plan make_plan(int64_t N, int64_t K, int nb) {
-  const int sms = sm_count();
-  const int nts[3] = {256, 128, 64};
+  const int slots = sm_count() * (nb <= 2 ? 2 : 1);
+  const char* e_nt = getenv("APH_GEMM_NT");
+  const char* e_grid = getenv("APH_GEMM_GRID");
+  const int forced_nt = e_nt ? atoi(e_nt) : 0;
+  const int forced_grid = e_grid ? atoi(e_grid) : 0;
   Plan best{};
-  bool found = false;
-  for (int split = 1; split <= 8 && !found; ++split) {
-    for (int i = 0; i < 3; ++i) {
-      const int nt = nts[i];
-      if (N % nt != 0) continue;
-      const int ks = KT * (CONSUMERS / (nt / 64));
-      const int k_stages = (int)((K + ks - 1) / ks);
-      if (split > k_stages) continue;
-      const int64_t ctas = (N / nt) * split;
-      best = Plan{nt, split, (k_stages + split - 1) / split, (int)ctas, k_stages, (int)(N / nt)};
-      if (ctas >= (int64_t)sms * 9 / 10) {
-        found = true;
-        break;
+  double best_cost = 1e30;
+  const int nts[3] = {256, 128, 64};
+  for (int i = 0; i < 3; ++i) {
+    const int nt = nts[i];
+    if (N % nt != 0) continue;
+    if (forced_nt != 0 && forced_nt != nt && N % forced_nt == 0) continue;
+    const int ks = KT * (CONSUMERS / (nt / 64));
+    Plan pl{};
+    pl.nt = nt;
+    pl.k_stages = (int)((K + ks - 1) / ks);
+    pl.n_slices = (int)(N / nt);
+    pl.total = pl.n_slices * pl.k_stages;
+    // wider slices move fewer activation bytes per weight byte (good at M <= 8); at M = 9..16 their larger
+    // reduction tile costs pipeline stages instead
+    const double width_bias = (nb == 1 ? -0.1 : 0.3) * (nt == 256 ? 2 : nt == 128 ? 1 : 0);
+    auto consider = [&](int grid, bool aligned) {
+      if (grid < 1 || grid > pl.total) return;
+      const int per_cta = (pl.total + grid - 1) / grid;
+      const bool shared = !(aligned && grid == pl.n_slices);
+      const double t_stage = nb == 1 ? 0.75 : nb == 2 ? 1.3 : 2.2;
+      const double cost = t_stage * per_cta + (shared ? 2.0 : 0.0) + (aligned ? 0.0 : (nb == 1 ? 1.8 : 6.0)) + width_bias;
+      if (cost < best_cost) {
+        best_cost = cost;
+        best = pl;
+        best.grid = grid;
       }
-    }
+    };
+    for (int split = 1; split <= 8; ++split)
+      if (pl.k_stages % split == 0 && (int64_t)pl.n_slices * split <= slots) consider(pl.n_slices * split, true);
+    consider(pl.total < slots ? pl.total : slots, false);
   }
-  // stages_per_chunk may leave the last chunk empty when split does not divide k_stages: shrink split
-  while (best.split > 1 && (best.split - 1) * best.stages_per_chunk >= best.k_stages) --best.split;
-  best.grid = best.n_slices * best.split;
-  (void)nb;
+  if (forced_grid > 0) best.grid = forced_grid < best.total ? forced_grid : best.total;
   return best;
 }
+
+static size_t plan_scratch_bytes(const Plan& pl, int nb) { return (size_t)pl.grid * 2 * (8 * nb) * pl.nt * sizeof(float); }
 
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -110,6 +139,17 @@ struct Operands {
   bool f16;
 };
 
+// Programmatic dependent launch (APH_PDL=0 turns it off): a kernel of this library may start while the previous
+// kernel of the stream drains; it prefetches weights and waits (griddepcontrol.wait) before touching anything an
+// earlier kernel wrote. Works eagerly and under stream capture (the graph keeps the programmatic edge).
+static bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("APH_PDL");
+    return e == nullptr || e[0] != '0';
+  }();
+  return on;
+}
+
 template <typename scalar_t, int NB, int NT, bool HAS_ZP>
 static int launch(const Params& p, const Operands& op, int grid, cudaStream_t stream) {
   using C = Cfg<scalar_t, NB, NT>;
@@ -147,8 +187,18 @@ static int launch(const Params& p, const Operands& op, int grid, cudaStream_t st
     tmS = tmB;  // never dereferenced
     tmZ = tmB;
   }
-  kern<<<grid, THREADS, C::SMEM_BYTES, stream>>>(p, tmB, tmA, tmS, tmZ);
-  APH_LAUNCH_CHECK();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(THREADS);
+  cfg.dynamicSmemBytes = C::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, p, tmB, tmA, tmS, tmZ);
+  APH_CHECK(le == cudaSuccess, APH_ERR_CUDA, "gptq_marlin_gemm: launch failed: %s", cudaGetErrorString(le));
   return APH_OK;
 }
 
@@ -174,10 +224,11 @@ static int run_typed(Params p, const Operands& op, bool has_zp, float* scratch, 
     p.m0 = (int)m0;
     p.m_rows = rows;
     p.k_stages = pl.k_stages;
-    p.split = pl.split;
-    p.stages_per_chunk = pl.stages_per_chunk;
-    const size_t need = pl.split > 1 ? (size_t)pl.n_slices * pl.split * (8 * nb) * pl.nt * sizeof(float) : 0;
-    APH_CHECK(need == 0 || (scratch != nullptr && scratch_bytes >= need), APH_ERR_WORKSPACE,
+    p.total = pl.total;
+    const size_t need = plan_scratch_bytes(pl, nb);
+    APH_CHECK(((int64_t)pl.total + pl.k_stages + 1) * pl.grid < (1LL << 31), APH_ERR_UNSUPPORTED,
+              "gptq_marlin_gemm: %d work items are beyond the 32-bit scheduling arithmetic", pl.total);
+    APH_CHECK(scratch != nullptr && scratch_bytes >= need, APH_ERR_WORKSPACE,
               "gptq_marlin_gemm: scratch of %zu bytes needed, %zu given", need, scratch_bytes);
     p.scratch = scratch;
     int st;
@@ -359,8 +410,9 @@ extern "C" size_t aph_gptq_marlin_gemm_scratch_bytes(int64_t size_m, int64_t siz
   if (size_m <= 0 || size_n <= 0 || size_k <= 0 || size_n % 64 != 0 || size_k % mg::KT != 0) return 0;
   size_t worst = 0;
   for (int nb = 1; nb <= 4; nb *= 2) {
-    const mg::Plan pl = mg::make_plan(size_n, size_k, nb);
-    const size_t need = pl.split > 1 ? (size_t)pl.n_slices * pl.split * (8 * nb) * pl.nt * sizeof(float) : 0;
+    // upper bound over the slice widths make_plan may pick: grid <= 2 SMs' worth of slots, NT <= 256
+    size_t need = (size_t)aphb200::sm_count() * (nb <= 2 ? 2 : 1) * 2 * (8 * nb) * 256 * sizeof(float);
+    if (getenv("APH_GEMM_GRID")) need *= 8;  // development sweeps may use several waves of CTAs
     if (need > worst) worst = need;
   }
   if (size_n % mgtc::NTILE == 0) {

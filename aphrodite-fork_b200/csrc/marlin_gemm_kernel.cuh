@@ -20,14 +20,13 @@ struct Params {
   const uint8_t* s;   // scales, bytes (channelwise path reads them directly)
   const uint8_t* zp;  // zero points, bytes (or null)
   void* c;
-  float* scratch;      // [n_slices][split][MP*NT] fp32 partials (split > 1 only)
+  float* scratch;      // [grid][2][MP*NT] fp32 partials: slot 0 = head of a CTA's item range, slot 1 = its tail
   int* counters;       // [n_slices] arrival counters, all-zero on entry and on exit
   int N, K;
   int m0, m_rows;      // this launch covers rows [m0, m0 + m_rows) of a / c
   int group_size;      // == K for channelwise
   int k_stages;        // ceil(K / (128 * KG)) pipeline stages over the whole K
-  int split;           // CTAs sharing one output slice (plain split-K over equal k chunks)
-  int stages_per_chunk;
+  int total;           // n_slices * k_stages work items (slice-major); CTA i owns [i*total/grid, (i+1)*total/grid)
   int dbg;             // development switch (APH_GEMM_DBG): 1 = skip the math, 2 = skip the loads
 };
 
@@ -52,12 +51,79 @@ struct Cfg {
   static constexpr int BUDGET = (224 * 1024) / CTAS_PER_SM - 2048 - RED_BYTES - 256;
   static constexpr int STAGES = BUDGET / STAGE_BYTES > 8 ? 8 : BUDGET / STAGE_BYTES;
   static_assert(STAGES >= 2, "pipeline too shallow");
-  static constexpr int BAR_BYTES = 2 * STAGES * 8 + 16;
+  static constexpr int BAR_BYTES = 2 * STAGES * 8 + 64;  // barriers + fix-up flags of the (at most two) shared slices
   static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + RED_BYTES + BAR_BYTES;
   static constexpr uint32_t MAGIC = F16 ? 0x64006400u : 0x43004300u;  // 1024 / 128 as packed pairs
   static constexpr float OFFSET = F16 ? 1024.f : 128.f;
   static constexpr uint32_t ONES = F16 ? 0x3c003c00u : 0x3f803f80u;
 };
+
+// The pieces ("segments") of output slices inside the item range [b, e) of one CTA, in PROCESSING order: the
+// pieces that share their slice with a neighbouring CTA first (at most two: the head and the tail of the range),
+// whole slices afterwards. The arrival on a shared slice is thus published early and the last arriver, who sums the
+// partials, finds them complete when it gets there at the end of its own whole slices: the fix-up round trip
+// (fence + atomic + reload) hides behind streaming instead of ending every CTA. f(slice, k0, cnt, whole).
+template <typename F>
+__device__ __forceinline__ void for_each_segment(int b, int e, int ks, F&& f) {
+  const int s_first = b / ks, s_last = (e - 1) / ks;
+#pragma unroll 1
+  for (int pass = 0; pass < 2; ++pass) {
+#pragma unroll 1
+    for (int sl = s_first; sl <= s_last; ++sl) {
+      const int sb = max(b, sl * ks), se = min(e, (sl + 1) * ks);
+      const bool whole = (se - sb) == ks;
+      if (whole == (pass == 1)) f(sl, sb - sl * ks, se - sb, whole);
+    }
+  }
+}
+
+// Deferred fix-up of the (at most two) shared slices of a CTA, run by all consumer threads after their last segment.
+// Kept out of line so that its registers do not count against the main loop's budget (96 per thread at two CTAs of
+// nine warps per SM).
+template <typename scalar_t, int MP, int NT, int CT>
+__device__ __noinline__ void sum_shared_slices(scalar_t* c, const float* scratch, int* counters, int N, int m_rows, int k_stages,
+                                               int total, const int* s_flag, int n_shared, int* list, int tid) {
+#pragma unroll 1
+  for (int j = 0; j < n_shared; ++j) {
+    if (!s_flag[4 * j + 3]) continue;  // CTA-uniform: somebody else arrived last
+    const int slice = s_flag[4 * j], first = s_flag[4 * j + 1], n_parts = s_flag[4 * j + 2];
+    const int s_begin = slice * k_stages;
+    // scratch tile index of every contributor
+    for (int ci = tid; ci < n_parts; ci += CT) {
+      const uint32_t cta = (uint32_t)(first + ci);
+      const int cta_begin = (int)(cta * (uint32_t)total / gridDim.x);
+      list[ci] = (int)cta * 2 + (cta_begin < s_begin ? 1 : 0);
+    }
+    fence_acq_rel_gpu();
+    named_bar_sync(1, CT);
+    const int nelem = m_rows * NT;
+    // up to 4 elements x 4 contributors = 16 independent loads in flight per thread (L2 latency, not bandwidth, is the cost)
+    for (int idx0 = tid; idx0 < nelem; idx0 += 4 * CT) {
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 1
+      for (int c0 = 0; c0 < n_parts; c0 += 4) {
+        float t[4][4];
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+          const float* src = scratch + (size_t)list[min(c0 + cc, n_parts - 1)] * (size_t)(MP * NT);
+#pragma unroll
+          for (int u = 0; u < 4; ++u) t[cc][u] = (c0 + cc < n_parts && idx0 + u * CT < nelem) ? __ldcg(src + idx0 + u * CT) : 0.f;
+        }
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc)  // fixed order: deterministic sums
+#pragma unroll
+          for (int u = 0; u < 4; ++u) v[u] += t[cc][u];
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = idx0 + u * CT;
+        if (idx < nelem) c[(int64_t)slice * NT + (int64_t)(idx / NT) * N + idx % NT] = ScalarTraits<scalar_t>::from_float(v[u]);
+      }
+    }
+    if (tid == 0) counters[slice] = 0;  // leave the caller's lock buffer all-zero
+    named_bar_sync(1, CT);                // `list` is reused
+  }
+}
 
 // Tensor maps (built on the host per call, marlin_gemm.cu):
 //   tmB: weights as a 2-D array of 8-byte words [K/16][N], box [8*KG][NT]
@@ -75,16 +141,19 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const bool grouped = p.group_size < p.K;
   const int gps = grouped ? KT / p.group_size : 0;  // groups per 128 k (1, 2, 4)
-  const int slice = blockIdx.x / p.split, chunk = blockIdx.x % p.split;
-  const int kb = chunk * p.stages_per_chunk;
-  const int nk = min(p.k_stages, kb + p.stages_per_chunk) - kb;  // > 0 by construction
+  // stream-K: the (slice, k stage) list is cut into gridDim.x equal contiguous ranges, so every CTA streams the
+  // same number of 16 KiB weight stages whatever the shape; a range may end one slice and start the next
+  const int item_begin = (int)((int64_t)blockIdx.x * p.total / gridDim.x);
+  const int item_end = (int)((int64_t)(blockIdx.x + 1) * p.total / gridDim.x);
+  const int nk = item_end - item_begin;  // > 0: the host keeps grid <= total
   // the 128-byte swizzle pattern is a function of the shared-memory address: align the ring to 1 KiB
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
   float* red = reinterpret_cast<float*>(smem + STAGES * C::STAGE_BYTES);
   const uint32_t full_bar = smem_base + STAGES * C::STAGE_BYTES + C::RED_BYTES;
   const uint32_t empty_bar = full_bar + STAGES * 8;
-  int* s_last = reinterpret_cast<int*>(smem + STAGES * C::STAGE_BYTES + C::RED_BYTES + 2 * STAGES * 8);
+  // fix-up flags of shared slice j (0, 1): [4j] slice, [4j+1] first contributing CTA, [4j+2] contributors, [4j+3] am I the last arriver
+  int* s_flag = reinterpret_cast<int*>(smem + STAGES * C::STAGE_BYTES + C::RED_BYTES + 2 * STAGES * 8);
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -94,6 +163,9 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  // programmatic dependent launch: the next kernel of the stream may start filling free CTA slots now; it streams
+  // its (immutable) weights while this grid drains and touches activations / outputs only after griddep_wait()
+  griddep_launch_dependents();
 
   if (w == SG * CONSUMERS) {
     // ============================ producer: one thread, tiled TMA loads ============================
@@ -106,27 +178,55 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
     const uint64_t pol_keep = policy_evict_last();     // activations are shared by every CTA
     const uint32_t stage_tx =
         (uint32_t)(C::B_BYTES + C::A_BYTES + KG * gps * NT * 2 + (HAS_ZP ? KG * gps * (NT / 8) * 4 : 0));
-#pragma unroll 1
-    for (int it = 0; it < nk; ++it) {
+    // arm the stage's barrier with its whole byte count and fetch what does not depend on earlier kernels
+    auto load_weights = [&](int it, int slice, int ks) {
       const int st = it % STAGES;
-      const int ks = kb + it;
-      mbar_wait(empty_bar + st * 8, ((it / STAGES) & 1) ^ 1);
       const uint32_t sB = smem_base + st * C::STAGE_BYTES;
       const uint32_t fb = full_bar + st * 8;
       if (p.dbg == 2) {
         mbar_arrive(fb);
-        continue;
+        return;
       }
       mbar_expect_tx(fb, stage_tx);
       tma_load_2d_hint(sB, &tmB, slice * NT, ks * 8 * KG, fb, pol_stream);
-#pragma unroll
-      for (int i = 0; i < 2 * KG; ++i)
-        tma_load_2d_hint(sB + C::B_BYTES + i * C::A_BOX, &tmA, ks * C::KS + 64 * i, p.m0, fb, pol_keep);
       if (grouped) {
         tma_load_2d(sB + C::B_BYTES + C::A_BYTES, &tmS, slice * NT, ks * KG * gps, fb);
         if constexpr (HAS_ZP) tma_load_2d(sB + C::B_BYTES + C::A_BYTES + C::S_BYTES, &tmZ, slice * (NT / 8), ks * KG * gps, fb);
       }
-    }
+    };
+    auto load_activations = [&](int it, int ks) {
+      if (p.dbg == 2) return;
+      const int st = it % STAGES;
+      const uint32_t sA = smem_base + st * C::STAGE_BYTES + C::B_BYTES;
+#pragma unroll
+      for (int i = 0; i < 2 * KG; ++i)
+        tma_load_2d_hint(sA + i * C::A_BOX, &tmA, ks * C::KS + 64 * i, p.m0, full_bar + st * 8, pol_keep);
+    };
+    // the first STAGES items: weights at once (the ring starts empty), their activations after the dependency wait
+    int pre_ks[STAGES];
+    int it = 0;
+    bool waited = false;
+    auto end_prologue = [&]() {
+      griddep_wait();  // activations come from the previous kernel
+      const int n = it < STAGES ? it : STAGES;
+      for (int i = 0; i < n; ++i) load_activations(i, pre_ks[i]);
+      waited = true;
+    };
+    for_each_segment(item_begin, item_end, p.k_stages, [&](int slice, int k0, int cnt, bool) {
+#pragma unroll 1
+      for (int j = 0; j < cnt; ++j, ++it) {
+        if (it < STAGES) {
+          load_weights(it, slice, k0 + j);
+          pre_ks[it] = k0 + j;
+        } else {
+          if (!waited) end_prologue();
+          mbar_wait(empty_bar + (it % STAGES) * 8, ((it / STAGES) & 1) ^ 1);
+          load_weights(it, slice, k0 + j);
+          load_activations(it, k0 + j);
+        }
+      }
+    });
+    if (!waited) end_prologue();
     return;
   }
 
@@ -144,16 +244,18 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
   for (int i = 0; i < 4; ++i) a_sw[i] = ((uint32_t)(i << 1) ^ a_x) << 4;
 
   float acc[4][NB][4], part[4][NB][4], asum[NB][4];
+  auto clear_accumulators = [&]() {
 #pragma unroll
-  for (int j = 0; j < 4; ++j)
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int b = 0; b < NB; ++b)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[j][b][e] = part[j][b][e] = 0.f;
 #pragma unroll
     for (int b = 0; b < NB; ++b)
 #pragma unroll
-      for (int e = 0; e < 4; ++e) acc[j][b][e] = part[j][b][e] = 0.f;
-#pragma unroll
-  for (int b = 0; b < NB; ++b)
-#pragma unroll
-    for (int e = 0; e < 4; ++e) asum[b][e] = 0.f;
+      for (int e = 0; e < 4; ++e) asum[b][e] = 0.f;
+  };
 
   // acc += s * (part - zc * asum); part = asum = 0.   sc[j][h], zc[j][h]: tile j, row g (h=0) / g+8 (h=1)
   auto flush = [&](const float (&sc)[4][2], const float (&zc)[4][2]) {
@@ -207,109 +309,129 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
   const int rpg_mask = grouped ? p.group_size / 16 - 1 : 0x7fffffff;
   const int rpg_shift = grouped ? 31 - __clz(p.group_size / 16) : 31;
 
+  constexpr int CT = SG * CONSUMERS * 32;
+  griddep_wait();  // free here (no activation tile arrives before the producer passed its own wait); orders the global writes below
+
+  // ---------------- segments: the pieces of output slices inside this CTA's item range ----------------
+  int it0 = 0;        // CTA-local index of the segment's first item (ring position)
+  int n_shared = 0;   // shared slices met so far (at most two)
+  for_each_segment(item_begin, item_end, p.k_stages, [&](int slice, int k0, int cnt, bool whole) {
+    clear_accumulators();
+
 #pragma unroll 1
-  for (int it = sg; it < nk; it += SG) {
-    const int st = it % STAGES;
-    mbar_wait(full_bar + st * 8, (it / STAGES) & 1);
-    const uint32_t sbase = smem_base + st * C::STAGE_BYTES;
-    if (p.dbg != 1)
+    for (int it = it0 + ((sg - it0) & (SG - 1)); it < it0 + cnt; it += SG) {
+      const int st = it % STAGES;
+      mbar_wait(full_bar + st * 8, (it / STAGES) & 1);
+      const uint32_t sbase = smem_base + st * C::STAGE_BYTES;
+      if (p.dbg != 1)
 #pragma unroll
-    for (int r = 0; r < 8; ++r) {
-      uint32_t q[4];
-      lds128(sbase + offB + r * (NT * 8), q[0], q[1], q[2], q[3]);
-      uint32_t bf[NB][2];
-      const uint32_t aaddr = sbase + offA + (r >> 2) * C::A_BOX + a_sw[r & 3];
-      if constexpr (NB == 1) {
-        ldsm_x2(aaddr, bf[0][0], bf[0][1]);
-      } else {
+      for (int r = 0; r < 8; ++r) {
+        uint32_t q[4];
+        lds128(sbase + offB + r * (NT * 8), q[0], q[1], q[2], q[3]);
+        uint32_t bf[NB][2];
+        const uint32_t aaddr = sbase + offA + (r >> 2) * C::A_BOX + a_sw[r & 3];
+        if constexpr (NB == 1) {
+          ldsm_x2(aaddr, bf[0][0], bf[0][1]);
+        } else {
 #pragma unroll
-        for (int bb = 0; bb < NB; bb += 2) ldsm_x4(aaddr + bb * 8 * 128, bf[bb][0], bf[bb][1], bf[bb + 1][0], bf[bb + 1][1]);
+          for (int bb = 0; bb < NB; bb += 2) ldsm_x4(aaddr + bb * 8 * 128, bf[bb][0], bf[bb][1], bf[bb + 1][0], bf[bb + 1][1]);
+        }
+#pragma unroll
+        for (int b = 0; b < NB; ++b) mma16816<F16>(asum[b], C::ONES, C::ONES, C::ONES, C::ONES, bf[b][0], bf[b][1]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t a0 = and_or(q[j], 0x000f000fu, C::MAGIC);
+          const uint32_t a2 = and_or(q[j] >> 4, 0x000f000fu, C::MAGIC);
+          const uint32_t a1 = and_or(q[j] >> 8, 0x000f000fu, C::MAGIC);
+          const uint32_t a3 = and_or(q[j] >> 12, 0x000f000fu, C::MAGIC);
+#pragma unroll
+          for (int b = 0; b < NB; ++b) mma16816<F16>(part[j][b], a0, a1, a2, a3, bf[b][0], bf[b][1]);
+        }
+        // quantisation-group boundary: group sizes 32 / 64 end inside the warp block, 128 at its end
+        if ((r & 1) == 1 && ((r + 1) & rpg_mask) == 0)
+          flush_from_smem(smem + st * C::STAGE_BYTES, wg * gps + (r >> rpg_shift));
       }
-#pragma unroll
-      for (int b = 0; b < NB; ++b) mma16816<F16>(asum[b], C::ONES, C::ONES, C::ONES, C::ONES, bf[b][0], bf[b][1]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty_bar + st * 8);
+    }
+    if (!grouped) {
+      // channelwise: one scale row, "single" permutation over 32-column blocks (marlin_utils.py:204-213)
+      float sc[4][2], zc[4][2];
+      const scalar_t* srow = reinterpret_cast<const scalar_t*>(p.s) + (int64_t)slice * NT + wn * 64;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const uint32_t a0 = and_or(q[j], 0x000f000fu, C::MAGIC);
-        const uint32_t a2 = and_or(q[j] >> 4, 0x000f000fu, C::MAGIC);
-        const uint32_t a1 = and_or(q[j] >> 8, 0x000f000fu, C::MAGIC);
-        const uint32_t a3 = and_or(q[j] >> 12, 0x000f000fu, C::MAGIC);
-#pragma unroll
-        for (int b = 0; b < NB; ++b) mma16816<F16>(part[j][b], a0, a1, a2, a3, bf[b][0], bf[b][1]);
+        const int pos = (j >> 1) * 32 + 8 * (g >> 1) + (g & 1) + 4 * (j & 1);
+        sc[j][0] = ScalarTraits<scalar_t>::to_float(srow[pos]);
+        sc[j][1] = ScalarTraits<scalar_t>::to_float(srow[pos + 2]);
+        zc[j][0] = zc[j][1] = C::OFFSET + 8.f;
       }
-      // quantisation-group boundary: group sizes 32 / 64 end inside the warp block, 128 at its end
-      if ((r & 1) == 1 && ((r + 1) & rpg_mask) == 0)
-        flush_from_smem(smem + st * C::STAGE_BYTES, wg * gps + (r >> rpg_shift));
+      if constexpr (HAS_ZP) {
+        const uint32_t zword = *reinterpret_cast<const uint32_t*>(p.zp + ((int64_t)slice * (NT / 8) + wn * 8 + g) * 4);
+        decode_zp(zword, zc);
+      }
+      flush(sc, zc);
     }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(empty_bar + st * 8);
-  }
-  if (!grouped) {
-    // channelwise: one scale row, "single" permutation over 32-column blocks (marlin_utils.py:204-213)
-    float sc[4][2], zc[4][2];
-    const scalar_t* srow = reinterpret_cast<const scalar_t*>(p.s) + (int64_t)slice * NT + wn * 64;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int pos = (j >> 1) * 32 + 8 * (g >> 1) + (g & 1) + 4 * (j & 1);
-      sc[j][0] = ScalarTraits<scalar_t>::to_float(srow[pos]);
-      sc[j][1] = ScalarTraits<scalar_t>::to_float(srow[pos + 2]);
-      zc[j][0] = zc[j][1] = C::OFFSET + 8.f;
-    }
-    if constexpr (HAS_ZP) {
-      const uint32_t zword = *reinterpret_cast<const uint32_t*>(p.zp + ((int64_t)slice * (NT / 8) + wn * 8 + g) * 4);
-      decode_zp(zword, zc);
-    }
-    flush(sc, zc);
-  }
 
-  // ---------------- reduce the stage groups through shared memory, then the split-K fix-up ----------------
+    // ---------------- reduce the consumer warps through shared memory ----------------
 #pragma unroll
-  for (int j = 0; j < 4; ++j)
+    for (int j = 0; j < 4; ++j)
 #pragma unroll
-    for (int b = 0; b < NB; ++b) {
-      float* r0 = red + (size_t)((sg * KG + wg) * MP + b * 8 + 2 * t) * C::RP + wn * 64 + 16 * j + g;
-      r0[0] = acc[j][b][0];
-      r0[C::RP] = acc[j][b][1];
-      r0[8] = acc[j][b][2];
-      r0[C::RP + 8] = acc[j][b][3];
-    }
-  constexpr int CT = SG * CONSUMERS * 32;
-  named_bar_sync(1, CT);
+      for (int b = 0; b < NB; ++b) {
+        float* r0 = red + (size_t)((sg * KG + wg) * MP + b * 8 + 2 * t) * C::RP + wn * 64 + 16 * j + g;
+        r0[0] = acc[j][b][0];
+        r0[C::RP] = acc[j][b][1];
+        r0[8] = acc[j][b][2];
+        r0[C::RP + 8] = acc[j][b][3];
+      }
+    named_bar_sync(1, CT);
 
-  scalar_t* cout = reinterpret_cast<scalar_t*>(p.c) + (int64_t)p.m0 * p.N + (int64_t)slice * NT;
-  const int nelem = p.m_rows * NT;
-  if (p.split == 1) {
-    for (int idx = tid; idx < nelem; idx += CT) {
-      const int m = idx / NT, n = idx % NT;
-      float v = 0.f;
+    const int nelem = p.m_rows * NT;
+    if (whole) {
+      // the whole k range of the slice was ours: write the result
+      scalar_t* cout = reinterpret_cast<scalar_t*>(p.c) + (int64_t)p.m0 * p.N + (int64_t)slice * NT;
+      for (int idx = tid; idx < nelem; idx += CT) {
+        const int m = idx / NT, n = idx % NT;
+        float v = 0.f;
 #pragma unroll
-      for (int kg = 0; kg < SG * KG; ++kg) v += red[(size_t)(kg * MP + m) * C::RP + n];
-      cout[(int64_t)m * p.N + n] = ScalarTraits<scalar_t>::from_float(v);
+        for (int kg = 0; kg < SG * KG; ++kg) v += red[(size_t)(kg * MP + m) * C::RP + n];
+        cout[(int64_t)m * p.N + n] = ScalarTraits<scalar_t>::from_float(v);
+      }
+      named_bar_sync(1, CT);  // `red` is reused by the next segment
+    } else {
+      // the slice is shared with neighbouring CTAs: fp32 partial to the scratch, arrival published by one thread
+      // (barrier + its fence make the other threads' stores visible first); the sum is deferred to the end
+      const int s_begin = slice * p.k_stages;
+      float* mine = p.scratch + ((size_t)blockIdx.x * 2 + (item_begin < s_begin ? 1 : 0)) * (size_t)(MP * NT);
+      for (int idx = tid; idx < nelem; idx += CT) {
+        const int m = idx / NT, n = idx % NT;
+        float v = 0.f;
+#pragma unroll
+        for (int kg = 0; kg < SG * KG; ++kg) v += red[(size_t)(kg * MP + m) * C::RP + n];
+        __stcg(mine + idx, v);
+      }
+      named_bar_sync(1, CT);
+      if (tid == 0) {
+        // CTAs whose ranges meet [s_begin, s_begin + k_stages): owner(x) = ceil((x + 1) * grid / total) - 1
+        const uint32_t G = gridDim.x, T = (uint32_t)p.total;  // (total + 1) * grid < 2^31 (host)
+        const int first = (int)((((uint32_t)s_begin + 1u) * G + T - 1u) / T) - 1;
+        const int last = (int)((((uint32_t)(s_begin + p.k_stages)) * G + T - 1u) / T) - 1;
+        fence_acq_rel_gpu();
+        const int arrived = atomicAdd(&p.counters[slice], 1);
+        s_flag[4 * n_shared + 0] = slice;
+        s_flag[4 * n_shared + 1] = first;
+        s_flag[4 * n_shared + 2] = last - first + 1;
+        s_flag[4 * n_shared + 3] = (arrived == last - first);
+      }
+      ++n_shared;
     }
-    return;
-  }
-  float* base = p.scratch + (size_t)slice * p.split * (size_t)(MP * NT);
-  float* mine = base + (size_t)chunk * (MP * NT);
-  for (int idx = tid; idx < nelem; idx += CT) {
-    const int m = idx / NT, n = idx % NT;
-    float v = 0.f;
-#pragma unroll
-    for (int kg = 0; kg < SG * KG; ++kg) v += red[(size_t)(kg * MP + m) * C::RP + n];
-    __stcg(mine + idx, v);
-  }
-  __threadfence();
-  named_bar_sync(1, CT);
-  if (tid == 0) *s_last = (atomicAdd(&p.counters[slice], 1) == p.split - 1);
-  named_bar_sync(1, CT);
-  if (!*s_last) return;
-  __threadfence();
-  // last arriver: deterministic sum over the chunks in index order
-  for (int idx = tid; idx < nelem; idx += CT) {
-    float v = 0.f;
-    for (int ci = 0; ci < p.split; ++ci) v += __ldcg(base + (size_t)ci * (MP * NT) + idx);
-    const int m = idx / NT, n = idx % NT;
-    cout[(int64_t)m * p.N + n] = ScalarTraits<scalar_t>::from_float(v);
-  }
-  if (tid == 0) p.counters[slice] = 0;  // leave the caller's lock buffer all-zero
+    it0 += cnt;
+  });
+
+  // ---------------- deferred fix-up: the last arriver of a shared slice sums the partials in CTA order ----------------
+  if (n_shared == 0) return;
+  named_bar_sync(1, CT);  // flags visible, `red` free
+  sum_shared_slices<scalar_t, MP, NT, CT>(reinterpret_cast<scalar_t*>(p.c) + (int64_t)p.m0 * p.N, p.scratch, p.counters, p.N, p.m_rows,
+                                          p.k_stages, p.total, s_flag, n_shared, reinterpret_cast<int*>(red), tid);
 }
 
 }  // namespace mg

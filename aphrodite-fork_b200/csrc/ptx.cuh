@@ -284,6 +284,14 @@ __device__ __forceinline__ void tc_mma_ts_stage8(uint32_t d_tmem, uint32_t a_tme
       "r"(a_tmem), "r"(b_desc_lo), "r"(b_desc_hi), "r"(idesc), "r"(accumulate_first), "r"(box_step16)
       : "memory");
 }
+// release / acquire fence at GPU scope (cheaper than the sequentially consistent fence __threadfence() emits)
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+
+// programmatic dependent launch (PDL): wait = all prerequisite grids completed and their writes are visible;
+// launch_dependents = the next kernel of the stream may be scheduled once every CTA of this grid issued it or exited
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
   uint32_t done;
   asm volatile(

@@ -19,7 +19,26 @@ def _ops():
     return A.ops
 
 
-def _run_case(T, KVH, D, bs, nb, dtype, kv, k_scale, v_scale, seed, neg_frac=0.05, strided=True):
+def _prefill_slots(T, bs, nb, seed):
+    """Slot mapping of a prefill: runs of consecutive slots (whole blocks in a shuffled order), with a ragged first
+    run, one padding token and one run broken in the middle, so that both the transposed group path and the
+    per-element path of the kernel are taken inside one call."""
+    blocks = synth.permutation(nb, seed)
+    slots = []
+    start = 3  # the first sequence starts in the middle of a block
+    for b in blocks:
+        slots.extend(int(b) * bs + o for o in range(start, bs))
+        start = 0
+        if len(slots) >= T:
+            break
+    slots = torch.tensor(slots[:T], dtype=torch.int64)
+    if T > 40:
+        slots[17] = -1
+        slots[33], slots[34] = slots[34].clone(), slots[33].clone()
+    return slots
+
+
+def _run_case(T, KVH, D, bs, nb, dtype, kv, k_scale, v_scale, seed, neg_frac=0.05, strided=True, prefill=False):
     ops = _ops()
     cache_dt = torch.uint8 if kv != "auto" else dtype
     x = 16 // torch.tensor([], dtype=cache_dt).element_size()
@@ -30,7 +49,9 @@ def _run_case(T, KVH, D, bs, nb, dtype, kv, k_scale, v_scale, seed, neg_frac=0.0
         key = synth.tensor((T, KVH, D), seed, dtype, 3.0)
         value = synth.tensor((T, KVH, D), seed + 7, dtype, 3.0)
     slots = torch.from_numpy(synth.permutation(nb * bs, seed + 1)[:T].copy()).to(torch.int64)
-    nneg = int(T * neg_frac)
+    if prefill:
+        slots = _prefill_slots(T, bs, nb, seed + 1)
+    nneg = 0 if prefill else int(T * neg_frac)
     if nneg:
         slots[torch.from_numpy(synth.permutation(T, seed + 2)[:nneg].copy())] = -1
     if kv == "auto":
@@ -63,6 +84,16 @@ def _run_case(T, KVH, D, bs, nb, dtype, kv, k_scale, v_scale, seed, neg_frac=0.0
 @pytest.mark.parametrize("bs", [8, 16, 32])
 def test_reshape_and_cache_sweep(kv, dtype, D, bs):
     _run_case(42, 8, D, bs, 64, dtype, kv, 1.0, 1.0, seed=D + bs)
+
+
+@pytest.mark.parametrize("kv", ["auto", "fp8", "fp8_e5m2"])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("bs", [8, 16, 32])
+def test_reshape_and_cache_prefill_runs(kv, dtype, bs):
+    # consecutive slots (the transposed 8-token group path) mixed with ragged / broken / padded groups
+    _run_case(203, 4, 128, bs, 203 // bs + 4, dtype, kv, 0.5 if kv != "auto" else 1.0, 0.25 if kv != "auto" else 1.0,
+              seed=bs + 11, prefill=True)
+    _run_case(64, 8, 64, bs, 64 // bs + 2, dtype, kv, 1.0, 1.0, seed=bs + 12, prefill=True, strided=False)
 
 
 @pytest.mark.parametrize("kv", ["fp8", "fp8_e5m2"])

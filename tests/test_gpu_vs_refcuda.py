@@ -55,6 +55,8 @@ def test_reshape_and_cache_equals_reference_cuda(kv, dtype, shape):
     qkv = synth.tensor((T, 3, KVH, D), T + D, dtype, 3.0).to(dev)  # strided slices of a fused qkv, as the caller passes
     key, value = qkv[:, 1], qkv[:, 2]
     slots = torch.from_numpy(synth.permutation(nb * bs, T + 1)[:T].copy()).to(torch.int64)
+    if T == 2048:  # prefill: consecutive slots
+        slots = torch.arange(5, 5 + T, dtype=torch.int64)
     slots[::17] = -1
     slots = slots.to(dev)
     ks = torch.tensor(0.37 if kv != "auto" else 1.0, device=dev)

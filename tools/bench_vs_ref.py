@@ -123,7 +123,7 @@ def gemm(name, K, N, M, g=128, iters=40):
         print(json.dumps({"op": "gptq_marlin_gemm", "shape": name, "M": M, "max_diff_over_max_ref": d}), flush=True)
 
 
-def cache(T, KVH, D, kv, iters=50):
+def cache(T, KVH, D, kv, iters=50, consecutive=False):
     bs = 16
     nb = T // bs + 64
     esz = 1 if kv != "auto" else 2
@@ -132,13 +132,15 @@ def cache(T, KVH, D, kv, iters=50):
     gen = torch.Generator(device=DEV).manual_seed(0)
     qkv = torch.randn(T, 3, KVH, D, device=DEV, generator=gen).to(torch.bfloat16)
     slots = torch.randperm(nb * bs, device=DEV, generator=gen)[:T].to(torch.int64)
+    if consecutive:  # prefill: every sequence fills whole blocks in order
+        slots = torch.arange(T, device=DEV, dtype=torch.int64)
     kc = torch.zeros(nb, KVH, D // x, bs, x, dtype=cdt, device=DEV)
     vc = torch.zeros(nb, KVH, D, bs, dtype=cdt, device=DEV)
     one = torch.tensor(1.0, device=DEV)
     byt = T * KVH * D * (2 * 2 + 2 * esz) + 8 * T
     for name, o in impls():
         us = timed(lambda i, o=o: o.reshape_and_cache(qkv[:, 1], qkv[:, 2], kc, vc, slots, kv, one, one), iters)
-        print(json.dumps({"op": "reshape_and_cache", "T": T, "kv": kv, "impl": name, "us": round(us, 2),
+        print(json.dumps({"op": "reshape_and_cache", "T": T, "kv": kv, "slots": "consecutive" if consecutive else "random", "impl": name, "us": round(us, 2),
                           "GBps": round(byt / us / 1e3, 1)}), flush=True)
 
 
@@ -163,3 +165,5 @@ if __name__ == "__main__":
         for T in (64, 8192):
             for kv in ("auto", "fp8"):
                 cache(T, 8, 128, kv)
+        for kv in ("auto", "fp8"):
+            cache(8192, 8, 128, kv, consecutive=True)
