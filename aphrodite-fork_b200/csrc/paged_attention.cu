@@ -1,6 +1,8 @@
 // Host entry points aph_paged_attention_v1 / _v2: argument checks (the reference's TORCH_CHECKs,
 // paged_attention_v1.cu:100-168), split-K partition choice and dispatch to the per-head-size
 // translation units (paged_attention_inst.cu).
+#include <cstdlib>
+
 #include "paged_attention.cuh"
 
 namespace aphb200 {
@@ -24,19 +26,41 @@ struct Split {
   int num_partitions;
 };
 
-// Partition choice: enough CTAs for >= 4 waves at 3 CTAs/SM, partitions of >= 256 tokens
-// (multiple of 256 so that they start on stage and page boundaries for every block size).
+// Partition choice (multiples of 256 tokens so that partitions start on stage and page boundaries for every block
+// size). Measured on B200 (tools/sweep_attention_split.py, profiles/r01_attention_split_sweep.log): a CTA costs about
+// (partition_tokens + 600) token-times, so few long partitions beat many short ones as long as the grid is not a
+// fractional number of waves. Rule: if the whole problem fits in ONE wave of CTAs (3 per SM) with partitions of at
+// least 512 tokens and fills at least 70 % of it, launch exactly that wave (long contexts at small batch: C5 24 us
+// instead of 39); otherwise aim at >= 4 waves so that the ragged last wave is a small fraction (C2: 4.6 waves).
 static Split choose_split(int num_seqs, int num_heads, int num_kv_heads, int max_seq_len) {
   const int G = num_heads / num_kv_heads;
   const int tiles = (G + HEADS_PER_CTA - 1) / HEADS_PER_CTA;
   const int64_t units = (int64_t)num_seqs * num_kv_heads * tiles;
-  const int64_t target = (int64_t)sm_count() * 3 * 4;
+  // development overrides (tools/sweep_attention_split.py): waves of CTAs aimed at, smallest partition
+  const char* e_w = getenv("APH_PA_WAVES");
+  const char* e_m = getenv("APH_PA_MIN_PART");
+  const int waves = e_w ? atoi(e_w) : 4;
+  const int min_part = e_m ? atoi(e_m) : 256;
+  const int64_t slots = (int64_t)sm_count() * 3;
+  const int msl = max_seq_len < 1 ? 1 : max_seq_len;
+  Split s;
+  if (e_w == nullptr && e_m == nullptr && units > 0 && units <= slots) {
+    const int64_t p_fit = slots / units;
+    int64_t pt = (msl + p_fit - 1) / p_fit;
+    pt = ((pt + 255) / 256) * 256;
+    const int64_t np = (msl + pt - 1) / pt;
+    if (pt >= 512 && np > 1 && units * np * 10 >= slots * 7) {
+      s.partition_tokens = (int)pt;
+      s.num_partitions = (int)np;
+      return s;
+    }
+  }
+  const int64_t target = slots * (waves > 0 ? waves : 4);
   int64_t p_want = units > 0 ? (target + units - 1) / units : 1;
   if (p_want < 1) p_want = 1;
-  int msl = max_seq_len < 1 ? 1 : max_seq_len;
   int64_t pt = (msl + p_want - 1) / p_want;
   pt = ((pt + 255) / 256) * 256;
-  Split s;
+  if (pt < min_part) pt = (min_part + 255) / 256 * 256;
   s.partition_tokens = (int)pt;
   s.num_partitions = (int)((msl + pt - 1) / pt);
   return s;

@@ -31,9 +31,20 @@ static int launch_one(const Params& p, cudaStream_t stream) {
   kern<<<grid, C::NTHREADS, C::SMEM_BYTES, stream>>>(p);
   APH_LAUNCH_CHECK();
   if (p.num_partitions > 1) {
-    dim3 rgrid(p.num_heads, p.num_seqs);
-    paged_attention_reduce_kernel<scalar_t, D><<<rgrid, D >= 128 ? 128 : 64, 0, stream>>>(p, KV != APH_KV_AUTO);
-    APH_LAUNCH_CHECK();
+    // programmatic dependent launch: the reduce grid is set up while the main kernel drains (it waits on
+    // griddepcontrol.wait before reading the partials)
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(p.num_heads, p.num_seqs);
+    cfg.blockDim = dim3(D >= 128 ? 128 : 64);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const cudaError_t le = cudaLaunchKernelEx(&cfg, paged_attention_reduce_kernel<scalar_t, D>, p, KV != APH_KV_AUTO);
+    APH_CHECK(le == cudaSuccess, APH_ERR_CUDA, "paged_attention: reduce launch failed: %s", cudaGetErrorString(le));
   }
   return APH_OK;
 }

@@ -41,6 +41,7 @@ __global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar
 
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;
+  griddep_launch_dependents();  // the split-K reduce (launched with PDL) may be set up while this grid drains
   const int G = p.num_heads / p.num_kv_heads;
   const int tiles = (G + HEADS_PER_CTA - 1) / HEADS_PER_CTA;
   const int kvh = blockIdx.x / tiles, tile = blockIdx.x % tiles;
@@ -392,21 +393,56 @@ __global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar
 // Follows the reference's reduce (attention_kernels.cuh:604-667) on fp32 partials.
 template <typename scalar_t, int D>
 __global__ void __launch_bounds__(128) paged_attention_reduce_kernel(const Params p, const bool fp8) {
+  // launched with programmatic stream serialization right behind the main kernel: everything it reads is that
+  // kernel's output, so wait for it first (the launch latency is what overlaps)
+  griddep_wait();
+  constexpr int WCAP = 512;  // partition weights kept in shared memory (recomputed beyond)
+  __shared__ float s_w[WCAP];
+  __shared__ float s_red[2][4];
   const int head = blockIdx.x, seq = blockIdx.y;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, nw = blockDim.x >> 5;
   const int L = p.seq_lens[seq];
   const int P = p.num_partitions;
   const int np = L <= 0 ? 0 : min(P, (L + p.partition_tokens - 1) / p.partition_tokens);
   const int64_t base = ((int64_t)seq * p.num_heads + head) * P;
+  const float2* ml = reinterpret_cast<const float2*>(p.part_ml) + base;  // (max, sum) of every partition
   const float v_scale = fp8 ? *p.v_scale : 1.f;
-  float m_tot = -INFINITY;
-  for (int j = 0; j < np; ++j) m_tot = fmaxf(m_tot, p.part_ml[(base + j) * 2]);
+  // the threads split the partitions: global max, then weights 2^(m_j - m) and the denominator
+  float m_loc = -INFINITY;
+  for (int j = tid; j < np; j += blockDim.x) m_loc = fmaxf(m_loc, ml[j].x);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m_loc = fmaxf(m_loc, __shfl_xor_sync(0xffffffffu, m_loc, o));
+  if (lane == 0) s_red[0][w] = m_loc;
+  __syncthreads();
+  float m_tot = s_red[0][0];
+  for (int i = 1; i < nw; ++i) m_tot = fmaxf(m_tot, s_red[0][i]);
   const float m_use = m_tot == -INFINITY ? 0.f : m_tot;
+  float d_loc = 0.f;
+  for (int j = tid; j < np; j += blockDim.x) {
+    const float2 v = ml[j];
+    const float wj = ex2(v.x - m_use);
+    if (j < WCAP) s_w[j] = wj;
+    d_loc += v.y * wj;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) d_loc += __shfl_xor_sync(0xffffffffu, d_loc, o);
+  if (lane == 0) s_red[1][w] = d_loc;
+  __syncthreads();
   float denom = 0.f;
-  for (int j = 0; j < np; ++j) denom += p.part_ml[(base + j) * 2 + 1] * ex2(p.part_ml[(base + j) * 2] - m_use);
+  for (int i = 0; i < nw; ++i) denom += s_red[1][i];
   const float inv = __fdividef(1.f, denom + 1e-6f) * v_scale;
-  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+  const float* po = p.part_o + base * D;
+  for (int d = tid; d < D; d += blockDim.x) {
     float acc = 0.f;
-    for (int j = 0; j < np; ++j) acc += p.part_o[(base + j) * D + d] * ex2(p.part_ml[(base + j) * 2] - m_use);
+    int j = 0;
+    for (; j + 8 <= np; j += 8) {  // eight independent loads in flight
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = po[(int64_t)(j + u) * D + d];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) acc += v[u] * (j + u < WCAP ? s_w[j + u] : ex2(ml[j + u].x - m_use));
+    }
+    for (; j < np; ++j) acc += po[(int64_t)j * D + d] * (j < WCAP ? s_w[j] : ex2(ml[j].x - m_use));
     ((scalar_t*)p.out)[(int64_t)seq * p.out_stride + (int64_t)head * D + d] =
         ScalarTraits<scalar_t>::from_float(acc * inv);
   }

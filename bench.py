@@ -200,7 +200,16 @@ def gemm_extras(torch, A, dev, iters=30):
     """W4A16 GEMM on the C3 shapes (Llama-3.1-8B, g128, bf16): us/call under a CUDA graph with weights rotated through
     > 256 MB of distinct buffers, HBM GB/s on the algorithmic bytes and TFLOP/s. Secondary numbers of BASELINE's metric."""
     UINT4B8 = 1125899907892224
-    shapes = {"qkv": (4096, 6144), "o": (4096, 4096), "gate_up": (4096, 28672), "down": (14336, 4096)}
+    shapes = {"qkv": (4096, 6144), "o": (4096, 4096), "gate_up": (4096, 28672), "down": (14336, 4096),
+              # C4 (Llama-3.1-70B, TP1 shapes of tests/benchmarks/kernels/benchmark_shapes.py:57-62): matrices large
+              # enough (235 MB) that one launch can approach the HBM roofline at all
+              "70b_gate_up": (8192, 57344), "70b_down": (28672, 8192)}
+    hbm_peak, _ = peaks()
+    tensor_peak = 1657.3
+    try:
+        tensor_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"])
+    except Exception:
+        pass
     res = {}
     gen = torch.Generator(device=dev).manual_seed(0)
     e = torch.empty(0, dtype=torch.int32, device=dev)
@@ -209,7 +218,7 @@ def gemm_extras(torch, A, dev, iters=30):
         bs = [torch.randint(-2**31, 2**31 - 1, (K // 16, N * 2), dtype=torch.int32, device=dev, generator=gen) for _ in range(nbuf)]
         ss = [(torch.rand(K // 128, N, device=dev, generator=gen) * 0.01 + 0.005).to(torch.bfloat16) for _ in range(nbuf)]
         ws = torch.zeros(N // 64 * 16, dtype=torch.int32, device=dev)
-        for M in (1, 16, 64, 256, 1024):
+        for M in ((1, 16, 64, 256, 1024) if not name.startswith("70b") else (1, 16, 256)):
             a = torch.randn(M, K, device=dev, generator=gen).to(torch.bfloat16)
             f = lambda i: A.ops.gptq_marlin_gemm(a, bs[i % nbuf], ss[i % nbuf], e, e, e, ws, UINT4B8, M, N, K, True)
             for i in range(3):
@@ -230,7 +239,9 @@ def gemm_extras(torch, A, dev, iters=30):
                 st.synchronize()
             us = e0.elapsed_time(e1) / iters * 1e3
             byt = K * N // 2 + (K // 128) * N * 2 + M * K * 2 + M * N * 2
-            res[f"{name}_m{M}"] = {"us": round(us, 2), "GBps": round(byt / us / 1e3, 1), "TFLOPs": round(2 * M * N * K / us / 1e6, 1)}
+            res[f"{name}_m{M}"] = {"us": round(us, 2), "GBps": round(byt / us / 1e3, 1), "TFLOPs": round(2 * M * N * K / us / 1e6, 1),
+                                   "frac_hbm": round(byt / us / 1e3 / hbm_peak, 3),
+                                   "frac_tensor": round(2 * M * N * K / us / 1e6 / tensor_peak, 3)}
         del bs, ss
     return res
 
@@ -342,34 +353,75 @@ def run_ours(args):
     per_gpu = per_step_bytes * steps / (ms * 1e-3) / 1e9
 
     # ---- e2e: public API, host-resident step inputs, copies inside the timed region ----
-    pin = dict(pin_memory=True)
-    q_h = q.cpu().pin_memory()
-    newkv_h = ((torch.rand(BATCH, 2, KVH, D) * 2 - 1) * sc).to(torch.bfloat16).pin_memory()
-    bt_h = bt.cpu().pin_memory()
-    sl_h = sl.cpu().pin_memory()
-    slots_h = (bt_h[:, -1].to(torch.int64) * BS + (BS - 1)).pin_memory()  # slot of token ctx-1 of every sequence
-    out_h = torch.empty(BATCH, H, D, dtype=torch.bfloat16, **pin)
-    h2d = sum(t.numel() * t.element_size() for t in (q_h, newkv_h, bt_h, sl_h, slots_h))
-    d2h = out_h.numel() * out_h.element_size()
+    # Every step copies ITS inputs (query, new K/V token, block tables, sequence lengths, slot mapping) from pinned host
+    # memory and copies ITS output back. The way a serving loop drives the API: the step's inputs are packed in one
+    # pinned staging buffer (one H2D copy), and three streams (copy-in / compute / copy-out) with two device staging
+    # buffers let step i+1's upload and step i-1's download run under step i's kernels.
+    def seg(nbytes):
+        return (nbytes + 255) // 256 * 256
+
+    parts = [("q", (BATCH, H, D), torch.bfloat16), ("newkv", (BATCH, 2, KVH, D), torch.bfloat16),
+             ("bt", (BATCH, CTX // BS), torch.int32), ("sl", (BATCH,), torch.int32), ("slots", (BATCH,), torch.int64)]
+    offs, total_in = {}, 0
+    for name, shape, dt in parts:
+        n = int(torch.tensor(shape).prod()) * torch.tensor([], dtype=dt).element_size()
+        offs[name] = (total_in, n, shape, dt)
+        total_in += seg(n)
+
+    def views(buf):
+        return {name: buf[o:o + n].view(dt).view(shape) for name, (o, n, shape, dt) in offs.items()}
+
+    in_h = torch.empty(total_in, dtype=torch.uint8, pin_memory=True)
+    hv = views(in_h)
+    hv["q"].copy_(q.cpu())
+    hv["newkv"].copy_(((torch.rand(BATCH, 2, KVH, D) * 2 - 1) * sc).to(torch.bfloat16))
+    hv["bt"].copy_(bt.cpu())
+    hv["sl"].copy_(sl.cpu())
+    hv["slots"].copy_(hv["bt"][:, -1].to(torch.int64) * BS + (BS - 1))  # slot of token ctx-1 of every sequence
+    NBUF = 2
+    in_d = [torch.empty(total_in, dtype=torch.uint8, device=dev) for _ in range(NBUF)]
+    dv = [views(b) for b in in_d]
+    out_h = [torch.empty(BATCH, H, D, dtype=torch.bfloat16, pin_memory=True) for _ in range(NBUF)]
+    h2d = sum(n for _, (o, n, shape, dt) in offs.items())
+    d2h = out_h[0].numel() * out_h[0].element_size()
+    s_in, s_out = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    s_cmp = torch.cuda.current_stream()
+    ev_in = [torch.cuda.Event() for _ in range(NBUF)]     # upload of buffer b finished
+    ev_cmp = [torch.cuda.Event() for _ in range(NBUF)]    # kernels reading buffer b finished
+    ev_out = [torch.cuda.Event() for _ in range(NBUF)]    # download into out_h[b] finished
 
     def e2e_step(i):
+        b = i % NBUF
         kc, vc = pools[i % npools]
-        qd = q_h.to(dev, non_blocking=True)
-        nkv = newkv_h.to(dev, non_blocking=True)
-        btd = bt_h.to(dev, non_blocking=True)
-        sld = sl_h.to(dev, non_blocking=True)
-        sd = slots_h.to(dev, non_blocking=True)
-        A.PagedAttention.write_to_paged_cache(nkv[:, 0], nkv[:, 1], kc, vc, sd, "fp8", one, one)
-        o = A.PagedAttention.forward_decode(qd, kc, vc, btd, sld, CTX, "fp8", KVH, sc, None, one, one)
-        out_h.copy_(o, non_blocking=True)
+        with torch.cuda.stream(s_in):
+            s_in.wait_event(ev_cmp[b])                    # the kernels of step i-2 are done with this staging buffer
+            in_d[b].copy_(in_h, non_blocking=True)
+            ev_in[b].record(s_in)
+        s_cmp.wait_event(ev_in[b])
+        v = dv[b]
+        A.PagedAttention.write_to_paged_cache(v["newkv"][:, 0], v["newkv"][:, 1], kc, vc, v["slots"], "fp8", one, one)
+        o = A.PagedAttention.forward_decode(v["q"], kc, vc, v["bt"], v["sl"], CTX, "fp8", KVH, sc, None, one, one)
+        ev_cmp[b].record(s_cmp)
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(ev_cmp[b])
+            out_h[b].copy_(o, non_blocking=True)
+            o.record_stream(s_out)
+            ev_out[b].record(s_out)
+
+    def e2e_drain():
+        for b in range(NBUF):
+            s_cmp.wait_event(ev_out[b])
+            s_cmp.wait_event(ev_in[b])
 
     for i in range(warm):
         e2e_step(i)
+    e2e_drain()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(steps):
         e2e_step(i)
+    e2e_drain()  # the last downloads are inside the timed region
     e1.record()
     barrier()
     ems = e0.elapsed_time(e1)
@@ -409,8 +461,9 @@ def run_ours(args):
                                  f"peak = {peak_src}"},
             "e2e": {"value": round(e2e_val, 2), "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": round(ems / steps, 5),
-                    "api": "PagedAttention.write_to_paged_cache + forward_decode (host-pinned q/new-kv/slots/"
-                           "block_tables/seq_lens -> device, output -> host)"},
+                    "api": "PagedAttention.write_to_paged_cache + forward_decode; every step uploads its q / new K,V token / "
+                           "block tables / seq lens / slot mapping from ONE packed pinned host buffer and downloads its "
+                           "output; copy-in, compute and copy-out streams with two staging buffers overlap neighbouring steps"},
             "gpu_launches": 2 * steps,
             "clocks": clocks,
             "extras": extras,
