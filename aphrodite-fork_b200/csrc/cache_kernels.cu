@@ -25,6 +25,8 @@ __global__ void reshape_and_cache_generic_kernel(const scalar_t* __restrict__ ke
                                                  int64_t value_stride, int num_heads, int head_size, int block_size,
                                                  int x, int64_t block_stride, const float* __restrict__ k_scale,
                                                  const float* __restrict__ v_scale) {
+  pdl_trigger();
+  pdl_wait();  // key / value come from the previous kernel; the cache may still be read by it
   const int64_t token = blockIdx.x;
   const int64_t slot = slot_mapping[token];
   if (slot < 0) return;
@@ -76,6 +78,8 @@ __global__ void __launch_bounds__(256)
   using InVec = Pack<scalar_t, LV>;
   __shared__ int64_t s_slot[TG];
   __shared__ int s_run;
+  pdl_trigger();
+  pdl_wait();  // key / value come from the previous kernel; the cache may still be read by it
   const int64_t t0 = (int64_t)blockIdx.x * TG;
   const int nt = (int)(num_tokens - t0 < TG ? num_tokens - t0 : TG);
   if (threadIdx.x < TG) s_slot[threadIdx.x] = (int)threadIdx.x < nt ? slot_mapping[t0 + threadIdx.x] : -1;
@@ -188,17 +192,16 @@ int launch_reshape_and_cache(const void* key, const void* value, void* key_cache
     // many tokens: at most 8 scattered elements per thread (memory-level parallelism comes from resident warps)
     while ((int64_t)ysplit * threads * 8 < (int64_t)TG * n && ysplit < 64) ysplit *= 2;
     dim3 grid((unsigned)groups, ysplit);
-    reshape_and_cache_vec_kernel<scalar_t, cache_t, KV><<<grid, threads, 0, stream>>>(
-        (const scalar_t*)key, (const scalar_t*)value, (cache_t*)key_cache, (cache_t*)value_cache, slot_mapping, num_tokens,
-        key_stride, value_stride, num_heads, head_size, block_size, block_stride, k_scale, v_scale);
+    APH_LAUNCH_PDL(reshape_and_cache_vec_kernel<scalar_t, cache_t, KV>, grid, dim3(threads), (size_t)0, stream,
+                   (const scalar_t*)key, (const scalar_t*)value, (cache_t*)key_cache, (cache_t*)value_cache, slot_mapping,
+                   num_tokens, key_stride, value_stride, num_heads, head_size, block_size, block_stride, k_scale, v_scale);
   } else {
     dim3 grid((unsigned)num_tokens, 1);
     const int threads = n < 512 ? ((n + 31) / 32) * 32 : 512;
-    reshape_and_cache_generic_kernel<scalar_t, cache_t, KV><<<grid, threads, 0, stream>>>(
-        (const scalar_t*)key, (const scalar_t*)value, (cache_t*)key_cache, (cache_t*)value_cache, slot_mapping,
-        key_stride, value_stride, num_heads, head_size, block_size, x, block_stride, k_scale, v_scale);
+    APH_LAUNCH_PDL(reshape_and_cache_generic_kernel<scalar_t, cache_t, KV>, grid, dim3(threads), (size_t)0, stream,
+                   (const scalar_t*)key, (const scalar_t*)value, (cache_t*)key_cache, (cache_t*)value_cache, slot_mapping,
+                   key_stride, value_stride, num_heads, head_size, block_size, x, block_stride, k_scale, v_scale);
   }
-  APH_LAUNCH_CHECK();
   return APH_OK;
 }
 

@@ -34,6 +34,38 @@ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 // free and the reference pays it on every GEMM call, gptq_marlin.cu:2104-2110).
 int sm_count();
 
+// Programmatic dependent launch (PDL). Every kernel of this library is launched with programmatic stream
+// serialization and (a) issues griddepcontrol.launch_dependents early, (b) issues griddepcontrol.wait before it reads
+// anything an earlier kernel may have written or writes anything an earlier kernel may still read. Back-to-back
+// kernels of a decode step then overlap launch latency and prologue with the previous kernel's tail; next to foreign
+// kernels (torch, NCCL) the attribute degrades to ordinary stream order. APH_PDL=0 switches the attribute off.
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
+#define APH_LAUNCH_PDL(...)                                                                               \
+  do {                                                                                                    \
+    cudaError_t e__ = ::aphb200::launch_pdl(__VA_ARGS__);                                                 \
+    if (e__ != cudaSuccess)                                                                               \
+      return ::aphb200::set_error(APH_ERR_CUDA, "CUDA launch failed: %s", cudaGetErrorString(e__));       \
+  } while (0)
+
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 template <typename T>
 struct ScalarTraits;
 template <>

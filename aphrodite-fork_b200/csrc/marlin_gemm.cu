@@ -139,17 +139,6 @@ struct Operands {
   bool f16;
 };
 
-// Programmatic dependent launch (APH_PDL=0 turns it off): a kernel of this library may start while the previous
-// kernel of the stream drains; it prefetches weights and waits (griddepcontrol.wait) before touching anything an
-// earlier kernel wrote. Works eagerly and under stream capture (the graph keeps the programmatic edge).
-static bool pdl_enabled() {
-  static const bool on = [] {
-    const char* e = getenv("APH_PDL");
-    return e == nullptr || e[0] != '0';
-  }();
-  return on;
-}
-
 template <typename scalar_t, int NB, int NT, bool HAS_ZP>
 static int launch(const Params& p, const Operands& op, int grid, cudaStream_t stream) {
   using C = Cfg<scalar_t, NB, NT>;
@@ -326,8 +315,20 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
     cudaMalloc(&p.trace, 72 * 8 * sizeof(unsigned long long));
     cudaMemsetAsync(p.trace, 0, 72 * 8 * sizeof(unsigned long long), stream);
   }
-  kern<<<pl.grid, mgtc::THREADS, C::SMEM_BYTES, stream>>>(p, tmB, tmA, tmS, tmZ);
-  APH_LAUNCH_CHECK();
+  {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)pl.grid);
+    cfg.blockDim = dim3(mgtc::THREADS);
+    cfg.dynamicSmemBytes = C::SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, p, tmB, tmA, tmS, tmZ);
+    APH_CHECK(le == cudaSuccess, APH_ERR_CUDA, "gptq_marlin_gemm: launch failed: %s", cudaGetErrorString(le));
+  }
   if (trace_path != nullptr) {
     unsigned long long host[72 * 8];
     cudaStreamSynchronize(stream);
@@ -355,31 +356,45 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
 }
 
 template <typename scalar_t>
-static int run_typed_tc(const Params& p0, const Operands& op, bool has_zp, float* scratch, size_t scratch_bytes, cudaStream_t stream) {
-  mgtc::Params p{};
-  p.s = p0.s;
-  p.zp = p0.zp;
-  p.c = p0.c;
-  p.counters = p0.counters;
-  p.N = p0.N;
-  p.K = p0.K;
-  p.group_size = p0.group_size;
-  // the arrival counters live in the caller's lock buffer (N / 64 * 16 ints): one per (slice, batch tile)
-  APH_CHECK((op.M + 255) / 256 <= 32, APH_ERR_UNSUPPORTED, "gptq_marlin_gemm: size_m above 8192 is not supported in one call");
+static int run_typed_tc(const Params& p0, const Operands& op0, bool has_zp, float* scratch, size_t scratch_bytes, cudaStream_t stream) {
+  // One launch covers every 256-row batch tile (the item list is (slice, batch tile, k stage)); APH_TC_CHUNK=1 runs
+  // one launch per 256 rows instead (development).
+  static const bool chunked = getenv("APH_TC_CHUNK") != nullptr;
+  const int64_t step = chunked ? 256 : (1LL << 40);
+  for (int64_t m0 = 0; m0 < op0.M; m0 += step) {
+    const int64_t rows = op0.M - m0 < step ? op0.M - m0 : step;
+    Operands op = op0;
+    op.a = static_cast<const char*>(op0.a) + (size_t)m0 * (size_t)op0.lda * 2;
+    op.M = rows;
+    mgtc::Params p{};
+    p.s = p0.s;
+    p.zp = p0.zp;
+    p.c = static_cast<char*>(p0.c) + (size_t)m0 * (size_t)p0.N * 2;
+    p.counters = p0.counters;  // arrival counters in the caller's lock buffer (N / 64 * 16 ints): one per slice
+    p.N = p0.N;
+    p.K = p0.K;
+    p.group_size = p0.group_size;
+    APH_CHECK((rows + 255) / 256 <= 32, APH_ERR_UNSUPPORTED, "gptq_marlin_gemm: size_m above 8192 is not supported in one call");
+    int st;
 #define APH_TC_CASE(MBV)                                                                                  \
   case MBV:                                                                                               \
-    return has_zp ? launch_tc<scalar_t, MBV, true>(p, op, scratch, scratch_bytes, stream)                 \
-                  : launch_tc<scalar_t, MBV, false>(p, op, scratch, scratch_bytes, stream);
-  switch (tile_rows_tc(op.M)) {
-    APH_TC_CASE(16)
-    APH_TC_CASE(32)
-    APH_TC_CASE(64)
-    APH_TC_CASE(128)
-    default:
-      return has_zp ? launch_tc<scalar_t, 256, true>(p, op, scratch, scratch_bytes, stream)
+    st = has_zp ? launch_tc<scalar_t, MBV, true>(p, op, scratch, scratch_bytes, stream)                   \
+                : launch_tc<scalar_t, MBV, false>(p, op, scratch, scratch_bytes, stream);                 \
+    break;
+    switch (tile_rows_tc(rows)) {
+      APH_TC_CASE(16)
+      APH_TC_CASE(32)
+      APH_TC_CASE(64)
+      APH_TC_CASE(128)
+      default:
+        st = has_zp ? launch_tc<scalar_t, 256, true>(p, op, scratch, scratch_bytes, stream)
                     : launch_tc<scalar_t, 256, false>(p, op, scratch, scratch_bytes, stream);
-  }
+        break;
+    }
 #undef APH_TC_CASE
+    if (st != APH_OK) return st;
+  }
+  return APH_OK;
 }
 
 // which path serves a problem: APH_GEMM_PATH = mma | tc forces one (development), default by batch size

@@ -78,8 +78,14 @@ struct Cfg {
   static constexpr int FIX_BYTES = 0;
   static constexpr int BUDGET = 227 * 1024 - 1024 - 1024 - FIX_BYTES - 4096;
   static constexpr int SA_SMEM = (BUDGET - 3 * W_STAGE) / ACT_BYTES;
-  static constexpr int SA = SA_SMEM < SA_TMEM ? SA_SMEM : SA_TMEM;
-  static_assert(SA >= 2 && SA <= 7, "activation ring depth");
+  // The ring depth is kept EVEN: stage `it` goes to dequantiser group it & 1 and to slot it % SA, so with an even
+  // depth every slot belongs to one group. With the odd depth 3 (the natural fit at 256 batch rows) a slot alternates
+  // between the groups, and tools/stress_gemm.py then showed a wrong 32..128-column stripe of one tile in ~0.1 % of
+  // the calls (plus sporadic launch failures at M = 1024); depth 2 is clean over 40 000 calls. The ordering hazard
+  // behind it has not been isolated; the even depth costs ~3 % at M >= 256.
+  static constexpr int SA_FIT = SA_SMEM < SA_TMEM ? SA_SMEM : SA_TMEM;
+  static constexpr int SA = SA_FIT > 2 ? (SA_FIT & ~1) : SA_FIT;
+  static_assert(SA >= 2 && SA <= 7 && (SA % 2 == 0), "activation ring depth");
   static constexpr int SW_FIT = (BUDGET - SA * ACT_BYTES) / W_STAGE;
   static constexpr int SW = SW_FIT > 8 ? 8 : SW_FIT;
   static_assert(SW >= 3, "weight ring too shallow");
@@ -197,6 +203,10 @@ __global__ void __launch_bounds__(THREADS, 1)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // programmatic dependent launch: the next kernel of the stream may be set up from here on; this kernel streams
+  // its (immutable) weights at once, every role that touches activations or global outputs waits for the previous
+  // kernel first (griddep_wait)
+  griddep_launch_dependents();
 
   // Every role walks the same list of segments (tile, k0..k1) and keeps the same global stage counter `it`.
 #define APH_SEGMENTS                                                                                         \
@@ -294,6 +304,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     // ==================== activation producer ====================
     if (lane != 0) return;
     prefetch_tensormap(&tmA);
+    griddep_wait();  // activations are the previous kernel's output
     const uint64_t pol_keep = policy_evict_last();  // activations are shared by every CTA
     int it = 0;
     APH_SEGMENTS {
@@ -366,6 +377,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 
   if (w >= W_DQ0) {
     // ================================ dequantiser warps ================================
+    griddep_wait();                       // they join the end-of-kernel merge (global reads / writes)
     const int qd = w & 3;                 // TMEM lane quadrant this warp may access
     const int dw = w - W_DQ0;
     const int h = (dw >> 2) & 1;          // which half of the stage's k16-rows
@@ -475,6 +487,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 
   // ================================ epilogue warps ================================
   {
+    griddep_wait();  // global writes (C, partials, counters) only after the previous kernel is complete
     const int qd = w & 3;
     const int etid = tid - W_EPI0 * 32;
     constexpr int ET = EPI_WARPS * 32;

@@ -28,23 +28,11 @@ static int launch_one(const Params& p, cudaStream_t stream) {
   const int G = p.num_heads / p.num_kv_heads;
   const int tiles = (G + HEADS_PER_CTA - 1) / HEADS_PER_CTA;
   dim3 grid(p.num_kv_heads * tiles, p.num_seqs, p.num_partitions);
-  kern<<<grid, C::NTHREADS, C::SMEM_BYTES, stream>>>(p);
-  APH_LAUNCH_CHECK();
+  APH_LAUNCH_PDL(kern, grid, dim3(C::NTHREADS), (size_t)C::SMEM_BYTES, stream, p);
   if (p.num_partitions > 1) {
-    // programmatic dependent launch: the reduce grid is set up while the main kernel drains (it waits on
-    // griddepcontrol.wait before reading the partials)
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(p.num_heads, p.num_seqs);
-    cfg.blockDim = dim3(D >= 128 ? 128 : 64);
-    cfg.dynamicSmemBytes = 0;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    const cudaError_t le = cudaLaunchKernelEx(&cfg, paged_attention_reduce_kernel<scalar_t, D>, p, KV != APH_KV_AUTO);
-    APH_CHECK(le == cudaSuccess, APH_ERR_CUDA, "paged_attention: reduce launch failed: %s", cudaGetErrorString(le));
+    // the reduce grid is set up while the main kernel drains (it waits before reading the partials)
+    APH_LAUNCH_PDL(paged_attention_reduce_kernel<scalar_t, D>, dim3(p.num_heads, p.num_seqs), dim3(D >= 128 ? 128 : 64), (size_t)0,
+                   stream, p, KV != APH_KV_AUTO);
   }
   return APH_OK;
 }

@@ -41,7 +41,8 @@ __global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar
 
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;
-  griddep_launch_dependents();  // the split-K reduce (launched with PDL) may be set up while this grid drains
+  pdl_trigger();  // the next kernel (the split-K reduce) may be set up while this grid drains
+  pdl_wait();     // q, the KV cache (the new token was just written) and the block tables come from earlier kernels
   const int G = p.num_heads / p.num_kv_heads;
   const int tiles = (G + HEADS_PER_CTA - 1) / HEADS_PER_CTA;
   const int kvh = blockIdx.x / tiles, tile = blockIdx.x % tiles;
@@ -395,7 +396,8 @@ template <typename scalar_t, int D>
 __global__ void __launch_bounds__(128) paged_attention_reduce_kernel(const Params p, const bool fp8) {
   // launched with programmatic stream serialization right behind the main kernel: everything it reads is that
   // kernel's output, so wait for it first (the launch latency is what overlaps)
-  griddep_wait();
+  pdl_wait();
+  pdl_trigger();
   constexpr int WCAP = 512;  // partition weights kept in shared memory (recomputed beyond)
   __shared__ float s_w[WCAP];
   __shared__ float s_red[2][4];

@@ -1,6 +1,8 @@
 // Error text, ABI version and small host helpers behind include/aphrodite_b200.h.
 #include <cstring>
 
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace aphb200 {
@@ -28,6 +30,14 @@ int sm_count() {
     cached[dev] = n;
   }
   return cached[dev];
+}
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("APH_PDL");
+    return e == nullptr || e[0] != '0';
+  }();
+  return on;
 }
 
 }  // namespace aphb200

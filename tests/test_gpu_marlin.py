@@ -117,6 +117,34 @@ def test_gptq_marlin_gemm_repeated_calls_leave_workspace_clean():
     assert outs[0] == outs[1] == outs[2]
 
 
+@pytest.mark.parametrize("M", [16, 256, 1024])
+def test_gptq_marlin_gemm_run_to_run_determinism_large_shape(M):
+    # the Llama-3.1-8B down projection: deep K, stream-K ranges shared by many CTAs, back-to-back launches over rotating
+    # weights. Every call on the same weights must return the same bits (fixed-order merges) and leave the lock buffer
+    # zero. (With an odd activation-ring depth at 256 batch rows ~0.1 % of the calls returned a wrong stripe of one
+    # tile; marlin_gemm_tc.cuh now keeps the depth even. tools/stress_gemm.py is the long version of this test.)
+    K, N = 14336, 4096
+    dev = "cuda"
+    gen = torch.Generator(device=dev).manual_seed(0)
+    nbuf = 3
+    bs = [torch.randint(-2**31, 2**31 - 1, (K // 16, N * 2), dtype=torch.int32, device=dev, generator=gen) for _ in range(nbuf)]
+    ss = [(torch.rand(K // 128, N, device=dev, generator=gen) * 0.01 + 0.005).to(torch.bfloat16) for _ in range(nbuf)]
+    a = torch.randn(M, K, device=dev, generator=gen).to(torch.bfloat16)
+    e = torch.empty(0, dtype=torch.int32, device=dev)
+    ws = torch.zeros(N // 64 * 16, dtype=torch.int32, device=dev)
+    ref = [None] * nbuf
+    for r in range(60):
+        outs = [(i % nbuf, _ops().gptq_marlin_gemm(a, bs[i % nbuf], ss[i % nbuf], e, e, e, ws, mf.UINT4B8, M, N, K, True))
+                for i in range(5)]
+        torch.cuda.synchronize()
+        for j, o in outs:
+            if ref[j] is None:
+                ref[j] = o.clone()
+            else:
+                assert torch.equal(ref[j], o), f"call {r}: output differs from the first call on the same inputs"
+    assert int(ws.abs().sum()) == 0
+
+
 def test_gptq_marlin_gemm_strided_a_and_flags():
     case(9, 512, 256, 128, torch.bfloat16, lda_pad=64, use_fp32_reduce=False)
     case(9, 512, 256, 128, torch.float16, lda_pad=8, use_atomic_add=True)
