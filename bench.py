@@ -34,8 +34,9 @@ H, KVH, D, BS = 32, 8, 128, 16
 BATCH, CTX = 64, 4096
 METRIC = "paged-attn decode KV GB/s"
 # dram__bytes_read.sum + dram__bytes_write.sum of the split-K kernel + its reduce for one launch of this workload, from the
-# `ncu --set full` capture summarised in profiles/r01_ncu_full_paged_attention_v1_raw.csv (539.1 MB + 8.5 MB)
-NCU_TRAFFIC_BYTES = 547_600_000
+# `ncu --set full` captures summarised in profiles/r01_ncu_full_attention_final.txt (main kernel 539.1 MB read + 6.8 MB
+# written, reduce 4.3 MB read)
+NCU_TRAFFIC_BYTES = 550_200_000
 WORKLOAD = "C2: paged_attention_v2 Llama-3-8B shape 32q/8kv d128, fp8_e4m3 KV, block 16, batch 64 x ctx 4096"
 
 
