@@ -89,6 +89,23 @@ def reshape_and_cache(
     _ops()[1].reshape_and_cache(key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype, k_scale, v_scale)
 
 
+def reshape_and_cache_flash(key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                            slot_mapping: torch.Tensor, kv_cache_dtype: str, k_scale: torch.Tensor,
+                            v_scale: torch.Tensor) -> None:
+    """aphrodite/_custom_ops.py:1459-1473 (NHD caches [num_blocks, block_size, num_heads, head_size])."""
+    _ops()[1].reshape_and_cache_flash(key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype, k_scale, v_scale)
+
+
+def copy_blocks(key_caches, value_caches, block_mapping: torch.Tensor) -> None:
+    """aphrodite/_custom_ops.py:1489-1492."""
+    _ops()[1].copy_blocks(key_caches, value_caches, block_mapping)
+
+
+def swap_blocks(src: torch.Tensor, dst: torch.Tensor, block_mapping: torch.Tensor) -> None:
+    """aphrodite/_custom_ops.py:1499-1501 (block_mapping is a CPU tensor)."""
+    _ops()[1].swap_blocks(src, dst, block_mapping)
+
+
 def convert_fp8(output: torch.Tensor, input: torch.Tensor, scale: float = 1.0, kv_dtype: str = "fp8") -> None:
     _ops()[1].convert_fp8(output, input, scale, kv_dtype)
 

@@ -238,6 +238,111 @@ int launch_convert(void* dst, const void* src, int64_t n, float scale, int kv, i
   return APH_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// reshape_and_cache_flash (reference cache_kernels.cu:264-306,412-497): caches in the NHD layout
+// [num_blocks, block_size, num_heads, head_size]. A token's head row is contiguous on both sides, so every work
+// item is one 128-bit input vector of K or V -> one vector store (16 bytes, 8 for fp8 from 16-bit, 4 from f32).
+// ------------------------------------------------------------------------------------------------
+template <typename scalar_t, typename cache_t, int KV, bool VEC>
+__global__ void __launch_bounds__(256)
+    reshape_and_cache_flash_kernel(const scalar_t* __restrict__ key, const scalar_t* __restrict__ value,
+                                   cache_t* __restrict__ key_cache, cache_t* __restrict__ value_cache,
+                                   const int64_t* __restrict__ slot_mapping, int64_t key_stride, int64_t value_stride,
+                                   int64_t block_stride, int64_t page_stride, int64_t head_stride, int num_heads,
+                                   int head_size, int block_size, const float* __restrict__ k_scale,
+                                   const float* __restrict__ v_scale) {
+  constexpr int LV = VEC ? 16 / sizeof(scalar_t) : 1;
+  pdl_trigger();
+  pdl_wait();
+  const int64_t token = blockIdx.x;
+  const int64_t slot = slot_mapping[token];
+  if (slot < 0) return;
+  const int64_t base = (slot / block_size) * block_stride + (slot % block_size) * page_stride;
+  float ks = 1.f, vs = 1.f;
+  if constexpr (KV != APH_KV_AUTO) {
+    ks = *k_scale;
+    vs = *v_scale;
+  }
+  const int vec_per_head = head_size / LV;
+  const int items = num_heads * vec_per_head;
+  for (int w = blockIdx.y * blockDim.x + threadIdx.x; w < 2 * items; w += gridDim.y * blockDim.x) {
+    const bool is_v = w >= items;
+    const int i = is_v ? w - items : w;
+    const int h = i / vec_per_head, e0 = (i - h * vec_per_head) * LV;
+    const scalar_t* src = (is_v ? value + token * value_stride : key + token * key_stride) + h * head_size + e0;
+    cache_t* dst = (is_v ? value_cache : key_cache) + base + (int64_t)h * head_stride + e0;
+    const float sc = is_v ? vs : ks;
+    const Pack<scalar_t, LV> in = *reinterpret_cast<const Pack<scalar_t, LV>*>(src);
+    Pack<cache_t, LV> o;
+#pragma unroll
+    for (int e = 0; e < LV; ++e) {
+      if constexpr (KV == APH_KV_AUTO)
+        o.v[e] = in.v[e];
+      else
+        o.v[e] = fp8_encode<KV>(ScalarTraits<scalar_t>::to_float(in.v[e]), sc);
+    }
+    *reinterpret_cast<Pack<cache_t, LV>*>(dst) = o;
+  }
+}
+
+template <typename scalar_t, typename cache_t, int KV>
+int launch_reshape_and_cache_flash(const void* key, const void* value, void* key_cache, void* value_cache,
+                                   const int64_t* slot_mapping, int64_t num_tokens, int64_t key_stride,
+                                   int64_t value_stride, int64_t block_stride, int64_t page_stride, int64_t head_stride,
+                                   int num_heads, int head_size, int block_size, const float* k_scale,
+                                   const float* v_scale, cudaStream_t stream) {
+  constexpr int LV = 16 / sizeof(scalar_t);
+  constexpr int64_t CB = sizeof(cache_t);
+  const bool vec_ok = head_size % LV == 0 && aligned16(key) && aligned16(value) && aligned16(key_cache) &&
+                      aligned16(value_cache) && key_stride % LV == 0 && value_stride % LV == 0 &&
+                      (block_stride * CB) % 16 == 0 && (page_stride * CB) % 16 == 0 && (head_stride * CB) % 16 == 0;
+  const int items = 2 * num_heads * head_size / (vec_ok ? LV : 1);
+  int threads = 256, ysplit = 1;
+  while (threads > 32 && threads / 2 >= items) threads /= 2;
+  const int sms = sm_count();
+  while (num_tokens * ysplit < 2LL * sms && ysplit * threads < items) ysplit *= 2;
+  dim3 grid((unsigned)num_tokens, ysplit);
+  if (vec_ok)
+    APH_LAUNCH_PDL(reshape_and_cache_flash_kernel<scalar_t, cache_t, KV, true>, grid, dim3(threads), (size_t)0, stream,
+                   (const scalar_t*)key, (const scalar_t*)value, (cache_t*)key_cache, (cache_t*)value_cache, slot_mapping,
+                   key_stride, value_stride, block_stride, page_stride, head_stride, num_heads, head_size, block_size, k_scale,
+                   v_scale);
+  else
+    APH_LAUNCH_PDL(reshape_and_cache_flash_kernel<scalar_t, cache_t, KV, false>, grid, dim3(threads), (size_t)0, stream,
+                   (const scalar_t*)key, (const scalar_t*)value, (cache_t*)key_cache, (cache_t*)value_cache, slot_mapping,
+                   key_stride, value_stride, block_stride, page_stride, head_stride, num_heads, head_size, block_size, k_scale,
+                   v_scale);
+  return APH_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// copy_blocks (reference cache_kernels.cu:71-170): for every layer and every (src, dst) pair copy one block of the
+// key cache and of the value cache. Blocks are whole multiples of 16 bytes in every supported layout: 128-bit
+// copies, the block split over gridDim.z CTAs when there are few (layer, pair) units.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    copy_blocks_kernel(const int64_t* __restrict__ key_ptrs, const int64_t* __restrict__ value_ptrs,
+                       const int64_t* __restrict__ block_mapping, int64_t block_bytes, int vec16) {
+  pdl_trigger();
+  pdl_wait();
+  const int layer = blockIdx.x, pair = blockIdx.y;
+  const int64_t src_blk = block_mapping[2 * pair], dst_blk = block_mapping[2 * pair + 1];
+#pragma unroll
+  for (int kv = 0; kv < 2; ++kv) {
+    uint8_t* base = reinterpret_cast<uint8_t*>(kv == 0 ? key_ptrs[layer] : value_ptrs[layer]);
+    const uint8_t* src = base + src_blk * block_bytes;
+    uint8_t* dst = base + dst_blk * block_bytes;
+    if (vec16) {
+      const int64_t n = block_bytes / 16;
+      for (int64_t i = blockIdx.z * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.z * blockDim.x)
+        reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(src)[i];
+    } else {
+      for (int64_t i = blockIdx.z * (int64_t)blockDim.x + threadIdx.x; i < block_bytes; i += (int64_t)gridDim.z * blockDim.x)
+        dst[i] = src[i];
+    }
+  }
+}
+
 }  // namespace
 }  // namespace aphb200
 
@@ -291,4 +396,71 @@ extern "C" int aph_convert_fp8(void* dst, const void* src, int64_t n, float scal
     case APH_DT_BF16: return launch_convert<__nv_bfloat16>(dst, src, n, scale, kv_dtype, direction, s);
     default: return set_error(APH_ERR_INVALID_ARGUMENT, "convert_fp8: unsupported dtype %d", dtype);
   }
+}
+
+extern "C" int aph_reshape_and_cache_flash(const void* key, const void* value, void* key_cache, void* value_cache,
+                                           const int64_t* slot_mapping, int64_t num_tokens, int64_t key_stride,
+                                           int64_t value_stride, int64_t block_stride, int64_t page_stride,
+                                           int64_t head_stride, int num_heads, int head_size, int block_size, int dtype,
+                                           int kv_dtype, const float* k_scale, const float* v_scale, void* stream) {
+  APH_CHECK(num_tokens >= 0 && num_heads > 0 && head_size > 0 && block_size > 0, APH_ERR_INVALID_ARGUMENT,
+            "reshape_and_cache_flash: bad sizes");
+  APH_CHECK(kv_dtype == APH_KV_AUTO || (k_scale && v_scale), APH_ERR_INVALID_ARGUMENT,
+            "reshape_and_cache_flash: fp8 kv cache needs k_scale and v_scale");
+  if (num_tokens == 0) return APH_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+#define APH_RCF(SC, CT, KVC)                                                                                             \
+  return launch_reshape_and_cache_flash<SC, CT, KVC>(key, value, key_cache, value_cache, slot_mapping, num_tokens,       \
+                                                     key_stride, value_stride, block_stride, page_stride, head_stride,   \
+                                                     num_heads, head_size, block_size, k_scale, v_scale, s)
+#define APH_RCF_DT(SC)                                                  \
+  switch (kv_dtype) {                                                   \
+    case APH_KV_AUTO: APH_RCF(SC, SC, APH_KV_AUTO);                     \
+    case APH_KV_FP8_E4M3: APH_RCF(SC, uint8_t, APH_KV_FP8_E4M3);        \
+    case APH_KV_FP8_E5M2: APH_RCF(SC, uint8_t, APH_KV_FP8_E5M2);        \
+    default: break;                                                     \
+  }
+  switch (dtype) {
+    case APH_DT_F32: APH_RCF_DT(float); break;
+    case APH_DT_F16: APH_RCF_DT(__half); break;
+    case APH_DT_BF16: APH_RCF_DT(__nv_bfloat16); break;
+    default: break;
+  }
+#undef APH_RCF_DT
+#undef APH_RCF
+  return set_error(APH_ERR_INVALID_ARGUMENT, "reshape_and_cache_flash: unsupported dtype %d / kv cache dtype %d", dtype,
+                   kv_dtype);
+}
+
+extern "C" int aph_copy_blocks(const int64_t* key_cache_ptrs, const int64_t* value_cache_ptrs, const int64_t* block_mapping,
+                               int num_layers, int64_t num_pairs, int64_t block_bytes, void* stream) {
+  APH_CHECK(num_layers >= 0 && num_pairs >= 0 && block_bytes > 0, APH_ERR_INVALID_ARGUMENT, "copy_blocks: bad sizes");
+  APH_CHECK(num_pairs <= 65535, APH_ERR_UNSUPPORTED, "copy_blocks: more than 65535 block pairs in one call");
+  if (num_layers == 0 || num_pairs == 0) return APH_OK;
+  const int64_t units = (int64_t)num_layers * num_pairs;
+  int zsplit = 1;
+  while (units * zsplit < 2LL * sm_count() && (int64_t)zsplit * 256 * 16 * 4 < block_bytes && zsplit < 64) zsplit *= 2;
+  dim3 grid((unsigned)num_layers, (unsigned)num_pairs, (unsigned)zsplit);
+  APH_LAUNCH_PDL(copy_blocks_kernel, grid, dim3(256), (size_t)0, (cudaStream_t)stream, key_cache_ptrs, value_cache_ptrs,
+                 block_mapping, block_bytes, (int)(block_bytes % 16 == 0));
+  return APH_OK;
+}
+
+// swap_blocks (reference cache_kernels.cu:25-67): block copies between two caches (device<->device, device<->host)
+// driven by a HOST list of (src, dst) pairs. Runs of pairs that are consecutive on both sides become one copy.
+extern "C" int aph_swap_blocks(const void* src, void* dst, const int64_t* block_mapping_host, int64_t num_pairs,
+                               int64_t block_bytes, int kind, void* stream) {
+  APH_CHECK(num_pairs >= 0 && block_bytes > 0, APH_ERR_INVALID_ARGUMENT, "swap_blocks: bad sizes");
+  APH_CHECK(kind == 0 || kind == 1 || kind == 2, APH_ERR_INVALID_ARGUMENT, "swap_blocks: kind must be 0 (d2d), 1 (d2h) or 2 (h2d)");
+  const cudaMemcpyKind mk = kind == 0 ? cudaMemcpyDeviceToDevice : kind == 1 ? cudaMemcpyDeviceToHost : cudaMemcpyHostToDevice;
+  for (int64_t i = 0; i < num_pairs;) {
+    const int64_t s0 = block_mapping_host[2 * i], d0 = block_mapping_host[2 * i + 1];
+    int64_t run = 1;
+    while (i + run < num_pairs && block_mapping_host[2 * (i + run)] == s0 + run && block_mapping_host[2 * (i + run) + 1] == d0 + run) ++run;
+    const cudaError_t e = cudaMemcpyAsync(static_cast<char*>(dst) + d0 * block_bytes, static_cast<const char*>(src) + s0 * block_bytes,
+                                          (size_t)(run * block_bytes), mk, (cudaStream_t)stream);
+    APH_CHECK(e == cudaSuccess, APH_ERR_CUDA, "swap_blocks: cudaMemcpyAsync failed: %s", cudaGetErrorString(e));
+    i += run;
+  }
+  return APH_OK;
 }

@@ -19,6 +19,7 @@
 
 #include <optional>
 #include <string>
+#include <vector>
 
 #include "../../include/aphrodite_b200.h"
 
@@ -184,6 +185,84 @@ void convert_fp8(torch::Tensor& dst_cache, torch::Tensor& src_cache, const doubl
 }
 
 // argument checks of the reference entry point, gptq_marlin.cu:2271-2332
+// ---- the rest of cache_kernels.cu a block manager calls ----
+void reshape_and_cache_flash(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache, torch::Tensor& value_cache,
+                             torch::Tensor& slot_mapping, const std::string& kv_cache_dtype, torch::Tensor& k_scale,
+                             torch::Tensor& v_scale) {
+  const char* op = "reshape_and_cache_flash";
+  TORCH_CHECK(key.is_cuda() && value.is_cuda() && key_cache.is_cuda() && value_cache.is_cuda(), op,
+              ": tensors must be on a CUDA device");
+  TORCH_CHECK(key.dim() == 3 && value.dim() == 3 && key_cache.dim() == 4 && value_cache.dim() == 4, op, ": bad tensor ranks");
+  TORCH_CHECK(key.stride(2) == 1 && key.stride(1) == key.size(2) && value.stride(2) == 1 && value.stride(1) == value.size(2), op,
+              ": key/value heads must be contiguous");
+  TORCH_CHECK(key_cache.stride(3) == 1 && value_cache.stride(3) == 1, op, ": cache head rows must be contiguous");
+  // reference: TORCH_CHECK(key_cache.stride(0) == value_cache.stride(0)) (cache_kernels.cu:438)
+  TORCH_CHECK(key_cache.stride(0) == value_cache.stride(0) && key_cache.stride(1) == value_cache.stride(1) &&
+                  key_cache.stride(2) == value_cache.stride(2),
+              op, ": key_cache and value_cache must share their strides");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long && slot_mapping.is_contiguous(), op,
+              ": slot_mapping must be contiguous int64");
+  TORCH_CHECK(k_scale.scalar_type() == at::ScalarType::Float && v_scale.scalar_type() == at::ScalarType::Float, op,
+              ": k_scale / v_scale must be float32 tensors");
+  const at::cuda::OptionalCUDAGuard guard(device_of(key));
+  // reference: num_tokens = slot_mapping.size(0) - with padding key.size(0) can be larger (cache_kernels.cu:423-431)
+  const int st = aph_reshape_and_cache_flash(
+      key.data_ptr(), value.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(), slot_mapping.data_ptr<int64_t>(),
+      slot_mapping.size(0), key.stride(0), value.stride(0), key_cache.stride(0), key_cache.stride(1), key_cache.stride(2),
+      (int)key.size(1), (int)key.size(2), (int)key_cache.size(1), dtype_code(key, op), kv_code(kv_cache_dtype),
+      k_scale.data_ptr<float>(), v_scale.data_ptr<float>(), stream_of());
+  check_status(st, op);
+}
+
+void copy_blocks(std::vector<torch::Tensor> const& key_caches, std::vector<torch::Tensor> const& value_caches,
+                 const torch::Tensor& block_mapping) {
+  const char* op = "copy_blocks";
+  const int64_t num_layers = (int64_t)key_caches.size();
+  TORCH_CHECK(num_layers == (int64_t)value_caches.size(), op, ": key_caches and value_caches differ in length");
+  if (num_layers == 0) return;
+  const torch::Device dev = key_caches[0].device();
+  TORCH_CHECK(dev.is_cuda(), op, ": caches must be on a CUDA device");
+  TORCH_CHECK(block_mapping.is_cuda() && block_mapping.scalar_type() == at::ScalarType::Long && block_mapping.dim() == 2 &&
+                  block_mapping.size(1) == 2 && block_mapping.is_contiguous(),
+              op, ": block_mapping must be a contiguous int64 [num_pairs, 2] tensor on the device");
+  std::vector<int64_t> ptrs(2 * num_layers);
+  for (int64_t l = 0; l < num_layers; ++l) {
+    ptrs[l] = reinterpret_cast<int64_t>(key_caches[l].data_ptr());
+    ptrs[num_layers + l] = reinterpret_cast<int64_t>(value_caches[l].data_ptr());
+  }
+  // one upload for both pointer tables (the reference uploads two, synchronously: cache_kernels.cu:148-156)
+  torch::Tensor ptrs_d = torch::from_blob(ptrs.data(), {2 * num_layers}, torch::kInt64).to(dev);
+  const at::cuda::OptionalCUDAGuard guard(dev);
+  const int64_t block_bytes = key_caches[0][0].numel() * key_caches[0].element_size();
+  const int st = aph_copy_blocks(ptrs_d.data_ptr<int64_t>(), ptrs_d.data_ptr<int64_t>() + num_layers, block_mapping.data_ptr<int64_t>(),
+                                 (int)num_layers, block_mapping.size(0), block_bytes, stream_of());
+  check_status(st, op);
+}
+
+void swap_blocks(torch::Tensor& src, torch::Tensor& dst, const torch::Tensor& block_mapping) {
+  const char* op = "swap_blocks";
+  int kind;
+  if (src.is_cuda() && dst.is_cuda()) {
+    TORCH_CHECK(src.device().index() == dst.device().index(), "src and dst must be on the same GPU");
+    kind = 0;
+  } else if (src.is_cuda() && dst.is_cpu()) {
+    kind = 1;
+  } else if (src.is_cpu() && dst.is_cuda()) {
+    kind = 2;
+  } else {
+    TORCH_CHECK(false, "Invalid device combination");
+  }
+  TORCH_CHECK(block_mapping.device().is_cpu(), "block_mapping must be on CPU");
+  TORCH_CHECK(block_mapping.scalar_type() == at::ScalarType::Long && block_mapping.dim() == 2 && block_mapping.size(1) == 2, op,
+              ": block_mapping must be int64 [num_pairs, 2]");
+  const torch::Tensor bm = block_mapping.contiguous();
+  const at::cuda::OptionalCUDAGuard guard(src.is_cuda() ? src.device() : dst.device());
+  // the stride, not numel: the blocks (padding included) are contiguous (cache_kernels.cu:50-53)
+  const int64_t block_bytes = src.element_size() * src.stride(0);
+  const int st = aph_swap_blocks(src.data_ptr(), dst.data_ptr(), bm.data_ptr<int64_t>(), bm.size(0), block_bytes, kind, stream_of());
+  check_status(st, op);
+}
+
 void check_gemm_args(const torch::Tensor& a, const torch::Tensor& b_q_weight, const torch::Tensor& b_scales,
                      const torch::Tensor& workspace, int64_t size_m, int64_t size_n, int64_t size_k) {
   const char* op = "gptq_marlin_gemm";
@@ -273,6 +352,18 @@ TORCH_LIBRARY_FRAGMENT(_C_cache_ops, ops) {
   ops.def(
       "convert_fp8(Tensor! dst_cache, Tensor src_cache, float scale, "
       "str kv_cache_dtype) -> ()");
+  // kernels/torch_bindings.cpp:680-713
+  ops.def("swap_blocks(Tensor src, Tensor! dst, Tensor block_mapping) -> ()");
+  ops.def(
+      "copy_blocks(Tensor(a!)[] key_caches, Tensor[](b!) value_caches, "
+      "Tensor block_mapping) -> ()");
+  ops.def(
+      "reshape_and_cache_flash(Tensor key, Tensor value,"
+      "                        Tensor! key_cache,"
+      "                        Tensor! value_cache,"
+      "                        Tensor slot_mapping,"
+      "                        str kv_cache_dtype,"
+      "                        Tensor k_scale, Tensor v_scale) -> ()");
 }
 #endif
 
@@ -284,4 +375,7 @@ TORCH_LIBRARY_IMPL(_C, CUDA, ops) {
 TORCH_LIBRARY_IMPL(_C_cache_ops, CUDA, ops) {
   ops.impl("reshape_and_cache", &reshape_and_cache);
   ops.impl("convert_fp8", &convert_fp8);
+  ops.impl("swap_blocks", &swap_blocks);
+  ops.impl("copy_blocks", &copy_blocks);
+  ops.impl("reshape_and_cache_flash", &reshape_and_cache_flash);
 }

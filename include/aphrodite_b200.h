@@ -75,6 +75,29 @@ int aph_convert_fp8(void* dst, const void* src, int64_t n, float scale, int dtyp
                     int direction, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * The rest of kernels/cache_kernels.cu that a block manager calls.
+ *
+ * reshape_and_cache_flash - replaces cache_kernels.cu:412-497 (kernel :264-306). Caches in the NHD layout
+ *   key_cache, value_cache [num_blocks, block_size, num_heads, head_size]; block_stride / page_stride / head_stride
+ *   are the cache strides of dims 0 / 1 / 2 in ELEMENTS (the caller may pass a padded or sliced cache).
+ *   Bit-exact with the reference, including the FP8 bytes.
+ * copy_blocks - replaces cache_kernels.cu:113-170 (kernel :71-93). key_cache_ptrs / value_cache_ptrs: DEVICE arrays of
+ *   num_layers cache base addresses; block_mapping: DEVICE int64 [num_pairs, 2] (src block, dst block);
+ *   block_bytes = bytes of one block (stride of dim 0 in bytes). Copies both caches of every layer.
+ * swap_blocks - replaces cache_kernels.cu:25-67. block_mapping_host: HOST int64 [num_pairs, 2]; kind 0 = device to
+ *   device, 1 = device to host, 2 = host to device; asynchronous copies on `stream`, consecutive pairs merged.
+ * ------------------------------------------------------------------------------------------- */
+int aph_reshape_and_cache_flash(const void* key, const void* value, void* key_cache, void* value_cache,
+                                const int64_t* slot_mapping, int64_t num_tokens, int64_t key_stride,
+                                int64_t value_stride, int64_t block_stride, int64_t page_stride, int64_t head_stride,
+                                int num_heads, int head_size, int block_size, int dtype, int kv_dtype,
+                                const float* k_scale, const float* v_scale, void* stream);
+int aph_copy_blocks(const int64_t* key_cache_ptrs, const int64_t* value_cache_ptrs, const int64_t* block_mapping,
+                    int num_layers, int64_t num_pairs, int64_t block_bytes, void* stream);
+int aph_swap_blocks(const void* src, void* dst, const int64_t* block_mapping_host, int64_t num_pairs,
+                    int64_t block_bytes, int kind, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * paged attention - replaces kernels/attention/paged_attention_v1.cu:170-192 and
  * paged_attention_v2.cu:176-201 (kernel attention_kernels.cuh:86-495, reduce :563-668).
  * One implementation serves both entry points: a GQA-packed split-K kernel whose partition

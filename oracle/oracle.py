@@ -142,3 +142,34 @@ def refcuda():
         torch.ops.load_library(path)
         _refcuda = torch.ops._refcuda
     return _refcuda
+
+
+# ---- the rest of kernels/cache_kernels.cu: index restatements in torch on the CPU ----
+def reshape_and_cache_flash(key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype, k_scale, v_scale):
+    """In-place on NHD caches [num_blocks, block_size, num_heads, head_size] (CPU tensors). Follows
+    cache_kernels.cu:264-306: slot < 0 skipped, block = slot / block_size, offset = slot % block_size,
+    cache[block, offset, h, e] = cvt(key[t, h, e]); the FP8 conversion is the write codec (fp8_encode)."""
+    bs = key_cache.shape[1]
+    if kv_cache_dtype != "auto":
+        key = fp8_encode(key.contiguous(), float(k_scale), kv_cache_dtype)
+        value = fp8_encode(value.contiguous(), float(v_scale), kv_cache_dtype)
+    for t in range(slot_mapping.numel()):  # num_tokens = slot_mapping.size(0) (cache_kernels.cu:423-431)
+        slot = int(slot_mapping[t])
+        if slot < 0:
+            continue
+        key_cache[slot // bs, slot % bs] = key[t]
+        value_cache[slot // bs, slot % bs] = value[t]
+
+
+def copy_blocks(key_caches, value_caches, block_mapping):
+    """cache_kernels.cu:71-93: for every layer and (src, dst) pair, in list order, dst block = src block."""
+    for kc, vc in zip(key_caches, value_caches):
+        for src, dst in block_mapping.tolist():
+            kc[dst] = kc[src].clone()
+            vc[dst] = vc[src].clone()
+
+
+def swap_blocks(src, dst, block_mapping):
+    """cache_kernels.cu:25-67: dst[dst_block] = src[src_block] for every pair (whole blocks, padding included)."""
+    for s, d in block_mapping.tolist():
+        dst[d] = src[s]

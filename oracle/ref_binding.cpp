@@ -11,6 +11,7 @@
 #include <torch/library.h>
 #include <optional>
 #include <string>
+#include <vector>
 
 void paged_attention_v1(
     torch::Tensor& out, torch::Tensor& query, torch::Tensor& key_cache,
@@ -41,7 +42,16 @@ void reshape_and_cache(torch::Tensor& key, torch::Tensor& value,
                        const std::string& kv_cache_dtype,
                        torch::Tensor& k_scale, torch::Tensor& v_scale);
 
+// kernels/cpu/cache.cpp:136-152 (block_mapping: int64 [num_pairs, 2])
+void copy_blocks(std::vector<torch::Tensor> const& key_caches,
+                 std::vector<torch::Tensor> const& value_caches,
+                 const torch::Tensor& block_mapping);
+
 TORCH_LIBRARY(_refcpu, ops) {
+  ops.def(
+      "copy_blocks(Tensor(a!)[] key_caches, Tensor[](b!) value_caches, "
+      "Tensor block_mapping) -> ()");
+  ops.impl("copy_blocks", torch::kCPU, &copy_blocks);
   ops.def(
       "paged_attention_v1("
       "    Tensor! out, Tensor query, Tensor key_cache,"

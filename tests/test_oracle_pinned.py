@@ -138,3 +138,21 @@ def test_gemm_oracle():
     w = synth.tensor((64, 32), 12, torch.bfloat16, 1.0)
     c = oracle.gemm(a, w)
     assert torch.allclose(c, a.double() @ w.double(), atol=1e-12)
+
+
+def test_copy_blocks_oracle_vs_live_reference_cpu():
+    """oracle.copy_blocks against the UNMODIFIED reference CPU backend (kernels/cpu/cache.cpp:136-152), bit-exact."""
+    ref = oracle.refcpu()
+    if ref is None or not hasattr(ref, "copy_blocks"):
+        pytest.skip("oracle/_ref not built")
+    layers, nb = 3, 24
+    kcs = [synth.tensor((nb, 4, 8, 16, 8), 70 + l, torch.bfloat16, 1.0) for l in range(layers)]
+    vcs = [synth.tensor((nb, 4, 64, 16), 80 + l, torch.bfloat16, 1.0) for l in range(layers)]
+    mapping = torch.tensor([[1, 20], [5, 21], [1, 22], [7, 3]], dtype=torch.int64)
+    ka, va = [t.clone() for t in kcs], [t.clone() for t in vcs]
+    kb, vb = [t.clone() for t in kcs], [t.clone() for t in vcs]
+    oracle.copy_blocks(ka, va, mapping)
+    ref.copy_blocks(kb, vb, mapping)
+    for l in range(layers):
+        assert torch.equal(ka[l].view(torch.int16), kb[l].view(torch.int16))
+        assert torch.equal(va[l].view(torch.int16), vb[l].view(torch.int16))
