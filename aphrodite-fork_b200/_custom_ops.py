@@ -131,3 +131,36 @@ def gptq_marlin_gemm(a: torch.Tensor,
     return _ops()[0].gptq_marlin_gemm(a, b_q_weight, b_scales, b_zeros, g_idx, perm, workspace, type_id, size_m,
                                       size_n, size_k, is_k_full, has_zp, use_atomic_add, use_fp32_reduce,
                                       is_zp_float)
+
+
+# aphrodite/_custom_ops.py:868-878 (checkpoint format -> Marlin wire format, run once per weight at load)
+def gptq_marlin_repack(b_q_weight: torch.Tensor, perm: torch.Tensor, size_k: int, size_n: int,
+                       num_bits: int) -> torch.Tensor:
+    return _ops()[0].gptq_marlin_repack(b_q_weight, perm, size_k, size_n, num_bits)
+
+
+def awq_marlin_repack(b_q_weight: torch.Tensor, size_k: int, size_n: int, num_bits: int) -> torch.Tensor:
+    return _ops()[0].awq_marlin_repack(b_q_weight, size_k, size_n, num_bits)
+
+
+# aphrodite/_custom_ops.py:881-906: one repack per expert, same loop as the reference
+def gptq_marlin_moe_repack(b_q_weight: torch.Tensor, perm: torch.Tensor, size_k: int, size_n: int,
+                           num_bits: int) -> torch.Tensor:
+    num_experts = b_q_weight.shape[0]
+    assert size_k % 16 == 0
+    output = torch.empty((num_experts, size_k // 16, size_n * (num_bits // 2)), device=b_q_weight.device,
+                         dtype=b_q_weight.dtype)
+    for e in range(num_experts):
+        output[e] = gptq_marlin_repack(b_q_weight[e], perm[e], size_k, size_n, num_bits)
+    return output
+
+
+def awq_marlin_moe_repack(b_q_weight: torch.Tensor, perm: torch.Tensor, size_k: int, size_n: int,
+                          num_bits: int) -> torch.Tensor:
+    num_experts = b_q_weight.shape[0]
+    assert size_k % 16 == 0
+    output = torch.empty((num_experts, size_k // 16, size_n * (num_bits // 2)), device=b_q_weight.device,
+                         dtype=b_q_weight.dtype)
+    for e in range(num_experts):
+        output[e] = awq_marlin_repack(b_q_weight[e], size_k, size_n, num_bits)
+    return output

@@ -308,6 +308,53 @@ torch::Tensor gptq_marlin_gemm(torch::Tensor& a, torch::Tensor& b_q_weight, torc
   return c;
 }
 
+// kernels/quantization/gptq_marlin/gptq_marlin_repack.cu:236-322 (same checks, same output shape)
+torch::Tensor gptq_marlin_repack(torch::Tensor& b_q_weight, torch::Tensor& perm, int64_t size_k, int64_t size_n,
+                                 int64_t num_bits) {
+  const char* op = "gptq_marlin_repack";
+  TORCH_CHECK(num_bits == 4 || num_bits == 8, "num_bits must be 4 or 8. Got = ", num_bits);
+  const int64_t pack = 32 / num_bits;
+  TORCH_CHECK(size_k % 16 == 0, "size_k = ", size_k, " is not divisible by tile_k_size = ", 16);
+  TORCH_CHECK(size_n % 64 == 0, "size_n = ", size_n, " is not divisible by tile_n_size = ", 64);
+  TORCH_CHECK(b_q_weight.dim() == 2 && b_q_weight.size(0) == size_k / pack, "Shape mismatch: b_q_weight.size(0) = ",
+              b_q_weight.size(0), ", size_k = ", size_k, ", pack_factor = ", pack);
+  TORCH_CHECK(b_q_weight.size(1) == size_n, "b_q_weight.size(1) = ", b_q_weight.size(1), " is not size_n = ", size_n);
+  TORCH_CHECK(b_q_weight.is_cuda(), "b_q_weight is not on GPU");
+  TORCH_CHECK(b_q_weight.is_contiguous(), "b_q_weight is not contiguous");
+  TORCH_CHECK(b_q_weight.scalar_type() == at::ScalarType::Int, "expected b_q_weight to be type int");
+  TORCH_CHECK(perm.is_cuda(), "perm is not on GPU");
+  TORCH_CHECK(perm.is_contiguous(), "perm is not contiguous");
+  TORCH_CHECK(perm.scalar_type() == at::ScalarType::Int, "expected perm type int");
+  TORCH_CHECK(perm.numel() == 0 || perm.numel() == size_k, "perm.size(0) = ", perm.numel(), " is not size_k = ", size_k);
+  const at::cuda::OptionalCUDAGuard guard(device_of(b_q_weight));
+  torch::Tensor out = torch::empty({size_k / 16, size_n * 16 / pack}, b_q_weight.options());
+  const int32_t* pm = perm.numel() > 0 ? perm.data_ptr<int32_t>() : nullptr;
+  check_status(aph_gptq_marlin_repack(out.data_ptr<int32_t>(), b_q_weight.data_ptr<int32_t>(), pm, size_k, size_n,
+                                      (int)num_bits, stream_of()), op);
+  return out;
+}
+
+// kernels/quantization/gptq_marlin/awq_marlin_repack.cu:189-268
+torch::Tensor awq_marlin_repack(torch::Tensor& b_q_weight, int64_t size_k, int64_t size_n, int64_t num_bits) {
+  const char* op = "awq_marlin_repack";
+  TORCH_CHECK(num_bits == 4 || num_bits == 8, "num_bits must be 4 or 8. Got = ", num_bits);
+  const int64_t pack = 32 / num_bits;
+  TORCH_CHECK(size_k % 16 == 0, "size_k = ", size_k, " is not divisible by tile_k_size = ", 16);
+  TORCH_CHECK(size_n % 64 == 0, "size_n = ", size_n, " is not divisible by tile_n_size = ", 64);
+  TORCH_CHECK(b_q_weight.dim() == 2 && b_q_weight.size(0) == size_k, "b_q_weight.size(0) = ", b_q_weight.size(0),
+              " is not size_k = ", size_k);
+  TORCH_CHECK(b_q_weight.size(1) == size_n / pack, "Shape mismatch: b_q_weight.size(1) = ", b_q_weight.size(1),
+              ", size_n = ", size_n, ", pack_factor = ", pack);
+  TORCH_CHECK(b_q_weight.is_cuda(), "b_q_weight is not on GPU");
+  TORCH_CHECK(b_q_weight.is_contiguous(), "b_q_weight is not contiguous");
+  TORCH_CHECK(b_q_weight.scalar_type() == at::ScalarType::Int, "expected b_q_weight to be type int");
+  const at::cuda::OptionalCUDAGuard guard(device_of(b_q_weight));
+  torch::Tensor out = torch::empty({size_k / 16, size_n * 16 / pack}, b_q_weight.options());
+  check_status(aph_awq_marlin_repack(out.data_ptr<int32_t>(), b_q_weight.data_ptr<int32_t>(), size_k, size_n,
+                                     (int)num_bits, stream_of()), op);
+  return out;
+}
+
 }  // namespace
 
 #ifdef APH_DEFINE_SCHEMAS
@@ -341,6 +388,13 @@ TORCH_LIBRARY_FRAGMENT(_C, ops) {
       "bool has_zp, bool use_atomic_add, bool use_fp32_reduce, "
       "bool is_zp_float) -> Tensor",
       {at::Tag::needs_fixed_stride_order});
+  // kernels/torch_bindings.cpp:337-347
+  ops.def(
+      "gptq_marlin_repack(Tensor b_q_weight, Tensor perm, "
+      "SymInt size_k, SymInt size_n, int num_bits) -> Tensor");
+  ops.def(
+      "awq_marlin_repack(Tensor b_q_weight, SymInt size_k, "
+      "SymInt size_n, int num_bits) -> Tensor");
 }
 TORCH_LIBRARY_FRAGMENT(_C_cache_ops, ops) {
   ops.def(
@@ -371,6 +425,8 @@ TORCH_LIBRARY_IMPL(_C, CUDA, ops) {
   ops.impl("paged_attention_v1", &paged_attention_v1);
   ops.impl("paged_attention_v2", &paged_attention_v2);
   ops.impl("gptq_marlin_gemm", &gptq_marlin_gemm);
+  ops.impl("gptq_marlin_repack", &gptq_marlin_repack);
+  ops.impl("awq_marlin_repack", &awq_marlin_repack);
 }
 TORCH_LIBRARY_IMPL(_C_cache_ops, CUDA, ops) {
   ops.impl("reshape_and_cache", &reshape_and_cache);

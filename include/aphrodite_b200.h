@@ -160,6 +160,20 @@ int aph_gptq_marlin_gemm(void* c, const void* a, const void* b_q_weight, const v
                          int use_atomic_add, int use_fp32_reduce, int is_zp_float, int dtype, void* scratch,
                          size_t scratch_bytes, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Marlin repack - replaces kernels/quantization/gptq_marlin/gptq_marlin_repack.cu:236-322 and
+ * awq_marlin_repack.cu:189-268: checkpoint formats -> the Marlin wire format gptq_marlin_gemm reads.
+ *   out         [size_k / 16, size_n * 16 / pack] int32, pack = 32 / num_bits (4 or 8 bits)
+ *   GPTQ input  [size_k / pack, size_n] int32 (packed along k); perm: int32 [size_k] act-order row order
+ *               (output row k reads input row perm[k]) or NULL
+ *   AWQ input   [size_k, size_n / pack] int32 (packed along n with AWQ's column interleave)
+ * size_k % 16 == 0 and size_n % 64 == 0. Bit-identical with the reference kernels.
+ * ------------------------------------------------------------------------------------------- */
+int aph_gptq_marlin_repack(int32_t* out, const int32_t* b_q_weight, const int32_t* perm, int64_t size_k,
+                           int64_t size_n, int num_bits, void* stream);
+int aph_awq_marlin_repack(int32_t* out, const int32_t* b_q_weight, int64_t size_k, int64_t size_n, int num_bits,
+                          void* stream);
+
 #ifdef __cplusplus
 }
 #endif

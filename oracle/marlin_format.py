@@ -11,6 +11,9 @@ What each function follows (paths relative to /root/reference):
   pack_zero_points             aphrodite/quantization/utils/marlin_utils.py:246-265
   quantize                     aphrodite/quantization/utils/quant_utils.py:242-329
   scalar type ids              aphrodite/scalar_type.py:133-159
+  gptq_pack / awq_pack         aphrodite/quantization/utils/quant_utils.py:461-569
+  gptq/awq_marlin_repack       kernels/quantization/gptq_marlin/gptq_marlin_repack.cu:236-322,
+                               awq_marlin_repack.cu:189-268; contract from tests/kernels/test_marlin_gemm.py:66-176
 
 The layout is restated as closed-form index arithmetic (not as the reference's list
 building), and the inverse maps (unpack_*) are derived here: they are what the GPU kernel's
@@ -96,6 +99,65 @@ def unpack_weights(b: np.ndarray, size_k: int, size_n: int, num_bits: int) -> np
     inv = np.argsort(weight_perm(num_bits))
     t = t.reshape(-1, 1024)[:, inv].reshape(t.shape)
     return t.reshape(size_k // TILE, size_n // TILE, TILE, TILE).transpose(0, 2, 1, 3).reshape(size_k, size_n)
+
+
+def gptq_pack(q: np.ndarray, num_bits: int) -> np.ndarray:
+    """GPTQ checkpoint format: q [K,N] -> [K/pack, N] int32, row pack*r+i in bits [num_bits*i, ...)."""
+    pack = 32 // num_bits
+    u = np.asarray(q, dtype=np.uint32)
+    out = np.zeros((u.shape[0] // pack, u.shape[1]), dtype=np.uint32)
+    for i in range(pack):
+        out |= u[i::pack, :] << np.uint32(num_bits * i)
+    return out.astype(np.int32)
+
+
+def gptq_unpack(w: np.ndarray, num_bits: int) -> np.ndarray:
+    pack = 32 // num_bits
+    u = np.asarray(w).astype(np.uint32)
+    q = np.zeros((u.shape[0] * pack, u.shape[1]), dtype=np.uint32)
+    for i in range(pack):
+        q[i::pack, :] = (u >> np.uint32(num_bits * i)) & np.uint32((1 << num_bits) - 1)
+    return q
+
+
+def awq_pack(q: np.ndarray, num_bits: int) -> np.ndarray:
+    """AWQ checkpoint format: q [K,N] -> [K, N/pack] int32; bit position i of a word holds column
+    pack*(n/pack) + interleave[i]."""
+    pack = 32 // num_bits
+    u = np.asarray(q, dtype=np.uint32)
+    k, n = u.shape
+    u = u.reshape(k, n // pack, pack)[:, :, _interleave(num_bits)]
+    out = np.zeros((k, n // pack), dtype=np.uint32)
+    for i in range(pack):
+        out |= u[:, :, i] << np.uint32(num_bits * i)
+    return out.astype(np.int32)
+
+
+def awq_unpack(w: np.ndarray, num_bits: int) -> np.ndarray:
+    pack = 32 // num_bits
+    u = np.asarray(w).astype(np.uint32)
+    k, nw = u.shape
+    q = np.zeros((k, nw, pack), dtype=np.uint32)
+    il = _interleave(num_bits)
+    for i in range(pack):
+        q[:, :, il[i]] = (u >> np.uint32(num_bits * i)) & np.uint32((1 << num_bits) - 1)
+    return q.reshape(k, nw * pack)
+
+
+def gptq_marlin_repack(w: np.ndarray, perm, size_k: int, size_n: int, num_bits: int) -> np.ndarray:
+    """What the repack kernel must produce: the Marlin packing of the unpacked matrix, rows taken in `perm`
+    order when act-order sort indices are given (test_marlin_gemm.py:97-118)."""
+    q = gptq_unpack(w, num_bits)
+    assert q.shape == (size_k, size_n), q.shape
+    if perm is not None and len(perm) > 0:
+        q = q[np.asarray(perm, dtype=np.int64), :]
+    return pack_weights(q, num_bits)
+
+
+def awq_marlin_repack(w: np.ndarray, size_k: int, size_n: int, num_bits: int) -> np.ndarray:
+    q = awq_unpack(w, num_bits)
+    assert q.shape == (size_k, size_n), q.shape
+    return pack_weights(q, num_bits)
 
 
 def _scale_perms():

@@ -118,6 +118,33 @@ def make_marlin(st, qu, mu, mt):
     print("marlin_golden.npz:", len(out), "arrays")
 
 
+def make_repack(st, qu, mu, mt):
+    """Checkpoint formats and the Marlin packing they must repack to, all from the reference's Python
+    (quant_utils.gptq_pack / awq_pack / sort_weights, marlin_utils_test.marlin_weights): the contract of
+    tests/kernels/test_marlin_gemm.py:66-176."""
+    out = {}
+    g = torch.Generator().manual_seed(1)
+    # (K, N, bits, act_order)
+    cases = [(128, 64, 4, False), (256, 192, 4, True), (128, 128, 8, False), (256, 64, 8, True), (64, 256, 4, False)]
+    for ci, (k, n, bits, act) in enumerate(cases):
+        q = torch.randint(0, 1 << bits, (k, n), generator=g, dtype=torch.int32)
+        pre = f"c{ci}_"
+        out[pre + "meta"] = np.array([k, n, bits, int(act)])
+        out[pre + "q"] = q.numpy()
+        out[pre + "gptq"] = qu.gptq_pack(q, bits, k, n).numpy()
+        out[pre + "awq"] = qu.awq_pack(q, bits, k, n).numpy()
+        perm = mt.get_weight_perm(bits)
+        out[pre + "marlin"] = mt.marlin_weights(q, k, n, bits, perm).numpy()
+        if act:
+            g_idx = torch.randint(0, k // 32, (k,), generator=g, dtype=torch.int32)
+            q_sorted, _, sort_indices = qu.sort_weights(q, g_idx)
+            out[pre + "sort_indices"] = sort_indices.numpy()
+            out[pre + "marlin_sorted"] = mt.marlin_weights(q_sorted, k, n, bits, perm).numpy()
+    out["num_cases"] = np.array([len(cases)])
+    np.savez_compressed(os.path.join(HERE, "marlin_repack_golden.npz"), **out)
+    print("marlin_repack_golden.npz:", len(out), "arrays")
+
+
 def load_refcpu():
     flags = open("/proc/cpuinfo").read()
     isa = "avx512bf16" if "avx512_bf16" in flags else ("avx512" if "avx512f" in flags else "avx2")
@@ -208,7 +235,11 @@ def make_cache(ref):
 if __name__ == "__main__":
     torch.manual_seed(0)
     mods = load_reference_python()
+    if sys.argv[1:] == ["repack"]:
+        make_repack(*mods)
+        sys.exit(0)
     make_marlin(*mods)
+    make_repack(*mods)
     ref = load_refcpu()
     make_attention(ref)
     make_cache(ref)

@@ -156,3 +156,22 @@ def test_copy_blocks_oracle_vs_live_reference_cpu():
     for l in range(layers):
         assert torch.equal(ka[l].view(torch.int16), kb[l].view(torch.int16))
         assert torch.equal(va[l].view(torch.int16), vb[l].view(torch.int16))
+
+
+def test_repack_oracle_matches_reference_python():
+    """gptq_pack / awq_pack and the repack contract against fixtures made by the reference's own Python
+    (tests/golden/make_golden.py make_repack)."""
+    from oracle import marlin_format as mf
+    g = np.load(os.path.join(G, "marlin_repack_golden.npz"))
+    for ci in range(int(g["num_cases"][0])):
+        k, n, bits, act = (int(v) for v in g[f"c{ci}_meta"])
+        q = g[f"c{ci}_q"]
+        np.testing.assert_array_equal(mf.gptq_pack(q, bits), g[f"c{ci}_gptq"])
+        np.testing.assert_array_equal(mf.awq_pack(q, bits), g[f"c{ci}_awq"])
+        np.testing.assert_array_equal(mf.gptq_unpack(g[f"c{ci}_gptq"], bits), q)
+        np.testing.assert_array_equal(mf.awq_unpack(g[f"c{ci}_awq"], bits), q)
+        np.testing.assert_array_equal(mf.gptq_marlin_repack(g[f"c{ci}_gptq"], None, k, n, bits), g[f"c{ci}_marlin"])
+        np.testing.assert_array_equal(mf.awq_marlin_repack(g[f"c{ci}_awq"], k, n, bits), g[f"c{ci}_marlin"])
+        if act:
+            np.testing.assert_array_equal(
+                mf.gptq_marlin_repack(g[f"c{ci}_gptq"], g[f"c{ci}_sort_indices"], k, n, bits), g[f"c{ci}_marlin_sorted"])
