@@ -164,3 +164,23 @@ def awq_marlin_moe_repack(b_q_weight: torch.Tensor, perm: torch.Tensor, size_k: 
     for e in range(num_experts):
         output[e] = awq_marlin_repack(b_q_weight[e], size_k, size_n, num_bits)
     return output
+
+
+# aphrodite/_custom_ops.py:36-37,178-219 (decode-layer glue)
+def silu_and_mul(out: torch.Tensor, x: torch.Tensor) -> None:
+    _ops()[0].silu_and_mul(out, x)
+
+
+def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor, head_size: int,
+                     cos_sin_cache: torch.Tensor, is_neox: bool) -> None:
+    # the reference copies query / key to contiguous buffers and back around its kernel (_custom_ops.py:186-192);
+    # this kernel takes the token stride, so slices of the qkv projection are rotated in place
+    _ops()[0].rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox)
+
+
+def rms_norm(out: torch.Tensor, input: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
+    _ops()[0].rms_norm(out, input, weight, epsilon)
+
+
+def fused_add_rms_norm(input: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
+    _ops()[0].fused_add_rms_norm(input, residual, weight, epsilon)

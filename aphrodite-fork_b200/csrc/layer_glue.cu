@@ -1,0 +1,276 @@
+// The glue of a decode layer for sm_100a: rms_norm, fused_add_rms_norm, silu_and_mul,
+// rotary_embedding. Replaces /root/reference/kernels/layernorm_kernels.cu:15-240, activation_kernels.cu:12-91 and
+// pos_encoding_kernels.cu:10-196. All four are a few hundred KiB at decode batch sizes, i.e. launch- and
+// latency-bound: every thread moves 16-byte vectors, a row is read from HBM exactly once (the normalisation keeps it in
+// registers between the sum of squares and the scaling; the reference reads it twice), and each kernel takes part in
+// the programmatic-dependent-launch chain of the step.
+//
+// Arithmetic follows the reference operation by operation, including where it rounds to the storage type:
+//   rms_norm            out = T(float(x) * rsqrtf(mean(x^2) + eps)) * w           (T multiply)
+//   fused_add_rms_norm  z = T(x + residual) (T add); residual = z; x = T(float(z) * rs) * w
+//   silu_and_mul        out = T(float(x) / (1 + expf(-float(x)))) * y              (T multiply)
+//   rotary_embedding    x' = x*cos - y*sin, y' = y*cos + x*sin, every product and sum rounded to T
+// so silu_and_mul and rotary_embedding are bit-identical with the reference kernels and the two norms differ only
+// through the summation order of the fp32 sum of squares.
+#include "common.cuh"
+
+namespace aphb200 {
+namespace {
+
+template <typename T, int N>
+struct alignas(sizeof(T) * N) Vec {
+  T v[N];
+};
+
+template <typename T>
+__device__ __forceinline__ T mul_t(T a, T b) {  // the reference's `scalar_t * scalar_t`: exact product, one rounding
+  return ScalarTraits<T>::from_float(ScalarTraits<T>::to_float(a) * ScalarTraits<T>::to_float(b));
+}
+template <typename T>
+__device__ __forceinline__ T add_t(T a, T b) {
+  return ScalarTraits<T>::from_float(ScalarTraits<T>::to_float(a) + ScalarTraits<T>::to_float(b));
+}
+template <typename T>
+__device__ __forceinline__ T sub_t(T a, T b) {
+  return ScalarTraits<T>::from_float(ScalarTraits<T>::to_float(a) - ScalarTraits<T>::to_float(b));
+}
+
+__device__ __forceinline__ float block_sum(float v, float* s_part) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = (blockDim.x + 31) >> 5;
+  if (lane == 0) s_part[warp] = v;
+  __syncthreads();
+  v = lane < nwarp ? s_part[lane] : 0.f;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// One CTA per token. VEC elements per 16-byte access (1 = unaligned / odd hidden size fallback). Up to ITER vectors
+// per thread stay in registers between the two phases; longer rows re-read what phase one wrote (L2 hits).
+template <typename T, int VEC, int ITER, bool FUSED_ADD>
+__global__ void __launch_bounds__(1024, 1)
+    rms_norm_kernel(T* __restrict__ out, T* __restrict__ input, T* __restrict__ residual, const T* __restrict__ weight,
+                    float epsilon, int hidden, int64_t in_stride) {
+  using V = Vec<T, VEC>;
+  __shared__ float s_part[32];
+  const int nvec = hidden / VEC;
+  const int64_t row = blockIdx.x;
+  V* in_v = reinterpret_cast<V*>(input + row * in_stride);
+  V* res_v = FUSED_ADD ? reinterpret_cast<V*>(residual + row * (int64_t)hidden) : nullptr;
+  V* out_v = FUSED_ADD ? in_v : reinterpret_cast<V*>(out + row * (int64_t)hidden);
+  const V* w_v = reinterpret_cast<const V*>(weight);
+  pdl_trigger();
+  V wreg[ITER];  // weights are immutable: fetched before waiting on the previous kernel
+#pragma unroll
+  for (int i = 0; i < ITER; ++i) {
+    const int idx = threadIdx.x + i * blockDim.x;
+    if (idx < nvec) wreg[i] = w_v[idx];
+  }
+  pdl_wait();
+  V keep[ITER];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < ITER; ++i) {
+    const int idx = threadIdx.x + i * blockDim.x;
+    if (idx < nvec) {
+      V x = in_v[idx];
+      if constexpr (FUSED_ADD) {
+        const V r = res_v[idx];
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) x.v[e] = add_t(x.v[e], r.v[e]);
+        res_v[idx] = x;
+      }
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) {
+        const float f = ScalarTraits<T>::to_float(x.v[e]);
+        ss += f * f;
+      }
+      keep[i] = x;
+    }
+  }
+  for (int idx = threadIdx.x + ITER * blockDim.x; idx < nvec; idx += blockDim.x) {
+    V x = in_v[idx];
+    if constexpr (FUSED_ADD) {
+      const V r = res_v[idx];
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) x.v[e] = add_t(x.v[e], r.v[e]);
+      res_v[idx] = x;
+    }
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) {
+      const float f = ScalarTraits<T>::to_float(x.v[e]);
+      ss += f * f;
+    }
+  }
+  ss = block_sum(ss, s_part);
+  const float rs = rsqrtf(ss / (float)hidden + epsilon);
+#pragma unroll
+  for (int i = 0; i < ITER; ++i) {
+    const int idx = threadIdx.x + i * blockDim.x;
+    if (idx < nvec) {
+      V x = keep[i];
+#pragma unroll
+      for (int e = 0; e < VEC; ++e)
+        x.v[e] = mul_t(ScalarTraits<T>::from_float(ScalarTraits<T>::to_float(x.v[e]) * rs), wreg[i].v[e]);
+      out_v[idx] = x;
+    }
+  }
+  for (int idx = threadIdx.x + ITER * blockDim.x; idx < nvec; idx += blockDim.x) {
+    V x = FUSED_ADD ? res_v[idx] : in_v[idx];
+    const V w = w_v[idx];
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) x.v[e] = mul_t(ScalarTraits<T>::from_float(ScalarTraits<T>::to_float(x.v[e]) * rs), w.v[e]);
+    out_v[idx] = x;
+  }
+}
+
+// grid (ceil(d / (VEC * blockDim)), tokens)
+template <typename T, int VEC>
+__global__ void __launch_bounds__(256)
+    silu_and_mul_kernel(T* __restrict__ out, const T* __restrict__ input, int d) {
+  using V = Vec<T, VEC>;
+  pdl_trigger();
+  pdl_wait();
+  const int64_t token = blockIdx.y;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= d / VEC) return;
+  const V x = reinterpret_cast<const V*>(input + token * 2 * d)[idx];
+  const V y = reinterpret_cast<const V*>(input + token * 2 * d + d)[idx];
+  V o;
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) {
+    const float f = ScalarTraits<T>::to_float(x.v[e]);
+    o.v[e] = mul_t(ScalarTraits<T>::from_float(__fdiv_rn(f, 1.0f + expf(-f))), y.v[e]);
+  }
+  reinterpret_cast<V*>(out + token * d)[idx] = o;
+}
+
+// One CTA per token; a thread owns one (head, rotation pair) at a time, query heads first, then key heads.
+template <typename T, bool NEOX>
+__global__ void __launch_bounds__(512)
+    rotary_embedding_kernel(const int64_t* __restrict__ positions, T* __restrict__ query, T* __restrict__ key,
+                            const T* __restrict__ cos_sin_cache, int rot_dim, int64_t query_stride, int64_t key_stride,
+                            int num_heads, int num_kv_heads, int head_size) {
+  pdl_trigger();
+  const int token = blockIdx.x;
+  const int embed = rot_dim / 2;
+  const T* cache = cos_sin_cache + positions[token] * rot_dim;  // positions and the table are step inputs, not kernel outputs
+  pdl_wait();
+  const int nq = num_heads * embed, total = nq + (key != nullptr ? num_kv_heads * embed : 0);
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const bool is_q = i < nq;
+    const int j = is_q ? i : i - nq;
+    const int head = j / embed, off = j % embed;
+    T* arr = (is_q ? query + token * query_stride : key + token * key_stride) + (int64_t)head * head_size;
+    const int xi = NEOX ? off : 2 * off, yi = NEOX ? embed + off : 2 * off + 1;
+    const T c = cache[off], s = cache[embed + off];
+    const T x = arr[xi], y = arr[yi];
+    arr[xi] = sub_t(mul_t(x, c), mul_t(y, s));
+    arr[yi] = add_t(mul_t(y, c), mul_t(x, s));
+  }
+}
+
+template <typename T, bool FUSED>
+int launch_norm(T* out, T* input, T* residual, const T* weight, float eps, int64_t tokens, int hidden, int64_t in_stride,
+                cudaStream_t stream) {
+  const bool vec_ok = hidden % (16 / (int)sizeof(T)) == 0 && aligned16(input) && aligned16(weight) &&
+                      (in_stride * sizeof(T)) % 16 == 0 && (FUSED ? aligned16(residual) : aligned16(out));
+  constexpr int VEC = 16 / (int)sizeof(T);
+  if (vec_ok) {
+    const int nvec = hidden / VEC;
+    // few tokens: one vector per thread (latency); many tokens: two per thread and smaller CTAs (occupancy)
+    int threads = tokens < 512 ? nvec : (nvec + 1) / 2;
+    threads = std::min(1024, std::max(32, (threads + 31) / 32 * 32));
+    APH_LAUNCH_PDL(rms_norm_kernel<T, VEC, 2, FUSED>, dim3((unsigned)tokens), dim3(threads), 0, stream, out, input, residual,
+                   weight, eps, hidden, in_stride);
+  } else {
+    const int threads = std::min(1024, std::max(32, (hidden + 31) / 32 * 32));
+    APH_LAUNCH_PDL(rms_norm_kernel<T, 1, 1, FUSED>, dim3((unsigned)tokens), dim3(threads), 0, stream, out, input, residual,
+                   weight, eps, hidden, in_stride);
+  }
+  return APH_OK;
+}
+
+template <typename T>
+int launch_silu(T* out, const T* input, int64_t tokens, int d, cudaStream_t stream) {
+  constexpr int VEC = 16 / (int)sizeof(T);
+  if (d % VEC == 0 && aligned16(out) && aligned16(input)) {
+    APH_LAUNCH_PDL(silu_and_mul_kernel<T, VEC>, dim3((unsigned)((d / VEC + 255) / 256), (unsigned)tokens), dim3(256), 0, stream, out,
+                   input, d);
+  } else {
+    APH_LAUNCH_PDL(silu_and_mul_kernel<T, 1>, dim3((unsigned)((d + 255) / 256), (unsigned)tokens), dim3(256), 0, stream, out, input, d);
+  }
+  return APH_OK;
+}
+
+template <typename T>
+int launch_rope(const int64_t* positions, T* q, T* k, const T* cache, int rot_dim, int64_t qs, int64_t ks, int nh, int nkv,
+                int head_size, bool neox, int64_t tokens, cudaStream_t stream) {
+  const int work = (nh + (k ? nkv : 0)) * rot_dim / 2;
+  const int threads = std::min(512, std::max(32, (work + 31) / 32 * 32));
+  if (neox)
+    APH_LAUNCH_PDL(rotary_embedding_kernel<T, true>, dim3((unsigned)tokens), dim3(threads), 0, stream, positions, q, k, cache, rot_dim,
+                   qs, ks, nh, nkv, head_size);
+  else
+    APH_LAUNCH_PDL(rotary_embedding_kernel<T, false>, dim3((unsigned)tokens), dim3(threads), 0, stream, positions, q, k, cache, rot_dim,
+                   qs, ks, nh, nkv, head_size);
+  return APH_OK;
+}
+
+}  // namespace
+}  // namespace aphb200
+
+using namespace aphb200;
+
+#define APH_DISPATCH_DT(dt, op, ...)                                                    \
+  switch (dt) {                                                                         \
+    case APH_DT_F32: { using T = float; return __VA_ARGS__; }                           \
+    case APH_DT_F16: { using T = __half; return __VA_ARGS__; }                          \
+    case APH_DT_BF16: { using T = __nv_bfloat16; return __VA_ARGS__; }                  \
+    default: return set_error(APH_ERR_INVALID_ARGUMENT, "%s: unknown dtype %d", op, dt); \
+  }
+
+extern "C" int aph_rms_norm(void* out, const void* input, const void* weight, float epsilon, int64_t num_tokens,
+                            int64_t hidden_size, int64_t input_stride, int dtype, void* stream) {
+  const char* op = "rms_norm";
+  APH_CHECK(num_tokens >= 0 && hidden_size > 0 && hidden_size < (1LL << 31), APH_ERR_INVALID_ARGUMENT, "%s: bad shape", op);
+  if (num_tokens == 0) return APH_OK;
+  APH_CHECK(out && input && weight, APH_ERR_INVALID_ARGUMENT, "%s: null tensor", op);
+  APH_DISPATCH_DT(dtype, op, launch_norm<T, false>((T*)out, (T*)const_cast<void*>(input), nullptr, (const T*)weight, epsilon, num_tokens,
+                                                   (int)hidden_size, input_stride, (cudaStream_t)stream));
+}
+
+extern "C" int aph_fused_add_rms_norm(void* input, void* residual, const void* weight, float epsilon, int64_t num_tokens,
+                                      int64_t hidden_size, int dtype, void* stream) {
+  const char* op = "fused_add_rms_norm";
+  APH_CHECK(num_tokens >= 0 && hidden_size > 0 && hidden_size < (1LL << 31), APH_ERR_INVALID_ARGUMENT, "%s: bad shape", op);
+  if (num_tokens == 0) return APH_OK;
+  APH_CHECK(input && residual && weight, APH_ERR_INVALID_ARGUMENT, "%s: null tensor", op);
+  APH_DISPATCH_DT(dtype, op, launch_norm<T, true>(nullptr, (T*)input, (T*)residual, (const T*)weight, epsilon, num_tokens,
+                                                  (int)hidden_size, hidden_size, (cudaStream_t)stream));
+}
+
+extern "C" int aph_silu_and_mul(void* out, const void* input, int64_t num_tokens, int64_t d, int dtype, void* stream) {
+  const char* op = "silu_and_mul";
+  APH_CHECK(num_tokens >= 0 && d > 0 && d < (1LL << 30), APH_ERR_INVALID_ARGUMENT, "%s: bad shape", op);
+  APH_CHECK(num_tokens <= 65535, APH_ERR_UNSUPPORTED, "%s: more than 65535 tokens per call", op);
+  if (num_tokens == 0) return APH_OK;
+  APH_CHECK(out && input, APH_ERR_INVALID_ARGUMENT, "%s: null tensor", op);
+  APH_DISPATCH_DT(dtype, op, launch_silu<T>((T*)out, (const T*)input, num_tokens, (int)d, (cudaStream_t)stream));
+}
+
+extern "C" int aph_rotary_embedding(const int64_t* positions, void* query, void* key, const void* cos_sin_cache,
+                                    int64_t num_tokens, int rot_dim, int64_t query_stride, int64_t key_stride, int num_heads,
+                                    int num_kv_heads, int head_size, int is_neox, int dtype, void* stream) {
+  const char* op = "rotary_embedding";
+  APH_CHECK(num_tokens >= 0 && rot_dim > 0 && rot_dim % 2 == 0 && rot_dim <= head_size, APH_ERR_INVALID_ARGUMENT,
+            "%s: rot_dim %d must be even and at most head_size %d", op, rot_dim, head_size);
+  APH_CHECK(num_heads > 0 && num_kv_heads > 0 && num_heads % num_kv_heads == 0, APH_ERR_INVALID_ARGUMENT,
+            "%s: num_heads %d is not a multiple of num_kv_heads %d", op, num_heads, num_kv_heads);
+  if (num_tokens == 0) return APH_OK;
+  APH_CHECK(positions && query && cos_sin_cache, APH_ERR_INVALID_ARGUMENT, "%s: null tensor", op);
+  APH_DISPATCH_DT(dtype, op, launch_rope<T>(positions, (T*)query, (T*)key, (const T*)cos_sin_cache, rot_dim, query_stride, key_stride,
+                                            num_heads, num_kv_heads, head_size, is_neox != 0, num_tokens, (cudaStream_t)stream));
+}

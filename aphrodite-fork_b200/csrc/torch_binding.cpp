@@ -355,6 +355,91 @@ torch::Tensor awq_marlin_repack(torch::Tensor& b_q_weight, int64_t size_k, int64
   return out;
 }
 
+// kernels/layernorm_kernels.cu:139-154
+void rms_norm(torch::Tensor& out, torch::Tensor& input, torch::Tensor& weight, double epsilon) {
+  const char* op = "rms_norm";
+  TORCH_CHECK(out.is_cuda() && input.is_cuda() && weight.is_cuda(), op, ": tensors must be on a CUDA device");
+  TORCH_CHECK(out.is_contiguous() && input.is_contiguous() && weight.is_contiguous(), op, ": tensors must be contiguous");
+  TORCH_CHECK(out.scalar_type() == input.scalar_type() && weight.scalar_type() == input.scalar_type(), op, ": dtype mismatch");
+  const int64_t hidden = input.size(-1);
+  TORCH_CHECK(weight.numel() == hidden && out.numel() == input.numel(), op, ": shape mismatch");
+  const at::cuda::OptionalCUDAGuard guard(device_of(input));
+  check_status(aph_rms_norm(out.data_ptr(), input.data_ptr(), weight.data_ptr(), (float)epsilon, input.numel() / hidden, hidden,
+                            hidden, dtype_code(input, op), stream_of()), op);
+}
+
+// kernels/layernorm_kernels.cu:168-240
+void fused_add_rms_norm(torch::Tensor& input, torch::Tensor& residual, torch::Tensor& weight, double epsilon) {
+  const char* op = "fused_add_rms_norm";
+  TORCH_CHECK(input.is_cuda() && residual.is_cuda() && weight.is_cuda(), op, ": tensors must be on a CUDA device");
+  TORCH_CHECK(input.is_contiguous() && residual.is_contiguous() && weight.is_contiguous(), op, ": tensors must be contiguous");
+  TORCH_CHECK(residual.scalar_type() == input.scalar_type() && weight.scalar_type() == input.scalar_type(), op, ": dtype mismatch");
+  const int64_t hidden = input.size(-1);
+  TORCH_CHECK(weight.numel() == hidden && residual.numel() == input.numel(), op, ": shape mismatch");
+  const at::cuda::OptionalCUDAGuard guard(device_of(input));
+  check_status(aph_fused_add_rms_norm(input.data_ptr(), residual.data_ptr(), weight.data_ptr(), (float)epsilon,
+                                      input.numel() / hidden, hidden, dtype_code(input, op), stream_of()), op);
+}
+
+// kernels/activation_kernels.cu:82-86
+void silu_and_mul(torch::Tensor& out, torch::Tensor& input) {
+  const char* op = "silu_and_mul";
+  TORCH_CHECK(out.is_cuda() && input.is_cuda(), op, ": tensors must be on a CUDA device");
+  TORCH_CHECK(out.is_contiguous() && input.is_contiguous(), op, ": tensors must be contiguous");
+  TORCH_CHECK(out.scalar_type() == input.scalar_type(), op, ": dtype mismatch");
+  TORCH_CHECK(input.size(-1) % 2 == 0, op, ": the last dimension of input must be even");
+  const int64_t d = input.size(-1) / 2;
+  TORCH_CHECK(out.numel() * 2 == input.numel() && out.size(-1) == d, op, ": shape mismatch");
+  const at::cuda::OptionalCUDAGuard guard(device_of(input));
+  const int64_t tokens = d > 0 ? out.numel() / d : 0;
+  // the grid's y dimension carries the tokens: long prefills go in slices of 65535 tokens
+  for (int64_t t0 = 0; t0 < tokens; t0 += 65535) {
+    const int64_t n = std::min<int64_t>(65535, tokens - t0);
+    check_status(aph_silu_and_mul((char*)out.data_ptr() + t0 * d * out.element_size(),
+                                  (const char*)input.data_ptr() + t0 * 2 * d * input.element_size(), n, d, dtype_code(input, op),
+                                  stream_of()), op);
+  }
+}
+
+// kernels/pos_encoding_kernels.cu:124-196 (same shape checks)
+void rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int64_t head_size,
+                      torch::Tensor& cos_sin_cache, bool is_neox) {
+  const char* op = "rotary_embedding";
+  TORCH_CHECK(positions.is_cuda() && query.is_cuda() && key.is_cuda() && cos_sin_cache.is_cuda(), op,
+              ": tensors must be on a CUDA device");
+  const int64_t num_tokens = positions.numel();
+  const int positions_ndim = positions.dim();
+  TORCH_CHECK(positions_ndim == 1 || positions_ndim == 2, "positions must have shape [num_tokens] or [batch_size, seq_len]");
+  if (positions_ndim == 1) {
+    TORCH_CHECK(query.size(0) == positions.size(0) && key.size(0) == positions.size(0),
+                "query, key and positions must have the same number of tokens");
+  } else {
+    TORCH_CHECK(query.size(0) == positions.size(0) && key.size(0) == positions.size(0) && query.size(1) == positions.size(1) &&
+                    key.size(1) == positions.size(1),
+                "query, key and positions must have the same batch_size and seq_len");
+  }
+  TORCH_CHECK(positions.scalar_type() == at::ScalarType::Long && positions.is_contiguous(), op, ": positions must be contiguous int64");
+  TORCH_CHECK(key.scalar_type() == query.scalar_type() && cos_sin_cache.scalar_type() == query.scalar_type(), op, ": dtype mismatch");
+  TORCH_CHECK(cos_sin_cache.dim() == 2 && cos_sin_cache.is_contiguous(), op, ": cos_sin_cache must be [max_position, rot_dim]");
+  if (num_tokens == 0) return;
+  const int64_t query_hidden = query.numel() / num_tokens, key_hidden = key.numel() / num_tokens;
+  TORCH_CHECK(query_hidden % head_size == 0);
+  TORCH_CHECK(key_hidden % head_size == 0);
+  const int64_t num_heads = query_hidden / head_size, num_kv_heads = key_hidden / head_size;
+  TORCH_CHECK(num_heads % num_kv_heads == 0);
+  const int seq_dim = positions_ndim - 1;
+  // the token dimensions may be strided (q / k are slices of the qkv projection); inside a token the layout is dense
+  TORCH_CHECK(query.stride(-1) == 1 && key.stride(-1) == 1, op, ": the last dimension must be contiguous");
+  if (positions_ndim == 2)
+    TORCH_CHECK(query.stride(0) == query.stride(1) * query.size(1) && key.stride(0) == key.stride(1) * key.size(1), op,
+                ": batch and sequence dimensions must collapse into one token stride");
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  check_status(aph_rotary_embedding(positions.data_ptr<int64_t>(), query.data_ptr(), key.data_ptr(), cos_sin_cache.data_ptr(),
+                                    num_tokens, (int)cos_sin_cache.size(1), query.stride(seq_dim), key.stride(seq_dim),
+                                    (int)num_heads, (int)num_kv_heads, (int)head_size, is_neox ? 1 : 0, dtype_code(query, op),
+                                    stream_of()), op);
+}
+
 }  // namespace
 
 #ifdef APH_DEFINE_SCHEMAS
@@ -395,6 +480,18 @@ TORCH_LIBRARY_FRAGMENT(_C, ops) {
   ops.def(
       "awq_marlin_repack(Tensor b_q_weight, SymInt size_k, "
       "SymInt size_n, int num_bits) -> Tensor");
+  // kernels/torch_bindings.cpp:84,140-148,178-181
+  ops.def("silu_and_mul(Tensor! result, Tensor input) -> ()");
+  ops.def(
+      "rms_norm(Tensor! result, Tensor input, Tensor weight, float epsilon) -> "
+      "()");
+  ops.def(
+      "fused_add_rms_norm(Tensor! input, Tensor! residual, Tensor weight, "
+      "float epsilon) -> ()");
+  ops.def(
+      "rotary_embedding(Tensor positions, Tensor! query,"
+      "                 Tensor! key, int head_size,"
+      "                 Tensor cos_sin_cache, bool is_neox) -> ()");
 }
 TORCH_LIBRARY_FRAGMENT(_C_cache_ops, ops) {
   ops.def(
@@ -427,6 +524,10 @@ TORCH_LIBRARY_IMPL(_C, CUDA, ops) {
   ops.impl("gptq_marlin_gemm", &gptq_marlin_gemm);
   ops.impl("gptq_marlin_repack", &gptq_marlin_repack);
   ops.impl("awq_marlin_repack", &awq_marlin_repack);
+  ops.impl("silu_and_mul", &silu_and_mul);
+  ops.impl("rms_norm", &rms_norm);
+  ops.impl("fused_add_rms_norm", &fused_add_rms_norm);
+  ops.impl("rotary_embedding", &rotary_embedding);
 }
 TORCH_LIBRARY_IMPL(_C_cache_ops, CUDA, ops) {
   ops.impl("reshape_and_cache", &reshape_and_cache);

@@ -1,13 +1,15 @@
-"""A Llama-shaped decode step built from the three hot-path kernels, tensor-parallel over `torch.distributed`.
+"""A Llama decode step built from this library's kernels only, tensor-parallel over `torch.distributed`.
 
 This is the caller side of SURVEY.md 3.1 reduced to what the hot path needs: per layer
-    qkv = W4A16 GEMM (column parallel)  ->  reshape_and_cache(k, v)  ->  paged attention (this rank's heads)
-    o   = W4A16 GEMM (row parallel)     ->  all_reduce
-    gu  = W4A16 GEMM (column parallel)  ->  SiLU(gate) * up
+    h   = fused_add_rms_norm(x, residual)                      (rms_norm for the first layer)
+    qkv = W4A16 GEMM (column parallel)  ->  rotary_embedding(q, k)  ->  reshape_and_cache(k, v)
+                                        ->  paged attention (this rank's heads)
+    o   = W4A16 GEMM (row parallel)     ->  all_reduce          ->  fused_add_rms_norm(o, residual)
+    gu  = W4A16 GEMM (column parallel)  ->  silu_and_mul
     dn  = W4A16 GEMM (row parallel)     ->  all_reduce
-with residual adds. RMSNorm / RoPE are left out on purpose (the reference's layernorm and
-pos_encoding kernels are the next row, not this one); weights are synthetic. One step can be captured in a CUDA
-graph, the NCCL all_reduces included, which is how the reference runs decode (`cuda_communicator.py`).
+and a final fused_add_rms_norm: 11 kernels per layer, every one launched with programmatic dependent launch, no
+torch elementwise kernels in between. Weights are synthetic. One step can be captured in a CUDA graph, the NCCL
+all_reduces included, which is how the reference runs decode (`cuda_communicator.py`).
 
 Reference call sites mirrored: modeling/models/llama.py:100-215 (layer structure and head split),
 modeling/layers/linear.py:474-484,1279-1283, attention/ops/paged_attn.py:60-160.
@@ -38,6 +40,8 @@ class DecodeConfig:
     block_size: int = 16
     kv_cache_dtype: str = "fp8"  # "auto" | "fp8" | "fp8_e4m3" | "fp8_e5m2"
     dtype: torch.dtype = torch.bfloat16
+    rms_norm_eps: float = 1e-5
+    rope_theta: float = 500000.0
 
     # benchmark_shapes.py:3-8 / :57-62
     @staticmethod
@@ -100,22 +104,35 @@ class DecodeLayer:
         self.k_scale = torch.ones((), dtype=torch.float32, device=device)
         self.v_scale = torch.ones((), dtype=torch.float32, device=device)
         self.scale = d ** -0.5
+        ln = lambda: (1.0 + 0.1 * torch.randn(cfg.hidden, device=device, generator=gen)).to(cfg.dtype)
+        self.input_layernorm, self.post_attention_layernorm = ln(), ln()
 
-    def forward(self, x: torch.Tensor, slot_mapping, block_tables, seq_lens, max_seq_len: int) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor], positions, cos_sin_cache, slot_mapping,
+                block_tables, seq_lens, max_seq_len: int):
+        """modeling/models/llama.py:270-292: returns (mlp output, residual stream)."""
         cfg, d = self.cfg, self.cfg.head_size
-        qkv = self.qkv(x)
+        if residual is None:
+            residual = x
+            h = torch.empty_like(x)
+            ops.rms_norm(h, x, self.input_layernorm, cfg.rms_norm_eps)
+        else:
+            ops.fused_add_rms_norm(x, residual, self.input_layernorm, cfg.rms_norm_eps)
+            h = x
+        qkv = self.qkv(h)
         q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
+        ops.rotary_embedding(positions, q, k, d, cos_sin_cache, True)  # in place on the slices of qkv
         q = q.reshape(-1, self.h, d)
         PagedAttention.write_to_paged_cache(k.reshape(-1, self.kvh, d), v.reshape(-1, self.kvh, d), self.key_cache,
                                             self.value_cache, slot_mapping, cfg.kv_cache_dtype, self.k_scale, self.v_scale)
         a = PagedAttention.forward_decode(q, self.key_cache, self.value_cache, block_tables, seq_lens, max_seq_len,
                                           cfg.kv_cache_dtype, self.kvh, self.scale, None, self.k_scale, self.v_scale,
                                           tp_rank=self.tp.rank)
-        x = x + self.tp.all_reduce(self.o(a.reshape(-1, self.q_size)))
-        gu = self.gate_up(x)
-        gate, up = gu.chunk(2, dim=-1)
-        x = x + self.tp.all_reduce(self.down(torch.nn.functional.silu(gate) * up))
-        return x
+        o = self.tp.all_reduce(self.o(a.reshape(-1, self.q_size)))
+        ops.fused_add_rms_norm(o, residual, self.post_attention_layernorm, cfg.rms_norm_eps)
+        gu = self.gate_up(o)
+        act = torch.empty(gu.shape[0], gu.shape[1] // 2, dtype=gu.dtype, device=gu.device)
+        ops.silu_and_mul(act, gu)
+        return self.tp.all_reduce(self.down(act)), residual
 
 
 class DecodeModel:
@@ -135,13 +152,21 @@ class DecodeModel:
         self.slot_mapping = last * bs + (ctx - 1) % bs  # the new token is the last position of each sequence
         self.layers: List[DecodeLayer] = [DecodeLayer(cfg, self.tp, num_blocks, device, gen) for _ in range(cfg.num_layers)]
         self.x = (torch.randn(batch, cfg.hidden, device=device, generator=gen) * 0.05).to(cfg.dtype)
+        self.norm = (1.0 + 0.1 * torch.randn(cfg.hidden, device=device, generator=gen)).to(cfg.dtype)
+        self.positions = torch.full((batch,), ctx - 1, dtype=torch.int64, device=device)
+        # modeling/layers/rotary_embedding.py:114-131: [max_position, rot_dim] = cos half | sin half
+        inv_freq = 1.0 / (cfg.rope_theta ** (torch.arange(0, cfg.head_size, 2, dtype=torch.float, device=device) / cfg.head_size))
+        freqs = torch.einsum("i,j->ij", torch.arange(ctx, dtype=torch.float, device=device), inv_freq)
+        self.cos_sin_cache = torch.cat((freqs.cos(), freqs.sin()), dim=-1).to(cfg.dtype)
         self.out = torch.empty_like(self.x)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
 
     def _forward(self) -> None:
-        x = self.x
+        x, residual = self.x.clone(), None  # the layers work in place on the residual stream
         for layer in self.layers:
-            x = layer.forward(x, self.slot_mapping, self.block_tables, self.seq_lens, self.ctx)
+            x, residual = layer.forward(x, residual, self.positions, self.cos_sin_cache, self.slot_mapping, self.block_tables,
+                                        self.seq_lens, self.ctx)
+        ops.fused_add_rms_norm(x, residual, self.norm, self.cfg.rms_norm_eps)
         self.out.copy_(x)
 
     def capture(self) -> None:
@@ -165,8 +190,9 @@ class DecodeModel:
         return self.out
 
     def launches_per_step(self) -> int:
-        """Kernels of this repo per step: 4 GEMMs + cache write + attention (+ its split-K reduce) per layer."""
-        return self.cfg.num_layers * 7
+        """Kernels of this repo per step: per layer 4 GEMMs, 2 norms, rotary, cache write, attention + its split-K
+        reduce, silu_and_mul; one final norm."""
+        return self.cfg.num_layers * 11 + 1
 
     def kv_bytes_per_step(self) -> int:
         l0 = self.layers[0]

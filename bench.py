@@ -248,9 +248,9 @@ def gemm_extras(torch, A, dev, iters=30):
 
 
 def decode_extras(torch, A, dev, world, steps=10):
-    """Decode tok/s of a Llama-shaped layer stack over the three kernels (+ NCCL all_reduce when world > 1), one CUDA
-    graph per step. 1 GPU: Llama-3.1-8B shapes (C3); N GPUs: Llama-3.1-70B shapes at TP = N (C4). Glue that is not on
-    the hot path (RMSNorm, RoPE) is left out, see aphrodite-fork_b200/decode.py."""
+    """Decode tok/s of a Llama layer stack built from this library's kernels only (+ NCCL all_reduce when world > 1),
+    one CUDA graph per step. 1 GPU: Llama-3.1-8B shapes (C3); N GPUs: Llama-3.1-70B shapes at TP = N (C4). RMSNorm,
+    RoPE and SiLU-mul are the library's own kernels, see aphrodite-fork_b200/decode.py."""
     from aphrodite_fork_b200.decode import DecodeConfig, DecodeModel
     from aphrodite_fork_b200.tp import TPGroup
     cfg = DecodeConfig.llama3_8b() if world == 1 else DecodeConfig.llama3_70b()

@@ -174,6 +174,26 @@ int aph_gptq_marlin_repack(int32_t* out, const int32_t* b_q_weight, const int32_
 int aph_awq_marlin_repack(int32_t* out, const int32_t* b_q_weight, int64_t size_k, int64_t size_n, int num_bits,
                           void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Decode-layer glue - replaces kernels/layernorm_kernels.cu:139-240, activation_kernels.cu:82-86
+ * and pos_encoding_kernels.cu:124-196. dtype: aph_dtype_t of every tensor of the call. Row-major, last dimension
+ * contiguous. The arithmetic rounds to the storage type exactly where the reference does.
+ *   aph_rms_norm            out[t] = T(x[t] * rsqrt(mean(x[t]^2) + eps)) * weight;  input rows input_stride apart
+ *   aph_fused_add_rms_norm  residual[t] += input[t];  input[t] = norm(residual[t]) * weight   (both in place)
+ *   aph_silu_and_mul        out[t][i] = silu(input[t][i]) * input[t][d + i],  input [tokens, 2 d], at most 65535 tokens
+ *   aph_rotary_embedding    rotates the first rot_dim elements of every head of query (and key unless NULL) in place
+ *                           by cos_sin_cache[positions[t]] ([max_position, rot_dim]: cos half, sin half);
+ *                           is_neox: pairs (i, i + rot_dim/2), else (2i, 2i+1); strides in elements per token
+ * ------------------------------------------------------------------------------------------- */
+int aph_rms_norm(void* out, const void* input, const void* weight, float epsilon, int64_t num_tokens,
+                 int64_t hidden_size, int64_t input_stride, int dtype, void* stream);
+int aph_fused_add_rms_norm(void* input, void* residual, const void* weight, float epsilon, int64_t num_tokens,
+                           int64_t hidden_size, int dtype, void* stream);
+int aph_silu_and_mul(void* out, const void* input, int64_t num_tokens, int64_t d, int dtype, void* stream);
+int aph_rotary_embedding(const int64_t* positions, void* query, void* key, const void* cos_sin_cache,
+                         int64_t num_tokens, int rot_dim, int64_t query_stride, int64_t key_stride, int num_heads,
+                         int num_kv_heads, int head_size, int is_neox, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -49,6 +49,13 @@ void convert_fp8(torch::Tensor& dst_cache, torch::Tensor& src_cache, const doubl
 void gather_cache(torch::Tensor const& src_cache, torch::Tensor const& dst, torch::Tensor const& block_table,
                   torch::Tensor const& cu_seq_lens, int64_t batch_size, std::optional<torch::Tensor> seq_starts);
 
+// kernels/layernorm_kernels.cu:139,168; activation_kernels.cu:82; pos_encoding_kernels.cu:124
+void rms_norm(torch::Tensor& out, torch::Tensor& input, torch::Tensor& weight, double epsilon);
+void fused_add_rms_norm(torch::Tensor& input, torch::Tensor& residual, torch::Tensor& weight, double epsilon);
+void silu_and_mul(torch::Tensor& out, torch::Tensor& input);
+void rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int64_t head_size,
+                      torch::Tensor& cos_sin_cache, bool is_neox);
+
 #define ATTN_SCHEMA_TAIL                                                                            \
   "Tensor query, Tensor key_cache, Tensor value_cache, int num_kv_heads, float scale, "            \
   "Tensor block_tables, Tensor seq_lens, int block_size, int max_seq_len, Tensor? alibi_slopes, "   \
@@ -90,4 +97,14 @@ TORCH_LIBRARY(_refcuda, ops) {
       "gather_cache(Tensor src_cache, Tensor! dst, Tensor block_table, Tensor cu_seq_lens, int batch_size, "
       "Tensor? seq_starts) -> ()");
   ops.impl("gather_cache", torch::kCUDA, &gather_cache);
+  ops.def("rms_norm(Tensor! result, Tensor input, Tensor weight, float epsilon) -> ()");
+  ops.impl("rms_norm", torch::kCUDA, &rms_norm);
+  ops.def("fused_add_rms_norm(Tensor! input, Tensor! residual, Tensor weight, float epsilon) -> ()");
+  ops.impl("fused_add_rms_norm", torch::kCUDA, &fused_add_rms_norm);
+  ops.def("silu_and_mul(Tensor! result, Tensor input) -> ()");
+  ops.impl("silu_and_mul", torch::kCUDA, &silu_and_mul);
+  ops.def(
+      "rotary_embedding(Tensor positions, Tensor! query, Tensor! key, int head_size, Tensor cos_sin_cache, "
+      "bool is_neox) -> ()");
+  ops.impl("rotary_embedding", torch::kCUDA, &rotary_embedding);
 }

@@ -145,6 +145,75 @@ def make_repack(st, qu, mu, mt):
     print("marlin_repack_golden.npz:", len(out), "arrays")
 
 
+def load_reference_layers():
+    """The reference's RMSNorm / SiluAndMul / RotaryEmbedding modules, loaded by path with the platform pinned to
+    'not CUDA' so that only their forward_native code is used."""
+    import torch.nn as nn
+
+    class CustomOp(nn.Module):
+        @classmethod
+        def register(cls, name):
+            return lambda c: c
+
+    class _Platform:
+        def __getattr__(self, name):
+            return lambda *a, **k: False
+
+    _stub("aphrodite.modeling._custom_op", CustomOp=CustomOp)
+    sys.modules["aphrodite.platforms"].current_platform = _Platform()
+    _stub("aphrodite.common.utils", LazyDict=dict)
+    _stub("aphrodite.distributed", divide=None, get_tensor_model_parallel_rank=None, get_tensor_model_parallel_world_size=None)
+    _stub("aphrodite.modeling.utils", set_weight_attrs=None)
+    base = f"{REF}/aphrodite/modeling/layers"
+    ln = _load("aphrodite.modeling.layers.layernorm", f"{base}/layernorm.py")
+    act = _load("aphrodite.modeling.layers.activation", f"{base}/activation.py")
+    rope = _load("aphrodite.modeling.layers.rotary_embedding", f"{base}/rotary_embedding.py")
+    return ln, act, rope
+
+
+@torch.no_grad()
+def make_glue():
+    """Inputs and forward_native outputs of the decode-layer glue (reference tests: tests/kernels/test_layernorm.py,
+    test_activation.py, test_pos_encoding.py compare the CUDA kernels against exactly these methods)."""
+    ln, act, rope = load_reference_layers()
+    out = {}
+    g = torch.Generator().manual_seed(2)
+    cases = [(7, 512, torch.bfloat16), (3, 4096, torch.float16), (5, 768, torch.float32), (4, 8192, torch.bfloat16)]
+    for ci, (t, h, dt) in enumerate(cases):
+        layer = ln.RMSNorm(h).to(dt)
+        layer.weight.data.normal_(mean=1.0, std=0.1, generator=g)
+        x = (torch.randn(t, h, generator=g) * (1 / (2 * h)) ** 0.5 * 30).to(dt)
+        res = (torch.randn(t, h, generator=g) * (1 / (2 * h)) ** 0.5 * 30).to(dt)
+        pre = f"norm{ci}_"
+        out[pre + "meta"] = np.array([t, h, {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}[dt]])
+        out[pre + "x"], out[pre + "res"], out[pre + "w"] = raw(x), raw(res), raw(layer.weight.data)
+        out[pre + "eps"] = np.array([layer.variance_epsilon])
+        out[pre + "out"] = raw(layer.forward_native(x))
+        o2, r2 = layer.forward_native(x, res)
+        out[pre + "fused_out"], out[pre + "fused_res"] = raw(o2), raw(r2)
+        xs = torch.randn(t, 2 * h, generator=g).to(dt)
+        out[pre + "silu_x"] = raw(xs)
+        out[pre + "silu_out"] = raw(act.SiluAndMul().forward_native(xs))
+    # (tokens, heads, kv heads, head size, rotary dim, neox, dtype)
+    rcases = [(9, 8, 2, 128, 128, True, torch.bfloat16), (5, 4, 4, 64, 32, False, torch.float16),
+              (6, 6, 2, 96, 96, False, torch.bfloat16), (4, 8, 1, 128, 64, True, torch.float32)]
+    for ci, (t, nh, nkv, d, rot, neox, dt) in enumerate(rcases):
+        layer = rope.RotaryEmbedding(d, rot, 4096, 10000, neox, dt)
+        pos = torch.randint(0, 4096, (t,), generator=g)
+        q = torch.randn(t, nh * d, generator=g).to(dt)
+        k = torch.randn(t, nkv * d, generator=g).to(dt)
+        pre = f"rope{ci}_"
+        out[pre + "meta"] = np.array([t, nh, nkv, d, rot, int(neox), {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}[dt]])
+        out[pre + "pos"], out[pre + "q"], out[pre + "k"] = pos.numpy(), raw(q), raw(k)
+        out[pre + "cache"] = raw(layer.cos_sin_cache[pos.unique()])  # only the rows that are used travel
+        out[pre + "cache_rows"] = pos.unique().numpy()
+        qo, ko = layer.forward_native(pos, q.clone(), k.clone())
+        out[pre + "q_out"], out[pre + "k_out"] = raw(qo), raw(ko)
+    out["num_norm"], out["num_rope"] = np.array([len(cases)]), np.array([len(rcases)])
+    np.savez_compressed(os.path.join(HERE, "glue_golden.npz"), **out)
+    print("glue_golden.npz:", len(out), "arrays")
+
+
 def load_refcpu():
     flags = open("/proc/cpuinfo").read()
     isa = "avx512bf16" if "avx512_bf16" in flags else ("avx512" if "avx512f" in flags else "avx2")
@@ -238,8 +307,12 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["repack"]:
         make_repack(*mods)
         sys.exit(0)
+    if sys.argv[1:] == ["glue"]:
+        make_glue()
+        sys.exit(0)
     make_marlin(*mods)
     make_repack(*mods)
+    make_glue()
     ref = load_refcpu()
     make_attention(ref)
     make_cache(ref)

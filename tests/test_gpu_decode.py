@@ -11,6 +11,7 @@ import torch
 import aphrodite_fork_b200 as A
 from aphrodite_fork_b200.decode import DecodeConfig, DecodeModel
 from oracle import oracle
+from oracle import layer_glue as lg
 from oracle import marlin_format as mf
 
 pytestmark = pytest.mark.gpu
@@ -26,24 +27,31 @@ def _bf16(x64):
 
 
 def _reference_step(model: DecodeModel, caches_before):
-    """The same step on the CPU: fp64 GEMMs on the dequantised weights rounded to bf16 where the kernels round."""
+    """The same step on the CPU: fp64 GEMMs on the dequantised weights rounded to bf16 where the kernels round, the
+    glue from oracle/layer_glue.py."""
     cfg = model.cfg
-    x = model.x.cpu()
+    x, residual = model.x.cpu().clone(), None
     bt, sl, slots = model.block_tables.cpu(), model.seq_lens.cpu(), model.slot_mapping.cpu()
+    pos, cache = model.positions.cpu(), model.cos_sin_cache.cpu()
     for layer, (kc, vc) in zip(model.layers, caches_before):
         d = cfg.head_size
-        qkv = _bf16(oracle.gemm(x, _dq(layer.qkv)))
+        if residual is None:
+            residual, h = x, lg.rms_norm(x, layer.input_layernorm.cpu(), cfg.rms_norm_eps)
+        else:
+            h, residual = lg.fused_add_rms_norm(x, residual, layer.input_layernorm.cpu(), cfg.rms_norm_eps)
+        qkv = _bf16(oracle.gemm(h, _dq(layer.qkv)))
         q, k, v = qkv.split([layer.q_size, layer.kv_size, layer.kv_size], dim=-1)
+        q, k = lg.rotary_embedding(pos, q.contiguous(), k.contiguous(), d, cache, True)
         k = k.reshape(-1, layer.kvh, d).contiguous()
         v = v.reshape(-1, layer.kvh, d).contiguous()
         oracle.reshape_and_cache(k, v, kc, vc, slots, cfg.kv_cache_dtype, 1.0, 1.0)
         _, a = oracle.paged_attention(q.reshape(-1, layer.h, d).contiguous(), kc, vc, layer.kvh, layer.scale, bt, sl,
                                       cfg.block_size, None, cfg.kv_cache_dtype, 1.0, 1.0)
-        x = x + _bf16(oracle.gemm(a.reshape(-1, layer.q_size), _dq(layer.o)))
-        gu = _bf16(oracle.gemm(x, _dq(layer.gate_up)))
-        gate, up = gu.chunk(2, dim=-1)
-        x = x + _bf16(oracle.gemm(torch.nn.functional.silu(gate) * up, _dq(layer.down)))
-    return x
+        o = _bf16(oracle.gemm(a.reshape(-1, layer.q_size), _dq(layer.o)))
+        h, residual = lg.fused_add_rms_norm(o, residual, layer.post_attention_layernorm.cpu(), cfg.rms_norm_eps)
+        gu = _bf16(oracle.gemm(h, _dq(layer.gate_up)))
+        x = _bf16(oracle.gemm(lg.silu_and_mul(gu), _dq(layer.down)))
+    return lg.fused_add_rms_norm(x, residual, model.norm.cpu(), cfg.rms_norm_eps)[0]
 
 
 @pytest.mark.parametrize("kv", ["auto", "fp8"])
@@ -74,7 +82,7 @@ def test_decode_step_under_cuda_graph_is_repeatable():
     g2 = model.step().clone()
     assert torch.equal(g1, g2)
     assert torch.allclose(g1.float(), eager.float(), rtol=2e-2, atol=1e-3)
-    assert model.launches_per_step() == 21
+    assert model.launches_per_step() == 34
 
 
 def _free_port():

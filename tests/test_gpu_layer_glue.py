@@ -1,0 +1,192 @@
+"""Decode-layer glue on the GPU (rms_norm, fused_add_rms_norm, silu_and_mul, rotary_embedding): against the
+reference-Python fixtures, the oracle (oracle/layer_glue.py) and - when oracle/_ref/refcuda.so is built - the
+reference's own CUDA kernels. Shapes follow /root/reference/tests/kernels/test_layernorm.py,
+test_activation.py and test_pos_encoding.py.
+
+Tolerances: silu_and_mul and rotary_embedding are elementwise with the reference's roundings -> bit-exact against
+the reference CUDA kernels and the oracle (rotary; SiLU up to the libm/CUDA expf difference on the CPU oracle).
+The norms differ from the reference only through the order of the fp32 sum of squares: at most 1 ulp of the
+storage type on a tiny fraction of elements."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import aphrodite_fork_b200 as A
+from oracle import layer_glue as lg
+from oracle import oracle
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+DEV = "cuda"
+DT = {0: torch.float32, 1: torch.float16, 2: torch.bfloat16}
+DTYPES = [torch.bfloat16, torch.float16, torch.float32]
+
+
+def _t(a, dt):
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    return (t.view(dt) if dt in (torch.float16, torch.bfloat16) else t).to(DEV)
+
+
+def _ulp_close(a: torch.Tensor, b: torch.Tensor, frac: float = 0.01):
+    """Equal except for at most `frac` of the elements, which may differ by one unit in the last place."""
+    if a.dtype == torch.float32:
+        torch.testing.assert_close(a, b, atol=1e-6, rtol=1e-5)
+        return
+    ia, ib = a.view(torch.int16).int(), b.view(torch.int16).int()
+    d = (ia - ib).abs()
+    assert int(d.max()) <= 1, int(d.max())
+    assert float((d > 0).float().mean()) <= frac, float((d > 0).float().mean())
+
+
+def _ref():
+    r = oracle.refcuda()
+    return r if r is not None and hasattr(r, "rms_norm") else None
+
+
+def test_glue_golden_fixtures():
+    g = np.load(os.path.join(G, "glue_golden.npz"))
+    for ci in range(int(g["num_norm"][0])):
+        pre = f"norm{ci}_"
+        dt = DT[int(g[pre + "meta"][2])]
+        x, res, w = _t(g[pre + "x"], dt), _t(g[pre + "res"], dt), _t(g[pre + "w"], dt)
+        eps = float(g[pre + "eps"][0])
+        out = torch.empty_like(x)
+        A.ops.rms_norm(out, x, w, eps)
+        torch.testing.assert_close(out, _t(g[pre + "out"], dt), atol=1e-2, rtol=1e-2)
+        xi, ri = x.clone(), res.clone()
+        A.ops.fused_add_rms_norm(xi, ri, w, eps)
+        torch.testing.assert_close(xi, _t(g[pre + "fused_out"], dt), atol=1e-2, rtol=1e-2)
+        torch.testing.assert_close(ri, _t(g[pre + "fused_res"], dt), atol=1e-6, rtol=1e-6)
+        sx = _t(g[pre + "silu_x"], dt)
+        so = torch.empty(sx.shape[0], sx.shape[1] // 2, dtype=dt, device=DEV)
+        A.ops.silu_and_mul(so, sx)
+        torch.testing.assert_close(so, _t(g[pre + "silu_out"], dt), atol=1e-3, rtol=1e-2)
+    for ci in range(int(g["num_rope"][0])):
+        pre = f"rope{ci}_"
+        t, nh, nkv, d, rot, neox, dc = (int(v) for v in g[pre + "meta"])
+        dt = DT[dc]
+        cache = torch.zeros(4096, rot, dtype=dt, device=DEV)
+        cache[torch.from_numpy(g[pre + "cache_rows"]).to(DEV)] = _t(g[pre + "cache"], dt)
+        q, k = _t(g[pre + "q"], dt), _t(g[pre + "k"], dt)
+        A.ops.rotary_embedding(torch.from_numpy(g[pre + "pos"]).to(DEV), q, k, d, cache, bool(neox))
+        if dt == torch.float32:
+            torch.testing.assert_close(q, _t(g[pre + "q_out"], dt), atol=1e-6, rtol=1e-6)
+            torch.testing.assert_close(k, _t(g[pre + "k_out"], dt), atol=1e-6, rtol=1e-6)
+        else:
+            assert torch.equal(q, _t(g[pre + "q_out"], dt)) and torch.equal(k, _t(g[pre + "k_out"], dt)), ci
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("tokens,hidden", [(1, 4096), (7, 768), (64, 4096), (83, 5120), (64, 8192), (4096, 4096), (5, 8199),
+                                           (3, 40000)])
+def test_rms_norm_and_fused_add(tokens, hidden, dtype):
+    gen = torch.Generator(device=DEV).manual_seed(tokens + hidden)
+    x = torch.randn(tokens, hidden, device=DEV, generator=gen).to(dtype)
+    res = torch.randn(tokens, hidden, device=DEV, generator=gen).to(dtype)
+    w = (1 + 0.1 * torch.randn(hidden, device=DEV, generator=gen)).to(dtype)
+    out = torch.empty_like(x)
+    A.ops.rms_norm(out, x, w, 1e-6)
+    xi, ri = x.clone(), res.clone()
+    A.ops.fused_add_rms_norm(xi, ri, w, 1e-6)
+    want = lg.rms_norm(x.cpu(), w.cpu(), 1e-6)
+    wo, wr = lg.fused_add_rms_norm(x.cpu(), res.cpu(), w.cpu(), 1e-6)
+    _ulp_close(out.cpu(), want)
+    _ulp_close(xi.cpu(), wo)
+    assert torch.equal(ri.cpu(), wr)
+    ref = _ref()
+    if ref is not None:
+        ro = torch.empty_like(x)
+        ref.rms_norm(ro, x, w, 1e-6)
+        rx, rr = x.clone(), res.clone()
+        ref.fused_add_rms_norm(rx, rr, w, 1e-6)
+        _ulp_close(out, ro)
+        _ulp_close(xi, rx)
+        assert torch.equal(ri, rr)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("tokens,d", [(1, 14336), (7, 512), (64, 14336), (83, 13824), (2048, 14336), (5, 1001)])
+def test_silu_and_mul(tokens, d, dtype):
+    gen = torch.Generator(device=DEV).manual_seed(tokens + d)
+    x = (torch.randn(tokens, 2 * d, device=DEV, generator=gen) * 3).to(dtype)
+    out = torch.empty(tokens, d, dtype=dtype, device=DEV)
+    A.ops.silu_and_mul(out, x)
+    _ulp_close(out.cpu(), lg.silu_and_mul(x.cpu()), frac=0.02)
+    ref = _ref()
+    if ref is not None:
+        ro = torch.empty_like(out)
+        ref.silu_and_mul(ro, x)
+        assert torch.equal(out, ro)
+
+
+def test_silu_and_mul_more_tokens_than_one_grid():
+    x = torch.randn(70000, 2 * 64, device=DEV).to(torch.bfloat16)
+    out = torch.empty(70000, 64, dtype=torch.bfloat16, device=DEV)
+    A.ops.silu_and_mul(out, x)
+    _ulp_close(out[-3000:].cpu(), lg.silu_and_mul(x[-3000:].cpu()), frac=0.02)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("neox", [True, False])
+@pytest.mark.parametrize("tokens,nh,nkv,d,rot", [(64, 32, 8, 128, 128), (1, 8, 1, 128, 128), (11, 12, 12, 64, 32), (7, 6, 2, 96, 96),
+                                                 (300, 64, 8, 128, 64), (5, 4, 4, 256, 256)])
+def test_rotary_embedding(tokens, nh, nkv, d, rot, neox, dtype):
+    gen = torch.Generator(device=DEV).manual_seed(tokens + nh + d)
+    max_pos = 8192
+    inv = 1.0 / (10000 ** (torch.arange(0, rot, 2, dtype=torch.float) / rot))
+    fr = torch.einsum("i,j->ij", torch.arange(max_pos, dtype=torch.float), inv)
+    cache = torch.cat((fr.cos(), fr.sin()), -1).to(dtype).to(DEV)
+    pos = torch.randint(0, max_pos, (tokens,), device=DEV, generator=gen)
+    # q and k as slices of one qkv projection output: token stride larger than the row
+    qkv = torch.randn(tokens, (nh + 2 * nkv) * d, device=DEV, generator=gen).to(dtype)
+    q, k, v = qkv.split([nh * d, nkv * d, nkv * d], dim=-1)
+    v0 = v.clone()
+    wq, wk = lg.rotary_embedding(pos.cpu(), q.cpu().contiguous(), k.cpu().contiguous(), d, cache.cpu(), neox)
+    ref = _ref()
+    if ref is not None:
+        rq, rk = q.contiguous(), k.contiguous()
+        ref.rotary_embedding(pos, rq, rk, d, cache, neox)
+    A.ops.rotary_embedding(pos, q, k, d, cache, neox)
+    assert torch.equal(v, v0)
+    if dtype == torch.float32:
+        torch.testing.assert_close(q.cpu(), wq, atol=1e-6, rtol=1e-6)
+        torch.testing.assert_close(k.cpu(), wk, atol=1e-6, rtol=1e-6)
+    else:
+        assert torch.equal(q.cpu(), wq) and torch.equal(k.cpu(), wk)
+    if ref is not None:
+        if dtype == torch.float32:
+            torch.testing.assert_close(q, rq, atol=1e-6, rtol=1e-6)
+            torch.testing.assert_close(k, rk, atol=1e-6, rtol=1e-6)
+        else:
+            assert torch.equal(q, rq) and torch.equal(k, rk)
+
+
+def test_rotary_embedding_batched_positions_shape():
+    """positions [batch, seq] with query [batch, seq, heads * head_size] (pos_encoding_kernels.cu:149-156)."""
+    b, s, nh, d = 3, 5, 4, 64
+    cache = torch.randn(128, d, device=DEV).to(torch.bfloat16)
+    pos = torch.randint(0, 128, (b, s), device=DEV)
+    q = torch.randn(b, s, nh * d, device=DEV).to(torch.bfloat16)
+    k = torch.randn(b, s, nh * d, device=DEV).to(torch.bfloat16)
+    wq, wk = lg.rotary_embedding(pos.cpu(), q.cpu().reshape(b * s, -1), k.cpu().reshape(b * s, -1), d, cache.cpu(), True)
+    A.ops.rotary_embedding(pos, q, k, d, cache, True)
+    assert torch.equal(q.cpu().reshape(b * s, -1), wq) and torch.equal(k.cpu().reshape(b * s, -1), wk)
+
+
+def test_glue_errors_and_empty():
+    x = torch.zeros(0, 64, dtype=torch.bfloat16, device=DEV)
+    w = torch.ones(64, dtype=torch.bfloat16, device=DEV)
+    A.ops.rms_norm(torch.empty_like(x), x, w, 1e-6)
+    A.ops.fused_add_rms_norm(x, x.clone(), w, 1e-6)
+    A.ops.silu_and_mul(torch.zeros(0, 32, dtype=torch.bfloat16, device=DEV), x)
+    y = torch.zeros(4, 64, dtype=torch.bfloat16, device=DEV)
+    with pytest.raises(RuntimeError, match="dtype mismatch"):
+        A.ops.rms_norm(torch.empty_like(y), y, w.float(), 1e-6)
+    with pytest.raises(RuntimeError, match="shape mismatch"):
+        A.ops.rms_norm(torch.empty_like(y), y, w[:32], 1e-6)
+    with pytest.raises(RuntimeError, match="same number of tokens"):
+        A.ops.rotary_embedding(torch.zeros(3, dtype=torch.int64, device=DEV), y, y.clone(), 64, torch.zeros(8, 64, dtype=torch.bfloat16, device=DEV), True)
+    with pytest.raises(RuntimeError):  # CPU tensors: the dispatcher has no CPU kernel for the op (no fallback)
+        A.ops.silu_and_mul(torch.zeros(4, 32, dtype=torch.bfloat16), y.cpu())

@@ -175,3 +175,47 @@ def test_repack_oracle_matches_reference_python():
         if act:
             np.testing.assert_array_equal(
                 mf.gptq_marlin_repack(g[f"c{ci}_gptq"], g[f"c{ci}_sort_indices"], k, n, bits), g[f"c{ci}_marlin_sorted"])
+
+
+def _rope_cache(g, pre, dt):
+    """Rebuild a [max_position, rot_dim] table holding the rows the fixture carries."""
+    rows = torch.from_numpy(g[pre + "cache_rows"])
+    part = _t(g[pre + "cache"], dt)
+    cache = torch.zeros(4096, part.shape[1], dtype=dt)
+    cache[rows] = part
+    return cache
+
+
+def test_glue_oracle_matches_reference_forward_native():
+    """oracle/layer_glue.py against the reference's RMSNorm / SiluAndMul / RotaryEmbedding forward_native
+    (tests/golden/make_golden.py make_glue). Rotary embedding rounds at the same places in both and must be
+    bit-exact; the norms and SiLU round to the storage type at different places in the CUDA kernels (which the
+    oracle follows) and in forward_native, so they carry the tolerance of the reference's own kernel tests
+    (tests/kernels/test_layernorm.py: atol = rtol = 1e-2)."""
+    from oracle import layer_glue as lg
+    g = np.load(os.path.join(G, "glue_golden.npz"))
+    for ci in range(int(g["num_norm"][0])):
+        pre = f"norm{ci}_"
+        dt = DT[int(g[pre + "meta"][2])]
+        x, res, w = _t(g[pre + "x"], dt), _t(g[pre + "res"], dt), _t(g[pre + "w"], dt)
+        eps = float(g[pre + "eps"][0])
+        torch.testing.assert_close(lg.rms_norm(x, w, eps), _t(g[pre + "out"], dt), atol=1e-2, rtol=1e-2)
+        o, r = lg.fused_add_rms_norm(x, res, w, eps)
+        torch.testing.assert_close(o, _t(g[pre + "fused_out"], dt), atol=1e-2, rtol=1e-2)
+        if dt == torch.float32:
+            torch.testing.assert_close(r, _t(g[pre + "fused_res"], dt), atol=1e-6, rtol=1e-6)
+        else:
+            assert torch.equal(r, _t(g[pre + "fused_res"], dt))  # one rounding of the same fp32 sum
+        torch.testing.assert_close(lg.silu_and_mul(_t(g[pre + "silu_x"], dt)), _t(g[pre + "silu_out"], dt), atol=1e-3,
+                                   rtol=1e-2)
+    for ci in range(int(g["num_rope"][0])):
+        pre = f"rope{ci}_"
+        t, nh, nkv, d, rot, neox, dc = (int(v) for v in g[pre + "meta"])
+        dt = DT[dc]
+        q, k = lg.rotary_embedding(torch.from_numpy(g[pre + "pos"]), _t(g[pre + "q"], dt), _t(g[pre + "k"], dt), d,
+                                   _rope_cache(g, pre, dt), bool(neox))
+        if dt == torch.float32:
+            torch.testing.assert_close(q, _t(g[pre + "q_out"], dt), atol=1e-6, rtol=1e-6)
+            torch.testing.assert_close(k, _t(g[pre + "k_out"], dt), atol=1e-6, rtol=1e-6)
+        else:
+            assert torch.equal(q, _t(g[pre + "q_out"], dt)) and torch.equal(k, _t(g[pre + "k_out"], dt)), ci
