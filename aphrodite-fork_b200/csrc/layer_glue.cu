@@ -172,6 +172,51 @@ __global__ void __launch_bounds__(512)
   }
 }
 
+// 16-byte version: a thread owns PV consecutive rotation pairs of one head. NeoX: PV = 8 (2-byte types), the x and y
+// halves are two vectors; GPT-J: PV = 4, one vector holds the four interleaved (x, y) pairs.
+template <typename T, bool NEOX>
+__global__ void __launch_bounds__(512)
+    rotary_embedding_vec_kernel(const int64_t* __restrict__ positions, T* __restrict__ query, T* __restrict__ key,
+                                const T* __restrict__ cos_sin_cache, int rot_dim, int64_t query_stride, int64_t key_stride,
+                                int num_heads, int num_kv_heads, int head_size) {
+  constexpr int VEC = 16 / (int)sizeof(T);
+  constexpr int PV = NEOX ? VEC : VEC / 2;
+  using V = Vec<T, VEC>;
+  using H = Vec<T, PV>;
+  pdl_trigger();
+  const int token = blockIdx.x;
+  const int embed = rot_dim / 2, per_head = embed / PV;
+  const T* cache = cos_sin_cache + positions[token] * rot_dim;
+  const int nq = num_heads * per_head, total = nq + (key != nullptr ? num_kv_heads * per_head : 0);
+  pdl_wait();
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const bool is_q = i < nq;
+    const int j = is_q ? i : i - nq;
+    const int head = j / per_head, off = (j % per_head) * PV;
+    T* arr = (is_q ? query + token * query_stride : key + token * key_stride) + (int64_t)head * head_size;
+    const H c = *reinterpret_cast<const H*>(cache + off), s = *reinterpret_cast<const H*>(cache + embed + off);
+    if constexpr (NEOX) {
+      V x = *reinterpret_cast<V*>(arr + off), y = *reinterpret_cast<V*>(arr + embed + off);
+      V ox, oy;
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) {
+        ox.v[e] = sub_t(mul_t(x.v[e], c.v[e]), mul_t(y.v[e], s.v[e]));
+        oy.v[e] = add_t(mul_t(y.v[e], c.v[e]), mul_t(x.v[e], s.v[e]));
+      }
+      *reinterpret_cast<V*>(arr + off) = ox;
+      *reinterpret_cast<V*>(arr + embed + off) = oy;
+    } else {
+      V xy = *reinterpret_cast<V*>(arr + 2 * off), o;
+#pragma unroll
+      for (int e = 0; e < PV; ++e) {
+        o.v[2 * e] = sub_t(mul_t(xy.v[2 * e], c.v[e]), mul_t(xy.v[2 * e + 1], s.v[e]));
+        o.v[2 * e + 1] = add_t(mul_t(xy.v[2 * e + 1], c.v[e]), mul_t(xy.v[2 * e], s.v[e]));
+      }
+      *reinterpret_cast<V*>(arr + 2 * off) = o;
+    }
+  }
+}
+
 template <typename T, bool FUSED>
 int launch_norm(T* out, T* input, T* residual, const T* weight, float eps, int64_t tokens, int hidden, int64_t in_stride,
                 cudaStream_t stream) {
@@ -208,14 +253,23 @@ int launch_silu(T* out, const T* input, int64_t tokens, int d, cudaStream_t stre
 template <typename T>
 int launch_rope(const int64_t* positions, T* q, T* k, const T* cache, int rot_dim, int64_t qs, int64_t ks, int nh, int nkv,
                 int head_size, bool neox, int64_t tokens, cudaStream_t stream) {
-  const int work = (nh + (k ? nkv : 0)) * rot_dim / 2;
+  constexpr int VEC = 16 / (int)sizeof(T);
+  const int pv = neox ? VEC : VEC / 2;
+  const bool vec_ok = (rot_dim / 2) % VEC == 0 && head_size % VEC == 0 && qs % VEC == 0 && (k == nullptr || ks % VEC == 0) &&
+                      aligned16(q) && (k == nullptr || aligned16(k)) && aligned16(cache);
+  const int work = (nh + (k ? nkv : 0)) * (rot_dim / 2) / (vec_ok ? pv : 1);
   const int threads = std::min(512, std::max(32, (work + 31) / 32 * 32));
-  if (neox)
-    APH_LAUNCH_PDL(rotary_embedding_kernel<T, true>, dim3((unsigned)tokens), dim3(threads), 0, stream, positions, q, k, cache, rot_dim,
-                   qs, ks, nh, nkv, head_size);
-  else
-    APH_LAUNCH_PDL(rotary_embedding_kernel<T, false>, dim3((unsigned)tokens), dim3(threads), 0, stream, positions, q, k, cache, rot_dim,
-                   qs, ks, nh, nkv, head_size);
+#define APH_ROPE(KERN, NEOX)                                                                                                  \
+  APH_LAUNCH_PDL(KERN<T, NEOX>, dim3((unsigned)tokens), dim3(threads), 0, stream, positions, q, k, cache, rot_dim, qs, ks, nh, nkv, \
+                 head_size)
+  if (vec_ok) {
+    if (neox) APH_ROPE(rotary_embedding_vec_kernel, true);
+    else APH_ROPE(rotary_embedding_vec_kernel, false);
+  } else {
+    if (neox) APH_ROPE(rotary_embedding_kernel, true);
+    else APH_ROPE(rotary_embedding_kernel, false);
+  }
+#undef APH_ROPE
   return APH_OK;
 }
 

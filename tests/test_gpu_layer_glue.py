@@ -5,7 +5,7 @@ test_activation.py and test_pos_encoding.py.
 
 Tolerances: silu_and_mul and rotary_embedding are elementwise with the reference's roundings -> bit-exact against
 the reference CUDA kernels and the oracle (rotary; SiLU up to the libm/CUDA expf difference on the CPU oracle).
-The norms differ from the reference only through the order of the fp32 sum of squares: at most 1 ulp of the
+The norms differ from the reference only through the order of the fp32 sum of squares: at most 2 ulp of the
 storage type on a tiny fraction of elements."""
 import os
 
@@ -30,13 +30,14 @@ def _t(a, dt):
 
 
 def _ulp_close(a: torch.Tensor, b: torch.Tensor, frac: float = 0.01):
-    """Equal except for at most `frac` of the elements, which may differ by one unit in the last place."""
+    """Equal except for at most `frac` of the elements, which may differ by up to two units in the last place (one ulp
+    in the rounding of x * rsqrt, carried through the multiplication by a weight > 1)."""
     if a.dtype == torch.float32:
         torch.testing.assert_close(a, b, atol=1e-6, rtol=1e-5)
         return
     ia, ib = a.view(torch.int16).int(), b.view(torch.int16).int()
     d = (ia - ib).abs()
-    assert int(d.max()) <= 1, int(d.max())
+    assert int(d.max()) <= 2, int(d.max())
     assert float((d > 0).float().mean()) <= frac, float((d > 0).float().mean())
 
 
@@ -131,7 +132,7 @@ def test_silu_and_mul_more_tokens_than_one_grid():
 @pytest.mark.parametrize("dtype", DTYPES)
 @pytest.mark.parametrize("neox", [True, False])
 @pytest.mark.parametrize("tokens,nh,nkv,d,rot", [(64, 32, 8, 128, 128), (1, 8, 1, 128, 128), (11, 12, 12, 64, 32), (7, 6, 2, 96, 96),
-                                                 (300, 64, 8, 128, 64), (5, 4, 4, 256, 256)])
+                                                 (300, 64, 8, 128, 64), (5, 4, 4, 256, 256), (3, 4, 2, 80, 20), (9, 8, 8, 64, 8)])
 def test_rotary_embedding(tokens, nh, nkv, d, rot, neox, dtype):
     gen = torch.Generator(device=DEV).manual_seed(tokens + nh + d)
     max_pos = 8192
