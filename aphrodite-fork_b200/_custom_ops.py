@@ -184,3 +184,49 @@ def rms_norm(out: torch.Tensor, input: torch.Tensor, weight: torch.Tensor, epsil
 
 def fused_add_rms_norm(input: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
     _ops()[0].fused_add_rms_norm(input, residual, weight, epsilon)
+
+
+# aphrodite/_custom_ops.py:36-72: the other activations of kernels/activation_kernels.cu
+def mul_and_silu(out: torch.Tensor, x: torch.Tensor) -> None:
+    _ops()[0].mul_and_silu(out, x)
+
+
+def gelu_and_mul(out: torch.Tensor, x: torch.Tensor) -> None:
+    _ops()[0].gelu_and_mul(out, x)
+
+
+def gelu_tanh_and_mul(out: torch.Tensor, x: torch.Tensor) -> None:
+    _ops()[0].gelu_tanh_and_mul(out, x)
+
+
+def fatrelu_and_mul(out: torch.Tensor, x: torch.Tensor, threshold: float = 0.0) -> None:
+    _ops()[0].fatrelu_and_mul(out, x, threshold)
+
+
+def gelu_fast(out: torch.Tensor, x: torch.Tensor) -> None:
+    _ops()[0].gelu_fast(out, x)
+
+
+def gelu_new(out: torch.Tensor, x: torch.Tensor) -> None:
+    _ops()[0].gelu_new(out, x)
+
+
+def gelu_quick(out: torch.Tensor, x: torch.Tensor) -> None:
+    _ops()[0].gelu_quick(out, x)
+
+
+# aphrodite/_custom_ops.py:195-208
+def batched_rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor, head_size: int,
+                             cos_sin_cache: torch.Tensor, is_neox: bool, rot_dim: int,
+                             cos_sin_cache_offsets: torch.Tensor) -> None:
+    _ops()[0].batched_rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox, rot_dim,
+                                       cos_sin_cache_offsets)
+
+
+# aphrodite/_custom_ops.py:222-232
+def advance_step_flashattn(num_seqs: int, num_queries: int, block_size: int, input_tokens: torch.Tensor,
+                           sampled_token_ids: torch.Tensor, input_positions: torch.Tensor, seq_lens: torch.Tensor,
+                           slot_mapping: torch.Tensor, block_tables: torch.Tensor) -> None:
+    """Advance a step on GPU for existing inputs for a multi-step runner"""
+    return _ops()[0].advance_step_flashattn(num_seqs, num_queries, block_size, input_tokens, sampled_token_ids,
+                                            input_positions, seq_lens, slot_mapping, block_tables)

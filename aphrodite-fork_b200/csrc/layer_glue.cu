@@ -126,10 +126,43 @@ __global__ void __launch_bounds__(1024, 1)
   }
 }
 
-// grid (ceil(d / (VEC * blockDim)), tokens)
-template <typename T, int VEC>
+// The activation functions of activation_kernels.cu:35-62,111-115,183-205, rounding to T where the reference does.
+enum : int { ACT_SILU = 0, ACT_GELU = 1, ACT_GELU_TANH = 2, ACT_FATRELU = 3, ACT_GELU_NEW = 4, ACT_GELU_FAST = 5, ACT_GELU_QUICK = 6 };
+
+template <typename T, int ACT>
+__device__ __forceinline__ T act_fn(T x, float param) {
+  using S = ScalarTraits<T>;
+  const float f = S::to_float(x);
+  if constexpr (ACT == ACT_SILU) {
+    return S::from_float(__fdiv_rn(f, 1.0f + expf(-f)));
+  } else if constexpr (ACT == ACT_GELU) {
+    constexpr float ALPHA = M_SQRT1_2;
+    return S::from_float(f * 0.5f * (1.0f + ::erf(f * ALPHA)));
+  } else if constexpr (ACT == ACT_GELU_TANH) {
+    constexpr float BETA = M_SQRT2 * M_2_SQRTPI * 0.5f;
+    constexpr float KAPPA = 0.044715;
+    float x_cube = f * f * f;
+    float inner = BETA * (f + KAPPA * x_cube);
+    return S::from_float(0.5f * f * (1.0f + ::tanhf(inner)));
+  } else if constexpr (ACT == ACT_FATRELU) {
+    return S::from_float(f > param ? f : 0.0f);
+  } else if constexpr (ACT == ACT_GELU_NEW) {
+    const float x3 = S::to_float(mul_t(mul_t(x, x), x));
+    const T t = S::from_float(tanhf(S::to_float(S::from_float(0.79788456f * S::to_float(add_t(x, S::from_float(0.044715f * x3)))))));
+    return mul_t(mul_t(S::from_float(0.5f), x), add_t(S::from_float(1.0f), t));
+  } else if constexpr (ACT == ACT_GELU_FAST) {
+    const T arg = mul_t(S::from_float(f * 0.79788456f), add_t(S::from_float(1.0f), mul_t(S::from_float(0.044715f * f), x)));
+    const T t = S::from_float(tanhf(S::to_float(arg)));
+    return mul_t(mul_t(S::from_float(0.5f), x), add_t(S::from_float(1.0f), t));
+  } else {
+    return S::from_float(__fdiv_rn(f, 1.0f + expf(-1.702f * f)));
+  }
+}
+
+// out[t][i] = act(in[t][i]) * in[t][d + i]  (ACT_FIRST) or in[t][i] * act(in[t][d + i]).  grid (ceil(d / (VEC * 256)), tokens)
+template <typename T, int VEC, int ACT, bool ACT_FIRST>
 __global__ void __launch_bounds__(256)
-    silu_and_mul_kernel(T* __restrict__ out, const T* __restrict__ input, int d) {
+    act_and_mul_kernel(T* __restrict__ out, const T* __restrict__ input, int d, float param) {
   using V = Vec<T, VEC>;
   pdl_trigger();
   pdl_wait();
@@ -140,23 +173,37 @@ __global__ void __launch_bounds__(256)
   const V y = reinterpret_cast<const V*>(input + token * 2 * d + d)[idx];
   V o;
 #pragma unroll
-  for (int e = 0; e < VEC; ++e) {
-    const float f = ScalarTraits<T>::to_float(x.v[e]);
-    o.v[e] = mul_t(ScalarTraits<T>::from_float(__fdiv_rn(f, 1.0f + expf(-f))), y.v[e]);
-  }
+  for (int e = 0; e < VEC; ++e)
+    o.v[e] = ACT_FIRST ? mul_t(act_fn<T, ACT>(x.v[e], param), y.v[e]) : mul_t(x.v[e], act_fn<T, ACT>(y.v[e], param));
   reinterpret_cast<V*>(out + token * d)[idx] = o;
+}
+
+// out[i] = act(in[i]) over a flat array
+template <typename T, int VEC, int ACT>
+__global__ void __launch_bounds__(256) activation_kernel(T* __restrict__ out, const T* __restrict__ input, int64_t n) {
+  using V = Vec<T, VEC>;
+  pdl_trigger();
+  pdl_wait();
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n / VEC) return;
+  const V x = reinterpret_cast<const V*>(input)[idx];
+  V o;
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) o.v[e] = act_fn<T, ACT>(x.v[e], 0.f);
+  reinterpret_cast<V*>(out)[idx] = o;
 }
 
 // One CTA per token; a thread owns one (head, rotation pair) at a time, query heads first, then key heads.
 template <typename T, bool NEOX>
 __global__ void __launch_bounds__(512)
     rotary_embedding_kernel(const int64_t* __restrict__ positions, T* __restrict__ query, T* __restrict__ key,
-                            const T* __restrict__ cos_sin_cache, int rot_dim, int64_t query_stride, int64_t key_stride,
-                            int num_heads, int num_kv_heads, int head_size) {
+                            const T* __restrict__ cos_sin_cache, const int64_t* __restrict__ cache_offsets, int rot_dim,
+                            int64_t query_stride, int64_t key_stride, int num_heads, int num_kv_heads, int head_size) {
   pdl_trigger();
   const int token = blockIdx.x;
   const int embed = rot_dim / 2;
-  const T* cache = cos_sin_cache + positions[token] * rot_dim;  // positions and the table are step inputs, not kernel outputs
+  // positions, offsets and the table are step inputs, not outputs of the previous kernel
+  const T* cache = cos_sin_cache + (positions[token] + (cache_offsets ? cache_offsets[token] : 0)) * rot_dim;
   pdl_wait();
   const int nq = num_heads * embed, total = nq + (key != nullptr ? num_kv_heads * embed : 0);
   for (int i = threadIdx.x; i < total; i += blockDim.x) {
@@ -177,8 +224,8 @@ __global__ void __launch_bounds__(512)
 template <typename T, bool NEOX>
 __global__ void __launch_bounds__(512)
     rotary_embedding_vec_kernel(const int64_t* __restrict__ positions, T* __restrict__ query, T* __restrict__ key,
-                                const T* __restrict__ cos_sin_cache, int rot_dim, int64_t query_stride, int64_t key_stride,
-                                int num_heads, int num_kv_heads, int head_size) {
+                                const T* __restrict__ cos_sin_cache, const int64_t* __restrict__ cache_offsets, int rot_dim,
+                                int64_t query_stride, int64_t key_stride, int num_heads, int num_kv_heads, int head_size) {
   constexpr int VEC = 16 / (int)sizeof(T);
   constexpr int PV = NEOX ? VEC : VEC / 2;
   using V = Vec<T, VEC>;
@@ -186,7 +233,7 @@ __global__ void __launch_bounds__(512)
   pdl_trigger();
   const int token = blockIdx.x;
   const int embed = rot_dim / 2, per_head = embed / PV;
-  const T* cache = cos_sin_cache + positions[token] * rot_dim;
+  const T* cache = cos_sin_cache + (positions[token] + (cache_offsets ? cache_offsets[token] : 0)) * rot_dim;
   const int nq = num_heads * per_head, total = nq + (key != nullptr ? num_kv_heads * per_head : 0);
   pdl_wait();
   for (int i = threadIdx.x; i < total; i += blockDim.x) {
@@ -217,6 +264,31 @@ __global__ void __launch_bounds__(512)
   }
 }
 
+// Multi-step decode bookkeeping (prepare_inputs/advance_step.cu:12-66): after sampling, move every running query one
+// token forward without a host round trip. One thread per query; block 0 also clears the CUDA-graph padding rows.
+__global__ void __launch_bounds__(256)
+    advance_step_flashattn_kernel(int num_seqs, int num_queries, int block_size, int64_t* __restrict__ input_tokens,
+                                  const int64_t* __restrict__ sampled_token_ids, int64_t* __restrict__ input_positions,
+                                  int* __restrict__ seq_lens, int64_t* __restrict__ slot_mapping,
+                                  const int* __restrict__ block_tables, int64_t block_tables_stride) {
+  pdl_trigger();
+  pdl_wait();
+  if (blockIdx.x == 0) {
+    for (int i = num_queries + threadIdx.x; i < num_seqs; i += blockDim.x) {
+      input_tokens[i] = 0;
+      input_positions[i] = 0;
+      slot_mapping[i] = -1;
+    }
+  }
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= num_queries) return;
+  input_tokens[q] = sampled_token_ids[q];
+  const int next_len = seq_lens[q] + 1, pos = next_len - 1;
+  seq_lens[q] = next_len;
+  input_positions[q] = pos;
+  slot_mapping[q] = (int64_t)(block_tables[block_tables_stride * q + pos / block_size] * block_size + pos % block_size);
+}
+
 template <typename T, bool FUSED>
 int launch_norm(T* out, T* input, T* residual, const T* weight, float eps, int64_t tokens, int hidden, int64_t in_stride,
                 cudaStream_t stream) {
@@ -238,21 +310,55 @@ int launch_norm(T* out, T* input, T* residual, const T* weight, float eps, int64
   return APH_OK;
 }
 
-template <typename T>
-int launch_silu(T* out, const T* input, int64_t tokens, int d, cudaStream_t stream) {
+template <typename T, int ACT, bool ACT_FIRST>
+int launch_gated(T* out, const T* input, int64_t tokens, int d, float param, cudaStream_t stream) {
   constexpr int VEC = 16 / (int)sizeof(T);
   if (d % VEC == 0 && aligned16(out) && aligned16(input)) {
-    APH_LAUNCH_PDL(silu_and_mul_kernel<T, VEC>, dim3((unsigned)((d / VEC + 255) / 256), (unsigned)tokens), dim3(256), 0, stream, out,
-                   input, d);
+    APH_LAUNCH_PDL((act_and_mul_kernel<T, VEC, ACT, ACT_FIRST>), dim3((unsigned)((d / VEC + 255) / 256), (unsigned)tokens), dim3(256), 0,
+                   stream, out, input, d, param);
   } else {
-    APH_LAUNCH_PDL(silu_and_mul_kernel<T, 1>, dim3((unsigned)((d + 255) / 256), (unsigned)tokens), dim3(256), 0, stream, out, input, d);
+    APH_LAUNCH_PDL((act_and_mul_kernel<T, 1, ACT, ACT_FIRST>), dim3((unsigned)((d + 255) / 256), (unsigned)tokens), dim3(256), 0, stream,
+                   out, input, d, param);
   }
   return APH_OK;
 }
 
 template <typename T>
-int launch_rope(const int64_t* positions, T* q, T* k, const T* cache, int rot_dim, int64_t qs, int64_t ks, int nh, int nkv,
-                int head_size, bool neox, int64_t tokens, cudaStream_t stream) {
+int launch_gated_any(int act, T* out, const T* input, int64_t tokens, int d, float param, cudaStream_t stream) {
+  switch (act) {
+    case APH_ACT_SILU_AND_MUL: return launch_gated<T, ACT_SILU, true>(out, input, tokens, d, param, stream);
+    case APH_ACT_MUL_AND_SILU: return launch_gated<T, ACT_SILU, false>(out, input, tokens, d, param, stream);
+    case APH_ACT_GELU_AND_MUL: return launch_gated<T, ACT_GELU, true>(out, input, tokens, d, param, stream);
+    case APH_ACT_GELU_TANH_AND_MUL: return launch_gated<T, ACT_GELU_TANH, true>(out, input, tokens, d, param, stream);
+    case APH_ACT_FATRELU_AND_MUL: return launch_gated<T, ACT_FATRELU, true>(out, input, tokens, d, param, stream);
+    default: return set_error(APH_ERR_INVALID_ARGUMENT, "act_and_mul: unknown activation %d", act);
+  }
+}
+
+template <typename T, int ACT>
+int launch_act(T* out, const T* input, int64_t n, cudaStream_t stream) {
+  constexpr int VEC = 16 / (int)sizeof(T);
+  if (n % VEC == 0 && aligned16(out) && aligned16(input)) {
+    APH_LAUNCH_PDL((activation_kernel<T, VEC, ACT>), dim3((unsigned)((n / VEC + 255) / 256)), dim3(256), 0, stream, out, input, n);
+  } else {
+    APH_LAUNCH_PDL((activation_kernel<T, 1, ACT>), dim3((unsigned)((n + 255) / 256)), dim3(256), 0, stream, out, input, n);
+  }
+  return APH_OK;
+}
+
+template <typename T>
+int launch_act_any(int act, T* out, const T* input, int64_t n, cudaStream_t stream) {
+  switch (act) {
+    case APH_ACT_GELU_NEW: return launch_act<T, ACT_GELU_NEW>(out, input, n, stream);
+    case APH_ACT_GELU_FAST: return launch_act<T, ACT_GELU_FAST>(out, input, n, stream);
+    case APH_ACT_GELU_QUICK: return launch_act<T, ACT_GELU_QUICK>(out, input, n, stream);
+    default: return set_error(APH_ERR_INVALID_ARGUMENT, "activation: unknown activation %d", act);
+  }
+}
+
+template <typename T>
+int launch_rope(const int64_t* positions, T* q, T* k, const T* cache, const int64_t* offsets, int rot_dim, int64_t qs, int64_t ks,
+                int nh, int nkv, int head_size, bool neox, int64_t tokens, cudaStream_t stream) {
   constexpr int VEC = 16 / (int)sizeof(T);
   const int pv = neox ? VEC : VEC / 2;
   const bool vec_ok = (rot_dim / 2) % VEC == 0 && head_size % VEC == 0 && qs % VEC == 0 && (k == nullptr || ks % VEC == 0) &&
@@ -260,8 +366,8 @@ int launch_rope(const int64_t* positions, T* q, T* k, const T* cache, int rot_di
   const int work = (nh + (k ? nkv : 0)) * (rot_dim / 2) / (vec_ok ? pv : 1);
   const int threads = std::min(512, std::max(32, (work + 31) / 32 * 32));
 #define APH_ROPE(KERN, NEOX)                                                                                                  \
-  APH_LAUNCH_PDL(KERN<T, NEOX>, dim3((unsigned)tokens), dim3(threads), 0, stream, positions, q, k, cache, rot_dim, qs, ks, nh, nkv, \
-                 head_size)
+  APH_LAUNCH_PDL(KERN<T, NEOX>, dim3((unsigned)tokens), dim3(threads), 0, stream, positions, q, k, cache, offsets, rot_dim, qs, ks, \
+                 nh, nkv, head_size)
   if (vec_ok) {
     if (neox) APH_ROPE(rotary_embedding_vec_kernel, true);
     else APH_ROPE(rotary_embedding_vec_kernel, false);
@@ -306,17 +412,30 @@ extern "C" int aph_fused_add_rms_norm(void* input, void* residual, const void* w
                                                   (int)hidden_size, hidden_size, (cudaStream_t)stream));
 }
 
-extern "C" int aph_silu_and_mul(void* out, const void* input, int64_t num_tokens, int64_t d, int dtype, void* stream) {
-  const char* op = "silu_and_mul";
+extern "C" int aph_act_and_mul(int act, void* out, const void* input, int64_t num_tokens, int64_t d, float param, int dtype,
+                               void* stream) {
+  const char* op = "act_and_mul";
   APH_CHECK(num_tokens >= 0 && d > 0 && d < (1LL << 30), APH_ERR_INVALID_ARGUMENT, "%s: bad shape", op);
   APH_CHECK(num_tokens <= 65535, APH_ERR_UNSUPPORTED, "%s: more than 65535 tokens per call", op);
   if (num_tokens == 0) return APH_OK;
   APH_CHECK(out && input, APH_ERR_INVALID_ARGUMENT, "%s: null tensor", op);
-  APH_DISPATCH_DT(dtype, op, launch_silu<T>((T*)out, (const T*)input, num_tokens, (int)d, (cudaStream_t)stream));
+  APH_DISPATCH_DT(dtype, op, launch_gated_any<T>(act, (T*)out, (const T*)input, num_tokens, (int)d, param, (cudaStream_t)stream));
+}
+
+extern "C" int aph_silu_and_mul(void* out, const void* input, int64_t num_tokens, int64_t d, int dtype, void* stream) {
+  return aph_act_and_mul(APH_ACT_SILU_AND_MUL, out, input, num_tokens, d, 0.f, dtype, stream);
+}
+
+extern "C" int aph_activation(int act, void* out, const void* input, int64_t numel, int dtype, void* stream) {
+  const char* op = "activation";
+  APH_CHECK(numel >= 0 && numel < (1LL << 38), APH_ERR_INVALID_ARGUMENT, "%s: bad shape", op);
+  if (numel == 0) return APH_OK;
+  APH_CHECK(out && input, APH_ERR_INVALID_ARGUMENT, "%s: null tensor", op);
+  APH_DISPATCH_DT(dtype, op, launch_act_any<T>(act, (T*)out, (const T*)input, numel, (cudaStream_t)stream));
 }
 
 extern "C" int aph_rotary_embedding(const int64_t* positions, void* query, void* key, const void* cos_sin_cache,
-                                    int64_t num_tokens, int rot_dim, int64_t query_stride, int64_t key_stride, int num_heads,
+                                    const int64_t* cos_sin_cache_offsets, int64_t num_tokens, int rot_dim, int64_t query_stride, int64_t key_stride, int num_heads,
                                     int num_kv_heads, int head_size, int is_neox, int dtype, void* stream) {
   const char* op = "rotary_embedding";
   APH_CHECK(num_tokens >= 0 && rot_dim > 0 && rot_dim % 2 == 0 && rot_dim <= head_size, APH_ERR_INVALID_ARGUMENT,
@@ -325,6 +444,22 @@ extern "C" int aph_rotary_embedding(const int64_t* positions, void* query, void*
             "%s: num_heads %d is not a multiple of num_kv_heads %d", op, num_heads, num_kv_heads);
   if (num_tokens == 0) return APH_OK;
   APH_CHECK(positions && query && cos_sin_cache, APH_ERR_INVALID_ARGUMENT, "%s: null tensor", op);
-  APH_DISPATCH_DT(dtype, op, launch_rope<T>(positions, (T*)query, (T*)key, (const T*)cos_sin_cache, rot_dim, query_stride, key_stride,
+  APH_DISPATCH_DT(dtype, op, launch_rope<T>(positions, (T*)query, (T*)key, (const T*)cos_sin_cache, cos_sin_cache_offsets, rot_dim, query_stride, key_stride,
                                             num_heads, num_kv_heads, head_size, is_neox != 0, num_tokens, (cudaStream_t)stream));
+}
+
+extern "C" int aph_advance_step_flashattn(int num_seqs, int num_queries, int block_size, int64_t* input_tokens,
+                                          const int64_t* sampled_token_ids, int64_t* input_positions, int32_t* seq_lens,
+                                          int64_t* slot_mapping, const int32_t* block_tables, int64_t block_tables_stride,
+                                          void* stream) {
+  const char* op = "advance_step_flashattn";
+  APH_CHECK(num_seqs >= 0 && num_queries >= 0 && num_queries <= num_seqs && block_size > 0, APH_ERR_INVALID_ARGUMENT,
+            "%s: need 0 <= num_queries <= num_seqs and block_size > 0", op);
+  if (num_seqs == 0) return APH_OK;
+  APH_CHECK(input_tokens && sampled_token_ids && input_positions && seq_lens && slot_mapping && block_tables,
+            APH_ERR_INVALID_ARGUMENT, "%s: null tensor", op);
+  const unsigned grid = (unsigned)std::max(1, (num_queries + 255) / 256);
+  APH_LAUNCH_PDL(advance_step_flashattn_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, num_seqs, num_queries, block_size,
+                 input_tokens, sampled_token_ids, input_positions, seq_lens, slot_mapping, block_tables, block_tables_stride);
+  return APH_OK;
 }

@@ -381,9 +381,8 @@ void fused_add_rms_norm(torch::Tensor& input, torch::Tensor& residual, torch::Te
                                       input.numel() / hidden, hidden, dtype_code(input, op), stream_of()), op);
 }
 
-// kernels/activation_kernels.cu:82-86
-void silu_and_mul(torch::Tensor& out, torch::Tensor& input) {
-  const char* op = "silu_and_mul";
+// kernels/activation_kernels.cu:64-149: out [..., d] = act(input[..., :d]) * input[..., d:]
+void act_and_mul(const char* op, int act, torch::Tensor& out, torch::Tensor& input, double param) {
   TORCH_CHECK(out.is_cuda() && input.is_cuda(), op, ": tensors must be on a CUDA device");
   TORCH_CHECK(out.is_contiguous() && input.is_contiguous(), op, ": tensors must be contiguous");
   TORCH_CHECK(out.scalar_type() == input.scalar_type(), op, ": dtype mismatch");
@@ -395,19 +394,48 @@ void silu_and_mul(torch::Tensor& out, torch::Tensor& input) {
   // the grid's y dimension carries the tokens: long prefills go in slices of 65535 tokens
   for (int64_t t0 = 0; t0 < tokens; t0 += 65535) {
     const int64_t n = std::min<int64_t>(65535, tokens - t0);
-    check_status(aph_silu_and_mul((char*)out.data_ptr() + t0 * d * out.element_size(),
-                                  (const char*)input.data_ptr() + t0 * 2 * d * input.element_size(), n, d, dtype_code(input, op),
-                                  stream_of()), op);
+    check_status(aph_act_and_mul(act, (char*)out.data_ptr() + t0 * d * out.element_size(),
+                                 (const char*)input.data_ptr() + t0 * 2 * d * input.element_size(), n, d, (float)param,
+                                 dtype_code(input, op), stream_of()), op);
   }
 }
+void silu_and_mul(torch::Tensor& out, torch::Tensor& input) { act_and_mul("silu_and_mul", APH_ACT_SILU_AND_MUL, out, input, 0); }
+void mul_and_silu(torch::Tensor& out, torch::Tensor& input) { act_and_mul("mul_and_silu", APH_ACT_MUL_AND_SILU, out, input, 0); }
+void gelu_and_mul(torch::Tensor& out, torch::Tensor& input) { act_and_mul("gelu_and_mul", APH_ACT_GELU_AND_MUL, out, input, 0); }
+void gelu_tanh_and_mul(torch::Tensor& out, torch::Tensor& input) {
+  act_and_mul("gelu_tanh_and_mul", APH_ACT_GELU_TANH_AND_MUL, out, input, 0);
+}
+void fatrelu_and_mul(torch::Tensor& out, torch::Tensor& input, double threshold) {
+  act_and_mul("fatrelu_and_mul", APH_ACT_FATRELU_AND_MUL, out, input, threshold);
+}
+
+// kernels/activation_kernels.cu:151-225: element-wise
+void activation(const char* op, int act, torch::Tensor& out, torch::Tensor& input) {
+  TORCH_CHECK(out.is_cuda() && input.is_cuda(), op, ": tensors must be on a CUDA device");
+  TORCH_CHECK(out.is_contiguous() && input.is_contiguous(), op, ": tensors must be contiguous");
+  TORCH_CHECK(out.scalar_type() == input.scalar_type() && out.numel() == input.numel(), op, ": dtype or shape mismatch");
+  const at::cuda::OptionalCUDAGuard guard(device_of(input));
+  check_status(aph_activation(act, out.data_ptr(), input.data_ptr(), input.numel(), dtype_code(input, op), stream_of()), op);
+}
+void gelu_new(torch::Tensor& out, torch::Tensor& input) { activation("gelu_new", APH_ACT_GELU_NEW, out, input); }
+void gelu_fast(torch::Tensor& out, torch::Tensor& input) { activation("gelu_fast", APH_ACT_GELU_FAST, out, input); }
+void gelu_quick(torch::Tensor& out, torch::Tensor& input) { activation("gelu_quick", APH_ACT_GELU_QUICK, out, input); }
 
 // kernels/pos_encoding_kernels.cu:124-196 (same shape checks)
-void rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int64_t head_size,
-                      torch::Tensor& cos_sin_cache, bool is_neox) {
-  const char* op = "rotary_embedding";
+void rotary_impl(const char* op, torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int64_t head_size,
+                 torch::Tensor& cos_sin_cache, bool is_neox, int64_t rot_dim, const torch::Tensor* offsets) {
   TORCH_CHECK(positions.is_cuda() && query.is_cuda() && key.is_cuda() && cos_sin_cache.is_cuda(), op,
               ": tensors must be on a CUDA device");
-  const int64_t num_tokens = positions.numel();
+  const int64_t num_tokens = offsets ? offsets->size(0) : positions.numel();
+  const int64_t* off_ptr = nullptr;
+  if (offsets) {
+    TORCH_CHECK(positions.size(0) == num_tokens || positions.numel() == num_tokens,
+                "positions must have the same num_tokens or batch_size as cos_sin_cache_offsets");
+    TORCH_CHECK(offsets->is_cuda() && offsets->scalar_type() == at::ScalarType::Long && offsets->is_contiguous(), op,
+                ": cos_sin_cache_offsets must be contiguous int64 on the GPU");
+    TORCH_CHECK(rot_dim == cos_sin_cache.size(1), op, ": rot_dim must equal cos_sin_cache.size(1)");
+    off_ptr = offsets->data_ptr<int64_t>();
+  }
   const int positions_ndim = positions.dim();
   TORCH_CHECK(positions_ndim == 1 || positions_ndim == 2, "positions must have shape [num_tokens] or [batch_size, seq_len]");
   if (positions_ndim == 1) {
@@ -435,9 +463,42 @@ void rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Ten
                 ": batch and sequence dimensions must collapse into one token stride");
   const at::cuda::OptionalCUDAGuard guard(device_of(query));
   check_status(aph_rotary_embedding(positions.data_ptr<int64_t>(), query.data_ptr(), key.data_ptr(), cos_sin_cache.data_ptr(),
-                                    num_tokens, (int)cos_sin_cache.size(1), query.stride(seq_dim), key.stride(seq_dim),
+                                    off_ptr, num_tokens, (int)cos_sin_cache.size(1), query.stride(seq_dim), key.stride(seq_dim),
                                     (int)num_heads, (int)num_kv_heads, (int)head_size, is_neox ? 1 : 0, dtype_code(query, op),
                                     stream_of()), op);
+}
+void rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int64_t head_size,
+                      torch::Tensor& cos_sin_cache, bool is_neox) {
+  rotary_impl("rotary_embedding", positions, query, key, head_size, cos_sin_cache, is_neox, cos_sin_cache.size(1), nullptr);
+}
+// kernels/pos_encoding_kernels.cu:204-290: one table holding several scalings (multi-LoRA), a row offset per token
+void batched_rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int64_t head_size,
+                              torch::Tensor& cos_sin_cache, bool is_neox, int64_t rot_dim, torch::Tensor& cos_sin_cache_offsets) {
+  rotary_impl("batched_rotary_embedding", positions, query, key, head_size, cos_sin_cache, is_neox, rot_dim, &cos_sin_cache_offsets);
+}
+
+// kernels/prepare_inputs/advance_step.cu:68-93,190-232 (same tensor checks)
+void advance_step_flashattn(int64_t num_seqs, int64_t num_queries, int64_t block_size, torch::Tensor& input_tokens,
+                            torch::Tensor& sampled_token_ids, torch::Tensor& input_positions, torch::Tensor& seq_lens,
+                            torch::Tensor& slot_mapping, torch::Tensor& block_tables) {
+  const char* op = "advance_step_flashattn";
+  auto verify = [&](const char* name, const torch::Tensor& t, int64_t s0, int64_t s1, at::ScalarType type) {
+    const bool ok = t.is_cuda() && (s0 == -1 || t.size(0) == s0) && (s1 == -1 || (t.dim() > 1 && t.size(1) == s1)) &&
+                    t.is_contiguous() && t.scalar_type() == type;
+    TORCH_CHECK(ok, "tensor: name = ", name, ", shape = ", t.sizes(), " is_cont = ", t.is_contiguous(), ", type = ", t.dtype(),
+                " is not as expected: shape = [", s0, ", ", s1, "], type = ", type);
+  };
+  verify("input_tokens", input_tokens, num_seqs, -1, at::kLong);
+  verify("sampled_token_ids", sampled_token_ids, num_queries, 1, at::kLong);
+  verify("input_positions", input_positions, num_seqs, -1, at::kLong);
+  verify("seq_lens", seq_lens, num_seqs, -1, at::kInt);
+  verify("slot_mapping", slot_mapping, num_seqs, -1, at::kLong);
+  verify("block_tables", block_tables, num_seqs, -1, at::kInt);
+  const at::cuda::OptionalCUDAGuard guard(device_of(sampled_token_ids));
+  check_status(aph_advance_step_flashattn((int)num_seqs, (int)num_queries, (int)block_size, input_tokens.data_ptr<int64_t>(),
+                                          sampled_token_ids.data_ptr<int64_t>(), input_positions.data_ptr<int64_t>(),
+                                          seq_lens.data_ptr<int32_t>(), slot_mapping.data_ptr<int64_t>(),
+                                          block_tables.data_ptr<int32_t>(), block_tables.stride(0), stream_of()), op);
 }
 
 }  // namespace
@@ -483,6 +544,24 @@ TORCH_LIBRARY_FRAGMENT(_C, ops) {
   // kernels/torch_bindings.cpp:84,140-148,178-181
   ops.def("silu_and_mul(Tensor! result, Tensor input) -> ()");
   ops.def(
+      "advance_step_flashattn(int num_seqs, int num_queries, int block_size, "
+      "Tensor! input_tokens, Tensor sampled_token_ids, "
+      "Tensor! input_positions, Tensor! seq_lens, Tensor! slot_mapping, "
+      "Tensor block_tables) -> ()");
+  ops.def("mul_and_silu(Tensor! out, Tensor input) -> ()");
+  ops.def("gelu_and_mul(Tensor! out, Tensor input) -> ()");
+  ops.def("gelu_tanh_and_mul(Tensor! out, Tensor input) -> ()");
+  ops.def("fatrelu_and_mul(Tensor! out, Tensor input, float threshold) -> ()");
+  ops.def("gelu_new(Tensor! out, Tensor input) -> ()");
+  ops.def("gelu_fast(Tensor! out, Tensor input) -> ()");
+  ops.def("gelu_quick(Tensor! out, Tensor input) -> ()");
+  ops.def(
+      "batched_rotary_embedding(Tensor positions, Tensor! query,"
+      "                         Tensor! key, int head_size,"
+      "                         Tensor cos_sin_cache, bool is_neox,"
+      "                         int rot_dim,"
+      "                         Tensor cos_sin_cache_offsets) -> ()");
+  ops.def(
       "rms_norm(Tensor! result, Tensor input, Tensor weight, float epsilon) -> "
       "()");
   ops.def(
@@ -525,6 +604,15 @@ TORCH_LIBRARY_IMPL(_C, CUDA, ops) {
   ops.impl("gptq_marlin_repack", &gptq_marlin_repack);
   ops.impl("awq_marlin_repack", &awq_marlin_repack);
   ops.impl("silu_and_mul", &silu_and_mul);
+  ops.impl("advance_step_flashattn", &advance_step_flashattn);
+  ops.impl("mul_and_silu", &mul_and_silu);
+  ops.impl("gelu_and_mul", &gelu_and_mul);
+  ops.impl("gelu_tanh_and_mul", &gelu_tanh_and_mul);
+  ops.impl("fatrelu_and_mul", &fatrelu_and_mul);
+  ops.impl("gelu_new", &gelu_new);
+  ops.impl("gelu_fast", &gelu_fast);
+  ops.impl("gelu_quick", &gelu_quick);
+  ops.impl("batched_rotary_embedding", &batched_rotary_embedding);
   ops.impl("rms_norm", &rms_norm);
   ops.impl("fused_add_rms_norm", &fused_add_rms_norm);
   ops.impl("rotary_embedding", &rotary_embedding);

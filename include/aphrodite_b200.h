@@ -190,9 +190,30 @@ int aph_rms_norm(void* out, const void* input, const void* weight, float epsilon
 int aph_fused_add_rms_norm(void* input, void* residual, const void* weight, float epsilon, int64_t num_tokens,
                            int64_t hidden_size, int dtype, void* stream);
 int aph_silu_and_mul(void* out, const void* input, int64_t num_tokens, int64_t d, int dtype, void* stream);
+/* The other activations of kernels/activation_kernels.cu:82-225. Gated (input [tokens, 2 d] -> out [tokens, d]):
+ * silu_and_mul, mul_and_silu (activation on the second half), gelu_and_mul (erf), gelu_tanh_and_mul, fatrelu_and_mul
+ * (param = threshold). Element-wise over numel values: gelu_new, gelu_fast, gelu_quick. */
+typedef enum {
+  APH_ACT_SILU_AND_MUL = 0, APH_ACT_MUL_AND_SILU = 1, APH_ACT_GELU_AND_MUL = 2, APH_ACT_GELU_TANH_AND_MUL = 3,
+  APH_ACT_FATRELU_AND_MUL = 4, APH_ACT_GELU_NEW = 5, APH_ACT_GELU_FAST = 6, APH_ACT_GELU_QUICK = 7
+} aph_activation_t;
+int aph_act_and_mul(int act, void* out, const void* input, int64_t num_tokens, int64_t d, float param, int dtype,
+                    void* stream);
+int aph_activation(int act, void* out, const void* input, int64_t numel, int dtype, void* stream);
+/* cos_sin_cache_offsets: NULL, or int64 [num_tokens] added to positions (batched_rotary_embedding,
+ * pos_encoding_kernels.cu:98-121,204-260) */
 int aph_rotary_embedding(const int64_t* positions, void* query, void* key, const void* cos_sin_cache,
-                         int64_t num_tokens, int rot_dim, int64_t query_stride, int64_t key_stride, int num_heads,
+                         const int64_t* cos_sin_cache_offsets, int64_t num_tokens, int rot_dim, int64_t query_stride, int64_t key_stride, int num_heads,
                          int num_kv_heads, int head_size, int is_neox, int dtype, void* stream);
+
+/* Multi-step decode bookkeeping - replaces kernels/prepare_inputs/advance_step.cu:12-66,190-232
+ * (advance_step_flashattn): for q < num_queries: input_tokens[q] = sampled_token_ids[q]; seq_lens[q] += 1;
+ * input_positions[q] = seq_lens[q] - 1; slot_mapping[q] = block_tables[q][pos / block_size] * block_size + pos % block_size;
+ * rows num_queries..num_seqs-1 (CUDA-graph padding) get token 0, position 0, slot -1. */
+int aph_advance_step_flashattn(int num_seqs, int num_queries, int block_size, int64_t* input_tokens,
+                               const int64_t* sampled_token_ids, int64_t* input_positions, int32_t* seq_lens,
+                               int64_t* slot_mapping, const int32_t* block_tables, int64_t block_tables_stride,
+                               void* stream);
 
 #ifdef __cplusplus
 }

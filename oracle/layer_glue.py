@@ -66,3 +66,60 @@ def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Te
         return t.reshape(shape)
 
     return one(query), one(key)
+
+
+# ---- the other activations of kernels/activation_kernels.cu:42-62,111-115,183-205 ----
+def _act(name: str, x: torch.Tensor, threshold: float = 0.0) -> torch.Tensor:
+    """act(x) rounded to x.dtype the way the CUDA function of that name rounds."""
+    dt, f = x.dtype, x.float()
+    if name == "silu":
+        return (f / (1.0 + torch.exp(-f))).to(dt)
+    if name == "gelu":
+        return (f * 0.5 * (1.0 + torch.erf(f * 0.7071067811865476))).to(dt)
+    if name == "gelu_tanh":
+        beta = torch.tensor(1.4142135623730951 * 1.1283791670955126 * 0.5, dtype=torch.float32)
+        inner = beta * (f + torch.tensor(0.044715, dtype=torch.float32) * (f * f * f))
+        return (0.5 * f * (1.0 + torch.tanh(inner))).to(dt)
+    if name == "fatrelu":
+        return torch.where(f > threshold, f, torch.zeros_like(f)).to(dt)
+    if name == "gelu_new":
+        x3 = _r(_r(f * f, dt) * f, dt)
+        s = _r(f + _r(0.044715 * x3, dt), dt)
+        t = _r(torch.tanh(_r(0.79788456 * s, dt)), dt)
+        return (_r(_r(torch.tensor(0.5), dt) * f, dt) * _r(1.0 + t, dt)).to(dt)
+    if name == "gelu_fast":
+        arg = _r(_r(f * 0.79788456, dt) * _r(1.0 + _r(_r(0.044715 * f, dt) * f, dt), dt), dt)
+        t = _r(torch.tanh(arg), dt)
+        return (_r(0.5 * f, dt) * _r(1.0 + t, dt)).to(dt)
+    if name == "gelu_quick":
+        return (f / (1.0 + torch.exp(-1.702 * f))).to(dt)
+    raise ValueError(name)
+
+
+def act_and_mul(name: str, x: torch.Tensor, threshold: float = 0.0) -> torch.Tensor:
+    """silu_and_mul / mul_and_silu / gelu_and_mul / gelu_tanh_and_mul / fatrelu_and_mul."""
+    dt = x.dtype
+    d = x.shape[-1] // 2
+    a, b = x[..., :d], x[..., d:]
+    if name == "mul_and_silu":
+        return (a.float() * _act("silu", b).float()).to(dt)
+    fn = {"silu_and_mul": "silu", "gelu_and_mul": "gelu", "gelu_tanh_and_mul": "gelu_tanh", "fatrelu_and_mul": "fatrelu"}[name]
+    return (_act(fn, a, threshold).float() * b.float()).to(dt)
+
+
+def activation(name: str, x: torch.Tensor) -> torch.Tensor:
+    """gelu_new / gelu_fast / gelu_quick."""
+    return _act(name, x)
+
+
+def advance_step_flashattn(num_seqs, num_queries, block_size, input_tokens, sampled_token_ids, input_positions, seq_lens,
+                           slot_mapping, block_tables):
+    """kernels/prepare_inputs/advance_step.cu:12-66, in place on CPU tensors (plain loop: integer work)."""
+    for i in range(num_queries, num_seqs):
+        input_tokens[i], input_positions[i], slot_mapping[i] = 0, 0, -1
+    for q in range(num_queries):
+        input_tokens[q] = sampled_token_ids[q, 0]
+        pos = int(seq_lens[q])
+        seq_lens[q] = pos + 1
+        input_positions[q] = pos
+        slot_mapping[q] = int(block_tables[q, pos // block_size]) * block_size + pos % block_size

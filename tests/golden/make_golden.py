@@ -194,6 +194,13 @@ def make_glue():
         xs = torch.randn(t, 2 * h, generator=g).to(dt)
         out[pre + "silu_x"] = raw(xs)
         out[pre + "silu_out"] = raw(act.SiluAndMul().forward_native(xs))
+        out[pre + "mul_and_silu_out"] = raw(act.MulAndSilu().forward_native(xs))
+        out[pre + "gelu_and_mul_out"] = raw(act.GeluAndMul("none").forward_native(xs))
+        out[pre + "gelu_tanh_and_mul_out"] = raw(act.GeluAndMul("tanh").forward_native(xs))
+        out[pre + "fatrelu_and_mul_out"] = raw(act.FatreluAndMul(0.3).forward_native(xs))
+        out[pre + "gelu_new_out"] = raw(act.NewGELU().forward_native(xs))
+        out[pre + "gelu_fast_out"] = raw(act.FastGELU().forward_native(xs))
+        out[pre + "gelu_quick_out"] = raw(act.QuickGELU().forward_native(xs))
     # (tokens, heads, kv heads, head size, rotary dim, neox, dtype)
     rcases = [(9, 8, 2, 128, 128, True, torch.bfloat16), (5, 4, 4, 64, 32, False, torch.float16),
               (6, 6, 2, 96, 96, False, torch.bfloat16), (4, 8, 1, 128, 64, True, torch.float32)]

@@ -191,3 +191,96 @@ def test_glue_errors_and_empty():
         A.ops.rotary_embedding(torch.zeros(3, dtype=torch.int64, device=DEV), y, y.clone(), 64, torch.zeros(8, 64, dtype=torch.bfloat16, device=DEV), True)
     with pytest.raises(RuntimeError):  # CPU tensors: the dispatcher has no CPU kernel for the op (no fallback)
         A.ops.silu_and_mul(torch.zeros(4, 32, dtype=torch.bfloat16), y.cpu())
+
+
+GATED = ["silu_and_mul", "mul_and_silu", "gelu_and_mul", "gelu_tanh_and_mul", "fatrelu_and_mul"]
+PLAIN = ["gelu_new", "gelu_fast", "gelu_quick"]
+
+
+def _call(o, name, out, x):
+    if name == "fatrelu_and_mul":
+        getattr(o, name)(out, x, 0.3)
+    else:
+        getattr(o, name)(out, x)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("name", GATED + PLAIN)
+@pytest.mark.parametrize("tokens,d", [(7, 512), (64, 14336), (5, 1001)])
+def test_activation_family(name, tokens, d, dtype):
+    """kernels/activation_kernels.cu:64-225 / tests/kernels/test_activation.py. Bit-exact against the reference CUDA
+    kernels for the 16-bit types (same operations, same roundings, same libdevice functions); against the CPU oracle
+    within 2 ulp (libm vs libdevice exp / tanh / erf)."""
+    gen = torch.Generator(device=DEV).manual_seed(tokens + d)
+    gated = name in GATED
+    x = (torch.randn(tokens, 2 * d if gated else d, device=DEV, generator=gen) * 2).to(dtype)
+    out = torch.empty(tokens, d, dtype=dtype, device=DEV)
+    _call(A.ops, name, out, x)
+    want = lg.act_and_mul(name, x.cpu(), 0.3) if gated else lg.activation(name, x.cpu())
+    if dtype == torch.float32:
+        torch.testing.assert_close(out.cpu(), want, atol=2e-6, rtol=2e-5)
+    else:
+        _ulp_close(out.cpu(), want, frac=0.03)
+    ref = _ref()
+    if ref is not None and hasattr(ref, name):
+        ro = torch.empty_like(out)
+        _call(ref, name, ro, x)
+        if dtype == torch.float32:
+            torch.testing.assert_close(out, ro, atol=1e-6, rtol=1e-5)
+        else:
+            assert torch.equal(out, ro)
+
+
+def test_activation_golden_fixtures():
+    g = np.load(os.path.join(G, "glue_golden.npz"))
+    for ci in range(int(g["num_norm"][0])):
+        pre = f"norm{ci}_"
+        dt = DT[int(g[pre + "meta"][2])]
+        sx = _t(g[pre + "silu_x"], dt)
+        for name in GATED + PLAIN:
+            gated = name in GATED
+            out = torch.empty(sx.shape[0], sx.shape[1] // 2 if gated else sx.shape[1], dtype=dt, device=DEV)
+            _call(A.ops, name, out, sx)
+            key = pre + ("silu_out" if name == "silu_and_mul" else name + "_out")
+            torch.testing.assert_close(out, _t(g[key], dt), atol=1e-2, rtol=1.6e-2)
+
+
+@pytest.mark.parametrize("neox", [True, False])
+def test_batched_rotary_embedding(neox):
+    """pos_encoding_kernels.cu:98-121: row = positions + offset of the token's scaling block in one stacked table."""
+    tokens, nh, nkv, d = 33, 8, 2, 128
+    gen = torch.Generator(device=DEV).manual_seed(5)
+    cache = torch.randn(3 * 512, d, device=DEV, generator=gen).to(torch.bfloat16)
+    pos = torch.randint(0, 512, (tokens,), device=DEV, generator=gen)
+    off = torch.randint(0, 3, (tokens,), device=DEV, generator=gen) * 512
+    q = torch.randn(tokens, nh * d, device=DEV, generator=gen).to(torch.bfloat16)
+    k = torch.randn(tokens, nkv * d, device=DEV, generator=gen).to(torch.bfloat16)
+    wq, wk = lg.rotary_embedding((pos + off).cpu(), q.cpu(), k.cpu(), d, cache.cpu(), neox)
+    ref = _ref()
+    if ref is not None and hasattr(ref, "batched_rotary_embedding"):
+        rq, rk = q.clone(), k.clone()
+        ref.batched_rotary_embedding(pos, rq, rk, d, cache, neox, d, off)
+    A.ops.batched_rotary_embedding(pos, q, k, d, cache, neox, d, off)
+    assert torch.equal(q.cpu(), wq) and torch.equal(k.cpu(), wk)
+    if ref is not None and hasattr(ref, "batched_rotary_embedding"):
+        assert torch.equal(q, rq) and torch.equal(k, rk)
+
+
+@pytest.mark.parametrize("num_seqs,num_queries", [(8, 8), (64, 50), (1000, 700), (1, 0)])
+def test_advance_step_flashattn(num_seqs, num_queries):
+    """Integer bookkeeping: bit-exact against the oracle loop (prepare_inputs/advance_step.cu:12-66)."""
+    bs, max_blocks = 16, 40
+    gen = torch.Generator().manual_seed(num_seqs)
+    tok = torch.randint(0, 32000, (num_seqs,), generator=gen)
+    sampled = torch.randint(0, 32000, (num_queries, 1), generator=gen)
+    pos = torch.randint(0, 500, (num_seqs,), generator=gen)
+    lens = torch.randint(1, bs * max_blocks - 1, (num_seqs,), generator=gen, dtype=torch.int32)
+    slots = torch.randint(0, 10000, (num_seqs,), generator=gen)
+    bt = torch.randint(0, 5000, (num_seqs, max_blocks), generator=gen, dtype=torch.int32)
+    dev = [t.to(DEV) for t in (tok, sampled, pos, lens, slots, bt)]
+    A.ops.advance_step_flashattn(num_seqs, num_queries, bs, dev[0], dev[1], dev[2], dev[3], dev[4], dev[5])
+    lg.advance_step_flashattn(num_seqs, num_queries, bs, tok, sampled, pos, lens, slots, bt)
+    for got, want in zip(dev, (tok, sampled, pos, lens, slots, bt)):
+        assert torch.equal(got.cpu(), want)
+    with pytest.raises(RuntimeError, match="is not as expected"):
+        A.ops.advance_step_flashattn(num_seqs + 1, num_queries, bs, dev[0], dev[1], dev[2], dev[3], dev[4], dev[5])

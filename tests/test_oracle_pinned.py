@@ -208,6 +208,15 @@ def test_glue_oracle_matches_reference_forward_native():
             assert torch.equal(r, _t(g[pre + "fused_res"], dt))  # one rounding of the same fp32 sum
         torch.testing.assert_close(lg.silu_and_mul(_t(g[pre + "silu_x"], dt)), _t(g[pre + "silu_out"], dt), atol=1e-3,
                                    rtol=1e-2)
+        sx = _t(g[pre + "silu_x"], dt)
+        # tests/kernels/test_activation.py compares the CUDA kernels with forward_native at atol = rtol = 1e-2 for
+        # the gelu_new / gelu_fast / gelu_quick family and at the default bf16 / fp16 tolerances for the gated ones
+        for name in ("mul_and_silu", "gelu_and_mul", "gelu_tanh_and_mul"):
+            torch.testing.assert_close(lg.act_and_mul(name, sx), _t(g[pre + name + "_out"], dt), atol=1e-3, rtol=1.6e-2)
+        torch.testing.assert_close(lg.act_and_mul("fatrelu_and_mul", sx, 0.3), _t(g[pre + "fatrelu_and_mul_out"], dt), atol=0,
+                                   rtol=0)
+        for name in ("gelu_new", "gelu_fast", "gelu_quick"):
+            torch.testing.assert_close(lg.activation(name, sx), _t(g[pre + name + "_out"], dt), atol=1e-2, rtol=1e-2)
     for ci in range(int(g["num_rope"][0])):
         pre = f"rope{ci}_"
         t, nh, nkv, d, rot, neox, dc = (int(v) for v in g[pre + "meta"])
