@@ -230,3 +230,18 @@ def advance_step_flashattn(num_seqs: int, num_queries: int, block_size: int, inp
     """Advance a step on GPU for existing inputs for a multi-step runner"""
     return _ops()[0].advance_step_flashattn(num_seqs, num_queries, block_size, input_tokens, sampled_token_ids,
                                             input_positions, seq_lens, slot_mapping, block_tables)
+
+
+# aphrodite/_custom_ops.py:1475-1518: the MLA cache ops
+def concat_and_cache_mla(kv_c: torch.Tensor, k_pe: torch.Tensor, kv_cache: torch.Tensor, slot_mapping: torch.Tensor,
+                         kv_cache_dtype: str, scale: torch.Tensor) -> None:
+    _ops()[1].concat_and_cache_mla(kv_c, k_pe, kv_cache, slot_mapping, kv_cache_dtype, scale)
+
+
+def copy_blocks_mla(kv_caches: list[torch.Tensor], block_mapping: torch.Tensor) -> None:
+    _ops()[1].copy_blocks_mla(kv_caches, block_mapping)
+
+
+def gather_cache(src_cache: torch.Tensor, dst: torch.Tensor, block_table: torch.Tensor, cu_seq_lens: torch.Tensor,
+                 batch_size: int, seq_starts: Optional[torch.Tensor] = None) -> None:
+    _ops()[1].gather_cache(src_cache, dst, block_table, cu_seq_lens, batch_size, seq_starts)

@@ -329,6 +329,7 @@ __global__ void __launch_bounds__(256)
   const int64_t src_blk = block_mapping[2 * pair], dst_blk = block_mapping[2 * pair + 1];
 #pragma unroll
   for (int kv = 0; kv < 2; ++kv) {
+    if (kv == 1 && value_ptrs == nullptr) break;  // copy_blocks_mla: one joint cache per layer
     uint8_t* base = reinterpret_cast<uint8_t*>(kv == 0 ? key_ptrs[layer] : value_ptrs[layer]);
     const uint8_t* src = base + src_blk * block_bytes;
     uint8_t* dst = base + dst_blk * block_bytes;
@@ -340,6 +341,81 @@ __global__ void __launch_bounds__(256)
       for (int64_t i = blockIdx.z * (int64_t)blockDim.x + threadIdx.x; i < block_bytes; i += (int64_t)gridDim.z * blockDim.x)
         dst[i] = src[i];
     }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// concat_and_cache_mla (reference cache_kernels.cu:308-348,463-500): cache row of a token = [kv_c | k_pe], optionally
+// FP8-encoded with one scale. One CTA per token, VEC source elements per thread and access.
+// ------------------------------------------------------------------------------------------------
+template <typename scalar_t, typename cache_t, int KV, int VEC>
+__global__ void __launch_bounds__(128)
+    concat_and_cache_mla_kernel(const scalar_t* __restrict__ kv_c, const scalar_t* __restrict__ k_pe, cache_t* __restrict__ kv_cache,
+                                const int64_t* __restrict__ slot_mapping, int64_t block_stride, int64_t entry_stride,
+                                int64_t kv_c_stride, int64_t k_pe_stride, int kv_lora_rank, int pe_dim, int block_size,
+                                const float* __restrict__ scale) {
+  pdl_trigger();
+  pdl_wait();
+  const int64_t token = blockIdx.x;
+  const int64_t slot = slot_mapping[token];
+  if (slot < 0) return;  // padded token
+  cache_t* row = kv_cache + (slot / block_size) * block_stride + (slot % block_size) * entry_stride;
+  const float sc = KV == APH_KV_AUTO ? 1.f : *scale;
+  const int n = (kv_lora_rank + pe_dim) / VEC;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int e = i * VEC;
+    const scalar_t* src = e < kv_lora_rank ? kv_c + token * kv_c_stride + e : k_pe + token * k_pe_stride + (e - kv_lora_rank);
+    const Pack<scalar_t, VEC> x = *reinterpret_cast<const Pack<scalar_t, VEC>*>(src);
+    Pack<cache_t, VEC> o;
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      if constexpr (KV == APH_KV_AUTO) o.v[j] = x.v[j];
+      else o.v[j] = fp8_encode<KV>(ScalarTraits<scalar_t>::to_float(x.v[j]), sc);
+    }
+    *reinterpret_cast<Pack<cache_t, VEC>*>(row + e) = o;
+  }
+}
+
+template <typename scalar_t, typename cache_t, int KV>
+int launch_concat_mla(const void* kv_c, const void* k_pe, void* kv_cache, const int64_t* slot_mapping, int64_t num_tokens,
+                      int kv_lora_rank, int pe_dim, int block_size, int64_t block_stride, int64_t entry_stride,
+                      int64_t kv_c_stride, int64_t k_pe_stride, const float* scale, cudaStream_t stream) {
+  constexpr int VEC = 16 / (int)sizeof(scalar_t);
+  const bool vec = kv_lora_rank % VEC == 0 && pe_dim % VEC == 0 && kv_c_stride % VEC == 0 && k_pe_stride % VEC == 0 &&
+                   aligned16(kv_c) && aligned16(k_pe) && aligned16(kv_cache) && (block_stride * sizeof(cache_t)) % 16 == 0 &&
+                   (entry_stride * sizeof(cache_t)) % 16 == 0;
+#define APH_MLA(V)                                                                                                              \
+  APH_LAUNCH_PDL((concat_and_cache_mla_kernel<scalar_t, cache_t, KV, V>), dim3((unsigned)num_tokens), dim3(128), (size_t)0, stream, \
+                 (const scalar_t*)kv_c, (const scalar_t*)k_pe, (cache_t*)kv_cache, slot_mapping, block_stride, entry_stride,     \
+                 kv_c_stride, k_pe_stride, kv_lora_rank, pe_dim, block_size, scale)
+  if (vec) APH_MLA(VEC);
+  else APH_MLA(1);
+#undef APH_MLA
+  return APH_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// gather_cache (reference cache_kernels.cu:582-735): dst[cu_seq_lens[b] + t] = cache[block_table[b][start_block + t / bs]][t % bs]
+// for t < cu_seq_lens[b+1] - cu_seq_lens[b]: the paged rows of every sequence laid out contiguously (MLA chunked
+// prefill). grid (splits, batch); a warp copies one entry at a time with 16-byte (or byte) accesses.
+// ------------------------------------------------------------------------------------------------
+template <typename V>
+__global__ void __launch_bounds__(256)
+    gather_cache_kernel(const uint8_t* __restrict__ src_cache, uint8_t* __restrict__ dst, const int32_t* __restrict__ block_table,
+                        const int32_t* __restrict__ cu_seq_lens, const int32_t* __restrict__ seq_starts, int block_size,
+                        int entry_bytes, int64_t block_table_stride, int64_t cache_block_stride, int64_t cache_entry_stride,
+                        int64_t dst_entry_stride) {
+  pdl_trigger();
+  pdl_wait();
+  const int b = blockIdx.y;
+  const int seq_start = cu_seq_lens[b], seq_len = cu_seq_lens[b + 1] - seq_start;
+  const int32_t* table = block_table + b * block_table_stride + (seq_starts != nullptr ? seq_starts[b] / block_size : 0);
+  const int warps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = entry_bytes / (int)sizeof(V);
+  for (int t = blockIdx.x * warps + warp; t < seq_len; t += gridDim.x * warps) {
+    const V* s = reinterpret_cast<const V*>(src_cache + table[t / block_size] * cache_block_stride + (t % block_size) * cache_entry_stride);
+    V* d = reinterpret_cast<V*>(dst + (int64_t)(seq_start + t) * dst_entry_stride);
+    for (int i = lane; i < n; i += 32) d[i] = s[i];
   }
 }
 
@@ -462,5 +538,67 @@ extern "C" int aph_swap_blocks(const void* src, void* dst, const int64_t* block_
     APH_CHECK(e == cudaSuccess, APH_ERR_CUDA, "swap_blocks: cudaMemcpyAsync failed: %s", cudaGetErrorString(e));
     i += run;
   }
+  return APH_OK;
+}
+
+// copy_blocks_mla (reference cache_kernels.cu:100-117,173-208): copy_blocks over one joint cache per layer.
+extern "C" int aph_copy_blocks_mla(const int64_t* kv_cache_ptrs, const int64_t* block_mapping, int num_layers, int64_t num_pairs,
+                                   int64_t block_bytes, void* stream) {
+  return aph_copy_blocks(kv_cache_ptrs, nullptr, block_mapping, num_layers, num_pairs, block_bytes, stream);
+}
+
+extern "C" int aph_concat_and_cache_mla(const void* kv_c, const void* k_pe, void* kv_cache, const int64_t* slot_mapping,
+                                        int64_t num_tokens, int kv_lora_rank, int pe_dim, int block_size, int64_t block_stride,
+                                        int64_t entry_stride, int64_t kv_c_stride, int64_t k_pe_stride, int dtype, int kv_dtype,
+                                        const float* scale, void* stream) {
+  const char* op = "concat_and_cache_mla";
+  APH_CHECK(num_tokens >= 0 && kv_lora_rank > 0 && pe_dim >= 0 && block_size > 0, APH_ERR_INVALID_ARGUMENT, "%s: bad sizes", op);
+  APH_CHECK(kv_dtype == APH_KV_AUTO || scale != nullptr, APH_ERR_INVALID_ARGUMENT, "%s: fp8 kv cache needs a scale", op);
+  if (num_tokens == 0) return APH_OK;
+  APH_CHECK(kv_c && k_pe && kv_cache && slot_mapping, APH_ERR_INVALID_ARGUMENT, "%s: null tensor", op);
+  cudaStream_t s = (cudaStream_t)stream;
+#define APH_MLA_KV(SC, CT, KVC)                                                                                            \
+  return launch_concat_mla<SC, CT, KVC>(kv_c, k_pe, kv_cache, slot_mapping, num_tokens, kv_lora_rank, pe_dim, block_size, \
+                                        block_stride, entry_stride, kv_c_stride, k_pe_stride, scale, s)
+#define APH_MLA_DT(SC)                                                     \
+  switch (kv_dtype) {                                                      \
+    case APH_KV_AUTO: APH_MLA_KV(SC, SC, APH_KV_AUTO);                     \
+    case APH_KV_FP8_E4M3: APH_MLA_KV(SC, uint8_t, APH_KV_FP8_E4M3);        \
+    case APH_KV_FP8_E5M2: APH_MLA_KV(SC, uint8_t, APH_KV_FP8_E5M2);        \
+    default: break;                                                        \
+  }
+  switch (dtype) {
+    case APH_DT_F32: APH_MLA_DT(float); break;
+    case APH_DT_F16: APH_MLA_DT(__half); break;
+    case APH_DT_BF16: APH_MLA_DT(__nv_bfloat16); break;
+    default: break;
+  }
+#undef APH_MLA_DT
+#undef APH_MLA_KV
+  return set_error(APH_ERR_INVALID_ARGUMENT, "%s: unsupported dtype %d / kv cache dtype %d", op, dtype, kv_dtype);
+}
+
+extern "C" int aph_gather_cache(const void* src_cache, void* dst, const int32_t* block_table, const int32_t* cu_seq_lens,
+                                const int32_t* seq_starts, int batch_size, int block_size, int64_t entry_bytes,
+                                int64_t block_table_stride, int64_t cache_block_stride_bytes, int64_t cache_entry_stride_bytes,
+                                int64_t dst_entry_stride_bytes, void* stream) {
+  const char* op = "gather_cache";
+  APH_CHECK(batch_size >= 0 && batch_size <= 65535 && block_size > 0 && entry_bytes > 0 && entry_bytes < (1LL << 31),
+            APH_ERR_INVALID_ARGUMENT, "%s: bad sizes", op);
+  if (batch_size == 0) return APH_OK;
+  APH_CHECK(src_cache && dst && block_table && cu_seq_lens, APH_ERR_INVALID_ARGUMENT, "%s: null tensor", op);
+  // enough CTAs for two waves whatever the batch size; a CTA's 8 warps take tokens round-robin
+  const int splits = std::max(1, std::min(1024, (4 * sm_count() + batch_size - 1) / batch_size));
+  const dim3 grid((unsigned)splits, (unsigned)batch_size);
+  const bool vec = entry_bytes % 16 == 0 && cache_block_stride_bytes % 16 == 0 && cache_entry_stride_bytes % 16 == 0 &&
+                   dst_entry_stride_bytes % 16 == 0 && aligned16(src_cache) && aligned16(dst);
+  if (vec)
+    APH_LAUNCH_PDL(gather_cache_kernel<uint4>, grid, dim3(256), (size_t)0, (cudaStream_t)stream, (const uint8_t*)src_cache, (uint8_t*)dst,
+                   block_table, cu_seq_lens, seq_starts, block_size, (int)entry_bytes, block_table_stride, cache_block_stride_bytes,
+                   cache_entry_stride_bytes, dst_entry_stride_bytes);
+  else
+    APH_LAUNCH_PDL(gather_cache_kernel<uint8_t>, grid, dim3(256), (size_t)0, (cudaStream_t)stream, (const uint8_t*)src_cache,
+                   (uint8_t*)dst, block_table, cu_seq_lens, seq_starts, block_size, (int)entry_bytes, block_table_stride,
+                   cache_block_stride_bytes, cache_entry_stride_bytes, dst_entry_stride_bytes);
   return APH_OK;
 }

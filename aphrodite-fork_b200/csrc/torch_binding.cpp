@@ -239,6 +239,74 @@ void copy_blocks(std::vector<torch::Tensor> const& key_caches, std::vector<torch
   check_status(st, op);
 }
 
+// kernels/cache_kernels.cu:173-208
+void copy_blocks_mla(std::vector<torch::Tensor> const& kv_caches, const torch::Tensor& block_mapping) {
+  const char* op = "copy_blocks_mla";
+  const int64_t num_layers = (int64_t)kv_caches.size();
+  if (num_layers == 0) return;
+  const torch::Device dev = kv_caches[0].device();
+  TORCH_CHECK(dev.is_cuda(), "kv_cache must be on CUDA");
+  TORCH_CHECK(block_mapping.is_cuda() && block_mapping.scalar_type() == at::ScalarType::Long && block_mapping.dim() == 2 &&
+                  block_mapping.size(1) == 2 && block_mapping.is_contiguous(),
+              op, ": block_mapping must be a contiguous int64 [num_pairs, 2] tensor on the device");
+  std::vector<int64_t> ptrs(num_layers);
+  for (int64_t l = 0; l < num_layers; ++l) ptrs[l] = reinterpret_cast<int64_t>(kv_caches[l].data_ptr());
+  torch::Tensor ptrs_d = torch::from_blob(ptrs.data(), {num_layers}, torch::kInt64).to(dev);
+  const at::cuda::OptionalCUDAGuard guard(dev);
+  const int64_t block_bytes = kv_caches[0].stride(0) * kv_caches[0].element_size();  // padding included, as the reference
+  check_status(aph_copy_blocks_mla(ptrs_d.data_ptr<int64_t>(), block_mapping.data_ptr<int64_t>(), (int)num_layers,
+                                   block_mapping.size(0), block_bytes, stream_of()), op);
+}
+
+// kernels/cache_kernels.cu:463-500
+void concat_and_cache_mla(torch::Tensor& kv_c, torch::Tensor& k_pe, torch::Tensor& kv_cache, torch::Tensor& slot_mapping,
+                          const std::string& kv_cache_dtype, torch::Tensor& scale) {
+  const char* op = "concat_and_cache_mla";
+  TORCH_CHECK(kv_c.is_cuda() && k_pe.is_cuda() && kv_cache.is_cuda() && slot_mapping.is_cuda() && scale.is_cuda(), op,
+              ": tensors must be on a CUDA device");
+  TORCH_CHECK(kv_c.dim() == 2 && k_pe.dim() == 2 && kv_cache.dim() == 3, op, ": kv_c, k_pe must be 2-D and kv_cache 3-D");
+  const int64_t kv_lora_rank = kv_c.size(1), pe_dim = k_pe.size(1);
+  TORCH_CHECK(kv_cache.size(2) == kv_lora_rank + pe_dim);
+  TORCH_CHECK(kv_c.stride(1) == 1 && k_pe.stride(1) == 1 && kv_cache.stride(2) == 1, op, ": the last dimension must be contiguous");
+  TORCH_CHECK(k_pe.scalar_type() == kv_c.scalar_type(), op, ": dtype mismatch");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long && slot_mapping.is_contiguous(), op,
+              ": slot_mapping must be contiguous int64");
+  TORCH_CHECK(scale.scalar_type() == at::ScalarType::Float, op, ": scale must be float32");
+  const int kv = kv_code(kv_cache_dtype);
+  TORCH_CHECK(kv == APH_KV_AUTO ? kv_cache.scalar_type() == kv_c.scalar_type() : kv_cache.element_size() == 1, op,
+              ": kv_cache dtype does not match kv_cache_dtype");
+  const at::cuda::OptionalCUDAGuard guard(device_of(kv_c));
+  check_status(aph_concat_and_cache_mla(kv_c.data_ptr(), k_pe.data_ptr(), kv_cache.data_ptr(), slot_mapping.data_ptr<int64_t>(),
+                                        slot_mapping.size(0), (int)kv_lora_rank, (int)pe_dim, (int)kv_cache.size(1),
+                                        kv_cache.stride(0), kv_cache.stride(1), kv_c.stride(0), k_pe.stride(0),
+                                        dtype_code(kv_c, op), kv, scale.data_ptr<float>(), stream_of()), op);
+}
+
+// kernels/cache_kernels.cu:676-735
+void gather_cache(torch::Tensor const& src_cache, torch::Tensor const& dst, torch::Tensor const& block_table,
+                  torch::Tensor const& cu_seq_lens, int64_t batch_size, std::optional<torch::Tensor> seq_starts) {
+  const char* op = "gather_cache";
+  TORCH_CHECK(src_cache.is_cuda(), op, ": src_cache must be on a CUDA device");
+  TORCH_CHECK(block_table.scalar_type() == at::ScalarType::Int, "block_table must be int32");
+  TORCH_CHECK(cu_seq_lens.scalar_type() == at::ScalarType::Int, "cu_seq_lens must be int32");
+  if (seq_starts.has_value()) {
+    TORCH_CHECK(seq_starts->scalar_type() == at::ScalarType::Int, "seq_starts must be int32");
+    TORCH_CHECK(src_cache.device() == seq_starts->device(), "src_cache and seq_starts must be on the same device");
+  }
+  TORCH_CHECK(src_cache.device() == dst.device(), "src_cache and dst must be on the same device");
+  TORCH_CHECK(src_cache.device() == block_table.device(), "src_cache and block_table must be on the same device");
+  TORCH_CHECK(src_cache.device() == cu_seq_lens.device(), "src_cache and cu_seq_lens must be on the same device");
+  TORCH_CHECK(src_cache.scalar_type() == dst.scalar_type(), "src_cache and dst must have the same dtype");
+  TORCH_CHECK(src_cache.dim() >= 3 && cu_seq_lens.numel() >= batch_size + 1 && cu_seq_lens.is_contiguous(), op, ": bad shapes");
+  const int64_t es = src_cache.element_size();
+  const int64_t entry = src_cache.flatten(2, -1).size(2);
+  const at::cuda::OptionalCUDAGuard guard(device_of(src_cache));
+  check_status(aph_gather_cache(src_cache.data_ptr(), dst.data_ptr(), block_table.data_ptr<int32_t>(), cu_seq_lens.data_ptr<int32_t>(),
+                                seq_starts.has_value() ? seq_starts->data_ptr<int32_t>() : nullptr, (int)batch_size,
+                                (int)src_cache.size(1), entry * es, block_table.stride(0), src_cache.stride(0) * es,
+                                src_cache.stride(1) * es, dst.stride(0) * es, stream_of()), op);
+}
+
 void swap_blocks(torch::Tensor& src, torch::Tensor& dst, const torch::Tensor& block_mapping) {
   const char* op = "swap_blocks";
   int kind;
@@ -587,6 +655,17 @@ TORCH_LIBRARY_FRAGMENT(_C_cache_ops, ops) {
   ops.def(
       "copy_blocks(Tensor(a!)[] key_caches, Tensor[](b!) value_caches, "
       "Tensor block_mapping) -> ()");
+  // kernels/torch_bindings.cpp:691-693,716-722,731-734
+  ops.def("copy_blocks_mla(Tensor(a!)[] kv_caches, Tensor block_mapping) -> ()");
+  ops.def(
+      "concat_and_cache_mla(Tensor kv_c, Tensor k_pe,"
+      "                     Tensor! kv_cache,"
+      "                     Tensor slot_mapping,"
+      "                     str kv_cache_dtype,"
+      "                     Tensor scale) -> ()");
+  ops.def(
+      "gather_cache(Tensor src_cache, Tensor! dst, Tensor block_table, "
+      "Tensor cu_seq_lens, int batch_size, Tensor? seq_starts) -> ()");
   ops.def(
       "reshape_and_cache_flash(Tensor key, Tensor value,"
       "                        Tensor! key_cache,"
@@ -623,4 +702,7 @@ TORCH_LIBRARY_IMPL(_C_cache_ops, CUDA, ops) {
   ops.impl("swap_blocks", &swap_blocks);
   ops.impl("copy_blocks", &copy_blocks);
   ops.impl("reshape_and_cache_flash", &reshape_and_cache_flash);
+  ops.impl("copy_blocks_mla", &copy_blocks_mla);
+  ops.impl("concat_and_cache_mla", &concat_and_cache_mla);
+  ops.impl("gather_cache", &gather_cache);
 }

@@ -160,6 +160,25 @@ int aph_gptq_marlin_gemm(void* c, const void* a, const void* b_q_weight, const v
                          int use_atomic_add, int use_fp32_reduce, int is_zp_float, int dtype, void* scratch,
                          size_t scratch_bytes, void* stream);
 
+/* MLA cache ops (rest of kernels/cache_kernels.cu).
+ *   aph_copy_blocks_mla       cache_kernels.cu:100-117,173-208: aph_copy_blocks over ONE joint cache per layer;
+ *                             block_bytes = stride(0) * element size (padding included)
+ *   aph_concat_and_cache_mla  cache_kernels.cu:308-348,463-500: kv_cache[slot] = [kv_c[t] | k_pe[t]] (slot < 0: skipped),
+ *                             FP8-encoded with *scale unless kv_dtype is APH_KV_AUTO; strides in elements
+ *   aph_gather_cache          cache_kernels.cu:582-735: dst[cu_seq_lens[b] + t] = cache[block_table[b][seq_starts[b] /
+ *                             block_size + t / block_size]][t % block_size]; seq_starts may be NULL; strides in BYTES
+ */
+int aph_copy_blocks_mla(const int64_t* kv_cache_ptrs, const int64_t* block_mapping, int num_layers, int64_t num_pairs,
+                        int64_t block_bytes, void* stream);
+int aph_concat_and_cache_mla(const void* kv_c, const void* k_pe, void* kv_cache, const int64_t* slot_mapping,
+                             int64_t num_tokens, int kv_lora_rank, int pe_dim, int block_size, int64_t block_stride,
+                             int64_t entry_stride, int64_t kv_c_stride, int64_t k_pe_stride, int dtype, int kv_dtype,
+                             const float* scale, void* stream);
+int aph_gather_cache(const void* src_cache, void* dst, const int32_t* block_table, const int32_t* cu_seq_lens,
+                     const int32_t* seq_starts, int batch_size, int block_size, int64_t entry_bytes,
+                     int64_t block_table_stride, int64_t cache_block_stride_bytes, int64_t cache_entry_stride_bytes,
+                     int64_t dst_entry_stride_bytes, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Marlin repack - replaces kernels/quantization/gptq_marlin/gptq_marlin_repack.cu:236-322 and
  * awq_marlin_repack.cu:189-268: checkpoint formats -> the Marlin wire format gptq_marlin_gemm reads.

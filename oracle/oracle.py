@@ -173,3 +173,32 @@ def swap_blocks(src, dst, block_mapping):
     """cache_kernels.cu:25-67: dst[dst_block] = src[src_block] for every pair (whole blocks, padding included)."""
     for s, d in block_mapping.tolist():
         dst[d] = src[s]
+
+
+def concat_and_cache_mla(kv_c, k_pe, kv_cache, slot_mapping, kv_cache_dtype, scale):
+    """kernels/cache_kernels.cu:308-348: kv_cache[slot] = [kv_c | k_pe], FP8-encoded when the cache is FP8. In place."""
+    bs = kv_cache.shape[1]
+    row = torch.cat((kv_c, k_pe), dim=-1)
+    if kv_cache_dtype != "auto":
+        row = fp8_encode(row, float(scale), kv_cache_dtype)
+    for t in range(slot_mapping.shape[0]):
+        s = int(slot_mapping[t])
+        if s >= 0:
+            kv_cache[s // bs, s % bs] = row[t].view(kv_cache.dtype) if row.dtype != kv_cache.dtype else row[t]
+
+
+def copy_blocks_mla(kv_caches, block_mapping):
+    """kernels/cache_kernels.cu:100-117: sequential (src, dst) block copies inside every layer's joint cache."""
+    for c in kv_caches:
+        for s, d in block_mapping.tolist():
+            c[d] = c[s].clone()
+
+
+def gather_cache(src_cache, dst, block_table, cu_seq_lens, batch_size, seq_starts=None):
+    """kernels/cache_kernels.cu:582-660: the paged rows of every sequence, contiguous in dst. In place."""
+    bs = src_cache.shape[1]
+    for b in range(batch_size):
+        start, end = int(cu_seq_lens[b]), int(cu_seq_lens[b + 1])
+        off = int(seq_starts[b]) // bs if seq_starts is not None else 0
+        for t in range(end - start):
+            dst[start + t] = src_cache[int(block_table[b, off + t // bs]), t % bs]

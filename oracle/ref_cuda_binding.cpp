@@ -34,6 +34,10 @@ void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tens
 void swap_blocks(torch::Tensor& src, torch::Tensor& dst, const torch::Tensor& block_mapping);
 void copy_blocks(std::vector<torch::Tensor> const& key_caches, std::vector<torch::Tensor> const& value_caches,
                  const torch::Tensor& block_mapping);
+void copy_blocks_mla(std::vector<torch::Tensor> const& kv_caches, const torch::Tensor& block_mapping);
+void advance_step_flashattn(int64_t num_seqs, int64_t num_queries, int64_t block_size, torch::Tensor& input_tokens,
+                            torch::Tensor& sampled_token_ids, torch::Tensor& input_positions, torch::Tensor& seq_lens,
+                            torch::Tensor& slot_mapping, torch::Tensor& block_tables);
 void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache,
                        torch::Tensor& value_cache, torch::Tensor& slot_mapping,
                        const std::string& kv_cache_dtype, torch::Tensor& k_scale, torch::Tensor& v_scale);
@@ -89,6 +93,12 @@ TORCH_LIBRARY(_refcuda, ops) {
   ops.impl("swap_blocks", torch::kCUDA, &swap_blocks);
   ops.def("copy_blocks(Tensor(a!)[] key_caches, Tensor[](b!) value_caches, Tensor block_mapping) -> ()");
   ops.impl("copy_blocks", torch::kCUDA, &copy_blocks);
+  ops.def(
+      "advance_step_flashattn(int num_seqs, int num_queries, int block_size, Tensor! input_tokens, Tensor sampled_token_ids, "
+      "Tensor! input_positions, Tensor! seq_lens, Tensor! slot_mapping, Tensor block_tables) -> ()");
+  ops.impl("advance_step_flashattn", torch::kCUDA, &advance_step_flashattn);
+  ops.def("copy_blocks_mla(Tensor(a!)[] kv_caches, Tensor block_mapping) -> ()");
+  ops.impl("copy_blocks_mla", torch::kCUDA, &copy_blocks_mla);
   ops.def(
       "reshape_and_cache(Tensor key, Tensor value, Tensor! key_cache, Tensor! value_cache, Tensor slot_mapping, "
       "str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()");

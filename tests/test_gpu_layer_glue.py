@@ -37,8 +37,11 @@ def _ulp_close(a: torch.Tensor, b: torch.Tensor, frac: float = 0.01):
         return
     ia, ib = a.view(torch.int16).int(), b.view(torch.int16).int()
     d = (ia - ib).abs()
-    assert int(d.max()) <= 2, int(d.max())
-    assert float((d > 0).float().mean()) <= frac, float((d > 0).float().mean())
+    # values in the far tails of the GELUs (|result| < 1e-6, where libm and libdevice erf / tanh differ in the last bits of
+    # 1 + erf(x)) are compared absolutely: their bit patterns are many "ulps" apart while both are zero for every purpose
+    tiny = (a.float() - b.float()).abs() <= 1e-6
+    assert bool(((d <= 2) | tiny).all()), int(d[~tiny].max())
+    assert float(((d > 0) & ~tiny).float().mean()) <= frac, float((d > 0).float().mean())
 
 
 def _ref():
@@ -278,7 +281,16 @@ def test_advance_step_flashattn(num_seqs, num_queries):
     slots = torch.randint(0, 10000, (num_seqs,), generator=gen)
     bt = torch.randint(0, 5000, (num_seqs, max_blocks), generator=gen, dtype=torch.int32)
     dev = [t.to(DEV) for t in (tok, sampled, pos, lens, slots, bt)]
+    ref = oracle.refcuda()
+    if ref is not None and hasattr(ref, "advance_step_flashattn") and num_seqs > 0:
+        rdev = [t.clone() for t in dev]
+        ref.advance_step_flashattn(num_seqs, num_queries, bs, rdev[0], rdev[1], rdev[2], rdev[3], rdev[4], rdev[5])
+    else:
+        rdev = None
     A.ops.advance_step_flashattn(num_seqs, num_queries, bs, dev[0], dev[1], dev[2], dev[3], dev[4], dev[5])
+    if rdev is not None:
+        for got, want in zip(dev, rdev):
+            assert torch.equal(got, want)
     lg.advance_step_flashattn(num_seqs, num_queries, bs, tok, sampled, pos, lens, slots, bt)
     for got, want in zip(dev, (tok, sampled, pos, lens, slots, bt)):
         assert torch.equal(got.cpu(), want)
