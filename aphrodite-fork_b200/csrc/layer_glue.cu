@@ -49,8 +49,8 @@ __device__ __forceinline__ float block_sum(float v, float* s_part) {
 
 // One CTA per token. VEC elements per 16-byte access (1 = unaligned / odd hidden size fallback). Up to ITER vectors
 // per thread stay in registers between the two phases; longer rows re-read what phase one wrote (L2 hits).
-template <typename T, int VEC, int ITER, bool FUSED_ADD>
-__global__ void __launch_bounds__(1024, 1)
+template <typename T, int VEC, int ITER, bool FUSED_ADD, int MAXT>
+__global__ void __launch_bounds__(MAXT, MAXT == 1024 ? 1 : 5)
     rms_norm_kernel(T* __restrict__ out, T* __restrict__ input, T* __restrict__ residual, const T* __restrict__ weight,
                     float epsilon, int hidden, int64_t in_stride) {
   using V = Vec<T, VEC>;
@@ -62,11 +62,16 @@ __global__ void __launch_bounds__(1024, 1)
   V* out_v = FUSED_ADD ? in_v : reinterpret_cast<V*>(out + row * (int64_t)hidden);
   const V* w_v = reinterpret_cast<const V*>(weight);
   pdl_trigger();
-  V wreg[ITER];  // weights are immutable: fetched before waiting on the previous kernel
+  // few tokens (latency-bound): the weights are immutable, fetch them before waiting on the previous kernel. Many tokens
+  // (bandwidth-bound): read them when needed (8 KiB, L1-resident) and keep the registers for occupancy.
+  constexpr bool PRELOAD_W = MAXT == 1024;
+  V wreg[PRELOAD_W ? ITER : 1];
+  if constexpr (PRELOAD_W) {
 #pragma unroll
-  for (int i = 0; i < ITER; ++i) {
-    const int idx = threadIdx.x + i * blockDim.x;
-    if (idx < nvec) wreg[i] = w_v[idx];
+    for (int i = 0; i < ITER; ++i) {
+      const int idx = threadIdx.x + i * blockDim.x;
+      if (idx < nvec) wreg[i] = w_v[idx];
+    }
   }
   pdl_wait();
   V keep[ITER];
@@ -111,9 +116,9 @@ __global__ void __launch_bounds__(1024, 1)
     const int idx = threadIdx.x + i * blockDim.x;
     if (idx < nvec) {
       V x = keep[i];
+      const V w = PRELOAD_W ? wreg[PRELOAD_W ? i : 0] : w_v[idx];
 #pragma unroll
-      for (int e = 0; e < VEC; ++e)
-        x.v[e] = mul_t(ScalarTraits<T>::from_float(ScalarTraits<T>::to_float(x.v[e]) * rs), wreg[i].v[e]);
+      for (int e = 0; e < VEC; ++e) x.v[e] = mul_t(ScalarTraits<T>::from_float(ScalarTraits<T>::to_float(x.v[e]) * rs), w.v[e]);
       out_v[idx] = x;
     }
   }
@@ -297,14 +302,20 @@ int launch_norm(T* out, T* input, T* residual, const T* weight, float eps, int64
   constexpr int VEC = 16 / (int)sizeof(T);
   if (vec_ok) {
     const int nvec = hidden / VEC;
-    // few tokens: one vector per thread (latency); many tokens: two per thread and smaller CTAs (occupancy)
-    int threads = tokens < 512 ? nvec : (nvec + 1) / 2;
-    threads = std::min(1024, std::max(32, (threads + 31) / 32 * 32));
-    APH_LAUNCH_PDL(rms_norm_kernel<T, VEC, 2, FUSED>, dim3((unsigned)tokens), dim3(threads), 0, stream, out, input, residual,
-                   weight, eps, hidden, in_stride);
+    // few tokens: one vector per thread (latency); many tokens: two per thread in CTAs of at most 256 threads, five of
+    // them per SM (occupancy, bytes in flight)
+    if (tokens < 512 || nvec > 512) {
+      const int threads = std::min(1024, std::max(32, (nvec + 31) / 32 * 32));
+      APH_LAUNCH_PDL((rms_norm_kernel<T, VEC, 2, FUSED, 1024>), dim3((unsigned)tokens), dim3(threads), 0, stream, out, input, residual,
+                     weight, eps, hidden, in_stride);
+    } else {
+      const int threads = std::max(32, ((nvec + 1) / 2 + 31) / 32 * 32);
+      APH_LAUNCH_PDL((rms_norm_kernel<T, VEC, 2, FUSED, 256>), dim3((unsigned)tokens), dim3(threads), 0, stream, out, input, residual,
+                     weight, eps, hidden, in_stride);
+    }
   } else {
     const int threads = std::min(1024, std::max(32, (hidden + 31) / 32 * 32));
-    APH_LAUNCH_PDL(rms_norm_kernel<T, 1, 1, FUSED>, dim3((unsigned)tokens), dim3(threads), 0, stream, out, input, residual,
+    APH_LAUNCH_PDL((rms_norm_kernel<T, 1, 1, FUSED, 1024>), dim3((unsigned)tokens), dim3(threads), 0, stream, out, input, residual,
                    weight, eps, hidden, in_stride);
   }
   return APH_OK;
@@ -456,7 +467,7 @@ extern "C" int aph_advance_step_flashattn(int num_seqs, int num_queries, int blo
   APH_CHECK(num_seqs >= 0 && num_queries >= 0 && num_queries <= num_seqs && block_size > 0, APH_ERR_INVALID_ARGUMENT,
             "%s: need 0 <= num_queries <= num_seqs and block_size > 0", op);
   if (num_seqs == 0) return APH_OK;
-  APH_CHECK(input_tokens && sampled_token_ids && input_positions && seq_lens && slot_mapping && block_tables,
+  APH_CHECK(input_tokens && (sampled_token_ids || num_queries == 0) && input_positions && seq_lens && slot_mapping && block_tables,
             APH_ERR_INVALID_ARGUMENT, "%s: null tensor", op);
   const unsigned grid = (unsigned)std::max(1, (num_queries + 255) / 256);
   APH_LAUNCH_PDL(advance_step_flashattn_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, num_seqs, num_queries, block_size,

@@ -37,9 +37,9 @@ def _ulp_close(a: torch.Tensor, b: torch.Tensor, frac: float = 0.01):
         return
     ia, ib = a.view(torch.int16).int(), b.view(torch.int16).int()
     d = (ia - ib).abs()
-    # values in the far tails of the GELUs (|result| < 1e-6, where libm and libdevice erf / tanh differ in the last bits of
-    # 1 + erf(x)) are compared absolutely: their bit patterns are many "ulps" apart while both are zero for every purpose
-    tiny = (a.float() - b.float()).abs() <= 1e-6
+    # values in the far tails of the GELUs (x < -4: 1 + erf(x) cancels to a few fp32 ulps, so libm and libdevice agree to
+    # ~1e-7 absolutely but not relatively) are compared absolutely: differences below 1e-5 on activations of order 1
+    tiny = (a.float() - b.float()).abs() <= 1e-5
     assert bool(((d <= 2) | tiny).all()), int(d[~tiny].max())
     assert float(((d > 0) & ~tiny).float().mean()) <= frac, float((d > 0).float().mean())
 
@@ -150,7 +150,8 @@ def test_rotary_embedding(tokens, nh, nkv, d, rot, neox, dtype):
     wq, wk = lg.rotary_embedding(pos.cpu(), q.cpu().contiguous(), k.cpu().contiguous(), d, cache.cpu(), neox)
     ref = _ref()
     if ref is not None:
-        rq, rk = q.contiguous(), k.contiguous()
+        # copies (contiguous() would alias q when there is one token and the reference kernel works in place)
+        rq, rk = q.clone(memory_format=torch.contiguous_format), k.clone(memory_format=torch.contiguous_format)
         ref.rotary_embedding(pos, rq, rk, d, cache, neox)
     A.ops.rotary_embedding(pos, q, k, d, cache, neox)
     assert torch.equal(v, v0)
