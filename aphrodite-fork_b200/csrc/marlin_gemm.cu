@@ -457,7 +457,7 @@ extern "C" int aph_gptq_marlin_gemm(void* c, const void* a, const void* b_q_weig
   APH_CHECK(b_q_type == mg::ID_UINT4 || b_q_type == mg::ID_UINT4B8, APH_ERR_UNSUPPORTED,
             "gptq_marlin_gemm: 8-bit weight types are not implemented yet");
   APH_CHECK(g_idx == nullptr && perm == nullptr, APH_ERR_UNSUPPORTED,
-            "gptq_marlin_gemm: act-order (g_idx / perm) is not implemented yet");
+            "gptq_marlin_gemm: act-order goes through aph_permute_cols + this call with g_idx = perm = NULL (is_k_full only)");
   APH_CHECK(dtype == APH_DT_F16 || dtype == APH_DT_BF16, APH_ERR_INVALID_ARGUMENT,
             "gpt_marlin_gemm only supports bfloat16 and float16");
   APH_CHECK(size_k % mg::KT == 0, APH_ERR_INVALID_ARGUMENT, "size_k = %lld is not divisible by tile_k = %d",

@@ -55,6 +55,26 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// Act-order: out[m][k] = a[m][perm[k]] (reference permute_cols_kernel, gptq_marlin.cu:459-515). With the weight rows
+// sorted by group (the repack above with `perm`) and a full K this turns an act-order GEMM into the plain grouped one.
+// 2-byte elements; a thread gathers 8 and stores them as one 16-byte vector.
+__global__ void __launch_bounds__(256)
+    permute_cols_kernel(uint16_t* __restrict__ out, const uint16_t* __restrict__ a, const int32_t* __restrict__ perm, int size_k,
+                        int64_t lda) {
+  pdl_trigger();
+  const int64_t row = blockIdx.y;
+  const int k0 = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (k0 >= size_k) return;
+  int src[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) src[j] = perm[k0 + j];  // immutable: before the wait
+  pdl_wait();
+  alignas(16) uint16_t v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = a[row * lda + src[j]];
+  *reinterpret_cast<uint4*>(out + row * size_k + k0) = *reinterpret_cast<const uint4*>(v);
+}
+
 template <bool AWQ>
 int launch_repack(int32_t* out, const int32_t* in, const int32_t* perm, int64_t size_k, int64_t size_n, int num_bits,
                   cudaStream_t stream) {
@@ -98,4 +118,16 @@ extern "C" int aph_awq_marlin_repack(int32_t* out, const int32_t* b_q_weight, in
   const int st = check_repack("awq_marlin_repack", out, b_q_weight, size_k, size_n, num_bits);
   if (st != APH_OK) return st;
   return launch_repack<true>(out, b_q_weight, nullptr, size_k, size_n, num_bits, (cudaStream_t)stream);
+}
+
+extern "C" int aph_permute_cols(void* out, const void* a, const int32_t* perm, int64_t size_m, int64_t size_k, int64_t lda,
+                                void* stream) {
+  const char* op = "permute_cols";
+  APH_CHECK(size_m >= 0 && size_m <= 65535 && size_k > 0 && size_k % 8 == 0 && size_k < (1LL << 31), APH_ERR_INVALID_ARGUMENT,
+            "%s: size_k must be a multiple of 8 and size_m at most 65535", op);
+  if (size_m == 0) return APH_OK;
+  APH_CHECK(out && a && perm && aligned16(out), APH_ERR_INVALID_ARGUMENT, "%s: null or misaligned tensor", op);
+  APH_LAUNCH_PDL(permute_cols_kernel, dim3((unsigned)((size_k / 8 + 255) / 256), (unsigned)size_m), dim3(256), (size_t)0,
+                 (cudaStream_t)stream, (uint16_t*)out, (const uint16_t*)a, perm, (int)size_k, lda);
+  return APH_OK;
 }

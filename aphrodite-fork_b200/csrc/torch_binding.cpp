@@ -366,11 +366,27 @@ torch::Tensor gptq_marlin_gemm(torch::Tensor& a, torch::Tensor& b_q_weight, torc
     sptr = scratch.data_ptr();
   }
   const void* zp = (has_zp && b_zeros.numel() > 0) ? b_zeros.data_ptr() : nullptr;
-  const int32_t* gi = g_idx.numel() > 0 ? g_idx.data_ptr<int32_t>() : nullptr;
-  const int32_t* pm = perm.numel() > 0 ? perm.data_ptr<int32_t>() : nullptr;
-  const int st = aph_gptq_marlin_gemm(c.data_ptr(), a.data_ptr(), b_q_weight.data_ptr(), b_scales.data_ptr(), zp, gi,
-                                      pm, workspace.data_ptr<int32_t>(), workspace.numel(), b_q_type_id, size_m,
-                                      size_n, size_k, a.stride(0), b_scales.size(0), is_k_full, has_zp,
+  // Act-order (gptq_marlin.cu:2344-2400,2187-2202): g_idx and perm both of length size_k. With a full K the weight rows are
+  // sorted by group, so the GEMM on the column-permuted activations is the plain grouped one.
+  TORCH_CHECK((g_idx.numel() == 0 && perm.numel() == 0) || (g_idx.numel() == size_k && perm.numel() == size_k),
+              "Unexpected g_idx.size(0) = ", g_idx.numel(), " and perm.size(0) = ", perm.numel(), ", where size_k = ", size_k);
+  const void* a_ptr = a.data_ptr();
+  int64_t lda = a.stride(0);
+  torch::Tensor a_tmp;
+  if (g_idx.numel() > 0) {
+    TORCH_CHECK(is_k_full, op, ": act-order with a partial K (row-parallel shards, is_k_full = False) is not implemented");
+    TORCH_CHECK(b_scales.size(0) > 1, "For act_order, num_groups must be > 1");
+    TORCH_CHECK(perm.is_cuda() && perm.scalar_type() == at::ScalarType::Int && perm.is_contiguous(), op,
+                ": perm must be a contiguous int32 tensor on the device");
+    a_tmp = torch::empty({size_m, size_k}, a.options());
+    check_status(aph_permute_cols(a_tmp.data_ptr(), a.data_ptr(), perm.data_ptr<int32_t>(), size_m, size_k, a.stride(0), stream_of()),
+                 op);
+    a_ptr = a_tmp.data_ptr();
+    lda = size_k;
+  }
+  const int st = aph_gptq_marlin_gemm(c.data_ptr(), a_ptr, b_q_weight.data_ptr(), b_scales.data_ptr(), zp, nullptr,
+                                      nullptr, workspace.data_ptr<int32_t>(), workspace.numel(), b_q_type_id, size_m,
+                                      size_n, size_k, lda, b_scales.size(0), is_k_full, has_zp,
                                       use_atomic_add, use_fp32_reduce, is_zp_float, dt, sptr, sbytes, stream_of());
   check_status(st, op);
   return c;

@@ -188,6 +188,12 @@ int aph_gather_cache(const void* src_cache, void* dst, const int32_t* block_tabl
  *   AWQ input   [size_k, size_n / pack] int32 (packed along n with AWQ's column interleave)
  * size_k % 16 == 0 and size_n % 64 == 0. Bit-identical with the reference kernels.
  * ------------------------------------------------------------------------------------------- */
+/* Act-order (desc_act) support - replaces permute_cols_kernel, gptq_marlin.cu:459-515,2187-2194: out[m][k] =
+ * a[m][perm[k]] for 2-byte element types, out dense [size_m, size_k]. With weights repacked with the same `perm`
+ * (rows sorted by group) and is_k_full, act-order GEMM = aph_permute_cols + aph_gptq_marlin_gemm with g_idx = perm =
+ * NULL; that is what the torch op does. */
+int aph_permute_cols(void* out, const void* a, const int32_t* perm, int64_t size_m, int64_t size_k, int64_t lda,
+                     void* stream);
 int aph_gptq_marlin_repack(int32_t* out, const int32_t* b_q_weight, const int32_t* perm, int64_t size_k,
                            int64_t size_n, int num_bits, void* stream);
 int aph_awq_marlin_repack(int32_t* out, const int32_t* b_q_weight, int64_t size_k, int64_t size_n, int num_bits,

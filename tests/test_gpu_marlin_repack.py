@@ -85,3 +85,36 @@ def test_repack_errors():
         A.ops.gptq_marlin_repack(w, empty, 256, 64, 4)
     with pytest.raises(RuntimeError, match="not on GPU"):
         A.ops.gptq_marlin_repack(w.cpu(), empty, 128, 64, 4)
+
+
+@pytest.mark.parametrize("m", [1, 16, 64, 300])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_act_order_gemm_full_k(m, dtype):
+    """desc_act checkpoints (tests/kernels/test_marlin_gemm.py:189-260 with act_order=True, is_k_full=True): rows of the
+    weight carry a shuffled group index; repack with sort_indices, GEMM with (g_idx, sort_indices)."""
+    k, n, gs = 2048, 512, 128
+    g = torch.Generator().manual_seed(7 + m)
+    w = torch.randn(k, n, generator=g).to(dtype)
+    w_ref, bq, s = mf.marlin_quantize(w, 4, gs)[:3]
+    q = mf.unpack_weights(bq.numpy(), k, n, 4)
+    rand_perm = torch.randperm(k, generator=g)
+    g_idx = (torch.arange(k) // gs)[rand_perm].to(torch.int32)       # quant_utils.permute_rows
+    w_shuffled = w_ref[rand_perm]
+    checkpoint = mf.gptq_pack(q[rand_perm.numpy()], 4)
+    sort_indices = torch.argsort(g_idx, stable=True).to(torch.int32)   # quant_utils.sort_weights
+    g_idx_sorted = g_idx[sort_indices.long()].contiguous()
+    b = A.ops.gptq_marlin_repack(_dev(checkpoint), sort_indices.to(DEV), k, n, 4)
+    a = torch.randn(m, k, generator=g).to(dtype).to(DEV)
+    ws = torch.zeros(148 * 64, dtype=torch.int32, device=DEV)
+    empty = torch.empty(0, dtype=torch.int32, device=DEV)
+    args = (a, b, s.to(DEV), empty, g_idx_sorted.to(DEV), sort_indices.to(DEV), ws, mf.UINT4B8, m, n, k, True, False, False, True, False)
+    c = A.ops.gptq_marlin_gemm(*args)
+    want = a.float().cpu().double() @ w_shuffled.double()
+    assert float((c.cpu().double() - want).abs().max()) <= 2e-2 * float(want.abs().max())
+    assert int(ws.abs().max()) == 0
+    ref = oracle.refcuda()
+    if ref is not None:
+        rc = ref.gptq_marlin_gemm(*args)
+        assert float((c.float() - rc.float()).abs().max()) <= 1e-2 * float(rc.float().abs().max())
+    with pytest.raises(RuntimeError, match="partial K"):
+        A.ops.gptq_marlin_gemm(*args[:11], False, *args[12:])
