@@ -54,7 +54,7 @@ def build(verbose: bool = False) -> str:
     hdrs = _headers()
     extra = ["-DAPH_FAST_BUILD"] if FAST else []
     jobs = []  # (object, command, deps)
-    for name in ("runtime", "cache_kernels", "paged_attention", "marlin_gemm", "marlin_repack", "layer_glue"):
+    for name in ("runtime", "cache_kernels", "paged_attention", "marlin_gemm", "marlin_repack", "layer_glue", "all_reduce"):
         src = os.path.join(CSRC, name + ".cu")
         obj = os.path.join(OBJ, name + ".o")
         jobs.append((obj, [NVCC, *NVCC_FLAGS, *extra, "-c", src, "-o", obj], [src, *hdrs]))

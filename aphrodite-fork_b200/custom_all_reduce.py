@@ -1,0 +1,62 @@
+"""One-shot all-reduce over NVLink peer memory for the decode step's row-parallel outputs.
+
+Host side of csrc/all_reduce.cu, the counterpart of the reference's CustomAllreduce
+(distributed/device_communicators/custom_all_reduce.py:47-304): the reference exchanges CUDA-IPC handles through
+Python and registers buffers with a C++ object; here the symmetric buffer and its peer mappings come from
+`torch.distributed._symmetric_memory` and the kernel is called through the C ABI on the current stream (capturable in a
+CUDA graph). Eligibility mirrors the reference (`should_custom_ar`, :216-229): contiguous, a multiple of 16 bytes, at
+most `max_size` bytes, world size 2/4/6/8; anything else goes to NCCL.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from ._loader import c_api
+
+_DT = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
+
+
+class OneShotAllReduce:
+    _SUPPORTED_WORLD_SIZES = (2, 4, 6, 8)  # custom_all_reduce.py:49
+
+    def __init__(self, group: dist.ProcessGroup, device: torch.device, max_size: int = 8 * 1024 * 1024, max_blocks: int = 0):
+        import torch.distributed._symmetric_memory as symm
+
+        self.group = group
+        self.world_size = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        if self.world_size not in self._SUPPORTED_WORLD_SIZES:
+            raise RuntimeError(f"one-shot all-reduce supports world sizes {self._SUPPORTED_WORLD_SIZES}")
+        self.lib = c_api()
+        self.lib.aph_all_reduce_signal_bytes.restype = ctypes.c_size_t
+        self.signal_bytes = int(self.lib.aph_all_reduce_signal_bytes())
+        self.max_size = max_size
+        self.max_blocks = max_blocks
+        self.device = torch.device(device)
+        self.buffer = symm.empty(self.signal_bytes + max_size, dtype=torch.uint8, device=self.device)
+        self.buffer[: self.signal_bytes].zero_()
+        self.handle = symm.rendezvous(self.buffer, group.group_name)
+        self.peer_ptrs = int(self.handle.buffer_ptrs_dev)
+        self.counters = torch.zeros(int(self.lib.aph_all_reduce_max_blocks()), dtype=torch.int32, device=self.device)
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group)  # every rank's flags are zero before anybody starts
+
+    def should_use(self, x: torch.Tensor) -> bool:
+        n = x.numel() * x.element_size()
+        return (x.is_cuda and x.is_contiguous() and x.dtype in _DT and n % 16 == 0 and 0 < n <= self.max_size
+                and x.data_ptr() % 16 == 0)
+
+    def all_reduce(self, x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """out = sum over ranks of x (out defaults to x: in place, as TPGroup.all_reduce)."""
+        out = x if out is None else out
+        st = self.lib.aph_one_shot_all_reduce(
+            ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(x.data_ptr()), ctypes.c_void_p(self.peer_ptrs),
+            ctypes.c_void_p(self.counters.data_ptr()), self.rank, self.world_size, ctypes.c_int64(x.numel()), _DT[x.dtype],
+            self.max_blocks, ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+        if st != 0:
+            raise RuntimeError(self.lib.aph_b200_last_error().decode())
+        return out

@@ -141,6 +141,8 @@ class DecodeModel:
     def __init__(self, cfg: DecodeConfig, batch: int, ctx: int, tp: Optional[TPGroup] = None, device="cuda", seed: int = 0):
         self.cfg, self.batch, self.ctx = cfg, batch, ctx
         self.tp = tp if tp is not None else TPGroup()
+        if self.tp.world_size > 1 and self.tp.custom is None and torch.device(device).type == "cuda":
+            self.tp.enable_custom_all_reduce(device)  # peer-memory all-reduce for the 1 MiB messages; NCCL if unavailable
         gen = torch.Generator(device=device).manual_seed(seed)
         bs = cfg.block_size
         blocks_per_seq = (ctx + bs - 1) // bs

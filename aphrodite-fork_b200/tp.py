@@ -129,8 +129,10 @@ def shard_marlin_weight(q_weight: torch.Tensor, scales: torch.Tensor, zeros: Opt
 class TPGroup:
     """The exchange step: all_reduce(sum) of the row-parallel partial outputs, in place, on the current stream.
 
-    world_size 1 never touches torch.distributed. The backend is whatever the process group was created with: NCCL
-    (NVLink / NVSwitch, NVLS when NCCL picks it) on GPUs, gloo in the CPU tests.
+    world_size 1 never touches torch.distributed. On GPUs small messages (<= 8 MiB, the reference's limit,
+    custom_all_reduce.py:53) go through the one-shot peer-memory kernel of csrc/all_reduce.cu when
+    `enable_custom_all_reduce()` succeeded; everything else - and every CPU test (gloo) - goes through the process
+    group's own all_reduce (NCCL over NVLink / NVSwitch on GPUs). APH_CUSTOM_AR=0 keeps NCCL for everything.
     """
 
     def __init__(self, group: Optional[dist.ProcessGroup] = None):
@@ -140,8 +142,25 @@ class TPGroup:
             self.rank = dist.get_rank(self.group)
         else:
             self.group, self.world_size, self.rank = None, 1, 0
+        self.custom = None
+        self.custom_error: Optional[str] = None
+
+    def enable_custom_all_reduce(self, device, max_size: int = 8 * 1024 * 1024) -> bool:
+        """Set up the peer-memory all-reduce; returns False (and keeps NCCL) when the world size or the platform does
+        not support it - the reason is kept in `custom_error`."""
+        import os
+        if self.world_size == 1 or os.environ.get("APH_CUSTOM_AR", "1") == "0":
+            return False
+        try:
+            from .custom_all_reduce import OneShotAllReduce
+            self.custom = OneShotAllReduce(self.group, device, max_size)
+        except Exception as e:  # no NVLink peer access, unsupported world size, ...: NCCL serves the exchange
+            self.custom, self.custom_error = None, f"{type(e).__name__}: {e}"
+        return self.custom is not None
 
     def all_reduce(self, x: torch.Tensor) -> torch.Tensor:
         if self.world_size > 1:
+            if self.custom is not None and self.custom.should_use(x):
+                return self.custom.all_reduce(x)
             dist.all_reduce(x, op=dist.ReduceOp.SUM, group=self.group)
         return x

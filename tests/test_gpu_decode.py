@@ -135,3 +135,89 @@ def test_tensor_parallel_decode_step_over_nccl():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert got == [(0, True, True, True), (1, True, True, True)]
+
+
+def _ar_worker(rank, world, port, q):
+    import faulthandler
+    import torch.distributed as dist
+    faulthandler.dump_traceback_later(150, exit=True)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        from aphrodite_fork_b200.tp import TPGroup
+        tp = TPGroup()
+        ok = tp.enable_custom_all_reduce(dev)
+        if not ok:
+            q.put((rank, "setup failed: " + str(tp.custom_error)))
+            return
+        bad = []
+        gen = torch.Generator(device=dev).manual_seed(100 + rank)
+        for dtype in (torch.bfloat16, torch.float16, torch.float32):
+            for shape in ((1, 4096), (64, 8192), (256, 8192), (3, 8), (64, 8200)):
+                for rep in range(3):
+                    x = torch.randn(shape, device=dev, generator=gen).to(dtype)
+                    parts = [torch.empty_like(x) for _ in range(world)]
+                    dist.all_gather(parts, x)
+                    want = parts[0].float()
+                    for p in parts[1:]:
+                        want = want + p.float()  # fp32, rank order, one rounding: the kernel's definition
+                    want = want.to(dtype)
+                    assert tp.custom.should_use(x)
+                    got = tp.all_reduce(x.clone())
+                    if not torch.equal(got, want):
+                        bad.append((str(dtype), shape, rep, float((got.float() - want.float()).abs().max())))
+        # too large / misaligned messages take NCCL
+        big = torch.ones(5 * 1024 * 1024, device=dev, dtype=torch.bfloat16)
+        assert not tp.custom.should_use(big)
+        assert float(tp.all_reduce(big)[0]) == world
+        # many back-to-back calls under a CUDA graph: the flags must survive replays
+        x = torch.randn(64, 8192, device=dev, generator=gen).to(torch.bfloat16)
+        y = torch.empty_like(x)
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            tp.custom.all_reduce(x, y)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(20):
+                tp.custom.all_reduce(x, y)
+        first = None
+        for _ in range(10):
+            g.replay()
+            torch.cuda.synchronize()
+            first = y.clone() if first is None else first
+            if not torch.equal(y, first):
+                bad.append(("graph replay differs",))
+        parts = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(parts, x)
+        want = sum(p.float() for p in parts[1:]) + parts[0].float() if world == 2 else None
+        if want is not None and not torch.equal(first, want.to(torch.bfloat16)):
+            bad.append(("graph result wrong",))
+        del g
+        torch.cuda.synchronize()
+        q.put((rank, bad))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_one_shot_all_reduce_over_peer_memory():
+    """csrc/all_reduce.cu against an fp32 rank-order sum of all_gather'ed inputs: bit-exact on every rank, eager and
+    under CUDA-graph replay (the reference's tests/distributed/test_custom_all_reduce.py runs the same two modes)."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_ar_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, bad in res:
+        assert bad == [], (rank, bad)
