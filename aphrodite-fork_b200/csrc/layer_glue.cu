@@ -207,9 +207,8 @@ __global__ void __launch_bounds__(512)
   pdl_trigger();
   const int token = blockIdx.x;
   const int embed = rot_dim / 2;
-  // positions, offsets and the table are step inputs, not outputs of the previous kernel
+  pdl_wait();  // positions may come from advance_step_flashattn earlier in the same chain: read them after the wait
   const T* cache = cos_sin_cache + (positions[token] + (cache_offsets ? cache_offsets[token] : 0)) * rot_dim;
-  pdl_wait();
   const int nq = num_heads * embed, total = nq + (key != nullptr ? num_kv_heads * embed : 0);
   for (int i = threadIdx.x; i < total; i += blockDim.x) {
     const bool is_q = i < nq;
@@ -238,9 +237,9 @@ __global__ void __launch_bounds__(512)
   pdl_trigger();
   const int token = blockIdx.x;
   const int embed = rot_dim / 2, per_head = embed / PV;
+  pdl_wait();  // positions may come from advance_step_flashattn earlier in the same chain
   const T* cache = cos_sin_cache + (positions[token] + (cache_offsets ? cache_offsets[token] : 0)) * rot_dim;
   const int nq = num_heads * per_head, total = nq + (key != nullptr ? num_kv_heads * per_head : 0);
-  pdl_wait();
   for (int i = threadIdx.x; i < total; i += blockDim.x) {
     const bool is_q = i < nq;
     const int j = is_q ? i : i - nq;

@@ -37,7 +37,9 @@ class OneShotAllReduce:
         self.max_size = max_size
         self.max_blocks = max_blocks
         self.device = torch.device(device)
-        self.buffer = symm.empty(self.signal_bytes + max_size, dtype=torch.uint8, device=self.device)
+        self.lib.aph_all_reduce_buffer_bytes.restype = ctypes.c_size_t
+        total = int(self.lib.aph_all_reduce_buffer_bytes(self.world_size, ctypes.c_int64(max_size)))
+        self.buffer = symm.empty(total, dtype=torch.uint8, device=self.device)
         self.buffer[: self.signal_bytes].zero_()
         self.handle = symm.rendezvous(self.buffer, group.group_name)
         self.peer_ptrs = int(self.handle.buffer_ptrs_dev)
@@ -56,7 +58,7 @@ class OneShotAllReduce:
         st = self.lib.aph_one_shot_all_reduce(
             ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(x.data_ptr()), ctypes.c_void_p(self.peer_ptrs),
             ctypes.c_void_p(self.counters.data_ptr()), self.rank, self.world_size, ctypes.c_int64(x.numel()), _DT[x.dtype],
-            self.max_blocks, ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+            ctypes.c_int64(self.max_size), self.max_blocks, ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
         if st != 0:
             raise RuntimeError(self.lib.aph_b200_last_error().decode())
         return out

@@ -243,17 +243,19 @@ int aph_advance_step_flashattn(int num_seqs, int num_queries, int block_size, in
 /* ---------------------------------------------------------------------------------------------
  * One-shot all-reduce over NVLink peer memory - replaces cross_device_reduce_1stage,
  * kernels/all_reduce/custom_all_reduce.cuh:296-318 (barriers :140-200, dispatch :525-600).
- * Every rank owns one symmetric buffer laid out [aph_all_reduce_signal_bytes() of flags, zeroed once | data], mapped
- * into every peer (CUDA IPC / torch symmetric memory); peer_bufs_dev is a DEVICE array of `world` base pointers in
- * rank order; counters is a rank-local zeroed uint32[aph_all_reduce_max_blocks()]. out[i] = sum over ranks of in[i],
- * added in fp32 in rank order and rounded once (bit-identical on every rank); out may alias in. numel * element size
- * must be a multiple of 16 and at most the data capacity of the buffers. All ranks must call with the same numel,
- * dtype and max_blocks, in the same order. world in {2, 4, 6, 8}.
+ * Every rank owns one symmetric buffer of aph_all_reduce_buffer_bytes(world, slot_bytes) bytes laid out
+ * [aph_all_reduce_signal_bytes() of flags, zeroed once | 2 halves x world slots x slot_bytes], mapped into every peer
+ * (CUDA IPC / torch symmetric memory); peer_bufs_dev is a DEVICE array of `world` base pointers in rank order; counters
+ * is a rank-local zeroed uint32[aph_all_reduce_max_blocks()]. Each rank pushes its input into its slot on every rank,
+ * one flag barrier, then out[i] = sum over slots, added in fp32 in rank order and rounded once (bit-identical on every
+ * rank); out may alias in. numel * element size must be a multiple of 16 and at most slot_bytes. All ranks must call
+ * with the same numel, dtype and max_blocks, in the same order. world in {2, 4, 6, 8}.
  * ------------------------------------------------------------------------------------------- */
 size_t aph_all_reduce_signal_bytes(void);
+size_t aph_all_reduce_buffer_bytes(int world, int64_t slot_bytes);
 int aph_all_reduce_max_blocks(void);
 int aph_one_shot_all_reduce(void* out, const void* in, const void* const* peer_bufs_dev, uint32_t* counters, int rank,
-                            int world, int64_t numel, int dtype, int max_blocks, void* stream);
+                            int world, int64_t numel, int dtype, int64_t slot_bytes, int max_blocks, void* stream);
 
 #ifdef __cplusplus
 }

@@ -94,7 +94,7 @@ def _free_port():
 def _nccl_worker(rank, world, port, q):
     import faulthandler
     import torch.distributed as dist
-    faulthandler.dump_traceback_later(150, exit=True)  # a hang must end with a stack trace, not with the suite's timeout
+    faulthandler.dump_traceback_later(90, exit=True)  # a hang must end with a stack trace, not with the suite's timeout
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -117,6 +117,9 @@ def _nccl_worker(rank, world, port, q):
         del model
         torch.cuda.synchronize()
         q.put(res)
+    except Exception:  # the parent must see the reason, not a queue timeout
+        import traceback
+        q.put((rank, "EXCEPTION " + traceback.format_exc()))
     finally:
         dist.destroy_process_group()
 
@@ -130,7 +133,7 @@ def test_tensor_parallel_decode_step_over_nccl():
     procs = [ctx.Process(target=_nccl_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    got = sorted(q.get(timeout=200) for _ in range(2))  # drain the queue before joining
+    got = sorted(q.get(timeout=120) for _ in range(2))  # drain the queue before joining
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
@@ -140,7 +143,7 @@ def test_tensor_parallel_decode_step_over_nccl():
 def _ar_worker(rank, world, port, q):
     import faulthandler
     import torch.distributed as dist
-    faulthandler.dump_traceback_later(150, exit=True)
+    faulthandler.dump_traceback_later(90, exit=True)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -201,6 +204,9 @@ def _ar_worker(rank, world, port, q):
         del g
         torch.cuda.synchronize()
         q.put((rank, bad))
+    except Exception:
+        import traceback
+        q.put((rank, "EXCEPTION " + traceback.format_exc()))
     finally:
         dist.destroy_process_group()
 
@@ -216,7 +222,7 @@ def test_one_shot_all_reduce_over_peer_memory():
     procs = [ctx.Process(target=_ar_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    res = [q.get(timeout=240) for _ in procs]
+    res = [q.get(timeout=120) for _ in procs]
     for p in procs:
         p.join(timeout=60)
     for rank, bad in res:
