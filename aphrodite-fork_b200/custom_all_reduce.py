@@ -48,8 +48,12 @@ class OneShotAllReduce:
         dist.barrier(group)  # every rank's flags are zero before anybody starts
 
     def should_use(self, x: torch.Tensor) -> bool:
+        """One-shot pushes world x the message per rank, so it only pays for small messages on larger groups: the
+        reference's thresholds (custom_all_reduce.cuh:563-570: any size at world 2, < 512 KiB up to 4 ranks, < 256 KiB up
+        to 8; larger ones would be its two-shot kernel, here NCCL)."""
         n = x.numel() * x.element_size()
-        return (x.is_cuda and x.is_contiguous() and x.dtype in _DT and n % 16 == 0 and 0 < n <= self.max_size
+        limit = self.max_size if self.world_size == 2 else (512 * 1024 - 1 if self.world_size <= 4 else 256 * 1024 - 1)
+        return (x.is_cuda and x.is_contiguous() and x.dtype in _DT and n % 16 == 0 and 0 < n <= min(limit, self.max_size)
                 and x.data_ptr() % 16 == 0)
 
     def all_reduce(self, x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
