@@ -273,8 +273,9 @@ def decode_extras(torch, A, dev, world, steps=10):
         ms = float(t.item())
     return {"model": ("llama-3.1-8b" if world == 1 else "llama-3.1-70b") + f" shapes, {cfg.num_layers} layers, W4A16 g128, fp8 KV",
             "tp": world, "batch": BATCH, "ctx": CTX, "ms_per_step": round(ms, 3), "tok_per_s": round(BATCH / (ms * 1e-3), 1),
-            "all_reduce": ("none" if world == 1 else "one-shot peer-memory kernel (csrc/all_reduce.cu)" if model.tp.custom is not None
-                           else f"NCCL ({model.tp.custom_error})"),
+            "all_reduce": ("none" if world == 1 else f"NCCL ({model.tp.custom_error})" if model.tp.custom is None
+                           else "one-shot peer-memory kernel (csrc/all_reduce.cu)" if model.tp.custom.should_use(model.x)
+                           else "NCCL (message above the one-shot threshold of this world size)"),
             "kernel_launches_per_step": model.launches_per_step(),
             "hbm_bytes_per_step_per_gpu": model.kv_bytes_per_step() + model.weight_bytes(),
             "hbm_GBps_per_gpu": round((model.kv_bytes_per_step() + model.weight_bytes()) / (ms * 1e-3) / 1e9, 1)}
