@@ -10,6 +10,7 @@ most `max_size` bytes, world size 2/4/6/8; anything else goes to NCCL.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional
 
 import torch
@@ -48,11 +49,13 @@ class OneShotAllReduce:
         dist.barrier(group)  # every rank's flags are zero before anybody starts
 
     def should_use(self, x: torch.Tensor) -> bool:
-        """One-shot pushes world x the message per rank, so it only pays for small messages on larger groups: the
-        reference's thresholds (custom_all_reduce.cuh:563-570: any size at world 2, < 512 KiB up to 4 ranks, < 256 KiB up
-        to 8; larger ones would be its two-shot kernel, here NCCL)."""
+        """One-shot pushes world x the message per rank, so on larger groups it only pays up to a size. The reference
+        stops at 512 KiB (<= 4 ranks) and 256 KiB (<= 8 ranks) for its pull kernel (custom_all_reduce.cuh:563-570); the
+        push kernel was measured against NCCL on 4 and 8 B200s at the decode step's 1 MiB messages and is still ahead
+        (profiles/r01_bench_n4_one_shot_vs_nccl.txt), so the limits here are 2 MiB and 1 MiB; larger messages take NCCL."""
         n = x.numel() * x.element_size()
-        limit = self.max_size if self.world_size == 2 else (512 * 1024 - 1 if self.world_size <= 4 else 256 * 1024 - 1)
+        limit = self.max_size if self.world_size == 2 else (2 * 1024 * 1024 if self.world_size <= 4 else 1024 * 1024)
+        limit = int(os.environ.get("APH_AR_LIMIT_BYTES", limit))  # development: sweep the threshold
         return (x.is_cuda and x.is_contiguous() and x.dtype in _DT and n % 16 == 0 and 0 < n <= min(limit, self.max_size)
                 and x.data_ptr() % 16 == 0)
 
