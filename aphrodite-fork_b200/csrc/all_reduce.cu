@@ -96,6 +96,141 @@ __global__ void __launch_bounds__(512, 1)
     for (int b = gridDim.x + threadIdx.x; b < AR_MAX_BLOCKS; b += blockDim.x) counters[b] = flag;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// All-reduce fused with what always follows it in a decoder layer (llama.py:270-292): residual add + RMSNorm
+// (fused_add_rms_norm, layernorm_kernels.cu:50-137). Same push / barrier as above, but CTAs own whole ROWS, so phase (C)
+// can finish the row: s = T(sum over ranks) (the all-reduce's rounding), z = T(s + residual) -> residual, then
+// x = T(z * rsqrt(mean(z^2) + eps)) * weight. One kernel and one pass over the row instead of two kernels.
+// ---------------------------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ T ar_round(float v) { return ScalarTraits<T>::from_float(v); }
+
+__device__ __forceinline__ float ar_block_sum(float v, float* s_part) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = (blockDim.x + 31) >> 5;
+  __syncthreads();  // s_part may still be read from the previous row
+  if (lane == 0) s_part[warp] = v;
+  __syncthreads();
+  v = lane < nwarp ? s_part[lane] : 0.f;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+template <typename T, int WORLD>
+__global__ void __launch_bounds__(512, 1)
+    all_reduce_add_rms_norm_kernel(T* x, T* residual, const T* __restrict__ weight, float epsilon,
+                                   uint8_t* const* __restrict__ peer_bufs, uint32_t* __restrict__ counters, int rank, int rows,
+                                   int hidden, int64_t slot_bytes) {
+  constexpr int VEC = 16 / (int)sizeof(T);
+  constexpr int ITER = 4;  // hidden <= 4 * 512 * VEC
+  using V = uint4;
+  __shared__ uint8_t* s_bufs[WORLD];
+  __shared__ float s_part[32];
+  pdl_trigger();
+  if (threadIdx.x < WORLD) s_bufs[threadIdx.x] = peer_bufs[threadIdx.x];
+  const int nvec = hidden / VEC;
+  V wreg[ITER];  // immutable: before the wait
+#pragma unroll
+  for (int it = 0; it < ITER; ++it) {
+    const int i = threadIdx.x + it * blockDim.x;
+    if (i < nvec) wreg[it] = reinterpret_cast<const V*>(weight)[i];
+  }
+  __syncthreads();
+  pdl_wait();
+  const uint32_t flag = counters[blockIdx.x] + 1;  // after the wait, see one_shot_all_reduce_kernel
+  const int64_t half_off = AR_SIGNAL_BYTES + (int64_t)(flag & 1) * WORLD * slot_bytes;
+  // (A) push this CTA's rows
+  for (int row = blockIdx.x; row < rows; row += gridDim.x)
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+      const int64_t idx = (int64_t)row * nvec + i;
+      const V v = reinterpret_cast<const V*>(x)[idx];
+#pragma unroll
+      for (int r = 0; r < WORLD; ++r) reinterpret_cast<V*>(s_bufs[r] + half_off + rank * slot_bytes)[idx] = v;
+    }
+  // (B)
+  __syncthreads();
+  if (threadIdx.x < WORLD) {
+    st_release_sys(&reinterpret_cast<ArSignals*>(s_bufs[threadIdx.x])->arrived[blockIdx.x][rank], flag);
+    const uint32_t* w = &reinterpret_cast<ArSignals*>(s_bufs[rank])->arrived[blockIdx.x][threadIdx.x];
+    for (uint32_t spins = 0; (int32_t)(ld_acquire_sys(w) - flag) < 0; ++spins) {
+      if (spins > 4096) __nanosleep(256);
+      if (spins > (1u << 28)) __trap();
+    }
+  }
+  __syncthreads();
+  // (C) finish the rows
+  const uint8_t* mine = s_bufs[rank] + half_off;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    V keep[ITER];
+    float ss = 0.f;
+#pragma unroll
+    for (int it = 0; it < ITER; ++it) {
+      const int i = threadIdx.x + it * blockDim.x;
+      if (i < nvec) {
+        const int64_t idx = (int64_t)row * nvec + i;
+        V v[WORLD];
+#pragma unroll
+        for (int r = 0; r < WORLD; ++r) v[r] = __ldcv(reinterpret_cast<const V*>(mine + r * slot_bytes) + idx);
+        const V res = reinterpret_cast<const V*>(residual)[idx];
+        V z;
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) {
+          float acc = ScalarTraits<T>::to_float(reinterpret_cast<const T*>(&v[0])[e]);
+#pragma unroll
+          for (int r = 1; r < WORLD; ++r) acc += ScalarTraits<T>::to_float(reinterpret_cast<const T*>(&v[r])[e]);
+          const float s = ScalarTraits<T>::to_float(ar_round<T>(acc));                                       // all-reduce output
+          const T zz = ar_round<T>(s + ScalarTraits<T>::to_float(reinterpret_cast<const T*>(&res)[e]));       // scalar_t add
+          reinterpret_cast<T*>(&z)[e] = zz;
+          const float f = ScalarTraits<T>::to_float(zz);
+          ss += f * f;
+        }
+        reinterpret_cast<V*>(residual)[idx] = z;
+        keep[it] = z;
+      }
+    }
+    ss = ar_block_sum(ss, s_part);
+    const float rs = rsqrtf(ss / (float)hidden + epsilon);
+#pragma unroll
+    for (int it = 0; it < ITER; ++it) {
+      const int i = threadIdx.x + it * blockDim.x;
+      if (i < nvec) {
+        V o;
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) {
+          const T n = ar_round<T>(ScalarTraits<T>::to_float(reinterpret_cast<const T*>(&keep[it])[e]) * rs);
+          reinterpret_cast<T*>(&o)[e] =
+              ar_round<T>(ScalarTraits<T>::to_float(n) * ScalarTraits<T>::to_float(reinterpret_cast<const T*>(&wreg[it])[e]));
+        }
+        reinterpret_cast<V*>(x)[(int64_t)row * nvec + i] = o;
+      }
+    }
+  }
+  if (threadIdx.x == 0) counters[blockIdx.x] = flag;
+  if (blockIdx.x == 0)
+    for (int b = gridDim.x + threadIdx.x; b < AR_MAX_BLOCKS; b += blockDim.x) counters[b] = flag;
+}
+
+template <typename T>
+int launch_ar_norm(void* x, void* residual, const void* weight, float eps, const void* const* peer_bufs, uint32_t* counters, int rank,
+                   int world, int rows, int hidden, int64_t slot_bytes, cudaStream_t stream) {
+  const int blocks = std::max(1, std::min(rows, AR_MAX_BLOCKS));
+#define APH_ARN(W)                                                                                                              \
+  case W:                                                                                                                       \
+    APH_LAUNCH_PDL((all_reduce_add_rms_norm_kernel<T, W>), dim3((unsigned)blocks), dim3(512), (size_t)0, stream, (T*)x, (T*)residual, \
+                   (const T*)weight, eps, (uint8_t* const*)peer_bufs, counters, rank, rows, hidden, slot_bytes);                  \
+    return APH_OK
+  switch (world) {
+    APH_ARN(2);
+    APH_ARN(4);
+    APH_ARN(6);
+    APH_ARN(8);
+    default: return set_error(APH_ERR_UNSUPPORTED, "all_reduce_add_rms_norm: world size %d (2, 4, 6 or 8)", world);
+  }
+#undef APH_ARN
+}
+
 template <typename T>
 int launch_one_shot(void* out, const void* in, const void* const* peer_bufs, uint32_t* counters, int rank, int world, int64_t n_vec,
                     int64_t slot_bytes, int blocks, cudaStream_t stream) {
@@ -149,4 +284,26 @@ extern "C" int aph_one_shot_all_reduce(void* out, const void* in, const void* co
     case APH_DT_BF16: return launch_one_shot<__nv_bfloat16>(out, in, peer_bufs_dev, counters, rank, world, n_vec, slot_bytes, blocks, s);
     default: return set_error(APH_ERR_INVALID_ARGUMENT, "%s: unknown dtype %d", op, dtype);
   }
+}
+
+extern "C" int aph_all_reduce_add_rms_norm(void* x, void* residual, const void* weight, float epsilon,
+                                           const void* const* peer_bufs_dev, uint32_t* counters, int rank, int world,
+                                           int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes, void* stream) {
+  const char* op = "all_reduce_add_rms_norm";
+  APH_CHECK(world >= 2 && world <= AR_MAX_RANKS && rank >= 0 && rank < world, APH_ERR_INVALID_ARGUMENT, "%s: rank %d of %d", op, rank,
+            world);
+  APH_CHECK(dtype == APH_DT_F16 || dtype == APH_DT_BF16, APH_ERR_UNSUPPORTED, "%s: float16 / bfloat16 only", op);
+  APH_CHECK(num_tokens >= 0 && hidden_size > 0 && hidden_size % 8 == 0 && hidden_size <= 4 * 512 * 8, APH_ERR_INVALID_ARGUMENT,
+            "%s: hidden size must be a multiple of 8 and at most 16384", op);
+  if (num_tokens == 0) return APH_OK;
+  APH_CHECK(x && residual && weight && peer_bufs_dev && counters, APH_ERR_INVALID_ARGUMENT, "%s: null pointer", op);
+  APH_CHECK(aligned16(x) && aligned16(residual) && aligned16(weight), APH_ERR_INVALID_ARGUMENT, "%s: tensors must be 16-byte aligned", op);
+  APH_CHECK(slot_bytes % 16 == 0 && num_tokens * hidden_size * 2 <= slot_bytes, APH_ERR_INVALID_ARGUMENT,
+            "%s: message does not fit the %lld-byte slots", op, (long long)slot_bytes);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (dtype == APH_DT_F16)
+    return launch_ar_norm<__half>(x, residual, weight, epsilon, peer_bufs_dev, counters, rank, world, (int)num_tokens, (int)hidden_size,
+                                  slot_bytes, s);
+  return launch_ar_norm<__nv_bfloat16>(x, residual, weight, epsilon, peer_bufs_dev, counters, rank, world, (int)num_tokens,
+                                       (int)hidden_size, slot_bytes, s);
 }

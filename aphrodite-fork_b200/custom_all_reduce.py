@@ -69,3 +69,21 @@ class OneShotAllReduce:
         if st != 0:
             raise RuntimeError(self.lib.aph_b200_last_error().decode())
         return out
+
+    def should_fuse_norm(self, x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor) -> bool:
+        h = x.shape[-1]
+        return (self.should_use(x) and x.dtype in (torch.float16, torch.bfloat16) and x.dim() == 2 and h % 8 == 0 and h <= 16384
+                and residual.is_contiguous() and residual.shape == x.shape and residual.dtype == x.dtype
+                and weight.is_contiguous() and weight.dtype == x.dtype and weight.numel() == h
+                and residual.data_ptr() % 16 == 0 and weight.data_ptr() % 16 == 0)
+
+    def all_reduce_add_rms_norm(self, x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
+        """x <- rms_norm(all_reduce(x) + residual) * weight, residual <- all_reduce(x) + residual: the all-reduce and the
+        fused_add_rms_norm that follows it in every decoder layer, in one kernel."""
+        st = self.lib.aph_all_reduce_add_rms_norm(
+            ctypes.c_void_p(x.data_ptr()), ctypes.c_void_p(residual.data_ptr()), ctypes.c_void_p(weight.data_ptr()),
+            ctypes.c_float(epsilon), ctypes.c_void_p(self.peer_ptrs), ctypes.c_void_p(self.counters.data_ptr()), self.rank,
+            self.world_size, ctypes.c_int64(x.shape[0]), ctypes.c_int64(x.shape[1]), _DT[x.dtype], ctypes.c_int64(self.max_size),
+            ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+        if st != 0:
+            raise RuntimeError(self.lib.aph_b200_last_error().decode())

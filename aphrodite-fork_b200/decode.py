@@ -4,10 +4,10 @@ This is the caller side of SURVEY.md 3.1 reduced to what the hot path needs: per
     h   = fused_add_rms_norm(x, residual)                      (rms_norm for the first layer)
     qkv = W4A16 GEMM (column parallel)  ->  rotary_embedding(q, k)  ->  reshape_and_cache(k, v)
                                         ->  paged attention (this rank's heads)
-    o   = W4A16 GEMM (row parallel)     ->  all_reduce          ->  fused_add_rms_norm(o, residual)
+    o   = W4A16 GEMM (row parallel)     ->  all_reduce + fused_add_rms_norm(o, residual)  (one kernel over peer memory)
     gu  = W4A16 GEMM (column parallel)  ->  silu_and_mul
-    dn  = W4A16 GEMM (row parallel)     ->  all_reduce
-and a final fused_add_rms_norm: 11 kernels per layer, every one launched with programmatic dependent launch, no
+    dn  = W4A16 GEMM (row parallel)     ->  all_reduce + the next layer's fused_add_rms_norm
+and a final norm: 11 kernels per layer, every one launched with programmatic dependent launch, no
 torch elementwise kernels in between. Weights are synthetic. One step can be captured in a CUDA graph, the NCCL
 all_reduces included, which is how the reference runs decode (`cuda_communicator.py`).
 
@@ -115,8 +115,8 @@ class DecodeLayer:
             residual = x
             h = torch.empty_like(x)
             ops.rms_norm(h, x, self.input_layernorm, cfg.rms_norm_eps)
-        else:
-            ops.fused_add_rms_norm(x, residual, self.input_layernorm, cfg.rms_norm_eps)
+        else:  # x is the previous layer's row-parallel partial: its all-reduce is fused with this add + norm
+            self.tp.all_reduce_add_rms_norm(x, residual, self.input_layernorm, cfg.rms_norm_eps)
             h = x
         qkv = self.qkv(h)
         q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
@@ -127,12 +127,12 @@ class DecodeLayer:
         a = PagedAttention.forward_decode(q, self.key_cache, self.value_cache, block_tables, seq_lens, max_seq_len,
                                           cfg.kv_cache_dtype, self.kvh, self.scale, None, self.k_scale, self.v_scale,
                                           tp_rank=self.tp.rank)
-        o = self.tp.all_reduce(self.o(a.reshape(-1, self.q_size)))
-        ops.fused_add_rms_norm(o, residual, self.post_attention_layernorm, cfg.rms_norm_eps)
+        o = self.o(a.reshape(-1, self.q_size))
+        self.tp.all_reduce_add_rms_norm(o, residual, self.post_attention_layernorm, cfg.rms_norm_eps)
         gu = self.gate_up(o)
         act = torch.empty(gu.shape[0], gu.shape[1] // 2, dtype=gu.dtype, device=gu.device)
         ops.silu_and_mul(act, gu)
-        return self.tp.all_reduce(self.down(act)), residual
+        return self.down(act), residual  # partial: reduced by the next all_reduce_add_rms_norm
 
 
 class DecodeModel:
@@ -168,7 +168,7 @@ class DecodeModel:
         for layer in self.layers:
             x, residual = layer.forward(x, residual, self.positions, self.cos_sin_cache, self.slot_mapping, self.block_tables,
                                         self.seq_lens, self.ctx)
-        ops.fused_add_rms_norm(x, residual, self.norm, self.cfg.rms_norm_eps)
+        self.tp.all_reduce_add_rms_norm(x, residual, self.norm, self.cfg.rms_norm_eps)
         self.out.copy_(x)
 
     def capture(self) -> None:

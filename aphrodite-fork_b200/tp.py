@@ -164,3 +164,16 @@ class TPGroup:
                 return self.custom.all_reduce(x)
             dist.all_reduce(x, op=dist.ReduceOp.SUM, group=self.group)
         return x
+
+    def all_reduce_add_rms_norm(self, x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
+        """In place: residual += all_reduce(x); x = rms_norm(residual) * weight - what every row-parallel output of a
+        decoder layer goes through (llama.py:270-292). One fused kernel over peer memory when eligible
+        (APH_FUSED_AR_NORM=0 keeps the two steps apart), else all_reduce + the fused_add_rms_norm op."""
+        import os
+        from . import _custom_ops as ops
+        if (self.world_size > 1 and self.custom is not None and os.environ.get("APH_FUSED_AR_NORM", "1") != "0"
+                and self.custom.should_fuse_norm(x, residual, weight)):
+            self.custom.all_reduce_add_rms_norm(x, residual, weight, epsilon)
+            return
+        self.all_reduce(x)
+        ops.fused_add_rms_norm(x, residual, weight, epsilon)

@@ -257,6 +257,14 @@ int aph_all_reduce_max_blocks(void);
 int aph_one_shot_all_reduce(void* out, const void* in, const void* const* peer_bufs_dev, uint32_t* counters, int rank,
                             int world, int64_t numel, int dtype, int64_t slot_bytes, int max_blocks, void* stream);
 
+/* aph_one_shot_all_reduce fused with the residual add + RMSNorm that follows every all-reduce of a decoder layer
+ * (aph_fused_add_rms_norm): x [num_tokens, hidden] holds this rank's partial on entry and the normalised sum on exit,
+ * residual += sum (rounded as the unfused pair rounds). Same buffers, counters and calling discipline as
+ * aph_one_shot_all_reduce (the two may be mixed freely); float16 / bfloat16, hidden_size % 8 == 0 and <= 16384. */
+int aph_all_reduce_add_rms_norm(void* x, void* residual, const void* weight, float epsilon,
+                                const void* const* peer_bufs_dev, uint32_t* counters, int rank, int world,
+                                int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -174,6 +174,27 @@ def _ar_worker(rank, world, port, q):
                     got = tp.all_reduce(x.clone())
                     if not torch.equal(got, want):
                         bad.append((str(dtype), shape, rep, float((got.float() - want.float()).abs().max())))
+        # all-reduce fused with the residual add + RMSNorm that follows it: against the unfused pair of kernels
+        from aphrodite_fork_b200 import _custom_ops as ops
+        for dtype in (torch.bfloat16, torch.float16):
+            for m, h in ((1, 4096), (64, 8192), (7, 1024), (130, 5120)):
+                x = torch.randn(m, h, device=dev, generator=gen).to(dtype)
+                res = torch.randn(m, h, device=dev, generator=gen).to(dtype)
+                w = (1 + 0.1 * torch.randn(h, device=dev, generator=gen)).to(dtype)
+                dist.broadcast(res, src=0)  # the residual stream and the weights are replicated
+                dist.broadcast(w, src=0)
+                if not tp.custom.should_fuse_norm(x, res, w):
+                    continue
+                x2, res2 = x.clone(), res.clone()
+                tp.custom.all_reduce(x2)
+                ops.fused_add_rms_norm(x2, res2, w, 1e-5)
+                tp.all_reduce_add_rms_norm(x, res, w, 1e-5)
+                if not torch.equal(res, res2):
+                    bad.append(("fused residual", str(dtype), m, h))
+                d = (x.view(torch.int16).int() - x2.view(torch.int16).int()).abs()
+                tiny = (x.float() - x2.float()).abs() <= 1e-5
+                if not bool(((d <= 2) | tiny).all()) or float(((d > 0) & ~tiny).float().mean()) > 0.01:
+                    bad.append(("fused norm", str(dtype), m, h, int(d.max())))
         # too large / misaligned messages take NCCL
         big = torch.ones(5 * 1024 * 1024, device=dev, dtype=torch.bfloat16)
         assert not tp.custom.should_use(big)
