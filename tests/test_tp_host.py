@@ -140,3 +140,41 @@ def test_tp_group_is_a_noop_without_a_process_group():
     g = tp.TPGroup()
     x = torch.ones(3)
     assert g.world_size == 1 and g.rank == 0 and g.all_reduce(x) is x and torch.equal(x, torch.ones(3))
+
+
+def test_one_shot_all_reduce_eligibility_rules():
+    """Host logic of custom_all_reduce.OneShotAllReduce.should_use / should_fuse_norm (no GPU, no peers: the object is
+    built without its buffers): size limits per world size, alignment, contiguity, dtypes."""
+    from aphrodite_fork_b200.custom_all_reduce import OneShotAllReduce
+
+    class FakeCuda(torch.Tensor):
+        """A CPU tensor that reports is_cuda (the rules only look at metadata)."""
+        @property
+        def is_cuda(self):
+            return True
+
+    def fake(*shape, dtype=torch.bfloat16):
+        return torch.zeros(*shape, dtype=dtype).as_subclass(FakeCuda)
+
+    os.environ.pop("APH_AR_LIMIT_BYTES", None)
+    ar = object.__new__(OneShotAllReduce)
+    ar.max_size = 8 * 1024 * 1024
+    for world, ok_rows, bad_rows in ((2, 256, 513), (4, 128, 129), (8, 64, 65)):  # rows of 8192 bf16 = 16 KiB each
+        ar.world_size = world
+        assert ar.should_use(fake(ok_rows, 8192)), (world, ok_rows)
+        assert not ar.should_use(fake(bad_rows, 8192)), (world, bad_rows)
+    ar.world_size = 2
+    assert not ar.should_use(fake(3, 4))                      # 24 bytes: not a multiple of 16
+    assert not ar.should_use(fake(64, 128).t())               # not contiguous
+    assert not ar.should_use(fake(64, 128, dtype=torch.int32))
+    assert not ar.should_use(torch.zeros(64, 128, dtype=torch.bfloat16))  # a CPU tensor
+    x, w = fake(64, 8192), fake(8192)
+    assert ar.should_fuse_norm(x, fake(64, 8192), w)
+    assert not ar.should_fuse_norm(fake(64, 8192, dtype=torch.float32), fake(64, 8192, dtype=torch.float32), fake(8192, dtype=torch.float32))
+    assert not ar.should_fuse_norm(fake(4, 32768), fake(4, 32768), fake(32768))   # hidden size above 16384
+    assert not ar.should_fuse_norm(x, fake(63, 8192), w)
+    os.environ["APH_AR_LIMIT_BYTES"] = "0"
+    try:
+        assert not ar.should_use(fake(1, 4096))
+    finally:
+        del os.environ["APH_AR_LIMIT_BYTES"]
