@@ -1,8 +1,8 @@
 """Same-box timing of the decode-layer glue kernels against the UNMODIFIED reference CUDA kernels
 (oracle/_ref/refcuda.so). Checker/measurement tool only. CUDA graph of back-to-back calls over rotating buffers,
-CUDA events on the capturing stream (tools/bench_vs_ref.py `timed`).
+CUDA events on the capturing stream (tests/tools/bench_vs_ref.py `timed`).
 
-    python tools/bench_glue.py > profiles/rNN_glue_vs_reference_cuda.jsonl
+    python tests/tools/bench_glue.py > profiles/rNN_glue_vs_reference_cuda.jsonl
 """
 import json
 import os

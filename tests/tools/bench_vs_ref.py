@@ -1,15 +1,15 @@
 """Same-box comparison: our kernels vs the UNMODIFIED reference CUDA kernels (oracle/_ref/refcuda.so,
-`make -C oracle refcuda`) on the BASELINE shapes. Checker/measurement tool only (tools/ is not the
+`make -C oracle refcuda`) on the BASELINE shapes. Checker/measurement tool only (tests/tools/ is checker tooling, not the
 product path). Timing: CUDA graph of `iters` back-to-back calls over rotating buffers larger than
 L2, CUDA events on the capturing stream, one warm replay before the timed one.
 
-    python tools/bench_vs_ref.py [attention] [gemm] [cache]  > profiles/rNN_vs_reference_cuda.jsonl
+    python tests/tools/bench_vs_ref.py [attention] [gemm] [cache]  > profiles/rNN_vs_reference_cuda.jsonl
 """
 import json
 import os
 import sys
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 import aphrodite_fork_b200 as A
 from oracle import oracle

@@ -1,6 +1,6 @@
 """Debug driver for the tcgen05 GEMM path: APH_GEMM_PATH=tc python tools/dbg_tc.py [M K N gs zp dtype]"""
 import os, sys
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests")); sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
 import torch
 import test_gpu_marlin as T
