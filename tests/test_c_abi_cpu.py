@@ -48,3 +48,54 @@ def test_argument_checks_return_status_and_message():
     assert st != 0 and b"65535" in lib.aph_b200_last_error()
     # zero work is a successful no-op
     assert lib.aph_copy_blocks(None, None, None, 0, ctypes.c_int64(0), ctypes.c_int64(16), None) == 0
+
+
+def test_argument_checks_of_the_next_row_entry_points():
+    """Host-side validation of the repack / glue / MLA / all-reduce entry points: bad arguments come back as a status
+    and a message before any CUDA call, empty work is a successful no-op."""
+    lib = _lib()
+    lib.aph_b200_last_error.restype = ctypes.c_char_p
+    lib.aph_all_reduce_signal_bytes.restype = ctypes.c_size_t
+    lib.aph_all_reduce_buffer_bytes.restype = ctypes.c_size_t
+    i64, f32 = ctypes.c_int64, ctypes.c_float
+    one = ctypes.c_void_p(16)  # a non-null, 16-byte aligned placeholder: only looked at, never dereferenced on these paths
+
+    assert lib.aph_gptq_marlin_repack(one, one, None, i64(128), i64(64), 3, None) != 0
+    assert b"num_bits must be 4 or 8" in lib.aph_b200_last_error()
+    assert lib.aph_awq_marlin_repack(one, one, i64(120), i64(64), 4, None) != 0
+    assert b"tile_k_size" in lib.aph_b200_last_error()
+    assert lib.aph_gptq_marlin_repack(one, one, None, i64(128), i64(96), 4, None) != 0
+    assert b"tile_n_size" in lib.aph_b200_last_error()
+    assert lib.aph_permute_cols(one, one, one, i64(4), i64(100), i64(100), None) != 0
+
+    assert lib.aph_rms_norm(None, None, None, f32(1e-6), i64(0), i64(4096), i64(4096), 2, None) == 0
+    assert lib.aph_fused_add_rms_norm(None, None, None, f32(1e-6), i64(4), i64(4096), 2, None) != 0
+    assert lib.aph_rms_norm(one, one, one, f32(1e-6), i64(4), i64(4096), i64(4096), 7, None) != 0
+    assert b"unknown dtype" in lib.aph_b200_last_error()
+    assert lib.aph_silu_and_mul(one, one, i64(70000), i64(128), 2, None) != 0
+    assert b"65535" in lib.aph_b200_last_error()
+    assert lib.aph_act_and_mul(99, one, one, i64(4), i64(128), f32(0), 2, None) != 0
+    assert lib.aph_activation(0, one, one, i64(128), 2, None) != 0  # silu_and_mul is not an element-wise activation
+    assert lib.aph_rotary_embedding(one, one, one, one, None, i64(4), 130, i64(1024), i64(256), 8, 2, 128, 1, 2, None) != 0
+    assert b"rot_dim" in lib.aph_b200_last_error()
+    assert lib.aph_rotary_embedding(one, one, one, one, None, i64(4), 128, i64(1024), i64(256), 8, 3, 128, 1, 2, None) != 0
+    assert lib.aph_advance_step_flashattn(4, 5, 16, one, one, one, one, one, one, i64(8), None) != 0
+
+    assert lib.aph_concat_and_cache_mla(one, one, one, one, i64(4), 512, 64, 16, i64(9216), i64(576), i64(512), i64(64), 2, 1, None,
+                                        None) != 0
+    assert b"scale" in lib.aph_b200_last_error()
+    assert lib.aph_gather_cache(one, one, one, one, None, 0, 16, i64(1152), i64(8), i64(18432), i64(1152), i64(1152), None) == 0
+    assert lib.aph_copy_blocks_mla(None, None, 0, i64(0), i64(16), None) == 0
+
+    assert lib.aph_all_reduce_signal_bytes() == 4096
+    assert lib.aph_all_reduce_buffer_bytes(4, i64(1 << 20)) == 4096 + 2 * 4 * (1 << 20)
+    assert 1 <= lib.aph_all_reduce_max_blocks() <= 148
+    assert lib.aph_one_shot_all_reduce(one, one, one, one, 0, 3, i64(1024), 2, i64(1 << 20), 0, None) != 0
+    assert b"world size 3" in lib.aph_b200_last_error()
+    assert lib.aph_one_shot_all_reduce(one, one, one, one, 2, 2, i64(1024), 2, i64(1 << 20), 0, None) != 0
+    assert lib.aph_one_shot_all_reduce(one, one, one, one, 0, 2, i64(1 << 20), 2, i64(1 << 20), 0, None) != 0
+    assert b"does not fit" in lib.aph_b200_last_error()
+    assert lib.aph_one_shot_all_reduce(one, one, one, one, 0, 2, i64(0), 2, i64(1 << 20), 0, None) == 0
+    assert lib.aph_all_reduce_add_rms_norm(one, one, one, f32(1e-5), one, one, 0, 2, i64(4), i64(4096), 0, i64(1 << 20), None) != 0
+    assert b"float16 / bfloat16" in lib.aph_b200_last_error()
+    assert lib.aph_all_reduce_add_rms_norm(one, one, one, f32(1e-5), one, one, 0, 2, i64(4), i64(32768), 2, i64(1 << 20), None) != 0
