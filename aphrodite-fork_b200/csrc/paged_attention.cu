@@ -2,8 +2,16 @@
 // paged_attention_v1.cu:100-168), split-K partition choice and dispatch to the per-head-size
 // translation units (paged_attention_inst.cu).
 #include <cstdlib>
+#include <mutex>
 
 #include "paged_attention.cuh"
+
+// Scratch of aph_paged_attention_v1_noalloc: the split-K partials live in this file-scope device array instead of a
+// caller buffer. Every GPU that loads the library holds these bytes until the process exits. In HOST code the name is
+// only a stand-in for the symbol, never a device address: the address is looked up per device with
+// cudaGetSymbolAddress (static_scratch() below) and that pointer is what the kernels receive.
+#define APH_PA_NOALLOC_SCRATCH_BYTES APH_PA_NOALLOC_MAX_SCRATCH_BYTES  // include/aphrodite_b200.h: 16 MiB
+static __device__ __align__(256) unsigned char g_pa_noalloc_scratch[APH_PA_NOALLOC_SCRATCH_BYTES];
 
 namespace aphb200 {
 namespace pa {
@@ -142,6 +150,26 @@ static int run(void* out, const void* query, const void* key_cache, const void* 
   }
 }
 
+// Device address of g_pa_noalloc_scratch on the CURRENT device, resolved once per device (set-up; no allocation).
+static int static_scratch(void** ptr_out) {
+  static std::mutex mu;
+  static void* ptrs[64] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  APH_CHECK(e == cudaSuccess && dev >= 0 && dev < 64, APH_ERR_CUDA, "paged_attention_v1_noalloc: cudaGetDevice: %s",
+            cudaGetErrorString(e));
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_pa_noalloc_scratch);
+    APH_CHECK(e == cudaSuccess && ptr != nullptr, APH_ERR_CUDA,
+              "paged_attention_v1_noalloc: cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e));
+    ptrs[dev] = ptr;
+  }
+  *ptr_out = ptrs[dev];
+  return APH_OK;
+}
+
 }  // namespace pa
 }  // namespace aphb200
 
@@ -192,4 +220,32 @@ extern "C" int aph_paged_attention_v2(void* out, float* exp_sums, float* max_log
                  out_stride, kv_block_stride, kv_head_stride, dtype, kv_dtype, k_scale, v_scale, tp_rank,
                  blocksparse_local_blocks, blocksparse_vert_stride, blocksparse_block_size,
                  blocksparse_head_sliding_step, workspace, workspace_bytes, stream);
+}
+
+extern "C" int aph_paged_attention_v1_noalloc(void* out, const void* query, const void* key_cache,
+                                              const void* value_cache, int num_seqs, int num_heads, int num_kv_heads,
+                                              int head_size, float scale, const int32_t* block_tables,
+                                              const int32_t* seq_lens, int block_size, int max_seq_len,
+                                              int max_num_blocks_per_seq, const float* alibi_slopes, int64_t q_stride,
+                                              int64_t out_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+                                              int dtype, int kv_dtype, const float* k_scale, const float* v_scale,
+                                              int tp_rank, int blocksparse_local_blocks, int blocksparse_vert_stride,
+                                              int blocksparse_block_size, int blocksparse_head_sliding_step,
+                                              void* stream) {
+  const size_t need = aph_paged_attention_workspace_bytes(num_seqs, num_heads, num_kv_heads, head_size, max_seq_len);
+  APH_CHECK(need <= (size_t)APH_PA_NOALLOC_SCRATCH_BYTES, APH_ERR_WORKSPACE,
+            "paged_attention_v1_noalloc: this problem needs %zu bytes of split-K scratch, the built-in scratch holds %zu "
+            "(use aph_paged_attention_v1 with a caller workspace)",
+            need, (size_t)APH_PA_NOALLOC_SCRATCH_BYTES);
+  void* scratch = nullptr;
+  if (need > 0) {
+    const int st = pa::static_scratch(&scratch);
+    if (st != APH_OK) return st;
+  }
+  // nothing in the scratch has to start at zero: every partial the reduce kernel reads is written by this call
+  return pa::run(out, query, key_cache, value_cache, num_seqs, num_heads, num_kv_heads, head_size, scale,
+                 block_tables, seq_lens, block_size, max_seq_len, max_num_blocks_per_seq, alibi_slopes, q_stride,
+                 out_stride, kv_block_stride, kv_head_stride, dtype, kv_dtype, k_scale, v_scale, tp_rank,
+                 blocksparse_local_blocks, blocksparse_vert_stride, blocksparse_block_size,
+                 blocksparse_head_sliding_step, scratch, need > 0 ? (size_t)APH_PA_NOALLOC_SCRATCH_BYTES : 0, stream);
 }

@@ -137,6 +137,26 @@ int aph_paged_attention_v2(void* out, float* exp_sums, float* max_logits, void* 
                            int blocksparse_block_size, int blocksparse_head_sliding_step, void* workspace,
                            size_t workspace_bytes, void* stream);
 
+/* aph_paged_attention_v1_noalloc - NO counterpart in the reference; added for
+ * callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments and result as aph_paged_attention_v1 without the workspace: the split-K partials go to a file-scope
+ * `static __device__` array of APH_PA_NOALLOC_MAX_SCRATCH_BYTES = 16 MiB inside the library (held by every
+ * GPU that loads the library until the process exits; its device address is resolved once per device with
+ * cudaGetSymbolAddress on the first call made with that device current). The call allocates nothing (no cudaMalloc /
+ * cudaFree / allocating library routine). Problems whose aph_paged_attention_workspace_bytes(...) exceed the 16 MiB are
+ * rejected with APH_ERR_WORKSPACE. All calls on a device share the one array: calls that overlap on the GPU (two
+ * streams, or two host threads on different streams) race on it - serialise them on one stream. */
+#define APH_PA_NOALLOC_MAX_SCRATCH_BYTES (16u << 20)
+int aph_paged_attention_v1_noalloc(void* out, const void* query, const void* key_cache, const void* value_cache,
+                                   int num_seqs, int num_heads, int num_kv_heads, int head_size, float scale,
+                                   const int32_t* block_tables, const int32_t* seq_lens, int block_size,
+                                   int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes,
+                                   int64_t q_stride, int64_t out_stride, int64_t kv_block_stride,
+                                   int64_t kv_head_stride, int dtype, int kv_dtype, const float* k_scale,
+                                   const float* v_scale, int tp_rank, int blocksparse_local_blocks,
+                                   int blocksparse_vert_stride, int blocksparse_block_size,
+                                   int blocksparse_head_sliding_step, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * gptq_marlin_gemm - replaces kernels/quantization/gptq_marlin/gptq_marlin.cu:2263-2468.
  *   c            [size_m, size_n] scalar dtype (written; caller-allocated here, the torch
