@@ -8,7 +8,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB = os.path.join(_HERE, "lib")
+# APH_B200_LIB_DIR: development only - a variant build of the same library (build.py build_variant)
+_LIB = os.environ.get("APH_B200_LIB_DIR") or os.path.join(_HERE, "lib")
 _loaded = None
 _capi = None
 

@@ -100,5 +100,30 @@ def build(verbose: bool = False) -> str:
     return libpath
 
 
+def build_variant(name: str, extra_flags: list[str]) -> str:
+    """Development: the library with marlin_gemm.cu recompiled with `extra_flags`, in aphrodite-fork_b200/lib_<name>/
+    (libaphrodite_b200.so + a copy of _C_b200.so, which finds its sibling through its $ORIGIN rpath). Select it with
+    APH_B200_LIB_DIR. Used by tests/tools/ring_fault_proof.py (-DAPH_RING_FAULT, -DAPH_RING_LEGACY)."""
+    import shutil
+    build()
+    out_dir = os.path.join(HERE, "lib_" + name)
+    os.makedirs(out_dir, exist_ok=True)
+    src = os.path.join(CSRC, "marlin_gemm.cu")
+    obj = os.path.join(OBJ, f"marlin_gemm_{name}.o")
+    if _newer(obj, [src, *_headers()]):
+        _run([NVCC, *NVCC_FLAGS, *extra_flags, "-c", src, "-o", obj])
+    objs = [os.path.join(OBJ, f) for f in sorted(os.listdir(OBJ))
+            if f.endswith(".o") and not f.startswith("marlin_gemm")] + [obj]
+    libpath = os.path.join(out_dir, "libaphrodite_b200.so")
+    if _newer(libpath, objs):
+        _run([NVCC, "-shared", "-o", libpath, *objs, "-gencode", "arch=compute_100a,code=sm_100a"])
+    shutil.copy2(os.path.join(LIB, "_C_b200.so"), os.path.join(out_dir, "_C_b200.so"))
+    shutil.copy2(os.path.join(LIB, "_C_b200_overlay.so"), os.path.join(out_dir, "_C_b200_overlay.so"))
+    return out_dir
+
+
 if __name__ == "__main__":
-    print(build(verbose=True))
+    if len(sys.argv) > 2 and sys.argv[1] == "variant":  # python build.py variant <name> <flag> ...
+        print(build_variant(sys.argv[2], sys.argv[3:]))
+    else:
+        print(build(verbose=True))

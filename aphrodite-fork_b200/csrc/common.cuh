@@ -40,6 +40,9 @@ int sm_count();
 // kernels of a decode step then overlap launch latency and prologue with the previous kernel's tail; next to foreign
 // kernels (torch, NCCL) the attribute degrades to ordinary stream order. APH_PDL=0 switches the attribute off.
 bool pdl_enabled();
+// APH_DEV_ENV=1 at process start: the development overrides (APH_GEMM_NT / _GRID, APH_PA_WAVES / _MIN_PART) are
+// re-read on every call (sweep tools); otherwise they are read once and the call path never touches getenv.
+bool dev_env_live();
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {

@@ -9,11 +9,12 @@
 //     (nibble pairs (0,4) (2,6) (1,5) (3,7) -> a0 a1 a2 a3), so small batches waste no
 //     tensor-core rows and the group scales are per accumulator ROW (8 per thread, one 16-byte
 //     load straight from the Marlin-permuted scale layout);
-//   * int4 -> bf16/f16 is the exponent-splice trick only ((q & 0xf) | 0x4300 = 128 + q); the
-//     "-8" / zero-point subtraction and the group scale are applied to the fp32 accumulator once
-//     per group:  acc += s[g,n] * (sum_k a_k (OFF + q_kn) - (OFF + zp[g,n]) * sum_k a_k), with
-//     sum_k a_k produced by one extra MMA against an all-ones tile. 7 ALU ops per 8 weights
-//     instead of the reference's 15;
+//   * int4 -> bf16/f16: exponent splice ((q & 0xf) | 0x4300 = 128 + q, one LOP3 per pair) and one exact packed
+//     subtraction of (128 + zero point) - 11 ALU ops per 8 weights (reference: 15). The group scale is NOT applied per
+//     weight: the MMA accumulates sum_k a_k (q_kn - z_n) in fp32 over one quantisation group and the scale multiplies
+//     that sum once (acc += s[g,n] * part), so no product is rounded to 16 bits. (Round 1 fed the un-subtracted
+//     128 + q to the MMA and cancelled the offset on the accumulator; for f16, where the offset is 1024, the tensor
+//     core's truncating fp32 accumulation then biased results by ~1 % for activations with a large mean.)
 //   * stream-K: the slice-major list of (output slice of 64/128/256 columns, 16 KiB weight stage) items is cut
 //     into one equal contiguous range per co-resident CTA slot (2 per SM), so every SM streams the same number
 //     of bytes whatever the shape (224 slices on 296 slots left 72 SMs half idle before); a slice shared by
@@ -53,12 +54,25 @@ struct Plan {
 // (it is bound by its own warps' latency, not by the SM), so t = 0.75 us x (stages of the longest CTA) + 2.0 us if
 // slices are shared + 1.8 us if ranges are unaligned (0.75 / 1.8 become 1.3 / 6.0 at 9..16 rows, where every
 // segment turn-around moves twice the accumulators); the cheapest candidate wins. APH_GEMM_NT / APH_GEMM_GRID force a plan (development).
+// development overrides: read once per process (no getenv on the call path), unless the process was started with
+// APH_DEV_ENV=1 (the sweep tools change them between calls)
+static int env_int(const char* name) {
+  const char* e = getenv(name);
+  return e ? atoi(e) : 0;
+}
+static int forced_nt_env() {
+  static const int v = env_int("APH_GEMM_NT");
+  return dev_env_live() ? env_int("APH_GEMM_NT") : v;
+}
+static int forced_grid_env() {
+  static const int v = env_int("APH_GEMM_GRID");
+  return dev_env_live() ? env_int("APH_GEMM_GRID") : v;
+}
+
 static Plan make_plan(int64_t N, int64_t K, int nb) {
   const int slots = sm_count() * (nb <= 2 ? 2 : 1);
-  const char* e_nt = getenv("APH_GEMM_NT");
-  const char* e_grid = getenv("APH_GEMM_GRID");
-  const int forced_nt = e_nt ? atoi(e_nt) : 0;
-  const int forced_grid = e_grid ? atoi(e_grid) : 0;
+  const int forced_nt = forced_nt_env();
+  const int forced_grid = forced_grid_env();
   Plan best{};
   double best_cost = 1e30;
   const int nts[3] = {256, 128, 64};
@@ -114,9 +128,38 @@ static EncodeTiledFn encode_tiled_fn() {
 }
 
 // 2-D row-major tensor [rows][cols] of `elt_bytes`-wide elements, row pitch in bytes, box [box_rows][box_cols].
+// A tensor map is a pure function of these arguments, and a serving process calls with the same few (weight, scale,
+// activation buffer) descriptions over and over: encoded maps are kept in a small per-thread direct-mapped cache, so an
+// eager (non-graph) call pays for the four driver calls (~1 us each) only the first time it sees a tensor.
+struct MapKey {
+  const void* base;
+  uint64_t cols, rows, pitch;
+  uint32_t box_cols, box_rows;
+  int dt, swz, promo;
+  bool operator==(const MapKey& o) const {
+    return base == o.base && cols == o.cols && rows == o.rows && pitch == o.pitch && box_cols == o.box_cols && box_rows == o.box_rows &&
+           dt == o.dt && swz == o.swz && promo == o.promo;
+  }
+};
+struct MapCacheEntry {
+  MapKey key;
+  bool valid;
+  alignas(64) CUtensorMap tm;
+};
 static int make_map_2d(CUtensorMap* tm, CUtensorMapDataType dt, int elt_bytes, const void* base, uint64_t cols, uint64_t rows,
                        uint64_t pitch_bytes, uint32_t box_cols, uint32_t box_rows, CUtensorMapSwizzle swz,
                        CUtensorMapL2promotion promo) {
+  constexpr int CACHE = 256;
+  static thread_local MapCacheEntry* cache = nullptr;
+  if (cache == nullptr) cache = new MapCacheEntry[CACHE]();  // per thread, lives as long as the thread
+  const MapKey key{base, cols, rows, pitch_bytes, box_cols, box_rows, (int)dt, (int)swz, (int)promo};
+  uint64_t h = (uint64_t)(uintptr_t)base * 0x9E3779B97F4A7C15ull;
+  h ^= (cols * 0x100000001B3ull) ^ (rows << 17) ^ ((uint64_t)box_rows << 40) ^ ((uint64_t)box_cols << 48) ^ ((uint64_t)swz << 3) ^ pitch_bytes;
+  MapCacheEntry& e = cache[(h ^ (h >> 29)) % CACHE];
+  if (e.valid && e.key == key) {
+    *tm = e.tm;
+    return APH_OK;
+  }
   EncodeTiledFn enc = encode_tiled_fn();
   APH_CHECK(enc != nullptr, APH_ERR_CUDA, "gptq_marlin_gemm: driver has no cuTensorMapEncodeTiled");
   const cuuint64_t dims[2] = {cols, rows};
@@ -129,6 +172,9 @@ static int make_map_2d(CUtensorMap* tm, CUtensorMapDataType dt, int elt_bytes, c
   APH_CHECK(r == CUDA_SUCCESS, APH_ERR_CUDA,
             "gptq_marlin_gemm: cuTensorMapEncodeTiled failed (%d) for [%llu x %llu] pitch %llu box [%u x %u]", (int)r,
             (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)pitch_bytes, box_rows, box_cols);
+  e.key = key;
+  e.tm = *tm;
+  e.valid = true;
   return APH_OK;
 }
 
@@ -308,13 +354,16 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
     tmS = tmB;  // never dereferenced
     tmZ = tmB;
   }
-  // development aid: APH_GEMM_TRACE=<file> dumps per-stage clock64 stamps of CTA 0 (synchronises!)
-  static const char* trace_path = getenv("APH_GEMM_TRACE");
   p.trace = nullptr;
+#ifdef APH_GEMM_TRACE
+  // development build only (APH_GEMM_TRACE_BUILD=1): APH_GEMM_TRACE=<file> dumps per-stage clock64 stamps of CTA 0.
+  // Allocates and synchronises - none of this exists in the product build.
+  static const char* trace_path = getenv("APH_GEMM_TRACE");
   if (trace_path != nullptr) {
     cudaMalloc(&p.trace, 72 * 8 * sizeof(unsigned long long));
     cudaMemsetAsync(p.trace, 0, 72 * 8 * sizeof(unsigned long long), stream);
   }
+#endif
   {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned)pl.grid);
@@ -329,6 +378,7 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
     const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, p, tmB, tmA, tmS, tmZ);
     APH_CHECK(le == cudaSuccess, APH_ERR_CUDA, "gptq_marlin_gemm: launch failed: %s", cudaGetErrorString(le));
   }
+#ifdef APH_GEMM_TRACE
   if (trace_path != nullptr) {
     unsigned long long host[72 * 8];
     cudaStreamSynchronize(stream);
@@ -352,6 +402,7 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
       fclose(f);
     }
   }
+#endif
   return APH_OK;
 }
 
@@ -427,7 +478,7 @@ extern "C" size_t aph_gptq_marlin_gemm_scratch_bytes(int64_t size_m, int64_t siz
   for (int nb = 1; nb <= 4; nb *= 2) {
     // upper bound over the slice widths make_plan may pick: grid <= 2 SMs' worth of slots, NT <= 256
     size_t need = (size_t)aphb200::sm_count() * (nb <= 2 ? 2 : 1) * 2 * (8 * nb) * 256 * sizeof(float);
-    if (getenv("APH_GEMM_GRID")) need *= 8;  // development sweeps may use several waves of CTAs
+    if (mg::forced_grid_env()) need *= 8;  // development sweeps may use several waves of CTAs
     if (need > worst) worst = need;
   }
   if (size_n % mgtc::NTILE == 0) {
@@ -486,8 +537,8 @@ extern "C" int aph_gptq_marlin_gemm(void* c, const void* a, const void* b_q_weig
   p.K = (int)size_k;
   p.group_size = (int)group_size;
   {
-    const char* e = getenv("APH_GEMM_DBG");
-    p.dbg = e ? atoi(e) : 0;
+    static const int dbg = mg::env_int("APH_GEMM_DBG");  // development: 1 = skip the math, 2 = skip the loads
+    p.dbg = dbg;
   }
   mg::Operands op{a, b_q_weight, b_scales, has_zp ? b_zeros : nullptr, size_m, lda, num_groups, dtype == APH_DT_F16};
   cudaStream_t s = (cudaStream_t)stream;

@@ -54,8 +54,6 @@ struct Cfg {
   static constexpr int BAR_BYTES = 2 * STAGES * 8 + 64;  // barriers + fix-up flags of the (at most two) shared slices
   static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + RED_BYTES + BAR_BYTES;
   static constexpr uint32_t MAGIC = F16 ? 0x64006400u : 0x43004300u;  // 1024 / 128 as packed pairs
-  static constexpr float OFFSET = F16 ? 1024.f : 128.f;
-  static constexpr uint32_t ONES = F16 ? 0x3c003c00u : 0x3f803f80u;
 };
 
 // The pieces ("segments") of output slices inside the item range [b, e) of one CTA, in PROCESSING order: the
@@ -179,8 +177,7 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
     const uint32_t stage_tx =
         (uint32_t)(C::B_BYTES + C::A_BYTES + KG * gps * NT * 2 + (HAS_ZP ? KG * gps * (NT / 8) * 4 : 0));
     // arm the stage's barrier with its whole byte count and fetch what does not depend on earlier kernels
-    auto load_weights = [&](int it, int slice, int ks) {
-      const int st = it % STAGES;
+    auto load_weights = [&](int st, int slice, int ks) {
       const uint32_t sB = smem_base + st * C::STAGE_BYTES;
       const uint32_t fb = full_bar + st * 8;
       if (p.dbg == 2) {
@@ -194,39 +191,68 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
         if constexpr (HAS_ZP) tma_load_2d(sB + C::B_BYTES + C::A_BYTES + C::S_BYTES, &tmZ, slice * (NT / 8), ks * KG * gps, fb);
       }
     };
-    auto load_activations = [&](int it, int ks) {
+    auto load_activations = [&](int st, int ks) {
       if (p.dbg == 2) return;
-      const int st = it % STAGES;
       const uint32_t sA = smem_base + st * C::STAGE_BYTES + C::B_BYTES;
 #pragma unroll
       for (int i = 0; i < 2 * KG; ++i)
         tma_load_2d_hint(sA + i * C::A_BOX, &tmA, ks * C::KS + 64 * i, p.m0, full_bar + st * 8, pol_keep);
     };
-    // the first STAGES items: weights at once (the ring starts empty), their activations after the dependency wait
+    // the first STAGES items: weights at once (the ring starts empty; item i < STAGES sits in slot i under either ring
+    // mapping), their activations after the dependency wait
     int pre_ks[STAGES];
     int it = 0;
     bool waited = false;
+    RingCursor<STAGES> ring;  // the producer handles every item
     auto end_prologue = [&]() {
       griddep_wait();  // activations come from the previous kernel
       const int n = it < STAGES ? it : STAGES;
       for (int i = 0; i < n; ++i) load_activations(i, pre_ks[i]);
       waited = true;
     };
+#ifdef APH_RING_FAULT
+    int held_st = -1, held_slice = 0, held_ks = 0;  // an odd item held back while the even item behind it goes out first
+#endif
     for_each_segment(item_begin, item_end, p.k_stages, [&](int slice, int k0, int cnt, bool) {
 #pragma unroll 1
       for (int j = 0; j < cnt; ++j, ++it) {
         if (it < STAGES) {
           load_weights(it, slice, k0 + j);
           pre_ks[it] = k0 + j;
+          ring.advance(it);
         } else {
           if (!waited) end_prologue();
-          mbar_wait(empty_bar + (it % STAGES) * 8, ((it / STAGES) & 1) ^ 1);
-          load_weights(it, slice, k0 + j);
-          load_activations(it, k0 + j);
+          const int st = ring.slot(it);
+          mbar_wait(empty_bar + st * 8, ring.phase(it) ^ 1);
+          ring.advance(it);
+#ifdef APH_RING_FAULT
+          if (it & 1) {
+            held_st = st;
+            held_slice = slice;
+            held_ks = k0 + j;
+            continue;
+          }
+#endif
+          load_weights(st, slice, k0 + j);
+          load_activations(st, k0 + j);
+#ifdef APH_RING_FAULT
+          if (held_st >= 0) {
+            ring_fault_delay();
+            load_weights(held_st, held_slice, held_ks);
+            load_activations(held_st, held_ks);
+            held_st = -1;
+          }
+#endif
         }
       }
     });
     if (!waited) end_prologue();
+#ifdef APH_RING_FAULT
+    if (held_st >= 0) {
+      load_weights(held_st, held_slice, held_ks);
+      load_activations(held_st, held_ks);
+    }
+#endif
     return;
   }
 
@@ -243,7 +269,9 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
 #pragma unroll
   for (int i = 0; i < 4; ++i) a_sw[i] = ((uint32_t)(i << 1) ^ a_x) << 4;
 
-  float acc[4][NB][4], part[4][NB][4], asum[NB][4];
+  // part = sum over the current quantisation group of a_k (q_kn - z_n), exact 16-bit weights times activations in fp32;
+  // acc += s_n * part at the end of the group
+  float acc[4][NB][4], part[4][NB][4];
   auto clear_accumulators = [&]() {
 #pragma unroll
     for (int j = 0; j < 4; ++j)
@@ -251,41 +279,40 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
       for (int b = 0; b < NB; ++b)
 #pragma unroll
         for (int e = 0; e < 4; ++e) acc[j][b][e] = part[j][b][e] = 0.f;
-#pragma unroll
-    for (int b = 0; b < NB; ++b)
-#pragma unroll
-      for (int e = 0; e < 4; ++e) asum[b][e] = 0.f;
   };
-
-  // acc += s * (part - zc * asum); part = asum = 0.   sc[j][h], zc[j][h]: tile j, row g (h=0) / g+8 (h=1)
-  auto flush = [&](const float (&sc)[4][2], const float (&zc)[4][2]) {
+  // what the spliced value OFF + q has subtracted from it, as a packed pair per (tile j, row g / g + 8): OFF + 8 for
+  // the symmetric types (uint4b8), OFF + zero point otherwise. (OFF + q) - (OFF + z) is exact in f16 and in bf16.
+  uint32_t czp[4][2];
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
-#pragma unroll
-      for (int b = 0; b < NB; ++b) {
-        acc[j][b][0] = fmaf(sc[j][0], fmaf(-zc[j][0], asum[b][0], part[j][b][0]), acc[j][b][0]);
-        acc[j][b][1] = fmaf(sc[j][0], fmaf(-zc[j][0], asum[b][1], part[j][b][1]), acc[j][b][1]);
-        acc[j][b][2] = fmaf(sc[j][1], fmaf(-zc[j][1], asum[b][0], part[j][b][2]), acc[j][b][2]);
-        acc[j][b][3] = fmaf(sc[j][1], fmaf(-zc[j][1], asum[b][1], part[j][b][3]), acc[j][b][3]);
-        part[j][b][0] = part[j][b][1] = part[j][b][2] = part[j][b][3] = 0.f;
-      }
-#pragma unroll
-    for (int b = 0; b < NB; ++b) asum[b][0] = asum[b][1] = asum[b][2] = asum[b][3] = 0.f;
-  };
-  auto decode_zp = [&](uint32_t zword, float (&zc)[4][2]) {
+  for (int j = 0; j < 4; ++j) czp[j][0] = czp[j][1] = C::MAGIC | 0x00080008u;
+  auto decode_zp = [&](uint32_t zword) {
     // nibble e' of the packed word holds column block interleave[e'] = {0,2,4,6,1,3,5,7}[e']
     constexpr int inv[8] = {0, 4, 1, 5, 2, 6, 3, 7};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      zc[j][0] = C::OFFSET + (float)((zword >> (4 * inv[2 * j])) & 0xf);
-      zc[j][1] = C::OFFSET + (float)((zword >> (4 * inv[2 * j + 1])) & 0xf);
+      const uint32_t z0 = (zword >> (4 * inv[2 * j])) & 0xf, z1 = (zword >> (4 * inv[2 * j + 1])) & 0xf;
+      czp[j][0] = C::MAGIC | z0 | (z0 << 16);
+      czp[j][1] = C::MAGIC | z1 | (z1 << 16);
     }
+  };
+  // acc += s * part; part = 0.   sc[j][h]: tile j, row g (h = 0) / g + 8 (h = 1)
+  auto flush = [&](const float (&sc)[4][2]) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int b = 0; b < NB; ++b) {
+        acc[j][b][0] = fmaf(sc[j][0], part[j][b][0], acc[j][b][0]);
+        acc[j][b][1] = fmaf(sc[j][0], part[j][b][1], acc[j][b][1]);
+        acc[j][b][2] = fmaf(sc[j][1], part[j][b][2], acc[j][b][2]);
+        acc[j][b][3] = fmaf(sc[j][1], part[j][b][3], acc[j][b][3]);
+        part[j][b][0] = part[j][b][1] = part[j][b][2] = part[j][b][3] = 0.f;
+      }
   };
   auto flush_from_smem = [&](const uint8_t* stage, int gl) {
     const uint8_t* sSp = stage + C::B_BYTES + C::A_BYTES;
     const uint4 sv = *reinterpret_cast<const uint4*>(sSp + gl * (NT * 2) + wn * 128 + g * 16);
     const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w};
-    float sc[4][2], zc[4][2];
+    float sc[4][2];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       if constexpr (F16) {
@@ -296,20 +323,26 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
         sc[j][0] = __uint_as_float(sw[j] << 16);
         sc[j][1] = __uint_as_float(sw[j] & 0xffff0000u);
       }
-      zc[j][0] = zc[j][1] = C::OFFSET + 8.f;
     }
-    if constexpr (HAS_ZP) {
-      const uint32_t zword = *reinterpret_cast<const uint32_t*>(sSp + C::S_BYTES + gl * (NT / 8) * 4 + wn * 32 + g * 4);
-      decode_zp(zword, zc);
+    flush(sc);
+  };
+  auto sub2 = [](uint32_t x, uint32_t c) -> uint32_t {
+    if constexpr (F16) {
+      __half2 v = __hsub2(*reinterpret_cast<__half2*>(&x), *reinterpret_cast<__half2*>(&c));
+      return *reinterpret_cast<uint32_t*>(&v);
+    } else {
+      __nv_bfloat162 v = __hsub2(*reinterpret_cast<__nv_bfloat162*>(&x), *reinterpret_cast<__nv_bfloat162*>(&c));
+      return *reinterpret_cast<uint32_t*>(&v);
     }
-    flush(sc, zc);
   };
 
-  // k16-rows per quantisation group (2, 4 or 8: powers of two) as a mask / shift; channelwise never flushes in the loop
+  // k16-rows per quantisation group (2, 4 or 8: powers of two) as a mask / shift; channelwise has one group per segment
   const int rpg_mask = grouped ? p.group_size / 16 - 1 : 0x7fffffff;
   const int rpg_shift = grouped ? 31 - __clz(p.group_size / 16) : 31;
 
   constexpr int CT = SG * CONSUMERS * 32;
+  static_assert(SG == 2, "RingCursor splits the ring between two consumer groups");
+  RingCursor<STAGES> ring;  // this warp handles the items of group sg only (it & 1 == sg), in order across segments
   griddep_wait();  // free here (no activation tile arrives before the producer passed its own wait); orders the global writes below
 
   // ---------------- segments: the pieces of output slices inside this CTA's item range ----------------
@@ -317,15 +350,25 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
   int n_shared = 0;   // shared slices met so far (at most two)
   for_each_segment(item_begin, item_end, p.k_stages, [&](int slice, int k0, int cnt, bool whole) {
     clear_accumulators();
+    if constexpr (HAS_ZP) {
+      if (!grouped) decode_zp(*reinterpret_cast<const uint32_t*>(p.zp + ((int64_t)slice * (NT / 8) + wn * 8 + g) * 4));
+    }
 
 #pragma unroll 1
     for (int it = it0 + ((sg - it0) & (SG - 1)); it < it0 + cnt; it += SG) {
-      const int st = it % STAGES;
-      mbar_wait(full_bar + st * 8, (it / STAGES) & 1);
+      const int st = ring.slot(it);
+      mbar_wait(full_bar + st * 8, ring.phase(it));
+      ring.advance(it);
       const uint32_t sbase = smem_base + st * C::STAGE_BYTES;
       if (p.dbg != 1)
 #pragma unroll
       for (int r = 0; r < 8; ++r) {
+        if constexpr (HAS_ZP) {
+          // first k16-row of a quantisation group: its zero points
+          if ((r & 1) == 0 && (r & rpg_mask) == 0 && grouped)
+            decode_zp(*reinterpret_cast<const uint32_t*>(smem + st * C::STAGE_BYTES + C::B_BYTES + C::A_BYTES + C::S_BYTES +
+                                                         (wg * gps + (r >> rpg_shift)) * (NT / 8) * 4 + wn * 32 + g * 4));
+        }
         uint32_t q[4];
         lds128(sbase + offB + r * (NT * 8), q[0], q[1], q[2], q[3]);
         uint32_t bf[NB][2];
@@ -337,13 +380,13 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
           for (int bb = 0; bb < NB; bb += 2) ldsm_x4(aaddr + bb * 8 * 128, bf[bb][0], bf[bb][1], bf[bb + 1][0], bf[bb + 1][1]);
         }
 #pragma unroll
-        for (int b = 0; b < NB; ++b) mma16816<F16>(asum[b], C::ONES, C::ONES, C::ONES, C::ONES, bf[b][0], bf[b][1]);
-#pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const uint32_t a0 = and_or(q[j], 0x000f000fu, C::MAGIC);
-          const uint32_t a2 = and_or(q[j] >> 4, 0x000f000fu, C::MAGIC);
-          const uint32_t a1 = and_or(q[j] >> 8, 0x000f000fu, C::MAGIC);
-          const uint32_t a3 = and_or(q[j] >> 12, 0x000f000fu, C::MAGIC);
+          // exponent splice (OFF + q, one LOP3 per pair) and exact subtraction of OFF + z: registers a0 / a2 hold
+          // row g of the tile (k low / high half), a1 / a3 row g + 8
+          const uint32_t a0 = sub2(and_or(q[j], 0x000f000fu, C::MAGIC), czp[j][0]);
+          const uint32_t a2 = sub2(and_or(q[j] >> 4, 0x000f000fu, C::MAGIC), czp[j][0]);
+          const uint32_t a1 = sub2(and_or(q[j] >> 8, 0x000f000fu, C::MAGIC), czp[j][1]);
+          const uint32_t a3 = sub2(and_or(q[j] >> 12, 0x000f000fu, C::MAGIC), czp[j][1]);
 #pragma unroll
           for (int b = 0; b < NB; ++b) mma16816<F16>(part[j][b], a0, a1, a2, a3, bf[b][0], bf[b][1]);
         }
@@ -356,20 +399,15 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
     }
     if (!grouped) {
       // channelwise: one scale row, "single" permutation over 32-column blocks (marlin_utils.py:204-213)
-      float sc[4][2], zc[4][2];
+      float sc[4][2];
       const scalar_t* srow = reinterpret_cast<const scalar_t*>(p.s) + (int64_t)slice * NT + wn * 64;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int pos = (j >> 1) * 32 + 8 * (g >> 1) + (g & 1) + 4 * (j & 1);
         sc[j][0] = ScalarTraits<scalar_t>::to_float(srow[pos]);
         sc[j][1] = ScalarTraits<scalar_t>::to_float(srow[pos + 2]);
-        zc[j][0] = zc[j][1] = C::OFFSET + 8.f;
       }
-      if constexpr (HAS_ZP) {
-        const uint32_t zword = *reinterpret_cast<const uint32_t*>(p.zp + ((int64_t)slice * (NT / 8) + wn * 8 + g) * 4);
-        decode_zp(zword, zc);
-      }
-      flush(sc, zc);
+      flush(sc);
     }
 
     // ---------------- reduce the consumer warps through shared memory ----------------

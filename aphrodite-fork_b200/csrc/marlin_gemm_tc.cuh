@@ -78,17 +78,17 @@ struct Cfg {
   static constexpr int FIX_BYTES = 0;
   static constexpr int BUDGET = 227 * 1024 - 1024 - 1024 - FIX_BYTES - 4096;
   static constexpr int SA_SMEM = (BUDGET - 3 * W_STAGE) / ACT_BYTES;
-  // The ring depth is kept EVEN: stage `it` goes to dequantiser group it & 1 and to slot it % SA, so with an even
-  // depth every slot belongs to one group. With the odd depth 3 (the natural fit at 256 batch rows) a slot alternates
-  // between the groups, and tools/stress_gemm.py then showed a wrong 32..128-column stripe of one tile in ~0.1 % of
-  // the calls (plus sporadic launch failures at M = 1024); depth 2 is clean over 40 000 calls. The ordering hazard
-  // behind it has not been isolated; the even depth costs ~3 % at M >= 256.
+  // Both rings are shared by the two dequantiser groups (stage `it` goes to group it & 1) and are walked with
+  // ptx::RingCursor: each group owns its own sub-ring of slots, so any depth >= 2 is safe, odd ones included (the
+  // natural fit at 256 batch rows is 3 + 3). Round 1 mapped slot = it % depth and had to keep the depth even; the
+  // reason (mbarrier parity aliasing when a slot alternates between the groups) is written up at RingCursor.
   static constexpr int SA_FIT = SA_SMEM < SA_TMEM ? SA_SMEM : SA_TMEM;
-  static constexpr int SA = SA_FIT > 2 ? (SA_FIT & ~1) : SA_FIT;
-  static_assert(SA >= 2 && SA <= 7 && (SA % 2 == 0), "activation ring depth");
+  static constexpr int SA = SA_FIT;
+  static_assert(SA >= 2 && SA <= 7, "activation ring depth");
   static constexpr int SW_FIT = (BUDGET - SA * ACT_BYTES) / W_STAGE;
   static constexpr int SW = SW_FIT > 8 ? 8 : SW_FIT;
   static_assert(SW >= 3, "weight ring too shallow");
+  static_assert(DQ_GROUPS == 2 && (NI == 1 || NI == 2), "RingCursor splits a ring between two groups taking alternate stages");
   static constexpr int ACT_OFF = 0;  // activation slots first: 1 KiB aligned
   static constexpr int W_OFF = SA * ACT_BYTES;
   static constexpr int FIX_OFF = W_OFF + SW * W_STAGE;
@@ -281,22 +281,48 @@ __global__ void __launch_bounds__(THREADS, 1)
     const uint64_t pol_stream = policy_evict_first();  // weights are read once (or re-read from L2 by the next batch tile)
     const uint32_t stage_tx = (uint32_t)(W_BYTES + gps * NTILE * 2 + (HAS_ZP ? gps * (NTILE / 8) * 4 : 0));
     int it = 0;
+    RingCursor<SW> ring;  // the producer handles every stage
+    auto issue = [&](int sw, int slice, int ks) {
+      const uint32_t dst = smem_base + C::W_OFF + sw * W_STAGE;
+      const uint32_t fb = fullw_bar + sw * 8;
+      mbar_expect_tx(fb, stage_tx);
+      tma_load_2d_hint(dst, &tmB, slice * NTILE, ks * 8, fb, pol_stream);
+      if (grouped) {
+        tma_load_2d(dst + W_BYTES, &tmS, slice * NTILE, ks * gps, fb);
+        if constexpr (HAS_ZP) tma_load_2d(dst + W_BYTES + S_BYTES, &tmZ, slice * (NTILE / 8), ks * gps, fb);
+      }
+    };
+#ifdef APH_RING_FAULT
+    int held_sw = -1, held_slice = 0, held_ks = 0;  // an odd stage held back while the even stage behind it goes out first
+#endif
     APH_SEGMENTS {
       APH_SEG_VARS
 #pragma unroll 1
       for (int ks = k0; ks < k1; ++ks, ++it) {
-        const int sw = it % SW;
-        mbar_wait_relaxed(emptyw_bar + sw * 8, ((it / SW) & 1) ^ 1);
-        const uint32_t dst = smem_base + C::W_OFF + sw * W_STAGE;
-        const uint32_t fb = fullw_bar + sw * 8;
-        mbar_expect_tx(fb, stage_tx);
-        tma_load_2d_hint(dst, &tmB, slice * NTILE, ks * 8, fb, pol_stream);
-        if (grouped) {
-          tma_load_2d(dst + W_BYTES, &tmS, slice * NTILE, ks * gps, fb);
-          if constexpr (HAS_ZP) tma_load_2d(dst + W_BYTES + S_BYTES, &tmZ, slice * (NTILE / 8), ks * gps, fb);
+        const int sw = ring.slot(it);
+        mbar_wait_relaxed(emptyw_bar + sw * 8, ring.phase(it) ^ 1);
+        ring.advance(it);
+#ifdef APH_RING_FAULT
+        if (it & 1) {
+          held_sw = sw;
+          held_slice = slice;
+          held_ks = ks;
+          continue;
         }
+#endif
+        issue(sw, slice, ks);
+#ifdef APH_RING_FAULT
+        if (held_sw >= 0) {
+          ring_fault_delay();
+          issue(held_sw, held_slice, held_ks);
+          held_sw = -1;
+        }
+#endif
       }
     }
+#ifdef APH_RING_FAULT
+    if (held_sw >= 0) issue(held_sw, held_slice, held_ks);
+#endif
     return;
   }
 
@@ -307,12 +333,14 @@ __global__ void __launch_bounds__(THREADS, 1)
     griddep_wait();  // activations are the previous kernel's output
     const uint64_t pol_keep = policy_evict_last();  // activations are shared by every CTA
     int it = 0;
+    RingCursor<SA> ring;  // handles every stage
     APH_SEGMENTS {
       APH_SEG_VARS
 #pragma unroll 1
       for (int ks = k0; ks < k1; ++ks, ++it) {
-        const int sa = it % SA;
-        mbar_wait_relaxed(emptya_bar + sa * 8, ((it / SA) & 1) ^ 1);
+        const int sa = ring.slot(it);
+        mbar_wait_relaxed(emptya_bar + sa * 8, ring.phase(it) ^ 1);
+        ring.advance(it);
         const uint32_t dst = smem_base + C::ACT_OFF + sa * C::ACT_BYTES;
         const uint32_t fb = ready_bar + sa * 8;
         mbar_expect_tx(fb, (uint32_t)C::ACT_BYTES);
@@ -334,6 +362,7 @@ __global__ void __launch_bounds__(THREADS, 1)
       constexpr uint32_t tmem0 = 0;
       int it = 0;
       bool ok = false;  // result of an early, non-blocking look at the barrier of this issuer's next stage
+      RingCursor<SA> ring;  // NI == 1: every stage; NI == 2: the stages of group mi
       APH_SEGMENTS {
         APH_SEG_VARS
         const int db = seg % NDBUF;
@@ -344,12 +373,13 @@ __global__ void __launch_bounds__(THREADS, 1)
 #pragma unroll 1
         for (int ks = k0; ks < k1; ++ks, ++it) {
           if (NI > 1 && (it % NI) != mi) continue;
-          const int sa = it % SA;
+          const int sa = ring.slot(it);
 #ifdef APH_GEMM_TRACE
           const bool tr = p.trace != nullptr && blockIdx.x == 0 && it < 64 && lane == 0;
           if (tr) p.trace[it * 8 + 0] = clock64();
 #endif
-          if (!ok) mbar_wait(ready_bar + sa * 8, (it / SA) & 1);  // activations landed and dequantised weights are in TMEM
+          if (!ok) mbar_wait(ready_bar + sa * 8, ring.phase(it));  // activations landed and dequantised weights are in TMEM
+          ring.advance(it);
           tc_fence_after();
 #ifdef APH_GEMM_TRACE
           if (tr) p.trace[it * 8 + 2] = clock64();
@@ -357,7 +387,7 @@ __global__ void __launch_bounds__(THREADS, 1)
           const uint32_t desc_lo = (((smem_base + C::ACT_OFF + sa * C::ACT_BYTES) >> 4) & 0x3fffu) | (1u << 16);
           const uint32_t a_tmem = tmem0 + C::A_COL0 + sa * 64;
           const int nx = it + NI;
-          ok = mbar_test(ready_bar + (nx % SA) * 8, (nx / SA) & 1);  // poll the next stage while these MMAs are issued
+          ok = mbar_test(ready_bar + ring.slot(nx) * 8, ring.phase(nx));  // poll the next stage while these MMAs are issued
           tc_mma_ts_stage8(d_tmem, a_tmem, desc_lo, DESC_HI, C::IDESC, acc, (uint32_t)(C::ACT_BOX >> 4));
           acc = 1;
           tc_commit_elect(emptya_bar + sa * 8);  // slot (activations + TMEM weights) free once these MMAs retire
@@ -424,6 +454,8 @@ __global__ void __launch_bounds__(THREADS, 1)
     };
 
     int it = 0;
+    RingCursor<SW> ring_w;  // this warp handles the stages of group grp only
+    RingCursor<SA> ring_a;
     APH_SEGMENTS {
       APH_SEG_VARS
       if (HAS_ZP && !grouped)
@@ -431,12 +463,15 @@ __global__ void __launch_bounds__(THREADS, 1)
 #pragma unroll 1
       for (int ks = k0; ks < k1; ++ks, ++it) {
         if ((it & 1) != grp) continue;
-        const int sw = it % SW, sa = it % SA;
+        const int sw = ring_w.slot(it), sa = ring_a.slot(it);
+        const uint32_t ph_w = ring_w.phase(it), ph_a = ring_a.phase(it);
+        ring_w.advance(it);
+        ring_a.advance(it);
 #ifdef APH_GEMM_TRACE
         const bool tr = p.trace != nullptr && blockIdx.x == 0 && it < 64 && (dw & 7) == 0 && lane == 0;
         if (tr) p.trace[it * 8 + 4] = clock64();
 #endif
-        mbar_wait(fullw_bar + sw * 8, (it / SW) & 1);
+        mbar_wait(fullw_bar + sw * 8, ph_w);
 #ifdef APH_GEMM_TRACE
         if (tr) p.trace[it * 8 + 5] = clock64();
 #endif
@@ -468,7 +503,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 #ifdef APH_GEMM_TRACE
         if (tr) p.trace[it * 8 + 6] = clock64();
 #endif
-        mbar_wait(emptya_bar + sa * 8, ((it / SA) & 1) ^ 1);  // the MMAs that read this TMEM slot have retired
+        mbar_wait(emptya_bar + sa * 8, ph_a ^ 1);  // the MMAs that read this TMEM slot have retired
         tc_fence_after();
 #ifdef APH_GEMM_TRACE
         if (tr) p.trace[it * 8 + 7] = clock64();

@@ -45,8 +45,10 @@ static Split choose_split(int num_seqs, int num_heads, int num_kv_heads, int max
   const int tiles = (G + HEADS_PER_CTA - 1) / HEADS_PER_CTA;
   const int64_t units = (int64_t)num_seqs * num_kv_heads * tiles;
   // development overrides (tools/sweep_attention_split.py): waves of CTAs aimed at, smallest partition
-  const char* e_w = getenv("APH_PA_WAVES");
-  const char* e_m = getenv("APH_PA_MIN_PART");
+  static const char* const e_w0 = getenv("APH_PA_WAVES");  // read once per process unless APH_DEV_ENV=1
+  static const char* const e_m0 = getenv("APH_PA_MIN_PART");
+  const char* const e_w = dev_env_live() ? getenv("APH_PA_WAVES") : e_w0;
+  const char* const e_m = dev_env_live() ? getenv("APH_PA_MIN_PART") : e_m0;
   const int waves = e_w ? atoi(e_w) : 4;
   const int min_part = e_m ? atoi(e_m) : 256;
   const int64_t slots = (int64_t)sm_count() * 3;
@@ -114,6 +116,7 @@ static int run(void* out, const void* query, const void* key_cache, const void* 
   p.max_blocks_per_seq = max_num_blocks_per_seq;
   p.partition_tokens = sp.partition_tokens;
   p.num_partitions = sp.num_partitions;
+  p.cluster_parts = 1;
   p.q_stride = q_stride;
   p.out_stride = out_stride;
   p.kv_block_stride = kv_block_stride;

@@ -16,7 +16,11 @@
 //     MMAs; k_scale is folded into the logit scale and v_scale into the output;
 //   * online softmax in the exp2 domain with warp-shuffle max/sum reductions, one pass over KV
 //     (the reference makes two sweeps and round-trips logits through shared memory);
-//   * the split-K partition size is chosen from the problem size, partials are fp32.
+//   * the split-K partition size is chosen from the problem size; up to 8 partitions of one (sequence, kv head) form
+//     a thread-block CLUSTER and are merged on chip: every CTA pushes its fp32 partial rows into the shared memory of
+//     the cluster's CTA that owns the head (DSMEM stores), one cluster barrier, and the owners write `out` - no partial
+//     round trip through HBM and no second kernel. Only splits finer than 8 go through fp32 partials in a workspace
+//     (one per cluster) and the reduce kernel.
 #pragma once
 #include "common.cuh"
 #include "ptx.cuh"
@@ -44,7 +48,8 @@ struct Params {
   int num_seqs, num_heads, num_kv_heads;
   int max_blocks_per_seq;
   int partition_tokens;       // tokens per partition (multiple of the stage size)
-  int num_partitions;
+  int num_partitions;         // grid z: partitions per (sequence, kv head tile), a multiple of cluster_parts
+  int cluster_parts;          // CTAs per thread-block cluster along z (1..8): the partitions a cluster merges on chip
   int64_t q_stride, out_stride, kv_block_stride, kv_head_stride;  // elements
   float scale;
   int tp_rank, bs_local_blocks, bs_vert_stride, bs_block_size, bs_head_sliding_step;

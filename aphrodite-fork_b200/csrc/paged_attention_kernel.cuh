@@ -24,7 +24,13 @@ struct Cfg {
   static constexpr int DP = D + 4;  // padded row of the cross-warp merge buffer (floats)
   static constexpr int PIPE_BYTES = NWARPS * NS * STAGE;
   static constexpr int MERGE_BYTES = NWARPS * HEADS_PER_CTA * DP * 4;
-  static constexpr int SMEM_BYTES = (PIPE_BYTES > MERGE_BYTES ? PIPE_BYTES : MERGE_BYTES) + NWARPS * NS * 8;
+  // cluster merge: rows a CTA receives from the partitions of its cluster, [slot][D] fp32 + (max, sum) per slot with
+  // slot = source rank x heads this CTA owns; cluster size CP needs CP * ceil(8 / CP) slots (at most 14 for CP <= 8,
+  // 8 for the powers of two, which is what head sizes above 128 are limited to so that 3 CTAs still fit an SM)
+  static constexpr int RECV_SLOTS = D <= 128 ? 14 : 8;
+  static constexpr int RECV_OFF = ((PIPE_BYTES > MERGE_BYTES ? PIPE_BYTES : MERGE_BYTES) + NWARPS * NS * 8 + 15) / 16 * 16;
+  static constexpr int RECV_BYTES = RECV_SLOTS * (D + 2) * 4;
+  static constexpr int SMEM_BYTES = RECV_OFF + RECV_BYTES;
   static constexpr int CTAS_PER_SM = (SMEM_BYTES + 1024) * 3 <= 227 * 1024 ? 3 : ((SMEM_BYTES + 1024) * 2 <= 227 * 1024 ? 2 : 1);
 };
 
@@ -53,15 +59,32 @@ __global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar
   const int part_start = part * p.partition_tokens;
   const int P = p.num_partitions;
 
+  // Partitions of one (sequence, kv head tile) are merged inside a thread-block cluster of CP CTAs along z: CTA rank r
+  // owns heads [r * HPR, (r + 1) * HPR) of the tile, every CTA pushes its partial rows to the owners (DSMEM), one
+  // cluster barrier, the owners finish. First barrier phase = "this CTA runs" (nobody may touch the shared memory of
+  // a CTA that has not started).
+  const int CP = p.cluster_parts;
+  if (CP > 1) cluster_arrive_relaxed();
+  const int crank = CP > 1 ? (int)cluster_ctarank() : 0;
+  const int HPR = (Gv + CP - 1) / CP;
+  float* recv_o = reinterpret_cast<float*>(smem + C::RECV_OFF);
+  float* recv_ml = recv_o + C::RECV_SLOTS * D;
+  float v_scale = 1.f;
+  if constexpr (C::FP8) v_scale = *p.v_scale;
+
   if (part_start >= L) {
     // Nothing to attend to. With a single partition the output is defined as zeros
     // (reference: empty loops leave accs = 0, attention_kernels.cuh:366-371).
-    if (P == 1 && L <= 0) {
-      scalar_t* o = (scalar_t*)p.out + (int64_t)seq * p.out_stride + (int64_t)head0 * D;
-      for (int i = threadIdx.x; i < Gv * D; i += C::NTHREADS) o[i] = ScalarTraits<scalar_t>::from_float(0.f);
+    if (CP == 1) {
+      if (P == 1 && L <= 0) {
+        scalar_t* o = (scalar_t*)p.out + (int64_t)seq * p.out_stride + (int64_t)head0 * D;
+        for (int i = threadIdx.x; i < Gv * D; i += C::NTHREADS) o[i] = ScalarTraits<scalar_t>::from_float(0.f);
+      }
+      return;
     }
-    return;
-  }
+    cluster_wait_acquire();  // end of phase one (this CTA pushes nothing, but may own heads)
+  } else {
+  // ======================= this CTA's partition =======================
   const int part_end = min(part_start + p.partition_tokens, L);
   const int n_stages = (part_end - part_start + ST - 1) / ST;
   const int n_my = w < n_stages ? (n_stages - w + NWARPS - 1) / NWARPS : 0;
@@ -121,13 +144,13 @@ __global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar
     }
   };
 
+  // ---- prologue: the first stages are in flight while the query is fetched and converted ----
+#pragma unroll 1
+  for (int i = 0; i < NS && i < n_my; ++i) issue(i);
+
   // ---- Q^T B-fragments (heads along N = lane/4) ----
   float sc = p.scale * LOG2E;
-  float v_scale = 1.f;
-  if constexpr (C::FP8) {
-    sc *= *p.k_scale;
-    v_scale = *p.v_scale;
-  }
+  if constexpr (C::FP8) sc *= *p.k_scale;
   uint32_t qb[KS][2];
   {
     const bool hv = g < Gv;
@@ -187,10 +210,6 @@ __global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar
 #pragma unroll
     for (int e = 0; e < 4; ++e) o_acc[mt][e] = 0.f;
   float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
-
-  // ---- prologue ----
-#pragma unroll 1
-  for (int i = 0; i < NS && i < n_my; ++i) issue(i);
 
 #pragma unroll 1
   for (int i = 0; i < n_my; ++i) {
@@ -360,6 +379,8 @@ __global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar
   }
   __syncthreads();
 
+  if (CP > 1) cluster_wait_acquire();  // end of phase one: every CTA of the cluster runs, its shared memory exists
+  const uint32_t recv_o_u32 = smem_u32(recv_o), recv_ml_u32 = smem_u32(recv_ml);
   for (int idx = threadIdx.x; idx < Gv * D; idx += C::NTHREADS) {
     const int h = idx / D, d = idx % D;
     float m_tot = -INFINITY;
@@ -374,13 +395,61 @@ __global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar
       l_tot += l_s[ww][h] * wgt;
     }
     const int head = head0 + h;
-    if (P == 1) {
+    if (CP > 1) {
+      // push this partition's row of head h to the CTA of the cluster that owns the head
+      const uint32_t owner = (uint32_t)(h / HPR);
+      const int slot = crank * HPR + h % HPR;
+      st_cluster_f32(cluster_map_shared(recv_o_u32 + (uint32_t)(slot * D + d) * 4u, owner), acc);
+      if (d == 0) {
+        st_cluster_f32(cluster_map_shared(recv_ml_u32 + (uint32_t)slot * 8u, owner), m_tot);
+        st_cluster_f32(cluster_map_shared(recv_ml_u32 + (uint32_t)slot * 8u + 4u, owner), l_tot);
+      }
+    } else if (P == 1) {
       // reference normaliser: 1 / (sum + 1e-6), attention_kernels.cuh:342
       const float inv = __fdividef(1.f, l_tot + 1e-6f);
       ((scalar_t*)p.out)[(int64_t)seq * p.out_stride + (int64_t)head * D + d] =
           ScalarTraits<scalar_t>::from_float(acc * inv * v_scale);
     } else {
       const int64_t pi = ((int64_t)seq * p.num_heads + head) * P + part;
+      p.part_o[pi * D + d] = acc;
+      if (d == 0) {
+        p.part_ml[pi * 2] = m_tot;
+        p.part_ml[pi * 2 + 1] = l_tot;
+      }
+    }
+  }
+  }  // this CTA's partition
+  if (CP == 1) return;
+
+  // ======================= cluster merge =======================
+  cluster_arrive_release();                 // phase two: my rows are on their way
+  const int nh = min(HPR, Gv - crank * HPR);  // heads this CTA owns
+  if (nh <= 0) return;                      // an exited CTA counts as arrived
+  cluster_wait_acquire();                   // every partition's rows have landed here
+  const int first_part = part - crank;
+  const int np_c = L <= first_part * p.partition_tokens
+                       ? 0
+                       : min(CP, (L - first_part * p.partition_tokens + p.partition_tokens - 1) / p.partition_tokens);
+  const int n_out = P / CP;                 // clusters per (sequence, kv head tile): > 1 = second level through the workspace
+  for (int idx = threadIdx.x; idx < nh * D; idx += C::NTHREADS) {
+    const int hl = idx / D, d = idx % D;
+    float m_tot = -INFINITY;
+    for (int src = 0; src < np_c; ++src) m_tot = fmaxf(m_tot, recv_ml[(src * HPR + hl) * 2]);
+    const float m_use = m_tot == -INFINITY ? 0.f : m_tot;
+    float acc = 0.f, l_tot = 0.f;
+    for (int src = 0; src < np_c; ++src) {
+      const int slot = src * HPR + hl;
+      const float wgt = ex2(recv_ml[slot * 2] - m_use);
+      acc += recv_o[slot * D + d] * wgt;
+      l_tot += recv_ml[slot * 2 + 1] * wgt;
+    }
+    const int head = head0 + crank * HPR + hl;
+    if (n_out == 1) {
+      const float inv = __fdividef(1.f, l_tot + 1e-6f);
+      ((scalar_t*)p.out)[(int64_t)seq * p.out_stride + (int64_t)head * D + d] =
+          ScalarTraits<scalar_t>::from_float(acc * inv * v_scale);
+    } else {
+      const int64_t pi = ((int64_t)seq * p.num_heads + head) * n_out + part / CP;
       p.part_o[pi * D + d] = acc;
       if (d == 0) {
         p.part_ml[pi * 2] = m_tot;

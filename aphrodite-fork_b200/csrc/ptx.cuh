@@ -306,5 +306,80 @@ __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
   return done != 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Thread-block clusters: the cluster-wide barrier (one barrier, alternating phases; every thread of every CTA of the
+// cluster arrives, exited threads count as arrived) and stores into another CTA's shared memory (DSMEM).
+__device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// address of the same shared-memory location in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t cluster_map_shared(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Position in a ring of DEPTH pipeline slots whose items are consumed by TWO groups taking alternate items
+// (item `it` belongs to group it & 1). Each group owns a sub-ring of its own: group 0 the even slots
+// (ceil(DEPTH/2) of them), group 1 the odd slots (floor(DEPTH/2)). A slot is therefore only ever filled for one
+// group, and every thread that waits on a slot's mbarriers meets EVERY phase of that slot in order.
+//
+// Why not slot = it % DEPTH: with an odd DEPTH a slot then alternates between the groups, so a group meets a slot
+// only every second phase and always waits with the same parity. mbarrier.try_wait.parity(P) is true whenever the
+// barrier's current phase has parity != P; it cannot tell "my phase 2k completed" from "phase 2k-2 completed and the
+// other group's phase 2k-1 is still in flight". A group that runs ahead of the other group's load (TMA loads complete
+// out of order) then reads a slot that still holds an older stage: a wrong result, silently. This was the cause of
+// the round-1 "odd ring depth" failures (about 0.1 % of calls); `-DAPH_RING_LEGACY` restores the flat mapping and
+// `-DAPH_RING_FAULT` makes the producers land the odd items late, which turns the rare failure into a deterministic
+// one (tools/ring_fault_proof.py).
+//
+// slot(it) / phase(it) describe item `it`; advance(it) must be called once for every item the thread handles, in
+// order. A thread may handle all items or only those of one group.
+template <int DEPTH>
+struct RingCursor {
+  static_assert(DEPTH >= 2, "a ring shared by two groups needs a slot per group");
+  static constexpr int D0 = (DEPTH + 1) / 2, D1 = DEPTH / 2;
+  int pos0 = 0, pos1 = 0;
+  uint32_t ph0 = 0, ph1 = 0;
+#ifdef APH_RING_LEGACY
+  __device__ __forceinline__ int slot(int it) const { return it % DEPTH; }
+  __device__ __forceinline__ uint32_t phase(int it) const { return (uint32_t)(it / DEPTH) & 1u; }
+  __device__ __forceinline__ void advance(int) {}
+#else
+  __device__ __forceinline__ int slot(int it) const { return (it & 1) ? 1 + 2 * pos1 : 2 * pos0; }
+  __device__ __forceinline__ uint32_t phase(int it) const { return (it & 1) ? ph1 : ph0; }
+  __device__ __forceinline__ void advance(int it) {
+    if (it & 1) {
+      if (++pos1 == D1) {
+        pos1 = 0;
+        ph1 ^= 1u;
+      }
+    } else {
+      if (++pos0 == D0) {
+        pos0 = 0;
+        ph0 ^= 1u;
+      }
+    }
+  }
+#endif
+};
+
+// -DAPH_RING_FAULT (development, tools/ring_fault_proof.py): how long a producer holds back an odd item while the
+// even item behind it is already in flight
+__device__ __forceinline__ void ring_fault_delay() {
+  const long long t0 = clock64();
+  while (clock64() - t0 < 12000) {
+  }
+}
+
 }  // namespace ptx
 }  // namespace aphb200

@@ -40,6 +40,11 @@ bool pdl_enabled() {
   return on;
 }
 
+bool dev_env_live() {
+  static const bool on = getenv("APH_DEV_ENV") != nullptr;
+  return on;
+}
+
 }  // namespace aphb200
 
 extern "C" int aph_b200_abi_version(void) { return APH_B200_ABI_VERSION; }

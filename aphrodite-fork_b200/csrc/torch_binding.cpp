@@ -8,14 +8,16 @@
 // Two build flavours of this one file (SURVEY.md 8b "Loading into a live Aphrodite"):
 //   -DAPH_DEFINE_SCHEMAS  standalone: also defines the schemas (TORCH_LIBRARY_FRAGMENT), for
 //                         processes where aphrodite._C is not loaded (the GPU test box);
-//   (no flag)             overlay: impl-only registration that overrides the CUDA kernels of an
-//                         already-imported aphrodite._C.
+//   (no flag)             overlay: impl-only registration on the BackendSelect key of an already-imported
+//                         aphrodite._C: CUDA calls run here, argument combinations this library does not serve
+//                         fall through to the reference's own CUDA kernel (bottom of this file).
 // convert_fp8 (cache_kernels.cu:499-577) is registered too because the reference's tests and
 // create_kv_caches_with_random depend on it.
 #include <ATen/cuda/CUDAContext.h>
 #include <c10/cuda/CUDAGuard.h>
 #include <torch/all.h>
 #include <torch/library.h>
+#include <ATen/core/dispatch/Dispatcher.h>
 
 #include <optional>
 #include <string>
@@ -25,7 +27,16 @@
 
 namespace {
 
+// A combination of arguments the reference serves and this library does not (APH_ERR_UNSUPPORTED; nothing has been
+// launched when it is reported). Standalone it surfaces as the RuntimeError it is; in the overlay flavour the op's
+// wrapper catches it and hands the call to the reference's own kernel (see Overlay below).
+struct UnsupportedHere : public c10::Error {
+  using c10::Error::Error;
+};
+
 inline void check_status(int st, const char* op) {
+  if (st == APH_ERR_UNSUPPORTED)
+    throw UnsupportedHere({__func__, __FILE__, static_cast<uint32_t>(__LINE__)}, std::string(op) + ": " + aph_b200_last_error());
   TORCH_CHECK(st == APH_OK, op, ": ", aph_b200_last_error());
 }
 
@@ -692,33 +703,49 @@ TORCH_LIBRARY_FRAGMENT(_C_cache_ops, ops) {
 }
 #endif
 
-TORCH_LIBRARY_IMPL(_C, CUDA, ops) {
-  ops.impl("paged_attention_v1", &paged_attention_v1);
-  ops.impl("paged_attention_v2", &paged_attention_v2);
-  ops.impl("gptq_marlin_gemm", &gptq_marlin_gemm);
-  ops.impl("gptq_marlin_repack", &gptq_marlin_repack);
-  ops.impl("awq_marlin_repack", &awq_marlin_repack);
-  ops.impl("silu_and_mul", &silu_and_mul);
-  ops.impl("advance_step_flashattn", &advance_step_flashattn);
-  ops.impl("mul_and_silu", &mul_and_silu);
-  ops.impl("gelu_and_mul", &gelu_and_mul);
-  ops.impl("gelu_tanh_and_mul", &gelu_tanh_and_mul);
-  ops.impl("fatrelu_and_mul", &fatrelu_and_mul);
-  ops.impl("gelu_new", &gelu_new);
-  ops.impl("gelu_fast", &gelu_fast);
-  ops.impl("gelu_quick", &gelu_quick);
-  ops.impl("batched_rotary_embedding", &batched_rotary_embedding);
-  ops.impl("rms_norm", &rms_norm);
-  ops.impl("fused_add_rms_norm", &fused_add_rms_norm);
-  ops.impl("rotary_embedding", &rotary_embedding);
-}
-TORCH_LIBRARY_IMPL(_C_cache_ops, CUDA, ops) {
-  ops.impl("reshape_and_cache", &reshape_and_cache);
-  ops.impl("convert_fp8", &convert_fp8);
-  ops.impl("swap_blocks", &swap_blocks);
-  ops.impl("copy_blocks", &copy_blocks);
-  ops.impl("reshape_and_cache_flash", &reshape_and_cache_flash);
-  ops.impl("copy_blocks_mla", &copy_blocks_mla);
-  ops.impl("concat_and_cache_mla", &concat_and_cache_mla);
-  ops.impl("gather_cache", &gather_cache);
-}
+#define APH_ALL_C_OPS(X)                                                                                              \
+  X(_C, paged_attention_v1) X(_C, paged_attention_v2) X(_C, gptq_marlin_gemm) X(_C, gptq_marlin_repack)                 \
+  X(_C, awq_marlin_repack) X(_C, silu_and_mul) X(_C, advance_step_flashattn) X(_C, mul_and_silu) X(_C, gelu_and_mul)    \
+  X(_C, gelu_tanh_and_mul) X(_C, fatrelu_and_mul) X(_C, gelu_new) X(_C, gelu_fast) X(_C, gelu_quick)                    \
+  X(_C, batched_rotary_embedding) X(_C, rms_norm) X(_C, fused_add_rms_norm) X(_C, rotary_embedding)
+#define APH_ALL_CACHE_OPS(X)                                                                                          \
+  X(_C_cache_ops, reshape_and_cache) X(_C_cache_ops, convert_fp8) X(_C_cache_ops, swap_blocks)                        \
+  X(_C_cache_ops, copy_blocks) X(_C_cache_ops, reshape_and_cache_flash) X(_C_cache_ops, copy_blocks_mla)              \
+  X(_C_cache_ops, concat_and_cache_mla) X(_C_cache_ops, gather_cache)
+
+#ifdef APH_DEFINE_SCHEMAS
+// standalone: these are the CUDA kernels of the ops
+#define APH_IMPL_CUDA(ns, name) ops.impl(#name, &name);
+TORCH_LIBRARY_IMPL(_C, CUDA, ops) { APH_ALL_C_OPS(APH_IMPL_CUDA) }
+TORCH_LIBRARY_IMPL(_C_cache_ops, CUDA, ops) { APH_ALL_CACHE_OPS(APH_IMPL_CUDA) }
+#else
+// Overlay onto a live aphrodite._C. The reference's CUDA kernels stay registered; ours sit on the BackendSelect key,
+// which every call meets BEFORE its backend key. A call whose tensors are on a CUDA device runs here; if this library
+// reports the argument combination as unsupported (nothing launched yet) - or the call is not for CUDA at all - it is
+// redispatched below BackendSelect and reaches the kernel the reference registered. So a drop-in overlay never turns
+// a configuration the reference serves into an error (8-bit Marlin weights, HQQ zero points, ...).
+namespace {
+template <const char* (*Name)(), auto Fn>
+struct Overlay;
+template <const char* (*Name)(), typename R, typename... A, R (*Fn)(A...)>
+struct Overlay<Name, Fn> {
+  static R call(c10::DispatchKeySet ks, A... args) {
+    if (ks.has_backend(c10::BackendComponent::CUDABit)) {
+      try {
+        return Fn(args...);
+      } catch (const UnsupportedHere&) {
+      }
+    }
+    static const auto op = c10::Dispatcher::singleton().findSchemaOrThrow(Name(), "").template typed<R(A...)>();
+    return op.redispatch(ks & c10::DispatchKeySet(c10::DispatchKeySet::FULL_AFTER, c10::DispatchKey::BackendSelect), args...);
+  }
+};
+#define APH_OVERLAY_NAME(ns, name) \
+  const char* aph_op_name_##name() { return #ns "::" #name; }
+APH_ALL_C_OPS(APH_OVERLAY_NAME)
+APH_ALL_CACHE_OPS(APH_OVERLAY_NAME)
+}  // namespace
+#define APH_IMPL_OVERLAY(ns, name) ops.impl(#name, &Overlay<&aph_op_name_##name, &name>::call);
+TORCH_LIBRARY_IMPL(_C, BackendSelect, ops) { APH_ALL_C_OPS(APH_IMPL_OVERLAY) }
+TORCH_LIBRARY_IMPL(_C_cache_ops, BackendSelect, ops) { APH_ALL_CACHE_OPS(APH_IMPL_OVERLAY) }
+#endif

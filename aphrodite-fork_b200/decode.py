@@ -78,7 +78,7 @@ class MarlinLinear:
 
 
 class DecodeLayer:
-    def __init__(self, cfg: DecodeConfig, tp: TPGroup, num_blocks: int, device, gen):
+    def __init__(self, cfg: DecodeConfig, tp: TPGroup, num_blocks: int, device, gen, weights_from: "Optional[DecodeLayer]" = None):
         self.cfg, self.tp = cfg, tp
         t = tp.world_size
         self.h, self.kvh = shard_heads(cfg.num_heads, cfg.num_kv_heads, t)
@@ -90,10 +90,13 @@ class DecodeLayer:
                             (2 * inter_l, cfg.hidden, cfg.hidden), (cfg.hidden, inter_l, cfg.intermediate)):
             verify_marlin_supports_shape(n_l, k_l, k, k if g == -1 else g)
         mk = lambda k, n, row: MarlinLinear(_synthetic_marlin(k, n, g, cfg.dtype, device, gen, row))
-        self.qkv = mk(cfg.hidden, self.q_size + 2 * self.kv_size, False)
-        self.o = mk(self.q_size, cfg.hidden, True)
-        self.gate_up = mk(cfg.hidden, 2 * inter_l, False)
-        self.down = mk(inter_l, cfg.hidden, True)
+        if weights_from is not None:  # another batch size over the same (immutable) weights
+            self.qkv, self.o, self.gate_up, self.down = weights_from.qkv, weights_from.o, weights_from.gate_up, weights_from.down
+        else:
+            self.qkv = mk(cfg.hidden, self.q_size + 2 * self.kv_size, False)
+            self.o = mk(self.q_size, cfg.hidden, True)
+            self.gate_up = mk(cfg.hidden, 2 * inter_l, False)
+            self.down = mk(inter_l, cfg.hidden, True)
         fp8 = cfg.kv_cache_dtype != "auto"
         shape = PagedAttention.get_kv_cache_shape(num_blocks, cfg.block_size, self.kvh, d)
         if fp8:
@@ -138,7 +141,8 @@ class DecodeLayer:
 class DecodeModel:
     """`num_layers` layers over one set of paged-cache metadata; `step()` runs one decode step for the whole batch."""
 
-    def __init__(self, cfg: DecodeConfig, batch: int, ctx: int, tp: Optional[TPGroup] = None, device="cuda", seed: int = 0):
+    def __init__(self, cfg: DecodeConfig, batch: int, ctx: int, tp: Optional[TPGroup] = None, device="cuda", seed: int = 0,
+                 weights_from: "Optional[DecodeModel]" = None):
         self.cfg, self.batch, self.ctx = cfg, batch, ctx
         self.tp = tp if tp is not None else TPGroup()
         if self.tp.world_size > 1 and self.tp.custom is None and torch.device(device).type == "cuda":
@@ -152,7 +156,9 @@ class DecodeModel:
         self.seq_lens = torch.full((batch,), ctx, dtype=torch.int32, device=device)
         last = self.block_tables[:, (ctx - 1) // bs].to(torch.int64)
         self.slot_mapping = last * bs + (ctx - 1) % bs  # the new token is the last position of each sequence
-        self.layers: List[DecodeLayer] = [DecodeLayer(cfg, self.tp, num_blocks, device, gen) for _ in range(cfg.num_layers)]
+        self.layers: List[DecodeLayer] = [
+            DecodeLayer(cfg, self.tp, num_blocks, device, gen, weights_from.layers[i] if weights_from is not None else None)
+            for i in range(cfg.num_layers)]
         self.x = (torch.randn(batch, cfg.hidden, device=device, generator=gen) * 0.05).to(cfg.dtype)
         self.norm = (1.0 + 0.1 * torch.randn(cfg.hidden, device=device, generator=gen)).to(cfg.dtype)
         self.positions = torch.full((batch,), ctx - 1, dtype=torch.int64, device=device)

@@ -12,8 +12,14 @@ token, slot mapping, block tables, sequence lengths) starting in pinned HOST mem
 output copied back, copies inside the timed region. The KV cache itself is device-resident state
 (it never lives on the host in the reference either: worker/cache_engine.py).
 
-Multi-GPU (torchrun, one rank per GPU): attention has no exchange step; every rank runs the same
-per-GPU workload on its own KV pool (weak scaling), value = total bytes / max-over-ranks time.
+Multi-GPU (torchrun, one rank per GPU): tensor parallelism as the reference shards this path
+(modeling/models/llama.py:118-127): the GLOBAL C2 batch is fixed and rank r of N serves 32/N query heads and
+max(1, 8/N) kv heads of every sequence from its own KV cache; attention has no exchange step, so
+there is no collective in the timed region. value = global KV bytes (every kv head once) / max-over-ranks
+time: STRONG scaling. The tensor-parallel decode step (GEMMs + all-reduces) is reported in `extras.decode`.
+
+After the timed loop the last output of the timed kernel is checked against the CPU oracle on 4 sampled
+sequences of the full problem (outside the timed region); a miss fails the run.
 
 --impl reference: the reference's own CPU implementation of the path (oracle/_ref = unmodified
 kernels/cpu/attention.cpp, bf16 KV because the CPU backend has no FP8) on the host cores, each step
@@ -33,10 +39,10 @@ sys.path.insert(0, ROOT)
 H, KVH, D, BS = 32, 8, 128, 16
 BATCH, CTX = 64, 4096
 METRIC = "paged-attn decode KV GB/s"
-# dram__bytes_read.sum + dram__bytes_write.sum of the split-K kernel + its reduce for one launch of this workload, from the
-# `ncu --set full` captures summarised in profiles/r01_ncu_full_attention_final.txt (main kernel 539.1 MB read + 6.8 MB
-# written, reduce 4.3 MB read)
+# dram__bytes_read.sum + dram__bytes_write.sum of one launch of this workload at N = 1, from an `ncu --set full` capture of
+# THIS command line; not measured in the run, so the line names the file it comes from
 NCU_TRAFFIC_BYTES = 550_200_000
+NCU_TRAFFIC_SOURCE = "profiles/r01_ncu_full_attention_final.txt (ncu --set full, main kernel 539.1 MB read + 6.8 MB written, reduce 4.3 MB read)"
 WORKLOAD = "C2: paged_attention_v2 Llama-3-8B shape 32q/8kv d128, fp8_e4m3 KV, block 16, batch 64 x ctx 4096"
 
 
@@ -247,38 +253,194 @@ def gemm_extras(torch, A, dev, iters=30):
     return res
 
 
+def attention_extras(torch, A, dev, iters=20):
+    """The other attention configs of BASELINE.json on one GPU, CUDA-graph replay over KV pools rotated through > 256 MB:
+    C5 (Qwen2-72B shape at TP 8: 8 q / 1 kv heads per GPU, 32 768 ctx, FP8-E5M2 KV, batch 1 / 8 / 32) and C1's shape on
+    the GPU (12 heads x 64, bf16 KV, 8 x 512; latency-bound)."""
+    hbm_peak, _ = peaks()
+    res = {}
+    cases = [("C5_b1", 8, 1, 128, 1, 32768, "fp8_e5m2"), ("C5_b8", 8, 1, 128, 8, 32768, "fp8_e5m2"),
+             ("C5_b32", 8, 1, 128, 32, 32768, "fp8_e5m2"), ("C4_tp8_b64", 8, 1, 128, 64, 4096, "fp8"),
+             ("C1_gpu", 12, 12, 64, 8, 512, "auto")]
+    g = torch.Generator(device=dev).manual_seed(0)
+    one = torch.tensor(1.0, device=dev)
+    for name, h, kvh, d, batch, ctx, kv in cases:
+        esz = 2 if kv == "auto" else 1
+        x = 16 // esz
+        nblk = batch * ctx // BS
+        byt = kv_bytes(batch, ctx, kvh, d, esz)
+        npools = max(2, min(64, -(-(300 << 20) // byt)))
+        pools = []
+        for _ in range(npools):
+            if kv == "auto":
+                kc = (torch.rand(nblk, kvh, d // x, BS, x, generator=g, device=dev) - 0.5).to(torch.bfloat16)
+                vc = (torch.rand(nblk, kvh, d, BS, generator=g, device=dev) - 0.5).to(torch.bfloat16)
+            else:  # any byte below 0x78 is a finite value in both FP8 formats
+                kc = torch.randint(0, 120, (nblk, kvh, d // x, BS, x), dtype=torch.uint8, device=dev, generator=g)
+                vc = torch.randint(0, 120, (nblk, kvh, d, BS), dtype=torch.uint8, device=dev, generator=g)
+            pools.append((kc, vc))
+        q = ((torch.rand(batch, h, d, generator=g, device=dev) * 2 - 1) * d ** -0.5).to(torch.bfloat16)
+        bt = torch.randperm(nblk, generator=g, device=dev).to(torch.int32).reshape(batch, ctx // BS)
+        sl = torch.full((batch,), ctx, dtype=torch.int32, device=dev)
+        f = lambda i: A.PagedAttention.forward_decode(q, pools[i % npools][0], pools[i % npools][1], bt, sl, ctx, kv, kvh,
+                                                      d ** -0.5, None, one, one)
+        for i in range(3):
+            f(i)
+        st = torch.cuda.Stream()
+        st.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(st):
+            gph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gph, stream=st):
+                for i in range(iters):
+                    f(i)
+            gph.replay()
+            st.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            gph.replay()
+            e1.record(st)
+            st.synchronize()
+        us = e0.elapsed_time(e1) / iters * 1e3
+        res[name] = {"heads": f"{h}q/{kvh}kv d{d}", "batch": batch, "ctx": ctx, "kv": kv, "us": round(us, 2),
+                     "kv_bytes": byt, "GBps": round(byt / us / 1e3, 1), "frac_hbm": round(byt / us / 1e3 / hbm_peak, 3)}
+        del pools, gph
+        torch.cuda.empty_cache()
+    return res
+
+
+def c1_cpu_decode_loop(seconds_target=6.0):
+    """BASELINE.md 4.2 (b), config C1 on the host cores: a 12-layer OPT-125m-shaped decode loop with random weights -
+    torch CPU linears + the reference CPU backend's reshape_and_cache and paged_attention_v1 (oracle/_ref), bf16,
+    block 16, 8 sequences x 512 context, 12 heads x 64."""
+    import torch
+    from oracle import oracle
+    ref = oracle.refcpu()
+    if ref is None:
+        return {"unavailable": "oracle/_ref (reference CPU backend) not built"}
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    L, hid, ffn, h, d, batch, ctx = 12, 768, 3072, 12, 64, 8, 512
+    dt = torch.bfloat16
+    g = torch.Generator().manual_seed(0)
+    nblk = batch * ctx // BS
+    mk = lambda *shape: (torch.randn(*shape, generator=g) * 0.02).to(dt)
+    layers = [dict(qkv=mk(3 * hid, hid), o=mk(hid, hid), up=mk(ffn, hid), down=mk(hid, ffn),
+                   kc=mk(nblk, h, d // 8, BS, 8), vc=mk(nblk, h, d, BS)) for _ in range(L)]
+    bt = torch.randperm(nblk, generator=g).to(torch.int32).reshape(batch, ctx // BS)
+    sl = torch.full((batch,), ctx, dtype=torch.int32)
+    slots = bt[:, -1].to(torch.int64) * BS + (BS - 1)
+    one = torch.tensor(1.0)
+    x0 = mk(batch, hid)
+    ln = torch.nn.functional.layer_norm
+
+    def step():
+        x = x0
+        for w in layers:
+            hdn = ln(x, (hid,))
+            qkv = torch.nn.functional.linear(hdn, w["qkv"])
+            q, k, v = qkv.split(hid, dim=-1)
+            ref.reshape_and_cache(k.reshape(batch, h, d), v.reshape(batch, h, d), w["kc"], w["vc"], slots, "auto", one, one)
+            a = torch.empty(batch, h, d, dtype=dt)
+            ref.paged_attention_v1(a, q.reshape(batch, h, d).contiguous(), w["kc"], w["vc"], h, d ** -0.5, bt, sl, BS, ctx, None,
+                                   "auto", one, one, 0, 0, 0, 64, 0)
+            x = x + torch.nn.functional.linear(a.reshape(batch, hid), w["o"])
+            hdn = ln(x, (hid,))
+            x = x + torch.nn.functional.linear(torch.relu(torch.nn.functional.linear(hdn, w["up"])), w["down"])
+        return x
+
+    step()
+    t0, n = time.perf_counter(), 0
+    while True:
+        step()
+        n += 1
+        el = time.perf_counter() - t0
+        if el >= seconds_target or n >= 500:
+            break
+    ms = el / n * 1e3
+    kvb = kv_bytes(batch, ctx, h, d, 2) * L
+    return {"config": "C1: OPT-125m shape, 12 layers, bf16, block 16, 8 seqs x 512 ctx, reference CPU backend (oracle/_ref) + torch CPU linears",
+            "cores": cores, "steps": n, "ms_per_step": round(ms, 3), "tok_per_s": round(batch / ms * 1e3, 1),
+            "kv_GBps": round(kvb / (ms * 1e-3) / 1e9, 2)}
+
+
 def decode_extras(torch, A, dev, world, steps=10):
-    """Decode tok/s of a Llama layer stack built from this library's kernels only (+ NCCL all_reduce when world > 1),
-    one CUDA graph per step. 1 GPU: Llama-3.1-8B shapes (C3); N GPUs: Llama-3.1-70B shapes at TP = N (C4). RMSNorm,
-    RoPE and SiLU-mul are the library's own kernels, see aphrodite-fork_b200/decode.py."""
+    """Decode tok/s of a Llama layer stack built from this library's kernels only (+ the all-reduce when world > 1),
+    one CUDA graph per step. 1 GPU: Llama-3.1-8B shapes (C3) at batch 1 / 16 / 64 / 256; N GPUs: Llama-3.1-70B shapes at
+    TP = N (C4), batch 64. RMSNorm, RoPE and SiLU-mul are the library's own kernels, see
+    aphrodite-fork_b200/decode.py. `roofline` = mandatory HBM bytes of a step on one GPU (this rank's weights + KV, each
+    once) / step time against the measured HBM peak."""
+    import torch.distributed as dist
     from aphrodite_fork_b200.decode import DecodeConfig, DecodeModel
     from aphrodite_fork_b200.tp import TPGroup
     cfg = DecodeConfig.llama3_8b() if world == 1 else DecodeConfig.llama3_70b()
-    model = DecodeModel(cfg, batch=BATCH, ctx=CTX, tp=TPGroup(), device=dev, seed=0)
-    model.capture()
-    for _ in range(3):
-        model.step()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(steps):
-        model.step()
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / steps
-    if world > 1:
-        import torch.distributed as dist
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    return {"model": ("llama-3.1-8b" if world == 1 else "llama-3.1-70b") + f" shapes, {cfg.num_layers} layers, W4A16 g128, fp8 KV",
-            "tp": world, "batch": BATCH, "ctx": CTX, "ms_per_step": round(ms, 3), "tok_per_s": round(BATCH / (ms * 1e-3), 1),
-            "all_reduce": ("none" if world == 1 else f"NCCL ({model.tp.custom_error})" if model.tp.custom is None
-                           else "one-shot peer-memory kernel (csrc/all_reduce.cu)" if model.tp.custom.should_use(model.x)
-                           else "NCCL (message above the one-shot threshold of this world size)"),
-            "kernel_launches_per_step": model.launches_per_step(),
-            "hbm_bytes_per_step_per_gpu": model.kv_bytes_per_step() + model.weight_bytes(),
-            "hbm_GBps_per_gpu": round((model.kv_bytes_per_step() + model.weight_bytes()) / (ms * 1e-3) / 1e9, 1)}
+    hbm_peak, _ = peaks()
+    tp = TPGroup()
+
+    def measure(model):
+        model.capture()
+        for _ in range(3):
+            model.step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            model.step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        byt = model.kv_bytes_per_step() + model.weight_bytes()
+        return {"batch": model.batch, "ctx": model.ctx, "ms_per_step": round(ms, 3), "tok_per_s": round(model.batch / (ms * 1e-3), 1),
+                "kernel_launches_per_step": model.launches_per_step(), "hbm_bytes_per_step_per_gpu": byt,
+                "roofline": {"bound": "hbm", "achieved": round(byt / (ms * 1e-3) / 1e9, 1), "peak": hbm_peak, "unit": "GB/s",
+                             "frac": round(byt / (ms * 1e-3) / 1e9 / hbm_peak, 4)}}
+
+    main = DecodeModel(cfg, batch=BATCH, ctx=CTX, tp=tp, device=dev, seed=0)
+    res = measure(main)
+    res.update({"model": ("llama-3.1-8b" if world == 1 else "llama-3.1-70b") + f" shapes, {cfg.num_layers} layers, W4A16 g128, fp8 KV",
+                "tp": world,
+                "all_reduce": ("none" if world == 1 else f"NCCL ({main.tp.custom_error})" if main.tp.custom is None
+                               else main.tp.describe(main.x) if hasattr(main.tp, "describe")
+                               else "one-shot peer-memory kernel (csrc/all_reduce.cu)" if main.tp.custom.should_use(main.x)
+                               else "NCCL (message above the one-shot threshold of this world size)")})
+    if world == 1:  # C3: "decode loop, batch 1-256"
+        sweep = {}
+        for b in (1, 16, 256):
+            main.graph = None
+            m = DecodeModel(cfg, batch=b, ctx=CTX, tp=tp, device=dev, seed=1, weights_from=main)
+            r = measure(m)
+            sweep[f"batch{b}"] = {k: r[k] for k in ("ms_per_step", "tok_per_s", "hbm_bytes_per_step_per_gpu", "roofline")}
+            del m
+            torch.cuda.empty_cache()
+        sweep[f"batch{BATCH}"] = {k: res[k] for k in ("ms_per_step", "tok_per_s", "hbm_bytes_per_step_per_gpu", "roofline")}
+        res["batch_sweep"] = sweep
+    return res
+
+
+def check_parity(torch, out, q, pool, bt, sl, kvh, scale, seqs=(0, 21, 42, 63), atol=1e-2, rtol=1.6e-2):
+    """The timed kernel's output for `seqs` against oracle/ (the checker, never the thing measured): the sequences'
+    KV blocks are gathered into a compact CPU cache, attention is evaluated in double over the FP8 cache dequantised
+    the way the reference reads it. Bound: |out - truth| <= atol + rtol |truth| (reference tests' atol for FP8 KV,
+    torch's bf16 rtol) - the bound of tests/test_gpu_attention.py."""
+    from oracle import oracle
+    kc, vc = pool
+    idx = torch.tensor(list(seqs), device=out.device)
+    blocks = bt[idx].to(torch.int64)                      # [n, blocks per seq]
+    n, per = blocks.shape
+    kc_s = kc[blocks.reshape(-1)].cpu()
+    vc_s = vc[blocks.reshape(-1)].cpu()
+    bt_s = torch.arange(n * per, dtype=torch.int32).reshape(n, per)
+    ref64, _ = oracle.paged_attention(q[idx].cpu(), kc_s, vc_s, kvh, scale, bt_s, sl[idx].cpu(), BS, kv_cache_dtype="fp8")
+    got = out[idx].cpu().double()
+    err = (got - ref64).abs()
+    return {"checked_seqs": len(seqs), "checked_values": int(err.numel()), "max_abs": float(err.max()),
+            "worst_excess": float((err - (atol + rtol * ref64.abs())).max()), "bound": f"{atol} + {rtol}*|truth|",
+            "against": "oracle/ (C restatement, fp64) on the full-size problem, last timed step"}
 
 
 def run_ours(args):
@@ -298,34 +460,40 @@ def run_ours(args):
     A.load()
     steps, warm = args.steps, max(args.warmup, 3)
 
-    # ---- synthetic C2 inputs (seed 0), KV pool = 16384 distinct blocks = 512 MiB FP8 > L2 ----
+    # ---- tensor-parallel shard of C2 (llama.py:118-127): fixed global batch, heads split over the ranks ----
+    assert H % world == 0 and (KVH % world == 0 or world % KVH == 0), f"{world} ranks cannot shard {H}q/{KVH}kv heads"
+    Hr, KVHr = H // world, max(1, KVH // world)
+    kv_replicas = max(1, world // KVH)  # ranks holding the same kv head (none up to 8 ranks)
+    # ---- synthetic inputs (seed 0): per pool 16384 distinct blocks; as many pools as it takes to rotate through
+    #      >= 1 GiB of KV, so no launch finds its KV in the 126 MB L2 (a rank's pool is only 64 MiB at N = 8) ----
     g = torch.Generator(device=dev).manual_seed(0 + rank)
     nblk = BATCH * CTX // BS
     sc = D ** -0.5
     one = torch.tensor(1.0, device=dev)
-    npools = 2  # alternate between two pools: 1 GiB of KV in rotation
+    pool_bytes = kv_bytes(BATCH, CTX, KVHr, D, 1)
+    npools = max(2, -(-(1 << 30) // pool_bytes))
     pools = []
     for _ in range(npools):
-        src = ((torch.rand(nblk, KVH, D // 16, BS, 16, generator=g, device=dev) * 2 - 1) * sc).to(torch.bfloat16)
+        src = ((torch.rand(nblk, KVHr, D // 16, BS, 16, generator=g, device=dev) * 2 - 1) * sc).to(torch.bfloat16)
         kc = torch.empty(src.shape, dtype=torch.uint8, device=dev)
         A.ops.convert_fp8(kc, src, 1.0, "fp8")
-        src = ((torch.rand(nblk, KVH, D, BS, generator=g, device=dev) * 2 - 1) * sc).to(torch.bfloat16)
+        src = ((torch.rand(nblk, KVHr, D, BS, generator=g, device=dev) * 2 - 1) * sc).to(torch.bfloat16)
         vc = torch.empty(src.shape, dtype=torch.uint8, device=dev)
         A.ops.convert_fp8(vc, src, 1.0, "fp8")
         pools.append((kc, vc))
     del src
-    q = ((torch.rand(BATCH, H, D, generator=g, device=dev) * 2 - 1) * sc).to(torch.bfloat16)
+    q = ((torch.rand(BATCH, Hr, D, generator=g, device=dev) * 2 - 1) * sc).to(torch.bfloat16)
     bt = torch.randperm(nblk, generator=g, device=dev).to(torch.int32).reshape(BATCH, CTX // BS)
     sl = torch.full((BATCH,), CTX, dtype=torch.int32, device=dev)
     out = torch.empty_like(q)
     P = (CTX + 511) // 512
-    exp_sums = torch.empty(BATCH, H, P, dtype=torch.float32, device=dev)
+    exp_sums = torch.empty(BATCH, Hr, P, dtype=torch.float32, device=dev)
     max_logits = torch.empty_like(exp_sums)
-    tmp_out = torch.empty(BATCH, H, P, D, dtype=torch.bfloat16, device=dev)
+    tmp_out = torch.empty(BATCH, Hr, P, D, dtype=torch.bfloat16, device=dev)
 
     def step(i):
         kc, vc = pools[i % npools]
-        A.ops.paged_attention_v2(out, exp_sums, max_logits, tmp_out, q, kc, vc, KVH, sc, bt, sl, BS, CTX, None, "fp8",
+        A.ops.paged_attention_v2(out, exp_sums, max_logits, tmp_out, q, kc, vc, KVHr, sc, bt, sl, BS, CTX, None, "fp8",
                                  one, one)
 
     def barrier():
@@ -352,9 +520,23 @@ def run_ours(args):
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
+    # algorithmic bytes: K and V of every kv head of the GLOBAL problem once (a kv head replicated over several ranks
+    # still counts once); what one rank's launch streams is pool_bytes
     per_step_bytes = kv_bytes(BATCH, CTX, KVH, D, 1)
-    value = per_step_bytes * steps * world / (ms * 1e-3) / 1e9
-    per_gpu = per_step_bytes * steps / (ms * 1e-3) / 1e9
+    value = per_step_bytes * steps / (ms * 1e-3) / 1e9
+    per_gpu = pool_bytes * steps / (ms * 1e-3) / 1e9
+
+    # ---- parity of the TIMED kernel on the FULL problem (outside the timed region): the output of the last timed
+    #      step against the CPU oracle on 4 sampled sequences; tolerance of tests/test_gpu_attention.py for FP8 KV ----
+    parity = check_parity(torch, out, q, pools[(steps - 1) % npools], bt, sl, KVHr, sc)
+    if world > 1:
+        t = torch.tensor([parity["max_abs"], parity["worst_excess"]], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        parity["max_abs"], parity["worst_excess"] = float(t[0]), float(t[1])
+        parity["ranks_checked"] = world
+    parity["ok"] = parity["worst_excess"] <= 0
+    if not parity["ok"]:
+        raise RuntimeError(f"bench.py: the timed kernel's output misses the oracle: {parity}")
 
     # ---- e2e: public API, host-resident step inputs, copies inside the timed region ----
     # Every step copies ITS inputs (query, new K/V token, block tables, sequence lengths, slot mapping) from pinned host
@@ -364,7 +546,7 @@ def run_ours(args):
     def seg(nbytes):
         return (nbytes + 255) // 256 * 256
 
-    parts = [("q", (BATCH, H, D), torch.bfloat16), ("newkv", (BATCH, 2, KVH, D), torch.bfloat16),
+    parts = [("q", (BATCH, Hr, D), torch.bfloat16), ("newkv", (BATCH, 2, KVHr, D), torch.bfloat16),
              ("bt", (BATCH, CTX // BS), torch.int32), ("sl", (BATCH,), torch.int32), ("slots", (BATCH,), torch.int64)]
     offs, total_in = {}, 0
     for name, shape, dt in parts:
@@ -378,14 +560,14 @@ def run_ours(args):
     in_h = torch.empty(total_in, dtype=torch.uint8, pin_memory=True)
     hv = views(in_h)
     hv["q"].copy_(q.cpu())
-    hv["newkv"].copy_(((torch.rand(BATCH, 2, KVH, D) * 2 - 1) * sc).to(torch.bfloat16))
+    hv["newkv"].copy_(((torch.rand(BATCH, 2, KVHr, D) * 2 - 1) * sc).to(torch.bfloat16))
     hv["bt"].copy_(bt.cpu())
     hv["sl"].copy_(sl.cpu())
     hv["slots"].copy_(hv["bt"][:, -1].to(torch.int64) * BS + (BS - 1))  # slot of token ctx-1 of every sequence
     NBUF = 2
     in_d = [torch.empty(total_in, dtype=torch.uint8, device=dev) for _ in range(NBUF)]
     dv = [views(b) for b in in_d]
-    out_h = [torch.empty(BATCH, H, D, dtype=torch.bfloat16, pin_memory=True) for _ in range(NBUF)]
+    out_h = [torch.empty(BATCH, Hr, D, dtype=torch.bfloat16, pin_memory=True) for _ in range(NBUF)]
     h2d = sum(n for _, (o, n, shape, dt) in offs.items())
     d2h = out_h[0].numel() * out_h[0].element_size()
     s_in, s_out = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
@@ -404,7 +586,7 @@ def run_ours(args):
         s_cmp.wait_event(ev_in[b])
         v = dv[b]
         A.PagedAttention.write_to_paged_cache(v["newkv"][:, 0], v["newkv"][:, 1], kc, vc, v["slots"], "fp8", one, one)
-        o = A.PagedAttention.forward_decode(v["q"], kc, vc, v["bt"], v["sl"], CTX, "fp8", KVH, sc, None, one, one)
+        o = A.PagedAttention.forward_decode(v["q"], kc, vc, v["bt"], v["sl"], CTX, "fp8", KVHr, sc, None, one, one)
         ev_cmp[b].record(s_cmp)
         with torch.cuda.stream(s_out):
             s_out.wait_event(ev_cmp[b])
@@ -433,7 +615,7 @@ def run_ours(args):
         t = torch.tensor([ems], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ems = float(t.item())
-    e2e_val = per_step_bytes * steps * world / (ems * 1e-3) / 1e9
+    e2e_val = per_step_bytes * steps / (ems * 1e-3) / 1e9
 
     # ---- secondary numbers of BASELINE's metric: W4A16 GEMM TFLOP/s (rank 0) and decode tok/s (all ranks) ----
     extras = {}
@@ -443,6 +625,8 @@ def run_ours(args):
         try:
             if rank == 0:
                 extras["gemm_w4a16"] = gemm_extras(torch, A, dev)
+                if world == 1:
+                    extras["attention_configs"] = attention_extras(torch, A, dev)
             barrier()
             torch.cuda.empty_cache()
             extras["decode"] = decode_extras(torch, A, dev, world)
@@ -453,17 +637,22 @@ def run_ours(args):
         peak, peak_src = peaks()
         line = {
             "metric": METRIC, "value": round(value, 2), "unit": "GB/s", "n_gpus": world, "steps": steps,
-            "warmup": warm, "ms_per_step": round(ms / steps, 5), "higher_is_better": True, "scaling": "weak",
+            "warmup": warm, "ms_per_step": round(ms / steps, 5), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f16 mma / f32 accumulate over fp8_e4m3 KV, bf16 q/out", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "per_gpu": "full C2 batch per rank (weak scaling, no collective on this path)",
-                       "l2": "two 512 MiB FP8 KV pools alternated, block tables = random permutation of distinct "
-                             "blocks: inputs larger than the 126 MB L2",
-                       "kv_bytes_per_step": per_step_bytes},
+            "config": {"workload": WORKLOAD,
+                       "parallelism": f"tp{world}: fixed global batch {BATCH} x {CTX}, {Hr} q / {KVHr} kv heads per rank"
+                                      + (f" (each kv head on {kv_replicas} ranks)" if kv_replicas > 1 else "")
+                                      + ", no collective in attention (llama.py:118-127)",
+                       "l2": f"{npools} FP8 KV pools of {pool_bytes >> 20} MiB per rank in rotation (>= 1 GiB), block tables = random "
+                             "permutation of distinct blocks: inputs larger than the 126 MB L2",
+                       "kv_bytes_per_step": per_step_bytes, "kv_bytes_per_step_per_gpu": pool_bytes},
             "roofline": {"bound": "hbm", "achieved": round(per_gpu, 2), "peak": peak, "unit": "GB/s",
-                         "frac": round(per_gpu / peak, 4), "traffic": NCU_TRAFFIC_BYTES,
-                         "note": f"algorithmic KV bytes / CUDA-event time of the whole op (split-K kernel + reduce) per launch; "
-                                 f"peak = {peak_src}"},
-            "e2e": {"value": round(e2e_val, 2), "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                         "frac": round(per_gpu / peak, 4), "traffic": NCU_TRAFFIC_BYTES if world == 1 else None,
+                         "traffic_source": NCU_TRAFFIC_SOURCE if world == 1 else None,
+                         "note": f"per GPU: algorithmic KV bytes of one rank's launch / CUDA-event time of the whole op per "
+                                 f"launch (max over ranks); peak = {peak_src}"},
+            "parity": parity,
+            "e2e": {"value": round(e2e_val, 2), "unit": "GB/s", "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
                     "ms_per_step": round(ems / steps, 5),
                     "api": "PagedAttention.write_to_paged_cache + forward_decode; every step uploads its q / new K,V token / "
                            "block tables / seq lens / slot mapping from ONE packed pinned host buffer and downloads its "
@@ -476,6 +665,14 @@ def run_ours(args):
             gbs, cores, kind, sample, cms, n = cpu_reference_run(12.0, 4, CTX)
             line["cpu_baseline"] = {"value": round(gbs, 3), "unit": "GB/s", "cores": cores, "kind": kind,
                                     "sample": sample, "ms_per_call": round(cms, 3)}
+            if not args.no_extras:
+                try:
+                    extras["c1_cpu_decode_loop"] = c1_cpu_decode_loop()
+                except Exception as ex:
+                    extras["c1_cpu_decode_loop"] = {"error": f"{type(ex).__name__}: {ex}"[:200]}
+        if extras:  # the secondary legs also as their own stderr lines (a long stdout line gets truncated in logs)
+            for k, v in extras.items():
+                print(json.dumps({"extra": k, "n_gpus": world, "result": v}), file=sys.stderr, flush=True)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -63,9 +63,9 @@ def quantized(K, N, bits, gs, zp, dtype, seed):
     return _cache[key]
 
 
-def case(M, K, N, gs, dtype, zp=False, seed=1, lda_pad=0, **kw):
+def case(M, K, N, gs, dtype, zp=False, seed=1, lda_pad=0, a_shift=0.0, a_scale=1.0, **kw):
     w_ref, b, s, bz = quantized(K, N, 4, gs, zp, dtype, seed)
-    a_full = synth.tensor((M, K + lda_pad), seed + 100, dtype, 1.0)
+    a_full = (a_shift + synth.tensor((M, K + lda_pad), seed + 100, torch.float64, a_scale)).to(dtype)
     a = a_full[:, :K]
     ref = oracle.gemm(a.contiguous(), w_ref)
     a_d = a_full.cuda()[:, :K]
@@ -109,6 +109,28 @@ def test_gptq_marlin_gemm_large_batch_tensor_memory_path(M, K, N, gs):
     case(M, K, N, gs, torch.float16, zp=(gs != -1), seed=12)
 
 
+@pytest.mark.parametrize("M", [1, 16, 64, 256])
+def test_gptq_marlin_gemm_gate_up_and_tp8_70b_shards(M):
+    # the widest C3 matrix (gate_up 4096 x 28672) and the Llama-3.1-70B TP = 8 per-rank shards the bench times
+    # (qkv 8192 x 1280, o 1024 x 8192, gate_up 8192 x 7168, down 3584 x 8192)
+    case(M, 4096, 28672, 128, torch.bfloat16, seed=31)
+    case(M, 8192, 1280, 128, torch.bfloat16, seed=32)
+    case(M, 1024, 8192, 128, torch.bfloat16, seed=33)
+    case(M, 8192, 7168, 128, torch.bfloat16, seed=34)
+    case(M, 3584, 8192, 128, torch.bfloat16, seed=35)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("gs,zp", [(-1, False), (-1, True), (128, False)])
+@pytest.mark.parametrize("M", [1, 8, 16, 48])
+def test_gptq_marlin_gemm_activations_with_a_mean(M, gs, zp, dtype):
+    # activations a = 1 + U(-0.5, 0.5) over a deep K: the register kernel's offset sums  sum a (OFF + q)  and
+    # OFF sum a  grow with |sum a| and cancel only at a flush; channelwise scales used to flush once per k range
+    # (error ~ OFF |sum a| 2^-23 per step, 1e-3 .. 2.5e-2 of the result at K = 4k .. 14k)
+    case(M, 8192, 256, gs, dtype, zp=zp, seed=41, a_shift=1.0, a_scale=0.5)
+    case(M, 14336, 128, gs, dtype, zp=zp, seed=42, a_shift=1.0, a_scale=0.5)
+
+
 def test_gptq_marlin_gemm_repeated_calls_leave_workspace_clean():
     # back-to-back launches share the lock buffer (arrival counters) and the scratch: results must not depend on history
     outs = []
@@ -121,8 +143,9 @@ def test_gptq_marlin_gemm_repeated_calls_leave_workspace_clean():
 def test_gptq_marlin_gemm_run_to_run_determinism_large_shape(M):
     # the Llama-3.1-8B down projection: deep K, stream-K ranges shared by many CTAs, back-to-back launches over rotating
     # weights. Every call on the same weights must return the same bits (fixed-order merges) and leave the lock buffer
-    # zero. (With an odd activation-ring depth at 256 batch rows ~0.1 % of the calls returned a wrong stripe of one
-    # tile; marlin_gemm_tc.cuh now keeps the depth even. tools/stress_gemm.py is the long version of this test.)
+    # zero. (Round 1: with an odd ring depth ~0.1 % of the calls returned a wrong stripe of one tile - mbarrier parity
+    # aliasing between the two dequantiser groups, fixed by ptx.cuh RingCursor; tests/tools/ring_fault_proof.py turns
+    # the rare failure into a deterministic one, tools/stress_gemm.py is the long version of this test.)
     K, N = 14336, 4096
     dev = "cuda"
     gen = torch.Generator(device=dev).manual_seed(0)

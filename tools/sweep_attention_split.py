@@ -3,6 +3,8 @@ partition) on the C2 and C5 shapes."""
 import os
 import sys
 
+os.environ["APH_DEV_ENV"] = "1"  # the library re-reads its development overrides on every call
+
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 os.environ["ONLY_OURS"] = "1"
 import bench_vs_ref as B

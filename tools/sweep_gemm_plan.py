@@ -4,6 +4,8 @@ import json
 import os
 import sys
 
+os.environ["APH_DEV_ENV"] = "1"  # the library re-reads its development overrides on every call
+
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench_gemm
