@@ -26,7 +26,7 @@ NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 if os.environ.get("APH_GEMM_TRACE_BUILD"):  # development: per-stage clock stamps in the tcgen05 GEMM (tools/trace_gemm.py)
     NVCC_FLAGS.append("-DAPH_GEMM_TRACE")
-HEAD_SIZES = [32, 64, 80, 96, 112, 128, 192, 256]
+HEAD_SIZES = [32, 64, 80, 96, 112, 120, 128, 192, 256]
 FAST = os.environ.get("APH_FAST_BUILD", "0") == "1"
 
 

@@ -34,6 +34,7 @@
 
 #include "marlin_gemm_kernel.cuh"
 #include "marlin_gemm_tc.cuh"
+#include "marlin_actorder.cuh"
 
 namespace aphb200 {
 namespace mg {
@@ -301,17 +302,24 @@ static PlanTc make_plan_tc(int64_t M, int64_t N, int64_t K, int mb) {
 }
 
 static int tile_rows_tc(int64_t rows) { return rows <= 16 ? 16 : rows <= 32 ? 32 : rows <= 64 ? 64 : rows <= 128 ? 128 : 256; }
+static int tile_rows_tc8(int64_t rows) { return rows <= 16 ? 16 : rows <= 64 ? 64 : 256; }  // 8-bit weights: fewer instantiations
 
 static size_t scratch_bytes_tc(int64_t M, int64_t N, int64_t K) {
-  const int mb = tile_rows_tc(M);
-  const PlanTc pl = make_plan_tc(M, N, K, mb);
-  return (size_t)pl.grid * 2 * mb * mgtc::NTILE * sizeof(float);
+  size_t worst = 0;
+  for (int mb : {tile_rows_tc(M), tile_rows_tc8(M)}) {
+    const PlanTc pl = make_plan_tc(M, N, K, mb);
+    const size_t need = (size_t)pl.grid * 2 * mb * mgtc::NTILE * sizeof(float);
+    if (need > worst) worst = need;
+  }
+  return worst;
 }
 
-template <typename scalar_t, int MB, bool HAS_ZP>
+template <typename scalar_t, int MB, bool HAS_ZP, int BITS = 4>
 static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t scratch_bytes, cudaStream_t stream) {
-  using C = mgtc::Cfg<scalar_t, MB>;
-  auto kern = mgtc::marlin_w4a16_tc_kernel<scalar_t, MB, HAS_ZP>;
+  using C = mgtc::Cfg<scalar_t, MB, BITS>;
+  constexpr int WPC = BITS / 4;    // 8-byte words per weight column and k16-row
+  constexpr int PACK = 32 / BITS;  // zero points per int32
+  auto kern = mgtc::marlin_w4a16_tc_kernel<scalar_t, MB, HAS_ZP, BITS>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -333,8 +341,8 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
   const int gps = grouped ? mgtc::KSTAGE / p.group_size : 0;
   const CUtensorMapDataType dt16 = op.f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   alignas(64) CUtensorMap tmB, tmA, tmS, tmZ;
-  int st = make_map_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_UINT64, 8, op.b, (uint64_t)p.N, (uint64_t)p.K / 16, (uint64_t)p.N * 8,
-                       mgtc::NTILE, 8, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+  int st = make_map_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_UINT64, 8, op.b, (uint64_t)p.N * WPC, (uint64_t)p.K / 16, (uint64_t)p.N * 8 * WPC,
+                       mgtc::NTILE * WPC, 8, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
   if (st != APH_OK) return st;
   st = make_map_2d(&tmA, dt16, 2, op.a, (uint64_t)p.K, (uint64_t)op.M, (uint64_t)op.lda * 2, 64, MB, CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
@@ -344,8 +352,8 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
                      CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
     if (st != APH_OK) return st;
     if (HAS_ZP) {
-      st = make_map_2d(&tmZ, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, op.zp, (uint64_t)p.N / 8, (uint64_t)op.num_groups,
-                       (uint64_t)p.N / 2, mgtc::NTILE / 8, gps, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+      st = make_map_2d(&tmZ, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, op.zp, (uint64_t)p.N / PACK, (uint64_t)op.num_groups,
+                       (uint64_t)p.N / PACK * 4, mgtc::NTILE / PACK, gps, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
       if (st != APH_OK) return st;
     } else {
       tmZ = tmS;
@@ -407,7 +415,8 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
 }
 
 template <typename scalar_t>
-static int run_typed_tc(const Params& p0, const Operands& op0, bool has_zp, float* scratch, size_t scratch_bytes, cudaStream_t stream) {
+static int run_typed_tc(const Params& p0, const Operands& op0, bool has_zp, int bits, float* scratch, size_t scratch_bytes,
+                        cudaStream_t stream) {
   // One launch covers every 256-row batch tile (the item list is (slice, batch tile, k stage)); APH_TC_CHUNK=1 runs
   // one launch per 256 rows instead (development).
   static const bool chunked = getenv("APH_TC_CHUNK") != nullptr;
@@ -427,6 +436,23 @@ static int run_typed_tc(const Params& p0, const Operands& op0, bool has_zp, floa
     p.group_size = p0.group_size;
     APH_CHECK((rows + 255) / 256 <= 32, APH_ERR_UNSUPPORTED, "gptq_marlin_gemm: size_m above 8192 is not supported in one call");
     int st;
+    if (bits == 8) {
+      // 8-bit weights (uint8b128 / uint8): batch tiles of 16, 64 or 256 rows
+      const int mb = tile_rows_tc8(rows);
+#define APH_TC_CASE8(MBV)                                                                                 \
+  st = has_zp ? launch_tc<scalar_t, MBV, true, 8>(p, op, scratch, scratch_bytes, stream)                  \
+              : launch_tc<scalar_t, MBV, false, 8>(p, op, scratch, scratch_bytes, stream);
+      if (mb == 16) {
+        APH_TC_CASE8(16)
+      } else if (mb == 64) {
+        APH_TC_CASE8(64)
+      } else {
+        APH_TC_CASE8(256)
+      }
+#undef APH_TC_CASE8
+      if (st != APH_OK) return st;
+      continue;
+    }
 #define APH_TC_CASE(MBV)                                                                                  \
   case MBV:                                                                                               \
     st = has_zp ? launch_tc<scalar_t, MBV, true>(p, op, scratch, scratch_bytes, stream)                   \
@@ -505,10 +531,12 @@ extern "C" int aph_gptq_marlin_gemm(void* c, const void* a, const void* b_q_weig
     APH_CHECK(b_q_type == mg::ID_UINT4B8 || b_q_type == mg::ID_UINT8B128, APH_ERR_INVALID_ARGUMENT,
               "b_q_type must be uint4b8 or uint8b128 when has_zp = False. Got = %lld", (long long)b_q_type);
   APH_CHECK(!is_zp_float, APH_ERR_UNSUPPORTED, "gptq_marlin_gemm: float zero points (HQQ) are not implemented");
-  APH_CHECK(b_q_type == mg::ID_UINT4 || b_q_type == mg::ID_UINT4B8, APH_ERR_UNSUPPORTED,
-            "gptq_marlin_gemm: 8-bit weight types are not implemented yet");
-  APH_CHECK(g_idx == nullptr && perm == nullptr, APH_ERR_UNSUPPORTED,
-            "gptq_marlin_gemm: act-order goes through aph_permute_cols + this call with g_idx = perm = NULL (is_k_full only)");
+  const int bits = (b_q_type == mg::ID_UINT8 || b_q_type == mg::ID_UINT8B128) ? 8 : 4;
+  // 8-bit weights run on the tensor-memory kernel for every batch size (128-column slices)
+  APH_CHECK(bits == 4 || size_n % mgtc::NTILE == 0, APH_ERR_UNSUPPORTED,
+            "gptq_marlin_gemm: 8-bit weights need size_n divisible by 128 here, got %lld", (long long)size_n);
+  APH_CHECK(perm == nullptr, APH_ERR_INVALID_ARGUMENT,
+            "gptq_marlin_gemm: pass activations that are already column-permuted (aph_permute_cols) and perm = NULL");
   APH_CHECK(dtype == APH_DT_F16 || dtype == APH_DT_BF16, APH_ERR_INVALID_ARGUMENT,
             "gpt_marlin_gemm only supports bfloat16 and float16");
   APH_CHECK(size_k % mg::KT == 0, APH_ERR_INVALID_ARGUMENT, "size_k = %lld is not divisible by tile_k = %d",
@@ -517,16 +545,25 @@ extern "C" int aph_gptq_marlin_gemm(void* c, const void* a, const void* b_q_weig
             (long long)size_n);
   APH_CHECK(lda % 8 == 0 && aligned16(a), APH_ERR_INVALID_ARGUMENT, "A.stride(0) must be divisible by 8 and A 16-byte aligned");
   APH_CHECK(aligned16(b_q_weight) && aligned16(b_scales), APH_ERR_INVALID_ARGUMENT, "weights / scales must be 16-byte aligned");
-  APH_CHECK(num_groups >= 1 && size_k % num_groups == 0, APH_ERR_INVALID_ARGUMENT,
+  APH_CHECK(num_groups >= 1 && (g_idx != nullptr || size_k % num_groups == 0), APH_ERR_INVALID_ARGUMENT,
             "size_k = %lld is not divisible by the number of groups %lld", (long long)size_k, (long long)num_groups);
   const int64_t group_size = size_k / num_groups;
-  APH_CHECK(num_groups == 1 || group_size == 32 || group_size == 64 || group_size == 128, APH_ERR_INVALID_ARGUMENT,
+  APH_CHECK(g_idx != nullptr || num_groups == 1 || group_size == 32 || group_size == 64 || group_size == 128, APH_ERR_INVALID_ARGUMENT,
             "Unsupported group_size = %lld", (long long)group_size);
   if (has_zp) APH_CHECK(b_zeros != nullptr && aligned16(b_zeros), APH_ERR_INVALID_ARGUMENT, "b_zeros missing or misaligned");
   const int64_t min_ws = size_n / 64 * 16;
   APH_CHECK(workspace != nullptr && workspace_ints >= min_ws, APH_ERR_INVALID_ARGUMENT,
             "workspace.numel = %lld is below min_workspace_size = %lld", (long long)workspace_ints, (long long)min_ws);
   if (size_m == 0) return APH_OK;
+  if (g_idx != nullptr) {
+    // act-order rows whose groups do not follow the k order (is_k_full = False): per-weight scales, marlin_actorder.cuh
+    APH_CHECK(!has_zp && b_q_type == mg::ID_UINT4B8, APH_ERR_UNSUPPORTED, "gptq_marlin_gemm: act-order is implemented for uint4b8 weights");
+    APH_CHECK(num_groups > 1, APH_ERR_INVALID_ARGUMENT, "For act_order, num_groups must be > 1");
+    APH_CHECK(size_m <= 65535 * (int64_t)mgao::MP, APH_ERR_UNSUPPORTED, "gptq_marlin_gemm: size_m too large for the act-order path");
+    if (dtype == APH_DT_F16)
+      return mgao::launch<__half>(c, a, b_q_weight, b_scales, g_idx, size_m, size_n, size_k, lda, (cudaStream_t)stream);
+    return mgao::launch<__nv_bfloat16>(c, a, b_q_weight, b_scales, g_idx, size_m, size_n, size_k, lda, (cudaStream_t)stream);
+  }
 
   mg::Params p;
   p.s = (const uint8_t*)b_scales;
@@ -542,9 +579,9 @@ extern "C" int aph_gptq_marlin_gemm(void* c, const void* a, const void* b_q_weig
   }
   mg::Operands op{a, b_q_weight, b_scales, has_zp ? b_zeros : nullptr, size_m, lda, num_groups, dtype == APH_DT_F16};
   cudaStream_t s = (cudaStream_t)stream;
-  if (mg::use_tc_path(size_m, size_n)) {
-    if (dtype == APH_DT_F16) return mg::run_typed_tc<__half>(p, op, has_zp != 0, (float*)scratch, scratch_bytes, s);
-    return mg::run_typed_tc<__nv_bfloat16>(p, op, has_zp != 0, (float*)scratch, scratch_bytes, s);
+  if (bits == 8 || mg::use_tc_path(size_m, size_n)) {
+    if (dtype == APH_DT_F16) return mg::run_typed_tc<__half>(p, op, has_zp != 0, bits, (float*)scratch, scratch_bytes, s);
+    return mg::run_typed_tc<__nv_bfloat16>(p, op, has_zp != 0, bits, (float*)scratch, scratch_bytes, s);
   }
   if (dtype == APH_DT_F16) return mg::run_typed<__half>(p, op, has_zp != 0, (float*)scratch, scratch_bytes, s);
   return mg::run_typed<__nv_bfloat16>(p, op, has_zp != 0, (float*)scratch, scratch_bytes, s);

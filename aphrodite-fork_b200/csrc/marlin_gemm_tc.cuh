@@ -38,10 +38,17 @@ constexpr int DQ_GROUPS = 2;  // group (it & 1) takes stage it
 constexpr int W_PROD = 0, W_MMA = 1, W_ACT = 2, W_MMA2 = 3, W_EPI0 = 4, W_DQ0 = 8;  // warp roles
 constexpr int EPI_WARPS = 4;
 constexpr int THREADS = (W_DQ0 + DQ_GROUP * DQ_GROUPS) * 32;
-constexpr int W_BYTES = 8 * NTILE * 8;
 constexpr int S_BYTES = 4 * NTILE * 2;
-constexpr int Z_BYTES = 4 * (NTILE / 8) * 4;
-constexpr int W_STAGE = W_BYTES + S_BYTES + Z_BYTES;  // 9472 bytes
+// one weight stage = 8 k16-rows x 128 columns of packed weights (4 bit: 8 KiB, 8 bit: 16 KiB) + up to 4 groups of
+// scales + their zero points (packed 32 / BITS per int32)
+template <int BITS>
+struct WStage {
+  static constexpr int PACK = 32 / BITS;
+  static constexpr int ROW_BYTES = NTILE * 2 * BITS;       // one k16-row of the slice: 16 x 128 weights
+  static constexpr int W_BYTES = 8 * ROW_BYTES;
+  static constexpr int Z_BYTES = 4 * (NTILE / PACK) * 4;
+  static constexpr int BYTES = W_BYTES + S_BYTES + Z_BYTES;  // 9472 bytes at 4 bit
+};
 
 // The work is the flattened list of (tile, k stage) pairs, tile = (column slice, batch tile); CTA b of G
 // takes the contiguous range [b*T/G, (b+1)*T/G) (stream-K): every SM gets the same number of stages
@@ -60,9 +67,10 @@ struct Params {
   unsigned long long* trace;  // development: per-stage clock64 stamps of CTA 0 (APH_GEMM_TRACE), else null
 };
 
-template <typename scalar_t, int MB>
+template <typename scalar_t, int MB, int BITS = 4>
 struct Cfg {
   static constexpr bool F16 = std::is_same<scalar_t, __half>::value;
+  static constexpr int W_BYTES = WStage<BITS>::W_BYTES, Z_BYTES = WStage<BITS>::Z_BYTES, W_STAGE = WStage<BITS>::BYTES;
   static constexpr int ACT_BOX = MB * 128;  // MB rows x 64 k, 128B-swizzled
   static constexpr int ACT_BYTES = 2 * ACT_BOX;
   static constexpr int TMEM_COLS = 512;
@@ -148,13 +156,14 @@ struct SegIter {
   }
 };
 
-template <typename scalar_t, int MB, bool HAS_ZP>
+template <typename scalar_t, int MB, bool HAS_ZP, int BITS = 4>
 __global__ void __launch_bounds__(THREADS, 1)
     marlin_w4a16_tc_kernel(const Params p, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmA,
                            const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUtensorMap tmZ) {
-  using C = Cfg<scalar_t, MB>;
+  using C = Cfg<scalar_t, MB, BITS>;
   constexpr bool F16 = C::F16;
   constexpr int SA = C::SA, SW = C::SW, NDBUF = C::NDBUF;
+  constexpr int W_BYTES = C::W_BYTES, W_STAGE = C::W_STAGE, PACK = 32 / BITS, ROW_BYTES = WStage<BITS>::ROW_BYTES;
   extern __shared__ uint8_t smem_raw[];
 
   const int tid = threadIdx.x, lane = tid & 31;
@@ -279,17 +288,17 @@ __global__ void __launch_bounds__(THREADS, 1)
     if (grouped) prefetch_tensormap(&tmS);
     if (HAS_ZP && grouped) prefetch_tensormap(&tmZ);
     const uint64_t pol_stream = policy_evict_first();  // weights are read once (or re-read from L2 by the next batch tile)
-    const uint32_t stage_tx = (uint32_t)(W_BYTES + gps * NTILE * 2 + (HAS_ZP ? gps * (NTILE / 8) * 4 : 0));
+    const uint32_t stage_tx = (uint32_t)(W_BYTES + gps * NTILE * 2 + (HAS_ZP ? gps * (NTILE / PACK) * 4 : 0));
     int it = 0;
     RingCursor<SW> ring;  // the producer handles every stage
     auto issue = [&](int sw, int slice, int ks) {
       const uint32_t dst = smem_base + C::W_OFF + sw * W_STAGE;
       const uint32_t fb = fullw_bar + sw * 8;
       mbar_expect_tx(fb, stage_tx);
-      tma_load_2d_hint(dst, &tmB, slice * NTILE, ks * 8, fb, pol_stream);
+      tma_load_2d_hint(dst, &tmB, slice * NTILE * (BITS / 4), ks * 8, fb, pol_stream);  // 8-byte words: 1 (2) per column at 4 (8) bit
       if (grouped) {
         tma_load_2d(dst + W_BYTES, &tmS, slice * NTILE, ks * gps, fb);
-        if constexpr (HAS_ZP) tma_load_2d(dst + W_BYTES + S_BYTES, &tmZ, slice * (NTILE / 8), ks * gps, fb);
+        if constexpr (HAS_ZP) tma_load_2d(dst + W_BYTES + S_BYTES, &tmZ, slice * (NTILE / PACK), ks * gps, fb);
       }
     };
 #ifdef APH_RING_FAULT
@@ -413,26 +422,46 @@ __global__ void __launch_bounds__(THREADS, 1)
     const int h = (dw >> 2) & 1;          // which half of the stage's k16-rows
     const int grp = dw >> 3;              // which stages: it & 1 == grp
     const int g = lane >> 2;
-    const uint32_t offW = (uint32_t)(C::W_OFF + (4 * h) * (NTILE * 8) + (qd >> 1) * 512 + lane * 16 + (qd & 1) * 8);
+    // this lane's words of a k16-row: 4 bit - one int32 per 16-column tile, the quadrant's two tiles are 8 bytes;
+    // 8 bit - two int32 per tile (gptq_marlin.cu:274-368), the quadrant's two tiles are 16 bytes
+    const uint32_t offW = (uint32_t)(C::W_OFF + (4 * h) * ROW_BYTES + (qd >> 1) * (ROW_BYTES / 2) + lane * (4 * BITS) + (qd & 1) * (2 * BITS));
     const uint32_t offS = (uint32_t)(C::W_OFF + W_BYTES + (qd >> 1) * 128 + g * 16 + (qd & 1) * 8);
-    const uint32_t offZ = (uint32_t)(C::W_OFF + W_BYTES + S_BYTES + (qd >> 1) * 32 + g * 4);
+    const uint32_t offZ = BITS == 4 ? (uint32_t)(C::W_OFF + W_BYTES + S_BYTES + (qd >> 1) * 32 + g * 4)
+                                    : (uint32_t)(C::W_OFF + W_BYTES + S_BYTES + (qd >> 1) * 64 + g * 8 + (qd & 1) * 4);
     const uint32_t a_lane = (uint32_t)(32 * qd) << 16;
     const int rpg_shift = grouped ? 31 - __clz(p.group_size / 16) : 3;  // log2(k16-rows per group): 1, 2, 3
     const bool two_groups = grouped && p.group_size == 32;              // a warp's 4 rows span two groups
 
-    uint32_t s_lo[2], s_hi[2], c_lo[2], c_hi[2];  // per 16-row tile: packed (x, x) for rows g and g + 8
-    c_lo[0] = c_lo[1] = c_hi[0] = c_hi[1] = C::MAGIC | 0x00080008u;
+    // what is subtracted from the spliced value, per 16-row tile for rows g and g + 8. 16-bit route (4 bit; 8 bit f16):
+    // packed pair (MAGIC + z, MAGIC + z). 8-bit bf16 goes through fp32 (2^23 + byte): the fp32 constant 2^23 + z.
+    constexpr bool VIA_F32 = BITS == 8 && !F16;
+    constexpr uint32_t BIAS = BITS == 4 ? 0x00080008u : 0x00800080u;  // the symmetric types: uint4b8, uint8b128
+    uint32_t s_lo[2], s_hi[2], c_lo[2], c_hi[2];
+    c_lo[0] = c_lo[1] = c_hi[0] = c_hi[1] = VIA_F32 ? 0x4B000080u : (C::MAGIC | BIAS);
     s_lo[0] = s_lo[1] = s_hi[0] = s_hi[1] = 0;
     auto set_zp = [&](uint32_t zword) {
-      // nibble e' of the packed word holds column block {0,2,4,6,1,3,5,7}[e']: tile j rows g / g+8 sit in
-      // nibbles j and j + 4
 #pragma unroll
       for (int tt = 0; tt < 2; ++tt) {
-        const int j = 2 * (qd & 1) + tt;
-        const uint32_t zl = (zword >> (4 * j)) & 0xf;
-        const uint32_t zh = (zword >> (4 * j + 16)) & 0xf;
-        c_lo[tt] = C::MAGIC | zl | (zl << 16);
-        c_hi[tt] = C::MAGIC | zh | (zh << 16);
+        uint32_t zl, zh;
+        if constexpr (BITS == 4) {
+          // nibble e' of the packed word holds column block {0,2,4,6,1,3,5,7}[e']: tile j rows g / g+8 sit in
+          // nibbles j and j + 4
+          const int j = 2 * (qd & 1) + tt;
+          zl = (zword >> (4 * j)) & 0xf;
+          zh = (zword >> (4 * j + 16)) & 0xf;
+        } else {
+          // 8 bit: four zero points per word, interleave {0,2,1,3}: this quadrant's word holds its two tiles, tile tt
+          // rows g / g+8 in bytes tt and tt + 2
+          zl = (zword >> (8 * tt)) & 0xff;
+          zh = (zword >> (8 * tt + 16)) & 0xff;
+        }
+        if constexpr (VIA_F32) {
+          c_lo[tt] = 0x4B000000u | zl;
+          c_hi[tt] = 0x4B000000u | zh;
+        } else {
+          c_lo[tt] = C::MAGIC | zl | (zl << 16);
+          c_hi[tt] = C::MAGIC | zh | (zh << 16);
+        }
       }
     };
     auto load_group = [&](uint32_t wstage, int gl) {
@@ -442,7 +471,22 @@ __global__ void __launch_bounds__(THREADS, 1)
       s_hi[0] = __byte_perm(sw0, sw0, 0x3232);
       s_lo[1] = __byte_perm(sw1, sw1, 0x1010);
       s_hi[1] = __byte_perm(sw1, sw1, 0x3232);
-      if constexpr (HAS_ZP) set_zp(lds32(wstage + offZ + gl * (NTILE / 8) * 4));
+      if constexpr (HAS_ZP) set_zp(lds32(wstage + offZ + gl * (NTILE / PACK) * 4));
+    };
+    // two bytes of an 8-bit word (b, b + 2) -> the exact 16-bit pair (q - z) [* s]
+    auto pair8 = [&](uint32_t word, int b, uint32_t cc, uint32_t ss) -> uint32_t {
+      if constexpr (VIA_F32) {
+        const float f0 = __uint_as_float(__byte_perm(word, 0x4B000000u, b == 0 ? 0x7650 : 0x7651)) - __uint_as_float(cc);
+        const float f1 = __uint_as_float(__byte_perm(word, 0x4B000000u, b == 0 ? 0x7652 : 0x7653)) - __uint_as_float(cc);
+        uint32_t v = __byte_perm(__float_as_uint(f0), __float_as_uint(f1), 0x7632);  // small integers: the top halves are exact bf16
+        if (grouped) {
+          __nv_bfloat162 t = __hmul2(*reinterpret_cast<__nv_bfloat162*>(&v), *reinterpret_cast<__nv_bfloat162*>(&ss));
+          v = *reinterpret_cast<uint32_t*>(&t);
+        }
+        return v;
+      } else {
+        return sub_mul2<F16>(__byte_perm(word, C::MAGIC, b == 0 ? 0x7250 : 0x7351), cc, ss, grouped);
+      }
     };
 
     int pending = -1;  // activation/TMEM slot whose stores are issued but not yet published to the MMA warp
@@ -459,7 +503,9 @@ __global__ void __launch_bounds__(THREADS, 1)
     APH_SEGMENTS {
       APH_SEG_VARS
       if (HAS_ZP && !grouped)
-        set_zp(*reinterpret_cast<const uint32_t*>(p.zp + ((int64_t)slice * (NTILE / 8) + (qd >> 1) * 8 + g) * 4));
+        set_zp(*reinterpret_cast<const uint32_t*>(
+            p.zp + (BITS == 4 ? ((int64_t)slice * (NTILE / 8) + (qd >> 1) * 8 + g) * 4
+                              : ((int64_t)slice * (NTILE / 4) + (qd >> 1) * 16 + g * 2 + (qd & 1)) * 4)));
 #pragma unroll 1
       for (int ks = k0; ks < k1; ++ks, ++it) {
         if ((it & 1) != grp) continue;
@@ -476,9 +522,14 @@ __global__ void __launch_bounds__(THREADS, 1)
         if (tr) p.trace[it * 8 + 5] = clock64();
 #endif
         const uint32_t wstage = smem_base + sw * W_STAGE;
-        uint32_t q[4][2];
+        uint32_t q[4][BITS / 2];  // 4 bit: one word per tile; 8 bit: two words per tile
 #pragma unroll
-        for (int i = 0; i < 4; ++i) lds64(wstage + offW + i * (NTILE * 8), q[i][0], q[i][1]);
+        for (int i = 0; i < 4; ++i) {
+          if constexpr (BITS == 4)
+            lds64(wstage + offW + i * ROW_BYTES, q[i][0], q[i][1]);
+          else
+            lds128(wstage + offW + i * ROW_BYTES, q[i][0], q[i][1], q[i][2], q[i][3]);
+        }
         // the previous stage's TMEM stores had the wait and the loads above to land: hand that slot to the MMA warps
         // before starting on this stage's arithmetic (publishing later would keep one more slot per group in limbo)
         if (pending >= 0) publish();
@@ -488,14 +539,22 @@ __global__ void __launch_bounds__(THREADS, 1)
           if (grouped && (i == 0 || (i == 2 && two_groups))) load_group(wstage, (4 * h + i) >> rpg_shift);
 #pragma unroll
           for (int tt = 0; tt < 2; ++tt) {
-            const uint32_t a0 = and_or(q[i][tt], 0x000f000fu, C::MAGIC);
-            const uint32_t a2 = and_or(q[i][tt] >> 4, 0x000f000fu, C::MAGIC);
-            const uint32_t a1 = and_or(q[i][tt] >> 8, 0x000f000fu, C::MAGIC);
-            const uint32_t a3 = and_or(q[i][tt] >> 12, 0x000f000fu, C::MAGIC);
-            a[tt][4 * i + 0] = sub_mul2<F16>(a0, c_lo[tt], s_lo[tt], grouped);
-            a[tt][4 * i + 1] = sub_mul2<F16>(a1, c_hi[tt], s_hi[tt], grouped);
-            a[tt][4 * i + 2] = sub_mul2<F16>(a2, c_lo[tt], s_lo[tt], grouped);
-            a[tt][4 * i + 3] = sub_mul2<F16>(a3, c_hi[tt], s_hi[tt], grouped);
+            if constexpr (BITS == 4) {
+              const uint32_t a0 = and_or(q[i][tt], 0x000f000fu, C::MAGIC);
+              const uint32_t a2 = and_or(q[i][tt] >> 4, 0x000f000fu, C::MAGIC);
+              const uint32_t a1 = and_or(q[i][tt] >> 8, 0x000f000fu, C::MAGIC);
+              const uint32_t a3 = and_or(q[i][tt] >> 12, 0x000f000fu, C::MAGIC);
+              a[tt][4 * i + 0] = sub_mul2<F16>(a0, c_lo[tt], s_lo[tt], grouped);
+              a[tt][4 * i + 1] = sub_mul2<F16>(a1, c_hi[tt], s_hi[tt], grouped);
+              a[tt][4 * i + 2] = sub_mul2<F16>(a2, c_lo[tt], s_lo[tt], grouped);
+              a[tt][4 * i + 3] = sub_mul2<F16>(a3, c_hi[tt], s_hi[tt], grouped);
+            } else {
+              // word 0 of a tile: row g, bytes (0, 2) = k low pair, (1, 3) = k high pair; word 1: row g + 8
+              a[tt][4 * i + 0] = pair8(q[i][2 * tt], 0, c_lo[tt], s_lo[tt]);
+              a[tt][4 * i + 2] = pair8(q[i][2 * tt], 1, c_lo[tt], s_lo[tt]);
+              a[tt][4 * i + 1] = pair8(q[i][2 * tt + 1], 0, c_hi[tt], s_hi[tt]);
+              a[tt][4 * i + 3] = pair8(q[i][2 * tt + 1], 1, c_hi[tt], s_hi[tt]);
+            }
           }
         }
         __syncwarp();

@@ -24,6 +24,7 @@ APH_DECL(32)
 APH_DECL(80)
 APH_DECL(96)
 APH_DECL(112)
+APH_DECL(120)
 APH_DECL(192)
 APH_DECL(256)
 #endif
@@ -31,49 +32,105 @@ APH_DECL(256)
 
 struct Split {
   int partition_tokens;
-  int num_partitions;
+  int num_partitions;  // grid z
+  int cluster_parts;   // partitions merged on chip by one thread-block cluster (1 = no cluster)
+  int out_partials() const { return num_partitions / cluster_parts; }  // partials per (sequence, head) in the workspace
 };
 
-// Partition choice (multiples of 256 tokens so that partitions start on stage and page boundaries for every block
-// size). Measured on B200 (tools/sweep_attention_split.py, profiles/r01_attention_split_sweep.log): a CTA costs about
-// (partition_tokens + 600) token-times, so few long partitions beat many short ones as long as the grid is not a
-// fractional number of waves. Rule: if the whole problem fits in ONE wave of CTAs (3 per SM) with partitions of at
-// least 512 tokens and fills at least 70 % of it, launch exactly that wave (long contexts at small batch: C5 24 us
-// instead of 39); otherwise aim at >= 4 waves so that the ragged last wave is a small fraction (C2: 4.6 waves).
-static Split choose_split(int num_seqs, int num_heads, int num_kv_heads, int max_seq_len) {
+// Split-K plan. A CTA streams one partition of one (sequence, kv head tile); 3 CTAs share an SM (`slots` = one wave).
+// Measured on B200 (tools/bench_attention.py, tools/sweep_attention_split.py; profiles/r02_attention_policy.jsonl,
+// r01_attention_split_sweep.log), in "token-times" (the time a CTA of a full wave needs per token, ~15 ns):
+//   * a grid that fits ONE wave costs about  partition_tokens + 600  (every CTA pays its start-up and merge once, nothing
+//     overlaps them), plus the merge: ~100 when the partitions of a (sequence, kv head) form one thread-block cluster
+//     and meet in shared memory, ~250 + 12 per cluster for clusters of 8 followed by the reduce kernel, ~500 for the reduce kernel alone;
+//   * a multi-wave grid costs about  (CTAs / slots, rounded up below 3 waves) x (partition_tokens + 370): start-up and tail of one CTA hide
+//     under the streaming of its neighbours, so short partitions are cheap - and clusters do NOT pay there (their CTAs
+//     are scheduled together and leave together: C2 107 us against 97 us), the partials go through the workspace.
+// The cheapest candidate wins. One-wave partitions are multiples of 64 tokens (4 warps x 16-token stages; a multiple
+// of every page size). A cluster of CP CTAs needs CP * ceil(heads per CTA / CP) rows in the kernel's receive buffer
+// (14 for head sizes up to 128, 8 above). APH_PA_CLUSTER (development): 0 = never use clusters, 1 = whenever the split
+// allows, 2 = as described.
+static Split choose_split(int num_seqs, int num_heads, int num_kv_heads, int head_size, int max_seq_len) {
   const int G = num_heads / num_kv_heads;
   const int tiles = (G + HEADS_PER_CTA - 1) / HEADS_PER_CTA;
   const int64_t units = (int64_t)num_seqs * num_kv_heads * tiles;
-  // development overrides (tools/sweep_attention_split.py): waves of CTAs aimed at, smallest partition
-  static const char* const e_w0 = getenv("APH_PA_WAVES");  // read once per process unless APH_DEV_ENV=1
-  static const char* const e_m0 = getenv("APH_PA_MIN_PART");
-  const char* const e_w = dev_env_live() ? getenv("APH_PA_WAVES") : e_w0;
-  const char* const e_m = dev_env_live() ? getenv("APH_PA_MIN_PART") : e_m0;
-  const int waves = e_w ? atoi(e_w) : 4;
-  const int min_part = e_m ? atoi(e_m) : 256;
   const int64_t slots = (int64_t)sm_count() * 3;
   const int msl = max_seq_len < 1 ? 1 : max_seq_len;
-  Split s;
-  if (e_w == nullptr && e_m == nullptr && units > 0 && units <= slots) {
-    const int64_t p_fit = slots / units;
-    int64_t pt = (msl + p_fit - 1) / p_fit;
+  // development overrides (tools/sweep_attention_split.py): waves of CTAs aimed at, smallest partition, cluster policy
+  static const char* const e_w0 = getenv("APH_PA_WAVES");  // read once per process unless APH_DEV_ENV=1
+  static const char* const e_m0 = getenv("APH_PA_MIN_PART");
+  static const char* const e_c0 = getenv("APH_PA_CLUSTER");
+  const char* const e_w = dev_env_live() ? getenv("APH_PA_WAVES") : e_w0;
+  const char* const e_m = dev_env_live() ? getenv("APH_PA_MIN_PART") : e_m0;
+  const char* const e_c = dev_env_live() ? getenv("APH_PA_CLUSTER") : e_c0;
+  const int waves = e_w ? atoi(e_w) : 4;
+  const int min_part = e_m ? atoi(e_m) : 256;
+  const int policy = e_c ? atoi(e_c) : 2;
+  const int gt = G < HEADS_PER_CTA ? G : HEADS_PER_CTA;
+  const int recv_slots = head_size <= 128 ? 14 : 8;  // Cfg::RECV_SLOTS
+  auto fits = [&](int cp) { return cp * ((gt + cp - 1) / cp) <= recv_slots; };
+
+  Split best{msl, 1, 1};
+  double best_cost = 1e30;
+  auto consider = [&](int pt, int np, int cp, double cost) {
+    if (cost < best_cost) {
+      best_cost = cost;
+      best = Split{pt, np, cp};
+    }
+  };
+  // ---- multi-wave candidate: aim at `waves` waves, every partition through the workspace ----
+  {
+    const int64_t target = slots * (waves > 0 ? waves : 4);
+    int64_t p_want = units > 0 ? (target + units - 1) / units : 1;
+    if (p_want < 1) p_want = 1;
+    int64_t pt = (msl + p_want - 1) / p_want;
     pt = ((pt + 255) / 256) * 256;
-    const int64_t np = (msl + pt - 1) / pt;
-    if (pt >= 512 && np > 1 && units * np * 10 >= slots * 7) {
-      s.partition_tokens = (int)pt;
-      s.num_partitions = (int)np;
-      return s;
+    if (pt < min_part) pt = (min_part + 255) / 256 * 256;
+    const int np = (int)((msl + pt - 1) / pt);
+    const double w = (double)units * np / (double)slots;
+    int cp = 1, z = np;
+    if (policy == 1 && np > 1) {  // development: clusters wherever the split allows
+      cp = np <= 8 ? np : 8;
+      while (!fits(cp)) ++cp;
+      z = (np + cp - 1) / cp * cp;
+    }
+    // few waves run in rounds (1.15 waves cost two), many waves flow
+    const double rounds = w <= 3.0 ? (double)(int64_t)(w + 0.999) : w;
+    consider((int)pt, z, cp, rounds * (double)(pt + (w <= 1.0 ? 600 : 370)) + (np > 1 ? 150.0 : 0.0));
+  }
+  // ---- one-wave candidates ----
+  if (e_w == nullptr && e_m == nullptr && units > 0 && units <= slots) {
+    const int max_np = (int)(slots / units);
+    for (int want = 1; want <= max_np && want <= 512; ++want) {
+      int64_t pt = (msl + want - 1) / want;
+      pt = ((pt + 63) / 64) * 64;
+      const int np = (int)((msl + pt - 1) / pt);
+      if ((int64_t)np * units > slots) continue;
+      if (np == 1) {
+        consider((int)pt, 1, 1, (double)pt + 600.0);
+        continue;
+      }
+      int cp = 1, z = np;
+      double merge = 500.0;
+      if (policy != 0) {
+        if (np <= 8) {
+          int c = np;
+          while (!fits(c)) ++c;
+          if ((int64_t)c * units <= slots) {
+            cp = c;
+            z = c;  // partitions that start beyond a sequence stay empty
+            merge = 100.0;
+          }
+        } else if ((int64_t)((np + 7) / 8 * 8) * units <= slots) {
+          cp = 8;
+          z = (np + 7) / 8 * 8;
+          merge = 250.0 + 12.0 * (z / 8);  // the reduce kernel walks one partial per cluster (C5 x 1: 16 partials 12.8 us, 32 partials 16.8 us)
+        }
+      }
+      consider((int)pt, z, cp, (double)pt + 600.0 + merge);
     }
   }
-  const int64_t target = slots * (waves > 0 ? waves : 4);
-  int64_t p_want = units > 0 ? (target + units - 1) / units : 1;
-  if (p_want < 1) p_want = 1;
-  int64_t pt = (msl + p_want - 1) / p_want;
-  pt = ((pt + 255) / 256) * 256;
-  if (pt < min_part) pt = (min_part + 255) / 256 * 256;
-  s.partition_tokens = (int)pt;
-  s.num_partitions = (int)((msl + pt - 1) / pt);
-  return s;
+  return best;
 }
 
 static int run(void* out, const void* query, const void* key_cache, const void* value_cache, int num_seqs,
@@ -93,13 +150,15 @@ static int run(void* out, const void* query, const void* key_cache, const void* 
   APH_CHECK(aligned16(key_cache) && aligned16(value_cache) && (kv_block_stride * esz) % 16 == 0 &&
                 (kv_head_stride * esz) % 16 == 0,
             APH_ERR_INVALID_ARGUMENT, "paged_attention: kv cache pages must be 16-byte aligned");
+  APH_CHECK(head_size % (16 / esz) == 0, APH_ERR_INVALID_ARGUMENT,
+            "paged_attention: head size %d is not a multiple of the %d elements of a key-cache chunk", head_size, 16 / esz);
   APH_CHECK(kv_head_stride == (int64_t)head_size * block_size, APH_ERR_INVALID_ARGUMENT,
             "paged_attention: kv cache must be contiguous within a (block, head) page");
   if (bs_vert_stride > 1)
     APH_CHECK(bs_block_size > 0, APH_ERR_INVALID_ARGUMENT, "paged_attention: blocksparse_block_size must be > 0");
   if (num_seqs == 0) return APH_OK;
 
-  const Split sp = choose_split(num_seqs, num_heads, num_kv_heads, max_seq_len);
+  const Split sp = choose_split(num_seqs, num_heads, num_kv_heads, head_size, max_seq_len);
   Params p;
   p.out = out;
   p.q = query;
@@ -116,7 +175,7 @@ static int run(void* out, const void* query, const void* key_cache, const void* 
   p.max_blocks_per_seq = max_num_blocks_per_seq;
   p.partition_tokens = sp.partition_tokens;
   p.num_partitions = sp.num_partitions;
-  p.cluster_parts = 1;
+  p.cluster_parts = sp.cluster_parts;
   p.q_stride = q_stride;
   p.out_stride = out_stride;
   p.kv_block_stride = kv_block_stride;
@@ -129,9 +188,9 @@ static int run(void* out, const void* query, const void* key_cache, const void* 
   p.bs_head_sliding_step = bs_head_sliding_step;
   p.part_o = nullptr;
   p.part_ml = nullptr;
-  if (sp.num_partitions > 1) {
-    const size_t n_o = (size_t)num_seqs * num_heads * sp.num_partitions * head_size;
-    const size_t need = n_o * 4 + (size_t)num_seqs * num_heads * sp.num_partitions * 8;
+  if (sp.out_partials() > 1) {
+    const size_t n_o = (size_t)num_seqs * num_heads * sp.out_partials() * head_size;
+    const size_t need = n_o * 4 + (size_t)num_seqs * num_heads * sp.out_partials() * 8;
     APH_CHECK(workspace != nullptr && workspace_bytes >= need && aligned16(workspace), APH_ERR_WORKSPACE,
               "paged_attention: workspace of %zu bytes needed, %zu given", need, workspace_bytes);
     p.part_o = (float*)workspace;
@@ -146,6 +205,7 @@ static int run(void* out, const void* query, const void* key_cache, const void* 
     case 80: return launch_pa_d80(p, dtype, kv_dtype, block_size, s);
     case 96: return launch_pa_d96(p, dtype, kv_dtype, block_size, s);
     case 112: return launch_pa_d112(p, dtype, kv_dtype, block_size, s);
+    case 120: return launch_pa_d120(p, dtype, kv_dtype, block_size, s);
     case 192: return launch_pa_d192(p, dtype, kv_dtype, block_size, s);
     case 256: return launch_pa_d256(p, dtype, kv_dtype, block_size, s);
 #endif
@@ -181,9 +241,9 @@ using namespace aphb200;
 extern "C" size_t aph_paged_attention_workspace_bytes(int num_seqs, int num_heads, int num_kv_heads, int head_size,
                                                       int max_seq_len) {
   if (num_seqs <= 0 || num_heads <= 0 || num_kv_heads <= 0 || head_size <= 0) return 0;
-  const pa::Split sp = pa::choose_split(num_seqs, num_heads, num_kv_heads, max_seq_len);
-  if (sp.num_partitions <= 1) return 0;
-  const size_t n = (size_t)num_seqs * num_heads * sp.num_partitions;
+  const pa::Split sp = pa::choose_split(num_seqs, num_heads, num_kv_heads, head_size, max_seq_len);
+  if (sp.out_partials() <= 1) return 0;
+  const size_t n = (size_t)num_seqs * num_heads * sp.out_partials();
   return n * head_size * 4 + n * 8;
 }
 

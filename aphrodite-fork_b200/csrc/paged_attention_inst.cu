@@ -1,5 +1,7 @@
 // One translation unit per head size (compiled with -DAPH_PA_HEAD_SIZE=<D>) so that the
 // template instantiations build in parallel. Defines launch_pa_d<D>().
+#include <algorithm>
+
 #include "paged_attention_kernel.cuh"
 
 #ifndef APH_PA_HEAD_SIZE
@@ -27,12 +29,22 @@ static int launch_one(const Params& p, cudaStream_t stream) {
   }
   const int G = p.num_heads / p.num_kv_heads;
   const int tiles = (G + HEADS_PER_CTA - 1) / HEADS_PER_CTA;
+  using std::min;
   dim3 grid(p.num_kv_heads * tiles, p.num_seqs, p.num_partitions);
-  APH_LAUNCH_PDL(kern, grid, dim3(C::NTHREADS), (size_t)C::SMEM_BYTES, stream, p);
-  if (p.num_partitions > 1) {
-    // the reduce grid is set up while the main kernel drains (it waits before reading the partials)
+  if (p.cluster_parts > 1 && p.cluster_parts * ((min(G, HEADS_PER_CTA) + p.cluster_parts - 1) / p.cluster_parts) > C::RECV_SLOTS)
+    return set_error(APH_ERR_INVALID_ARGUMENT, "paged_attention: cluster of %d partitions does not fit the merge buffer", p.cluster_parts);
+  {
+    const cudaError_t e = launch_pdl_cluster(kern, grid, dim3(C::NTHREADS), (size_t)C::SMEM_BYTES, stream, p.cluster_parts, p);
+    if (e != cudaSuccess) return set_error(APH_ERR_CUDA, "CUDA launch failed: %s", cudaGetErrorString(e));
+  }
+  const int n_out = p.num_partitions / p.cluster_parts;  // partials per (sequence, head) left in the workspace
+  if (n_out > 1) {
+    // second level: the reduce grid is set up while the main kernel drains (it waits before reading the partials)
+    Params pr = p;
+    pr.num_partitions = n_out;
+    pr.partition_tokens = p.partition_tokens * p.cluster_parts;
     APH_LAUNCH_PDL(paged_attention_reduce_kernel<scalar_t, D>, dim3(p.num_heads, p.num_seqs), dim3(D >= 128 ? 128 : 64), (size_t)0,
-                   stream, p, KV != APH_KV_AUTO);
+                   stream, pr, KV != APH_KV_AUTO);
   }
   return APH_OK;
 }
@@ -54,17 +66,19 @@ int APH_CAT(launch_pa_d, APH_PA_HEAD_SIZE)(const Params& p, int dtype, int kv_dt
   if (kv_dtype == APH_KV_AUTO) {
     if (dtype == APH_DT_BF16) return launch_bs<__nv_bfloat16, APH_KV_AUTO>(p, block_size, stream);
     if (dtype == APH_DT_F16) return launch_bs<__half, APH_KV_AUTO>(p, block_size, stream);
-    return set_error(APH_ERR_UNSUPPORTED, "paged_attention: float32 KV cache is not implemented on this path");
+    return launch_bs<float, APH_KV_AUTO>(p, block_size, stream);  // float32 cache (x = 4)
   }
-  if (kv_dtype == APH_KV_FP8_E4M3) {
-    if (dtype == APH_DT_BF16) return launch_bs<__nv_bfloat16, APH_KV_FP8_E4M3>(p, block_size, stream);
-    if (dtype == APH_DT_F16) return launch_bs<__half, APH_KV_FP8_E4M3>(p, block_size, stream);
-    return launch_bs<float, APH_KV_FP8_E4M3>(p, block_size, stream);
-  }
-  if (kv_dtype == APH_KV_FP8_E5M2) {
-    if (dtype == APH_DT_BF16) return launch_bs<__nv_bfloat16, APH_KV_FP8_E5M2>(p, block_size, stream);
-    if (dtype == APH_DT_F16) return launch_bs<__half, APH_KV_FP8_E5M2>(p, block_size, stream);
-    return launch_bs<float, APH_KV_FP8_E5M2>(p, block_size, stream);
+  if constexpr (APH_PA_HEAD_SIZE % 16 == 0) {  // an FP8 cache stores 16 elements per chunk
+    if (kv_dtype == APH_KV_FP8_E4M3) {
+      if (dtype == APH_DT_BF16) return launch_bs<__nv_bfloat16, APH_KV_FP8_E4M3>(p, block_size, stream);
+      if (dtype == APH_DT_F16) return launch_bs<__half, APH_KV_FP8_E4M3>(p, block_size, stream);
+      return launch_bs<float, APH_KV_FP8_E4M3>(p, block_size, stream);
+    }
+    if (kv_dtype == APH_KV_FP8_E5M2) {
+      if (dtype == APH_DT_BF16) return launch_bs<__nv_bfloat16, APH_KV_FP8_E5M2>(p, block_size, stream);
+      if (dtype == APH_DT_F16) return launch_bs<__half, APH_KV_FP8_E5M2>(p, block_size, stream);
+      return launch_bs<float, APH_KV_FP8_E5M2>(p, block_size, stream);
+    }
   }
   return set_error(APH_ERR_INVALID_ARGUMENT, "paged_attention: unsupported kv cache dtype %d", kv_dtype);
 }

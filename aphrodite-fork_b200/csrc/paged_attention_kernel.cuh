@@ -12,16 +12,21 @@ template <typename scalar_t, int KV, int D, int BS>
 struct Cfg {
   static constexpr int ESZ = (KV == APH_KV_AUTO) ? (int)sizeof(scalar_t) : 1;  // cache element bytes
   static constexpr bool FP8 = KV != APH_KV_AUTO;
-  static constexpr bool F16MMA = FP8 || std::is_same<scalar_t, __half>::value;
+  // float32 query with an "auto" cache: the cache holds float32 too (x = 4 per chunk). K and V are rounded to f16 in
+  // registers on their way to the MMA (11 significant bits; the reference computes this case in fp32 - the difference
+  // is ~5e-4 relative, inside its test's 1e-3 absolute bound for attention-sized values; |K|, |V| must fit f16)
+  static constexpr bool F32KV = (KV == APH_KV_AUTO) && std::is_same<scalar_t, float>::value;
+  static constexpr bool F16MMA = FP8 || F32KV || std::is_same<scalar_t, __half>::value;
   static constexpr int ST = BS > 16 ? BS : 16;  // tokens per pipeline stage
   static constexpr int SG = ST / 16;            // 16-token MMA groups per stage
   static constexpr int SP = ST / BS;            // cache pages per stage
   static constexpr int KPAGE = D * BS * ESZ;    // bytes of one K (or V) page of one kv head
   static constexpr int STAGE = 2 * SP * KPAGE;  // bytes per stage (K pages then V pages)
   static constexpr int NS = (16384 / STAGE) >= 2 ? ((16384 / STAGE) > 8 ? 8 : (16384 / STAGE)) : 2;
-  static constexpr int NWARPS = (STAGE * NS * 4 <= 160 * 1024) ? 4 : 2;
+  static constexpr int NWARPS = (STAGE * NS * 4 <= 160 * 1024) ? 4 : (STAGE * NS * 2 <= 200 * 1024 ? 2 : 1);
   static constexpr int NTHREADS = NWARPS * 32;
-  static constexpr int DP = D + 4;  // padded row of the cross-warp merge buffer (floats)
+  static constexpr int DPAD = (D + 15) / 16 * 16;  // head size 120: the MMAs run over 128, the last 8 are zero (Q) / discarded (O)
+  static constexpr int DP = DPAD + 4;  // padded row of the cross-warp merge buffer (floats)
   static constexpr int PIPE_BYTES = NWARPS * NS * STAGE;
   static constexpr int MERGE_BYTES = NWARPS * HEADS_PER_CTA * DP * 4;
   // cluster merge: rows a CTA receives from the partitions of its cluster, [slot][D] fp32 + (max, sum) per slot with
@@ -40,7 +45,8 @@ __global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar
   using C = Cfg<scalar_t, KV, D, BS>;
   constexpr bool F16 = C::F16MMA;
   constexpr int NWARPS = C::NWARPS, NS = C::NS, ST = C::ST, SG = C::SG, SP = C::SP, KPAGE = C::KPAGE;
-  constexpr int KS = D / 16;  // k-steps of Q K^T == m-tiles of P V
+  constexpr int KS = C::DPAD / 16;  // k-steps of Q K^T == m-tiles of P V
+  static_assert(D % 16 == 0 || !C::FP8, "an FP8 cache stores 16 elements per chunk: the head size must be a multiple of 16");
 
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ float m_s[NWARPS][HEADS_PER_CTA], l_s[NWARPS][HEADS_PER_CTA];
@@ -161,10 +167,11 @@ __global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar
     for (int ks = 0; ks < KS; ++ks) {
       const int d0 = C::FP8 ? 16 * ks + 4 * t : 16 * ks + 2 * t;
       const int d1 = C::FP8 ? d0 + 2 : d0 + 8;
-      qf[ks][0] = hv ? ScalarTraits<scalar_t>::to_float(qp[d0]) : 0.f;
-      qf[ks][1] = hv ? ScalarTraits<scalar_t>::to_float(qp[d0 + 1]) : 0.f;
-      qf[ks][2] = hv ? ScalarTraits<scalar_t>::to_float(qp[d1]) : 0.f;
-      qf[ks][3] = hv ? ScalarTraits<scalar_t>::to_float(qp[d1 + 1]) : 0.f;
+      const bool v0 = hv && (D % 16 == 0 || d0 < D), v1 = hv && (D % 16 == 0 || d1 < D);
+      qf[ks][0] = v0 ? ScalarTraits<scalar_t>::to_float(qp[d0]) : 0.f;
+      qf[ks][1] = v0 ? ScalarTraits<scalar_t>::to_float(qp[d0 + 1]) : 0.f;
+      qf[ks][2] = v1 ? ScalarTraits<scalar_t>::to_float(qp[d1]) : 0.f;
+      qf[ks][3] = v1 ? ScalarTraits<scalar_t>::to_float(qp[d1 + 1]) : 0.f;
       amax = fmaxf(amax, fmaxf(fmaxf(fabsf(qf[ks][0]), fabsf(qf[ks][1])), fmaxf(fabsf(qf[ks][2]), fabsf(qf[ks][3]))));
     }
     float qs = 1.f;
@@ -225,7 +232,25 @@ __global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar
       if (gs >= part_end) break;
       // ---------------- S^T = K Q^T ----------------
       float s[4] = {0.f, 0.f, 0.f, 0.f};
-      if constexpr (!C::FP8) {
+      if constexpr (C::F32KV) {
+        // chunks of 4 floats: element d of token ts sits at chunk d / 4, row ts, float d % 4
+        const int tsA = sg * 16 + g, tsB = tsA + 8;
+        const uint32_t baseA = stage_k + (tsA / BS) * KPAGE + (t >> 1) * (BS * 16) + (tsA % BS) * 16 + (t & 1) * 8;
+        const uint32_t baseB = stage_k + (tsB / BS) * KPAGE + (t >> 1) * (BS * 16) + (tsB % BS) * 16 + (t & 1) * 8;
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) {
+          uint32_t f[8];
+          lds64(baseA + (4 * ks) * (BS * 16), f[0], f[1]);
+          lds64(baseB + (4 * ks) * (BS * 16), f[2], f[3]);
+          lds64(baseA + (4 * ks + 2) * (BS * 16), f[4], f[5]);
+          lds64(baseB + (4 * ks + 2) * (BS * 16), f[6], f[7]);
+          uint32_t a[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) a[e] = pack2<true>(__uint_as_float(f[2 * e]), __uint_as_float(f[2 * e + 1]));
+          if (D % 16 != 0 && ks == KS - 1) a[2] = a[3] = 0u;
+          mma16816<F16>(s, a[0], a[1], a[2], a[3], qb[ks][0], qb[ks][1]);
+        }
+      } else if constexpr (!C::FP8) {
         const int mi = lane >> 3, r = lane & 7;
         const int ts = sg * 16 + r + (mi & 1) * 8;
         const uint32_t base = stage_k + (ts / BS) * KPAGE + (mi >> 1) * (BS * 16) + (ts % BS) * 16;
@@ -233,6 +258,7 @@ __global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar
         for (int ks = 0; ks < KS; ++ks) {
           uint32_t a0, a1, a2, a3;
           ldsm_x4(base + ks * (BS * 32), a0, a1, a2, a3);
+          if (D % 16 != 0 && ks == KS - 1) a2 = a3 = 0u;  // elements 120..127 do not exist: whatever lies there must not meet even a zero
           mma16816<F16>(s, a0, a1, a2, a3, qb[ks][0], qb[ks][1]);
         }
       } else {
@@ -301,7 +327,31 @@ __global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar
 
       // ---------------- O^T += V^T P^T ----------------
       const bool tail = gs + 16 > L;  // V of tokens >= L may hold anything (NaN): zero it
-      if constexpr (!C::FP8) {
+      if constexpr (C::F32KV) {
+        // V page [D][bs] floats: row d, tokens (2t, 2t+1) and (2t+8, 2t+9) of the group are two 8-byte loads
+        const int ts0 = sg * 16 + 2 * t, ts1 = ts0 + 8;
+        const uint32_t base0 = stage_v + (ts0 / BS) * KPAGE + g * (BS * 4) + (ts0 % BS) * 4;
+        const uint32_t base1 = stage_v + (ts1 / BS) * KPAGE + g * (BS * 4) + (ts1 % BS) * 4;
+        const int c0 = gs + 2 * t, c2 = c0 + 8;
+#pragma unroll
+        for (int mt = 0; mt < KS; ++mt) {
+          uint32_t f[8];
+          lds64(base0 + (16 * mt) * (BS * 4), f[0], f[1]);      // a0: row g
+          lds64(base0 + (16 * mt + 8) * (BS * 4), f[2], f[3]);  // a1: row g + 8
+          lds64(base1 + (16 * mt) * (BS * 4), f[4], f[5]);      // a2: row g, tokens + 8
+          lds64(base1 + (16 * mt + 8) * (BS * 4), f[6], f[7]);  // a3
+          if (tail) {
+            if (c0 >= L) f[0] = f[2] = 0u;
+            if (c0 + 1 >= L) f[1] = f[3] = 0u;
+            if (c2 >= L) f[4] = f[6] = 0u;
+            if (c2 + 1 >= L) f[5] = f[7] = 0u;
+          }
+          uint32_t a[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) a[e] = pack2<true>(__uint_as_float(f[2 * e]), __uint_as_float(f[2 * e + 1]));
+          mma16816<F16>(o_acc[mt], a[0], a[1], a[2], a[3], pb0, pb1);
+        }
+      } else if constexpr (!C::FP8) {
         const int mi = lane >> 3, r = lane & 7;
         const int ts = sg * 16 + (mi >> 1) * 8;
         const uint32_t base = stage_v + (ts / BS) * KPAGE + (r + (mi & 1) * 8) * (BS * 2) + (ts % BS) * 2;

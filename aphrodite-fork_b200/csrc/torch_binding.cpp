@@ -385,8 +385,9 @@ torch::Tensor gptq_marlin_gemm(torch::Tensor& a, torch::Tensor& b_q_weight, torc
   int64_t lda = a.stride(0);
   torch::Tensor a_tmp;
   if (g_idx.numel() > 0) {
-    TORCH_CHECK(is_k_full, op, ": act-order with a partial K (row-parallel shards, is_k_full = False) is not implemented");
     TORCH_CHECK(b_scales.size(0) > 1, "For act_order, num_groups must be > 1");
+    TORCH_CHECK(g_idx.is_cuda() && g_idx.scalar_type() == at::ScalarType::Int && g_idx.is_contiguous(), op,
+                ": g_idx must be a contiguous int32 tensor on the device");
     TORCH_CHECK(perm.is_cuda() && perm.scalar_type() == at::ScalarType::Int && perm.is_contiguous(), op,
                 ": perm must be a contiguous int32 tensor on the device");
     a_tmp = torch::empty({size_m, size_k}, a.options());
@@ -395,7 +396,10 @@ torch::Tensor gptq_marlin_gemm(torch::Tensor& a, torch::Tensor& b_q_weight, torc
     a_ptr = a_tmp.data_ptr();
     lda = size_k;
   }
-  const int st = aph_gptq_marlin_gemm(c.data_ptr(), a_ptr, b_q_weight.data_ptr(), b_scales.data_ptr(), zp, nullptr,
+  // rows sorted by group AND the whole K here (is_k_full): the plain grouped kernels serve it. A row-parallel shard
+  // (is_k_full = False) keeps its per-row group index: the act-order kernel (marlin_actorder.cuh).
+  const int32_t* g_ptr = (g_idx.numel() > 0 && !is_k_full) ? g_idx.data_ptr<int32_t>() : nullptr;
+  const int st = aph_gptq_marlin_gemm(c.data_ptr(), a_ptr, b_q_weight.data_ptr(), b_scales.data_ptr(), zp, g_ptr,
                                       nullptr, workspace.data_ptr<int32_t>(), workspace.numel(), b_q_type_id, size_m,
                                       size_n, size_k, lda, b_scales.size(0), is_k_full, has_zp,
                                       use_atomic_add, use_fp32_reduce, is_zp_float, dt, sptr, sbytes, stream_of());

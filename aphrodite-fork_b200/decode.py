@@ -23,7 +23,8 @@ import torch
 
 from . import _custom_ops as ops
 from .paged_attn import PagedAttention
-from .tp import MarlinShard, TPGroup, shard_heads, verify_marlin_supports_shape, marlin_make_workspace
+from .tp import (MarlinShard, TPGroup, marlin_make_workspace, shard_heads, shard_marlin_weight,
+                 verify_marlin_supports_shape)
 
 SCALAR_TYPE_UINT4B8 = 1125899907892224  # kernels/core/scalar_type.hpp:100-138
 
@@ -110,6 +111,49 @@ class DecodeLayer:
         ln = lambda: (1.0 + 0.1 * torch.randn(cfg.hidden, device=device, generator=gen)).to(cfg.dtype)
         self.input_layernorm, self.post_attention_layernorm = ln(), ln()
 
+    @classmethod
+    def shard_of(cls, full: "DecodeLayer", tp: TPGroup) -> "DecodeLayer":
+        """This rank's shard of an UNSHARDED layer, cut the way the reference cuts a checkpoint (linear.py:474-484 column
+        parallel with q / k / v and gate / up split separately, :1279-1283 row parallel; llama.py:118-127 heads): the
+        sharded step must reproduce the unsharded one up to the summation order of the all-reduce."""
+        cfg, t, r = full.cfg, tp.world_size, tp.rank
+        self = cls.__new__(cls)
+        self.cfg, self.tp = cfg, tp
+        self.h, self.kvh = shard_heads(cfg.num_heads, cfg.num_kv_heads, t)
+        d, g = cfg.head_size, cfg.group_size
+        self.q_size, self.kv_size = self.h * d, self.kvh * d
+        kv_rank = r * cfg.num_kv_heads // t  # kv heads are replicated once t exceeds their number
+
+        def columns(w: MarlinShard, c0: int, c1: int) -> MarlinShard:  # a block of output columns (multiples of 64)
+            return MarlinShard(w.q_weight[:, 2 * c0:2 * c1].contiguous(), w.scales[:, c0:c1].contiguous(), None, w.size_k,
+                               c1 - c0, g, False)
+
+        def column_parallel(blocks) -> MarlinLinear:  # [(block, parts, part index)] -> this rank's columns, concatenated
+            sh = [shard_marlin_weight(b.q_weight, b.scales, None, b.size_k, b.size_n, g, parts, idx, "column") for b, parts, idx in blocks]
+            return MarlinLinear(MarlinShard(torch.cat([x.q_weight for x in sh], 1).contiguous(), torch.cat([x.scales for x in sh], 1).contiguous(),
+                                            None, sh[0].size_k, sum(x.size_n for x in sh), g, False))
+
+        def row_parallel(w: MarlinShard) -> MarlinLinear:
+            return MarlinLinear(shard_marlin_weight(w.q_weight, w.scales, None, w.size_k, w.size_n, g, t, r, "row"))
+
+        fq, fkv = full.q_size, full.kv_size
+        wq = full.qkv.w
+        kv_parts = min(t, cfg.num_kv_heads)
+        self.qkv = column_parallel([(columns(wq, 0, fq), t, r), (columns(wq, fq, fq + fkv), kv_parts, kv_rank),
+                                    (columns(wq, fq + fkv, fq + 2 * fkv), kv_parts, kv_rank)])
+        self.o = row_parallel(full.o.w)
+        wg, inter = full.gate_up.w, cfg.intermediate
+        self.gate_up = column_parallel([(columns(wg, 0, inter), t, r), (columns(wg, inter, 2 * inter), t, r)])
+        self.down = row_parallel(full.down.w)
+        k0 = kv_rank * self.kvh
+        kc = full.key_cache[:, k0:k0 + self.kvh].contiguous()
+        vc = full.value_cache[:, k0:k0 + self.kvh].contiguous()
+        self.kv_cache = torch.stack([kc.reshape(kc.shape[0], -1), vc.reshape(vc.shape[0], -1)]).contiguous()
+        self.key_cache, self.value_cache = PagedAttention.split_kv_cache(self.kv_cache, self.kvh, d)
+        self.k_scale, self.v_scale, self.scale = full.k_scale, full.v_scale, full.scale
+        self.input_layernorm, self.post_attention_layernorm = full.input_layernorm, full.post_attention_layernorm
+        return self
+
     def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor], positions, cos_sin_cache, slot_mapping,
                 block_tables, seq_lens, max_seq_len: int):
         """modeling/models/llama.py:270-292: returns (mlp output, residual stream)."""
@@ -168,6 +212,20 @@ class DecodeModel:
         self.cos_sin_cache = torch.cat((freqs.cos(), freqs.sin()), dim=-1).to(cfg.dtype)
         self.out = torch.empty_like(self.x)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
+
+    @classmethod
+    def shard_of(cls, full: "DecodeModel", tp: TPGroup) -> "DecodeModel":
+        """The tensor-parallel model whose ranks together hold exactly `full` (an unsharded model on this device)."""
+        self = cls.__new__(cls)
+        for k in ("cfg", "batch", "ctx", "block_tables", "seq_lens", "slot_mapping", "x", "norm", "positions", "cos_sin_cache"):
+            setattr(self, k, getattr(full, k))
+        self.tp = tp
+        if tp.world_size > 1 and tp.custom is None and full.x.is_cuda:
+            tp.enable_custom_all_reduce(full.x.device)
+        self.layers = [DecodeLayer.shard_of(l, tp) for l in full.layers]
+        self.out = torch.empty_like(full.x)
+        self.graph = None
+        return self
 
     def _forward(self) -> None:
         x, residual = self.x.clone(), None  # the layers work in place on the residual stream

@@ -145,6 +145,13 @@ class TPGroup:
         self.custom = None
         self.custom_error: Optional[str] = None
 
+    @classmethod
+    def single(cls) -> "TPGroup":
+        """A group of one rank whatever torch.distributed says (the unsharded model next to a sharded one)."""
+        g = cls.__new__(cls)
+        g.group, g.world_size, g.rank, g.custom, g.custom_error = None, 1, 0, None, None
+        return g
+
     def enable_custom_all_reduce(self, device, max_size: int = 8 * 1024 * 1024) -> bool:
         """Set up the peer-memory all-reduce; returns False (and keeps NCCL) when the world size or the platform does
         not support it - the reason is kept in `custom_error`."""

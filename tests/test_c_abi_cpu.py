@@ -104,7 +104,5 @@ def test_argument_checks_of_the_next_row_entry_points():
 def test_noalloc_attention_entry_point_rejects_oversized_problems_on_the_host():
     """aph_paged_attention_v1_noalloc (static device scratch, no allocation): the size check is host-side."""
     from test_zz_no_alloc import reject_check
-    lib = _lib()
-    lib.aph_b200_last_error.restype = ctypes.c_char_p
-    lib.aph_paged_attention_workspace_bytes.restype = ctypes.c_size_t
-    reject_check(lib)
+    _lib()
+    reject_check()

@@ -169,8 +169,8 @@ def test_paged_attention_golden_reference_cpu():
     for ci in range(int(g["num_cases"][0])):
         S, H, KVH, D, max_len, dtc, alibi, ver, nb = [int(v) for v in g[f"a{ci}_meta"]]
         dt = DT[dtc]
-        if dt == torch.float32 or (not FULL and D not in (64, 128)):
-            continue  # f32 KV cache: not implemented on this path (raises, see test below)
+        if not FULL and D not in (64, 128):
+            continue
         x = 16 // torch.tensor([], dtype=dt).element_size()
         sc = float(D) ** -0.5
         q = synth.tensor((S, H, D), 200 + ci, dt, sc).cuda()
@@ -202,13 +202,12 @@ def test_paged_attention_errors():
     with pytest.raises(RuntimeError):
         A.ops.paged_attention_v1(out, q, kc, vc, 8, 1.0, bt, sl, 24, 1, None, "auto", one, one)
     q120 = torch.zeros(1, 8, 120, dtype=torch.bfloat16, device=dev)
+    kc8 = torch.zeros(4, 8, 120 * 16, dtype=torch.uint8, device=dev)
+    with pytest.raises(RuntimeError):  # an FP8 cache stores 16 elements per chunk: head size 120 cannot be laid out
+        A.ops.paged_attention_v1(torch.empty_like(q120), q120, kc8, kc8, 8, 1.0, bt, sl, 16, 1, None, "fp8", one, one)
+    q100 = torch.zeros(1, 8, 100, dtype=torch.bfloat16, device=dev)
     with pytest.raises(RuntimeError):
-        A.ops.paged_attention_v1(torch.empty_like(q120), q120, kc, vc, 8, 1.0, bt, sl, 16, 1, None, "auto", one, one)
-    qf = torch.zeros(1, 8, 128, dtype=torch.float32, device=dev)
-    kcf = torch.zeros(4, 8, 32, 16, 4, dtype=torch.float32, device=dev)
-    vcf = torch.zeros(4, 8, 128, 16, dtype=torch.float32, device=dev)
-    with pytest.raises(RuntimeError):
-        A.ops.paged_attention_v1(torch.empty_like(qf), qf, kcf, vcf, 8, 1.0, bt, sl, 16, 1, None, "auto", one, one)
+        A.ops.paged_attention_v1(torch.empty_like(q100), q100, kc, vc, 8, 1.0, bt, sl, 16, 1, None, "auto", one, one)
 
 
 def test_paged_attention_cuda_graph_capture():
@@ -233,3 +232,87 @@ def test_paged_attention_cuda_graph_capture():
         gph.replay()
         st.synchronize()
     check_close(out, ref64, torch.bfloat16, 1e-2, "cuda graph replay")
+
+
+def _full_size_case(S, H, KVH, D, ctx, kv, seed, ragged_tail=True):
+    """Full-size problems (BASELINE configs): the FP8 cache is drawn directly as bytes (|x| < 1 in either format) with
+    a seeded CPU generator - the hash generator's float64 staging would need gigabytes here."""
+    bs = 16
+    g = torch.Generator().manual_seed(seed)
+    nb = S * ctx // bs
+    q = ((torch.rand(S, H, D, generator=g) * 2 - 1) * D ** -0.5).to(torch.bfloat16)
+    draw = lambda shape: (torch.randint(0, 0x38, shape, dtype=torch.uint8, generator=g)
+                          + 128 * torch.randint(0, 2, shape, dtype=torch.uint8, generator=g))
+    kc = draw((nb, KVH, D // 16, bs, 16))
+    vc = draw((nb, KVH, D, bs))
+    bt = torch.randperm(nb, generator=g).to(torch.int32).reshape(S, ctx // bs)
+    lens = [ctx] * S
+    if ragged_tail and S >= 4:
+        lens[1], lens[2], lens[3] = 1, ctx - 17, ctx // 2 + 5
+    return q, kc, vc, bt, torch.tensor(lens, dtype=torch.int32)
+
+
+@pytest.mark.parametrize("version", [1, 2])
+def test_paged_attention_c2_full_geometry(version):
+    """BASELINE config 2 as benchmarked: 64 sequences x 4096 context, 32 q / 8 kv heads, d 128, FP8-E4M3 KV, block 16."""
+    A = _A()
+    S, H, KVH, D, ctx = 64, 32, 8, 128, 4096
+    q, kc, vc, bt, sl = _full_size_case(S, H, KVH, D, ctx, "fp8", 1001)
+    ref64, _ = oracle.paged_attention(q, kc, vc, KVH, D ** -0.5, bt, sl, 16, kv_cache_dtype="fp8")
+    dev = "cuda"
+    one = torch.tensor(1.0, device=dev)
+    out = torch.full((S, H, D), float("nan"), dtype=torch.bfloat16, device=dev)
+    args = (q.to(dev), kc.to(dev), vc.to(dev), KVH, D ** -0.5, bt.to(dev), sl.to(dev), 16, ctx, None, "fp8", one, one)
+    if version == 1:
+        A.ops.paged_attention_v1(out, *args)
+    else:
+        P = ctx // 512
+        es = torch.empty(S, H, P, dtype=torch.float32, device=dev)
+        A.ops.paged_attention_v2(out, es, torch.empty_like(es), torch.empty(S, H, P, D, dtype=torch.bfloat16, device=dev), *args)
+    check_close(out, ref64, torch.bfloat16, 1e-2, f"C2 full geometry v{version}")
+
+
+@pytest.mark.parametrize("S", [1, 8])
+def test_paged_attention_c5_long_context(S):
+    """BASELINE config 5 per GPU: 8 q / 1 kv heads (Qwen2-72B at TP 8), 32 768 context, FP8-E5M2 KV."""
+    A = _A()
+    H, KVH, D, ctx = 8, 1, 128, 32768
+    q, kc, vc, bt, sl = _full_size_case(S, H, KVH, D, ctx, "fp8_e5m2", 1005)
+    ref64, _ = oracle.paged_attention(q, kc, vc, KVH, D ** -0.5, bt, sl, 16, kv_cache_dtype="fp8_e5m2")
+    dev = "cuda"
+    one = torch.tensor(1.0, device=dev)
+    out = A.PagedAttention.forward_decode(q.to(dev), kc.to(dev), vc.to(dev), bt.to(dev), sl.to(dev), ctx, "fp8_e5m2", KVH,
+                                          D ** -0.5, None, one, one)
+    check_close(out, ref64, torch.bfloat16, 1e-2, f"C5 x{S}")
+
+
+def test_paged_attention_tp8_shard_of_c2_and_c4():
+    """One rank's shard at TP 8: 4 q / 1 kv heads (C2 sharded, bench.py --gpus 8) and 8 q / 1 kv heads (C4), 64 x 4096."""
+    A = _A()
+    dev = "cuda"
+    one = torch.tensor(1.0, device=dev)
+    for H in (4, 8):
+        q, kc, vc, bt, sl = _full_size_case(64, H, 1, 128, 4096, "fp8", 1010 + H)
+        ref64, _ = oracle.paged_attention(q, kc, vc, 1, 128 ** -0.5, bt, sl, 16, kv_cache_dtype="fp8")
+        out = A.PagedAttention.forward_decode(q.to(dev), kc.to(dev), vc.to(dev), bt.to(dev), sl.to(dev), 4096, "fp8", 1, 128 ** -0.5,
+                                              None, one, one)
+        check_close(out, ref64, torch.bfloat16, 1e-2, f"TP8 shard H{H}")
+
+
+@pytest.mark.skipif(not FULL, reason="fast build has only head sizes 64/128")
+@pytest.mark.parametrize("version", [1, 2])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+def test_paged_attention_head_size_120(version, dtype):
+    # paged_attention_v1.cu:119-120 lists head size 120 (15 chunks of 8 16-bit elements / 30 chunks of 4 floats)
+    run_case(5, 16, 4, 120, 16, ragged(5, 900, 120), dtype, "auto", seed=120, version=version)
+    run_case(3, 8, 8, 120, 8, [1, 40, 333], dtype, "auto", seed=121, version=version, alibi=True)
+
+
+@pytest.mark.parametrize("version", [1, 2])
+@pytest.mark.parametrize("D,bs", [(64, 16), (128, 16), (128, 32), (80, 8), (256, 16)])
+def test_paged_attention_float32_cache(version, D, bs):
+    # test_attention.py:117-326 sweeps dtype = float with kv_cache_dtype "auto": query, cache and output in float32
+    if not FULL and (D not in (64, 128) or bs != 16):
+        pytest.skip("fast build")
+    run_case(4, 16, 4, D, bs, ragged(4, 700, D + bs), torch.float32, "auto", seed=200 + D, version=version)
+    run_case(2, 8, 1, D, bs, [2100, 17], torch.float32, "auto", seed=201 + D, version=version, q_strided=True)

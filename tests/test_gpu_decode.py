@@ -111,7 +111,18 @@ def _nccl_worker(rank, world, port, q):
         same = bool(torch.equal(out, ref))
         model.capture()
         g = model.step().float()
-        res = (rank, same, bool(torch.isfinite(out).all()), bool(torch.allclose(g, out, rtol=2e-2, atol=1e-3)))
+        # against the UNSHARDED model: every rank builds the same full model (same seed), steps it alone, then steps its
+        # shard of that model with the other ranks; a sharding mistake that is consistent across ranks shows up here
+        full = DecodeModel(cfg, batch=8, ctx=200, tp=TPGroup.single(), device=f"cuda:{rank}", seed=5)
+        sharded = DecodeModel.shard_of(full, TPGroup())
+        want = full.step().float()
+        got = sharded.step().float()
+        rel = float((got - want).abs().max() / want.abs().max())
+        kv_ok = all(torch.equal(ls.key_cache, lf.key_cache[:, rank * ls.kvh:(rank + 1) * ls.kvh])
+                    and torch.equal(ls.value_cache, lf.value_cache[:, rank * ls.kvh:(rank + 1) * ls.kvh])
+                    for ls, lf in zip(sharded.layers[:1], full.layers[:1]))  # layer 0 sees identical inputs: cache writes bit-equal
+        res = (rank, same, bool(torch.isfinite(out).all()), bool(torch.allclose(g, out, rtol=2e-2, atol=1e-3)), rel, kv_ok)
+        del full, sharded
         # the captured graph holds the communicator: drop it before the group is torn down
         model.graph = None
         del model
@@ -137,7 +148,11 @@ def test_tensor_parallel_decode_step_over_nccl():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    assert got == [(0, True, True, True), (1, True, True, True)]
+    for r, res in enumerate(got):
+        assert res[:4] == (r, True, True, True), res
+        # sharded vs unsharded step: same weights, same KV, only the all-reduce's summation order differs (bf16 hidden states)
+        assert res[4] < 3e-2, f"rank {r}: tensor-parallel step differs from the unsharded model by {res[4]:.3e} of max|ref|"
+        assert res[5], f"rank {r}: the shard's layer-0 cache write differs from the unsharded model's"
 
 
 def _ar_worker(rank, world, port, q):

@@ -63,15 +63,15 @@ def quantized(K, N, bits, gs, zp, dtype, seed):
     return _cache[key]
 
 
-def case(M, K, N, gs, dtype, zp=False, seed=1, lda_pad=0, a_shift=0.0, a_scale=1.0, **kw):
-    w_ref, b, s, bz = quantized(K, N, 4, gs, zp, dtype, seed)
+def case(M, K, N, gs, dtype, zp=False, seed=1, lda_pad=0, a_shift=0.0, a_scale=1.0, bits=4, **kw):
+    w_ref, b, s, bz = quantized(K, N, bits, gs, zp, dtype, seed)
     a_full = (a_shift + synth.tensor((M, K + lda_pad), seed + 100, torch.float64, a_scale)).to(dtype)
     a = a_full[:, :K]
     ref = oracle.gemm(a.contiguous(), w_ref)
     a_d = a_full.cuda()[:, :K]
-    out = run_gemm(a_d, b, s, bz, M, N, K, 4, zp, **kw)
+    out = run_gemm(a_d, b, s, bz, M, N, K, bits, zp, **kw)
     assert out.shape == (M, N) and out.dtype == dtype
-    return check(out, ref, dtype, f"M{M} K{K} N{N} g{gs} {dtype} zp{zp}")
+    return check(out, ref, dtype, f"M{M} K{K} N{N} g{gs} {dtype} zp{zp} {bits}bit")
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
@@ -131,6 +131,18 @@ def test_gptq_marlin_gemm_activations_with_a_mean(M, gs, zp, dtype):
     case(M, 14336, 128, gs, dtype, zp=zp, seed=42, a_shift=1.0, a_scale=0.5)
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("gs,zp", [(-1, False), (32, False), (64, True), (128, False), (128, True), (-1, True)])
+@pytest.mark.parametrize("M", [1, 16, 33, 64, 300])
+def test_gptq_marlin_gemm_8bit_weights(M, gs, zp, dtype):
+    # uint8b128 (GPTQ 8 bit) and uint8 + zero points, reference test sweep test_marlin_gemm.py:181-254 (quant types
+    # uint4b8 AND uint8b128); dequant gptq_marlin.cu:274-368
+    case(M, 512, 256, gs, dtype, zp=zp, seed=51, bits=8)
+    case(M, 1024, 128, gs, dtype, zp=zp, seed=52, bits=8)
+    if M in (1, 64):
+        case(M, 4096, 4096, gs, dtype, zp=zp, seed=53, bits=8)
+
+
 def test_gptq_marlin_gemm_repeated_calls_leave_workspace_clean():
     # back-to-back launches share the lock buffer (arrival counters) and the scratch: results must not depend on history
     outs = []
@@ -181,16 +193,16 @@ def test_gptq_marlin_gemm_golden_reference_python():
     g = np.load(os.path.join(os.path.dirname(__file__), "golden", "marlin_golden.npz"))
     for ci in range(int(g["num_cases"][0])):
         K, N, bits, gs, zp, dtc = [int(v) for v in g[f"c{ci}_meta"]]
-        if bits != 4:
-            continue
         dt = DT[dtc]
+        if bits == 8 and N % 128 != 0:
+            continue  # 8-bit weights run on the 128-column tensor-memory kernel only
         w_ref = torch.from_numpy(g[f"c{ci}_w_ref"]).view(dt)
         b = torch.from_numpy(g[f"c{ci}_b_q_weight"])
         s = torch.from_numpy(g[f"c{ci}_b_scales"]).view(dt)
         bz = torch.from_numpy(g[f"c{ci}_b_zeros"]) if zp else None
         for M in (1, 16, 37):
             a = synth.tensor((M, K), 900 + ci + M, dt, 1.0)
-            out = run_gemm(a.cuda(), b, s, bz, M, N, K, 4, bool(zp))
+            out = run_gemm(a.cuda(), b, s, bz, M, N, K, bits, bool(zp))
             check(out, oracle.gemm(a, w_ref), dt, f"golden {ci} M{M}")
 
 

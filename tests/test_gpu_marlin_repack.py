@@ -116,5 +116,45 @@ def test_act_order_gemm_full_k(m, dtype):
     if ref is not None:
         rc = ref.gptq_marlin_gemm(*args)
         assert float((c.float() - rc.float()).abs().max()) <= 1e-2 * float(rc.float().abs().max())
-    with pytest.raises(RuntimeError, match="partial K"):
-        A.ops.gptq_marlin_gemm(*args[:11], False, *args[12:])
+    # the same call with is_k_full = False (what a caller passes for any row-parallel shard) takes the act-order kernel
+    c2 = A.ops.gptq_marlin_gemm(*args[:11], False, *args[12:])
+    assert float((c2.cpu().double() - want).abs().max()) <= 2e-2 * float(want.abs().max())
+
+
+@pytest.mark.parametrize("m", [1, 16, 33, 300])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("tp,rank", [(2, 1), (4, 2)])
+def test_act_order_gemm_row_parallel_shard(m, dtype, tp, rank):
+    """The row-parallel shard of a desc_act checkpoint (is_k_full = False; marlin_utils.py:176-185, gptq_marlin.py): the
+    rank holds K / tp shuffled rows with THEIR slice of g_idx and the scale table of the whole weight; rows are sorted
+    by group inside the shard (marlin_sort_g_idx), groups start and end anywhere. Truth = a_shard @ (those rows of w_ref);
+    also compared with the reference CUDA kernel when it is built (gptq_marlin.cu:921-985,1280-1300)."""
+    k, n, gs = 2048, 512, 128
+    g = torch.Generator().manual_seed(100 + m + tp)
+    w = torch.randn(k, n, generator=g).to(dtype)
+    w_ref, bq, s = mf.marlin_quantize(w, 4, gs)[:3]       # s: Marlin-permuted scales of the whole weight
+    q = mf.unpack_weights(bq.numpy(), k, n, 4)
+    rand_perm = torch.randperm(k, generator=g)
+    g_idx = (torch.arange(k) // gs)[rand_perm].to(torch.int32)
+    kl = k // tp
+    rows = slice(rank * kl, (rank + 1) * kl)
+    g_idx_l = g_idx[rows]
+    w_l = w_ref[rand_perm][rows]
+    checkpoint_l = mf.gptq_pack(q[rand_perm.numpy()][rows], 4)
+    sort_indices = torch.argsort(g_idx_l, stable=True).to(torch.int32)
+    g_idx_sorted = g_idx_l[sort_indices.long()].contiguous()
+    b = A.ops.gptq_marlin_repack(_dev(checkpoint_l), sort_indices.to(DEV), kl, n, 4)
+    a = torch.randn(m, kl, generator=g).to(dtype).to(DEV)
+    ws = torch.zeros(148 * 64, dtype=torch.int32, device=DEV)
+    empty = torch.empty(0, dtype=torch.int32, device=DEV)
+    args = (a, b, s.to(DEV), empty, g_idx_sorted.to(DEV), sort_indices.to(DEV), ws, mf.UINT4B8, m, n, kl, False, False, False, True, False)
+    c = A.ops.gptq_marlin_gemm(*args)
+    want = a.float().cpu().double() @ w_l.double()
+    err = (c.cpu().double() - want).abs()
+    assert float(err.mean() / want.abs().mean()) < 5e-3
+    assert float(err.max()) <= (1e-2 if dtype == torch.bfloat16 else 2e-3) * float(want.abs().max())
+    assert int(ws.abs().max()) == 0
+    ref = oracle.refcuda()
+    if ref is not None:
+        rc = ref.gptq_marlin_gemm(*args)
+        assert float((c.float() - rc.float()).abs().max()) <= 1e-2 * float(rc.float().abs().max())

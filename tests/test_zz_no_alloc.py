@@ -3,11 +3,18 @@ the call) against aph_paged_attention_v1 with a caller workspace, both called th
 in a row. The entry point has no counterpart in the reference. This file
 is named so that pytest collects it last."""
 import ctypes
+import os
+import subprocess
+import sys
 
 import pytest
 import torch
 
-from helpers import RTOL, make_attention_case
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for _p in (ROOT, os.path.join(ROOT, "tests", "golden")):  # also runs as a script (reject-child), without conftest.py
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+from helpers import RTOL, make_attention_case  # noqa: E402
 
 pytestmark = pytest.mark.gpu
 MAX_SCRATCH = 16 << 20  # APH_PA_NOALLOC_MAX_SCRATCH_BYTES, include/aphrodite_b200.h
@@ -33,8 +40,9 @@ def test_noalloc_entry_point_matches_the_workspace_entry_point_twice():
     dev = "cuda"
     ks = torch.tensor(1.0, device=dev)
     vs = torch.tensor(1.0, device=dev)
-    # two different problems back to back: the shared scratch keeps the first call's partials
-    cases = [(6, 32, 8, 128, 16, [3000, 1, 517, 4096, 2049, 777], "fp8", 11),
+    # two different problems back to back: the shared scratch keeps the first call's partials. Long contexts at a small
+    # batch: splits finer than the 8 partitions a thread-block cluster merges on chip, so the scratch is really used
+    cases = [(2, 32, 8, 128, 16, [20000, 9000], "fp8", 11),
              (3, 16, 2, 128, 16, [9000, 4000, 257], "auto", 12)]
     for S, H, KVH, D, bs, lens, kv, seed in cases:
         q, kc, vc, bt, sl = [t.to(dev) for t in make_attention_case(S, H, KVH, D, bs, lens, torch.bfloat16, kv, seed)]
@@ -66,7 +74,12 @@ def oversized_case(lib):
     raise AssertionError("no candidate problem exceeds the built-in scratch; update the list")
 
 
-def reject_check(lib):
+def reject_child():
+    """Runs with APH_PA_CLUSTER=0: with cluster merging no real problem needs more than a few MB of partials, so the
+    size check is exercised with the round-1 behaviour (every partition through the scratch)."""
+    lib = ctypes.CDLL(os.path.join(ROOT, "aphrodite-fork_b200", "lib", "libaphrodite_b200.so"))
+    lib.aph_b200_last_error.restype = ctypes.c_char_p
+    lib.aph_paged_attention_workspace_bytes.restype = ctypes.c_size_t
     S, H, KVH, D, max_len = oversized_case(lib)
     one = ctypes.c_void_p(256)  # never dereferenced: the size check comes first
     i64 = ctypes.c_int64
@@ -74,8 +87,18 @@ def reject_check(lib):
                                             2048, None, i64(H * D), i64(H * D), i64(KVH * D * 16), i64(D * 16), 2, 1, one,
                                             one, 0, 0, 0, 64, 0, None)
     assert st == 3 and b"built-in scratch" in lib.aph_b200_last_error()  # APH_ERR_WORKSPACE
+    print("rejected")
+
+
+def reject_check():
+    r = subprocess.run([sys.executable, os.path.abspath(__file__), "reject-child"], env=dict(os.environ, APH_PA_CLUSTER="0"),
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "rejected" in r.stdout, r.stderr[-2000:]
 
 
 def test_noalloc_entry_point_rejects_problems_beyond_its_scratch():
-    import aphrodite_fork_b200 as A
-    reject_check(A.c_api())
+    reject_check()
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "reject-child":
+    reject_child()
