@@ -10,6 +10,15 @@
 // still reads in call n, and nobody can start call n + 2 before every rank has passed the barrier of call n + 1, i.e.
 // finished call n. That removes the reference's second barrier. Flags are per-CTA counters that only grow; a waiter
 // accepts any value >= its own flag because a fast peer may already have published the next one.
+// TWO-SHOT variants (replace cross_device_reduce_2stage, custom_all_reduce.cuh:321-400) for larger groups, where pushing
+// the whole message to every peer costs (world - 1) x the message of NVLink egress per rank (7 MiB for the 1 MiB
+// messages of a TP 8 decode step): every 16-byte vector has an OWNER rank (by the thread that handles it, so the CTA
+// pairing of the barrier still holds); (A) push each vector to its owner only, (B1) barrier, (C1) the owner adds the
+// `world` partials in rank order in fp32, rounds once and pushes the sum into slot `owner` of every rank - that slot
+// position is unused on the other ranks, (B2) barrier, (C2) every rank reads the sums from its own buffer. Egress per
+// rank: 2 (world - 1) / world x the message. Same double buffering, same bit-identical results on every rank.
+// The per-CTA counters hold the CALL number n; call n uses half n & 1 and the barrier flags 2n and 2n + 1, so one-shot
+// and two-shot calls can be mixed freely.
 // Layout of a rank's buffer (from the host: torch symmetric memory / CUDA IPC): [ 4 KiB flags | 2 halves x world slots
 // x slot_bytes ]. A CTA only waits for the CTA with the same index on the peers and grids are at most 128 CTAs of 512
 // threads, so every waiting CTA is resident (no deadlock on a 148-SM part).
@@ -36,11 +45,55 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   return v;
 }
 
+// Barrier with the CTA of the same index on every peer: publish `flag` (release: this CTA's earlier stores, ordered
+// before it by the CTA barrier, become visible with it) and wait until every peer has published at least `flag`.
+// A peer that never arrives (crashed rank, mismatched call sequence) must end as a launch failure, not as a hung GPU:
+// back off after the first microseconds and trap after about a minute.
+template <int WORLD>
+__device__ __forceinline__ void ar_barrier(uint8_t* const* s_bufs, int rank, uint32_t flag) {
+  __syncthreads();
+  if (threadIdx.x < WORLD) {
+    st_release_sys(&reinterpret_cast<ArSignals*>(s_bufs[threadIdx.x])->arrived[blockIdx.x][rank], flag);
+    const uint32_t* w = &reinterpret_cast<ArSignals*>(s_bufs[rank])->arrived[blockIdx.x][threadIdx.x];
+    for (uint32_t spins = 0; (int32_t)(ld_acquire_sys(w) - flag) < 0; ++spins) {
+      if (spins > 4096) __nanosleep(256);
+      if (spins > (1u << 28)) __trap();
+    }
+  }
+  __syncthreads();
+}
+
+// every counter advances once per call, also those of CTAs this call did not need: the call number (and with it the
+// buffer half) is then the same in every CTA whatever grid sizes the calls used
+__device__ __forceinline__ void ar_finish(uint32_t* counters, uint32_t call) {
+  if (threadIdx.x == 0) counters[blockIdx.x] = call;
+  if (blockIdx.x == 0)
+    for (int b = gridDim.x + threadIdx.x; b < AR_MAX_BLOCKS; b += blockDim.x) counters[b] = call;
+}
+
 template <typename T, int WORLD>
+__device__ __forceinline__ uint4 ar_sum_slots(const uint8_t* mine, int64_t slot_bytes, int64_t idx) {
+  constexpr int VEC = 16 / (int)sizeof(T);
+  uint4 v[WORLD];
+#pragma unroll
+  for (int r = 0; r < WORLD; ++r) v[r] = __ldcv(reinterpret_cast<const uint4*>(mine + r * slot_bytes) + idx);  // peers wrote them: no stale L1
+  float acc[VEC];
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) acc[e] = ScalarTraits<T>::to_float(reinterpret_cast<const T*>(&v[0])[e]);
+#pragma unroll
+  for (int r = 1; r < WORLD; ++r)
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) acc[e] += ScalarTraits<T>::to_float(reinterpret_cast<const T*>(&v[r])[e]);
+  uint4 o;
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) reinterpret_cast<T*>(&o)[e] = ScalarTraits<T>::from_float(acc[e]);
+  return o;
+}
+
+template <typename T, int WORLD, bool TWO_SHOT>
 __global__ void __launch_bounds__(512, 1)
     one_shot_all_reduce_kernel(T* out, const T* in, uint8_t* const* __restrict__ peer_bufs,  // out may alias in
                                uint32_t* __restrict__ counters, int rank, int64_t n_vec, int64_t slot_bytes) {
-  constexpr int VEC = 16 / (int)sizeof(T);
   using V = uint4;
   __shared__ uint8_t* s_bufs[WORLD];
   pdl_trigger();
@@ -49,51 +102,38 @@ __global__ void __launch_bounds__(512, 1)
   pdl_wait();
   // Read AFTER the wait: under programmatic dependent launch this grid may start while an earlier all-reduce of the same
   // stream is still running (every kernel of the step triggers its dependents at once), and that one updates the counters.
-  const uint32_t flag = counters[blockIdx.x] + 1;
-  const int64_t half_off = AR_SIGNAL_BYTES + (int64_t)(flag & 1) * WORLD * slot_bytes;
+  const uint32_t call = counters[blockIdx.x] + 1;
+  const int64_t half_off = AR_SIGNAL_BYTES + (int64_t)(call & 1) * WORLD * slot_bytes;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x, first = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  // (A) push
-  for (int64_t i = first; i < n_vec; i += stride) {
-    const V v = reinterpret_cast<const V*>(in)[i];
-#pragma unroll
-    for (int r = 0; r < WORLD; ++r) reinterpret_cast<V*>(s_bufs[r] + half_off + rank * slot_bytes)[i] = v;
-  }
-  // (B) barrier: the release publishes this CTA's pushes (ordered before it by the CTA barrier) to each peer
-  __syncthreads();
-  if (threadIdx.x < WORLD) {
-    st_release_sys(&reinterpret_cast<ArSignals*>(s_bufs[threadIdx.x])->arrived[blockIdx.x][rank], flag);
-    const uint32_t* w = &reinterpret_cast<ArSignals*>(s_bufs[rank])->arrived[blockIdx.x][threadIdx.x];
-    // a peer that never arrives (crashed rank, mismatched call sequence) must end as a launch failure, not as a hung GPU:
-    // back off after the first microseconds and trap after about a minute
-    for (uint32_t spins = 0; (int32_t)(ld_acquire_sys(w) - flag) < 0; ++spins) {
-      if (spins > 4096) __nanosleep(256);
-      if (spins > (1u << 28)) __trap();
-    }
-  }
-  __syncthreads();
-  // (C) local sum in rank order
   const uint8_t* mine = s_bufs[rank] + half_off;
-  for (int64_t i = first; i < n_vec; i += stride) {
-    V v[WORLD];
+  if (!TWO_SHOT) {
+    // (A) push to everybody
+    for (int64_t i = first; i < n_vec; i += stride) {
+      const V v = reinterpret_cast<const V*>(in)[i];
 #pragma unroll
-    for (int r = 0; r < WORLD; ++r) v[r] = __ldcv(reinterpret_cast<const V*>(mine + r * slot_bytes) + i);  // peers wrote them: no stale L1
-    float acc[VEC];
+      for (int r = 0; r < WORLD; ++r) reinterpret_cast<V*>(s_bufs[r] + half_off + rank * slot_bytes)[i] = v;
+    }
+    ar_barrier<WORLD>(s_bufs, rank, 2 * call);  // (B)
+    // (C) local sum in rank order
+    for (int64_t i = first; i < n_vec; i += stride) reinterpret_cast<V*>(out)[i] = ar_sum_slots<T, WORLD>(mine, slot_bytes, i);
+  } else {
+    const int owner = (int)threadIdx.x * WORLD / (int)blockDim.x;  // of every vector this thread handles
+    // (A) push to the owner only
+    for (int64_t i = first; i < n_vec; i += stride)
+      reinterpret_cast<V*>(s_bufs[owner] + half_off + rank * slot_bytes)[i] = reinterpret_cast<const V*>(in)[i];
+    ar_barrier<WORLD>(s_bufs, rank, 2 * call);  // (B1)
+    // (C1) the owner reduces and hands the sum to everybody, in slot `rank` (unused at these positions on the peers)
+    if (owner == rank)
+      for (int64_t i = first; i < n_vec; i += stride) {
+        const V o = ar_sum_slots<T, WORLD>(mine, slot_bytes, i);
 #pragma unroll
-    for (int e = 0; e < VEC; ++e) acc[e] = ScalarTraits<T>::to_float(reinterpret_cast<const T*>(&v[0])[e]);
-#pragma unroll
-    for (int r = 1; r < WORLD; ++r)
-#pragma unroll
-      for (int e = 0; e < VEC; ++e) acc[e] += ScalarTraits<T>::to_float(reinterpret_cast<const T*>(&v[r])[e]);
-    V o;
-#pragma unroll
-    for (int e = 0; e < VEC; ++e) reinterpret_cast<T*>(&o)[e] = ScalarTraits<T>::from_float(acc[e]);
-    reinterpret_cast<V*>(out)[i] = o;
+        for (int r = 0; r < WORLD; ++r) reinterpret_cast<V*>(s_bufs[r] + half_off + rank * slot_bytes)[i] = o;
+      }
+    ar_barrier<WORLD>(s_bufs, rank, 2 * call + 1);  // (B2)
+    // (C2)
+    for (int64_t i = first; i < n_vec; i += stride) reinterpret_cast<V*>(out)[i] = __ldcv(reinterpret_cast<const V*>(mine + owner * slot_bytes) + i);
   }
-  // every counter advances once per call, also those of CTAs this call did not need: the flag (and with it the buffer
-  // half) is then the same call number in every CTA whatever grid sizes the calls used
-  if (threadIdx.x == 0) counters[blockIdx.x] = flag;
-  if (blockIdx.x == 0)
-    for (int b = gridDim.x + threadIdx.x; b < AR_MAX_BLOCKS; b += blockDim.x) counters[b] = flag;
+  ar_finish(counters, call);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -118,7 +158,7 @@ __device__ __forceinline__ float ar_block_sum(float v, float* s_part) {
   return v;
 }
 
-template <typename T, int WORLD>
+template <typename T, int WORLD, bool TWO_SHOT>
 __global__ void __launch_bounds__(512, 1)
     all_reduce_add_rms_norm_kernel(T* x, T* residual, const T* __restrict__ weight, float epsilon,
                                    uint8_t* const* __restrict__ peer_bufs, uint32_t* __restrict__ counters, int rank, int rows,
@@ -139,29 +179,36 @@ __global__ void __launch_bounds__(512, 1)
   }
   __syncthreads();
   pdl_wait();
-  const uint32_t flag = counters[blockIdx.x] + 1;  // after the wait, see one_shot_all_reduce_kernel
-  const int64_t half_off = AR_SIGNAL_BYTES + (int64_t)(flag & 1) * WORLD * slot_bytes;
-  // (A) push this CTA's rows
+  const uint32_t call = counters[blockIdx.x] + 1;  // after the wait, see one_shot_all_reduce_kernel
+  const int64_t half_off = AR_SIGNAL_BYTES + (int64_t)(call & 1) * WORLD * slot_bytes;
+  const uint8_t* mine = s_bufs[rank] + half_off;
+  const int owner = (int)threadIdx.x * WORLD / (int)blockDim.x;  // TWO_SHOT: owner of every vector this thread handles
+  // (A) push this CTA's rows: to everybody, or (two-shot) to the owner of each vector
   for (int row = blockIdx.x; row < rows; row += gridDim.x)
     for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
       const int64_t idx = (int64_t)row * nvec + i;
       const V v = reinterpret_cast<const V*>(x)[idx];
+      if (TWO_SHOT) {
+        reinterpret_cast<V*>(s_bufs[owner] + half_off + rank * slot_bytes)[idx] = v;
+      } else {
 #pragma unroll
-      for (int r = 0; r < WORLD; ++r) reinterpret_cast<V*>(s_bufs[r] + half_off + rank * slot_bytes)[idx] = v;
+        for (int r = 0; r < WORLD; ++r) reinterpret_cast<V*>(s_bufs[r] + half_off + rank * slot_bytes)[idx] = v;
+      }
     }
-  // (B)
-  __syncthreads();
-  if (threadIdx.x < WORLD) {
-    st_release_sys(&reinterpret_cast<ArSignals*>(s_bufs[threadIdx.x])->arrived[blockIdx.x][rank], flag);
-    const uint32_t* w = &reinterpret_cast<ArSignals*>(s_bufs[rank])->arrived[blockIdx.x][threadIdx.x];
-    for (uint32_t spins = 0; (int32_t)(ld_acquire_sys(w) - flag) < 0; ++spins) {
-      if (spins > 4096) __nanosleep(256);
-      if (spins > (1u << 28)) __trap();
-    }
+  ar_barrier<WORLD>(s_bufs, rank, 2 * call);  // (B) / (B1)
+  if (TWO_SHOT) {
+    // (C1) the owner reduces its vectors and hands the rounded sums to every rank (slot `rank` at these positions)
+    if (owner == rank)
+      for (int row = blockIdx.x; row < rows; row += gridDim.x)
+        for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+          const int64_t idx = (int64_t)row * nvec + i;
+          const V o = ar_sum_slots<T, WORLD>(mine, slot_bytes, idx);
+#pragma unroll
+          for (int r = 0; r < WORLD; ++r) reinterpret_cast<V*>(s_bufs[r] + half_off + rank * slot_bytes)[idx] = o;
+        }
+    ar_barrier<WORLD>(s_bufs, rank, 2 * call + 1);  // (B2)
   }
-  __syncthreads();
   // (C) finish the rows
-  const uint8_t* mine = s_bufs[rank] + half_off;
   for (int row = blockIdx.x; row < rows; row += gridDim.x) {
     V keep[ITER];
     float ss = 0.f;
@@ -170,17 +217,13 @@ __global__ void __launch_bounds__(512, 1)
       const int i = threadIdx.x + it * blockDim.x;
       if (i < nvec) {
         const int64_t idx = (int64_t)row * nvec + i;
-        V v[WORLD];
-#pragma unroll
-        for (int r = 0; r < WORLD; ++r) v[r] = __ldcv(reinterpret_cast<const V*>(mine + r * slot_bytes) + idx);
+        // the all-reduce's output, rounded to T: summed here in rank order (one-shot) or by the vector's owner (two-shot)
+        const V sum = TWO_SHOT ? __ldcv(reinterpret_cast<const V*>(mine + owner * slot_bytes) + idx) : ar_sum_slots<T, WORLD>(mine, slot_bytes, idx);
         const V res = reinterpret_cast<const V*>(residual)[idx];
         V z;
 #pragma unroll
         for (int e = 0; e < VEC; ++e) {
-          float acc = ScalarTraits<T>::to_float(reinterpret_cast<const T*>(&v[0])[e]);
-#pragma unroll
-          for (int r = 1; r < WORLD; ++r) acc += ScalarTraits<T>::to_float(reinterpret_cast<const T*>(&v[r])[e]);
-          const float s = ScalarTraits<T>::to_float(ar_round<T>(acc));                                       // all-reduce output
+          const float s = ScalarTraits<T>::to_float(reinterpret_cast<const T*>(&sum)[e]);                     // all-reduce output
           const T zz = ar_round<T>(s + ScalarTraits<T>::to_float(reinterpret_cast<const T*>(&res)[e]));       // scalar_t add
           reinterpret_cast<T*>(&z)[e] = zz;
           const float f = ScalarTraits<T>::to_float(zz);
@@ -207,19 +250,21 @@ __global__ void __launch_bounds__(512, 1)
       }
     }
   }
-  if (threadIdx.x == 0) counters[blockIdx.x] = flag;
-  if (blockIdx.x == 0)
-    for (int b = gridDim.x + threadIdx.x; b < AR_MAX_BLOCKS; b += blockDim.x) counters[b] = flag;
+  ar_finish(counters, call);
 }
 
 template <typename T>
 int launch_ar_norm(void* x, void* residual, const void* weight, float eps, const void* const* peer_bufs, uint32_t* counters, int rank,
-                   int world, int rows, int hidden, int64_t slot_bytes, cudaStream_t stream) {
+                   int world, int rows, int hidden, int64_t slot_bytes, bool two_shot, cudaStream_t stream) {
   const int blocks = std::max(1, std::min(rows, AR_MAX_BLOCKS));
-#define APH_ARN(W)                                                                                                              \
-  case W:                                                                                                                       \
-    APH_LAUNCH_PDL((all_reduce_add_rms_norm_kernel<T, W>), dim3((unsigned)blocks), dim3(512), (size_t)0, stream, (T*)x, (T*)residual, \
-                   (const T*)weight, eps, (uint8_t* const*)peer_bufs, counters, rank, rows, hidden, slot_bytes);                  \
+#define APH_ARN(W)                                                                                                                   \
+  case W:                                                                                                                            \
+    if (two_shot)                                                                                                                    \
+      APH_LAUNCH_PDL((all_reduce_add_rms_norm_kernel<T, W, true>), dim3((unsigned)blocks), dim3(512), (size_t)0, stream, (T*)x,      \
+                     (T*)residual, (const T*)weight, eps, (uint8_t* const*)peer_bufs, counters, rank, rows, hidden, slot_bytes);      \
+    else                                                                                                                             \
+      APH_LAUNCH_PDL((all_reduce_add_rms_norm_kernel<T, W, false>), dim3((unsigned)blocks), dim3(512), (size_t)0, stream, (T*)x,     \
+                     (T*)residual, (const T*)weight, eps, (uint8_t* const*)peer_bufs, counters, rank, rows, hidden, slot_bytes);      \
     return APH_OK
   switch (world) {
     APH_ARN(2);
@@ -233,20 +278,70 @@ int launch_ar_norm(void* x, void* residual, const void* weight, float eps, const
 
 template <typename T>
 int launch_one_shot(void* out, const void* in, const void* const* peer_bufs, uint32_t* counters, int rank, int world, int64_t n_vec,
-                    int64_t slot_bytes, int blocks, cudaStream_t stream) {
-#define APH_AR(W)                                                                                                             \
-  case W:                                                                                                                     \
-    APH_LAUNCH_PDL((one_shot_all_reduce_kernel<T, W>), dim3((unsigned)blocks), dim3(512), (size_t)0, stream, (T*)out, (const T*)in, \
-                   (uint8_t* const*)peer_bufs, counters, rank, n_vec, slot_bytes);                                                      \
+                    int64_t slot_bytes, int blocks, bool two_shot, cudaStream_t stream) {
+#define APH_AR(W)                                                                                                                  \
+  case W:                                                                                                                          \
+    if (two_shot)                                                                                                                  \
+      APH_LAUNCH_PDL((one_shot_all_reduce_kernel<T, W, true>), dim3((unsigned)blocks), dim3(512), (size_t)0, stream, (T*)out,      \
+                     (const T*)in, (uint8_t* const*)peer_bufs, counters, rank, n_vec, slot_bytes);                                  \
+    else                                                                                                                           \
+      APH_LAUNCH_PDL((one_shot_all_reduce_kernel<T, W, false>), dim3((unsigned)blocks), dim3(512), (size_t)0, stream, (T*)out,     \
+                     (const T*)in, (uint8_t* const*)peer_bufs, counters, rank, n_vec, slot_bytes);                                  \
     return APH_OK
   switch (world) {
     APH_AR(2);
     APH_AR(4);
     APH_AR(6);
     APH_AR(8);
-    default: return set_error(APH_ERR_UNSUPPORTED, "one_shot_all_reduce: world size %d (2, 4, 6 or 8)", world);
+    default: return set_error(APH_ERR_UNSUPPORTED, "all_reduce: world size %d (2, 4, 6 or 8)", world);
   }
 #undef APH_AR
+}
+
+int all_reduce_entry(const char* op, bool two_shot, void* out, const void* in, const void* const* peer_bufs_dev, uint32_t* counters,
+                     int rank, int world, int64_t numel, int dtype, int64_t slot_bytes, int max_blocks, void* stream) {
+  APH_CHECK(world >= 2 && world <= AR_MAX_RANKS && rank >= 0 && rank < world, APH_ERR_INVALID_ARGUMENT, "%s: rank %d of %d", op, rank,
+            world);
+  APH_CHECK(numel >= 0, APH_ERR_INVALID_ARGUMENT, "%s: negative size", op);
+  if (numel == 0) return APH_OK;
+  APH_CHECK(out && in && peer_bufs_dev && counters, APH_ERR_INVALID_ARGUMENT, "%s: null pointer", op);
+  const int esz = dtype == APH_DT_F32 ? 4 : 2;
+  APH_CHECK((numel * esz) % 16 == 0 && aligned16(out) && aligned16(in), APH_ERR_INVALID_ARGUMENT,
+            "%s: the message must be a multiple of 16 bytes and 16-byte aligned", op);
+  APH_CHECK(slot_bytes % 16 == 0 && numel * esz <= slot_bytes, APH_ERR_INVALID_ARGUMENT,
+            "%s: message of %lld bytes does not fit the %lld-byte slots", op, (long long)(numel * esz), (long long)slot_bytes);
+  const int64_t n_vec = numel * esz / 16;
+  int blocks = (int)std::min<int64_t>((n_vec + 511) / 512, std::min(max_blocks > 0 ? max_blocks : AR_MAX_BLOCKS, AR_MAX_BLOCKS));
+  blocks = std::max(blocks, 1);
+  cudaStream_t s = (cudaStream_t)stream;
+  switch (dtype) {
+    case APH_DT_F32: return launch_one_shot<float>(out, in, peer_bufs_dev, counters, rank, world, n_vec, slot_bytes, blocks, two_shot, s);
+    case APH_DT_F16: return launch_one_shot<__half>(out, in, peer_bufs_dev, counters, rank, world, n_vec, slot_bytes, blocks, two_shot, s);
+    case APH_DT_BF16:
+      return launch_one_shot<__nv_bfloat16>(out, in, peer_bufs_dev, counters, rank, world, n_vec, slot_bytes, blocks, two_shot, s);
+    default: return set_error(APH_ERR_INVALID_ARGUMENT, "%s: unknown dtype %d", op, dtype);
+  }
+}
+
+int ar_norm_entry(const char* op, bool two_shot, void* x, void* residual, const void* weight, float epsilon, const void* const* peer_bufs_dev,
+                  uint32_t* counters, int rank, int world, int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes,
+                  void* stream) {
+  APH_CHECK(world >= 2 && world <= AR_MAX_RANKS && rank >= 0 && rank < world, APH_ERR_INVALID_ARGUMENT, "%s: rank %d of %d", op, rank,
+            world);
+  APH_CHECK(dtype == APH_DT_F16 || dtype == APH_DT_BF16, APH_ERR_UNSUPPORTED, "%s: float16 / bfloat16 only", op);
+  APH_CHECK(num_tokens >= 0 && hidden_size > 0 && hidden_size % 8 == 0 && hidden_size <= 4 * 512 * 8, APH_ERR_INVALID_ARGUMENT,
+            "%s: hidden size must be a multiple of 8 and at most 16384", op);
+  if (num_tokens == 0) return APH_OK;
+  APH_CHECK(x && residual && weight && peer_bufs_dev && counters, APH_ERR_INVALID_ARGUMENT, "%s: null pointer", op);
+  APH_CHECK(aligned16(x) && aligned16(residual) && aligned16(weight), APH_ERR_INVALID_ARGUMENT, "%s: tensors must be 16-byte aligned", op);
+  APH_CHECK(slot_bytes % 16 == 0 && num_tokens * hidden_size * 2 <= slot_bytes, APH_ERR_INVALID_ARGUMENT,
+            "%s: message does not fit the %lld-byte slots", op, (long long)slot_bytes);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (dtype == APH_DT_F16)
+    return launch_ar_norm<__half>(x, residual, weight, epsilon, peer_bufs_dev, counters, rank, world, (int)num_tokens, (int)hidden_size,
+                                  slot_bytes, two_shot, s);
+  return launch_ar_norm<__nv_bfloat16>(x, residual, weight, epsilon, peer_bufs_dev, counters, rank, world, (int)num_tokens,
+                                       (int)hidden_size, slot_bytes, two_shot, s);
 }
 
 }  // namespace
@@ -263,47 +358,27 @@ extern "C" size_t aph_all_reduce_buffer_bytes(int world, int64_t slot_bytes) {
 
 extern "C" int aph_one_shot_all_reduce(void* out, const void* in, const void* const* peer_bufs_dev, uint32_t* counters, int rank,
                                        int world, int64_t numel, int dtype, int64_t slot_bytes, int max_blocks, void* stream) {
-  const char* op = "one_shot_all_reduce";
-  APH_CHECK(world >= 2 && world <= AR_MAX_RANKS && rank >= 0 && rank < world, APH_ERR_INVALID_ARGUMENT, "%s: rank %d of %d", op, rank,
-            world);
-  APH_CHECK(numel >= 0, APH_ERR_INVALID_ARGUMENT, "%s: negative size", op);
-  if (numel == 0) return APH_OK;
-  APH_CHECK(out && in && peer_bufs_dev && counters, APH_ERR_INVALID_ARGUMENT, "%s: null pointer", op);
-  const int esz = dtype == APH_DT_F32 ? 4 : 2;
-  APH_CHECK((numel * esz) % 16 == 0 && aligned16(out) && aligned16(in), APH_ERR_INVALID_ARGUMENT,
-            "%s: the message must be a multiple of 16 bytes and 16-byte aligned", op);
-  APH_CHECK(slot_bytes % 16 == 0 && numel * esz <= slot_bytes, APH_ERR_INVALID_ARGUMENT,
-            "%s: message of %lld bytes does not fit the %lld-byte slots", op, (long long)(numel * esz), (long long)slot_bytes);
-  const int64_t n_vec = numel * esz / 16;
-  int blocks = (int)std::min<int64_t>((n_vec + 511) / 512, std::min(max_blocks > 0 ? max_blocks : AR_MAX_BLOCKS, AR_MAX_BLOCKS));
-  blocks = std::max(blocks, 1);
-  cudaStream_t s = (cudaStream_t)stream;
-  switch (dtype) {
-    case APH_DT_F32: return launch_one_shot<float>(out, in, peer_bufs_dev, counters, rank, world, n_vec, slot_bytes, blocks, s);
-    case APH_DT_F16: return launch_one_shot<__half>(out, in, peer_bufs_dev, counters, rank, world, n_vec, slot_bytes, blocks, s);
-    case APH_DT_BF16: return launch_one_shot<__nv_bfloat16>(out, in, peer_bufs_dev, counters, rank, world, n_vec, slot_bytes, blocks, s);
-    default: return set_error(APH_ERR_INVALID_ARGUMENT, "%s: unknown dtype %d", op, dtype);
-  }
+  return all_reduce_entry("one_shot_all_reduce", false, out, in, peer_bufs_dev, counters, rank, world, numel, dtype, slot_bytes, max_blocks,
+                          stream);
+}
+
+extern "C" int aph_two_shot_all_reduce(void* out, const void* in, const void* const* peer_bufs_dev, uint32_t* counters, int rank,
+                                       int world, int64_t numel, int dtype, int64_t slot_bytes, int max_blocks, void* stream) {
+  return all_reduce_entry("two_shot_all_reduce", true, out, in, peer_bufs_dev, counters, rank, world, numel, dtype, slot_bytes, max_blocks,
+                          stream);
 }
 
 extern "C" int aph_all_reduce_add_rms_norm(void* x, void* residual, const void* weight, float epsilon,
                                            const void* const* peer_bufs_dev, uint32_t* counters, int rank, int world,
                                            int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes, void* stream) {
-  const char* op = "all_reduce_add_rms_norm";
-  APH_CHECK(world >= 2 && world <= AR_MAX_RANKS && rank >= 0 && rank < world, APH_ERR_INVALID_ARGUMENT, "%s: rank %d of %d", op, rank,
-            world);
-  APH_CHECK(dtype == APH_DT_F16 || dtype == APH_DT_BF16, APH_ERR_UNSUPPORTED, "%s: float16 / bfloat16 only", op);
-  APH_CHECK(num_tokens >= 0 && hidden_size > 0 && hidden_size % 8 == 0 && hidden_size <= 4 * 512 * 8, APH_ERR_INVALID_ARGUMENT,
-            "%s: hidden size must be a multiple of 8 and at most 16384", op);
-  if (num_tokens == 0) return APH_OK;
-  APH_CHECK(x && residual && weight && peer_bufs_dev && counters, APH_ERR_INVALID_ARGUMENT, "%s: null pointer", op);
-  APH_CHECK(aligned16(x) && aligned16(residual) && aligned16(weight), APH_ERR_INVALID_ARGUMENT, "%s: tensors must be 16-byte aligned", op);
-  APH_CHECK(slot_bytes % 16 == 0 && num_tokens * hidden_size * 2 <= slot_bytes, APH_ERR_INVALID_ARGUMENT,
-            "%s: message does not fit the %lld-byte slots", op, (long long)slot_bytes);
-  cudaStream_t s = (cudaStream_t)stream;
-  if (dtype == APH_DT_F16)
-    return launch_ar_norm<__half>(x, residual, weight, epsilon, peer_bufs_dev, counters, rank, world, (int)num_tokens, (int)hidden_size,
-                                  slot_bytes, s);
-  return launch_ar_norm<__nv_bfloat16>(x, residual, weight, epsilon, peer_bufs_dev, counters, rank, world, (int)num_tokens,
-                                       (int)hidden_size, slot_bytes, s);
+  return ar_norm_entry("all_reduce_add_rms_norm", false, x, residual, weight, epsilon, peer_bufs_dev, counters, rank, world, num_tokens,
+                       hidden_size, dtype, slot_bytes, stream);
+}
+
+extern "C" int aph_two_shot_all_reduce_add_rms_norm(void* x, void* residual, const void* weight, float epsilon,
+                                                    const void* const* peer_bufs_dev, uint32_t* counters, int rank, int world,
+                                                    int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes,
+                                                    void* stream) {
+  return ar_norm_entry("two_shot_all_reduce_add_rms_norm", true, x, residual, weight, epsilon, peer_bufs_dev, counters, rank, world,
+                       num_tokens, hidden_size, dtype, slot_bytes, stream);
 }

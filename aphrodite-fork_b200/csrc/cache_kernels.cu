@@ -12,8 +12,10 @@ namespace aphb200 {
 
 namespace {
 
+// N elements moved as one vector. The alignment is capped at 16 bytes: that is all the callers check (aligned16), so a
+// pack of 8 floats leaves as two 16-byte accesses instead of one 32-byte access that would need a 32-byte aligned cache.
 template <typename T, int N>
-struct alignas(sizeof(T) * N) Pack {
+struct alignas(sizeof(T) * N > 16 ? 16 : sizeof(T) * N) Pack {
   T v[N];
 };
 
@@ -532,7 +534,12 @@ extern "C" int aph_swap_blocks(const void* src, void* dst, const int64_t* block_
   for (int64_t i = 0; i < num_pairs;) {
     const int64_t s0 = block_mapping_host[2 * i], d0 = block_mapping_host[2 * i + 1];
     int64_t run = 1;
-    while (i + run < num_pairs && block_mapping_host[2 * (i + run)] == s0 + run && block_mapping_host[2 * (i + run) + 1] == d0 + run) ++run;
+    // inside ONE tensor (src == dst) a merged run could overlap itself (blocks 0,1 -> 1,2), where the reference's
+    // block-by-block copies are well defined: merge only runs whose source and destination ranges are disjoint
+    const bool same = kind == 0 && src == dst;
+    while (i + run < num_pairs && block_mapping_host[2 * (i + run)] == s0 + run && block_mapping_host[2 * (i + run) + 1] == d0 + run &&
+           (!same || (s0 + run < d0 || d0 + run < s0)))
+      ++run;
     const cudaError_t e = cudaMemcpyAsync(static_cast<char*>(dst) + d0 * block_bytes, static_cast<const char*>(src) + s0 * block_bytes,
                                           (size_t)(run * block_bytes), mk, (cudaStream_t)stream);
     APH_CHECK(e == cudaSuccess, APH_ERR_CUDA, "swap_blocks: cudaMemcpyAsync failed: %s", cudaGetErrorString(e));

@@ -41,6 +41,7 @@ namespace mg {
 
 struct Plan {
   int nt, grid, k_stages, n_slices, total;
+  int cluster_split;  // aligned split-K plans with 2..8 pieces per slice run as thread-block clusters (0 otherwise)
 };
 
 // Decomposition. The output is cut into slices of NT columns and K into stages of 16 KiB of packed weights (so the
@@ -70,6 +71,50 @@ static int forced_grid_env() {
   return dev_env_live() ? env_int("APH_GEMM_GRID") : v;
 }
 
+// Co-resident thread-block clusters of `size` CTAs of the register kernel <NB, NT> (cudaOccupancyMaxActiveClusters,
+// cached): a cluster plan must fit one wave, and clusters pack worse than single CTAs (they cannot straddle GPCs).
+template <int NB, int NT>
+static int mma_max_clusters_of(int size) {
+  static int cache[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  if (cache[size] == 0) {
+    using C = Cfg<__nv_bfloat16, NB, NT>;
+    auto kern = marlin_w4a16_kernel<__nv_bfloat16, NB, NT, false>;
+    int n = -1;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES) == cudaSuccess) {
+      cudaLaunchConfig_t cfg{};
+      cfg.gridDim = dim3((unsigned)(size * 32));
+      cfg.blockDim = dim3(THREADS);
+      cfg.dynamicSmemBytes = C::SMEM_BYTES;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = (unsigned)size;
+      at[0].val.clusterDim.y = 1;
+      at[0].val.clusterDim.z = 1;
+      cfg.attrs = at;
+      cfg.numAttrs = 1;
+      if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) n = -1;
+    }
+    (void)cudaGetLastError();
+    cache[size] = n;
+  }
+  return cache[size];
+}
+template <int NB>
+static int mma_max_clusters_nb(int nt, int size) {
+  return nt == 256 ? mma_max_clusters_of<NB, 256>(size) : nt == 128 ? mma_max_clusters_of<NB, 128>(size) : mma_max_clusters_of<NB, 64>(size);
+}
+static int mma_max_clusters(int nb, int nt, int size) {
+  return nb == 1 ? mma_max_clusters_nb<1>(nt, size) : nb == 2 ? mma_max_clusters_nb<2>(nt, size) : mma_max_clusters_nb<4>(nt, size);
+}
+
+static bool cluster_allowed() {  // APH_GEMM_CLUSTER=0 (development): split-K pieces always meet through the scratch
+  static const bool on = [] {
+    const char* e = getenv("APH_GEMM_CLUSTER");
+    return e == nullptr || e[0] != '0';
+  }();
+  return dev_env_live() ? !(getenv("APH_GEMM_CLUSTER") && getenv("APH_GEMM_CLUSTER")[0] == '0') : on;
+}
+
 static Plan make_plan(int64_t N, int64_t K, int nb) {
   const int slots = sm_count() * (nb <= 2 ? 2 : 1);
   const int forced_nt = forced_nt_env();
@@ -94,19 +139,29 @@ static Plan make_plan(int64_t N, int64_t K, int nb) {
       if (grid < 1 || grid > pl.total) return;
       const int per_cta = (pl.total + grid - 1) / grid;
       const bool shared = !(aligned && grid == pl.n_slices);
+      const int split = aligned ? grid / pl.n_slices : 0;
+      // the pieces of a slice meet in shared memory when they can form a thread-block cluster (2..8 CTAs): cheaper than
+      // the scratch + counter + last-arriver fix-up of the other shared plans
+      // (rank 0 receives the other pieces' partials in its idle pipeline ring: at most 40 KiB of it)
+      const bool cluster = cluster_allowed() && aligned && split >= 2 && split <= 8 && (split - 1) * 8 * nb * nt * 4 <= 40 * 1024 &&
+                           mma_max_clusters(nb, nt, split) >= pl.n_slices;
       const double t_stage = nb == 1 ? 0.75 : nb == 2 ? 1.3 : 2.2;
-      const double cost = t_stage * per_cta + (shared ? 2.0 : 0.0) + (aligned ? 0.0 : (nb == 1 ? 1.8 : 6.0)) + width_bias;
+      const double cost = t_stage * per_cta + (shared ? (cluster ? 0.8 : 2.0) : 0.0) + (aligned ? 0.0 : (nb == 1 ? 1.8 : 6.0)) + width_bias;
       if (cost < best_cost) {
         best_cost = cost;
         best = pl;
         best.grid = grid;
+        best.cluster_split = cluster ? split : 0;
       }
     };
     for (int split = 1; split <= 8; ++split)
       if (pl.k_stages % split == 0 && (int64_t)pl.n_slices * split <= slots) consider(pl.n_slices * split, true);
     consider(pl.total < slots ? pl.total : slots, false);
   }
-  if (forced_grid > 0) best.grid = forced_grid < best.total ? forced_grid : best.total;
+  if (forced_grid > 0) {
+    best.grid = forced_grid < best.total ? forced_grid : best.total;
+    best.cluster_split = 0;
+  }
   return best;
 }
 
@@ -188,6 +243,7 @@ struct Operands {
 
 template <typename scalar_t, int NB, int NT, bool HAS_ZP>
 static int launch(const Params& p, const Operands& op, int grid, cudaStream_t stream) {
+  const int cluster_split = p.cluster_split;
   using C = Cfg<scalar_t, NB, NT>;
   auto kern = marlin_w4a16_kernel<scalar_t, NB, NT, HAS_ZP>;
   static bool attr_set[64] = {false};
@@ -228,11 +284,22 @@ static int launch(const Params& p, const Operands& op, int grid, cudaStream_t st
   cfg.blockDim = dim3(THREADS);
   cfg.dynamicSmemBytes = C::SMEM_BYTES;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (cluster_split > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = (unsigned)cluster_split;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cfg.numAttrs = na;
   const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, p, tmB, tmA, tmS, tmZ);
   APH_CHECK(le == cudaSuccess, APH_ERR_CUDA, "gptq_marlin_gemm: launch failed: %s", cudaGetErrorString(le));
   return APH_OK;
@@ -261,6 +328,7 @@ static int run_typed(Params p, const Operands& op, bool has_zp, float* scratch, 
     p.m_rows = rows;
     p.k_stages = pl.k_stages;
     p.total = pl.total;
+    p.cluster_split = pl.cluster_split;
     const size_t need = plan_scratch_bytes(pl, nb);
     APH_CHECK(((int64_t)pl.total + pl.k_stages + 1) * pl.grid < (1LL << 31), APH_ERR_UNSUPPORTED,
               "gptq_marlin_gemm: %d work items are beyond the 32-bit scheduling arithmetic", pl.total);
@@ -284,11 +352,17 @@ static int run_typed(Params p, const Operands& op, bool has_zp, float* scratch, 
 // ------------------------------------------------------------------------------------------------
 struct PlanTc {
   int grid, total, k_stages, m_tiles, n_slices;
+  int cluster_split;  // 0 = stream-K; S >= 2 = thread-block clusters of S CTAs split the k range of one tile each
 };
 
 // Stream-K: one persistent CTA per SM, each taking an equal share of the (tile, k stage) list; fewer CTAs
 // only when the problem is too small to give each at least 4 stages.
-static PlanTc make_plan_tc(int64_t M, int64_t N, int64_t K, int mb) {
+// How many thread-block clusters of `size` CTAs of a kernel can be resident at once (cudaOccupancyMaxActiveClusters; the
+// CTAs of a cluster share a GPC, so this is NOT #SMs / size: 48 clusters of 3 one-SM CTAs do not fit a B200 although
+// 144 <= 148, and a second wave doubles the time). Cached per (kernel, size).
+using MaxClustersFn = int (*)(int size);
+
+static PlanTc make_plan_tc(int64_t M, int64_t N, int64_t K, int mb, MaxClustersFn max_clusters = nullptr) {
   PlanTc pl;
   pl.n_slices = (int)(N / mgtc::NTILE);
   pl.k_stages = (int)((K + mgtc::KSTAGE - 1) / mgtc::KSTAGE);
@@ -298,6 +372,25 @@ static PlanTc make_plan_tc(int64_t M, int64_t N, int64_t K, int mb) {
   if (g > pl.total / 4) g = pl.total / 4;
   if (g < 1) g = 1;
   pl.grid = g;
+  pl.cluster_split = 0;
+  // Few tiles (the qkv / o / down shapes of a decode step, every tensor-parallel shard): stream-K would cut every tile
+  // into pieces that meet through an fp32 scratch, an atomic counter and a last-arriver merge - about 5 us of the ~15 us
+  // such a call takes (stage traces, profiles/r02_gemm_tc_stage_traces.txt). Instead S CTAs of one thread-block cluster
+  // split a tile's k range and add their accumulators through distributed shared memory. APH_TC_CLUSTER=0: never.
+  static const bool allow = [] {
+    const char* e = getenv("APH_TC_CLUSTER");
+    return e == nullptr || e[0] != '0';
+  }();
+  const int tiles = pl.n_slices * pl.m_tiles;
+  if (allow && max_clusters != nullptr && tiles * 2 <= sm_count() && pl.k_stages >= 4) {
+    int s = sm_count() / tiles;
+    if (s > 8) s = 8;                                   // portable cluster size
+    while (s > 1 && (pl.k_stages / s < 2 || max_clusters(s) < tiles)) --s;  // >= 2 stages per CTA, one wave of clusters
+    if (s >= 2) {
+      pl.cluster_split = s;
+      pl.grid = tiles * s;
+    }
+  }
   return pl;
 }
 
@@ -314,12 +407,12 @@ static size_t scratch_bytes_tc(int64_t M, int64_t N, int64_t K) {
   return worst;
 }
 
-template <typename scalar_t, int MB, bool HAS_ZP, int BITS = 4>
+template <typename scalar_t, int MB, bool HAS_ZP, int BITS = 4, bool ZPF = false>
 static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t scratch_bytes, cudaStream_t stream) {
   using C = mgtc::Cfg<scalar_t, MB, BITS>;
   constexpr int WPC = BITS / 4;    // 8-byte words per weight column and k16-row
   constexpr int PACK = 32 / BITS;  // zero points per int32
-  auto kern = mgtc::marlin_w4a16_tc_kernel<scalar_t, MB, HAS_ZP, BITS>;
+  auto kern = mgtc::marlin_w4a16_tc_kernel<scalar_t, MB, HAS_ZP, BITS, ZPF>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -328,14 +421,41 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
       return set_error(APH_ERR_CUDA, "gptq_marlin_gemm: cannot reserve %d bytes of shared memory", C::SMEM_BYTES);
     attr_set[dev] = true;
   }
-  const PlanTc pl = make_plan_tc(op.M, p.N, p.K, MB);
+  // co-resident clusters of this instantiation, per cluster size (queried once per size)
+  static int max_cl[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  struct Q {
+    static int get(int size) {
+      if (max_cl[size] == 0) {
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3((unsigned)(size * 16));
+        cfg.blockDim = dim3(mgtc::THREADS);
+        cfg.dynamicSmemBytes = C::SMEM_BYTES;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = (unsigned)size;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, mgtc::marlin_w4a16_tc_kernel<scalar_t, MB, HAS_ZP, BITS, ZPF>, &cfg) != cudaSuccess || n <= 0) {
+          (void)cudaGetLastError();
+          n = -1;
+        }
+        max_cl[size] = n;
+      }
+      return max_cl[size];
+    }
+  };
+  const PlanTc pl = make_plan_tc(op.M, p.N, p.K, MB, &Q::get);
   p.k_stages = pl.k_stages;
   p.m_tiles = pl.m_tiles;
   p.total = pl.total;
   p.M = (int)op.M;
-  const size_t need = (size_t)pl.grid * 2 * MB * mgtc::NTILE * sizeof(float);
-  APH_CHECK(scratch != nullptr && scratch_bytes >= need, APH_ERR_WORKSPACE, "gptq_marlin_gemm: scratch of %zu bytes needed, %zu given",
-            need, scratch_bytes);
+  p.cluster_split = pl.cluster_split;
+  const size_t need = pl.cluster_split ? 0 : (size_t)pl.grid * 2 * MB * mgtc::NTILE * sizeof(float);
+  APH_CHECK(need == 0 || (scratch != nullptr && scratch_bytes >= need), APH_ERR_WORKSPACE,
+            "gptq_marlin_gemm: scratch of %zu bytes needed, %zu given", need, scratch_bytes);
   p.scratch = scratch;
   const bool grouped = p.group_size < p.K;
   const int gps = grouped ? mgtc::KSTAGE / p.group_size : 0;
@@ -351,7 +471,11 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
     st = make_map_2d(&tmS, dt16, 2, op.s, (uint64_t)p.N, (uint64_t)op.num_groups, (uint64_t)p.N * 2, mgtc::NTILE, gps,
                      CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
     if (st != APH_OK) return st;
-    if (HAS_ZP) {
+    if (HAS_ZP && ZPF) {  // float zero points: a second table shaped like the scales
+      st = make_map_2d(&tmZ, dt16, 2, op.zp, (uint64_t)p.N, (uint64_t)op.num_groups, (uint64_t)p.N * 2, mgtc::NTILE, gps,
+                       CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+      if (st != APH_OK) return st;
+    } else if (HAS_ZP) {
       st = make_map_2d(&tmZ, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, op.zp, (uint64_t)p.N / PACK, (uint64_t)op.num_groups,
                        (uint64_t)p.N / PACK * 4, mgtc::NTILE / PACK, gps, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
       if (st != APH_OK) return st;
@@ -378,11 +502,22 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
     cfg.blockDim = dim3(mgtc::THREADS);
     cfg.dynamicSmemBytes = C::SMEM_BYTES;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (pl.cluster_split) {
+      attr[na].id = cudaLaunchAttributeClusterDimension;
+      attr[na].val.clusterDim.x = (unsigned)pl.cluster_split;
+      attr[na].val.clusterDim.y = 1;
+      attr[na].val.clusterDim.z = 1;
+      ++na;
+    }
+    if (pdl_enabled()) {
+      attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[na].val.programmaticStreamSerializationAllowed = 1;
+      ++na;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cfg.numAttrs = na;
     const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, p, tmB, tmA, tmS, tmZ);
     APH_CHECK(le == cudaSuccess, APH_ERR_CUDA, "gptq_marlin_gemm: launch failed: %s", cudaGetErrorString(le));
   }
@@ -436,6 +571,22 @@ static int run_typed_tc(const Params& p0, const Operands& op0, bool has_zp, int 
     p.group_size = p0.group_size;
     APH_CHECK((rows + 255) / 256 <= 32, APH_ERR_UNSUPPORTED, "gptq_marlin_gemm: size_m above 8192 is not supported in one call");
     int st;
+    if (bits == 0) {
+      // HQQ: uint4 weights with float16 zero points (is_zp_float; f16 only, grouped only - checked by the caller)
+      if constexpr (std::is_same<scalar_t, __half>::value) {
+        const int mb = tile_rows_tc8(rows);
+        if (mb == 16)
+          st = launch_tc<scalar_t, 16, true, 4, true>(p, op, scratch, scratch_bytes, stream);
+        else if (mb == 64)
+          st = launch_tc<scalar_t, 64, true, 4, true>(p, op, scratch, scratch_bytes, stream);
+        else
+          st = launch_tc<scalar_t, 256, true, 4, true>(p, op, scratch, scratch_bytes, stream);
+      } else {
+        st = set_error(APH_ERR_INVALID_ARGUMENT, "Computation type must be float16 (half) when using float zero points.");
+      }
+      if (st != APH_OK) return st;
+      continue;
+    }
     if (bits == 8) {
       // 8-bit weights (uint8b128 / uint8): batch tiles of 16, 64 or 256 rows
       const int mb = tile_rows_tc8(rows);
@@ -530,7 +681,14 @@ extern "C" int aph_gptq_marlin_gemm(void* c, const void* a, const void* b_q_weig
   else
     APH_CHECK(b_q_type == mg::ID_UINT4B8 || b_q_type == mg::ID_UINT8B128, APH_ERR_INVALID_ARGUMENT,
               "b_q_type must be uint4b8 or uint8b128 when has_zp = False. Got = %lld", (long long)b_q_type);
-  APH_CHECK(!is_zp_float, APH_ERR_UNSUPPORTED, "gptq_marlin_gemm: float zero points (HQQ) are not implemented");
+  if (is_zp_float) {
+    // HQQ (gptq_marlin.cu:2284-2288,2416-2424): float16 zero points [num_groups, size_n] laid out like the scales
+    APH_CHECK(has_zp && b_q_type == mg::ID_UINT4, APH_ERR_INVALID_ARGUMENT, "float zero points need has_zp and uint4 weights");
+    APH_CHECK(dtype == APH_DT_F16, APH_ERR_INVALID_ARGUMENT, "Computation type must be float16 (half) when using float zero points.");
+    APH_CHECK(num_groups > 1, APH_ERR_INVALID_ARGUMENT, "float zero points need grouped quantisation (num_groups must be != -1)");
+    APH_CHECK(size_n % mgtc::NTILE == 0, APH_ERR_UNSUPPORTED,
+              "gptq_marlin_gemm: float zero points need size_n divisible by 128 here, got %lld", (long long)size_n);
+  }
   const int bits = (b_q_type == mg::ID_UINT8 || b_q_type == mg::ID_UINT8B128) ? 8 : 4;
   // 8-bit weights run on the tensor-memory kernel for every batch size (128-column slices)
   APH_CHECK(bits == 4 || size_n % mgtc::NTILE == 0, APH_ERR_UNSUPPORTED,
@@ -579,6 +737,7 @@ extern "C" int aph_gptq_marlin_gemm(void* c, const void* a, const void* b_q_weig
   }
   mg::Operands op{a, b_q_weight, b_scales, has_zp ? b_zeros : nullptr, size_m, lda, num_groups, dtype == APH_DT_F16};
   cudaStream_t s = (cudaStream_t)stream;
+  if (is_zp_float) return mg::run_typed_tc<__half>(p, op, true, 0 /* HQQ */, (float*)scratch, scratch_bytes, s);
   if (bits == 8 || mg::use_tc_path(size_m, size_n)) {
     if (dtype == APH_DT_F16) return mg::run_typed_tc<__half>(p, op, has_zp != 0, bits, (float*)scratch, scratch_bytes, s);
     return mg::run_typed_tc<__nv_bfloat16>(p, op, has_zp != 0, bits, (float*)scratch, scratch_bytes, s);

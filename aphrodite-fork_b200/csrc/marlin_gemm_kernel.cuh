@@ -28,6 +28,8 @@ struct Params {
   int k_stages;        // ceil(K / (128 * KG)) pipeline stages over the whole K
   int total;           // n_slices * k_stages work items (slice-major); CTA i owns [i*total/grid, (i+1)*total/grid)
   int dbg;             // development switch (APH_GEMM_DBG): 1 = skip the math, 2 = skip the loads
+  int cluster_split;   // S >= 2: aligned split-K plan launched as thread-block clusters of S CTAs (the S pieces of one
+                       // slice); their partials meet in rank 0's shared memory instead of the scratch. 0: scratch + counters
 };
 
 // One pipeline stage holds KG x NWN warp blocks of (128 k x 64 n): 16 KiB of weights whatever the slice
@@ -167,7 +169,10 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
 
   if (w == SG * CONSUMERS) {
     // ============================ producer: one thread, tiled TMA loads ============================
-    if (lane != 0) return;
+    if (lane != 0) {
+      if (p.cluster_split > 1) cluster_sync_twice_unaligned();  // every thread takes part in the cluster merge's two phases
+      return;
+    }
     prefetch_tensormap(&tmB);
     prefetch_tensormap(&tmA);
     if (grouped) prefetch_tensormap(&tmS);
@@ -253,6 +258,7 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
       load_activations(held_st, held_ks);
     }
 #endif
+    if (p.cluster_split > 1) cluster_sync_twice_unaligned();
     return;
   }
 
@@ -424,6 +430,42 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
     named_bar_sync(1, CT);
 
     const int nelem = p.m_rows * NT;
+    if (p.cluster_split > 1) {
+      // ---- cluster split-K: the CTAs of this cluster hold the partial sums of ONE slice (aligned plan: a CTA's range is
+      //      one piece of one slice). Ranks 1.. push their partial into rank 0's idle pipeline ring through DSMEM, rank 0
+      //      adds them in rank order and writes the result: no scratch round trip, no atomics, no last-arriver pass.
+      //      Phase one of the cluster barrier = "my main loop is over, my ring is idle" (and: every CTA runs). ----
+      const int crank = (int)cluster_ctarank();
+      cluster_arrive_release();
+      cluster_wait_acquire();
+      if (crank != 0) {
+        for (int idx = tid; idx < nelem; idx += CT) {
+          const int m = idx / NT, n = idx % NT;
+          float v = 0.f;
+#pragma unroll
+          for (int kg = 0; kg < SG * KG; ++kg) v += red[(size_t)(kg * MP + m) * C::RP + n];
+          st_cluster_f32(cluster_map_shared(smem_base + (uint32_t)(((crank - 1) * MP * NT + idx) * 4), 0u), v);
+        }
+        cluster_arrive_release();  // rank 0 reads after this phase
+        cluster_wait_acquire();
+        it0 += cnt;
+        return;
+      }
+      cluster_arrive_release();
+      cluster_wait_acquire();
+      const float* recv = reinterpret_cast<const float*>(smem);
+      scalar_t* cout = reinterpret_cast<scalar_t*>(p.c) + (int64_t)p.m0 * p.N + (int64_t)slice * NT;
+      for (int idx = tid; idx < nelem; idx += CT) {
+        const int m = idx / NT, n = idx % NT;
+        float v = 0.f;
+#pragma unroll
+        for (int kg = 0; kg < SG * KG; ++kg) v += red[(size_t)(kg * MP + m) * C::RP + n];
+        for (int r = 1; r < p.cluster_split; ++r) v += recv[(r - 1) * MP * NT + idx];  // rank order: deterministic
+        cout[(int64_t)m * p.N + n] = ScalarTraits<scalar_t>::from_float(v);
+      }
+      it0 += cnt;
+      return;
+    }
     if (whole) {
       // the whole k range of the slice was ours: write the result
       scalar_t* cout = reinterpret_cast<scalar_t*>(p.c) + (int64_t)p.m0 * p.N + (int64_t)slice * NT;

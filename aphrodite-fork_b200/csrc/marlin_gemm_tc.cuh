@@ -46,8 +46,8 @@ struct WStage {
   static constexpr int PACK = 32 / BITS;
   static constexpr int ROW_BYTES = NTILE * 2 * BITS;       // one k16-row of the slice: 16 x 128 weights
   static constexpr int W_BYTES = 8 * ROW_BYTES;
-  static constexpr int Z_BYTES = 4 * (NTILE / PACK) * 4;
-  static constexpr int BYTES = W_BYTES + S_BYTES + Z_BYTES;  // 9472 bytes at 4 bit
+  static constexpr int Z_BYTES = BITS == 4 ? S_BYTES : 4 * (NTILE / PACK) * 4;  // 4 bit: room for HQQ's 16-bit float zero points
+  static constexpr int BYTES = W_BYTES + S_BYTES + Z_BYTES;
 };
 
 // The work is the flattened list of (tile, k stage) pairs, tile = (column slice, batch tile); CTA b of G
@@ -64,6 +64,8 @@ struct Params {
   int k_stages;       // ceil(K / 128)
   int m_tiles;        // ceil(M / MB)
   int total;          // T = tiles * k_stages
+  int cluster_split;  // 0: stream-K ranges. S >= 2: CTA b = tile * S + r is rank r of a thread-block cluster of S CTAs that
+                      // share tile b / S; r takes the r-th S-th of the tile's k stages and the partials meet in shared memory
   unsigned long long* trace;  // development: per-stage clock64 stamps of CTA 0 (APH_GEMM_TRACE), else null
 };
 
@@ -156,7 +158,8 @@ struct SegIter {
   }
 };
 
-template <typename scalar_t, int MB, bool HAS_ZP, int BITS = 4>
+// ZPF: the zero points are 16-bit FLOATS laid out like the scales (HQQ, gptq_marlin.cu:1190-1300): w = (q - z) * s
+template <typename scalar_t, int MB, bool HAS_ZP, int BITS = 4, bool ZPF = false>
 __global__ void __launch_bounds__(THREADS, 1)
     marlin_w4a16_tc_kernel(const Params p, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmA,
                            const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUtensorMap tmZ) {
@@ -175,7 +178,10 @@ __global__ void __launch_bounds__(THREADS, 1)
   const bool grouped = p.group_size < p.K;
   const int gps = grouped ? KSTAGE / p.group_size : 0;  // groups per stage (1, 2, 4)
   const int G = gridDim.x, T = p.total, KS = p.k_stages;
-  const int lo = range_lo(blockIdx.x, T, G), hi = range_lo(blockIdx.x + 1, T, G);  // hi > lo: G <= T
+  const int CS = p.cluster_split;
+  // stream-K: equal contiguous ranges of the flattened (tile, stage) list. Cluster split-K: the r-th part of one tile.
+  const int lo = CS ? (int)(blockIdx.x / CS) * KS + (int)((blockIdx.x % CS) * KS / CS) : range_lo(blockIdx.x, T, G);
+  const int hi = CS ? (int)(blockIdx.x / CS) * KS + (int)((blockIdx.x % CS + 1) * KS / CS) : range_lo(blockIdx.x + 1, T, G);  // hi > lo
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
   const uint32_t bar0 = smem_base + C::BAR_OFF;
@@ -283,12 +289,15 @@ __global__ void __launch_bounds__(THREADS, 1)
 #endif
   if (w == W_PROD) {
     // ==================== weight producer: packed weights, scales, zero points ====================
-    if (lane != 0) return;
+    if (lane != 0) {
+      if (CS) cluster_sync_twice_unaligned();
+      return;
+    }
     prefetch_tensormap(&tmB);
     if (grouped) prefetch_tensormap(&tmS);
     if (HAS_ZP && grouped) prefetch_tensormap(&tmZ);
     const uint64_t pol_stream = policy_evict_first();  // weights are read once (or re-read from L2 by the next batch tile)
-    const uint32_t stage_tx = (uint32_t)(W_BYTES + gps * NTILE * 2 + (HAS_ZP ? gps * (NTILE / PACK) * 4 : 0));
+    const uint32_t stage_tx = (uint32_t)(W_BYTES + gps * NTILE * 2 + (HAS_ZP ? (ZPF ? gps * NTILE * 2 : gps * (NTILE / PACK) * 4) : 0));
     int it = 0;
     RingCursor<SW> ring;  // the producer handles every stage
     auto issue = [&](int sw, int slice, int ks) {
@@ -298,7 +307,7 @@ __global__ void __launch_bounds__(THREADS, 1)
       tma_load_2d_hint(dst, &tmB, slice * NTILE * (BITS / 4), ks * 8, fb, pol_stream);  // 8-byte words: 1 (2) per column at 4 (8) bit
       if (grouped) {
         tma_load_2d(dst + W_BYTES, &tmS, slice * NTILE, ks * gps, fb);
-        if constexpr (HAS_ZP) tma_load_2d(dst + W_BYTES + S_BYTES, &tmZ, slice * (NTILE / PACK), ks * gps, fb);
+        if constexpr (HAS_ZP) tma_load_2d(dst + W_BYTES + S_BYTES, &tmZ, ZPF ? slice * NTILE : slice * (NTILE / PACK), ks * gps, fb);
       }
     };
 #ifdef APH_RING_FAULT
@@ -332,12 +341,16 @@ __global__ void __launch_bounds__(THREADS, 1)
 #ifdef APH_RING_FAULT
     if (held_sw >= 0) issue(held_sw, held_slice, held_ks);
 #endif
+    if (CS) cluster_sync_twice_unaligned();
     return;
   }
 
   if (w == W_ACT) {
     // ==================== activation producer ====================
-    if (lane != 0) return;
+    if (lane != 0) {
+      if (CS) cluster_sync_twice_unaligned();
+      return;
+    }
     prefetch_tensormap(&tmA);
     griddep_wait();  // activations are the previous kernel's output
     const uint64_t pol_keep = policy_evict_last();  // activations are shared by every CTA
@@ -357,6 +370,7 @@ __global__ void __launch_bounds__(THREADS, 1)
         tma_load_2d_hint(dst + C::ACT_BOX, &tmA, ks * KSTAGE + 64, mt * MB, fb, pol_keep);
       }
     }
+    if (CS) cluster_sync_twice_unaligned();
     return;
   }
 
@@ -407,8 +421,18 @@ __global__ void __launch_bounds__(THREADS, 1)
         tc_commit_elect(done_bar + db * 8);
       }
     }
-    if (w != W_MMA) return;
+    if (w != W_MMA) {
+      if (CS) cluster_sync_twice_unaligned();
+      return;
+    }
     __syncwarp();
+    if (CS) {
+      // every thread of the cluster takes part in the two phases of the epilogue's merge (see there)
+      cluster_arrive_release();
+      cluster_wait_acquire();
+      cluster_arrive_release();
+      cluster_wait_acquire();
+    }
     named_bar_sync(2, (EPI_WARPS + 1) * 32);  // every TMEM read of the epilogue is done
     tmem_dealloc(tmem_base, C::TMEM_COLS);
     return;
@@ -437,7 +461,10 @@ __global__ void __launch_bounds__(THREADS, 1)
     constexpr bool VIA_F32 = BITS == 8 && !F16;
     constexpr uint32_t BIAS = BITS == 4 ? 0x00080008u : 0x00800080u;  // the symmetric types: uint4b8, uint8b128
     uint32_t s_lo[2], s_hi[2], c_lo[2], c_hi[2];
-    c_lo[0] = c_lo[1] = c_hi[0] = c_hi[1] = VIA_F32 ? 0x4B000080u : (C::MAGIC | BIAS);
+    uint32_t z_lo[2] = {0u, 0u}, z_hi[2] = {0u, 0u};  // ZPF only
+    (void)z_lo;
+    (void)z_hi;
+    c_lo[0] = c_lo[1] = c_hi[0] = c_hi[1] = ZPF ? C::MAGIC : VIA_F32 ? 0x4B000080u : (C::MAGIC | BIAS);
     s_lo[0] = s_lo[1] = s_hi[0] = s_hi[1] = 0;
     auto set_zp = [&](uint32_t zword) {
 #pragma unroll
@@ -471,7 +498,16 @@ __global__ void __launch_bounds__(THREADS, 1)
       s_hi[0] = __byte_perm(sw0, sw0, 0x3232);
       s_lo[1] = __byte_perm(sw1, sw1, 0x1010);
       s_hi[1] = __byte_perm(sw1, sw1, 0x3232);
-      if constexpr (HAS_ZP) set_zp(lds32(wstage + offZ + gl * (NTILE / PACK) * 4));
+      if constexpr (ZPF) {
+        // float zero points: same layout as the scales; the subtraction takes two exact / rounded steps (q, then q - z)
+        lds64(wstage + offS + S_BYTES + gl * (NTILE * 2), sw0, sw1);
+        z_lo[0] = __byte_perm(sw0, sw0, 0x1010);
+        z_hi[0] = __byte_perm(sw0, sw0, 0x3232);
+        z_lo[1] = __byte_perm(sw1, sw1, 0x1010);
+        z_hi[1] = __byte_perm(sw1, sw1, 0x3232);
+      } else if constexpr (HAS_ZP) {
+        set_zp(lds32(wstage + offZ + gl * (NTILE / PACK) * 4));
+      }
     };
     // two bytes of an 8-bit word (b, b + 2) -> the exact 16-bit pair (q - z) [* s]
     auto pair8 = [&](uint32_t word, int b, uint32_t cc, uint32_t ss) -> uint32_t {
@@ -502,7 +538,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     RingCursor<SA> ring_a;
     APH_SEGMENTS {
       APH_SEG_VARS
-      if (HAS_ZP && !grouped)
+      if (HAS_ZP && !ZPF && !grouped)
         set_zp(*reinterpret_cast<const uint32_t*>(
             p.zp + (BITS == 4 ? ((int64_t)slice * (NTILE / 8) + (qd >> 1) * 8 + g) * 4
                               : ((int64_t)slice * (NTILE / 4) + (qd >> 1) * 16 + g * 2 + (qd & 1)) * 4)));
@@ -544,10 +580,17 @@ __global__ void __launch_bounds__(THREADS, 1)
               const uint32_t a2 = and_or(q[i][tt] >> 4, 0x000f000fu, C::MAGIC);
               const uint32_t a1 = and_or(q[i][tt] >> 8, 0x000f000fu, C::MAGIC);
               const uint32_t a3 = and_or(q[i][tt] >> 12, 0x000f000fu, C::MAGIC);
-              a[tt][4 * i + 0] = sub_mul2<F16>(a0, c_lo[tt], s_lo[tt], grouped);
-              a[tt][4 * i + 1] = sub_mul2<F16>(a1, c_hi[tt], s_hi[tt], grouped);
-              a[tt][4 * i + 2] = sub_mul2<F16>(a2, c_lo[tt], s_lo[tt], grouped);
-              a[tt][4 * i + 3] = sub_mul2<F16>(a3, c_hi[tt], s_hi[tt], grouped);
+              if constexpr (ZPF) {
+                a[tt][4 * i + 0] = sub_mul2<F16>(sub_mul2<F16>(a0, c_lo[tt], 0u, false), z_lo[tt], s_lo[tt], true);
+                a[tt][4 * i + 1] = sub_mul2<F16>(sub_mul2<F16>(a1, c_hi[tt], 0u, false), z_hi[tt], s_hi[tt], true);
+                a[tt][4 * i + 2] = sub_mul2<F16>(sub_mul2<F16>(a2, c_lo[tt], 0u, false), z_lo[tt], s_lo[tt], true);
+                a[tt][4 * i + 3] = sub_mul2<F16>(sub_mul2<F16>(a3, c_hi[tt], 0u, false), z_hi[tt], s_hi[tt], true);
+              } else {
+                a[tt][4 * i + 0] = sub_mul2<F16>(a0, c_lo[tt], s_lo[tt], grouped);
+                a[tt][4 * i + 1] = sub_mul2<F16>(a1, c_hi[tt], s_hi[tt], grouped);
+                a[tt][4 * i + 2] = sub_mul2<F16>(a2, c_lo[tt], s_lo[tt], grouped);
+                a[tt][4 * i + 3] = sub_mul2<F16>(a3, c_hi[tt], s_hi[tt], grouped);
+              }
             } else {
               // word 0 of a tile: row g, bytes (0, 2) = k low pair, (1, 3) = k high pair; word 1: row g + 8
               a[tt][4 * i + 0] = pair8(q[i][2 * tt], 0, c_lo[tt], s_lo[tt]);
@@ -574,10 +617,17 @@ __global__ void __launch_bounds__(THREADS, 1)
       }
     }
     if (pending >= 0) publish();
+    if (CS) {  // cluster split-K: the epilogue warps merge through shared memory, nothing to do here but to be counted
+      cluster_sync_twice_unaligned();
+      return;
+    }
     merge_phase(EPI_WARPS * 32 + tid - W_DQ0 * 32);
     return;
   }
-  if (w < W_EPI0) return;  // second issuer warp idles when NI == 1
+  if (w < W_EPI0) {  // second issuer warp idles when NI == 1
+    if (CS) cluster_sync_twice_unaligned();
+    return;
+  }
 
   // ================================ epilogue warps ================================
   {
@@ -623,6 +673,86 @@ __global__ void __launch_bounds__(THREADS, 1)
 #endif
       const uint32_t d0 = tmem_base + d_lane + (db * C::NI + (two ? 0 : lone)) * MB;
       const uint32_t d1 = tmem_base + d_lane + (db * C::NI + 1) * MB;
+      if (CS) {
+        // ---- cluster split-K: the CS CTAs of the cluster hold partial sums of the same tile. Chunk cc (16 batch rows)
+        //      belongs to rank cc % CS: everybody pushes its other chunks into the owner's (now idle) pipeline rings
+        //      through DSMEM, the owner adds the CS partials in rank order and writes C. No scratch, no atomics.
+        //      Barrier phase one = "my MMAs are complete, my rings are idle" (also: every CTA of the cluster runs). ----
+        const int crank = (int)cluster_ctarank();
+        const int chunks = (m_rows + 15) / 16;
+        const int owned_max = (MB / 16 + CS - 1) / CS;
+        float* recv = reinterpret_cast<float*>(smem);  // [source rank][owned chunk][128 columns][16 rows]
+        auto load_chunk = [&](int cc, uint32_t (&v)[16]) {
+          tmem_ld_32x32b_x16(d0 + 16 * cc, v);
+          if (two) {
+            uint32_t v2[16];
+            tmem_ld_32x32b_x16(d1 + 16 * cc, v2);
+            tmem_wait_ld();
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(v2[j]));
+          } else {
+            tmem_wait_ld();
+          }
+        };
+        cluster_arrive_release();
+        cluster_wait_acquire();
+        const uint32_t recv_u32 = smem_base;
+#pragma unroll 1
+        for (int cc = 0; cc < chunks; ++cc) {
+          const int owner = cc % CS;
+          if (owner == crank) continue;
+          uint32_t v[16];
+          load_chunk(cc, v);
+          const uint32_t dst = cluster_map_shared(recv_u32 + (uint32_t)(((crank * owned_max + cc / CS) * NTILE + n_local) * 64), (uint32_t)owner);
+#pragma unroll
+          for (int j = 0; j < 16; j += 4)
+            asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + j * 4), "r"(v[j]), "r"(v[j + 1]), "r"(v[j + 2]),
+                         "r"(v[j + 3])
+                         : "memory");
+        }
+        cluster_arrive_release();
+        cluster_wait_acquire();
+#pragma unroll 1
+        for (int cc = crank; cc < chunks; cc += CS) {
+          const int rows = m_rows - 16 * cc;
+          uint32_t v[16];
+          load_chunk(cc, v);
+          float acc[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+#pragma unroll 1
+          for (int r = 0; r < CS; ++r) {  // rank order: deterministic
+            if (r == crank) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) acc[j] += __uint_as_float(v[j]);
+            } else {
+              const float4* src = reinterpret_cast<const float4*>(recv + (size_t)((r * owned_max + cc / CS) * NTILE + n_local) * 16);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float4 t = src[j];
+                acc[4 * j] += t.x;
+                acc[4 * j + 1] += t.y;
+                acc[4 * j + 2] += t.z;
+                acc[4 * j + 3] += t.w;
+              }
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            *reinterpret_cast<scalar_t*>(stage + j * (NTILE * 2) + n_local * 2) = ScalarTraits<scalar_t>::from_float(acc[j] * s_n);
+          named_bar_sync(1, ET);
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const int vec = etid + i * ET, row = vec >> 4, c16 = vec & 15;
+            if (row < rows)
+              *reinterpret_cast<uint4*>(crow + (int64_t)(16 * cc + row) * p.N + c16 * 8) =
+                  *reinterpret_cast<const uint4*>(stage + row * (NTILE * 2) + c16 * 16);
+          }
+          named_bar_sync(1, ET);  // the staging tile is reused by the next chunk
+        }
+        tc_fence_before();
+        continue;  // exactly one segment per CTA in this mode
+      }
 #pragma unroll 1
       for (int cc = 0; cc < MB / 16; ++cc) {
         const int rows = m_rows - 16 * cc;  // batch rows in this chunk of 16 accumulator columns
@@ -697,7 +827,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 #ifdef APH_GEMM_TRACE
     if (p.trace != nullptr && b == 0 && etid == 0) p.trace[512 + 48 + 0] = clock64();
 #endif
-    merge_phase(etid);
+    if (!CS) merge_phase(etid);
 #ifdef APH_GEMM_TRACE
     if (p.trace != nullptr && b == 0 && etid == 0) p.trace[512 + 48 + 1] = clock64();
 #endif

@@ -312,6 +312,12 @@ __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+// Both phases of a two-phase cluster rendezvous for a thread that has nothing to contribute (warp-specialised kernels:
+// producer / dequantiser / idle warps). Not .aligned: the lanes of a warp may reach it from different places. Every
+// thread of the cluster takes part in every phase, so nothing depends on how exited threads are counted.
+__device__ __forceinline__ void cluster_sync_twice_unaligned() {
+  asm volatile("barrier.cluster.arrive.release;\n\tbarrier.cluster.wait.acquire;\n\tbarrier.cluster.arrive.release;\n\tbarrier.cluster.wait.acquire;" ::: "memory");
+}
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));

@@ -48,13 +48,24 @@ class OneShotAllReduce:
         torch.cuda.synchronize(self.device)
         dist.barrier(group)  # every rank's flags are zero before anybody starts
 
+    def two_shot(self, nbytes: int) -> bool:
+        """One-shot pushes (world - 1) x the message per rank, two-shot 2 (world - 1) / world x for one more flag barrier
+        (csrc/all_reduce.cu; the reference switches at 512 / 256 KiB for 4 / 8 ranks, custom_all_reduce.cuh:563-570).
+        APH_AR_TWO_SHOT_BYTES (development) moves the threshold; 0 = never."""
+        env = os.environ.get("APH_AR_TWO_SHOT_BYTES")
+        if env is not None:
+            return int(env) > 0 and nbytes >= int(env)
+        if self.world_size <= 2:
+            return False
+        return nbytes >= (512 * 1024 if self.world_size <= 4 else 128 * 1024)
+
     def should_use(self, x: torch.Tensor) -> bool:
         """One-shot pushes world x the message per rank, so on larger groups it only pays up to a size. The reference
         stops at 512 KiB (<= 4 ranks) and 256 KiB (<= 8 ranks) for its pull kernel (custom_all_reduce.cuh:563-570); the
         push kernel was measured against NCCL on 4 and 8 B200s at the decode step's 1 MiB messages and is still ahead
         (profiles/r01_bench_n4_one_shot_vs_nccl.txt), so the limits here are 2 MiB and 1 MiB; larger messages take NCCL."""
         n = x.numel() * x.element_size()
-        limit = self.max_size if self.world_size == 2 else (2 * 1024 * 1024 if self.world_size <= 4 else 1024 * 1024)
+        limit = self.max_size  # with the two-shot kernel for the larger messages the peer-memory path holds up to 8 MiB
         limit = int(os.environ.get("APH_AR_LIMIT_BYTES", limit))  # development: sweep the threshold
         return (x.is_cuda and x.is_contiguous() and x.dtype in _DT and n % 16 == 0 and 0 < n <= min(limit, self.max_size)
                 and x.data_ptr() % 16 == 0)
@@ -62,7 +73,8 @@ class OneShotAllReduce:
     def all_reduce(self, x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """out = sum over ranks of x (out defaults to x: in place, as TPGroup.all_reduce)."""
         out = x if out is None else out
-        st = self.lib.aph_one_shot_all_reduce(
+        fn = self.lib.aph_two_shot_all_reduce if self.two_shot(x.numel() * x.element_size()) else self.lib.aph_one_shot_all_reduce
+        st = fn(
             ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(x.data_ptr()), ctypes.c_void_p(self.peer_ptrs),
             ctypes.c_void_p(self.counters.data_ptr()), self.rank, self.world_size, ctypes.c_int64(x.numel()), _DT[x.dtype],
             ctypes.c_int64(self.max_size), self.max_blocks, ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
@@ -80,7 +92,9 @@ class OneShotAllReduce:
     def all_reduce_add_rms_norm(self, x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
         """x <- rms_norm(all_reduce(x) + residual) * weight, residual <- all_reduce(x) + residual: the all-reduce and the
         fused_add_rms_norm that follows it in every decoder layer, in one kernel."""
-        st = self.lib.aph_all_reduce_add_rms_norm(
+        fn = (self.lib.aph_two_shot_all_reduce_add_rms_norm if self.two_shot(x.numel() * x.element_size())
+              else self.lib.aph_all_reduce_add_rms_norm)
+        st = fn(
             ctypes.c_void_p(x.data_ptr()), ctypes.c_void_p(residual.data_ptr()), ctypes.c_void_p(weight.data_ptr()),
             ctypes.c_float(epsilon), ctypes.c_void_p(self.peer_ptrs), ctypes.c_void_p(self.counters.data_ptr()), self.rank,
             self.world_size, ctypes.c_int64(x.shape[0]), ctypes.c_int64(x.shape[1]), _DT[x.dtype], ctypes.c_int64(self.max_size),

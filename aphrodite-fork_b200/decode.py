@@ -122,7 +122,8 @@ class DecodeLayer:
         self.h, self.kvh = shard_heads(cfg.num_heads, cfg.num_kv_heads, t)
         d, g = cfg.head_size, cfg.group_size
         self.q_size, self.kv_size = self.h * d, self.kvh * d
-        kv_rank = r * cfg.num_kv_heads // t  # kv heads are replicated once t exceeds their number
+        kv_parts = min(t, cfg.num_kv_heads)  # kv heads are split t ways, or replicated once t exceeds their number
+        kv_rank = r * kv_parts // t           # which of the kv_parts shards this rank holds
 
         def columns(w: MarlinShard, c0: int, c1: int) -> MarlinShard:  # a block of output columns (multiples of 64)
             return MarlinShard(w.q_weight[:, 2 * c0:2 * c1].contiguous(), w.scales[:, c0:c1].contiguous(), None, w.size_k,
@@ -138,7 +139,6 @@ class DecodeLayer:
 
         fq, fkv = full.q_size, full.kv_size
         wq = full.qkv.w
-        kv_parts = min(t, cfg.num_kv_heads)
         self.qkv = column_parallel([(columns(wq, 0, fq), t, r), (columns(wq, fq, fq + fkv), kv_parts, kv_rank),
                                     (columns(wq, fq + fkv, fq + 2 * fkv), kv_parts, kv_rank)])
         self.o = row_parallel(full.o.w)

@@ -15,6 +15,13 @@
  *   - all calls are asynchronous on `stream`, never synchronise, never allocate: scratch is
  *     passed in by the caller (sizes from the *_workspace_bytes functions) so that the calls
  *     are CUDA-graph capturable, like the reference ops (worker/model_runner.py:1487-1646);
+ *   - programmatic dependent launch (PDL): every kernel is launched with the programmatic-stream-serialisation
+ *     attribute and reads what it treats as IMMUTABLE - GEMM weights / scales / zero points, norm weights, the
+ *     permutation of aph_permute_cols - BEFORE it waits for the previous kernel of the stream. Contract: those tensors
+ *     must not be written by a kernel that triggers its dependents early (i.e. another PDL kernel of this library) on
+ *     the same stream right before the call; this library's own weight-producing kernels (aph_*_marlin_repack,
+ *     aph_convert_fp8) are plain launches for that reason. Activations, KV caches, block tables and all outputs are
+ *     only touched after the wait. APH_PDL=0 turns the attribute off;
  *   - return value: 0 on success, an aph_status_t otherwise; aph_b200_last_error() returns a
  *     thread-local message (the torch binding turns it into c10::Error / RuntimeError, the
  *     reference's error behaviour: TORCH_CHECK, SURVEY.md 8b "Errors").
@@ -277,6 +284,14 @@ int aph_all_reduce_max_blocks(void);
 int aph_one_shot_all_reduce(void* out, const void* in, const void* const* peer_bufs_dev, uint32_t* counters, int rank,
                             int world, int64_t numel, int dtype, int64_t slot_bytes, int max_blocks, void* stream);
 
+/* Two-shot variant - replaces cross_device_reduce_2stage, custom_all_reduce.cuh:321-400 (dispatch :563-570). Same buffers,
+ * counters, arguments and result (bit-identical on every rank) as aph_one_shot_all_reduce, and the two may be mixed
+ * freely call by call. Every 16-byte vector has an owner rank: partials go to the owner only, the owner adds them in
+ * rank order in fp32, rounds once and hands the sum to every rank. NVLink egress per rank: 2 (world - 1) / world x the
+ * message instead of (world - 1) x, for one more flag barrier: the choice for larger groups and messages. */
+int aph_two_shot_all_reduce(void* out, const void* in, const void* const* peer_bufs_dev, uint32_t* counters, int rank,
+                            int world, int64_t numel, int dtype, int64_t slot_bytes, int max_blocks, void* stream);
+
 /* aph_one_shot_all_reduce fused with the residual add + RMSNorm that follows every all-reduce of a decoder layer
  * (aph_fused_add_rms_norm): x [num_tokens, hidden] holds this rank's partial on entry and the normalised sum on exit,
  * residual += sum (rounded as the unfused pair rounds). Same buffers, counters and calling discipline as
@@ -284,6 +299,10 @@ int aph_one_shot_all_reduce(void* out, const void* in, const void* const* peer_b
 int aph_all_reduce_add_rms_norm(void* x, void* residual, const void* weight, float epsilon,
                                 const void* const* peer_bufs_dev, uint32_t* counters, int rank, int world,
                                 int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes, void* stream);
+/* the same on top of aph_two_shot_all_reduce (identical results) */
+int aph_two_shot_all_reduce_add_rms_norm(void* x, void* residual, const void* weight, float epsilon,
+                                         const void* const* peer_bufs_dev, uint32_t* counters, int rank, int world,
+                                         int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -80,12 +80,12 @@ def main(mode):
     n_before = len(calls)
     a = torch.zeros(4, 256, dtype=torch.float16, device=dev)
     e = torch.empty(0, dtype=torch.int32, device=dev)
-    ws = torch.zeros(128 // 64 * 16, dtype=torch.int32, device=dev)
-    bq = torch.zeros(256 // 16, 128 * 16 // 8, dtype=torch.int32, device=dev)
-    sc = torch.ones(2, 128, dtype=torch.float16, device=dev)
-    zp_float = torch.ones(2, 128, dtype=torch.float16, device=dev)
-    UINT4 = 1125899906843648
-    r = ops.gptq_marlin_gemm(a, bq, sc, zp_float, e, e, ws, UINT4, 4, 128, 256, True, True, False, True, True)  # HQQ float zero points
+    ws = torch.zeros(64 // 64 * 16, dtype=torch.int32, device=dev)
+    bq = torch.zeros(256 // 16, 64 * 16 // 4, dtype=torch.int32, device=dev)
+    sc = torch.ones(2, 64, dtype=torch.float16, device=dev)
+    UINT8B128 = 1125899923621888
+    # 8-bit weights with 64 output columns: this library's 8-bit path works on 128-column slices (APH_ERR_UNSUPPORTED)
+    r = ops.gptq_marlin_gemm(a, bq, sc, e, e, e, ws, UINT8B128, 4, 64, 256, True, False, False, True, False)
     res["unsupported_call_reached"] = calls[n_before:]
     res["unsupported_call_shape"] = list(r.shape)
     # torch.library.opcheck of the hot ops' schemas (tests/kernels/utils.py:950-963 does the same in the reference)

@@ -135,3 +135,18 @@ def test_swap_blocks_bit_exact(direction, cdt):
     assert torch.equal(_bits(d_t.cpu()), _bits(want))
     with pytest.raises(RuntimeError):
         ops.swap_blocks(s_t, d_t, mapping.cuda())  # block_mapping must be on CPU (cache_kernels.cu:46)
+
+
+def test_swap_blocks_inside_one_tensor_with_overlapping_runs():
+    """src and dst are the SAME cache and consecutive pairs shift blocks by one (0 -> 1, 1 -> 2, 2 -> 3): the reference
+    copies block by block in list order (cache_kernels.cu:55-66), so block 0 cascades; a merged run must not change that."""
+    ops = _ops()
+    cache = synth.tensor((12, 4, 64, 16), 9, torch.bfloat16, 1.0)
+    mapping = torch.tensor([[0, 1], [1, 2], [2, 3], [8, 5], [9, 6]], dtype=torch.int64)
+    want = cache.clone()
+    for s_, d_ in mapping.tolist():
+        want[d_] = want[s_]
+    dev = cache.cuda()
+    ops.swap_blocks(dev, dev, mapping)
+    torch.cuda.synchronize()
+    assert torch.equal(_bits(dev.cpu()), _bits(want))

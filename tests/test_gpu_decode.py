@@ -94,7 +94,7 @@ def _free_port():
 def _nccl_worker(rank, world, port, q):
     import faulthandler
     import torch.distributed as dist
-    faulthandler.dump_traceback_later(90, exit=True)  # a hang must end with a stack trace, not with the suite's timeout
+    faulthandler.dump_traceback_later(300, exit=True)  # a hang must end with a stack trace, not with the suite's timeout
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -118,6 +118,7 @@ def _nccl_worker(rank, world, port, q):
         want = full.step().float()
         got = sharded.step().float()
         rel = float((got - want).abs().max() / want.abs().max())
+        assert sharded.layers[0].key_cache.shape[1] == sharded.layers[0].kvh == 4 // world
         kv_ok = all(torch.equal(ls.key_cache, lf.key_cache[:, rank * ls.kvh:(rank + 1) * ls.kvh])
                     and torch.equal(ls.value_cache, lf.value_cache[:, rank * ls.kvh:(rank + 1) * ls.kvh])
                     for ls, lf in zip(sharded.layers[:1], full.layers[:1]))  # layer 0 sees identical inputs: cache writes bit-equal
@@ -144,7 +145,7 @@ def test_tensor_parallel_decode_step_over_nccl():
     procs = [ctx.Process(target=_nccl_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    got = sorted(q.get(timeout=120) for _ in range(2))  # drain the queue before joining
+    got = sorted(q.get(timeout=360) for _ in range(2))  # drain the queue before joining
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
@@ -158,7 +159,7 @@ def test_tensor_parallel_decode_step_over_nccl():
 def _ar_worker(rank, world, port, q):
     import faulthandler
     import torch.distributed as dist
-    faulthandler.dump_traceback_later(90, exit=True)
+    faulthandler.dump_traceback_later(300, exit=True)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -173,7 +174,14 @@ def _ar_worker(rank, world, port, q):
             return
         bad = []
         gen = torch.Generator(device=dev).manual_seed(100 + rank)
-        for dtype in (torch.bfloat16, torch.float16, torch.float32):
+        # every message once through the one-shot and once through the two-shot kernel (the threshold between them is a
+        # host-side policy, APH_AR_TWO_SHOT_BYTES forces it), then with the default policy: the calls mix freely
+        for mode in ("0", "16", None):
+          if mode is None:
+              os.environ.pop("APH_AR_TWO_SHOT_BYTES", None)
+          else:
+              os.environ["APH_AR_TWO_SHOT_BYTES"] = mode
+          for dtype in (torch.bfloat16, torch.float16, torch.float32):
             for shape in ((1, 4096), (64, 8192), (256, 8192), (3, 8), (64, 8200)):
                 for rep in range(3):
                     x = torch.randn(shape, device=dev, generator=gen).to(dtype)
@@ -188,10 +196,12 @@ def _ar_worker(rank, world, port, q):
                     assert tp.custom.should_use(x)
                     got = tp.all_reduce(x.clone())
                     if not torch.equal(got, want):
-                        bad.append((str(dtype), shape, rep, float((got.float() - want.float()).abs().max())))
+                        bad.append((mode, str(dtype), shape, rep, float((got.float() - want.float()).abs().max())))
         # all-reduce fused with the residual add + RMSNorm that follows it: against the unfused pair of kernels
         from aphrodite_fork_b200 import _custom_ops as ops
-        for dtype in (torch.bfloat16, torch.float16):
+        for mode in ("0", "16"):
+          os.environ["APH_AR_TWO_SHOT_BYTES"] = mode
+          for dtype in (torch.bfloat16, torch.float16):
             for m, h in ((1, 4096), (64, 8192), (7, 1024), (130, 5120)):
                 x = torch.randn(m, h, device=dev, generator=gen).to(dtype)
                 res = torch.randn(m, h, device=dev, generator=gen).to(dtype)
@@ -205,11 +215,12 @@ def _ar_worker(rank, world, port, q):
                 ops.fused_add_rms_norm(x2, res2, w, 1e-5)
                 tp.all_reduce_add_rms_norm(x, res, w, 1e-5)
                 if not torch.equal(res, res2):
-                    bad.append(("fused residual", str(dtype), m, h))
+                    bad.append(("fused residual", mode, str(dtype), m, h))
                 d = (x.view(torch.int16).int() - x2.view(torch.int16).int()).abs()
                 tiny = (x.float() - x2.float()).abs() <= 1e-5
                 if not bool(((d <= 2) | tiny).all()) or float(((d > 0) & ~tiny).float().mean()) > 0.01:
-                    bad.append(("fused norm", str(dtype), m, h, int(d.max())))
+                    bad.append(("fused norm", mode, str(dtype), m, h, int(d.max())))
+        os.environ.pop("APH_AR_TWO_SHOT_BYTES", None)
         # too large / misaligned messages take NCCL
         big = torch.ones(5 * 1024 * 1024, device=dev, dtype=torch.bfloat16)
         assert not tp.custom.should_use(big)
@@ -263,7 +274,7 @@ def test_one_shot_all_reduce_over_peer_memory():
     procs = [ctx.Process(target=_ar_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
-    res = [q.get(timeout=120) for _ in procs]
+    res = [q.get(timeout=360) for _ in procs]
     for p in procs:
         p.join(timeout=60)
     for rank, bad in res:

@@ -143,6 +143,43 @@ def test_gptq_marlin_gemm_8bit_weights(M, gs, zp, dtype):
         case(M, 4096, 4096, gs, dtype, zp=zp, seed=53, bits=8)
 
 
+@pytest.mark.parametrize("gs", [32, 64, 128])
+@pytest.mark.parametrize("M", [1, 16, 50, 300])
+def test_gptq_marlin_gemm_hqq_float_zero_points(M, gs):
+    # is_zp_float (HQQ, gptq_marlin.cu:1190-1300,2284-2288): uint4 weights, float16 zero points laid out like the scales,
+    # w = (q - z) * s with both steps rounded to float16; float16 only
+    K, N = 1024, 256
+    rng = np.random.default_rng(M + gs)
+    q = rng.integers(0, 16, (K, N))
+    sc = torch.from_numpy(rng.uniform(0.005, 0.02, (K // gs, N))).to(torch.float16)
+    zf = torch.from_numpy(8 + rng.uniform(-1.5, 1.5, (K // gs, N))).to(torch.float16)
+    qh = torch.from_numpy(q).to(torch.float16)
+    w_ref = (qh - zf.repeat_interleave(gs, 0)) * sc.repeat_interleave(gs, 0)  # float16 arithmetic, like the kernel's dequant
+    b = torch.from_numpy(mf.pack_weights(q, 4))
+    s_m = torch.from_numpy(mf.permute_scales(sc.numpy(), K, N, gs))
+    z_m = torch.from_numpy(mf.permute_scales(zf.numpy(), K, N, gs))
+    a = synth.tensor((M, K), 300 + M, torch.float16, 1.0)
+    ops, dev = _ops(), "cuda"
+    ws = torch.zeros(N // 64 * 16, dtype=torch.int32, device=dev)
+    e = torch.empty(0, dtype=torch.int32, device=dev)
+    args = (a.to(dev), b.to(dev), s_m.to(dev), z_m.to(dev), e, e, ws, mf.UINT4, M, N, K, True, True, False, True, True)
+    out = ops.gptq_marlin_gemm(*args)
+    check(out, oracle.gemm(a, w_ref), torch.float16, f"HQQ M{M} g{gs}")
+    assert int(ws.abs().sum()) == 0
+    ref = oracle.refcuda()
+    if ref is not None:
+        try:
+            rc = ref.gptq_marlin_gemm(*args)
+        except RuntimeError as e:  # the reference instantiates its HQQ kernel for one group size only (gptq_marlin.cu:1767-1790)
+            assert "Unsupported shapes" in str(e)
+            rc = None
+        if rc is not None:
+            assert float((out.float() - rc.float()).abs().max()) <= 2e-3 * float(rc.float().abs().max())
+    with pytest.raises(RuntimeError, match="float16"):
+        ops.gptq_marlin_gemm(a.to(dev).to(torch.bfloat16), b.to(dev), s_m.to(dev).to(torch.bfloat16), z_m.to(dev).to(torch.bfloat16), e, e,
+                             ws, mf.UINT4, M, N, K, True, True, False, True, True)
+
+
 def test_gptq_marlin_gemm_repeated_calls_leave_workspace_clean():
     # back-to-back launches share the lock buffer (arrival counters) and the scratch: results must not depend on history
     outs = []

@@ -32,5 +32,5 @@ def test_overlay_serves_cuda_calls_and_falls_back_for_unsupported_arguments():
     assert res["mode"] == "overlay"
     assert res["stand_in_calls_after_supported_call"] == [], "a supported CUDA call must not reach the reference's kernel"
     assert res["attention_max_abs_err"] < 1e-2 and res["silu_max_abs_err"] < 0.07
-    assert res["unsupported_call_reached"] == ["gptq_marlin_gemm"] and res["unsupported_call_shape"] == [4, 128]
+    assert res["unsupported_call_reached"] == ["gptq_marlin_gemm"] and res["unsupported_call_shape"] == [4, 64]
     assert res["opcheck"] == "ok"

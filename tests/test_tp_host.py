@@ -159,10 +159,17 @@ def test_one_shot_all_reduce_eligibility_rules():
     os.environ.pop("APH_AR_LIMIT_BYTES", None)
     ar = object.__new__(OneShotAllReduce)
     ar.max_size = 8 * 1024 * 1024
-    for world, ok_rows, bad_rows in ((2, 256, 513), (4, 128, 129), (8, 64, 65)):  # rows of 8192 bf16 = 16 KiB each
+    os.environ.pop("APH_AR_TWO_SHOT_BYTES", None)
+    for world in (2, 4, 8):  # rows of 8192 bf16 = 16 KiB each: the peer-memory path holds up to max_size at every world size
         ar.world_size = world
-        assert ar.should_use(fake(ok_rows, 8192)), (world, ok_rows)
-        assert not ar.should_use(fake(bad_rows, 8192)), (world, bad_rows)
+        assert ar.should_use(fake(512, 8192)), world
+        assert not ar.should_use(fake(513, 8192)), world
+    # one-shot below, two-shot from a size on (larger groups pay (world - 1) x the message for a one-shot push)
+    for world, one_shot_rows, two_shot_rows in ((2, 512, None), (4, 31, 32), (8, 7, 8)):
+        ar.world_size = world
+        assert not ar.two_shot(one_shot_rows * 16384), world
+        if two_shot_rows is not None:
+            assert ar.two_shot(two_shot_rows * 16384), world
     ar.world_size = 2
     assert not ar.should_use(fake(3, 4))                      # 24 bytes: not a multiple of 16
     assert not ar.should_use(fake(64, 128).t())               # not contiguous
@@ -178,3 +185,38 @@ def test_one_shot_all_reduce_eligibility_rules():
         assert not ar.should_use(fake(1, 4096))
     finally:
         del os.environ["APH_AR_LIMIT_BYTES"]
+
+
+def test_decode_layer_shards_partition_the_unsharded_layer():
+    """DecodeLayer.shard_of (decode.py): the ranks' shards of an unsharded layer - q / k / v and gate / up split
+    separately (linear.py:474-484), row-parallel K splits (:1279-1283), kv heads split or replicated
+    (llama.py:118-127) - tile the full tensors exactly. Pure tensor slicing: runs on the CPU."""
+    from aphrodite_fork_b200.decode import DecodeConfig, DecodeLayer
+    cfg = DecodeConfig(hidden=1024, intermediate=2048, num_heads=16, num_kv_heads=4, head_size=128, num_layers=1)
+    gen = torch.Generator().manual_seed(0)
+    full = DecodeLayer(cfg, tp.TPGroup.single(), 6, "cpu", gen)
+    d, H, KVH = cfg.head_size, cfg.num_heads, cfg.num_kv_heads
+    for t in (2, 4, 8):
+        shards = []
+        for r in range(t):
+            g = tp.TPGroup.single()
+            g.world_size, g.rank = t, r
+            shards.append(DecodeLayer.shard_of(full, g))
+        hl, kvl = H // t, max(1, KVH // t)
+        wq = full.qkv.w
+        for r, sh in enumerate(shards):
+            assert (sh.h, sh.kvh) == (hl, kvl)
+            kv_first = (r * min(t, KVH) // t) * kvl  # first kv head held by rank r (replicated once t > KVH)
+            cols = lambda c0, n: wq.scales[:, c0:c0 + n]
+            want_s = torch.cat([cols(r * hl * d, hl * d), cols(H * d + kv_first * d, kvl * d), cols(H * d + KVH * d + kv_first * d, kvl * d)], 1)
+            assert torch.equal(sh.qkv.w.scales, want_s)
+            assert sh.qkv.w.q_weight.shape == (cfg.hidden // 16, 2 * (hl + 2 * kvl) * d)
+            assert torch.equal(sh.key_cache, full.key_cache[:, kv_first:kv_first + kvl])
+            assert torch.equal(sh.value_cache, full.value_cache[:, kv_first:kv_first + kvl])
+            assert torch.equal(sh.o.w.q_weight, full.o.w.q_weight[r * hl * d // 16:(r + 1) * hl * d // 16])
+            il = cfg.intermediate // t
+            assert torch.equal(sh.gate_up.w.scales, torch.cat([full.gate_up.w.scales[:, r * il:(r + 1) * il],
+                                                               full.gate_up.w.scales[:, cfg.intermediate + r * il:cfg.intermediate + (r + 1) * il]], 1))
+            assert torch.equal(sh.down.w.q_weight, full.down.w.q_weight[r * il // 16:(r + 1) * il // 16])
+        # the row-parallel shards together hold every k16-row of o and down exactly once
+        assert torch.equal(torch.cat([sh.o.w.q_weight for sh in shards]), full.o.w.q_weight)

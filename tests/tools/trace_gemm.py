@@ -1,6 +1,6 @@
-"""One eager call of the GEMM on a big shape (for compute-sanitizer): python tools/dbg_tc_big.py M K N"""
+"""APH_GEMM_PATH=tc APH_GEMM_TRACE=gpurun_out/trace.txt python tests/tools/trace_gemm.py M K N  (one warm call, then the traced call)"""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 import aphrodite_fork_b200 as A
 A.load()
@@ -14,4 +14,4 @@ ws = torch.zeros(N // 64 * 16, dtype=torch.int32, device=dev)
 for i in range(3):
     out = A.ops.gptq_marlin_gemm(a, b, s, e, e, e, ws, 1125899907892224, M, N, K, True)
 torch.cuda.synchronize()
-print("ok", out.float().abs().mean().item(), int(ws.abs().sum()))
+print(open(os.environ["APH_GEMM_TRACE"]).read())

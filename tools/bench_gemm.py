@@ -55,7 +55,10 @@ def bench(name, K, N, M, g=128, iters=50):
 
 if __name__ == "__main__":
     A.load()
+    shapes = dict(SHAPES)
+    shapes.update({"70b_tp8_qkv": (8192, 1280), "70b_tp8_o": (1024, 8192), "70b_tp8_gate_up": (8192, 7168), "70b_tp8_down": (3584, 8192)})
     ms = [int(x) for x in sys.argv[1].split(",")] if len(sys.argv) > 1 else [1, 16, 64, 256]
-    for name, (K, N) in SHAPES.items():
-        for M in ms:
-            print(json.dumps(bench(name, K, N, M)), flush=True)
+    only = sys.argv[2].split(",") if len(sys.argv) > 2 else list(shapes)
+    for name in only:
+        K, N = shapes[name]
+        print(json.dumps({"shape": name, **{f"m{M}": bench(name, K, N, M)["us"] for M in ms}}), flush=True)
