@@ -27,8 +27,10 @@
 //   * programmatic dependent launch: the kernel triggers its dependents at once and the next GEMM of the stream
 //     fills its ring with weights while this one drains; activations / outputs are touched after griddepcontrol.wait.
 // Large batches (M >= 64) are meant for the tcgen05 path; here they run as chunks of 32 rows.
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <vector>
 
 #include <cuda.h>  // CUtensorMap types only; the encoder is fetched through the runtime (no libcuda link)
 
@@ -300,7 +302,41 @@ static int launch(const Params& p, const Operands& op, int grid, cudaStream_t st
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
+#ifdef APH_GEMM_TRACE
+  // development build only: APH_GEMM_TRACE=<file> appends a per-CTA timeline summary of this launch (synchronises!)
+  static const char* trace_path = getenv("APH_GEMM_TRACE");
+  Params pt = p;
+  if (trace_path != nullptr) {
+    cudaMalloc(&pt.trace, (size_t)grid * 8 * sizeof(unsigned long long));
+    cudaMemsetAsync(pt.trace, 0, (size_t)grid * 8 * sizeof(unsigned long long), stream);
+  }
+  const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, pt, tmB, tmA, tmS, tmZ);
+  if (trace_path != nullptr && le == cudaSuccess) {
+    std::vector<unsigned long long> h((size_t)grid * 8);
+    cudaStreamSynchronize(stream);
+    cudaMemcpy(h.data(), pt.trace, h.size() * 8, cudaMemcpyDeviceToHost);
+    cudaFree(pt.trace);
+    if (FILE* f = fopen(trace_path, "a")) {
+      unsigned long long t0 = ~0ull;
+      for (int b = 0; b < grid; ++b)
+        if (h[b * 8] && h[b * 8] < t0) t0 = h[b * 8];
+      fprintf(f, "# mma kernel NB=%d NT=%d grid=%d total=%d k_stages=%d cluster=%d STAGES=%d: ns after the first CTA's entry, min / median / max over CTAs\n",
+              NB, NT, grid, p.total, p.k_stages, cluster_split, C::STAGES);
+      const char* names[6] = {"entry", "last load issued", "first stage landed", "main loop done", "segments written", "fix-up done"};
+      for (int e = 0; e < 6; ++e) {
+        std::vector<long long> v;
+        for (int b = 0; b < grid; ++b)
+          if (h[b * 8 + e]) v.push_back((long long)(h[b * 8 + e] - t0));
+        if (v.empty()) continue;
+        std::sort(v.begin(), v.end());
+        fprintf(f, "%-20s n=%4zu  %7lld %7lld %7lld\n", names[e], v.size(), v.front(), v[v.size() / 2], v.back());
+      }
+      fclose(f);
+    }
+  }
+#else
   const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, p, tmB, tmA, tmS, tmZ);
+#endif
   APH_CHECK(le == cudaSuccess, APH_ERR_CUDA, "gptq_marlin_gemm: launch failed: %s", cudaGetErrorString(le));
   return APH_OK;
 }
@@ -724,6 +760,7 @@ extern "C" int aph_gptq_marlin_gemm(void* c, const void* a, const void* b_q_weig
   }
 
   mg::Params p;
+  p.trace = nullptr;
   p.s = (const uint8_t*)b_scales;
   p.zp = has_zp ? (const uint8_t*)b_zeros : nullptr;
   p.c = c;

@@ -28,6 +28,7 @@ struct Params {
   int k_stages;        // ceil(K / (128 * KG)) pipeline stages over the whole K
   int total;           // n_slices * k_stages work items (slice-major); CTA i owns [i*total/grid, (i+1)*total/grid)
   int dbg;             // development switch (APH_GEMM_DBG): 1 = skip the math, 2 = skip the loads
+  unsigned long long* trace;  // development (APH_GEMM_TRACE builds): [grid][8] globaltimer stamps, else null
   int cluster_split;   // S >= 2: aligned split-K plan launched as thread-block clusters of S CTAs (the S pieces of one
                        // slice); their partials meet in rank 0's shared memory instead of the scratch. 0: scratch + counters
 };
@@ -129,6 +130,22 @@ __device__ __noinline__ void sum_shared_slices(scalar_t* c, const float* scratch
 //   tmB: weights as a 2-D array of 8-byte words [K/16][N], box [8*KG][NT]
 //   tmA: activations [M][K] 16-bit, box [MP][64], SWIZZLE_128B, rows >= M read as zero
 //   tmS: scales [groups][N] 16-bit, box [KG*gps][NT];  tmZ: zero points [groups][N/8] 32-bit, box [KG*gps][NT/8]
+#ifdef APH_GEMM_TRACE
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define APH_MMA_STAMP(slot, cond)                                              \
+  do {                                                                         \
+    if (p.trace != nullptr && (cond)) p.trace[blockIdx.x * 8 + (slot)] = global_ns(); \
+  } while (0)
+#else
+#define APH_MMA_STAMP(slot, cond) \
+  do {                            \
+  } while (0)
+#endif
+
 template <typename scalar_t, int NB, int NT, bool HAS_ZP>
 __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
     marlin_w4a16_kernel(const Params p, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmA,
@@ -155,6 +172,7 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
   // fix-up flags of shared slice j (0, 1): [4j] slice, [4j+1] first contributing CTA, [4j+2] contributors, [4j+3] am I the last arriver
   int* s_flag = reinterpret_cast<int*>(smem + STAGES * C::STAGE_BYTES + C::RED_BYTES + 2 * STAGES * 8);
 
+  APH_MMA_STAMP(0, tid == 0);  // entry
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(full_bar + s * 8, 1);
@@ -252,6 +270,7 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
       }
     });
     if (!waited) end_prologue();
+    APH_MMA_STAMP(1, true);  // producer: last load issued
 #ifdef APH_RING_FAULT
     if (held_st >= 0) {
       load_weights(held_st, held_slice, held_ks);
@@ -364,6 +383,7 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
     for (int it = it0 + ((sg - it0) & (SG - 1)); it < it0 + cnt; it += SG) {
       const int st = ring.slot(it);
       mbar_wait(full_bar + st * 8, ring.phase(it));
+      APH_MMA_STAMP(2, tid == 0 && it == 0);  // first stage landed
       ring.advance(it);
       const uint32_t sbase = smem_base + st * C::STAGE_BYTES;
       if (p.dbg != 1)
@@ -416,6 +436,7 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
       flush(sc);
     }
 
+    APH_MMA_STAMP(3, tid == 0);  // main loop of the (last) segment done
     // ---------------- reduce the consumer warps through shared memory ----------------
 #pragma unroll
     for (int j = 0; j < 4; ++j)
@@ -507,11 +528,13 @@ __global__ void __launch_bounds__(THREADS, Cfg<scalar_t, NB, NT>::CTAS_PER_SM)
     it0 += cnt;
   });
 
+  APH_MMA_STAMP(4, tid == 0);  // segments written / published
   // ---------------- deferred fix-up: the last arriver of a shared slice sums the partials in CTA order ----------------
   if (n_shared == 0) return;
   named_bar_sync(1, CT);  // flags visible, `red` free
   sum_shared_slices<scalar_t, MP, NT, CT>(reinterpret_cast<scalar_t*>(p.c) + (int64_t)p.m0 * p.N, p.scratch, p.counters, p.N, p.m_rows,
                                           p.k_stages, p.total, s_flag, n_shared, reinterpret_cast<int*>(red), tid);
+  APH_MMA_STAMP(5, tid == 0);  // fix-up done
 }
 
 }  // namespace mg

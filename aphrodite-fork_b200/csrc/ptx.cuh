@@ -14,17 +14,20 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+// The suspend-time hint lets a waiting warp sleep inside try_wait until the phase completes (it is woken by the
+// barrier) instead of coming back every few hundred cycles: in the tcgen05 GEMM a quarter of all issued instructions
+// were such polls (ncu source view, profiles/r02_ncu_source_gemm_tc_gate_up_m64.txt).
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
       "WAIT_LOOP:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
       "@p bra DONE;\n"
       "bra WAIT_LOOP;\n"
       "DONE:\n"
       "}\n" ::"r"(bar),
-      "r"(parity)
+      "r"(parity), "r"(0x989680)
       : "memory");
 }
 // 1-D bulk async copy global -> shared, completion counted in bytes on an mbarrier.

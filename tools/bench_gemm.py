@@ -4,6 +4,8 @@ import json
 import os
 import sys
 
+os.environ.setdefault("APH_DEV_ENV", "1")  # development overrides are re-read on every call
+
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import aphrodite_fork_b200 as A
