@@ -96,7 +96,8 @@ static Split choose_split(int num_seqs, int num_heads, int num_kv_heads, int hea
     }
     // few waves run in rounds (1.15 waves cost two), many waves flow
     const double rounds = w <= 3.0 ? (double)(int64_t)(w + 0.999) : w;
-    consider((int)pt, z, cp, rounds * (double)(pt + (w <= 1.0 ? 600 : 370)) + (np > 1 ? 150.0 : 0.0));
+    // the reduce kernel hides under the last wave of a multi-wave grid (~150); behind a single wave it is exposed (~500)
+    consider((int)pt, z, cp, rounds * (double)(pt + (w <= 1.0 ? 600 : 370)) + (np > 1 ? (w <= 1.0 ? 500.0 : 150.0) : 0.0));
   }
   // ---- one-wave candidates ----
   if (e_w == nullptr && e_m == nullptr && units > 0 && units <= slots) {

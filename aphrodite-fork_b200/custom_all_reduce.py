@@ -57,7 +57,9 @@ class OneShotAllReduce:
             return int(env) > 0 and nbytes >= int(env)
         if self.world_size <= 2:
             return False
-        return nbytes >= (512 * 1024 if self.world_size <= 4 else 128 * 1024)
+        # measured on 8 B200s (profiles/r02_all_reduce_n8.jsonl, us one-shot / two-shot): 256 KiB 11.6 / 14.9,
+        # 1 MiB 25.4 / 16.9, 4 MiB 60 / 27 - the curves cross near 512 KiB
+        return nbytes >= 512 * 1024
 
     def should_use(self, x: torch.Tensor) -> bool:
         """One-shot pushes world x the message per rank, so on larger groups it only pays up to a size. The reference

@@ -165,6 +165,15 @@ class TPGroup:
             self.custom, self.custom_error = None, f"{type(e).__name__}: {e}"
         return self.custom is not None
 
+    def describe(self, x: torch.Tensor) -> str:
+        """Which exchange a message like `x` takes (for benchmark records)."""
+        if self.world_size == 1:
+            return "none"
+        if self.custom is None or not self.custom.should_use(x):
+            return "NCCL" + (f" ({self.custom_error})" if self.custom_error else "")
+        kind = "two-shot" if self.custom.two_shot(x.numel() * x.element_size()) else "one-shot"
+        return f"{kind} peer-memory kernel fused with the residual add + RMSNorm (csrc/all_reduce.cu)"
+
     def all_reduce(self, x: torch.Tensor) -> torch.Tensor:
         if self.world_size > 1:
             if self.custom is not None and self.custom.should_use(x):

@@ -472,6 +472,7 @@ def run_ours(args):
     one = torch.tensor(1.0, device=dev)
     pool_bytes = kv_bytes(BATCH, CTX, KVHr, D, 1)
     npools = max(2, -(-(1 << 30) // pool_bytes))
+    npools += npools % 2  # even: the end-to-end leg's two lanes take alternate pools
     pools = []
     for _ in range(npools):
         src = ((torch.rand(nblk, KVHr, D // 16, BS, 16, generator=g, device=dev) * 2 - 1) * sc).to(torch.bfloat16)
@@ -503,6 +504,17 @@ def run_ours(args):
 
     for i in range(warm):
         step(i)
+    # the K timed steps are replayed from one CUDA graph (the reference replays captured decode steps the same way):
+    # a rank's kernel is only ~20 us at 8 GPUs, eager launches from Python would measure the host, not the device
+    side = torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        timed_graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(timed_graph, stream=side):
+            for i in range(steps):
+                step(i)
+    torch.cuda.current_stream().wait_stream(side)
+    timed_graph.replay()  # untimed: K more warm-up steps
     sampler = ClockSampler(local)
     barrier()
     if rank == 0:
@@ -510,8 +522,7 @@ def run_ours(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record()
-    for i in range(steps):
-        step(i)
+    timed_graph.replay()  # exactly K steps
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
@@ -522,6 +533,10 @@ def run_ours(args):
         ms = float(t.item())
     # algorithmic bytes: K and V of every kv head of the GLOBAL problem once (a kv head replicated over several ranks
     # still counts once); what one rank's launch streams is pool_bytes
+    # kernels of this repo per step: the attention kernel, plus the split-K reduce kernel unless the partitions are merged
+    # on chip by thread-block clusters (no workspace needed then)
+    capi = A.c_api()
+    launches_per_step = 2 if capi.aph_paged_attention_workspace_bytes(BATCH, Hr, KVHr, D, CTX) > 0 else 1
     per_step_bytes = kv_bytes(BATCH, CTX, KVH, D, 1)
     value = per_step_bytes * steps / (ms * 1e-3) / 1e9
     per_gpu = pool_bytes * steps / (ms * 1e-3) / 1e9
@@ -570,44 +585,49 @@ def run_ours(args):
     out_h = [torch.empty(BATCH, Hr, D, dtype=torch.bfloat16, pin_memory=True) for _ in range(NBUF)]
     h2d = sum(n for _, (o, n, shape, dt) in offs.items())
     d2h = out_h[0].numel() * out_h[0].element_size()
-    s_in, s_out = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
-    s_cmp = torch.cuda.current_stream()
-    ev_in = [torch.cuda.Event() for _ in range(NBUF)]     # upload of buffer b finished
-    ev_cmp = [torch.cuda.Event() for _ in range(NBUF)]    # kernels reading buffer b finished
-    ev_out = [torch.cuda.Event() for _ in range(NBUF)]    # download into out_h[b] finished
+    # One step = upload of ITS inputs, write_to_paged_cache + forward_decode, download of ITS output. The way the
+    # reference serves decode (worker/model_runner.py:1487-1646 replays one captured CUDA graph per step), every step is
+    # one graph replay; two lanes (stream + staging buffers each) take alternate steps so that a step's copies run under
+    # its neighbour's kernels. Consecutive steps use different KV pools, so the lanes never touch the same cache.
+    lanes = [torch.cuda.Stream(device=dev) for _ in range(NBUF)]
+    s_main = torch.cuda.current_stream()
 
-    def e2e_step(i):
-        b = i % NBUF
-        kc, vc = pools[i % npools]
-        with torch.cuda.stream(s_in):
-            s_in.wait_event(ev_cmp[b])                    # the kernels of step i-2 are done with this staging buffer
-            in_d[b].copy_(in_h, non_blocking=True)
-            ev_in[b].record(s_in)
-        s_cmp.wait_event(ev_in[b])
+    def e2e_body(b, pool):
+        kc, vc = pools[pool]
+        in_d[b].copy_(in_h, non_blocking=True)
         v = dv[b]
         A.PagedAttention.write_to_paged_cache(v["newkv"][:, 0], v["newkv"][:, 1], kc, vc, v["slots"], "fp8", one, one)
         o = A.PagedAttention.forward_decode(v["q"], kc, vc, v["bt"], v["sl"], CTX, "fp8", KVHr, sc, None, one, one)
-        ev_cmp[b].record(s_cmp)
-        with torch.cuda.stream(s_out):
-            s_out.wait_event(ev_cmp[b])
-            out_h[b].copy_(o, non_blocking=True)
-            o.record_stream(s_out)
-            ev_out[b].record(s_out)
+        out_h[b].copy_(o, non_blocking=True)
 
-    def e2e_drain():
-        for b in range(NBUF):
-            s_cmp.wait_event(ev_out[b])
-            s_cmp.wait_event(ev_in[b])
+    graphs = {}
+    for pool in range(npools):  # npools is even: pool parity = lane
+        b = pool % NBUF
+        lanes[b].wait_stream(s_main)
+        with torch.cuda.stream(lanes[b]):
+            e2e_body(b, pool)  # warm-up outside capture
+            lanes[b].synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=lanes[b]):
+                e2e_body(b, pool)
+        graphs[pool] = g
 
-    for i in range(warm):
-        e2e_step(i)
-    e2e_drain()
+    def e2e_run(n):
+        ev = torch.cuda.Event()
+        ev.record(s_main)
+        for ln in lanes:
+            ln.wait_event(ev)
+        for i in range(n):
+            with torch.cuda.stream(lanes[i % NBUF]):
+                graphs[i % npools].replay()
+        for ln in lanes:
+            s_main.wait_stream(ln)  # the last downloads are inside the timed region
+
+    e2e_run(warm)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for i in range(steps):
-        e2e_step(i)
-    e2e_drain()  # the last downloads are inside the timed region
+    e2e_run(steps)
     e1.record()
     barrier()
     ems = e0.elapsed_time(e1)
@@ -656,8 +676,8 @@ def run_ours(args):
                     "ms_per_step": round(ems / steps, 5),
                     "api": "PagedAttention.write_to_paged_cache + forward_decode; every step uploads its q / new K,V token / "
                            "block tables / seq lens / slot mapping from ONE packed pinned host buffer and downloads its "
-                           "output; copy-in, compute and copy-out streams with two staging buffers overlap neighbouring steps"},
-            "gpu_launches": 2 * steps,
+                           "output; a step is one CUDA-graph replay (copies included), two lanes take alternate steps"},
+            "gpu_launches": launches_per_step * steps,
             "clocks": clocks,
             "extras": extras,
         }

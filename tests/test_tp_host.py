@@ -165,7 +165,7 @@ def test_one_shot_all_reduce_eligibility_rules():
         assert ar.should_use(fake(512, 8192)), world
         assert not ar.should_use(fake(513, 8192)), world
     # one-shot below, two-shot from a size on (larger groups pay (world - 1) x the message for a one-shot push)
-    for world, one_shot_rows, two_shot_rows in ((2, 512, None), (4, 31, 32), (8, 7, 8)):
+    for world, one_shot_rows, two_shot_rows in ((2, 512, None), (4, 31, 32), (8, 31, 32)):
         ar.world_size = world
         assert not ar.two_shot(one_shot_rows * 16384), world
         if two_shot_rows is not None:
