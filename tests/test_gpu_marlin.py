@@ -170,8 +170,8 @@ def test_gptq_marlin_gemm_hqq_float_zero_points(M, gs):
     if ref is not None:
         try:
             rc = ref.gptq_marlin_gemm(*args)
-        except RuntimeError as e:  # the reference instantiates its HQQ kernel for one group size only (gptq_marlin.cu:1767-1790)
-            assert "Unsupported shapes" in str(e)
+        except RuntimeError as err:  # the reference instantiates its HQQ kernel for one group size only (gptq_marlin.cu:1767-1790)
+            assert "Unsupported shapes" in str(err)
             rc = None
         if rc is not None:
             assert float((out.float() - rc.float()).abs().max()) <= 2e-3 * float(rc.float().abs().max())
