@@ -41,8 +41,9 @@ BATCH, CTX = 64, 4096
 METRIC = "paged-attn decode KV GB/s"
 # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this workload at N = 1, from an `ncu --set full` capture of
 # THIS command line; not measured in the run, so the line names the file it comes from
-NCU_TRAFFIC_BYTES = 550_200_000
-NCU_TRAFFIC_SOURCE = "profiles/r01_ncu_full_attention_final.txt (ncu --set full, main kernel 539.1 MB read + 6.8 MB written, reduce 4.3 MB read)"
+NCU_TRAFFIC_BYTES = 545_738_240
+NCU_TRAFFIC_SOURCE = ("profiles/r02_ncu_attention_c2_c4tp8.txt (ncu --set full of the split-K kernel at C2: 539.06 MB read + 6.68 MB "
+                      "written; the reduce kernel that follows re-reads the 6.7 MB of partials)")
 WORKLOAD = "C2: paged_attention_v2 Llama-3-8B shape 32q/8kv d128, fp8_e4m3 KV, block 16, batch 64 x ctx 4096"
 
 
