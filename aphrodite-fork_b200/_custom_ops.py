@@ -232,6 +232,17 @@ def advance_step_flashattn(num_seqs: int, num_queries: int, block_size: int, inp
                                             input_positions, seq_lens, slot_mapping, block_tables)
 
 
+# aphrodite/_custom_ops.py:236-251
+def advance_step_flashinfer(num_seqs: int, num_queries: int, block_size: int, input_tokens: torch.Tensor,
+                            sampled_token_ids: torch.Tensor, input_positions: torch.Tensor, seq_lens: torch.Tensor,
+                            slot_mapping: torch.Tensor, block_tables: torch.Tensor, paged_kv_indices: torch.Tensor,
+                            paged_kv_indptr: torch.Tensor, paged_kv_last_page_len: torch.Tensor,
+                            block_table_bound: torch.Tensor) -> None:
+    return _ops()[0].advance_step_flashinfer(num_seqs, num_queries, block_size, input_tokens, sampled_token_ids,
+                                             input_positions, seq_lens, slot_mapping, block_tables, paged_kv_indices,
+                                             paged_kv_indptr, paged_kv_last_page_len, block_table_bound)
+
+
 # aphrodite/_custom_ops.py:1475-1518: the MLA cache ops
 def concat_and_cache_mla(kv_c: torch.Tensor, k_pe: torch.Tensor, kv_cache: torch.Tensor, slot_mapping: torch.Tensor,
                          kv_cache_dtype: str, scale: torch.Tensor) -> None:

@@ -100,20 +100,39 @@ def build(verbose: bool = False) -> str:
     return libpath
 
 
+# translation units a variant build may recompile: (object stem, source, extra flags, flag prefixes that select it)
+_VARIANT_UNITS = (
+    ("marlin_gemm", "marlin_gemm.cu", [], ("-DAPH_RING", "-DAPH_GEMM")),
+    ("paged_attention", "paged_attention.cu", [], ("-DAPH_PA_",)),
+    ("paged_attention_d128", "paged_attention_inst.cu", ["-DAPH_PA_HEAD_SIZE=128"], ("-DAPH_PA_",)),
+)
+
+
 def build_variant(name: str, extra_flags: list[str]) -> str:
-    """Development: the library with marlin_gemm.cu recompiled with `extra_flags`, in aphrodite-fork_b200/lib_<name>/
-    (libaphrodite_b200.so + a copy of _C_b200.so, which finds its sibling through its $ORIGIN rpath). Select it with
-    APH_B200_LIB_DIR. Used by tests/tools/ring_fault_proof.py (-DAPH_RING_FAULT, -DAPH_RING_LEGACY)."""
+    """Development: the library with the translation units `extra_flags` address recompiled with them, in
+    aphrodite-fork_b200/lib_<name>/ (libaphrodite_b200.so + copies of the torch bindings, which find their sibling
+    through an $ORIGIN rpath). Select it with APH_B200_LIB_DIR. Used by tests/tools/ring_fault_proof.py
+    (-DAPH_RING_FAULT, -DAPH_RING_LEGACY), the GEMM trace (-DAPH_GEMM_TRACE) and attention experiments (any -DAPH_PA_...
+    flag recompiles paged_attention.cu and the head-size-128 kernels)."""
     import shutil
     build()
     out_dir = os.path.join(HERE, "lib_" + name)
+    var_obj = os.path.join(OBJ, "variants", name)
     os.makedirs(out_dir, exist_ok=True)
-    src = os.path.join(CSRC, "marlin_gemm.cu")
-    obj = os.path.join(OBJ, f"marlin_gemm_{name}.o")
-    if _newer(obj, [src, *_headers()]):
-        _run([NVCC, *NVCC_FLAGS, *extra_flags, "-c", src, "-o", obj])
-    objs = [os.path.join(OBJ, f) for f in sorted(os.listdir(OBJ))
-            if f.endswith(".o") and not f.startswith("marlin_gemm")] + [obj]
+    os.makedirs(var_obj, exist_ok=True)
+    rebuilt, replaced = [], set()
+    for stem, src_name, more, prefixes in _VARIANT_UNITS:
+        if not any(f.startswith(prefixes) for f in extra_flags):
+            continue
+        src = os.path.join(CSRC, src_name)
+        obj = os.path.join(var_obj, stem + ".o")
+        if _newer(obj, [src, *_headers()]):
+            _run([NVCC, *NVCC_FLAGS, *extra_flags, *more, "-c", src, "-o", obj])
+        rebuilt.append(obj)
+        replaced.add(stem + ".o")
+    if not rebuilt:
+        raise SystemExit(f"no translation unit is selected by {extra_flags}")
+    objs = [os.path.join(OBJ, f) for f in sorted(os.listdir(OBJ)) if f.endswith(".o") and f not in replaced] + rebuilt
     libpath = os.path.join(out_dir, "libaphrodite_b200.so")
     if _newer(libpath, objs):
         _run([NVCC, "-shared", "-o", libpath, *objs, "-gencode", "arch=compute_100a,code=sm_100a"])

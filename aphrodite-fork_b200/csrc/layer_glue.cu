@@ -293,6 +293,94 @@ __global__ void __launch_bounds__(256)
   slot_mapping[q] = (int64_t)(block_tables[block_tables_stride * q + pos / block_size] * block_size + pos % block_size);
 }
 
+// The FlashInfer flavour of the same bookkeeping (prepare_inputs/advance_step.cu:91-167): besides the per-query
+// updates it rebuilds FlashInfer's CSR view of the block tables (paged_kv_indptr / paged_kv_indices /
+// paged_kv_last_page_len). The reference runs three launches with a quadratic prefix sum; here one CTA does the
+// per-query pass and a chunked block scan of the page counts (kernel 1), then a grid copies each row's live pages
+// into the flat list (kernel 2).
+__global__ void __launch_bounds__(1024)
+    advance_step_flashinfer_kernel(int num_seqs, int num_queries, int block_size, int64_t* __restrict__ input_tokens,
+                                   const int64_t* __restrict__ sampled_token_ids, int64_t* __restrict__ input_positions,
+                                   int* __restrict__ seq_lens, int64_t* __restrict__ slot_mapping,
+                                   const int* __restrict__ block_tables, int64_t block_tables_stride,
+                                   int* __restrict__ paged_kv_indptr, int* __restrict__ paged_kv_last_page_len,
+                                   int* __restrict__ block_table_bound) {
+  __shared__ int warp_sums[32];
+  __shared__ int carry_s;
+  pdl_trigger();
+  pdl_wait();
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = num_queries + tid; i < num_seqs; i += blockDim.x) {
+    input_tokens[i] = 0;
+    input_positions[i] = 0;
+    slot_mapping[i] = -1;
+  }
+  if (tid == 0) {
+    carry_s = 0;
+    paged_kv_indptr[0] = 0;
+  }
+  __syncthreads();
+  for (int base = 0; base < num_queries; base += blockDim.x) {
+    const int q = base + tid;
+    int bound = 0;
+    if (q < num_queries) {
+      input_tokens[q] = sampled_token_ids[q];
+      const int next_len = seq_lens[q] + 1, pos = next_len - 1;
+      const int blk = pos / block_size, off = pos % block_size;
+      seq_lens[q] = next_len;
+      input_positions[q] = pos;
+      paged_kv_last_page_len[q] = off + 1;
+      slot_mapping[q] = (int64_t)(block_tables[block_tables_stride * q + blk] * block_size + off);
+      bound = (next_len + block_size - 1) / block_size;
+      block_table_bound[q] = bound;
+    }
+    int incl = bound;  // inclusive scan of this chunk: warp shuffles, then the warp totals
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int up = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += up;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int w = warp_sums[lane];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, w, d);
+        if (lane >= d) w += up;
+      }
+      warp_sums[lane] = w;
+    }
+    __syncthreads();
+    const int carry = carry_s;
+    incl += carry + (warp ? warp_sums[warp - 1] : 0);
+    if (q < num_queries) paged_kv_indptr[q + 1] = incl;
+    __syncthreads();
+    if (tid == blockDim.x - 1) carry_s = incl;
+    __syncthreads();
+  }
+  const int total = carry_s;  // CUDA-graph padding rows point at the end of the list
+  for (int i = num_queries + 1 + tid; i <= num_seqs; i += blockDim.x) paged_kv_indptr[i] = total;
+}
+
+// One CTA per (row, 1024-column chunk): paged_kv_indices[indptr[q] + col] = block_tables[q][col] for col < bound[q].
+__global__ void __launch_bounds__(256)
+    advance_step_flashinfer_indices_kernel(const int* __restrict__ block_tables, int64_t block_tables_stride,
+                                           int* __restrict__ paged_kv_indices, int64_t indices_capacity,
+                                           const int* __restrict__ paged_kv_indptr, const int* __restrict__ block_table_bound) {
+  pdl_trigger();
+  pdl_wait();
+  const int q = blockIdx.y;
+  const int bound = block_table_bound[q];
+  const int64_t start = paged_kv_indptr[q];
+  const int* row = block_tables + block_tables_stride * q;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int col = (blockIdx.x * 4 + r) * 256 + threadIdx.x;
+    if (col < bound && col < block_tables_stride && start + col < indices_capacity) paged_kv_indices[start + col] = row[col];
+  }
+}
+
 template <typename T, bool FUSED>
 int launch_norm(T* out, T* input, T* residual, const T* weight, float eps, int64_t tokens, int hidden, int64_t in_stride,
                 cudaStream_t stream) {
@@ -456,6 +544,31 @@ extern "C" int aph_rotary_embedding(const int64_t* positions, void* query, void*
   APH_CHECK(positions && query && cos_sin_cache, APH_ERR_INVALID_ARGUMENT, "%s: null tensor", op);
   APH_DISPATCH_DT(dtype, op, launch_rope<T>(positions, (T*)query, (T*)key, (const T*)cos_sin_cache, cos_sin_cache_offsets, rot_dim, query_stride, key_stride,
                                             num_heads, num_kv_heads, head_size, is_neox != 0, num_tokens, (cudaStream_t)stream));
+}
+
+extern "C" int aph_advance_step_flashinfer(int num_seqs, int num_queries, int block_size, int64_t* input_tokens,
+                                           const int64_t* sampled_token_ids, int64_t* input_positions, int32_t* seq_lens,
+                                           int64_t* slot_mapping, const int32_t* block_tables, int64_t block_tables_stride,
+                                           int32_t* paged_kv_indices, int64_t paged_kv_indices_len, int32_t* paged_kv_indptr,
+                                           int32_t* paged_kv_last_page_len, int32_t* block_table_bound, void* stream) {
+  const char* op = "advance_step_flashinfer";
+  APH_CHECK(num_seqs >= 0 && num_queries >= 0 && num_queries <= num_seqs && block_size > 0, APH_ERR_INVALID_ARGUMENT,
+            "%s: need 0 <= num_queries <= num_seqs and block_size > 0", op);
+  APH_CHECK(block_tables_stride >= 0 && paged_kv_indices_len >= 0, APH_ERR_INVALID_ARGUMENT, "%s: negative stride or length", op);
+  APH_CHECK(paged_kv_indptr, APH_ERR_INVALID_ARGUMENT, "%s: null paged_kv_indptr", op);
+  APH_CHECK(num_seqs == 0 || (input_tokens && (sampled_token_ids || num_queries == 0) && input_positions && seq_lens && slot_mapping &&
+                              block_tables && paged_kv_last_page_len && block_table_bound && (paged_kv_indices || paged_kv_indices_len == 0)),
+            APH_ERR_INVALID_ARGUMENT, "%s: null tensor", op);
+  APH_CHECK(num_queries <= 65535, APH_ERR_UNSUPPORTED, "%s: num_queries = %d is above the 65535 rows one launch covers", op, num_queries);
+  APH_LAUNCH_PDL(advance_step_flashinfer_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream, num_seqs, num_queries, block_size,
+                 input_tokens, sampled_token_ids, input_positions, seq_lens, slot_mapping, block_tables, block_tables_stride,
+                 paged_kv_indptr, paged_kv_last_page_len, block_table_bound);
+  if (num_queries == 0 || block_tables_stride == 0) return APH_OK;
+  const unsigned chunks = (unsigned)((block_tables_stride + 1023) / 1024);
+  APH_LAUNCH_PDL(advance_step_flashinfer_indices_kernel, dim3(chunks, (unsigned)num_queries), dim3(256), 0, (cudaStream_t)stream,
+                 block_tables, block_tables_stride, paged_kv_indices, paged_kv_indices_len, (const int*)paged_kv_indptr,
+                 (const int*)block_table_bound);
+  return APH_OK;
 }
 
 extern "C" int aph_advance_step_flashattn(int num_seqs, int num_queries, int block_size, int64_t* input_tokens,

@@ -443,12 +443,12 @@ static size_t scratch_bytes_tc(int64_t M, int64_t N, int64_t K) {
   return worst;
 }
 
-template <typename scalar_t, int MB, bool HAS_ZP, int BITS = 4, bool ZPF = false>
+template <typename scalar_t, int MB, bool HAS_ZP, int BITS = 4, bool ZPF = false, bool G128 = false>
 static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t scratch_bytes, cudaStream_t stream) {
   using C = mgtc::Cfg<scalar_t, MB, BITS>;
   constexpr int WPC = BITS / 4;    // 8-byte words per weight column and k16-row
   constexpr int PACK = 32 / BITS;  // zero points per int32
-  auto kern = mgtc::marlin_w4a16_tc_kernel<scalar_t, MB, HAS_ZP, BITS, ZPF>;
+  auto kern = mgtc::marlin_w4a16_tc_kernel<scalar_t, MB, HAS_ZP, BITS, ZPF, G128>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -474,7 +474,7 @@ static int launch_tc(mgtc::Params p, const Operands& op, float* scratch, size_t 
         cfg.attrs = at;
         cfg.numAttrs = 1;
         int n = 0;
-        if (cudaOccupancyMaxActiveClusters(&n, mgtc::marlin_w4a16_tc_kernel<scalar_t, MB, HAS_ZP, BITS, ZPF>, &cfg) != cudaSuccess || n <= 0) {
+        if (cudaOccupancyMaxActiveClusters(&n, mgtc::marlin_w4a16_tc_kernel<scalar_t, MB, HAS_ZP, BITS, ZPF, G128>, &cfg) != cudaSuccess || n <= 0) {
           (void)cudaGetLastError();
           n = -1;
         }
@@ -640,19 +640,25 @@ static int run_typed_tc(const Params& p0, const Operands& op0, bool has_zp, int 
       if (st != APH_OK) return st;
       continue;
     }
-#define APH_TC_CASE(MBV)                                                                                  \
-  case MBV:                                                                                               \
-    st = has_zp ? launch_tc<scalar_t, MBV, true>(p, op, scratch, scratch_bytes, stream)                   \
-                : launch_tc<scalar_t, MBV, false>(p, op, scratch, scratch_bytes, stream);                 \
+    // group_size 128 = one group per 128-k stage has a build of its own (mgtc: G128)
+    const bool g128 = p.group_size == 128 && p.group_size < p.K;
+#define APH_TC_CASE(MBV)                                                                                      \
+  case MBV:                                                                                                   \
+    if (g128)                                                                                                 \
+      st = has_zp ? launch_tc<scalar_t, MBV, true, 4, false, true>(p, op, scratch, scratch_bytes, stream)     \
+                  : launch_tc<scalar_t, MBV, false, 4, false, true>(p, op, scratch, scratch_bytes, stream);   \
+    else                                                                                                      \
+      st = has_zp ? launch_tc<scalar_t, MBV, true>(p, op, scratch, scratch_bytes, stream)                     \
+                  : launch_tc<scalar_t, MBV, false>(p, op, scratch, scratch_bytes, stream);                   \
     break;
     switch (tile_rows_tc(rows)) {
       APH_TC_CASE(16)
       APH_TC_CASE(32)
       APH_TC_CASE(64)
       APH_TC_CASE(128)
+      APH_TC_CASE(256)
       default:
-        st = has_zp ? launch_tc<scalar_t, 256, true>(p, op, scratch, scratch_bytes, stream)
-                    : launch_tc<scalar_t, 256, false>(p, op, scratch, scratch_bytes, stream);
+        st = set_error(APH_ERR_INVALID_ARGUMENT, "gptq_marlin_gemm: no batch tile for %lld rows", (long long)rows);
         break;
     }
 #undef APH_TC_CASE

@@ -159,7 +159,10 @@ struct SegIter {
 };
 
 // ZPF: the zero points are 16-bit FLOATS laid out like the scales (HQQ, gptq_marlin.cu:1190-1300): w = (q - z) * s
-template <typename scalar_t, int MB, bool HAS_ZP, int BITS = 4, bool ZPF = false>
+// G128: the build for group_size == 128 == one group per stage (the C3 / C4 case): the grouping tests of the generic
+// build (grouped? how many groups per stage? which rows start one?) are compile-time facts, and the dequantisers'
+// arithmetic becomes one straight block the scheduler can interleave freely
+template <typename scalar_t, int MB, bool HAS_ZP, int BITS = 4, bool ZPF = false, bool G128 = false>
 __global__ void __launch_bounds__(THREADS, 1)
     marlin_w4a16_tc_kernel(const Params p, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmA,
                            const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUtensorMap tmZ) {
@@ -175,8 +178,8 @@ __global__ void __launch_bounds__(THREADS, 1)
 #endif
   // the warp index through a shuffle: ptxas then knows the role branches below are warp-uniform
   const int w = __shfl_sync(0xffffffffu, tid >> 5, 0);
-  const bool grouped = p.group_size < p.K;
-  const int gps = grouped ? KSTAGE / p.group_size : 0;  // groups per stage (1, 2, 4)
+  const bool grouped = G128 || p.group_size < p.K;
+  const int gps = G128 ? 1 : grouped ? KSTAGE / p.group_size : 0;  // groups per stage (1, 2, 4)
   const int G = gridDim.x, T = p.total, KS = p.k_stages;
   const int CS = p.cluster_split;
   // stream-K: equal contiguous ranges of the flattened (tile, stage) list. Cluster split-K: the r-th part of one tile.
@@ -383,9 +386,11 @@ __global__ void __launch_bounds__(THREADS, 1)
       // This CTA owns all 512 TMEM columns, so its allocation starts at lane 0, column 0.
       if (tmem_base != 0) __trap();
       constexpr uint32_t tmem0 = 0;
-      int it = 0;
+      int it = 0;  // global index of the segment's first stage
       bool ok = false;  // result of an early, non-blocking look at the barrier of this issuer's next stage
-      RingCursor<SA> ring;  // NI == 1: every stage; NI == 2: the stages of group mi
+      // NI == 1: every stage; NI == 2: the stages of group mi, i.e. those with (index & 1) == mi
+      using Cursor = typename std::conditional<NI == 2, GroupCursor<SA>, RingCursor<SA>>::type;
+      Cursor ring(mi);
       APH_SEGMENTS {
         APH_SEG_VARS
         const int db = seg % NDBUF;
@@ -393,29 +398,31 @@ __global__ void __launch_bounds__(THREADS, 1)
         tc_fence_after();
         const uint32_t d_tmem = tmem0 + (db * NI + mi) * MB;
         uint32_t acc = 0;
+        const int it_seg = it;
+        it += k1 - k0;
 #pragma unroll 1
-        for (int ks = k0; ks < k1; ++ks, ++it) {
-          if (NI > 1 && (it % NI) != mi) continue;
-          const int sa = ring.slot(it);
+        for (int ks = k0 + (NI == 2 ? ((mi ^ it_seg) & 1) : 0); ks < k1; ks += NI) {
+          const int its = it_seg + (ks - k0);
+          const int sa = ring.slot(its);
 #ifdef APH_GEMM_TRACE
-          const bool tr = p.trace != nullptr && blockIdx.x == 0 && it < 64 && lane == 0;
-          if (tr) p.trace[it * 8 + 0] = clock64();
+          const bool tr = p.trace != nullptr && blockIdx.x == 0 && its < 64 && lane == 0;
+          if (tr) p.trace[its * 8 + 0] = clock64();
 #endif
-          if (!ok) mbar_wait(ready_bar + sa * 8, ring.phase(it));  // activations landed and dequantised weights are in TMEM
-          ring.advance(it);
+          if (!ok) mbar_wait(ready_bar + sa * 8, ring.phase(its));  // activations landed and dequantised weights are in TMEM
+          ring.advance(its);
           tc_fence_after();
 #ifdef APH_GEMM_TRACE
-          if (tr) p.trace[it * 8 + 2] = clock64();
+          if (tr) p.trace[its * 8 + 2] = clock64();
 #endif
           const uint32_t desc_lo = (((smem_base + C::ACT_OFF + sa * C::ACT_BYTES) >> 4) & 0x3fffu) | (1u << 16);
           const uint32_t a_tmem = tmem0 + C::A_COL0 + sa * 64;
-          const int nx = it + NI;
+          const int nx = its + NI;
           ok = mbar_test(ready_bar + ring.slot(nx) * 8, ring.phase(nx));  // poll the next stage while these MMAs are issued
           tc_mma_ts_stage8(d_tmem, a_tmem, desc_lo, DESC_HI, C::IDESC, acc, (uint32_t)(C::ACT_BOX >> 4));
           acc = 1;
           tc_commit_elect(emptya_bar + sa * 8);  // slot (activations + TMEM weights) free once these MMAs retire
 #ifdef APH_GEMM_TRACE
-          if (tr) p.trace[it * 8 + 3] = clock64();
+          if (tr) p.trace[its * 8 + 3] = clock64();
 #endif
         }
         tc_commit_elect(done_bar + db * 8);
@@ -453,8 +460,8 @@ __global__ void __launch_bounds__(THREADS, 1)
     const uint32_t offZ = BITS == 4 ? (uint32_t)(C::W_OFF + W_BYTES + S_BYTES + (qd >> 1) * 32 + g * 4)
                                     : (uint32_t)(C::W_OFF + W_BYTES + S_BYTES + (qd >> 1) * 64 + g * 8 + (qd & 1) * 4);
     const uint32_t a_lane = (uint32_t)(32 * qd) << 16;
-    const int rpg_shift = grouped ? 31 - __clz(p.group_size / 16) : 3;  // log2(k16-rows per group): 1, 2, 3
-    const bool two_groups = grouped && p.group_size == 32;              // a warp's 4 rows span two groups
+    const int rpg_shift = G128 ? 3 : grouped ? 31 - __clz(p.group_size / 16) : 3;  // log2(k16-rows per group): 1, 2, 3
+    const bool two_groups = !G128 && grouped && p.group_size == 32;                // a warp's 4 rows span two groups
 
     // what is subtracted from the spliced value, per 16-row tile for rows g and g + 8. 16-bit route (4 bit; 8 bit f16):
     // packed pair (MAGIC + z, MAGIC + z). 8-bit bf16 goes through fp32 (2^23 + byte): the fp32 constant 2^23 + z.
@@ -533,29 +540,32 @@ __global__ void __launch_bounds__(THREADS, 1)
       if (lane == 0) mbar_arrive(ready_bar + pending * 8);
     };
 
-    int it = 0;
-    RingCursor<SW> ring_w;  // this warp handles the stages of group grp only
-    RingCursor<SA> ring_a;
+    int it = 0;  // global index of the segment's first stage
+    GroupCursor<SW> ring_w(grp);  // this warp handles the stages of group grp only: the stages with (index & 1) == grp
+    GroupCursor<SA> ring_a(grp);
     APH_SEGMENTS {
       APH_SEG_VARS
       if (HAS_ZP && !ZPF && !grouped)
         set_zp(*reinterpret_cast<const uint32_t*>(
             p.zp + (BITS == 4 ? ((int64_t)slice * (NTILE / 8) + (qd >> 1) * 8 + g) * 4
                               : ((int64_t)slice * (NTILE / 4) + (qd >> 1) * 16 + g * 2 + (qd & 1)) * 4)));
+      const int it_seg = it;
+      it += k1 - k0;
 #pragma unroll 1
-      for (int ks = k0; ks < k1; ++ks, ++it) {
-        if ((it & 1) != grp) continue;
-        const int sw = ring_w.slot(it), sa = ring_a.slot(it);
-        const uint32_t ph_w = ring_w.phase(it), ph_a = ring_a.phase(it);
-        ring_w.advance(it);
-        ring_a.advance(it);
+      for (int ks = k0 + ((grp ^ it_seg) & 1); ks < k1; ks += 2) {
+        const int its = it_seg + (ks - k0);  // (its & 1) == grp
+        (void)its;
+        const int sw = ring_w.slot(its), sa = ring_a.slot(its);
+        const uint32_t ph_w = ring_w.phase(its), ph_a = ring_a.phase(its);
+        ring_w.advance();
+        ring_a.advance();
 #ifdef APH_GEMM_TRACE
-        const bool tr = p.trace != nullptr && blockIdx.x == 0 && it < 64 && (dw & 7) == 0 && lane == 0;
-        if (tr) p.trace[it * 8 + 4] = clock64();
+        const bool tr = p.trace != nullptr && blockIdx.x == 0 && its < 64 && (dw & 7) == 0 && lane == 0;
+        if (tr) p.trace[its * 8 + 4] = clock64();
 #endif
         mbar_wait(fullw_bar + sw * 8, ph_w);
 #ifdef APH_GEMM_TRACE
-        if (tr) p.trace[it * 8 + 5] = clock64();
+        if (tr) p.trace[its * 8 + 5] = clock64();
 #endif
         const uint32_t wstage = smem_base + sw * W_STAGE;
         uint32_t q[4][BITS / 2];  // 4 bit: one word per tile; 8 bit: two words per tile
@@ -572,7 +582,11 @@ __global__ void __launch_bounds__(THREADS, 1)
         uint32_t a[2][16];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          if (grouped && (i == 0 || (i == 2 && two_groups))) load_group(wstage, (4 * h + i) >> rpg_shift);
+          if constexpr (G128) {
+            if (i == 0) load_group(wstage, 0);
+          } else {
+            if (grouped && (i == 0 || (i == 2 && two_groups))) load_group(wstage, (4 * h + i) >> rpg_shift);
+          }
 #pragma unroll
           for (int tt = 0; tt < 2; ++tt) {
             if constexpr (BITS == 4) {
@@ -586,10 +600,10 @@ __global__ void __launch_bounds__(THREADS, 1)
                 a[tt][4 * i + 2] = sub_mul2<F16>(sub_mul2<F16>(a2, c_lo[tt], 0u, false), z_lo[tt], s_lo[tt], true);
                 a[tt][4 * i + 3] = sub_mul2<F16>(sub_mul2<F16>(a3, c_hi[tt], 0u, false), z_hi[tt], s_hi[tt], true);
               } else {
-                a[tt][4 * i + 0] = sub_mul2<F16>(a0, c_lo[tt], s_lo[tt], grouped);
-                a[tt][4 * i + 1] = sub_mul2<F16>(a1, c_hi[tt], s_hi[tt], grouped);
-                a[tt][4 * i + 2] = sub_mul2<F16>(a2, c_lo[tt], s_lo[tt], grouped);
-                a[tt][4 * i + 3] = sub_mul2<F16>(a3, c_hi[tt], s_hi[tt], grouped);
+                a[tt][4 * i + 0] = sub_mul2<F16>(a0, c_lo[tt], s_lo[tt], G128 || grouped);
+                a[tt][4 * i + 1] = sub_mul2<F16>(a1, c_hi[tt], s_hi[tt], G128 || grouped);
+                a[tt][4 * i + 2] = sub_mul2<F16>(a2, c_lo[tt], s_lo[tt], G128 || grouped);
+                a[tt][4 * i + 3] = sub_mul2<F16>(a3, c_hi[tt], s_hi[tt], G128 || grouped);
               }
             } else {
               // word 0 of a tile: row g, bytes (0, 2) = k low pair, (1, 3) = k high pair; word 1: row g + 8
@@ -603,12 +617,12 @@ __global__ void __launch_bounds__(THREADS, 1)
         __syncwarp();
         if (lane == 0) mbar_arrive(emptyw_bar + sw * 8);  // this warp's words of the stage are in registers
 #ifdef APH_GEMM_TRACE
-        if (tr) p.trace[it * 8 + 6] = clock64();
+        if (tr) p.trace[its * 8 + 6] = clock64();
 #endif
         mbar_wait(emptya_bar + sa * 8, ph_a ^ 1);  // the MMAs that read this TMEM slot have retired
         tc_fence_after();
 #ifdef APH_GEMM_TRACE
-        if (tr) p.trace[it * 8 + 7] = clock64();
+        if (tr) p.trace[its * 8 + 7] = clock64();
 #endif
         const uint32_t a_tmem = tmem_base + a_lane + C::A_COL0 + sa * 64 + (4 * h) * 8;
         tmem_st_16x128b_x8(a_tmem, a[0]);

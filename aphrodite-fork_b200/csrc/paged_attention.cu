@@ -34,6 +34,7 @@ struct Split {
   int partition_tokens;
   int num_partitions;  // grid z
   int cluster_parts;   // partitions merged on chip by one thread-block cluster (1 = no cluster)
+  bool dense;          // the four-CTAs-per-SM build of the kernel (paged_attention.cuh: ring_bytes_for)
   int out_partials() const { return num_partitions / cluster_parts; }  // partials per (sequence, head) in the workspace
 };
 
@@ -50,7 +51,7 @@ struct Split {
 // of every page size). A cluster of CP CTAs needs CP * ceil(heads per CTA / CP) rows in the kernel's receive buffer
 // (14 for head sizes up to 128, 8 above). APH_PA_CLUSTER (development): 0 = never use clusters, 1 = whenever the split
 // allows, 2 = as described.
-static Split choose_split(int num_seqs, int num_heads, int num_kv_heads, int head_size, int max_seq_len) {
+static Split choose_split(int num_seqs, int num_heads, int num_kv_heads, int head_size, int max_seq_len, bool has_dense) {
   const int G = num_heads / num_kv_heads;
   const int tiles = (G + HEADS_PER_CTA - 1) / HEADS_PER_CTA;
   const int64_t units = (int64_t)num_seqs * num_kv_heads * tiles;
@@ -67,15 +68,17 @@ static Split choose_split(int num_seqs, int num_heads, int num_kv_heads, int hea
   const int min_part = e_m ? atoi(e_m) : 256;
   const int policy = e_c ? atoi(e_c) : 2;
   const int gt = G < HEADS_PER_CTA ? G : HEADS_PER_CTA;
-  const int recv_slots = head_size <= 128 ? 14 : 8;  // Cfg::RECV_SLOTS
+  const int recv_slots = recv_slots_for(head_size);  // Cfg::RECV_SLOTS
   auto fits = [&](int cp) { return cp * ((gt + cp - 1) / cp) <= recv_slots; };
+  static const char* const e_d0 = getenv("APH_PA_DENSE");  // development: 0 never, 1 wherever the build exists
+  const char* const e_d = dev_env_live() ? getenv("APH_PA_DENSE") : e_d0;
 
-  Split best{msl, 1, 1};
+  Split best{msl, 1, 1, false};
   double best_cost = 1e30;
-  auto consider = [&](int pt, int np, int cp, double cost) {
+  auto consider = [&](int pt, int np, int cp, double cost, bool dense = false) {
     if (cost < best_cost) {
       best_cost = cost;
-      best = Split{pt, np, cp};
+      best = Split{pt, np, cp, dense};
     }
   };
   // ---- multi-wave candidate: aim at `waves` waves, every partition through the workspace ----
@@ -97,7 +100,10 @@ static Split choose_split(int num_seqs, int num_heads, int num_kv_heads, int hea
     // few waves run in rounds (1.15 waves cost two), many waves flow
     const double rounds = w <= 3.0 ? (double)(int64_t)(w + 0.999) : w;
     // the reduce kernel hides under the last wave of a multi-wave grid (~150); behind a single wave it is exposed (~500)
-    consider((int)pt, z, cp, rounds * (double)(pt + (w <= 1.0 ? 600 : 370)) + (np > 1 ? (w <= 1.0 ? 500.0 : 150.0) : 0.0));
+    // many waves: the dense build (4 CTAs per SM, 8 receive rows) is 1.5-2 % ahead (C2 96.7 -> 95.3 us, 256 x 1024 91.7 -> 89.7)
+    bool dense = has_dense && w > 3.0 && (cp == 1 || cp * ((gt + cp - 1) / cp) <= recv_slots_for(head_size, true));
+    if (e_d) dense = has_dense && atoi(e_d) != 0 && (cp == 1 || cp * ((gt + cp - 1) / cp) <= recv_slots_for(head_size, true));
+    consider((int)pt, z, cp, rounds * (double)(pt + (w <= 1.0 ? 600 : 370)) + (np > 1 ? (w <= 1.0 ? 500.0 : 150.0) : 0.0), dense);
   }
   // ---- one-wave candidates ----
   if (e_w == nullptr && e_m == nullptr && units > 0 && units <= slots) {
@@ -159,7 +165,10 @@ static int run(void* out, const void* query, const void* key_cache, const void* 
     APH_CHECK(bs_block_size > 0, APH_ERR_INVALID_ARGUMENT, "paged_attention: blocksparse_block_size must be > 0");
   if (num_seqs == 0) return APH_OK;
 
-  const Split sp = choose_split(num_seqs, num_heads, num_kv_heads, head_size, max_seq_len);
+  // where paged_attention_inst.cu instantiates the dense build (HAS_DENSE there): 1-byte caches, head sizes 64 and 128,
+  // pages of 8 or 16 tokens (a 32-token page is a stage of its own: the ring cannot get shallower)
+  const bool has_dense = kv_dtype != APH_KV_AUTO && (head_size == 64 || head_size == 128) && block_size <= 16;
+  const Split sp = choose_split(num_seqs, num_heads, num_kv_heads, head_size, max_seq_len, has_dense);
   Params p;
   p.out = out;
   p.q = query;
@@ -177,6 +186,7 @@ static int run(void* out, const void* query, const void* key_cache, const void* 
   p.partition_tokens = sp.partition_tokens;
   p.num_partitions = sp.num_partitions;
   p.cluster_parts = sp.cluster_parts;
+  p.dense = sp.dense ? 1 : 0;
   p.q_stride = q_stride;
   p.out_stride = out_stride;
   p.kv_block_stride = kv_block_stride;
@@ -242,7 +252,8 @@ using namespace aphb200;
 extern "C" size_t aph_paged_attention_workspace_bytes(int num_seqs, int num_heads, int num_kv_heads, int head_size,
                                                       int max_seq_len) {
   if (num_seqs <= 0 || num_heads <= 0 || num_kv_heads <= 0 || head_size <= 0) return 0;
-  const pa::Split sp = pa::choose_split(num_seqs, num_heads, num_kv_heads, head_size, max_seq_len);
+  // (which build of the kernel runs does not change the split, so the cache type need not be known here)
+  const pa::Split sp = pa::choose_split(num_seqs, num_heads, num_kv_heads, head_size, max_seq_len, false);
   if (sp.out_partials() <= 1) return 0;
   const size_t n = (size_t)num_seqs * num_heads * sp.out_partials();
   return n * head_size * 4 + n * 8;

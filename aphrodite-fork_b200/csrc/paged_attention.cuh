@@ -32,6 +32,14 @@ constexpr int NW = 4;            // warps per CTA
 constexpr int THREADS = NW * 32;
 constexpr int HEADS_PER_CTA = 8;  // q heads packed into the MMA N dimension
 constexpr float LOG2E = 1.4426950408889634f;
+// Two builds of the main kernel. The default gives every warp a 16 KiB ring of pipeline stages and room for the
+// cluster merge of any cluster size up to 8 (rows a CTA receives: one per source rank x owned head, CP * ceil(8 / CP),
+// at most 14): three CTAs per SM. The DENSE build trades ring depth for occupancy - 12 KiB rings, 8 receive rows
+// (clusters of 1, 2, 4, 8) - so that four CTAs fit an SM; it is ahead where many waves of CTAs flow through the SMs
+// (the kernel is then short of warps to hide latencies, not of bytes in flight per warp) and behind on one-wave grids
+// (profiles/r02_attention_dense_variant.txt). Used for the 1-byte caches at head sizes 64 and 128.
+constexpr int ring_bytes_for(bool dense) { return dense ? 12288 : 16384; }
+constexpr int recv_slots_for(int head_size, bool dense = false) { return head_size <= 128 && !dense ? 14 : 8; }
 
 struct Params {
   void* out;                 // [S, H, D] scalar
@@ -50,6 +58,7 @@ struct Params {
   int partition_tokens;       // tokens per partition (multiple of the stage size)
   int num_partitions;         // grid z: partitions per (sequence, kv head tile), a multiple of cluster_parts
   int cluster_parts;          // CTAs per thread-block cluster along z (1..8): the partitions a cluster merges on chip
+  int dense;                  // run the four-CTAs-per-SM build of the kernel where there is one (see ring_bytes_for)
   int64_t q_stride, out_stride, kv_block_stride, kv_head_stride;  // elements
   float scale;
   int tp_rank, bs_local_blocks, bs_vert_stride, bs_block_size, bs_head_sliding_step;

@@ -14,11 +14,11 @@ namespace pa {
 #define APH_CAT2(a, b) a##b
 #define APH_CAT(a, b) APH_CAT2(a, b)
 
-template <typename scalar_t, int KV, int BS>
-static int launch_one(const Params& p, cudaStream_t stream) {
+template <typename scalar_t, int KV, int BS, bool DENSE>
+static int launch_main(const Params& p, cudaStream_t stream) {
   constexpr int D = APH_PA_HEAD_SIZE;
-  using C = Cfg<scalar_t, KV, D, BS>;
-  auto kern = paged_attention_kernel<scalar_t, KV, D, BS>;
+  using C = Cfg<scalar_t, KV, D, BS, DENSE>;
+  auto kern = paged_attention_kernel<scalar_t, KV, D, BS, DENSE>;
   static bool attr_set[64] = {false};  // per device; idempotent, so a benign race at worst
   int dev = 0;
   cudaGetDevice(&dev);
@@ -33,10 +33,24 @@ static int launch_one(const Params& p, cudaStream_t stream) {
   dim3 grid(p.num_kv_heads * tiles, p.num_seqs, p.num_partitions);
   if (p.cluster_parts > 1 && p.cluster_parts * ((min(G, HEADS_PER_CTA) + p.cluster_parts - 1) / p.cluster_parts) > C::RECV_SLOTS)
     return set_error(APH_ERR_INVALID_ARGUMENT, "paged_attention: cluster of %d partitions does not fit the merge buffer", p.cluster_parts);
-  {
-    const cudaError_t e = launch_pdl_cluster(kern, grid, dim3(C::NTHREADS), (size_t)C::SMEM_BYTES, stream, p.cluster_parts, p);
-    if (e != cudaSuccess) return set_error(APH_ERR_CUDA, "CUDA launch failed: %s", cudaGetErrorString(e));
+  const cudaError_t e = launch_pdl_cluster(kern, grid, dim3(C::NTHREADS), (size_t)C::SMEM_BYTES, stream, p.cluster_parts, p);
+  if (e != cudaSuccess) return set_error(APH_ERR_CUDA, "CUDA launch failed: %s", cudaGetErrorString(e));
+  return APH_OK;
+}
+
+template <typename scalar_t, int KV, int BS>
+static int launch_one(const Params& p, cudaStream_t stream) {
+  constexpr int D = APH_PA_HEAD_SIZE;
+  // the dense build exists where it buys a fourth CTA per SM (dense_variant_exists() in paged_attention.cu says the same)
+  constexpr bool HAS_DENSE = KV != APH_KV_AUTO && (D == 64 || D == 128) &&
+                             Cfg<scalar_t, KV, D, BS, true>::CTAS_PER_SM > Cfg<scalar_t, KV, D, BS, false>::CTAS_PER_SM;
+  int st;
+  if constexpr (HAS_DENSE) {
+    st = p.dense ? launch_main<scalar_t, KV, BS, true>(p, stream) : launch_main<scalar_t, KV, BS, false>(p, stream);
+  } else {
+    st = launch_main<scalar_t, KV, BS, false>(p, stream);
   }
+  if (st != APH_OK) return st;
   const int n_out = p.num_partitions / p.cluster_parts;  // partials per (sequence, head) left in the workspace
   if (n_out > 1) {
     // second level: the reduce grid is set up while the main kernel drains (it waits before reading the partials)

@@ -8,7 +8,7 @@
 namespace aphb200 {
 namespace pa {
 
-template <typename scalar_t, int KV, int D, int BS>
+template <typename scalar_t, int KV, int D, int BS, bool DENSE = false>
 struct Cfg {
   static constexpr int ESZ = (KV == APH_KV_AUTO) ? (int)sizeof(scalar_t) : 1;  // cache element bytes
   static constexpr bool FP8 = KV != APH_KV_AUTO;
@@ -22,7 +22,8 @@ struct Cfg {
   static constexpr int SP = ST / BS;            // cache pages per stage
   static constexpr int KPAGE = D * BS * ESZ;    // bytes of one K (or V) page of one kv head
   static constexpr int STAGE = 2 * SP * KPAGE;  // bytes per stage (K pages then V pages)
-  static constexpr int NS = (16384 / STAGE) >= 2 ? ((16384 / STAGE) > 8 ? 8 : (16384 / STAGE)) : 2;
+  static constexpr int RING = ring_bytes_for(DENSE);
+  static constexpr int NS = (RING / STAGE) >= 2 ? ((RING / STAGE) > 8 ? 8 : (RING / STAGE)) : 2;
   static constexpr int NWARPS = (STAGE * NS * 4 <= 160 * 1024) ? 4 : (STAGE * NS * 2 <= 200 * 1024 ? 2 : 1);
   static constexpr int NTHREADS = NWARPS * 32;
   static constexpr int DPAD = (D + 15) / 16 * 16;  // head size 120: the MMAs run over 128, the last 8 are zero (Q) / discarded (O)
@@ -32,17 +33,19 @@ struct Cfg {
   // cluster merge: rows a CTA receives from the partitions of its cluster, [slot][D] fp32 + (max, sum) per slot with
   // slot = source rank x heads this CTA owns; cluster size CP needs CP * ceil(8 / CP) slots (at most 14 for CP <= 8,
   // 8 for the powers of two, which is what head sizes above 128 are limited to so that 3 CTAs still fit an SM)
-  static constexpr int RECV_SLOTS = D <= 128 ? 14 : 8;
+  static constexpr int RECV_SLOTS = recv_slots_for(D, DENSE);
   static constexpr int RECV_OFF = ((PIPE_BYTES > MERGE_BYTES ? PIPE_BYTES : MERGE_BYTES) + NWARPS * NS * 8 + 15) / 16 * 16;
   static constexpr int RECV_BYTES = RECV_SLOTS * (D + 2) * 4;
   static constexpr int SMEM_BYTES = RECV_OFF + RECV_BYTES;
-  static constexpr int CTAS_PER_SM = (SMEM_BYTES + 1024) * 3 <= 227 * 1024 ? 3 : ((SMEM_BYTES + 1024) * 2 <= 227 * 1024 ? 2 : 1);
+  static constexpr int CTAS_PER_SM = (SMEM_BYTES + 1024) * 4 <= 227 * 1024 && NTHREADS * 4 * 128 <= 65536
+                                         ? 4
+                                         : ((SMEM_BYTES + 1024) * 3 <= 227 * 1024 ? 3 : ((SMEM_BYTES + 1024) * 2 <= 227 * 1024 ? 2 : 1));
 };
 
-template <typename scalar_t, int KV, int D, int BS>
-__global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS>::NTHREADS, Cfg<scalar_t, KV, D, BS>::CTAS_PER_SM)
+template <typename scalar_t, int KV, int D, int BS, bool DENSE = false>
+__global__ void __launch_bounds__(Cfg<scalar_t, KV, D, BS, DENSE>::NTHREADS, Cfg<scalar_t, KV, D, BS, DENSE>::CTAS_PER_SM)
     paged_attention_kernel(const Params p) {
-  using C = Cfg<scalar_t, KV, D, BS>;
+  using C = Cfg<scalar_t, KV, D, BS, DENSE>;
   constexpr bool F16 = C::F16MMA;
   constexpr int NWARPS = C::NWARPS, NS = C::NS, ST = C::ST, SG = C::SG, SP = C::SP, KPAGE = C::KPAGE;
   constexpr int KS = C::DPAD / 16;  // k-steps of Q K^T == m-tiles of P V

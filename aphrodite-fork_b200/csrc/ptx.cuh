@@ -359,6 +359,8 @@ struct RingCursor {
   static constexpr int D0 = (DEPTH + 1) / 2, D1 = DEPTH / 2;
   int pos0 = 0, pos1 = 0;
   uint32_t ph0 = 0, ph1 = 0;
+  __device__ __forceinline__ RingCursor() {}
+  __device__ __forceinline__ explicit RingCursor(int) {}  // same constructor as GroupCursor (the group is not used)
 #ifdef APH_RING_LEGACY
   __device__ __forceinline__ int slot(int it) const { return it % DEPTH; }
   __device__ __forceinline__ uint32_t phase(int it) const { return (uint32_t)(it / DEPTH) & 1u; }
@@ -377,6 +379,30 @@ struct RingCursor {
         pos0 = 0;
         ph0 ^= 1u;
       }
+    }
+  }
+#endif
+};
+
+// The same mapping for a thread that only ever handles the items of ONE group (its & 1 == grp): a plain counter over
+// the group's sub-ring. `its` (the item's global index) is only looked at by the APH_RING_LEGACY build.
+template <int DEPTH>
+struct GroupCursor {
+  static_assert(DEPTH >= 2, "a ring shared by two groups needs a slot per group");
+  int pos = 0, n, base;
+  uint32_t ph = 0;
+  __device__ __forceinline__ explicit GroupCursor(int grp) : n(grp ? DEPTH / 2 : (DEPTH + 1) / 2), base(grp) {}
+#ifdef APH_RING_LEGACY
+  __device__ __forceinline__ int slot(int its) const { return its % DEPTH; }
+  __device__ __forceinline__ uint32_t phase(int its) const { return (uint32_t)(its / DEPTH) & 1u; }
+  __device__ __forceinline__ void advance(int = 0) {}
+#else
+  __device__ __forceinline__ int slot(int) const { return base + 2 * pos; }
+  __device__ __forceinline__ uint32_t phase(int) const { return ph; }
+  __device__ __forceinline__ void advance(int = 0) {
+    if (++pos == n) {
+      pos = 0;
+      ph ^= 1u;
     }
   }
 #endif

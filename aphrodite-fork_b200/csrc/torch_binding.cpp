@@ -600,6 +600,39 @@ void advance_step_flashattn(int64_t num_seqs, int64_t num_queries, int64_t block
                                           block_tables.data_ptr<int32_t>(), block_tables.stride(0), stream_of()), op);
 }
 
+// kernels/prepare_inputs/advance_step.cu:234-311 (same tensor checks; sampled_token_ids is read flat, as there)
+void advance_step_flashinfer(int64_t num_seqs, int64_t num_queries, int64_t block_size, torch::Tensor& input_tokens,
+                             torch::Tensor& sampled_token_ids, torch::Tensor& input_positions, torch::Tensor& seq_lens,
+                             torch::Tensor& slot_mapping, torch::Tensor& block_tables, torch::Tensor& paged_kv_indices,
+                             torch::Tensor& paged_kv_indptr, torch::Tensor& paged_kv_last_page_len,
+                             torch::Tensor& block_table_bound) {
+  const char* op = "advance_step_flashinfer";
+  auto verify = [&](const char* name, const torch::Tensor& t, int64_t s0, at::ScalarType type) {
+    const bool ok = t.is_cuda() && (s0 == -1 || (t.dim() > 0 && t.size(0) == s0)) && t.is_contiguous() && t.scalar_type() == type;
+    TORCH_CHECK(ok, "tensor: name = ", name, ", shape = ", t.sizes(), " is_cont = ", t.is_contiguous(), ", type = ", t.dtype(),
+                " is not as expected: shape = [", s0, ", -1], type = ", type);
+  };
+  verify("input_tokens", input_tokens, num_seqs, at::kLong);
+  verify("sampled_token_ids", sampled_token_ids, -1, at::kLong);
+  TORCH_CHECK(sampled_token_ids.numel() >= num_queries, op, ": sampled_token_ids holds fewer than num_queries = ", num_queries, " ids");
+  verify("input_positions", input_positions, num_seqs, at::kLong);
+  verify("seq_lens", seq_lens, num_seqs, at::kInt);
+  verify("slot_mapping", slot_mapping, num_seqs, at::kLong);
+  verify("block_tables", block_tables, num_seqs, at::kInt);
+  verify("paged_kv_indices", paged_kv_indices, -1, at::kInt);
+  verify("paged_kv_indptr", paged_kv_indptr, num_seqs + 1, at::kInt);
+  verify("paged_kv_last_page_len", paged_kv_last_page_len, num_seqs, at::kInt);
+  verify("block_table_bound", block_table_bound, num_seqs, at::kInt);
+  const at::cuda::OptionalCUDAGuard guard(device_of(sampled_token_ids));
+  check_status(aph_advance_step_flashinfer(
+                   (int)num_seqs, (int)num_queries, (int)block_size, input_tokens.data_ptr<int64_t>(), sampled_token_ids.data_ptr<int64_t>(),
+                   input_positions.data_ptr<int64_t>(), seq_lens.data_ptr<int32_t>(), slot_mapping.data_ptr<int64_t>(),
+                   block_tables.data_ptr<int32_t>(), block_tables.dim() > 1 ? block_tables.stride(0) : 0, paged_kv_indices.data_ptr<int32_t>(),
+                   paged_kv_indices.numel(), paged_kv_indptr.data_ptr<int32_t>(), paged_kv_last_page_len.data_ptr<int32_t>(),
+                   block_table_bound.data_ptr<int32_t>(), stream_of()),
+               op);
+}
+
 }  // namespace
 
 #ifdef APH_DEFINE_SCHEMAS
@@ -647,6 +680,15 @@ TORCH_LIBRARY_FRAGMENT(_C, ops) {
       "Tensor! input_tokens, Tensor sampled_token_ids, "
       "Tensor! input_positions, Tensor! seq_lens, Tensor! slot_mapping, "
       "Tensor block_tables) -> ()");
+  ops.def(
+      "advance_step_flashinfer("
+      "    int num_seqs, int num_queries, int block_size,"
+      "    Tensor! input_tokens, Tensor sampled_token_ids,"
+      "    Tensor! input_positions, Tensor! seq_lens, Tensor! slot_mapping,"
+      "    Tensor block_tables, Tensor! paged_kv_indices,"
+      "    Tensor! paged_kv_indptr, Tensor! paged_kv_last_page_len,"
+      "    Tensor! block_table_bounds"
+      ") -> ()");
   ops.def("mul_and_silu(Tensor! out, Tensor input) -> ()");
   ops.def("gelu_and_mul(Tensor! out, Tensor input) -> ()");
   ops.def("gelu_tanh_and_mul(Tensor! out, Tensor input) -> ()");
@@ -709,7 +751,7 @@ TORCH_LIBRARY_FRAGMENT(_C_cache_ops, ops) {
 
 #define APH_ALL_C_OPS(X)                                                                                              \
   X(_C, paged_attention_v1) X(_C, paged_attention_v2) X(_C, gptq_marlin_gemm) X(_C, gptq_marlin_repack)                 \
-  X(_C, awq_marlin_repack) X(_C, silu_and_mul) X(_C, advance_step_flashattn) X(_C, mul_and_silu) X(_C, gelu_and_mul)    \
+  X(_C, awq_marlin_repack) X(_C, silu_and_mul) X(_C, advance_step_flashattn) X(_C, advance_step_flashinfer) X(_C, mul_and_silu) X(_C, gelu_and_mul)    \
   X(_C, gelu_tanh_and_mul) X(_C, fatrelu_and_mul) X(_C, gelu_new) X(_C, gelu_fast) X(_C, gelu_quick)                    \
   X(_C, batched_rotary_embedding) X(_C, rms_norm) X(_C, fused_add_rms_norm) X(_C, rotary_embedding)
 #define APH_ALL_CACHE_OPS(X)                                                                                          \

@@ -267,6 +267,18 @@ int aph_advance_step_flashattn(int num_seqs, int num_queries, int block_size, in
                                int64_t* slot_mapping, const int32_t* block_tables, int64_t block_tables_stride,
                                void* stream);
 
+/* The FlashInfer flavour - replaces kernels/prepare_inputs/advance_step.cu:91-167,234-311 (advance_step_flashinfer):
+ * the updates above, plus paged_kv_last_page_len[q] = pos % block_size + 1, block_table_bound[q] =
+ * ceil(seq_lens[q] / block_size), paged_kv_indptr[0] = 0, paged_kv_indptr[q + 1] = sum of block_table_bound[0..q],
+ * paged_kv_indptr[num_queries + 1 .. num_seqs] = paged_kv_indptr[num_queries], and paged_kv_indices[indptr[q] + c] =
+ * block_tables[q][c] for c < block_table_bound[q]. paged_kv_indices_len is the capacity of paged_kv_indices in
+ * elements: writes beyond it are dropped (the reference writes out of bounds). Two launches on `stream`. */
+int aph_advance_step_flashinfer(int num_seqs, int num_queries, int block_size, int64_t* input_tokens,
+                                const int64_t* sampled_token_ids, int64_t* input_positions, int32_t* seq_lens,
+                                int64_t* slot_mapping, const int32_t* block_tables, int64_t block_tables_stride,
+                                int32_t* paged_kv_indices, int64_t paged_kv_indices_len, int32_t* paged_kv_indptr,
+                                int32_t* paged_kv_last_page_len, int32_t* block_table_bound, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * One-shot all-reduce over NVLink peer memory - replaces cross_device_reduce_1stage,
  * kernels/all_reduce/custom_all_reduce.cuh:296-318 (barriers :140-200, dispatch :525-600).

@@ -123,3 +123,30 @@ def advance_step_flashattn(num_seqs, num_queries, block_size, input_tokens, samp
         seq_lens[q] = pos + 1
         input_positions[q] = pos
         slot_mapping[q] = int(block_tables[q, pos // block_size]) * block_size + pos % block_size
+
+
+def advance_step_flashinfer(num_seqs, num_queries, block_size, input_tokens, sampled_token_ids, input_positions, seq_lens,
+                            slot_mapping, block_tables, paged_kv_indices, paged_kv_indptr, paged_kv_last_page_len,
+                            block_table_bound):
+    """kernels/prepare_inputs/advance_step.cu:91-167 (the three kernels in launch order), in place on CPU tensors."""
+    flat = sampled_token_ids.reshape(-1)
+    for i in range(num_queries, num_seqs):
+        input_tokens[i], input_positions[i], slot_mapping[i] = 0, 0, -1
+    for q in range(num_queries):
+        input_tokens[q] = flat[q]
+        pos = int(seq_lens[q])
+        seq_lens[q] = pos + 1
+        input_positions[q] = pos
+        paged_kv_last_page_len[q] = pos % block_size + 1
+        slot_mapping[q] = int(block_tables[q, pos // block_size]) * block_size + pos % block_size
+        block_table_bound[q] = -(-(pos + 1) // block_size)
+    paged_kv_indptr[0] = 0
+    total = 0
+    for q in range(num_queries):
+        total += int(block_table_bound[q])
+        paged_kv_indptr[q + 1] = total
+    for i in range(num_queries + 1, num_seqs + 1):
+        paged_kv_indptr[i] = total
+    for q in range(num_queries):
+        start, n = int(paged_kv_indptr[q]), int(block_table_bound[q])
+        paged_kv_indices[start:start + n] = block_tables[q, :n]

@@ -38,6 +38,11 @@ void copy_blocks_mla(std::vector<torch::Tensor> const& kv_caches, const torch::T
 void advance_step_flashattn(int64_t num_seqs, int64_t num_queries, int64_t block_size, torch::Tensor& input_tokens,
                             torch::Tensor& sampled_token_ids, torch::Tensor& input_positions, torch::Tensor& seq_lens,
                             torch::Tensor& slot_mapping, torch::Tensor& block_tables);
+void advance_step_flashinfer(int64_t num_seqs, int64_t num_queries, int64_t block_size, torch::Tensor& input_tokens,
+                             torch::Tensor& sampled_token_ids, torch::Tensor& input_positions, torch::Tensor& seq_lens,
+                             torch::Tensor& slot_mapping, torch::Tensor& block_tables, torch::Tensor& paged_kv_indices,
+                             torch::Tensor& paged_kv_indptr, torch::Tensor& paged_kv_last_page_len,
+                             torch::Tensor& block_table_bounds);
 void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache,
                        torch::Tensor& value_cache, torch::Tensor& slot_mapping,
                        const std::string& kv_cache_dtype, torch::Tensor& k_scale, torch::Tensor& v_scale);
@@ -97,6 +102,11 @@ TORCH_LIBRARY(_refcuda, ops) {
       "advance_step_flashattn(int num_seqs, int num_queries, int block_size, Tensor! input_tokens, Tensor sampled_token_ids, "
       "Tensor! input_positions, Tensor! seq_lens, Tensor! slot_mapping, Tensor block_tables) -> ()");
   ops.impl("advance_step_flashattn", torch::kCUDA, &advance_step_flashattn);
+  ops.def(
+      "advance_step_flashinfer(int num_seqs, int num_queries, int block_size, Tensor! input_tokens, Tensor sampled_token_ids, "
+      "Tensor! input_positions, Tensor! seq_lens, Tensor! slot_mapping, Tensor block_tables, Tensor! paged_kv_indices, "
+      "Tensor! paged_kv_indptr, Tensor! paged_kv_last_page_len, Tensor! block_table_bounds) -> ()");
+  ops.impl("advance_step_flashinfer", torch::kCUDA, &advance_step_flashinfer);
   ops.def("copy_blocks_mla(Tensor(a!)[] kv_caches, Tensor block_mapping) -> ()");
   ops.impl("copy_blocks_mla", torch::kCUDA, &copy_blocks_mla);
   ops.def(

@@ -80,6 +80,10 @@ def test_argument_checks_of_the_next_row_entry_points():
     assert b"rot_dim" in lib.aph_b200_last_error()
     assert lib.aph_rotary_embedding(one, one, one, one, None, i64(4), 128, i64(1024), i64(256), 8, 3, 128, 1, 2, None) != 0
     assert lib.aph_advance_step_flashattn(4, 5, 16, one, one, one, one, one, one, i64(8), None) != 0
+    assert lib.aph_advance_step_flashinfer(4, 5, 16, one, one, one, one, one, one, i64(8), one, i64(64), one, one, one, None) != 0
+    assert b"num_queries <= num_seqs" in lib.aph_b200_last_error()
+    assert lib.aph_advance_step_flashinfer(4, 4, 16, one, one, one, one, one, one, i64(8), one, i64(64), None, one, one, None) != 0
+    assert b"paged_kv_indptr" in lib.aph_b200_last_error()
 
     assert lib.aph_concat_and_cache_mla(one, one, one, one, i64(4), 512, 64, 16, i64(9216), i64(576), i64(512), i64(64), 2, 1, None,
                                         None) != 0

@@ -297,3 +297,48 @@ def test_advance_step_flashattn(num_seqs, num_queries):
         assert torch.equal(got.cpu(), want)
     with pytest.raises(RuntimeError, match="is not as expected"):
         A.ops.advance_step_flashattn(num_seqs + 1, num_queries, bs, dev[0], dev[1], dev[2], dev[3], dev[4], dev[5])
+
+
+@pytest.mark.parametrize("num_seqs,num_queries,max_blocks", [(8, 8, 40), (64, 50, 40), (3000, 2500, 24), (1, 0, 8), (300, 300, 1100)])
+def test_advance_step_flashinfer(num_seqs, num_queries, max_blocks):
+    """Integer bookkeeping plus the CSR page list: bit-exact against the oracle loops and the reference's three kernels
+    (prepare_inputs/advance_step.cu:91-167). 2500 queries take the scan through three 1024-row chunks; 1100 columns take
+    the page copy through two column chunks."""
+    bs = 16
+    gen = torch.Generator().manual_seed(num_seqs)
+    tok = torch.randint(0, 32000, (num_seqs,), generator=gen)
+    sampled = torch.randint(0, 32000, (num_queries, 1), generator=gen)
+    pos = torch.randint(0, 500, (num_seqs,), generator=gen)
+    lens = torch.randint(1, bs * max_blocks - 1, (num_seqs,), generator=gen, dtype=torch.int32)
+    slots = torch.randint(0, 10000, (num_seqs,), generator=gen)
+    bt = torch.randint(0, 5000, (num_seqs, max_blocks), generator=gen, dtype=torch.int32)
+    indices = torch.full((num_seqs * max_blocks + 1,), -7, dtype=torch.int32)
+    indptr = torch.full((num_seqs + 1,), -7, dtype=torch.int32)
+    last = torch.full((num_seqs,), -7, dtype=torch.int32)
+    bound = torch.full((num_seqs,), -7, dtype=torch.int32)
+    host = (tok, sampled, pos, lens, slots, bt, indices, indptr, last, bound)
+    dev = [t.to(DEV) for t in host]
+    ref = oracle.refcuda()
+    rdev = None
+    if ref is not None and hasattr(ref, "advance_step_flashinfer"):
+        rdev = [t.clone() for t in dev]
+        ref.advance_step_flashinfer(num_seqs, num_queries, bs, *rdev)
+    A.ops.advance_step_flashinfer(num_seqs, num_queries, bs, *dev)
+    if rdev is not None:
+        for got, want in zip(dev, rdev):
+            assert torch.equal(got, want)
+    lg.advance_step_flashinfer(num_seqs, num_queries, bs, *host)
+    for got, want in zip(dev, host):
+        assert torch.equal(got.cpu(), want)
+    # a second step on the advanced state (what a multi-step runner does), and a too-short page list: no write lands
+    # beyond its end (the element after the capacity given to the op keeps its value)
+    A.ops.advance_step_flashinfer(num_seqs, num_queries, bs, *dev)
+    lg.advance_step_flashinfer(num_seqs, num_queries, bs, *host)
+    for got, want in zip(dev, host):
+        assert torch.equal(got.cpu(), want)
+    if num_queries:
+        short = torch.full((int(host[7][num_queries]),), -7, dtype=torch.int32, device=DEV)
+        A.ops.advance_step_flashinfer(num_seqs, num_queries, bs, *dev[:6], short[:-1], *dev[7:])
+        assert int(short[-1]) == -7
+    with pytest.raises(RuntimeError, match="is not as expected"):
+        A.ops.advance_step_flashinfer(num_seqs + 1, num_queries, bs, *dev)

@@ -228,3 +228,21 @@ def test_glue_oracle_matches_reference_forward_native():
             torch.testing.assert_close(k, _t(g[pre + "k_out"], dt), atol=1e-6, rtol=1e-6)
         else:
             assert torch.equal(q, _t(g[pre + "q_out"], dt)) and torch.equal(k, _t(g[pre + "k_out"], dt)), ci
+
+
+
+def test_advance_step_flashinfer_oracle_known_answer():
+    """Hand-worked case of prepare_inputs/advance_step.cu:91-167: block size 4, three sequences of which two run.
+    Lengths 3 and 8 become 4 and 9: positions 3 and 8, pages 1 and 3, last-page fill 4 and 1."""
+    import torch
+    from oracle import layer_glue as lg
+    tok, pos, slots = torch.tensor([5, 6, 7]), torch.tensor([9, 9, 9]), torch.tensor([1, 1, 1])
+    sampled, lens = torch.tensor([[11], [12]]), torch.tensor([3, 8, 2], dtype=torch.int32)
+    bt = torch.tensor([[10, 11, 12], [20, 21, 22], [30, 31, 32]], dtype=torch.int32)
+    indices, indptr = torch.full((8,), -1, dtype=torch.int32), torch.full((4,), -1, dtype=torch.int32)
+    last, bound = torch.full((3,), -1, dtype=torch.int32), torch.full((3,), -1, dtype=torch.int32)
+    lg.advance_step_flashinfer(3, 2, 4, tok, sampled, pos, lens, slots, bt, indices, indptr, last, bound)
+    assert tok.tolist() == [11, 12, 0] and pos.tolist() == [3, 8, 0] and lens.tolist() == [4, 9, 2]
+    assert slots.tolist() == [10 * 4 + 3, 22 * 4 + 0, -1]
+    assert last.tolist() == [4, 1, -1] and bound.tolist() == [1, 3, -1]
+    assert indptr.tolist() == [0, 1, 4, 4] and indices.tolist() == [10, 20, 21, 22, -1, -1, -1, -1]
