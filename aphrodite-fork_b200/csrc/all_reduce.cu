@@ -19,9 +19,20 @@
 // rank: 2 (world - 1) / world x the message. Same double buffering, same bit-identical results on every rank.
 // The per-CTA counters hold the CALL number n; call n uses half n & 1 and the barrier flags 2n and 2n + 1, so one-shot
 // and two-shot calls can be mixed freely.
+// MULTIMEM variants (NVLS: the reduction happens inside the NVSwitch): the host also passes the MULTICAST mapping of the
+// symmetric buffer - one address that stands for the same offset in every rank's buffer. (A) every rank copies its
+// partial into slot 0 of its OWN buffer (no NVLink traffic), (B1) barrier, (C1) the owner of a vector issues ONE
+// multimem.ld_reduce on the multicast address (the switch reads the `world` copies and returns their fp32-accumulated sum)
+// and ONE multimem.st of the rounded sum to slot 1 (the switch writes it into every rank's buffer), (B2) barrier, (C2)
+// every rank reads slot 1 of its own buffer. NVLink bytes per rank: about 1 x the message in each direction (two-shot:
+// 2 (world - 1) / world), and each vector costs its owner two instructions instead of 2 x world. The order of the
+// additions is the switch's, not rank order: the result is identical on all ranks (one owner computes it) and the same
+// from run to run, but may differ from the rank-order sum in the last bit.
 // Layout of a rank's buffer (from the host: torch symmetric memory / CUDA IPC): [ 4 KiB flags | 2 halves x world slots
 // x slot_bytes ]. A CTA only waits for the CTA with the same index on the peers and grids are at most 128 CTAs of 512
 // threads, so every waiting CTA is resident (no deadlock on a 148-SM part).
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace aphb200 {
@@ -43,6 +54,27 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
+}
+
+// sum over the ranks of the 16 bytes at multicast address p (fp32 accumulation for the 16-bit types), and the broadcast store
+template <typename T>
+__device__ __forceinline__ uint4 multimem_ld_reduce(const void* p) {
+  uint4 v;
+  if constexpr (std::is_same<T, float>::value) {
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  } else if constexpr (std::is_same<T, __half>::value) {
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  } else {
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  }
+  return v;
+}
+__device__ __forceinline__ void multimem_st(void* p, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
 }
 
 // Barrier with the CTA of the same index on every peer: publish `flag` (release: this CTA's earlier stores, ordered
@@ -90,10 +122,12 @@ __device__ __forceinline__ uint4 ar_sum_slots(const uint8_t* mine, int64_t slot_
   return o;
 }
 
-template <typename T, int WORLD, bool TWO_SHOT>
+constexpr int AR_ONE_SHOT = 0, AR_TWO_SHOT = 1, AR_MULTIMEM = 2;
+
+template <typename T, int WORLD, int MODE>
 __global__ void __launch_bounds__(512, 1)
     one_shot_all_reduce_kernel(T* out, const T* in, uint8_t* const* __restrict__ peer_bufs,  // out may alias in
-                               uint32_t* __restrict__ counters, int rank, int64_t n_vec, int64_t slot_bytes) {
+                               uint8_t* multicast_buf, uint32_t* __restrict__ counters, int rank, int64_t n_vec, int64_t slot_bytes) {
   using V = uint4;
   __shared__ uint8_t* s_bufs[WORLD];
   pdl_trigger();
@@ -106,7 +140,7 @@ __global__ void __launch_bounds__(512, 1)
   const int64_t half_off = AR_SIGNAL_BYTES + (int64_t)(call & 1) * WORLD * slot_bytes;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x, first = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint8_t* mine = s_bufs[rank] + half_off;
-  if (!TWO_SHOT) {
+  if (MODE == AR_ONE_SHOT) {
     // (A) push to everybody
     for (int64_t i = first; i < n_vec; i += stride) {
       const V v = reinterpret_cast<const V*>(in)[i];
@@ -116,7 +150,7 @@ __global__ void __launch_bounds__(512, 1)
     ar_barrier<WORLD>(s_bufs, rank, 2 * call);  // (B)
     // (C) local sum in rank order
     for (int64_t i = first; i < n_vec; i += stride) reinterpret_cast<V*>(out)[i] = ar_sum_slots<T, WORLD>(mine, slot_bytes, i);
-  } else {
+  } else if (MODE == AR_TWO_SHOT) {
     const int owner = (int)threadIdx.x * WORLD / (int)blockDim.x;  // of every vector this thread handles
     // (A) push to the owner only
     for (int64_t i = first; i < n_vec; i += stride)
@@ -132,6 +166,22 @@ __global__ void __launch_bounds__(512, 1)
     ar_barrier<WORLD>(s_bufs, rank, 2 * call + 1);  // (B2)
     // (C2)
     for (int64_t i = first; i < n_vec; i += stride) reinterpret_cast<V*>(out)[i] = __ldcv(reinterpret_cast<const V*>(mine + owner * slot_bytes) + i);
+  } else {
+    const int owner = (int)threadIdx.x * WORLD / (int)blockDim.x;
+    // (A) my partial into slot 0 of my own buffer
+    for (int64_t i = first; i < n_vec; i += stride)
+      reinterpret_cast<V*>(s_bufs[rank] + half_off)[i] = reinterpret_cast<const V*>(in)[i];
+    ar_barrier<WORLD>(s_bufs, rank, 2 * call);  // (B1)
+    // (C1) the owner lets the switch add the `world` copies and broadcast the sum into slot 1 of every buffer. The
+    // multimem.st are relaxed.sys (strong) operations: the CTA barrier + release.sys flag store of ar_barrier orders them
+    // before the flag like the pushes of the other variants.
+    if (owner == rank) {
+      uint8_t* mc = multicast_buf + half_off;
+      for (int64_t i = first; i < n_vec; i += stride) multimem_st(reinterpret_cast<V*>(mc + slot_bytes) + i, multimem_ld_reduce<T>(reinterpret_cast<const V*>(mc) + i));
+    }
+    ar_barrier<WORLD>(s_bufs, rank, 2 * call + 1);  // (B2)
+    // (C2)
+    for (int64_t i = first; i < n_vec; i += stride) reinterpret_cast<V*>(out)[i] = __ldcv(reinterpret_cast<const V*>(mine + slot_bytes) + i);
   }
   ar_finish(counters, call);
 }
@@ -158,11 +208,12 @@ __device__ __forceinline__ float ar_block_sum(float v, float* s_part) {
   return v;
 }
 
-template <typename T, int WORLD, bool TWO_SHOT>
+template <typename T, int WORLD, int MODE>
 __global__ void __launch_bounds__(512, 1)
     all_reduce_add_rms_norm_kernel(T* x, T* residual, const T* __restrict__ weight, float epsilon,
-                                   uint8_t* const* __restrict__ peer_bufs, uint32_t* __restrict__ counters, int rank, int rows,
-                                   int hidden, int64_t slot_bytes) {
+                                   uint8_t* const* __restrict__ peer_bufs, uint8_t* multicast_buf, uint32_t* __restrict__ counters,
+                                   int rank, int rows, int hidden, int64_t slot_bytes) {
+  constexpr bool TWO_SHOT = MODE == AR_TWO_SHOT, MULTIMEM = MODE == AR_MULTIMEM;
   constexpr int VEC = 16 / (int)sizeof(T);
   constexpr int ITER = 4;  // hidden <= 4 * 512 * VEC
   using V = uint4;
@@ -182,13 +233,15 @@ __global__ void __launch_bounds__(512, 1)
   const uint32_t call = counters[blockIdx.x] + 1;  // after the wait, see one_shot_all_reduce_kernel
   const int64_t half_off = AR_SIGNAL_BYTES + (int64_t)(call & 1) * WORLD * slot_bytes;
   const uint8_t* mine = s_bufs[rank] + half_off;
-  const int owner = (int)threadIdx.x * WORLD / (int)blockDim.x;  // TWO_SHOT: owner of every vector this thread handles
+  const int owner = (int)threadIdx.x * WORLD / (int)blockDim.x;  // two-shot, multimem: owner of every vector this thread handles
   // (A) push this CTA's rows: to everybody, or (two-shot) to the owner of each vector
   for (int row = blockIdx.x; row < rows; row += gridDim.x)
     for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
       const int64_t idx = (int64_t)row * nvec + i;
       const V v = reinterpret_cast<const V*>(x)[idx];
-      if (TWO_SHOT) {
+      if (MULTIMEM) {
+        reinterpret_cast<V*>(s_bufs[rank] + half_off)[idx] = v;  // slot 0 of my own buffer
+      } else if (TWO_SHOT) {
         reinterpret_cast<V*>(s_bufs[owner] + half_off + rank * slot_bytes)[idx] = v;
       } else {
 #pragma unroll
@@ -208,6 +261,18 @@ __global__ void __launch_bounds__(512, 1)
         }
     ar_barrier<WORLD>(s_bufs, rank, 2 * call + 1);  // (B2)
   }
+  if (MULTIMEM) {
+    // (C1) the owner lets the switch add the copies and broadcast the rounded sums into slot 1 of every buffer
+    if (owner == rank) {
+      uint8_t* mc = multicast_buf + half_off;
+      for (int row = blockIdx.x; row < rows; row += gridDim.x)
+        for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+          const int64_t idx = (int64_t)row * nvec + i;
+          multimem_st(reinterpret_cast<V*>(mc + slot_bytes) + idx, multimem_ld_reduce<T>(reinterpret_cast<const V*>(mc) + idx));
+        }
+    }
+    ar_barrier<WORLD>(s_bufs, rank, 2 * call + 1);  // (B2)
+  }
   // (C) finish the rows
   for (int row = blockIdx.x; row < rows; row += gridDim.x) {
     V keep[ITER];
@@ -218,7 +283,9 @@ __global__ void __launch_bounds__(512, 1)
       if (i < nvec) {
         const int64_t idx = (int64_t)row * nvec + i;
         // the all-reduce's output, rounded to T: summed here in rank order (one-shot) or by the vector's owner (two-shot)
-        const V sum = TWO_SHOT ? __ldcv(reinterpret_cast<const V*>(mine + owner * slot_bytes) + idx) : ar_sum_slots<T, WORLD>(mine, slot_bytes, idx);
+        const V sum = MULTIMEM   ? __ldcv(reinterpret_cast<const V*>(mine + slot_bytes) + idx)
+                      : TWO_SHOT ? __ldcv(reinterpret_cast<const V*>(mine + owner * slot_bytes) + idx)
+                                 : ar_sum_slots<T, WORLD>(mine, slot_bytes, idx);
         const V res = reinterpret_cast<const V*>(residual)[idx];
         V z;
 #pragma unroll
@@ -254,17 +321,22 @@ __global__ void __launch_bounds__(512, 1)
 }
 
 template <typename T>
-int launch_ar_norm(void* x, void* residual, const void* weight, float eps, const void* const* peer_bufs, uint32_t* counters, int rank,
-                   int world, int rows, int hidden, int64_t slot_bytes, bool two_shot, cudaStream_t stream) {
+int launch_ar_norm(void* x, void* residual, const void* weight, float eps, const void* const* peer_bufs, void* mc, uint32_t* counters,
+                   int rank, int world, int rows, int hidden, int64_t slot_bytes, int mode, cudaStream_t stream) {
   const int blocks = std::max(1, std::min(rows, AR_MAX_BLOCKS));
-#define APH_ARN(W)                                                                                                                   \
-  case W:                                                                                                                            \
-    if (two_shot)                                                                                                                    \
-      APH_LAUNCH_PDL((all_reduce_add_rms_norm_kernel<T, W, true>), dim3((unsigned)blocks), dim3(512), (size_t)0, stream, (T*)x,      \
-                     (T*)residual, (const T*)weight, eps, (uint8_t* const*)peer_bufs, counters, rank, rows, hidden, slot_bytes);      \
-    else                                                                                                                             \
-      APH_LAUNCH_PDL((all_reduce_add_rms_norm_kernel<T, W, false>), dim3((unsigned)blocks), dim3(512), (size_t)0, stream, (T*)x,     \
-                     (T*)residual, (const T*)weight, eps, (uint8_t* const*)peer_bufs, counters, rank, rows, hidden, slot_bytes);      \
+#define APH_ARN_MODE(W, MODE)                                                                                                      \
+  APH_LAUNCH_PDL((all_reduce_add_rms_norm_kernel<T, W, MODE>), dim3((unsigned)blocks), dim3(512), (size_t)0, stream, (T*)x,        \
+                 (T*)residual, (const T*)weight, eps, (uint8_t* const*)peer_bufs, (uint8_t*)mc, counters, rank, rows, hidden,       \
+                 slot_bytes)
+#define APH_ARN(W)                        \
+  case W:                                 \
+    if (mode == AR_TWO_SHOT) {            \
+      APH_ARN_MODE(W, AR_TWO_SHOT);       \
+    } else if (mode == AR_MULTIMEM) {     \
+      APH_ARN_MODE(W, AR_MULTIMEM);       \
+    } else {                              \
+      APH_ARN_MODE(W, AR_ONE_SHOT);       \
+    }                                     \
     return APH_OK
   switch (world) {
     APH_ARN(2);
@@ -274,19 +346,24 @@ int launch_ar_norm(void* x, void* residual, const void* weight, float eps, const
     default: return set_error(APH_ERR_UNSUPPORTED, "all_reduce_add_rms_norm: world size %d (2, 4, 6 or 8)", world);
   }
 #undef APH_ARN
+#undef APH_ARN_MODE
 }
 
 template <typename T>
-int launch_one_shot(void* out, const void* in, const void* const* peer_bufs, uint32_t* counters, int rank, int world, int64_t n_vec,
-                    int64_t slot_bytes, int blocks, bool two_shot, cudaStream_t stream) {
-#define APH_AR(W)                                                                                                                  \
-  case W:                                                                                                                          \
-    if (two_shot)                                                                                                                  \
-      APH_LAUNCH_PDL((one_shot_all_reduce_kernel<T, W, true>), dim3((unsigned)blocks), dim3(512), (size_t)0, stream, (T*)out,      \
-                     (const T*)in, (uint8_t* const*)peer_bufs, counters, rank, n_vec, slot_bytes);                                  \
-    else                                                                                                                           \
-      APH_LAUNCH_PDL((one_shot_all_reduce_kernel<T, W, false>), dim3((unsigned)blocks), dim3(512), (size_t)0, stream, (T*)out,     \
-                     (const T*)in, (uint8_t* const*)peer_bufs, counters, rank, n_vec, slot_bytes);                                  \
+int launch_one_shot(void* out, const void* in, const void* const* peer_bufs, void* mc, uint32_t* counters, int rank, int world,
+                    int64_t n_vec, int64_t slot_bytes, int blocks, int mode, cudaStream_t stream) {
+#define APH_AR_MODE(W, MODE)                                                                                                    \
+  APH_LAUNCH_PDL((one_shot_all_reduce_kernel<T, W, MODE>), dim3((unsigned)blocks), dim3(512), (size_t)0, stream, (T*)out,      \
+                 (const T*)in, (uint8_t* const*)peer_bufs, (uint8_t*)mc, counters, rank, n_vec, slot_bytes)
+#define APH_AR(W)                        \
+  case W:                                \
+    if (mode == AR_TWO_SHOT) {           \
+      APH_AR_MODE(W, AR_TWO_SHOT);       \
+    } else if (mode == AR_MULTIMEM) {    \
+      APH_AR_MODE(W, AR_MULTIMEM);       \
+    } else {                             \
+      APH_AR_MODE(W, AR_ONE_SHOT);       \
+    }                                    \
     return APH_OK
   switch (world) {
     APH_AR(2);
@@ -296,10 +373,12 @@ int launch_one_shot(void* out, const void* in, const void* const* peer_bufs, uin
     default: return set_error(APH_ERR_UNSUPPORTED, "all_reduce: world size %d (2, 4, 6 or 8)", world);
   }
 #undef APH_AR
+#undef APH_AR_MODE
 }
 
-int all_reduce_entry(const char* op, bool two_shot, void* out, const void* in, const void* const* peer_bufs_dev, uint32_t* counters,
+int all_reduce_entry(const char* op, int mode, void* out, const void* in, const void* const* peer_bufs_dev, void* mc, uint32_t* counters,
                      int rank, int world, int64_t numel, int dtype, int64_t slot_bytes, int max_blocks, void* stream) {
+  APH_CHECK(mode != AR_MULTIMEM || (mc != nullptr && aligned16(mc)), APH_ERR_INVALID_ARGUMENT, "%s: null or misaligned multicast address", op);
   APH_CHECK(world >= 2 && world <= AR_MAX_RANKS && rank >= 0 && rank < world, APH_ERR_INVALID_ARGUMENT, "%s: rank %d of %d", op, rank,
             world);
   APH_CHECK(numel >= 0, APH_ERR_INVALID_ARGUMENT, "%s: negative size", op);
@@ -315,17 +394,18 @@ int all_reduce_entry(const char* op, bool two_shot, void* out, const void* in, c
   blocks = std::max(blocks, 1);
   cudaStream_t s = (cudaStream_t)stream;
   switch (dtype) {
-    case APH_DT_F32: return launch_one_shot<float>(out, in, peer_bufs_dev, counters, rank, world, n_vec, slot_bytes, blocks, two_shot, s);
-    case APH_DT_F16: return launch_one_shot<__half>(out, in, peer_bufs_dev, counters, rank, world, n_vec, slot_bytes, blocks, two_shot, s);
+    case APH_DT_F32: return launch_one_shot<float>(out, in, peer_bufs_dev, mc, counters, rank, world, n_vec, slot_bytes, blocks, mode, s);
+    case APH_DT_F16: return launch_one_shot<__half>(out, in, peer_bufs_dev, mc, counters, rank, world, n_vec, slot_bytes, blocks, mode, s);
     case APH_DT_BF16:
-      return launch_one_shot<__nv_bfloat16>(out, in, peer_bufs_dev, counters, rank, world, n_vec, slot_bytes, blocks, two_shot, s);
+      return launch_one_shot<__nv_bfloat16>(out, in, peer_bufs_dev, mc, counters, rank, world, n_vec, slot_bytes, blocks, mode, s);
     default: return set_error(APH_ERR_INVALID_ARGUMENT, "%s: unknown dtype %d", op, dtype);
   }
 }
 
-int ar_norm_entry(const char* op, bool two_shot, void* x, void* residual, const void* weight, float epsilon, const void* const* peer_bufs_dev,
-                  uint32_t* counters, int rank, int world, int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes,
+int ar_norm_entry(const char* op, int mode, void* x, void* residual, const void* weight, float epsilon, const void* const* peer_bufs_dev,
+                  void* mc, uint32_t* counters, int rank, int world, int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes,
                   void* stream) {
+  APH_CHECK(mode != AR_MULTIMEM || (mc != nullptr && aligned16(mc)), APH_ERR_INVALID_ARGUMENT, "%s: null or misaligned multicast address", op);
   APH_CHECK(world >= 2 && world <= AR_MAX_RANKS && rank >= 0 && rank < world, APH_ERR_INVALID_ARGUMENT, "%s: rank %d of %d", op, rank,
             world);
   APH_CHECK(dtype == APH_DT_F16 || dtype == APH_DT_BF16, APH_ERR_UNSUPPORTED, "%s: float16 / bfloat16 only", op);
@@ -338,10 +418,10 @@ int ar_norm_entry(const char* op, bool two_shot, void* x, void* residual, const 
             "%s: message does not fit the %lld-byte slots", op, (long long)slot_bytes);
   cudaStream_t s = (cudaStream_t)stream;
   if (dtype == APH_DT_F16)
-    return launch_ar_norm<__half>(x, residual, weight, epsilon, peer_bufs_dev, counters, rank, world, (int)num_tokens, (int)hidden_size,
-                                  slot_bytes, two_shot, s);
-  return launch_ar_norm<__nv_bfloat16>(x, residual, weight, epsilon, peer_bufs_dev, counters, rank, world, (int)num_tokens,
-                                       (int)hidden_size, slot_bytes, two_shot, s);
+    return launch_ar_norm<__half>(x, residual, weight, epsilon, peer_bufs_dev, mc, counters, rank, world, (int)num_tokens, (int)hidden_size,
+                                  slot_bytes, mode, s);
+  return launch_ar_norm<__nv_bfloat16>(x, residual, weight, epsilon, peer_bufs_dev, mc, counters, rank, world, (int)num_tokens,
+                                       (int)hidden_size, slot_bytes, mode, s);
 }
 
 }  // namespace
@@ -358,27 +438,41 @@ extern "C" size_t aph_all_reduce_buffer_bytes(int world, int64_t slot_bytes) {
 
 extern "C" int aph_one_shot_all_reduce(void* out, const void* in, const void* const* peer_bufs_dev, uint32_t* counters, int rank,
                                        int world, int64_t numel, int dtype, int64_t slot_bytes, int max_blocks, void* stream) {
-  return all_reduce_entry("one_shot_all_reduce", false, out, in, peer_bufs_dev, counters, rank, world, numel, dtype, slot_bytes, max_blocks,
-                          stream);
+  return all_reduce_entry("one_shot_all_reduce", AR_ONE_SHOT, out, in, peer_bufs_dev, nullptr, counters, rank, world, numel, dtype, slot_bytes,
+                          max_blocks, stream);
 }
 
 extern "C" int aph_two_shot_all_reduce(void* out, const void* in, const void* const* peer_bufs_dev, uint32_t* counters, int rank,
                                        int world, int64_t numel, int dtype, int64_t slot_bytes, int max_blocks, void* stream) {
-  return all_reduce_entry("two_shot_all_reduce", true, out, in, peer_bufs_dev, counters, rank, world, numel, dtype, slot_bytes, max_blocks,
-                          stream);
+  return all_reduce_entry("two_shot_all_reduce", AR_TWO_SHOT, out, in, peer_bufs_dev, nullptr, counters, rank, world, numel, dtype, slot_bytes,
+                          max_blocks, stream);
 }
 
 extern "C" int aph_all_reduce_add_rms_norm(void* x, void* residual, const void* weight, float epsilon,
                                            const void* const* peer_bufs_dev, uint32_t* counters, int rank, int world,
                                            int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes, void* stream) {
-  return ar_norm_entry("all_reduce_add_rms_norm", false, x, residual, weight, epsilon, peer_bufs_dev, counters, rank, world, num_tokens,
-                       hidden_size, dtype, slot_bytes, stream);
+  return ar_norm_entry("all_reduce_add_rms_norm", AR_ONE_SHOT, x, residual, weight, epsilon, peer_bufs_dev, nullptr, counters, rank, world,
+                       num_tokens, hidden_size, dtype, slot_bytes, stream);
 }
 
 extern "C" int aph_two_shot_all_reduce_add_rms_norm(void* x, void* residual, const void* weight, float epsilon,
                                                     const void* const* peer_bufs_dev, uint32_t* counters, int rank, int world,
                                                     int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes,
                                                     void* stream) {
-  return ar_norm_entry("two_shot_all_reduce_add_rms_norm", true, x, residual, weight, epsilon, peer_bufs_dev, counters, rank, world,
-                       num_tokens, hidden_size, dtype, slot_bytes, stream);
+  return ar_norm_entry("two_shot_all_reduce_add_rms_norm", AR_TWO_SHOT, x, residual, weight, epsilon, peer_bufs_dev, nullptr, counters, rank,
+                       world, num_tokens, hidden_size, dtype, slot_bytes, stream);
+}
+
+extern "C" int aph_multimem_all_reduce(void* out, const void* in, const void* const* peer_bufs_dev, void* multicast_buf, uint32_t* counters,
+                                       int rank, int world, int64_t numel, int dtype, int64_t slot_bytes, int max_blocks, void* stream) {
+  return all_reduce_entry("multimem_all_reduce", AR_MULTIMEM, out, in, peer_bufs_dev, multicast_buf, counters, rank, world, numel, dtype,
+                          slot_bytes, max_blocks, stream);
+}
+
+extern "C" int aph_multimem_all_reduce_add_rms_norm(void* x, void* residual, const void* weight, float epsilon,
+                                                    const void* const* peer_bufs_dev, void* multicast_buf, uint32_t* counters, int rank,
+                                                    int world, int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes,
+                                                    void* stream) {
+  return ar_norm_entry("multimem_all_reduce_add_rms_norm", AR_MULTIMEM, x, residual, weight, epsilon, peer_bufs_dev, multicast_buf, counters,
+                       rank, world, num_tokens, hidden_size, dtype, slot_bytes, stream);
 }

@@ -321,7 +321,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 #pragma unroll 1
       for (int ks = k0; ks < k1; ++ks, ++it) {
         const int sw = ring.slot(it);
-        mbar_wait_relaxed(emptyw_bar + sw * 8, ring.phase(it) ^ 1);
+        mbar_wait(emptyw_bar + sw * 8, ring.phase(it) ^ 1);
         ring.advance(it);
 #ifdef APH_RING_FAULT
         if (it & 1) {
@@ -364,7 +364,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 #pragma unroll 1
       for (int ks = k0; ks < k1; ++ks, ++it) {
         const int sa = ring.slot(it);
-        mbar_wait_relaxed(emptya_bar + sa * 8, ring.phase(it) ^ 1);
+        mbar_wait(emptya_bar + sa * 8, ring.phase(it) ^ 1);
         ring.advance(it);
         const uint32_t dst = smem_base + C::ACT_OFF + sa * C::ACT_BYTES;
         const uint32_t fb = ready_bar + sa * 8;
@@ -680,7 +680,14 @@ __global__ void __launch_bounds__(THREADS, 1)
 #ifdef APH_GEMM_TRACE
       if (etr) p.trace[512 + seg * 8 + 0] = clock64();
 #endif
-      mbar_wait(done_bar + db * 8, (seg / NDBUF) & 1);
+      // The accumulator is complete one main-loop pass over this segment from now (~350 ns per stage). A waiting warp
+      // is woken by every barrier event of the CTA, and four warps polling through the whole pass took 7 % of the
+      // kernel's issue slots from the dequantisers (profiles/r02_ncu_gemm_tc_gate_up_m64_g128.txt): sleep through most
+      // of the pass first (__nanosleep(t) returns within 2 t).
+      if (!mbar_test(done_bar + db * 8, (seg / NDBUF) & 1)) {
+        __nanosleep((unsigned)min((k1 - k0) * 150, 200000));
+        mbar_wait(done_bar + db * 8, (seg / NDBUF) & 1);
+      }
       tc_fence_after();
 #ifdef APH_GEMM_TRACE
       if (etr) p.trace[512 + seg * 8 + 1] = clock64();

@@ -44,6 +44,11 @@ class OneShotAllReduce:
         self.buffer[: self.signal_bytes].zero_()
         self.handle = symm.rendezvous(self.buffer, group.group_name)
         self.peer_ptrs = int(self.handle.buffer_ptrs_dev)
+        # NVLS: the multicast mapping of the same buffer, 0 where the device / driver / container has no multicast support
+        try:
+            self.multicast_ptr = int(self.handle.multicast_ptr or 0)
+        except Exception:  # older torch: no such attribute
+            self.multicast_ptr = 0
         self.counters = torch.zeros(int(self.lib.aph_all_reduce_max_blocks()), dtype=torch.int32, device=self.device)
         torch.cuda.synchronize(self.device)
         dist.barrier(group)  # every rank's flags are zero before anybody starts
@@ -61,6 +66,21 @@ class OneShotAllReduce:
         # 1 MiB 25.4 / 16.9, 4 MiB 60 / 27 - the curves cross near 512 KiB
         return nbytes >= 512 * 1024
 
+    def mode(self, nbytes: int) -> str:
+        """Which kernel serves a message: "one_shot", "two_shot" or "multimem" (csrc/all_reduce.cu). APH_AR_MODE
+        (development) forces one; multimem needs the multicast mapping."""
+        env = os.environ.get("APH_AR_MODE")
+        if env in ("one_shot", "two_shot"):
+            return env
+        if os.environ.get("APH_AR_TWO_SHOT_BYTES") is not None:  # an explicit choice between the two rank-order kernels
+            return "two_shot" if self.two_shot(nbytes) else "one_shot"
+        if env == "multimem" and self.multicast_ptr:
+            return env
+        # Measured on 8 B200s (profiles/r02_all_reduce_multimem_n8.jsonl, us one-shot / two-shot / multimem): 256 KiB
+        # 11.5 / 14.9 / 16.3, 1 MiB 24.8 / 16.8 / 26.1, 4 MiB 60 / 26.9 / 36.0 - at these sizes the switch reduction's
+        # round trip costs more than the NVLink bytes it saves, so multimem stays opt-in (APH_AR_MODE=multimem).
+        return "two_shot" if self.two_shot(nbytes) else "one_shot"
+
     def should_use(self, x: torch.Tensor) -> bool:
         """One-shot pushes world x the message per rank, so on larger groups it only pays up to a size. The reference
         stops at 512 KiB (<= 4 ranks) and 256 KiB (<= 8 ranks) for its pull kernel (custom_all_reduce.cuh:563-570); the
@@ -75,11 +95,17 @@ class OneShotAllReduce:
     def all_reduce(self, x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """out = sum over ranks of x (out defaults to x: in place, as TPGroup.all_reduce)."""
         out = x if out is None else out
-        fn = self.lib.aph_two_shot_all_reduce if self.two_shot(x.numel() * x.element_size()) else self.lib.aph_one_shot_all_reduce
-        st = fn(
-            ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(x.data_ptr()), ctypes.c_void_p(self.peer_ptrs),
-            ctypes.c_void_p(self.counters.data_ptr()), self.rank, self.world_size, ctypes.c_int64(x.numel()), _DT[x.dtype],
-            ctypes.c_int64(self.max_size), self.max_blocks, ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+        mode = self.mode(x.numel() * x.element_size())
+        common = (self.rank, self.world_size, ctypes.c_int64(x.numel()), _DT[x.dtype], ctypes.c_int64(self.max_size), self.max_blocks,
+                  ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+        ptrs = (ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(x.data_ptr()), ctypes.c_void_p(self.peer_ptrs))
+        cnt = ctypes.c_void_p(self.counters.data_ptr())
+        if mode == "multimem":
+            st = self.lib.aph_multimem_all_reduce(*ptrs, ctypes.c_void_p(self.multicast_ptr), cnt, *common)
+        elif mode == "two_shot":
+            st = self.lib.aph_two_shot_all_reduce(*ptrs, cnt, *common)
+        else:
+            st = self.lib.aph_one_shot_all_reduce(*ptrs, cnt, *common)
         if st != 0:
             raise RuntimeError(self.lib.aph_b200_last_error().decode())
         return out
@@ -94,12 +120,17 @@ class OneShotAllReduce:
     def all_reduce_add_rms_norm(self, x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
         """x <- rms_norm(all_reduce(x) + residual) * weight, residual <- all_reduce(x) + residual: the all-reduce and the
         fused_add_rms_norm that follows it in every decoder layer, in one kernel."""
-        fn = (self.lib.aph_two_shot_all_reduce_add_rms_norm if self.two_shot(x.numel() * x.element_size())
-              else self.lib.aph_all_reduce_add_rms_norm)
-        st = fn(
-            ctypes.c_void_p(x.data_ptr()), ctypes.c_void_p(residual.data_ptr()), ctypes.c_void_p(weight.data_ptr()),
-            ctypes.c_float(epsilon), ctypes.c_void_p(self.peer_ptrs), ctypes.c_void_p(self.counters.data_ptr()), self.rank,
-            self.world_size, ctypes.c_int64(x.shape[0]), ctypes.c_int64(x.shape[1]), _DT[x.dtype], ctypes.c_int64(self.max_size),
-            ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+        mode = self.mode(x.numel() * x.element_size())
+        head = (ctypes.c_void_p(x.data_ptr()), ctypes.c_void_p(residual.data_ptr()), ctypes.c_void_p(weight.data_ptr()),
+                ctypes.c_float(epsilon), ctypes.c_void_p(self.peer_ptrs))
+        tail = (ctypes.c_void_p(self.counters.data_ptr()), self.rank, self.world_size, ctypes.c_int64(x.shape[0]),
+                ctypes.c_int64(x.shape[1]), _DT[x.dtype], ctypes.c_int64(self.max_size),
+                ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+        if mode == "multimem":
+            st = self.lib.aph_multimem_all_reduce_add_rms_norm(*head, ctypes.c_void_p(self.multicast_ptr), *tail)
+        elif mode == "two_shot":
+            st = self.lib.aph_two_shot_all_reduce_add_rms_norm(*head, *tail)
+        else:
+            st = self.lib.aph_all_reduce_add_rms_norm(*head, *tail)
         if st != 0:
             raise RuntimeError(self.lib.aph_b200_last_error().decode())

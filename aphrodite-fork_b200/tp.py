@@ -171,7 +171,7 @@ class TPGroup:
             return "none"
         if self.custom is None or not self.custom.should_use(x):
             return "NCCL" + (f" ({self.custom_error})" if self.custom_error else "")
-        kind = "two-shot" if self.custom.two_shot(x.numel() * x.element_size()) else "one-shot"
+        kind = self.custom.mode(x.numel() * x.element_size()).replace("_", "-")
         return f"{kind} peer-memory kernel fused with the residual add + RMSNorm (csrc/all_reduce.cu)"
 
     def all_reduce(self, x: torch.Tensor) -> torch.Tensor:

@@ -316,6 +316,21 @@ int aph_two_shot_all_reduce_add_rms_norm(void* x, void* residual, const void* we
                                          const void* const* peer_bufs_dev, uint32_t* counters, int rank, int world,
                                          int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes, void* stream);
 
+/* The NVLS ("multimem") variants - the reference has no counterpart (its custom all-reduce predates NVSwitch reductions;
+ * NCCL's NVLS algorithm is what it would fall back to): multicast_buf is the MULTICAST mapping of the same symmetric
+ * buffer (one address = the same offset in every rank's buffer; torch symmetric memory: handle.multicast_ptr). Each
+ * 16-byte vector is summed inside the switch by one multimem.ld_reduce of its owner rank and handed to every rank by one
+ * multimem.st. Same buffers, counters and calling discipline as the calls above (all may be mixed freely). The result is
+ * identical on every rank and from run to run; the order of the additions is the switch's, so it may differ from the
+ * rank-order sum of the other two variants in the last bit. Needs a device and driver with multicast support. */
+int aph_multimem_all_reduce(void* out, const void* in, const void* const* peer_bufs_dev, void* multicast_buf,
+                            uint32_t* counters, int rank, int world, int64_t numel, int dtype, int64_t slot_bytes,
+                            int max_blocks, void* stream);
+int aph_multimem_all_reduce_add_rms_norm(void* x, void* residual, const void* weight, float epsilon,
+                                         const void* const* peer_bufs_dev, void* multicast_buf, uint32_t* counters,
+                                         int rank, int world, int64_t num_tokens, int64_t hidden_size, int dtype,
+                                         int64_t slot_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

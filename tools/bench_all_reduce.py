@@ -1,5 +1,5 @@
 """Development microbench (torchrun, one rank per GPU): the row-parallel outputs' all-reduce of a decode step in
-isolation - NCCL, the one-shot and the two-shot peer-memory kernels (csrc/all_reduce.cu), alone and fused with the
+isolation - NCCL, the one-shot, two-shot and (where the box has multicast support) multimem kernels (csrc/all_reduce.cu), alone and fused with the
 residual add + RMSNorm - for messages of rows x 8192 bf16. CUDA-graph replay of 50 calls, max over ranks; rank 0 prints
 one JSON line per size with the microseconds per call and the NVLink egress per rank each variant implies.
     python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 tools/bench_all_reduce.py"""
@@ -58,14 +58,20 @@ def main():
         out = {"rows": rows, "KiB": nbytes // 1024, "world": world}
         out["nccl"] = timed(lambda: dist.all_reduce(x))
         out["nccl_plus_norm"] = timed(lambda: (dist.all_reduce(x), ops.fused_add_rms_norm(x, res, w, 1e-5)))
-        for name, thr in (("one_shot", "0"), ("two_shot", "16")):
-            os.environ["APH_AR_TWO_SHOT_BYTES"] = thr
+        modes = ("one_shot", "two_shot") + (("multimem", "multimem_32cta") if tp.custom.multicast_ptr else ())
+        for name in modes:
+            os.environ["APH_AR_MODE"] = name.split("_32")[0]
+            tp.custom.max_blocks = 32 if name.endswith("32cta") else 0
             x.normal_(0, 0.01)
             out[name] = timed(lambda: tp.custom.all_reduce(x))
             x.normal_(0, 0.01)
             res.zero_()
             out[name + "_fused_norm"] = timed(lambda: tp.custom.all_reduce_add_rms_norm(x, res, w, 1e-5))
-        out["egress_KiB_per_rank"] = {"one_shot": nbytes * (world - 1) // 1024, "two_shot": 2 * nbytes * (world - 1) // world // 1024}
+        os.environ.pop("APH_AR_MODE", None)
+        tp.custom.max_blocks = 0
+        out["default_mode"] = tp.custom.mode(nbytes)
+        out["egress_KiB_per_rank"] = {"one_shot": nbytes * (world - 1) // 1024, "two_shot": 2 * nbytes * (world - 1) // world // 1024,
+                                      "multimem": nbytes // 1024}
         if rank == 0:
             print(json.dumps(out), flush=True)
     dist.destroy_process_group()

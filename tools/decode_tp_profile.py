@@ -23,9 +23,12 @@ def main():
     layers = int(os.environ.get("LAYERS", "16"))
     cfg = DecodeConfig.llama3_70b(num_layers=layers)
     base = None
-    for name, env in (("default", {}), ("one_shot", {"APH_AR_TWO_SHOT_BYTES": "0"}), ("two_shot", {"APH_AR_TWO_SHOT_BYTES": "16"}),
-                      ("unfused_norm", {"APH_FUSED_AR_NORM": "0"}), ("nccl", {"APH_CUSTOM_AR": "0"})):
-        for k in ("APH_AR_TWO_SHOT_BYTES", "APH_FUSED_AR_NORM", "APH_CUSTOM_AR"):
+    only = os.environ.get("POLICIES")
+    for name, env in (("default", {}), ("one_shot", {"APH_AR_MODE": "one_shot"}), ("two_shot", {"APH_AR_MODE": "two_shot"}),
+                      ("multimem", {"APH_AR_MODE": "multimem"}), ("unfused_norm", {"APH_FUSED_AR_NORM": "0"}), ("nccl", {"APH_CUSTOM_AR": "0"})):
+        if only and name not in only.split(","):
+            continue
+        for k in ("APH_AR_TWO_SHOT_BYTES", "APH_AR_MODE", "APH_FUSED_AR_NORM", "APH_CUSTOM_AR"):
             os.environ.pop(k, None)
         os.environ.update(env)
         model = DecodeModel(cfg, batch=64, ctx=4096, tp=TPGroup(), device=dev, seed=0, weights_from=base)
