@@ -28,8 +28,18 @@
 // 2 (world - 1) / world), and each vector costs its owner two instructions instead of 2 x world. The order of the
 // additions is the switch's, not rank order: the result is identical on all ranks (one owner computes it) and the same
 // from run to run, but may differ from the rank-order sum in the last bit.
+// LL variants (the low-latency protocol of NCCL's "LL" algorithm restated for this two-shot exchange): every 8 bytes on the
+// wire are 4 bytes of data + a 4-byte flag = the call number, written with one store (8-byte stores are single-copy
+// atomic), so DATA ARRIVAL IS THE SIGNAL: no flag barrier, no system-scope fence and no round trip anywhere. (A) a thread
+// pushes each vector it does not own to the owner's receive lines, (C1) the owner polls the world - 1 lines of a vector
+// until their flags show this call, adds in rank order in fp32, rounds once and pushes the sum to every rank's result
+// lines, (C2) everybody polls its result lines. Twice the bytes on the wire of two-shot, but two one-way NVLink latencies
+// instead of two barriers of about 4 us each: the choice up to AR_LL_MAX_BYTES. The lines live in their own region
+// behind the slots (zeroed once by the host; a flag never repeats, and a line is only rewritten after its reader has
+// moved on: a rank can push call n + 1 only after it has received every owner's results of call n, which the owners send
+// after reading all lines of call n). Same rank-order sums as one-shot / two-shot: bit-identical to them.
 // Layout of a rank's buffer (from the host: torch symmetric memory / CUDA IPC): [ 4 KiB flags | 2 halves x world slots
-// x slot_bytes ]. A CTA only waits for the CTA with the same index on the peers and grids are at most 128 CTAs of 512
+// x slot_bytes | LL lines ]. A CTA only waits for the CTA with the same index on the peers and grids are at most 128 CTAs of 512
 // threads, so every waiting CTA is resident (no deadlock on a 148-SM part).
 #include <type_traits>
 
@@ -41,6 +51,13 @@ namespace {
 constexpr int AR_MAX_BLOCKS = 128;
 constexpr int AR_MAX_RANKS = 8;
 constexpr int AR_SIGNAL_BYTES = 4096;
+
+// LL: messages up to 2 MiB; a "row" is the 512 vectors one pass of a CTA covers
+constexpr int64_t AR_LL_MAX_BYTES = 2 << 20;
+constexpr int AR_LL_ROWS = 512;
+__host__ __device__ constexpr int ar_ll_chunk(int world) { return (512 + world - 1) / world; }  // threads (= vectors of a row) per owner
+__host__ __device__ constexpr int64_t ar_ll_recv_bytes(int world) { return (int64_t)world * AR_LL_ROWS * ar_ll_chunk(world) * 32; }
+__host__ __device__ constexpr int64_t ar_ll_result_bytes() { return (int64_t)AR_LL_ROWS * 512 * 32; }
 
 struct ArSignals {
   uint32_t arrived[AR_MAX_BLOCKS][AR_MAX_RANKS];
@@ -75,6 +92,63 @@ __device__ __forceinline__ uint4 multimem_ld_reduce(const void* p) {
 __device__ __forceinline__ void multimem_st(void* p, const uint4& v) {
   asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                : "memory");
+}
+
+// One 16-byte vector = two LL lines of {data, flag, data, flag}. The loads poll until both flags show this call.
+__device__ __forceinline__ void ll_store(uint8_t* lines, const uint4& v, uint32_t flag) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %2};" ::"l"(lines), "r"(v.x), "r"(flag), "r"(v.y) : "memory");
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %2};" ::"l"(lines + 16), "r"(v.z), "r"(flag), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ll_load(const uint8_t* lines, uint32_t flag) {
+  uint4 v;
+  uint32_t f0, f1, f2, f3;
+  for (uint32_t spins = 0;; ++spins) {
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(f0), "=r"(v.y), "=r"(f1) : "l"(lines) : "memory");
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.z), "=r"(f2), "=r"(v.w), "=r"(f3) : "l"(lines + 16) : "memory");
+    if (f0 == flag && f1 == flag && f2 == flag && f3 == flag) break;
+    if (spins > 4096) __nanosleep(128);
+    if (spins > (1u << 27)) __trap();  // a peer that never sends: end as a launch failure, not as a hung GPU
+  }
+  return v;
+}
+// rank-order fp32 sum of one vector: `own` for this rank, the received lines for the others. All world - 1 pairs of
+// lines are requested before the first flag is looked at (one L2 latency per attempt, not one per peer).
+template <typename T, int WORLD>
+__device__ __forceinline__ uint4 ll_sum(const uint4& own, const uint8_t* recv, int64_t src_stride, int rank, uint32_t flag) {
+  constexpr int VEC = 16 / (int)sizeof(T);
+  uint4 v[WORLD];
+  for (uint32_t spins = 0;; ++spins) {
+    uint32_t f[WORLD][4];
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r) {
+      const uint8_t* lines = recv + r * src_stride;
+      if (r != rank) {
+        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v[r].x), "=r"(f[r][0]), "=r"(v[r].y), "=r"(f[r][1]) : "l"(lines) : "memory");
+        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(v[r].z), "=r"(f[r][2]), "=r"(v[r].w), "=r"(f[r][3])
+                     : "l"(lines + 16)
+                     : "memory");
+      }
+    }
+    bool ok = true;
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r)
+      if (r != rank) ok = ok && f[r][0] == flag && f[r][1] == flag && f[r][2] == flag && f[r][3] == flag;
+    if (ok) break;
+    if (spins > 4096) __nanosleep(128);
+    if (spins > (1u << 27)) __trap();  // a peer that never sends: end as a launch failure, not as a hung GPU
+  }
+  float acc[VEC];
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) acc[e] = ScalarTraits<T>::to_float(reinterpret_cast<const T*>(rank == 0 ? &own : &v[0])[e]);
+#pragma unroll
+  for (int r = 1; r < WORLD; ++r)
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) acc[e] += ScalarTraits<T>::to_float(reinterpret_cast<const T*>(r == rank ? &own : &v[r])[e]);
+  uint4 o;
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) reinterpret_cast<T*>(&o)[e] = ScalarTraits<T>::from_float(acc[e]);
+  return o;
 }
 
 // Barrier with the CTA of the same index on every peer: publish `flag` (release: this CTA's earlier stores, ordered
@@ -122,7 +196,7 @@ __device__ __forceinline__ uint4 ar_sum_slots(const uint8_t* mine, int64_t slot_
   return o;
 }
 
-constexpr int AR_ONE_SHOT = 0, AR_TWO_SHOT = 1, AR_MULTIMEM = 2;
+constexpr int AR_ONE_SHOT = 0, AR_TWO_SHOT = 1, AR_MULTIMEM = 2, AR_LL = 3;
 
 template <typename T, int WORLD, int MODE>
 __global__ void __launch_bounds__(512, 1)
@@ -166,6 +240,25 @@ __global__ void __launch_bounds__(512, 1)
     ar_barrier<WORLD>(s_bufs, rank, 2 * call + 1);  // (B2)
     // (C2)
     for (int64_t i = first; i < n_vec; i += stride) reinterpret_cast<V*>(out)[i] = __ldcv(reinterpret_cast<const V*>(mine + owner * slot_bytes) + i);
+  } else if (MODE == AR_LL) {
+    constexpr int CS = ar_ll_chunk(WORLD);
+    const int owner = (int)threadIdx.x / CS, lj = (int)threadIdx.x - owner * CS;
+    const int64_t ll_off = AR_SIGNAL_BYTES + (int64_t)2 * WORLD * slot_bytes;  // receive lines [source][row][chunk], then result lines [row][512]
+    const int64_t src_stride = (int64_t)AR_LL_ROWS * CS * 32;
+    // (A) vectors owned elsewhere go to their owner's receive lines
+    if (owner != rank)
+      for (int64_t i = first; i < n_vec; i += stride)
+        ll_store(s_bufs[owner] + ll_off + rank * src_stride + ((i >> 9) * CS + lj) * 32, reinterpret_cast<const V*>(in)[i], call);
+    // (C1) the owner adds in rank order as the lines arrive and sends the rounded sum to every rank's result lines
+    if (owner == rank)
+      for (int64_t i = first; i < n_vec; i += stride) {
+        const V o = ll_sum<T, WORLD>(reinterpret_cast<const V*>(in)[i], s_bufs[rank] + ll_off + ((i >> 9) * CS + lj) * 32, src_stride, rank, call);
+#pragma unroll
+        for (int r = 0; r < WORLD; ++r) ll_store(s_bufs[r] + ll_off + ar_ll_recv_bytes(WORLD) + i * 32, o, call);
+      }
+    // (C2)
+    for (int64_t i = first; i < n_vec; i += stride)
+      reinterpret_cast<V*>(out)[i] = ll_load(s_bufs[rank] + ll_off + ar_ll_recv_bytes(WORLD) + i * 32, call);
   } else {
     const int owner = (int)threadIdx.x * WORLD / (int)blockDim.x;
     // (A) my partial into slot 0 of my own buffer
@@ -213,7 +306,8 @@ __global__ void __launch_bounds__(512, 1)
     all_reduce_add_rms_norm_kernel(T* x, T* residual, const T* __restrict__ weight, float epsilon,
                                    uint8_t* const* __restrict__ peer_bufs, uint8_t* multicast_buf, uint32_t* __restrict__ counters,
                                    int rank, int rows, int hidden, int64_t slot_bytes) {
-  constexpr bool TWO_SHOT = MODE == AR_TWO_SHOT, MULTIMEM = MODE == AR_MULTIMEM;
+  constexpr bool TWO_SHOT = MODE == AR_TWO_SHOT, MULTIMEM = MODE == AR_MULTIMEM, LL = MODE == AR_LL;
+  constexpr int CS = ar_ll_chunk(WORLD);
   constexpr int VEC = 16 / (int)sizeof(T);
   constexpr int ITER = 4;  // hidden <= 4 * 512 * VEC
   using V = uint4;
@@ -233,8 +327,30 @@ __global__ void __launch_bounds__(512, 1)
   const uint32_t call = counters[blockIdx.x] + 1;  // after the wait, see one_shot_all_reduce_kernel
   const int64_t half_off = AR_SIGNAL_BYTES + (int64_t)(call & 1) * WORLD * slot_bytes;
   const uint8_t* mine = s_bufs[rank] + half_off;
-  const int owner = (int)threadIdx.x * WORLD / (int)blockDim.x;  // two-shot, multimem: owner of every vector this thread handles
+  // two-shot, multimem, LL: the owner of every vector this thread handles
+  const int owner = LL ? (int)threadIdx.x / CS : (int)threadIdx.x * WORLD / (int)blockDim.x;
+  const int lj = (int)threadIdx.x - owner * CS;
+  const int64_t ll_off = AR_SIGNAL_BYTES + (int64_t)2 * WORLD * slot_bytes, src_stride = (int64_t)AR_LL_ROWS * CS * 32;
+  const int passes = (nvec + (int)blockDim.x - 1) / (int)blockDim.x;  // LL: line row of (row, pass) = row * passes + pass < AR_LL_ROWS
+  if (LL) {
+    // (A) + (C1) without barriers: push what others own, add what I own as it arrives and hand the sums to every rank
+    for (int row = blockIdx.x; row < rows; row += gridDim.x)
+      for (int i = threadIdx.x, ps = 0; i < nvec; i += blockDim.x, ++ps)
+        if (owner != rank)
+          ll_store(s_bufs[owner] + ll_off + rank * src_stride + ((int64_t)(row * passes + ps) * CS + lj) * 32,
+                   reinterpret_cast<const V*>(x)[(int64_t)row * nvec + i], call);
+    if (owner == rank)
+      for (int row = blockIdx.x; row < rows; row += gridDim.x)
+        for (int i = threadIdx.x, ps = 0; i < nvec; i += blockDim.x, ++ps) {
+          const int64_t lrow = (int64_t)row * passes + ps;
+          const V o = ll_sum<T, WORLD>(reinterpret_cast<const V*>(x)[(int64_t)row * nvec + i], s_bufs[rank] + ll_off + (lrow * CS + lj) * 32,
+                                       src_stride, rank, call);
+#pragma unroll
+          for (int r = 0; r < WORLD; ++r) ll_store(s_bufs[r] + ll_off + ar_ll_recv_bytes(WORLD) + (lrow * 512 + threadIdx.x) * 32, o, call);
+        }
+  }
   // (A) push this CTA's rows: to everybody, or (two-shot) to the owner of each vector
+  if (!LL)
   for (int row = blockIdx.x; row < rows; row += gridDim.x)
     for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
       const int64_t idx = (int64_t)row * nvec + i;
@@ -248,7 +364,7 @@ __global__ void __launch_bounds__(512, 1)
         for (int r = 0; r < WORLD; ++r) reinterpret_cast<V*>(s_bufs[r] + half_off + rank * slot_bytes)[idx] = v;
       }
     }
-  ar_barrier<WORLD>(s_bufs, rank, 2 * call);  // (B) / (B1)
+  if (!LL) ar_barrier<WORLD>(s_bufs, rank, 2 * call);  // (B) / (B1)
   if (TWO_SHOT) {
     // (C1) the owner reduces its vectors and hands the rounded sums to every rank (slot `rank` at these positions)
     if (owner == rank)
@@ -283,7 +399,8 @@ __global__ void __launch_bounds__(512, 1)
       if (i < nvec) {
         const int64_t idx = (int64_t)row * nvec + i;
         // the all-reduce's output, rounded to T: summed here in rank order (one-shot) or by the vector's owner (two-shot)
-        const V sum = MULTIMEM   ? __ldcv(reinterpret_cast<const V*>(mine + slot_bytes) + idx)
+        const V sum = LL         ? ll_load(s_bufs[rank] + ll_off + ar_ll_recv_bytes(WORLD) + (((int64_t)row * passes + it) * 512 + threadIdx.x) * 32, call)
+                      : MULTIMEM ? __ldcv(reinterpret_cast<const V*>(mine + slot_bytes) + idx)
                       : TWO_SHOT ? __ldcv(reinterpret_cast<const V*>(mine + owner * slot_bytes) + idx)
                                  : ar_sum_slots<T, WORLD>(mine, slot_bytes, idx);
         const V res = reinterpret_cast<const V*>(residual)[idx];
@@ -334,6 +451,8 @@ int launch_ar_norm(void* x, void* residual, const void* weight, float eps, const
       APH_ARN_MODE(W, AR_TWO_SHOT);       \
     } else if (mode == AR_MULTIMEM) {     \
       APH_ARN_MODE(W, AR_MULTIMEM);       \
+    } else if (mode == AR_LL) {           \
+      APH_ARN_MODE(W, AR_LL);             \
     } else {                              \
       APH_ARN_MODE(W, AR_ONE_SHOT);       \
     }                                     \
@@ -361,6 +480,8 @@ int launch_one_shot(void* out, const void* in, const void* const* peer_bufs, voi
       APH_AR_MODE(W, AR_TWO_SHOT);       \
     } else if (mode == AR_MULTIMEM) {    \
       APH_AR_MODE(W, AR_MULTIMEM);       \
+    } else if (mode == AR_LL) {          \
+      APH_AR_MODE(W, AR_LL);             \
     } else {                             \
       APH_AR_MODE(W, AR_ONE_SHOT);       \
     }                                    \
@@ -389,6 +510,8 @@ int all_reduce_entry(const char* op, int mode, void* out, const void* in, const 
             "%s: the message must be a multiple of 16 bytes and 16-byte aligned", op);
   APH_CHECK(slot_bytes % 16 == 0 && numel * esz <= slot_bytes, APH_ERR_INVALID_ARGUMENT,
             "%s: message of %lld bytes does not fit the %lld-byte slots", op, (long long)(numel * esz), (long long)slot_bytes);
+  APH_CHECK(mode != AR_LL || numel * esz <= AR_LL_MAX_BYTES, APH_ERR_INVALID_ARGUMENT, "%s: the LL lines hold messages up to %lld bytes", op,
+            (long long)AR_LL_MAX_BYTES);
   const int64_t n_vec = numel * esz / 16;
   int blocks = (int)std::min<int64_t>((n_vec + 511) / 512, std::min(max_blocks > 0 ? max_blocks : AR_MAX_BLOCKS, AR_MAX_BLOCKS));
   blocks = std::max(blocks, 1);
@@ -416,6 +539,9 @@ int ar_norm_entry(const char* op, int mode, void* x, void* residual, const void*
   APH_CHECK(aligned16(x) && aligned16(residual) && aligned16(weight), APH_ERR_INVALID_ARGUMENT, "%s: tensors must be 16-byte aligned", op);
   APH_CHECK(slot_bytes % 16 == 0 && num_tokens * hidden_size * 2 <= slot_bytes, APH_ERR_INVALID_ARGUMENT,
             "%s: message does not fit the %lld-byte slots", op, (long long)slot_bytes);
+  APH_CHECK(mode != AR_LL || (num_tokens * hidden_size * 2 <= AR_LL_MAX_BYTES && num_tokens * ((hidden_size / 8 + 511) / 512) <= AR_LL_ROWS),
+            APH_ERR_INVALID_ARGUMENT, "%s: the LL lines hold messages up to %lld bytes in at most %d passes of 512 vectors", op,
+            (long long)AR_LL_MAX_BYTES, AR_LL_ROWS);
   cudaStream_t s = (cudaStream_t)stream;
   if (dtype == APH_DT_F16)
     return launch_ar_norm<__half>(x, residual, weight, epsilon, peer_bufs_dev, mc, counters, rank, world, (int)num_tokens, (int)hidden_size,
@@ -433,7 +559,22 @@ extern "C" size_t aph_all_reduce_signal_bytes(void) { return AR_SIGNAL_BYTES; }
 extern "C" int aph_all_reduce_max_blocks(void) { return AR_MAX_BLOCKS; }
 
 extern "C" size_t aph_all_reduce_buffer_bytes(int world, int64_t slot_bytes) {
-  return (size_t)AR_SIGNAL_BYTES + (size_t)2 * world * slot_bytes;
+  return (size_t)AR_SIGNAL_BYTES + (size_t)2 * world * slot_bytes + (size_t)ar_ll_recv_bytes(world) + (size_t)ar_ll_result_bytes();
+}
+extern "C" size_t aph_all_reduce_ll_max_bytes(void) { return (size_t)AR_LL_MAX_BYTES; }
+extern "C" int aph_all_reduce_ll_max_passes(void) { return AR_LL_ROWS; }
+
+extern "C" int aph_ll_all_reduce(void* out, const void* in, const void* const* peer_bufs_dev, uint32_t* counters, int rank, int world,
+                                 int64_t numel, int dtype, int64_t slot_bytes, int max_blocks, void* stream) {
+  return all_reduce_entry("ll_all_reduce", AR_LL, out, in, peer_bufs_dev, nullptr, counters, rank, world, numel, dtype, slot_bytes, max_blocks,
+                          stream);
+}
+
+extern "C" int aph_ll_all_reduce_add_rms_norm(void* x, void* residual, const void* weight, float epsilon, const void* const* peer_bufs_dev,
+                                              uint32_t* counters, int rank, int world, int64_t num_tokens, int64_t hidden_size, int dtype,
+                                              int64_t slot_bytes, void* stream) {
+  return ar_norm_entry("ll_all_reduce_add_rms_norm", AR_LL, x, residual, weight, epsilon, peer_bufs_dev, nullptr, counters, rank, world,
+                       num_tokens, hidden_size, dtype, slot_bytes, stream);
 }
 
 extern "C" int aph_one_shot_all_reduce(void* out, const void* in, const void* const* peer_bufs_dev, uint32_t* counters, int rank,

@@ -683,9 +683,9 @@ __global__ void __launch_bounds__(THREADS, 1)
       // The accumulator is complete one main-loop pass over this segment from now (~350 ns per stage). A waiting warp
       // is woken by every barrier event of the CTA, and four warps polling through the whole pass took 7 % of the
       // kernel's issue slots from the dequantisers (profiles/r02_ncu_gemm_tc_gate_up_m64_g128.txt): sleep through most
-      // of the pass first (__nanosleep(t) returns within 2 t).
+      // of the pass first (__nanosleep(t) returns within 2 t: 100 ns per stage asks for at most 200).
       if (!mbar_test(done_bar + db * 8, (seg / NDBUF) & 1)) {
-        __nanosleep((unsigned)min((k1 - k0) * 150, 200000));
+        __nanosleep((unsigned)min((k1 - k0) * 100, 200000));
         mbar_wait(done_bar + db * 8, (seg / NDBUF) & 1);
       }
       tc_fence_after();

@@ -41,7 +41,10 @@ class OneShotAllReduce:
         self.lib.aph_all_reduce_buffer_bytes.restype = ctypes.c_size_t
         total = int(self.lib.aph_all_reduce_buffer_bytes(self.world_size, ctypes.c_int64(max_size)))
         self.buffer = symm.empty(total, dtype=torch.uint8, device=self.device)
-        self.buffer[: self.signal_bytes].zero_()
+        self.buffer.zero_()  # the flags and the LL lines start at zero (a line's flag is the call number, from 1 on)
+        self.lib.aph_all_reduce_ll_max_bytes.restype = ctypes.c_size_t
+        self.ll_max_bytes = int(self.lib.aph_all_reduce_ll_max_bytes())
+        self.ll_max_passes = int(self.lib.aph_all_reduce_ll_max_passes())
         self.handle = symm.rendezvous(self.buffer, group.group_name)
         self.peer_ptrs = int(self.handle.buffer_ptrs_dev)
         # NVLS: the multicast mapping of the same buffer, 0 where the device / driver / container has no multicast support
@@ -66,19 +69,27 @@ class OneShotAllReduce:
         # 1 MiB 25.4 / 16.9, 4 MiB 60 / 27 - the curves cross near 512 KiB
         return nbytes >= 512 * 1024
 
-    def mode(self, nbytes: int) -> str:
-        """Which kernel serves a message: "one_shot", "two_shot" or "multimem" (csrc/all_reduce.cu). APH_AR_MODE
-        (development) forces one; multimem needs the multicast mapping."""
+    def mode(self, nbytes: int, rows: int = 0, hidden: int = 0) -> str:
+        """Which kernel serves a message: "ll", "one_shot", "two_shot" or "multimem" (csrc/all_reduce.cu). rows / hidden
+        describe the fused add + RMSNorm call (its LL form holds rows x ceil(hidden / 4096) passes of 512 vectors).
+        APH_AR_MODE (development) forces one; multimem needs the multicast mapping."""
+        ll_ok = nbytes <= self.ll_max_bytes and rows * ((hidden // 8 + 511) // 512) <= self.ll_max_passes
         env = os.environ.get("APH_AR_MODE")
         if env in ("one_shot", "two_shot"):
             return env
-        if os.environ.get("APH_AR_TWO_SHOT_BYTES") is not None:  # an explicit choice between the two rank-order kernels
-            return "two_shot" if self.two_shot(nbytes) else "one_shot"
         if env == "multimem" and self.multicast_ptr:
             return env
+        if env == "ll" and ll_ok:
+            return env
+        if os.environ.get("APH_AR_TWO_SHOT_BYTES") is not None:  # an explicit choice between the two barrier kernels
+            return "two_shot" if self.two_shot(nbytes) else "one_shot"
         # Measured on 8 B200s (profiles/r02_all_reduce_multimem_n8.jsonl, us one-shot / two-shot / multimem): 256 KiB
         # 11.5 / 14.9 / 16.3, 1 MiB 24.8 / 16.8 / 26.1, 4 MiB 60 / 26.9 / 36.0 - at these sizes the switch reduction's
         # round trip costs more than the NVLink bytes it saves, so multimem stays opt-in (APH_AR_MODE=multimem).
+        # LL against the best barrier kernel, 8 B200s, fused with the norm (profiles/r02_all_reduce_ll_n8.jsonl): 16 KiB 9.4 vs
+        # 9.9 us, 256 KiB 10.2 vs 13.2, 1 MiB 15.6 vs 18.0, 2 MiB 27.0 vs 20.3 (the doubled bytes win). Two ranks: ahead to 256 KiB.
+        if ll_ok and env != "no_ll" and nbytes <= (1 << 20 if self.world_size > 2 else 1 << 19):
+            return "ll"
         return "two_shot" if self.two_shot(nbytes) else "one_shot"
 
     def should_use(self, x: torch.Tensor) -> bool:
@@ -102,6 +113,8 @@ class OneShotAllReduce:
         cnt = ctypes.c_void_p(self.counters.data_ptr())
         if mode == "multimem":
             st = self.lib.aph_multimem_all_reduce(*ptrs, ctypes.c_void_p(self.multicast_ptr), cnt, *common)
+        elif mode == "ll":
+            st = self.lib.aph_ll_all_reduce(*ptrs, cnt, *common)
         elif mode == "two_shot":
             st = self.lib.aph_two_shot_all_reduce(*ptrs, cnt, *common)
         else:
@@ -120,7 +133,7 @@ class OneShotAllReduce:
     def all_reduce_add_rms_norm(self, x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
         """x <- rms_norm(all_reduce(x) + residual) * weight, residual <- all_reduce(x) + residual: the all-reduce and the
         fused_add_rms_norm that follows it in every decoder layer, in one kernel."""
-        mode = self.mode(x.numel() * x.element_size())
+        mode = self.mode(x.numel() * x.element_size(), x.shape[0], x.shape[1])
         head = (ctypes.c_void_p(x.data_ptr()), ctypes.c_void_p(residual.data_ptr()), ctypes.c_void_p(weight.data_ptr()),
                 ctypes.c_float(epsilon), ctypes.c_void_p(self.peer_ptrs))
         tail = (ctypes.c_void_p(self.counters.data_ptr()), self.rank, self.world_size, ctypes.c_int64(x.shape[0]),
@@ -128,6 +141,8 @@ class OneShotAllReduce:
                 ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
         if mode == "multimem":
             st = self.lib.aph_multimem_all_reduce_add_rms_norm(*head, ctypes.c_void_p(self.multicast_ptr), *tail)
+        elif mode == "ll":
+            st = self.lib.aph_ll_all_reduce_add_rms_norm(*head, *tail)
         elif mode == "two_shot":
             st = self.lib.aph_two_shot_all_reduce_add_rms_norm(*head, *tail)
         else:

@@ -316,6 +316,20 @@ int aph_two_shot_all_reduce_add_rms_norm(void* x, void* residual, const void* we
                                          const void* const* peer_bufs_dev, uint32_t* counters, int rank, int world,
                                          int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes, void* stream);
 
+/* The LL variants: the same two-shot exchange with NCCL's low-latency wire format - every 8 bytes carry 4 bytes of data
+ * and the call number as a flag in one atomic store, so the arrival of the data is the signal and there is no flag
+ * barrier and no fence (two one-way NVLink latencies instead of two barriers; twice the bytes on the wire). Messages up
+ * to aph_all_reduce_ll_max_bytes(); the fused form also needs num_tokens * ceil(hidden_size / 4096) <=
+ * aph_all_reduce_ll_max_passes(). Rank-order fp32 sums: bit-identical to the one-shot / two-shot calls, with which they
+ * mix freely. The buffer (aph_all_reduce_buffer_bytes) must be ZEROED once before the first call. */
+size_t aph_all_reduce_ll_max_bytes(void);
+int aph_all_reduce_ll_max_passes(void);
+int aph_ll_all_reduce(void* out, const void* in, const void* const* peer_bufs_dev, uint32_t* counters, int rank,
+                      int world, int64_t numel, int dtype, int64_t slot_bytes, int max_blocks, void* stream);
+int aph_ll_all_reduce_add_rms_norm(void* x, void* residual, const void* weight, float epsilon,
+                                   const void* const* peer_bufs_dev, uint32_t* counters, int rank, int world,
+                                   int64_t num_tokens, int64_t hidden_size, int dtype, int64_t slot_bytes, void* stream);
+
 /* The NVLS ("multimem") variants - the reference has no counterpart (its custom all-reduce predates NVSwitch reductions;
  * NCCL's NVLS algorithm is what it would fall back to): multicast_buf is the MULTICAST mapping of the same symmetric
  * buffer (one address = the same offset in every rank's buffer; torch symmetric memory: handle.multicast_ptr). Each

@@ -92,7 +92,14 @@ def test_argument_checks_of_the_next_row_entry_points():
     assert lib.aph_copy_blocks_mla(None, None, 0, i64(0), i64(16), None) == 0
 
     assert lib.aph_all_reduce_signal_bytes() == 4096
-    assert lib.aph_all_reduce_buffer_bytes(4, i64(1 << 20)) == 4096 + 2 * 4 * (1 << 20)
+    # flags | 2 halves x world slots | LL lines: world x 512 passes x ceil(512 / world) receive lines + 512 x 512 result lines of 32 bytes
+    assert lib.aph_all_reduce_buffer_bytes(4, i64(1 << 20)) == 4096 + 2 * 4 * (1 << 20) + 4 * 512 * 128 * 32 + 512 * 512 * 32
+    lib.aph_all_reduce_ll_max_bytes.restype = ctypes.c_size_t
+    assert lib.aph_all_reduce_ll_max_bytes() == 2 << 20 and lib.aph_all_reduce_ll_max_passes() == 512
+    assert lib.aph_ll_all_reduce(one, one, one, one, 0, 2, i64(4 << 20), 2, i64(16 << 20), 0, None) != 0
+    assert b"LL lines" in lib.aph_b200_last_error()
+    assert lib.aph_multimem_all_reduce(one, one, one, None, one, 0, 2, i64(1024), 2, i64(1 << 20), 0, None) != 0
+    assert b"multicast" in lib.aph_b200_last_error()
     assert 1 <= lib.aph_all_reduce_max_blocks() <= 148
     assert lib.aph_one_shot_all_reduce(one, one, one, one, 0, 3, i64(1024), 2, i64(1 << 20), 0, None) != 0
     assert b"world size 3" in lib.aph_b200_last_error()

@@ -179,11 +179,11 @@ def _ar_worker(rank, world, port, q):
         # ... and, where the box has multicast (NVLS) support, through the multimem kernel: the switch adds in its own
         # order, so that result is checked to one ulp of the rank-order sum and to be identical on every rank
         has_mc = bool(tp.custom.multicast_ptr)
-        for mode in ("0", "16", None) + (("multimem",) if has_mc else ()):
+        for mode in ("0", "16", "ll", None) + (("multimem",) if has_mc else ()):
           os.environ.pop("APH_AR_TWO_SHOT_BYTES", None)
           os.environ.pop("APH_AR_MODE", None)
-          if mode == "multimem":
-              os.environ["APH_AR_MODE"] = "multimem"
+          if mode in ("multimem", "ll"):
+              os.environ["APH_AR_MODE"] = mode
           elif mode is not None:
               os.environ["APH_AR_TWO_SHOT_BYTES"] = mode
           exact = mode != "multimem"  # the default policy only picks the rank-order kernels
@@ -219,11 +219,11 @@ def _ar_worker(rank, world, port, q):
         os.environ.pop("APH_AR_MODE", None)
         # all-reduce fused with the residual add + RMSNorm that follows it: against the unfused pair of kernels
         from aphrodite_fork_b200 import _custom_ops as ops
-        for mode in ("0", "16") + (("multimem",) if has_mc else ()):
+        for mode in ("0", "16", "ll") + (("multimem",) if has_mc else ()):
           os.environ.pop("APH_AR_TWO_SHOT_BYTES", None)
           os.environ.pop("APH_AR_MODE", None)
-          if mode == "multimem":
-              os.environ["APH_AR_MODE"] = "multimem"  # the unfused call below goes through the multimem kernel too
+          if mode in ("multimem", "ll"):
+              os.environ["APH_AR_MODE"] = mode  # the unfused call below goes through the same kind of kernel
           else:
               os.environ["APH_AR_TWO_SHOT_BYTES"] = mode
           for dtype in (torch.bfloat16, torch.float16):
@@ -251,7 +251,7 @@ def _ar_worker(rank, world, port, q):
                     bad.append(("fused norm", mode, str(dtype), m, h, int(d.max())))
         os.environ.pop("APH_AR_TWO_SHOT_BYTES", None)
         os.environ.pop("APH_AR_MODE", None)
-        os.environ["APH_AR_TWO_SHOT_BYTES"] = "1048576"  # the rank-order kernels for the exact checks below
+        # (the default policy only picks rank-order kernels: the exact checks below run through it - LL for these sizes)
         # too large / misaligned messages take NCCL
         big = torch.ones(5 * 1024 * 1024, device=dev, dtype=torch.bfloat16)
         assert not tp.custom.should_use(big)

@@ -58,7 +58,7 @@ def main():
         out = {"rows": rows, "KiB": nbytes // 1024, "world": world}
         out["nccl"] = timed(lambda: dist.all_reduce(x))
         out["nccl_plus_norm"] = timed(lambda: (dist.all_reduce(x), ops.fused_add_rms_norm(x, res, w, 1e-5)))
-        modes = ("one_shot", "two_shot") + (("multimem", "multimem_32cta") if tp.custom.multicast_ptr else ())
+        modes = ("one_shot", "two_shot", "ll") + (("multimem",) if tp.custom.multicast_ptr and os.environ.get("WITH_MULTIMEM") else ())
         for name in modes:
             os.environ["APH_AR_MODE"] = name.split("_32")[0]
             tp.custom.max_blocks = 32 if name.endswith("32cta") else 0
@@ -71,7 +71,7 @@ def main():
         tp.custom.max_blocks = 0
         out["default_mode"] = tp.custom.mode(nbytes)
         out["egress_KiB_per_rank"] = {"one_shot": nbytes * (world - 1) // 1024, "two_shot": 2 * nbytes * (world - 1) // world // 1024,
-                                      "multimem": nbytes // 1024}
+                                      "ll": 4 * nbytes * (world - 1) // world // 1024, "multimem": nbytes // 1024}
         if rank == 0:
             print(json.dumps(out), flush=True)
     dist.destroy_process_group()

@@ -25,7 +25,7 @@ def main():
     base = None
     only = os.environ.get("POLICIES")
     for name, env in (("default", {}), ("one_shot", {"APH_AR_MODE": "one_shot"}), ("two_shot", {"APH_AR_MODE": "two_shot"}),
-                      ("multimem", {"APH_AR_MODE": "multimem"}), ("unfused_norm", {"APH_FUSED_AR_NORM": "0"}), ("nccl", {"APH_CUSTOM_AR": "0"})):
+                      ("multimem", {"APH_AR_MODE": "multimem"}), ("ll", {"APH_AR_MODE": "ll"}), ("unfused_norm", {"APH_FUSED_AR_NORM": "0"}), ("nccl", {"APH_CUSTOM_AR": "0"})):
         if only and name not in only.split(","):
             continue
         for k in ("APH_AR_TWO_SHOT_BYTES", "APH_AR_MODE", "APH_FUSED_AR_NORM", "APH_CUSTOM_AR"):
