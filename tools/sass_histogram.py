@@ -10,7 +10,7 @@ import sys
 
 LIB = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "aphrodite-fork_b200", "lib", "libaphrodite_b200.so")
 OPS = ["UTCHMMA", "UTCQMMA", "STTM", "LDTM", "UTMALDG", "UBLKCP", "UTMAPF", "HMMA", "LDSM", "MOVM", "SYNCS", "UCGABAR_ARV", "UCGABAR_WAIT",
-       "ACQBULK", "PREEXIT", "UTCBAR", "ELECT", "REDUX", "ATOM", "RED", "F2FP", "MUFU.EX2"]
+       "ACQBULK", "PREEXIT", "UTCBAR", "ELECT", "REDUX", "ATOM", "RED", "F2FP", "MUFU.EX2", "LDGMC", "STGMC", "NANOSLEEP"]
 
 
 def main():
