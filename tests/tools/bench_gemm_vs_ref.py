@@ -39,6 +39,7 @@ def bench(fn, K, N, M, g=128, iters=30):
                 f(i)
         gph.replay()
         st.synchronize()
+        torch.cuda._sleep(2_000_000)  # the host enqueues the launch while the device is busy: the events see kernels only
         e0.record(st)
         gph.replay()
         e1.record(st)

@@ -30,6 +30,7 @@ def timed(fn, iters=50):
     torch.cuda.synchronize()
     dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda._sleep(2_000_000)  # the host enqueues the launches while the device is busy: the events see kernels only
     e0.record()
     g.replay()
     g.replay()

@@ -54,6 +54,7 @@ def bench(name, h, kvh, d, batch, ctx, kv, iters=20):
             gph.replay()
             st.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda._sleep(2_000_000)  # the host enqueues the launches while the device is busy: the events see kernels only
             e0.record(st)
             gph.replay()
             gph.replay()

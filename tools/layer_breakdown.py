@@ -32,6 +32,7 @@ def timed(make_call, n_variants, iters=20):
         g.replay()
         st.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda._sleep(2_000_000)  # the host enqueues the launches while the device is busy: the events see kernels only
         e0.record(st)
         g.replay()
         g.replay()
