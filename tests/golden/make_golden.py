@@ -145,6 +145,58 @@ def make_repack(st, qu, mu, mt):
     print("marlin_repack_golden.npz:", len(out), "arrays")
 
 
+def make_marlin_utils(st, qu, mu, mt):
+    """Host helpers of the Marlin format (marlin_utils.py:188-300, quant_utils.py:485-540) evaluated by the reference's own
+    Python: scale / zero-point permutations, column packers, g_idx sort, ScalarType ids, the support predicates."""
+    out = {}
+    g = torch.Generator().manual_seed(7)
+    sp, sps = mu.get_scale_perms()
+    out["scale_perm"], out["scale_perm_single"] = np.array(sp), np.array(sps)
+    # (size_k, size_n, group_size, num_bits)
+    cases = [(256, 128, 128, 4), (256, 192, 64, 4), (128, 256, 32, 8), (512, 64, -1, 4), (256, 320, 128, 8)]
+    for ci, (k, n, gs, bits) in enumerate(cases):
+        pre = f"c{ci}_"
+        groups = 1 if gs == -1 else k // gs
+        s = torch.randn(groups, n, generator=g)
+        zp = torch.randint(0, 1 << bits, (groups, n), generator=g, dtype=torch.int32)
+        out[pre + "meta"] = np.array([k, n, gs, bits, groups])
+        out[pre + "s"], out[pre + "zp"] = s.numpy(), zp.numpy()
+        out[pre + "s_marlin"] = mu.marlin_permute_scales(s, k, n, gs).numpy()
+        out[pre + "zp_marlin"] = mu.marlin_zero_points(zp, groups, n, bits).numpy()
+        packed = qu.pack_cols(zp, bits, groups, n)
+        out[pre + "zp_packed"] = packed.numpy()
+        out[pre + "zp_unpacked"] = qu.unpack_cols(packed, bits, groups, n).numpy()
+        # an AWQ checkpoint's zero points: interleaved for AWQ's dequantiser, then packed along the columns
+        inter = np.array([0, 2, 4, 6, 1, 3, 5, 7]) if bits == 4 else np.array([0, 2, 1, 3])
+        awq = zp.reshape(-1, len(inter))[:, inter].reshape(groups, n).contiguous()
+        awq_packed = qu.pack_cols(awq, bits, groups, n)
+        out[pre + "awq_zp_packed"] = awq_packed.numpy()
+        out[pre + "awq_zp_marlin"] = mu.awq_to_marlin_zero_points(awq_packed, groups, n, bits).numpy()
+    g_idx = torch.randint(0, 8, (256,), generator=g, dtype=torch.int32)
+    srt, order = mu.marlin_sort_g_idx(g_idx)
+    out["g_idx"], out["g_idx_sorted"], out["g_idx_order"] = g_idx.numpy(), srt.numpy(), order.numpy()
+    moe_s = torch.randn(3, 2, 128, generator=g)
+    out["moe_s"], out["moe_s_marlin"] = moe_s.numpy(), mu.marlin_moe_permute_scales(moe_s, 256, 128, 128).numpy()
+    for name in ("uint4", "uint8", "uint4b8", "uint8b128"):
+        out["id_" + name] = np.array([getattr(st.scalar_types, name).id], dtype=np.int64)
+    # the support predicates: (type, group size, has_zp) -> supported?
+    rows = []
+    for ti, name in enumerate(("uint4", "uint8", "uint4b8", "uint8b128")):
+        for gs in (-1, 32, 64, 128, 256):
+            for has_zp in (False, True):
+                rows.append([ti, gs, int(has_zp), int(mu.check_marlin_supported(getattr(st.scalar_types, name), gs, has_zp, 100))])
+    out["supported"] = np.array(rows)
+    shapes = []
+    for o, i, full, gs in ((4096, 4096, 4096, 128), (4100, 4096, 4096, 128), (4096, 4000, 4096, 128), (1024, 1792, 14336, 128),
+                           (1024, 1856, 14848, 128), (512, 1024, 8192, -1), (512, 1088, 8704, 64)):
+        ok, _ = mu.check_marlin_supports_shape(o, i, full, gs)
+        shapes.append([o, i, full, gs, int(ok)])
+    out["shapes"] = np.array(shapes)
+    out["num_cases"] = np.array([len(cases)])
+    np.savez_compressed(os.path.join(HERE, "marlin_utils_golden.npz"), **out)
+    print("marlin_utils_golden.npz:", len(out), "arrays")
+
+
 def load_reference_layers():
     """The reference's RMSNorm / SiluAndMul / RotaryEmbedding modules, loaded by path with the platform pinned to
     'not CUDA' so that only their forward_native code is used."""
@@ -314,11 +366,15 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["repack"]:
         make_repack(*mods)
         sys.exit(0)
+    if sys.argv[1:] == ["marlin_utils"]:
+        make_marlin_utils(*mods)
+        sys.exit(0)
     if sys.argv[1:] == ["glue"]:
         make_glue()
         sys.exit(0)
     make_marlin(*mods)
     make_repack(*mods)
+    make_marlin_utils(*mods)
     make_glue()
     ref = load_refcpu()
     make_attention(ref)

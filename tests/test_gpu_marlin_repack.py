@@ -158,3 +158,59 @@ def test_act_order_gemm_row_parallel_shard(m, dtype, tp, rank):
     if ref is not None:
         rc = ref.gptq_marlin_gemm(*args)
         assert float((c.float() - rc.float()).abs().max()) <= 1e-2 * float(rc.float().abs().max())
+
+
+@pytest.mark.parametrize("fmt,bits,gs,act_order", [("gptq", 4, 128, False), ("gptq", 8, -1, False), ("gptq", 4, 64, True),
+                                                  ("awq", 4, 128, False), ("awq", 8, 64, False)])
+def test_checkpoint_to_linear_through_the_host_helpers(fmt, bits, gs, act_order):
+    """What the reference's GPTQMarlinLinearMethod / AWQMarlinLinearMethod do at load time
+    (quantization/gptq_marlin.py process_weights_after_loading, awq_marlin.py), with this library's ops and its
+    marlin_utils on DEVICE tensors: checkpoint layout -> repack, permute scales, lay out zero points, sort g_idx ->
+    apply_*_marlin_linear. Checked against x @ w_ref of the oracle's quantiser (test_marlin_gemm.py:254: max-rel 4e-2)."""
+    from aphrodite_fork_b200 import marlin_utils as mu
+    k, n = 1024, 768
+    g = torch.Generator().manual_seed(bits + k + (gs if gs > 0 else 7))
+    w = (torch.randn(k, n, generator=g) * 0.05).to(torch.bfloat16)
+    x = torch.randn(3, 5, k, generator=g).to(torch.bfloat16).to(DEV)  # any leading shape
+    groups = 1 if gs == -1 else k // gs
+    if fmt == "gptq":
+        if act_order:  # random group membership: rows are quantised with the scale of g_idx[row]
+            g_idx = torch.randint(0, groups, (k,), generator=g, dtype=torch.int32)
+            order = torch.argsort(g_idx, stable=True)
+            w_sorted_ref, q_sorted, s, _ = mf.quantize(w[order], bits, gs, False)
+            inv = torch.argsort(order)
+            w_ref, q = w_sorted_ref[inv], q_sorted[inv]
+        else:
+            w_ref, q, s, _ = mf.quantize(w, bits, gs, False)
+        qweight = _dev(mf.gptq_pack(q.numpy().astype(np.uint32), bits))       # checkpoint: packed along K
+        scales = s.to(DEV)
+        qtype = mu.scalar_types.uint4b8 if bits == 4 else mu.scalar_types.uint8b128
+        mu.verify_marlin_supported(qtype, gs, has_zp=False)
+        mu.verify_marlin_supports_shape(n, k, k, gs)
+        if act_order:
+            g_sorted, sort_idx = mu.marlin_sort_g_idx(g_idx.to(DEV))
+        else:
+            g_sorted, sort_idx = mu.marlin_make_empty_g_idx(DEV), mu.marlin_make_empty_g_idx(DEV)
+        b = A.ops.gptq_marlin_repack(qweight, sort_idx, k, n, bits)
+        sm = mu.marlin_permute_scales(scales, k, n, gs)
+        out = mu.apply_gptq_marlin_linear(x, b, sm, mu.marlin_make_empty_zp(DEV), g_sorted, sort_idx, mu.marlin_make_workspace(n, DEV),
+                                          qtype, n, k, has_zp=False, is_k_full=mu.marlin_is_k_full(act_order, False))
+    else:
+        w_ref, q, s, zp = mf.quantize(w, bits, gs, True)
+        qweight = _dev(mf.awq_pack(q.numpy().astype(np.uint32), bits))        # checkpoint: packed along N, AWQ's interleave
+        inter = [0, 2, 4, 6, 1, 3, 5, 7] if bits == 4 else [0, 2, 1, 3]
+        qzeros = mu.pack_cols(zp.reshape(-1, len(inter))[:, inter].reshape(groups, n).contiguous().to(DEV), bits, groups, n)
+        qtype = mu.scalar_types.uint4 if bits == 4 else mu.scalar_types.uint8
+        mu.verify_marlin_supported(qtype, gs, has_zp=True)
+        b = A.ops.awq_marlin_repack(qweight, k, n, bits)
+        sm = mu.marlin_permute_scales(s.to(DEV), k, n, gs)
+        zm = mu.awq_to_marlin_zero_points(qzeros, groups, n, bits)
+        assert zm.is_cuda and sm.is_cuda
+        e = mu.marlin_make_empty_g_idx(DEV)
+        out = mu.apply_awq_marlin_linear(x, b, sm, zm, e, e, mu.marlin_make_workspace(n, DEV), qtype, n, k,
+                                         bias=torch.ones(n, dtype=torch.bfloat16, device=DEV))
+        out = out - 1
+    assert out.shape == (3, 5, n)
+    want = x.cpu().float() @ w_ref.float()
+    err = (out.cpu().float() - want).abs().mean() / want.abs().mean()
+    assert float(err) < 4e-2, float(err)
