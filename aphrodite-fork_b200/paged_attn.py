@@ -4,6 +4,7 @@ decode call with the reference's v1/v2 heuristic and scratch allocation, so that
 against the reference class runs against these kernels unchanged."""
 from __future__ import annotations
 
+from dataclasses import dataclass
 from typing import List, Optional, Tuple
 
 import torch
@@ -15,11 +16,19 @@ from . import _custom_ops as ops
 _PARTITION_SIZE = 512
 
 
+@dataclass
+class PagedAttentionMetadata:
+    """paged_attn.py:17-30: what a decode batch carries for the paged cache."""
+    seq_lens_tensor: Optional[torch.Tensor]  # (batch,) tokens seen so far per sequence
+    max_decode_seq_len: int                  # 0 for a prefill-only batch
+    block_tables: Optional[torch.Tensor]     # (batch, max_blocks_per_seq) physical block of every logical block
+
+
 class PagedAttention:
 
     @staticmethod
     def get_supported_head_sizes() -> List[int]:
-        return [32, 64, 80, 96, 112, 128, 192, 256]
+        return [32, 64, 80, 96, 112, 120, 128, 192, 256]
 
     @staticmethod
     def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int, head_size: int) -> Tuple[int, ...]:
@@ -84,3 +93,20 @@ class PagedAttention:
                                    kv_cache_dtype, k_scale, v_scale, tp_rank, blocksparse_local_blocks,
                                    blocksparse_vert_stride, blocksparse_block_size, blocksparse_head_sliding_step)
         return output
+
+    @staticmethod
+    def forward_prefix(*args, **kwargs) -> torch.Tensor:
+        """The reference's prefix-prefill path (paged_attn.py:193-230) is a Triton kernel outside the decode hot path this
+        library replaces (out of scope); in an overlay deployment the reference's own class serves it."""
+        raise NotImplementedError("forward_prefix (prefix prefill) is not part of the decode hot path this library serves")
+
+    @staticmethod
+    def swap_blocks(src_kv_cache: torch.Tensor, dst_kv_cache: torch.Tensor, src_to_dst: torch.Tensor) -> None:
+        """paged_attn.py:233-244: K then V planes of a [2, num_blocks, ...] cache."""
+        ops.swap_blocks(src_kv_cache[0], dst_kv_cache[0], src_to_dst)
+        ops.swap_blocks(src_kv_cache[1], dst_kv_cache[1], src_to_dst)
+
+    @staticmethod
+    def copy_blocks(kv_caches: List[torch.Tensor], src_to_dists: torch.Tensor) -> None:
+        """paged_attn.py:247-254."""
+        ops.copy_blocks([kv[0] for kv in kv_caches], [kv[1] for kv in kv_caches], src_to_dists)

@@ -6,7 +6,7 @@ __path__.insert(0, _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.absp
 
 from ._loader import load, library_paths, c_api  # noqa: E402,F401
 from . import _custom_ops as ops  # noqa: E402,F401
-from .paged_attn import PagedAttention  # noqa: E402,F401
+from .paged_attn import PagedAttention, PagedAttentionMetadata  # noqa: E402,F401
 from . import tp  # noqa: E402,F401
 from . import marlin_utils  # noqa: E402,F401
 from .tp import TPGroup, shard_heads, shard_marlin_weight  # noqa: E402,F401

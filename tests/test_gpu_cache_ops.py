@@ -150,3 +150,39 @@ def test_swap_blocks_inside_one_tensor_with_overlapping_runs():
     ops.swap_blocks(dev, dev, mapping)
     torch.cuda.synchronize()
     assert torch.equal(_bits(dev.cpu()), _bits(want))
+
+
+def test_paged_attention_class_swap_and_copy_blocks():
+    """The reference's PagedAttention.swap_blocks / copy_blocks (attention/ops/paged_attn.py:233-254) take whole
+    [2, num_blocks, ...] caches: K plane, then V plane, through the same ops."""
+    import aphrodite_fork_b200 as A
+    nb, kvh, d, bs = 24, 4, 64, 16
+    shape = A.PagedAttention.get_kv_cache_shape(nb, bs, kvh, d)
+    assert shape == (2, nb, bs * kvh * d)
+    src = synth.tensor(shape, 21, torch.bfloat16, 1.0)
+    dst = synth.tensor(shape, 22, torch.bfloat16, 1.0)
+    mapping = torch.tensor([[1, 5], [2, 6], [9, 0]], dtype=torch.int64)
+    want = dst.clone()
+    for s_, d_ in mapping.tolist():
+        want[:, d_] = src[:, s_]
+    d_dev = dst.cuda()
+    A.PagedAttention.swap_blocks(src.cuda(), d_dev, mapping)
+    torch.cuda.synchronize()
+    assert torch.equal(_bits(d_dev.cpu()), _bits(want))
+    # copy_blocks: the same (src, dst) pairs applied inside every layer's cache
+    layers = [synth.tensor(shape, 30 + i, torch.bfloat16, 1.0) for i in range(3)]
+    wants = [l.clone() for l in layers]
+    pairs = torch.tensor([[0, 7], [0, 8], [3, 4]], dtype=torch.int64)
+    for w in wants:
+        for s_, d_ in pairs.tolist():
+            w[:, d_] = w[:, s_]
+    devs = [l.cuda() for l in layers]
+    A.PagedAttention.copy_blocks(devs, pairs.cuda())
+    torch.cuda.synchronize()
+    for got, w in zip(devs, wants):
+        assert torch.equal(_bits(got.cpu()), _bits(w))
+    k, v = A.PagedAttention.split_kv_cache(devs[0], kvh, d)
+    assert k.shape == (nb, kvh, d // 8, bs, 8) and v.shape == (nb, kvh, d, bs)
+    with pytest.raises(NotImplementedError):
+        A.PagedAttention.forward_prefix()
+    assert 120 in A.PagedAttention.get_supported_head_sizes()
