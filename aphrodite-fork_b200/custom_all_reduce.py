@@ -11,7 +11,8 @@ from __future__ import annotations
 
 import ctypes
 import os
-from typing import Optional
+from contextlib import contextmanager
+from typing import Optional, Union
 
 import torch
 import torch.distributed as dist
@@ -149,3 +150,104 @@ class OneShotAllReduce:
             st = self.lib.aph_all_reduce_add_rms_norm(*head, *tail)
         if st != 0:
             raise RuntimeError(self.lib.aph_b200_last_error().decode())
+
+
+def is_weak_contiguous(inp: torch.Tensor) -> bool:
+    """Dense in memory, whatever the stride order (the reference's helper, custom_all_reduce.py:37-42)."""
+    return inp.is_contiguous() or (inp.untyped_storage().nbytes() - inp.storage_offset() * inp.element_size()
+                                   == inp.numel() * inp.element_size())
+
+
+class CustomAllreduce:
+    """The reference's communicator interface (distributed/device_communicators/custom_all_reduce.py:45-304) on top of
+    OneShotAllReduce, for code written against `ca_comm.custom_all_reduce(x)` / `with ca_comm.capture():`. Same
+    constructor arguments, same `disabled` convention (anything that rules the peer-memory path out leaves the object
+    disabled instead of raising; callers then fall back to NCCL), same eligibility rule.
+
+    What differs underneath: the buffers are torch symmetric memory, not hand-exchanged CUDA-IPC handles, and the
+    kernels PUSH from the caller's tensor, so nothing has to be registered - `registered=` and `register_graph_buffers()`
+    are accepted and do nothing, and a warm-up call inside `capture()` performs the real reduction (the reference
+    returns an uninitialised tensor there)."""
+
+    _SUPPORTED_WORLD_SIZES = [2, 4, 6, 8]
+
+    def __init__(self, group: dist.ProcessGroup, device: Union[int, str, torch.device], max_size: int = 8192 * 1024) -> None:
+        self._IS_CAPTURING = False
+        self.disabled = True
+        self.disabled_reason: Optional[str] = None
+        self._impl: Optional[OneShotAllReduce] = None
+        self.group = group
+        self.max_size = max_size
+        if isinstance(device, int):
+            device = torch.device(f"cuda:{device}")
+        elif isinstance(device, str):
+            device = torch.device(device)
+        self.device = device
+        self.rank = dist.get_rank(group=group)
+        self.world_size = dist.get_world_size(group=group)
+        self.fully_connected = True  # B200 boards: every GPU reaches every peer through NVSwitch
+        if self.world_size == 1:
+            self.disabled_reason = "single GPU"
+            return
+        if self.world_size not in self._SUPPORTED_WORLD_SIZES:
+            self.disabled_reason = f"unsupported world size {self.world_size} (supported: {self._SUPPORTED_WORLD_SIZES})"
+            return
+        if device.type != "cuda" or not torch.cuda.is_available():
+            self.disabled_reason = "not a CUDA device"
+            return
+        try:
+            self._impl = OneShotAllReduce(group, device, max_size)
+        except Exception as e:  # no peer access / no symmetric memory for this group: stay disabled like the reference
+            self.disabled_reason = f"{type(e).__name__}: {e}"
+            return
+        self.disabled = False
+
+    @contextmanager
+    def capture(self):
+        """Wrap CUDA-graph capture (and its warm-up) of code that calls custom_all_reduce."""
+        try:
+            self._IS_CAPTURING = True
+            yield
+        finally:
+            self._IS_CAPTURING = False
+            if not self.disabled:
+                self.register_graph_buffers()
+
+    def register_graph_buffers(self) -> None:
+        """Nothing to register: the kernels read the caller's tensor locally and write peers through symmetric memory."""
+
+    def should_custom_ar(self, inp: torch.Tensor) -> bool:
+        if self.disabled:
+            return False
+        inp_size = inp.numel() * inp.element_size()
+        if inp_size % 16 != 0 or not is_weak_contiguous(inp):
+            return False
+        if inp.dtype not in _DT or inp.data_ptr() % 16 != 0 or inp_size == 0:
+            return False
+        if self.world_size == 2 or self.fully_connected:
+            return inp_size < self.max_size
+        return False
+
+    @staticmethod
+    def _flat(t: torch.Tensor) -> torch.Tensor:
+        return t if t.is_contiguous() else t.as_strided((t.numel(),), (1,), t.storage_offset())
+
+    def all_reduce(self, inp: torch.Tensor, *, out: Optional[torch.Tensor] = None, registered: bool = False) -> torch.Tensor:
+        """Out-of-place all-reduce (sum). `registered` is accepted for compatibility (see the class comment)."""
+        if out is None:
+            out = torch.empty_like(inp)  # same strides as inp: element i of the storage is element i of the result
+        self._impl.all_reduce(self._flat(inp), self._flat(out))
+        return out
+
+    def custom_all_reduce(self, input: torch.Tensor) -> Optional[torch.Tensor]:
+        """None when this path does not serve the message (disabled, too large, misaligned): the caller uses NCCL."""
+        if self.disabled or not self.should_custom_ar(input):
+            return None
+        return self.all_reduce(input, registered=self._IS_CAPTURING)
+
+    def close(self) -> None:
+        self._impl = None
+        self.disabled = True
+
+    def __del__(self):
+        self.close()

@@ -285,6 +285,47 @@ def _ar_worker(rank, world, port, q):
             bad.append(("graph result wrong",))
         del g
         torch.cuda.synchronize()
+        # the adapter with the reference's communicator interface (custom_all_reduce.py:45-304): eager, warm-up inside
+        # capture(), and a captured graph; ineligible messages come back as None
+        from aphrodite_fork_b200.custom_all_reduce import CustomAllreduce
+        ca = CustomAllreduce(dist.group.WORLD, dev)
+        if ca.disabled:
+            bad.append(("CustomAllreduce disabled", ca.disabled_reason))
+        else:
+            x = torch.randn(16, 4096, device=dev, generator=gen).to(torch.bfloat16)
+            parts = [torch.empty_like(x) for _ in range(world)]
+            dist.all_gather(parts, x)
+            want = parts[0].float()
+            for p in parts[1:]:
+                want = want + p.float()
+            want = want.to(torch.bfloat16)
+            got = ca.custom_all_reduce(x)
+            if got is None or got.data_ptr() == x.data_ptr() or not torch.equal(got, want):
+                bad.append(("CustomAllreduce eager",))
+            xt = x.t()  # dense, permuted strides: weakly contiguous
+            got_t = ca.custom_all_reduce(xt)
+            if got_t is None or got_t.shape != xt.shape or not torch.equal(got_t, want.t()):
+                bad.append(("CustomAllreduce weakly contiguous",))
+            if ca.custom_all_reduce(torch.ones(3, device=dev)) is not None or ca.custom_all_reduce(
+                    torch.ones(8192 * 1024 // 2, dtype=torch.bfloat16, device=dev)) is not None:
+                bad.append(("CustomAllreduce served an ineligible message",))
+            with ca.capture():
+                s2 = torch.cuda.Stream()
+                s2.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(s2):
+                    warm = ca.custom_all_reduce(x)
+                torch.cuda.current_stream().wait_stream(s2)
+                torch.cuda.synchronize()
+                g2 = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g2):
+                    y2 = ca.custom_all_reduce(x)
+            g2.replay()
+            torch.cuda.synchronize()
+            if not torch.equal(warm, want) or not torch.equal(y2, want):
+                bad.append(("CustomAllreduce under capture",))
+            del g2
+            ca.close()
+        torch.cuda.synchronize()
         q.put((rank, bad))
     except Exception:
         import traceback

@@ -187,6 +187,62 @@ def test_one_shot_all_reduce_eligibility_rules():
         del os.environ["APH_AR_LIMIT_BYTES"]
 
 
+def test_all_reduce_mode_policy_and_the_reference_style_communicator():
+    """Host policy of custom_all_reduce.py: LL lines up to 1 MiB (512 KiB at two ranks), two-shot above, environment
+    overrides; and CustomAllreduce, the adapter with the reference's interface (custom_all_reduce.py:45-304): `disabled`
+    instead of exceptions, custom_all_reduce() -> None when the message is not served."""
+    from aphrodite_fork_b200.custom_all_reduce import CustomAllreduce, OneShotAllReduce, is_weak_contiguous
+    for k in ("APH_AR_MODE", "APH_AR_TWO_SHOT_BYTES", "APH_AR_LIMIT_BYTES"):
+        os.environ.pop(k, None)
+    ar = object.__new__(OneShotAllReduce)
+    ar.max_size, ar.multicast_ptr, ar.ll_max_bytes, ar.ll_max_passes = 8 << 20, 0, 2 << 20, 512
+    ar.world_size = 8
+    assert ar.mode(16 << 10) == "ll" and ar.mode(1 << 20) == "ll" and ar.mode((1 << 20) + 16) == "two_shot"
+    assert ar.mode(1 << 20, rows=64, hidden=8192) == "ll"            # 64 rows x 2 passes of 512 vectors
+    assert ar.mode(1 << 20, rows=4096, hidden=128) == "two_shot"     # 4096 passes do not fit the 512 line rows
+    ar.world_size = 2
+    assert ar.mode(512 << 10) == "ll" and ar.mode(1 << 20) == "one_shot"
+    os.environ["APH_AR_MODE"] = "multimem"
+    assert ar.mode(1 << 20) == "one_shot"                            # no multicast mapping: the request is ignored
+    ar.multicast_ptr = 0x1000
+    assert ar.mode(1 << 20) == "multimem"
+    os.environ["APH_AR_MODE"] = "two_shot"
+    assert ar.mode(16) == "two_shot"
+    os.environ.pop("APH_AR_MODE")
+    os.environ["APH_AR_TWO_SHOT_BYTES"] = "0"
+    assert ar.mode(4 << 20) == "one_shot"
+    os.environ.pop("APH_AR_TWO_SHOT_BYTES")
+
+    t = torch.arange(24.0).reshape(4, 6)
+    assert is_weak_contiguous(t) and is_weak_contiguous(t.t()) and not is_weak_contiguous(t.t()[:2])
+    import torch.distributed as dist
+    created = not dist.is_initialized()
+    if created:
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(29600 + os.getpid() % 200))
+        dist.init_process_group("gloo", rank=0, world_size=1)
+    try:
+        ca = CustomAllreduce(dist.group.WORLD, "cpu")
+        assert ca.disabled and ca.disabled_reason == "single GPU"
+        assert ca.custom_all_reduce(torch.ones(16)) is None and not ca.should_custom_ar(torch.ones(16))
+        with ca.capture():
+            assert ca._IS_CAPTURING
+        assert not ca._IS_CAPTURING
+        ca.close()
+    finally:
+        if created:
+            dist.destroy_process_group()
+    # the eligibility rule of an enabled communicator (metadata only)
+    ca = object.__new__(CustomAllreduce)
+    ca.disabled, ca.world_size, ca.fully_connected, ca.max_size, ca._impl = False, 8, True, 8192 * 1024, None
+    assert ca.should_custom_ar(torch.zeros(64, 8192, dtype=torch.bfloat16))
+    assert not ca.should_custom_ar(torch.zeros(512, 8192, dtype=torch.bfloat16))   # == max_size: the reference's rule is "<"
+    assert not ca.should_custom_ar(torch.zeros(3, 4, dtype=torch.bfloat16))        # 24 bytes
+    assert not ca.should_custom_ar(torch.zeros(64, 8, dtype=torch.int32))          # not a floating type this path sums
+    assert ca.should_custom_ar(torch.zeros(64, 128, dtype=torch.bfloat16).t())     # dense with permuted strides
+    ca.disabled = True
+    assert not ca.should_custom_ar(torch.zeros(64, 8192, dtype=torch.bfloat16))
+
+
 def test_decode_layer_shards_partition_the_unsharded_layer():
     """DecodeLayer.shard_of (decode.py): the ranks' shards of an unsharded layer - q / k / v and gate / up split
     separately (linear.py:474-484), row-parallel K splits (:1279-1283), kv heads split or replicated
