@@ -35,7 +35,7 @@
 // until their flags show this call, adds in rank order in fp32, rounds once and pushes the sum to every rank's result
 // lines, (C2) everybody polls its result lines. Twice the bytes on the wire of two-shot, but two one-way NVLink latencies
 // instead of two barriers of about 4 us each: the choice up to AR_LL_MAX_BYTES. The lines live in their own region
-// behind the slots (zeroed once by the host; a flag never repeats, and a line is only rewritten after its reader has
+// behind the slots (zeroed once by the host; a flag is never 0 and repeats only after 2^32 calls, and a line is only rewritten after its reader has
 // moved on: a rank can push call n + 1 only after it has received every owner's results of call n, which the owners send
 // after reading all lines of call n). Same rank-order sums as one-shot / two-shot: bit-identical to them.
 // Layout of a rank's buffer (from the host: torch symmetric memory / CUDA IPC): [ 4 KiB flags | 2 halves x world slots
@@ -211,6 +211,7 @@ __global__ void __launch_bounds__(512, 1)
   // Read AFTER the wait: under programmatic dependent launch this grid may start while an earlier all-reduce of the same
   // stream is still running (every kernel of the step triggers its dependents at once), and that one updates the counters.
   const uint32_t call = counters[blockIdx.x] + 1;
+  const uint32_t ll_flag = call ? call : 0x80000000u;  // never 0: that is what a line that was never written holds
   const int64_t half_off = AR_SIGNAL_BYTES + (int64_t)(call & 1) * WORLD * slot_bytes;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x, first = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint8_t* mine = s_bufs[rank] + half_off;
@@ -248,17 +249,17 @@ __global__ void __launch_bounds__(512, 1)
     // (A) vectors owned elsewhere go to their owner's receive lines
     if (owner != rank)
       for (int64_t i = first; i < n_vec; i += stride)
-        ll_store(s_bufs[owner] + ll_off + rank * src_stride + ((i >> 9) * CS + lj) * 32, reinterpret_cast<const V*>(in)[i], call);
+        ll_store(s_bufs[owner] + ll_off + rank * src_stride + ((i >> 9) * CS + lj) * 32, reinterpret_cast<const V*>(in)[i], ll_flag);
     // (C1) the owner adds in rank order as the lines arrive and sends the rounded sum to every rank's result lines
     if (owner == rank)
       for (int64_t i = first; i < n_vec; i += stride) {
-        const V o = ll_sum<T, WORLD>(reinterpret_cast<const V*>(in)[i], s_bufs[rank] + ll_off + ((i >> 9) * CS + lj) * 32, src_stride, rank, call);
+        const V o = ll_sum<T, WORLD>(reinterpret_cast<const V*>(in)[i], s_bufs[rank] + ll_off + ((i >> 9) * CS + lj) * 32, src_stride, rank, ll_flag);
 #pragma unroll
-        for (int r = 0; r < WORLD; ++r) ll_store(s_bufs[r] + ll_off + ar_ll_recv_bytes(WORLD) + i * 32, o, call);
+        for (int r = 0; r < WORLD; ++r) ll_store(s_bufs[r] + ll_off + ar_ll_recv_bytes(WORLD) + i * 32, o, ll_flag);
       }
     // (C2)
     for (int64_t i = first; i < n_vec; i += stride)
-      reinterpret_cast<V*>(out)[i] = ll_load(s_bufs[rank] + ll_off + ar_ll_recv_bytes(WORLD) + i * 32, call);
+      reinterpret_cast<V*>(out)[i] = ll_load(s_bufs[rank] + ll_off + ar_ll_recv_bytes(WORLD) + i * 32, ll_flag);
   } else {
     const int owner = (int)threadIdx.x * WORLD / (int)blockDim.x;
     // (A) my partial into slot 0 of my own buffer
@@ -325,6 +326,7 @@ __global__ void __launch_bounds__(512, 1)
   __syncthreads();
   pdl_wait();
   const uint32_t call = counters[blockIdx.x] + 1;  // after the wait, see one_shot_all_reduce_kernel
+  const uint32_t ll_flag = call ? call : 0x80000000u;  // never 0: that is what a line that was never written holds
   const int64_t half_off = AR_SIGNAL_BYTES + (int64_t)(call & 1) * WORLD * slot_bytes;
   const uint8_t* mine = s_bufs[rank] + half_off;
   // two-shot, multimem, LL: the owner of every vector this thread handles
@@ -338,15 +340,15 @@ __global__ void __launch_bounds__(512, 1)
       for (int i = threadIdx.x, ps = 0; i < nvec; i += blockDim.x, ++ps)
         if (owner != rank)
           ll_store(s_bufs[owner] + ll_off + rank * src_stride + ((int64_t)(row * passes + ps) * CS + lj) * 32,
-                   reinterpret_cast<const V*>(x)[(int64_t)row * nvec + i], call);
+                   reinterpret_cast<const V*>(x)[(int64_t)row * nvec + i], ll_flag);
     if (owner == rank)
       for (int row = blockIdx.x; row < rows; row += gridDim.x)
         for (int i = threadIdx.x, ps = 0; i < nvec; i += blockDim.x, ++ps) {
           const int64_t lrow = (int64_t)row * passes + ps;
           const V o = ll_sum<T, WORLD>(reinterpret_cast<const V*>(x)[(int64_t)row * nvec + i], s_bufs[rank] + ll_off + (lrow * CS + lj) * 32,
-                                       src_stride, rank, call);
+                                       src_stride, rank, ll_flag);
 #pragma unroll
-          for (int r = 0; r < WORLD; ++r) ll_store(s_bufs[r] + ll_off + ar_ll_recv_bytes(WORLD) + (lrow * 512 + threadIdx.x) * 32, o, call);
+          for (int r = 0; r < WORLD; ++r) ll_store(s_bufs[r] + ll_off + ar_ll_recv_bytes(WORLD) + (lrow * 512 + threadIdx.x) * 32, o, ll_flag);
         }
   }
   // (A) push this CTA's rows: to everybody, or (two-shot) to the owner of each vector
@@ -399,7 +401,7 @@ __global__ void __launch_bounds__(512, 1)
       if (i < nvec) {
         const int64_t idx = (int64_t)row * nvec + i;
         // the all-reduce's output, rounded to T: summed here in rank order (one-shot) or by the vector's owner (two-shot)
-        const V sum = LL         ? ll_load(s_bufs[rank] + ll_off + ar_ll_recv_bytes(WORLD) + (((int64_t)row * passes + it) * 512 + threadIdx.x) * 32, call)
+        const V sum = LL         ? ll_load(s_bufs[rank] + ll_off + ar_ll_recv_bytes(WORLD) + (((int64_t)row * passes + it) * 512 + threadIdx.x) * 32, ll_flag)
                       : MULTIMEM ? __ldcv(reinterpret_cast<const V*>(mine + slot_bytes) + idx)
                       : TWO_SHOT ? __ldcv(reinterpret_cast<const V*>(mine + owner * slot_bytes) + idx)
                                  : ar_sum_slots<T, WORLD>(mine, slot_bytes, idx);
