@@ -683,6 +683,9 @@ def run_ours(args):
                                       + ", no collective in attention (llama.py:118-127)",
                        "l2": f"{npools} FP8 KV pools of {pool_bytes >> 20} MiB per rank in rotation (>= 1 GiB), block tables = random "
                              "permutation of distinct blocks: inputs larger than the 126 MB L2",
+                       "timing": "CUDA events on the launching stream around ONE graph replay of the K steps, max over ranks; "
+                                 "about 1 ms of device-side spinning is queued before the opening event so that the host's "
+                                 "graph-launch latency is not inside the timed region",
                        "kv_bytes_per_step": per_step_bytes, "kv_bytes_per_step_per_gpu": pool_bytes},
             "roofline": {"bound": "hbm", "achieved": round(per_gpu, 2), "peak": peak, "unit": "GB/s",
                          "frac": round(per_gpu / peak, 4), "traffic": NCU_TRAFFIC_BYTES if world == 1 else None,
