@@ -117,6 +117,11 @@ def _tp_worker(rank, world, port, result_q):
         full = a.float() @ w_ref.float()
         ok_col = torch.allclose(torch.cat(parts, dim=1), full, rtol=1e-5, atol=1e-4)
         ok_row = torch.allclose(y_row, full, rtol=1e-4, atol=1e-3)
+        # the reference-style communicator on a CPU group of 2: stays disabled (callers then use the group's all_reduce),
+        # exactly like the reference without its custom all-reduce library
+        from aphrodite_fork_b200.custom_all_reduce import CustomAllreduce
+        ca = CustomAllreduce(dist.group.WORLD, "cpu")
+        ok_row = ok_row and ca.disabled and ca.disabled_reason == "not a CUDA device" and ca.custom_all_reduce(y_row) is None
         result_q.put((rank, ok_col, ok_row))
     finally:
         dist.destroy_process_group()
